@@ -1,0 +1,196 @@
+/*
+ * mslam_b200.h -- C ABI of the B200-native ORB + Hamming-matching hot path.
+ *
+ * This is the drop-in boundary for modular-slam's feature front-end.  Every entry point cites the
+ * reference interface it replaces (paths relative to the reference repository root):
+ *
+ *   IFeatureDetector<RgbFrame,uint8_t,32>::detect   src/lib/modular_slam/include/modular_slam/frontend/feature/feature_interface.hpp:50-56
+ *     implemented by OrbOpenCvDetector::Pimpl::detect  src/lib/modular_slam/orb_feature.cpp:33-65
+ *     (toGrayScale src/lib/modular_slam/frame.cpp:6-27, then cv::ORB::create(1000)->detectAndCompute, orb_feature.cpp:25,40)
+ *   IFeatureMatcher<uint8_t,32>::match              feature_interface.hpp:62-70
+ *     implemented by OrbOpenCvMatcher::Pimpl::match    src/lib/modular_slam/orb_feature.cpp:84-117
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no allocation crosses the boundary (caller provides capacity, gets a count);
+ *   - every function returns MSLAM_B200_OK (0) or a negative mslam_b200_status;
+ *   - "host" entry points take host pointers (pageable or pinned), run synchronously and include the
+ *     host<->device copies; "_dev" entry points take device pointers, enqueue on the context's stream and
+ *     return immediately (call mslam_b200_synchronize, or order further work on the same stream);
+ *   - there is no CPU fallback: without a CUDA device mslam_b200_create fails with MSLAM_B200_E_CUDA.
+ *   - a context is single-threaded (the reference caller is: slam.hpp:74-99), one context per thread/GPU.
+ */
+#ifndef MSLAM_B200_H_
+#define MSLAM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define MSLAM_B200_API __attribute__((visibility("default")))
+#else
+#define MSLAM_B200_API
+#endif
+
+#define MSLAM_B200_VERSION 100 /* major*100 + minor */
+#define MSLAM_B200_MAX_LEVELS 16
+#define MSLAM_B200_DESC_BYTES 32
+
+typedef enum mslam_b200_status
+{
+    MSLAM_B200_OK = 0,
+    MSLAM_B200_E_INVALID = -1,  /* bad argument (null pointer, size outside the context's limits, ...) */
+    MSLAM_B200_E_CUDA = -2,     /* CUDA runtime error or no device; see mslam_b200_last_cuda_error */
+    MSLAM_B200_E_CAPACITY = -3, /* an output (or internal candidate list) did not fit; counts report the need */
+    MSLAM_B200_E_NOMEM = -4
+} mslam_b200_status;
+
+typedef struct mslam_b200_ctx mslam_b200_ctx;
+
+/* Defaults (mslam_b200_default_config) are the reference's hard-coded values:
+ * cv::ORB::create(1000) => nfeatures 1000, scaleFactor 1.2f, nlevels 8, edgeThreshold 31, fastThreshold 20,
+ * HARRIS_SCORE, patchSize 31 (orb_feature.cpp:25); ratio 0.7 (orb_feature.cpp:101). */
+typedef struct mslam_b200_config
+{
+    int struct_size;    /* = sizeof(mslam_b200_config), for forward compatibility */
+    int device;         /* CUDA device ordinal */
+    int max_width;      /* largest frame the context accepts */
+    int max_height;
+    int max_batch;      /* frames per detect_batch call / frame pairs per match batch */
+    int nfeatures;      /* ORB nfeatures */
+    int nlevels;        /* ORB nlevels (<= MSLAM_B200_MAX_LEVELS) */
+    float scale_factor; /* ORB scaleFactor */
+    int fast_threshold; /* FAST threshold */
+    int edge_threshold; /* ORB edgeThreshold (border filter); patch size stays 31, so must be >= 31 */
+    int max_keypoints;  /* per-frame output capacity inside the context (retainBest keeps ties, so the count can
+                           exceed nfeatures); 0 => nfeatures + nfeatures/4 + 64 */
+    int max_descriptors;/* largest descriptor set per side in the matcher; 0 => max_keypoints */
+    double ratio;       /* Lowe ratio of the kNN matcher, compared exactly as the reference does:
+                           (double)(float)d0 < ratio * (double)(float)d1 */
+    void* stream;       /* optional cudaStream_t to run on (e.g. the caller's); NULL => context-owned stream */
+} mslam_b200_config;
+
+/* what cv::KeyPoint carries out of detectAndCompute (the reference interface keeps only pt, orb_feature.cpp:52-58) */
+typedef struct mslam_b200_keypoint
+{
+    float x, y;     /* level-0 pixel coordinates: (float)x_l * scale_l */
+    float size;     /* 31 * scale_l */
+    float angle;    /* degrees, cv::fastAtan2 of the intensity centroid */
+    float response; /* Harris response */
+    int octave;     /* pyramid level */
+} mslam_b200_keypoint;
+
+/* ---- library / context -------------------------------------------------------------------------------------- */
+MSLAM_B200_API int mslam_b200_version(void);
+MSLAM_B200_API const char* mslam_b200_status_string(int status);
+MSLAM_B200_API void mslam_b200_default_config(mslam_b200_config* cfg);
+MSLAM_B200_API int mslam_b200_create(const mslam_b200_config* cfg, mslam_b200_ctx** out_ctx);
+MSLAM_B200_API void mslam_b200_destroy(mslam_b200_ctx* ctx);
+MSLAM_B200_API int mslam_b200_set_stream(mslam_b200_ctx* ctx, void* cuda_stream);
+MSLAM_B200_API int mslam_b200_synchronize(mslam_b200_ctx* ctx);
+/* text of the last CUDA error seen by this context ("" if none) */
+MSLAM_B200_API const char* mslam_b200_last_cuda_error(mslam_b200_ctx* ctx);
+/* number of kernels this library has launched on the context since creation (bench.py "gpu_launches") */
+MSLAM_B200_API long long mslam_b200_launch_count(mslam_b200_ctx* ctx);
+/* pinned host memory for callers that want full-speed H2D/D2H through the host entry points */
+MSLAM_B200_API int mslam_b200_host_alloc(void** ptr, size_t bytes);
+MSLAM_B200_API int mslam_b200_host_free(void* ptr);
+/* per-level geometry the context derived (cv::ORB layer sizes / scales / feature budget); arrays of nlevels */
+MSLAM_B200_API int mslam_b200_level_geometry(mslam_b200_ctx* ctx, int width, int height, int* w, int* h, float* scale,
+                                             int* n_per_level);
+
+/* ---- detection: replaces IFeatureDetector::detect / OrbOpenCvDetector::detect (orb_feature.cpp:33-65) ---------- */
+/* One frame.  `bgr` is RgbFrame::data (3 interleaved bytes per pixel, weights applied in memory order exactly as
+ * toGrayScale does, frame.cpp:15-19); row stride in bytes (>= 3*width).  Keypoints come out in canonical order
+ * (octave, y, x); OpenCV's own order inside a level is a std::nth_element artefact.  n_out receives the count
+ * found; MSLAM_B200_E_CAPACITY if it exceeds `capacity` (the first `capacity` are still written). */
+MSLAM_B200_API int mslam_b200_detect(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int height, int stride_bytes,
+                                     mslam_b200_keypoint* out_kp, uint8_t* out_desc /* capacity x 32 */, int capacity,
+                                     int* n_out);
+/* A batch of independent frames of one size (frames[i] = pointer to frame i).  Outputs are [n_frames][capacity]. */
+MSLAM_B200_API int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width,
+                                           int height, int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc,
+                                           int capacity, int* n_out /* [n_frames] */);
+/* Device-resident variant: d_bgr is [n_frames][height][width][3] dense in device memory; outputs are device arrays
+ * [n_frames][capacity] (keypoints, descriptors) and [n_frames] (counts, un-clamped).  Asynchronous. */
+MSLAM_B200_API int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames, int width,
+                                               int height, mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity,
+                                               int* d_counts);
+/* Describe GIVEN keypoints (parity aid: "descriptors bit-exact given identical keypoints").  kp[].x/.y/.octave are
+ * read (level-0 coordinates, as detect returns them); angle is recomputed and written back together with desc. */
+MSLAM_B200_API int mslam_b200_describe(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int height, int stride_bytes,
+                                       mslam_b200_keypoint* kp, int n_kp, uint8_t* out_desc);
+
+/* ---- matching: replaces IFeatureMatcher::match / OrbOpenCvMatcher::match (orb_feature.cpp:84-117) -------------- */
+/* match(from, to): kNN (k=2) with query = `to`, train = `from`, ties -> lower train index; keep the best iff
+ * d0 < ratio*d1; emit {fromIndex = trainIdx, toIndex = queryIdx} in ascending toIndex (orb_feature.cpp:96-114).
+ * Strides are in bytes so the adapter can pass &v[0].descriptor[0] with stride sizeof(OrbKeypoint) = 64, as the
+ * reference itself does (orb_feature.cpp:88-91).  n_from < 2 or n_to < 1 => zero matches (reference: undefined). */
+MSLAM_B200_API int mslam_b200_match_knn_ratio(mslam_b200_ctx* ctx, const uint8_t* from, int n_from, int from_stride,
+                                              const uint8_t* to, int n_to, int to_stride, uint64_t* out_from_idx,
+                                              uint64_t* out_to_idx, int* out_dist /* may be NULL */, int capacity,
+                                              int* n_out);
+/* Raw k=2 result per query row (cv::BFMatcher::knnMatch(query, train, 2)); -1 where train has fewer rows. */
+MSLAM_B200_API int mslam_b200_knn2(mslam_b200_ctx* ctx, const uint8_t* query, int n_query, int query_stride,
+                                   const uint8_t* train, int n_train, int train_stride, int* idx0, int* dist0, int* idx1,
+                                   int* dist1);
+/* BFMatcher(NORM_HAMMING, crossCheck=true).match(query, train): mutual nearest neighbours, lowest-index argmin on
+ * both sides, ascending query index (BASELINE.json configs[2]; not used by the reference itself). */
+MSLAM_B200_API int mslam_b200_match_crosscheck(mslam_b200_ctx* ctx, const uint8_t* query, int n_query, int query_stride,
+                                               const uint8_t* train, int n_train, int train_stride, int* out_query_idx,
+                                               int* out_train_idx, int* out_dist, int capacity, int* n_out);
+/* Batches of independent (from, to) pairs, dense [n_pairs][capacity][32] descriptor blocks and [n_pairs] counts.
+ * Host variant copies in/out; outputs [n_pairs][capacity] (+ [n_pairs] match counts).  mode 0 = knn+ratio
+ * (out_a = fromIndex, out_b = toIndex), mode 1 = cross-check with query = `to`, train = `from`
+ * (out_a = trainIdx, out_b = queryIdx). */
+MSLAM_B200_API int mslam_b200_match_batch(mslam_b200_ctx* ctx, int mode, const uint8_t* from, const int* n_from,
+                                          const uint8_t* to, const int* n_to, int n_pairs, int capacity, int* out_a,
+                                          int* out_b, int* out_dist, int* n_out);
+MSLAM_B200_API int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, const uint8_t* d_from, const int* d_n_from,
+                                              const uint8_t* d_to, const int* d_n_to, int n_pairs, int capacity,
+                                              int* d_out_a, int* d_out_b, int* d_out_dist, int* d_n_out);
+
+/* ---- keyframe-database scoring (loop-candidate verification; rgbd_feature_frontend.cpp:499-533 intent) --------- */
+/* score[q][k] = |match(from = query frame q, to = keyframe k)| with the knn+ratio semantics above.
+ * Descriptor blocks are device arrays [n][cap][32] with per-frame counts; scores is a device array
+ * [n_query_frames][n_keyframes] (int32).  Asynchronous. */
+MSLAM_B200_API int mslam_b200_db_scores_dev(mslam_b200_ctx* ctx, const uint8_t* d_queries, const int* d_q_counts,
+                                            int n_query_frames, int q_cap, const uint8_t* d_db, const int* d_k_counts,
+                                            int n_keyframes, int k_cap, int* d_scores);
+/* per query frame: top-k keyframes by (score desc, id asc); ids are local index + id_base (shard start).
+ * d_out_score / d_out_id are device arrays [n_query_frames][k]; (-1,-1) pads when n_keyframes < k. */
+MSLAM_B200_API int mslam_b200_db_topk_dev(mslam_b200_ctx* ctx, const int* d_scores, int n_query_frames, int n_keyframes,
+                                          int id_base, int k, int* d_out_score, int* d_out_id);
+/* merge n_lists candidate lists per query (e.g. the all-gathered per-shard top-k, laid out
+ * [n_lists][n_query_frames][k]) into one top-k with the same (score desc, id asc) order. */
+MSLAM_B200_API int mslam_b200_db_merge_topk_dev(mslam_b200_ctx* ctx, const int* d_scores, const int* d_ids, int n_lists,
+                                                int n_query_frames, int k, int* d_out_score, int* d_out_id);
+/* host convenience wrapper: scores + top-k of one shard, host in / host out */
+MSLAM_B200_API int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queries, const int* q_counts,
+                                       int n_query_frames, int q_cap, const uint8_t* db, const int* k_counts,
+                                       int n_keyframes, int k_cap, int id_base, int k, int* out_score, int* out_id,
+                                       int* out_all_scores /* may be NULL; [n_query_frames][n_keyframes] */);
+
+/* ---- measurement / parity aids ------------------------------------------------------------------------------- */
+typedef enum mslam_b200_stage
+{
+    MSLAM_B200_STAGE_PYRAMID = 0,  /* u8 level image, dense w_l*h_l */
+    MSLAM_B200_STAGE_BLURRED = 1,  /* u8 blurred level image */
+    MSLAM_B200_STAGE_N_FAST = 2,   /* int: NMS+border survivors of the level */
+    MSLAM_B200_STAGE_N_CUT1 = 3,   /* int: survivors of retainBest(2*n_l) on the FAST score */
+    MSLAM_B200_STAGE_N_FINAL = 4   /* int: keypoints kept on the level */
+} mslam_b200_stage;
+/* copy an intermediate of the LAST detect call (frame index in that batch, level) to host memory */
+MSLAM_B200_API int mslam_b200_debug_read(mslam_b200_ctx* ctx, int stage, int frame, int level, void* out, size_t bytes);
+/* integer-pipe roofline denominators, measured on the context's device with register-only loops over all SMs:
+ * out[0] = POPC.32 results/s, out[1] = LOP3 (xor) results/s, out[2] = 256-bit pair evaluations/s of the plain
+ * 8x(xor,popc,add) sequence, out[3] = SM clock (MHz) the loops ran at (from clock64/globaltimer). */
+MSLAM_B200_API int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out4);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSLAM_B200_H_ */

@@ -1,0 +1,65 @@
+// common.cuh -- shared device/host structures of the B200 ORB + Hamming hot path.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/mslam_b200.h"
+
+namespace mslam_b200
+{
+
+constexpr int kMaxLevels = MSLAM_B200_MAX_LEVELS;
+constexpr int kPatchRadius = 15; // ORB patchSize 31 (cv::ORB default; orb_feature.cpp:25)
+constexpr int kHarrisBlock = 7;
+
+// One pyramid level of the batch.  Level planes are level-major in HBM:
+//   pixel (b, y, x) of level l lives at  pyr + img_off + b*img_frame_stride + y*pitch + x
+struct LevelDesc
+{
+    int w, h, pitch; // pitch: bytes per row, multiple of 16
+    int n_keep;      // cv::ORB nfeaturesPerLevel[l]
+    int cand_cap;    // capacity of this level's candidate list (upper bound of strict 3x3 maxima)
+    int tiles_x, tiles_y; // FAST tiling of the interior
+    int tile_base;   // first FAST tile index of this level inside the fused launch
+    long long img_off;          // bytes
+    long long img_frame_stride; // bytes
+    long long cand_off;         // elements, within one frame's candidate block
+    int xtab_off, ytab_off;     // offsets into the resize tap tables (short2 {ofs, alpha1})
+    float scale;                // (float)pow((double)scaleFactor, l)
+    float inv_scale;            // 1.f / scale
+};
+
+struct PipeParams
+{
+    int nlevels, n_frames, W, H;
+    int edge, fast_thr, kp_cap, pad0;
+    long long cand_frame_stride; // elements per frame in the candidate arrays
+    int total_fast_tiles, pad1;
+    LevelDesc lv[kMaxLevels];
+};
+
+// per-(frame, level) bookkeeping in HBM, zeroed at the start of every batch
+struct LevelCounters
+{
+    unsigned int n_fast;  // NMS + border survivors
+    unsigned int n_cut1;  // survivors of retainBest(2 n_l) on the FAST score
+    unsigned int n_final; // survivors of retainBest(n_l) on the Harris response
+    unsigned int pad;
+};
+
+// selected keypoint of one level, before orientation / description
+struct SelRec
+{
+    unsigned int yx_score; // y << 20 | x << 8 | fast score
+    float response;
+};
+
+#define MSLAM_CUDA_OK(expr)                                                                                            \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        cudaError_t e__ = (expr);                                                                                      \
+        if(e__ != cudaSuccess)                                                                                         \
+            return ctx_fail(ctx, e__, #expr);                                                                          \
+    } while(0)
+
+} // namespace mslam_b200

@@ -1,0 +1,930 @@
+// context.cu -- host side of the C ABI declared in include/mslam_b200.h: context, HBM layout, launch
+// sequencing.  The reference interfaces each entry point replaces are cited in the header.
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.h"
+
+using namespace mslam_b200;
+
+struct mslam_b200_ctx
+{
+    mslam_b200_config cfg;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    long long launches = 0;
+    char err[512] = {0};
+
+    // geometry of the frame size currently configured (cv::ORB layer table)
+    int geo_w = 0, geo_h = 0;
+    PipeParams P;
+    int kp_cap = 0, desc_cap = 0;
+
+    // ---- HBM: detector ----
+    uint8_t* d_bgr = nullptr;  // [max_batch][H][W][3]
+    uint8_t* d_pyr = nullptr;  // level-major planes, see LevelDesc
+    uint8_t* d_blur = nullptr; // same layout
+    size_t pyr_bytes = 0, bgr_bytes = 0;
+    short2 *d_xtab = nullptr, *d_ytab = nullptr;
+    int tab_cap = 0;
+    unsigned *d_cand = nullptr, *d_cand2 = nullptr, *d_keys = nullptr, *d_keys2 = nullptr;
+    long long cand_elems = 0; // per frame
+    uint8_t* d_zero = nullptr; // one block, zeroed per batch: counters | hist | err
+    size_t zero_bytes = 0;
+    LevelCounters* d_ctr = nullptr;
+    unsigned* d_hist = nullptr;
+    int* d_err = nullptr;
+    SelRec* d_sel = nullptr;
+    mslam_b200_keypoint* d_kp = nullptr;
+    uint8_t* d_desc = nullptr;
+    int* d_counts = nullptr;
+    // ---- pinned host staging ----
+    int* h_counts = nullptr;
+    int* h_err = nullptr;
+    int last_frames = 0;
+    // ---- HBM: matcher ----
+    uint8_t *d_mfrom = nullptr, *d_mto = nullptr, *d_raw = nullptr;
+    int *d_nfrom = nullptr, *d_nto = nullptr;
+    unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
+    int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
+    int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
+};
+
+static int ctx_fail(mslam_b200_ctx* ctx, cudaError_t e, const char* what)
+{
+    if(ctx)
+        snprintf(ctx->err, sizeof(ctx->err), "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+    return MSLAM_B200_E_CUDA;
+}
+
+static inline size_t align_up(size_t v, size_t a)
+{
+    return (v + a - 1) / a * a;
+}
+
+// ---- cv::ORB layer geometry (OpenCV orb.cpp getScale / detectAndCompute / computeKeyPoints) ----
+static void level_geometry(int W, int H, int nlevels, float scale_factor, int* w, int* h, float* scale)
+{
+    for(int l = 0; l < nlevels; ++l)
+    {
+        const float s = (float)pow((double)scale_factor, (double)l);
+        scale[l] = s;
+        w[l] = (int)lrintf((float)W / s);
+        h[l] = (int)lrintf((float)H / s);
+    }
+}
+
+static void features_per_level(int nfeatures, int nlevels, float scale_factor, int* n_l)
+{
+    const float factor = (float)(1.0 / (double)scale_factor);
+    float nd = (float)nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nlevels));
+    int sum = 0;
+    for(int l = 0; l < nlevels - 1; ++l)
+    {
+        n_l[l] = (int)lrintf(nd);
+        sum += n_l[l];
+        nd *= factor;
+    }
+    n_l[nlevels - 1] = std::max(nfeatures - sum, 0);
+}
+
+// INTER_LINEAR_EXACT taps: IEEE double, no FMA (file compiled with -ffp-contract=off)
+static void resize_taps(int src, int dst, short2* tab)
+{
+    const double inv = (double)dst / (double)src;
+    const double scale = 1.0 / inv;
+    for(int v = 0; v < dst; ++v)
+    {
+        const double f = scale * ((double)v + 0.5) - 0.5;
+        int i = (int)floor(f);
+        int a1 = 0;
+        if(i < 0)
+            i = 0;
+        else if(i >= src - 1)
+            i = src - 1;
+        else
+            a1 = (int)lrint((f - (double)i) * 256.0);
+        tab[v].x = (short)i;
+        tab[v].y = (short)a1;
+    }
+}
+
+struct Geometry
+{
+    PipeParams P;
+    size_t pyr_bytes;
+    long long cand_elems;
+    int tab_elems;
+    std::vector<short2> xtab, ytab;
+};
+
+static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int H, Geometry* g)
+{
+    PipeParams& P = g->P;
+    memset(&P, 0, sizeof(P));
+    P.nlevels = cfg.nlevels;
+    P.W = W;
+    P.H = H;
+    P.edge = cfg.edge_threshold;
+    P.fast_thr = cfg.fast_threshold;
+    P.kp_cap = kp_cap;
+    int w[kMaxLevels], h[kMaxLevels], nl[kMaxLevels];
+    float sc[kMaxLevels];
+    level_geometry(W, H, cfg.nlevels, cfg.scale_factor, w, h, sc);
+    features_per_level(cfg.nfeatures, cfg.nlevels, cfg.scale_factor, nl);
+    size_t off = 0;
+    long long coff = 0;
+    int toff_x = 0, toff_y = 0, tiles = 0;
+    g->xtab.clear();
+    g->ytab.clear();
+    for(int l = 0; l < cfg.nlevels; ++l)
+    {
+        LevelDesc& L = P.lv[l];
+        L.w = std::max(w[l], 1);
+        L.h = std::max(h[l], 1);
+        L.pitch = (int)align_up((size_t)L.w, 64);
+        L.n_keep = nl[l];
+        L.scale = sc[l];
+        L.inv_scale = 1.f / sc[l];
+        L.img_off = (long long)off;
+        L.img_frame_stride = (long long)align_up((size_t)L.pitch * L.h, 256);
+        off += (size_t)L.img_frame_stride * cfg.max_batch;
+        const int wi = L.w - 2 * cfg.edge_threshold, hi = L.h - 2 * cfg.edge_threshold;
+        L.cand_cap = (wi > 0 && hi > 0) ? ((wi + 1) / 2) * ((hi + 1) / 2) : 0;
+        L.cand_off = coff;
+        coff += (long long)align_up((size_t)L.cand_cap, 4);
+        fast_tiles(L.w, L.h, cfg.edge_threshold, &L.tiles_x, &L.tiles_y);
+        L.tile_base = tiles;
+        tiles += L.tiles_x * L.tiles_y;
+        L.xtab_off = toff_x;
+        L.ytab_off = toff_y;
+        if(l > 0)
+        {
+            g->xtab.resize(toff_x + L.w);
+            g->ytab.resize(toff_y + L.h);
+            resize_taps(P.lv[l - 1].w, L.w, g->xtab.data() + toff_x);
+            resize_taps(P.lv[l - 1].h, L.h, g->ytab.data() + toff_y);
+            toff_x += L.w;
+            toff_y += L.h;
+        }
+    }
+    P.total_fast_tiles = tiles;
+    P.cand_frame_stride = std::max<long long>(coff, 4);
+    g->pyr_bytes = off;
+    g->cand_elems = P.cand_frame_stride;
+    g->tab_elems = std::max(toff_x, toff_y) + 1;
+}
+
+static int set_geometry(mslam_b200_ctx* ctx, int W, int H)
+{
+    if(W == ctx->geo_w && H == ctx->geo_h)
+        return MSLAM_B200_OK;
+    if(W < 1 || H < 1 || W > ctx->cfg.max_width || H > ctx->cfg.max_height || W > 4095 || H > 4095)
+        return MSLAM_B200_E_INVALID;
+    Geometry g;
+    build_geometry(ctx->cfg, ctx->kp_cap, W, H, &g);
+    if(g.pyr_bytes > ctx->pyr_bytes || g.cand_elems > ctx->cand_elems || g.tab_elems > ctx->tab_cap)
+        return MSLAM_B200_E_INVALID; // cannot happen for W,H <= max (geometry is monotone); guard anyway
+    if(!g.xtab.empty())
+    {
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_xtab, g.xtab.data(), g.xtab.size() * sizeof(short2), cudaMemcpyHostToDevice,
+                                      ctx->stream));
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_ytab, g.ytab.data(), g.ytab.size() * sizeof(short2), cudaMemcpyHostToDevice,
+                                      ctx->stream));
+        MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream)); // the host vectors die with this scope
+    }
+    ctx->P = g.P;
+    ctx->geo_w = W;
+    ctx->geo_h = H;
+    return MSLAM_B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int mslam_b200_version(void)
+{
+    return MSLAM_B200_VERSION;
+}
+
+const char* mslam_b200_status_string(int s)
+{
+    switch(s)
+    {
+    case MSLAM_B200_OK: return "ok";
+    case MSLAM_B200_E_INVALID: return "invalid argument";
+    case MSLAM_B200_E_CUDA: return "CUDA error (no device, or a runtime failure; see mslam_b200_last_cuda_error)";
+    case MSLAM_B200_E_CAPACITY: return "output or candidate capacity exceeded";
+    case MSLAM_B200_E_NOMEM: return "out of memory";
+    default: return "unknown status";
+    }
+}
+
+void mslam_b200_default_config(mslam_b200_config* cfg)
+{
+    if(!cfg)
+        return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->struct_size = (int)sizeof(*cfg);
+    cfg->device = 0;
+    cfg->max_width = 640;
+    cfg->max_height = 480;
+    cfg->max_batch = 1;
+    cfg->nfeatures = 1000; // cv::ORB::create(1000), orb_feature.cpp:25
+    cfg->nlevels = 8;
+    cfg->scale_factor = 1.2f;
+    cfg->fast_threshold = 20;
+    cfg->edge_threshold = 31;
+    cfg->max_keypoints = 0;
+    cfg->max_descriptors = 0;
+    cfg->ratio = 0.7; // orb_feature.cpp:101
+    cfg->stream = nullptr;
+}
+
+const char* mslam_b200_last_cuda_error(mslam_b200_ctx* ctx)
+{
+    return ctx ? ctx->err : "";
+}
+
+long long mslam_b200_launch_count(mslam_b200_ctx* ctx)
+{
+    return ctx ? ctx->launches : 0;
+}
+
+int mslam_b200_host_alloc(void** ptr, size_t bytes)
+{
+    if(!ptr)
+        return MSLAM_B200_E_INVALID;
+    return cudaHostAlloc(ptr, bytes, cudaHostAllocDefault) == cudaSuccess ? MSLAM_B200_OK : MSLAM_B200_E_NOMEM;
+}
+
+int mslam_b200_host_free(void* ptr)
+{
+    return cudaFreeHost(ptr) == cudaSuccess ? MSLAM_B200_OK : MSLAM_B200_E_CUDA;
+}
+
+void mslam_b200_destroy(mslam_b200_ctx* ctx)
+{
+    if(!ctx)
+        return;
+    cudaSetDevice(ctx->cfg.device);
+    if(ctx->stream)
+        cudaStreamSynchronize(ctx->stream);
+    void* dev[] = {ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
+                   ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
+                   ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
+                   ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout};
+    for(void* p : dev)
+        if(p)
+            cudaFree(p);
+    void* host[] = {ctx->h_counts, ctx->h_err, ctx->h_out_a, ctx->h_out_b, ctx->h_out_d, ctx->h_nout, ctx->h_n2};
+    for(void* p : host)
+        if(p)
+            cudaFreeHost(p);
+    if(ctx->own_stream && ctx->stream)
+        cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
+{
+    if(!cfg_in || !out_ctx || cfg_in->struct_size != (int)sizeof(mslam_b200_config))
+        return MSLAM_B200_E_INVALID;
+    *out_ctx = nullptr;
+    const mslam_b200_config& c = *cfg_in;
+    if(c.max_width < 1 || c.max_height < 1 || c.max_width > 4095 || c.max_height > 4095 || c.max_batch < 1 ||
+       c.max_batch > 65535 || c.nfeatures < 1 || c.nlevels < 1 || c.nlevels > kMaxLevels || !(c.scale_factor > 1.f) ||
+       c.fast_threshold < 1 || c.fast_threshold > 254 || c.edge_threshold < 31 || !(c.ratio > 0.0))
+        return MSLAM_B200_E_INVALID;
+    int ndev = 0;
+    if(cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || c.device < 0 || c.device >= ndev)
+        return MSLAM_B200_E_CUDA; // no CPU fallback by design
+    mslam_b200_ctx* ctx = new(std::nothrow) mslam_b200_ctx();
+    if(!ctx)
+        return MSLAM_B200_E_NOMEM;
+    ctx->cfg = c;
+    ctx->kp_cap = c.max_keypoints > 0 ? c.max_keypoints : c.nfeatures + c.nfeatures / 4 + 64;
+    ctx->desc_cap = c.max_descriptors > 0 ? c.max_descriptors : ctx->kp_cap;
+    if(ctx->desc_cap > 65535)
+    {
+        delete ctx;
+        return MSLAM_B200_E_INVALID; // train index is packed into 16 bits of the kNN key
+    }
+#define CREATE_OK(expr)                                                                                                \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        cudaError_t e__ = (expr);                                                                                      \
+        if(e__ != cudaSuccess)                                                                                         \
+        {                                                                                                              \
+            fprintf(stderr, "mslam_b200_create: %s failed: %s\n", #expr, cudaGetErrorString(e__));                     \
+            const int rc__ = e__ == cudaErrorMemoryAllocation ? MSLAM_B200_E_NOMEM : MSLAM_B200_E_CUDA;                \
+            mslam_b200_destroy(ctx);                                                                                   \
+            return rc__;                                                                                               \
+        }                                                                                                              \
+    } while(0)
+    CREATE_OK(cudaSetDevice(c.device));
+    cudaDeviceProp prop;
+    CREATE_OK(cudaGetDeviceProperties(&prop, c.device));
+    ctx->sm_count = prop.multiProcessorCount;
+    if(c.stream)
+        ctx->stream = (cudaStream_t)c.stream;
+    else
+    {
+        CREATE_OK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        ctx->own_stream = true;
+    }
+    Geometry g;
+    build_geometry(c, ctx->kp_cap, c.max_width, c.max_height, &g);
+    const size_t B = (size_t)c.max_batch;
+    ctx->pyr_bytes = g.pyr_bytes;
+    ctx->cand_elems = g.cand_elems;
+    ctx->tab_cap = g.tab_elems + 64;
+    ctx->bgr_bytes = B * c.max_width * c.max_height * 3;
+    CREATE_OK(cudaMalloc(&ctx->d_bgr, ctx->bgr_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_pyr, ctx->pyr_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_blur, ctx->pyr_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_xtab, ctx->tab_cap * sizeof(short2)));
+    CREATE_OK(cudaMalloc(&ctx->d_ytab, ctx->tab_cap * sizeof(short2)));
+    const size_t cand_bytes = B * (size_t)ctx->cand_elems * sizeof(unsigned);
+    CREATE_OK(cudaMalloc(&ctx->d_cand, cand_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_cand2, cand_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_keys, cand_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_keys2, cand_bytes));
+    const size_t ctr_bytes = align_up(B * c.nlevels * sizeof(LevelCounters), 256);
+    const size_t hist_bytes = align_up(B * c.nlevels * 256 * sizeof(unsigned), 256);
+    const size_t err_bytes = align_up(B * sizeof(int), 256);
+    ctx->zero_bytes = ctr_bytes + hist_bytes + err_bytes;
+    CREATE_OK(cudaMalloc(&ctx->d_zero, ctx->zero_bytes));
+    ctx->d_ctr = reinterpret_cast<LevelCounters*>(ctx->d_zero);
+    ctx->d_hist = reinterpret_cast<unsigned*>(ctx->d_zero + ctr_bytes);
+    ctx->d_err = reinterpret_cast<int*>(ctx->d_zero + ctr_bytes + hist_bytes);
+    CREATE_OK(cudaMalloc(&ctx->d_sel, B * c.nlevels * (size_t)ctx->kp_cap * sizeof(SelRec)));
+    CREATE_OK(cudaMalloc(&ctx->d_kp, B * (size_t)ctx->kp_cap * sizeof(mslam_b200_keypoint)));
+    CREATE_OK(cudaMalloc(&ctx->d_desc, B * (size_t)ctx->kp_cap * 32));
+    CREATE_OK(cudaMalloc(&ctx->d_counts, B * sizeof(int)));
+    CREATE_OK(cudaHostAlloc(&ctx->h_counts, B * sizeof(int), cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_err, B * sizeof(int), cudaHostAllocDefault));
+    // matcher
+    const size_t dc = (size_t)ctx->desc_cap;
+    CREATE_OK(cudaMalloc(&ctx->d_mfrom, B * dc * 32));
+    CREATE_OK(cudaMalloc(&ctx->d_mto, B * dc * 32));
+    CREATE_OK(cudaMalloc(&ctx->d_raw, dc * 128));
+    CREATE_OK(cudaMalloc(&ctx->d_nfrom, B * sizeof(int)));
+    CREATE_OK(cudaMalloc(&ctx->d_nto, B * sizeof(int)));
+    CREATE_OK(cudaMalloc(&ctx->d_key0, B * dc * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_key1, B * dc * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_key0b, B * dc * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_key1b, B * dc * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_out_a, B * dc * sizeof(int)));
+    CREATE_OK(cudaMalloc(&ctx->d_out_b, B * dc * sizeof(int)));
+    CREATE_OK(cudaMalloc(&ctx->d_out_d, B * dc * sizeof(int)));
+    CREATE_OK(cudaMalloc(&ctx->d_nout, B * sizeof(int)));
+    CREATE_OK(cudaHostAlloc(&ctx->h_out_a, B * dc * sizeof(int), cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_out_b, B * dc * sizeof(int), cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_out_d, B * dc * sizeof(int), cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_nout, B * sizeof(int), cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_n2, 2 * B * sizeof(int), cudaHostAllocDefault));
+#undef CREATE_OK
+    *out_ctx = ctx;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_set_stream(mslam_b200_ctx* ctx, void* cuda_stream)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if(ctx->own_stream)
+    {
+        cudaStreamDestroy(ctx->stream);
+        ctx->own_stream = false;
+    }
+    if(cuda_stream)
+        ctx->stream = (cudaStream_t)cuda_stream;
+    else
+    {
+        MSLAM_CUDA_OK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        ctx->own_stream = true;
+    }
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_synchronize(mslam_b200_ctx* ctx)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_level_geometry(mslam_b200_ctx* ctx, int width, int height, int* w, int* h, float* scale, int* n_per_level)
+{
+    if(!ctx || width < 1 || height < 1)
+        return MSLAM_B200_E_INVALID;
+    int lw[kMaxLevels], lh[kMaxLevels], nl[kMaxLevels];
+    float sc[kMaxLevels];
+    level_geometry(width, height, ctx->cfg.nlevels, ctx->cfg.scale_factor, lw, lh, sc);
+    features_per_level(ctx->cfg.nfeatures, ctx->cfg.nlevels, ctx->cfg.scale_factor, nl);
+    for(int l = 0; l < ctx->cfg.nlevels; ++l)
+    {
+        if(w) w[l] = lw[l];
+        if(h) h[l] = lh[l];
+        if(scale) scale[l] = sc[l];
+        if(n_per_level) n_per_level[l] = nl[l];
+    }
+    return MSLAM_B200_OK;
+}
+
+// ---- detection ---------------------------------------------------------------------------------------------------
+static int run_pyramid(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames)
+{
+    ctx->P.n_frames = n_frames;
+    launch_gray(ctx->stream, d_bgr, ctx->d_pyr, ctx->P, &ctx->launches);
+    launch_pyramid(ctx->stream, ctx->d_pyr, ctx->P, ctx->d_xtab, ctx->d_ytab, &ctx->launches);
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames, int width, int height,
+                                mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity, int* d_counts)
+{
+    if(!ctx || !d_bgr || !d_kp || !d_desc || !d_counts || n_frames < 1 || n_frames > ctx->cfg.max_batch || capacity < 1)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    int rc = set_geometry(ctx, width, height);
+    if(rc)
+        return rc;
+    cudaStream_t st = ctx->stream;
+    MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
+    run_pyramid(ctx, d_bgr, n_frames);
+    const PipeParams& P = ctx->P;
+    launch_fast(st, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, &ctx->launches);
+    launch_select(st, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist, ctx->d_sel,
+                  ctx->d_err, P, &ctx->launches);
+    launch_blur(st, ctx->d_pyr, ctx->d_blur, P, &ctx->launches);
+    launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, d_kp, d_desc, d_counts, capacity,
+                           std::min(capacity, ctx->kp_cap * P.nlevels), P, &ctx->launches);
+    ctx->last_frames = n_frames;
+    MSLAM_CUDA_OK(cudaGetLastError());
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
+                            int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(!ctx || !frames || !out_kp || !out_desc || !n_out || n_frames < 1 || n_frames > ctx->cfg.max_batch ||
+       capacity < 1 || width < 1 || height < 1 || stride_bytes < 3 * width || width > ctx->cfg.max_width ||
+       height > ctx->cfg.max_height)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    const size_t row = (size_t)width * 3, frame_bytes = row * height;
+    for(int i = 0; i < n_frames; ++i)
+    {
+        if(!frames[i])
+            return MSLAM_B200_E_INVALID;
+        if((size_t)stride_bytes == row)
+            MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_bgr + i * frame_bytes, frames[i], frame_bytes, cudaMemcpyHostToDevice, st));
+        else
+            MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * frame_bytes, row, frames[i], (size_t)stride_bytes, row,
+                                            (size_t)height, cudaMemcpyHostToDevice, st));
+    }
+    const int icap = ctx->kp_cap;
+    int rc = mslam_b200_detect_batch_dev(ctx, ctx->d_bgr, n_frames, width, height, ctx->d_kp, ctx->d_desc, icap,
+                                         ctx->d_counts);
+    if(rc)
+        return rc;
+    const int ncopy = std::min(capacity, icap);
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_counts, ctx->d_counts, n_frames * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_err, ctx->d_err, n_frames * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpy2DAsync(out_kp, (size_t)capacity * sizeof(mslam_b200_keypoint), ctx->d_kp,
+                                    (size_t)icap * sizeof(mslam_b200_keypoint), (size_t)ncopy * sizeof(mslam_b200_keypoint),
+                                    (size_t)n_frames, cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpy2DAsync(out_desc, (size_t)capacity * 32, ctx->d_desc, (size_t)icap * 32, (size_t)ncopy * 32,
+                                    (size_t)n_frames, cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    rc = MSLAM_B200_OK;
+    for(int i = 0; i < n_frames; ++i)
+    {
+        n_out[i] = ctx->h_counts[i];
+        if(ctx->h_counts[i] > capacity || ctx->h_err[i])
+            rc = MSLAM_B200_E_CAPACITY;
+    }
+    return rc;
+}
+
+int mslam_b200_detect(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int height, int stride_bytes,
+                      mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    const uint8_t* frames[1] = {bgr};
+    return mslam_b200_detect_batch(ctx, frames, 1, width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
+}
+
+int mslam_b200_describe(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int height, int stride_bytes,
+                        mslam_b200_keypoint* kp, int n_kp, uint8_t* out_desc)
+{
+    if(!ctx || !bgr || !kp || !out_desc || n_kp < 0 || width < 1 || height < 1 || stride_bytes < 3 * width ||
+       width > ctx->cfg.max_width || height > ctx->cfg.max_height)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    int rc = set_geometry(ctx, width, height);
+    if(rc)
+        return rc;
+    cudaStream_t st = ctx->stream;
+    const PipeParams& P0 = ctx->P;
+    const int nl = P0.nlevels, icap = ctx->kp_cap;
+    // bucket the given keypoints by level, keeping the caller's order inside a level
+    std::vector<std::vector<int>> per(nl);
+    for(int i = 0; i < n_kp; ++i)
+    {
+        const int l = kp[i].octave;
+        if(l < 0 || l >= nl)
+            return MSLAM_B200_E_INVALID;
+        per[l].push_back(i);
+    }
+    std::vector<LevelCounters> ctr(nl);
+    std::vector<SelRec> sel((size_t)nl * icap);
+    std::vector<int> slot_to_src;
+    for(int l = 0; l < nl; ++l)
+    {
+        if((int)per[l].size() > icap)
+            return MSLAM_B200_E_CAPACITY;
+        memset(&ctr[l], 0, sizeof(LevelCounters));
+        ctr[l].n_final = (unsigned)per[l].size();
+        const LevelDesc& L = P0.lv[l];
+        for(size_t r = 0; r < per[l].size(); ++r)
+        {
+            const mslam_b200_keypoint& k = kp[per[l][r]];
+            // same mapping OpenCV's computeOrbDescriptors uses: cvRound(pt * (1.f / scale_l))
+            const int x = (int)lrintf(k.x * L.inv_scale), y = (int)lrintf(k.y * L.inv_scale);
+            if(x < P0.edge || y < P0.edge || x >= L.w - P0.edge || y >= L.h - P0.edge)
+                return MSLAM_B200_E_INVALID;
+            sel[(size_t)l * icap + r].yx_score = ((unsigned)y << 20) | ((unsigned)x << 8);
+            sel[(size_t)l * icap + r].response = k.response;
+            slot_to_src.push_back(per[l][r]);
+        }
+    }
+    if(n_kp > icap)
+        return MSLAM_B200_E_CAPACITY;
+    const size_t row = (size_t)width * 3;
+    MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr, row, bgr, (size_t)stride_bytes, row, (size_t)height, cudaMemcpyHostToDevice, st));
+    MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_ctr, ctr.data(), nl * sizeof(LevelCounters), cudaMemcpyHostToDevice, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_sel, sel.data(), sel.size() * sizeof(SelRec), cudaMemcpyHostToDevice, st));
+    run_pyramid(ctx, ctx->d_bgr, 1);
+    launch_blur(st, ctx->d_pyr, ctx->d_blur, ctx->P, &ctx->launches);
+    launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,
+                           std::max(n_kp, 1), ctx->P, &ctx->launches);
+    std::vector<mslam_b200_keypoint> hk((size_t)std::max(n_kp, 1));
+    std::vector<uint8_t> hd((size_t)std::max(n_kp, 1) * 32);
+    if(n_kp > 0)
+    {
+        MSLAM_CUDA_OK(cudaMemcpyAsync(hk.data(), ctx->d_kp, n_kp * sizeof(mslam_b200_keypoint), cudaMemcpyDeviceToHost, st));
+        MSLAM_CUDA_OK(cudaMemcpyAsync(hd.data(), ctx->d_desc, (size_t)n_kp * 32, cudaMemcpyDeviceToHost, st));
+    }
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    ctx->last_frames = 1;
+    for(int s = 0; s < n_kp; ++s)
+    {
+        const int i = slot_to_src[s];
+        kp[i].angle = hk[s].angle;
+        kp[i].size = hk[s].size;
+        memcpy(out_desc + (size_t)i * 32, hd.data() + (size_t)s * 32, 32);
+    }
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_debug_read(mslam_b200_ctx* ctx, int stage, int frame, int level, void* out, size_t bytes)
+{
+    if(!ctx || !out || frame < 0 || frame >= ctx->cfg.max_batch || level < 0 || level >= ctx->P.nlevels || ctx->geo_w == 0)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    const LevelDesc& L = ctx->P.lv[level];
+    MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if(stage == MSLAM_B200_STAGE_PYRAMID || stage == MSLAM_B200_STAGE_BLURRED)
+    {
+        if(bytes < (size_t)L.w * L.h)
+            return MSLAM_B200_E_INVALID;
+        const uint8_t* base = (stage == MSLAM_B200_STAGE_PYRAMID ? ctx->d_pyr : ctx->d_blur) + L.img_off +
+                              (long long)frame * L.img_frame_stride;
+        MSLAM_CUDA_OK(cudaMemcpy2D(out, (size_t)L.w, base, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost));
+        return MSLAM_B200_OK;
+    }
+    if(stage >= MSLAM_B200_STAGE_N_FAST && stage <= MSLAM_B200_STAGE_N_FINAL)
+    {
+        if(bytes < sizeof(int))
+            return MSLAM_B200_E_INVALID;
+        LevelCounters c;
+        MSLAM_CUDA_OK(cudaMemcpy(&c, ctx->d_ctr + (size_t)frame * ctx->P.nlevels + level, sizeof(c), cudaMemcpyDeviceToHost));
+        const unsigned v = stage == MSLAM_B200_STAGE_N_FAST ? c.n_fast : stage == MSLAM_B200_STAGE_N_CUT1 ? c.n_cut1 : c.n_final;
+        *(int*)out = (int)v;
+        return MSLAM_B200_OK;
+    }
+    return MSLAM_B200_E_INVALID;
+}
+
+// ---- matching ----------------------------------------------------------------------------------------------------
+// gather 32-byte descriptors out of a strided record array (e.g. OrbKeypoint, 64 B, descriptor at +32)
+__global__ void k_pack_desc(const uint8_t* __restrict__ raw, int stride, int n, uint8_t* __restrict__ dense)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x; // one 4-byte word per thread
+    if(i >= n * 8)
+        return;
+    const int row = i >> 3, wd = i & 7;
+    const uint8_t* s = raw + (size_t)row * stride + wd * 4;
+    uchar4 v = make_uchar4(s[0], s[1], s[2], s[3]);
+    reinterpret_cast<uchar4*>(dense)[i] = v;
+}
+
+static int upload_desc(mslam_b200_ctx* ctx, const uint8_t* src, int n, int stride, uint8_t* d_dst)
+{
+    if(n <= 0)
+        return MSLAM_B200_OK;
+    cudaStream_t st = ctx->stream;
+    if(stride == 32)
+        MSLAM_CUDA_OK(cudaMemcpyAsync(d_dst, src, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+    else if(stride > 32 && stride <= 128)
+    {
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_raw, src, (size_t)(n - 1) * stride + 32, cudaMemcpyHostToDevice, st));
+        k_pack_desc<<<(n * 8 + 255) / 256, 256, 0, st>>>(ctx->d_raw, stride, n, d_dst);
+        ++ctx->launches;
+    }
+    else
+        MSLAM_CUDA_OK(cudaMemcpy2DAsync(d_dst, 32, src, (size_t)stride, 32, (size_t)n, cudaMemcpyHostToDevice, st));
+    return MSLAM_B200_OK;
+}
+
+static int upload_counts(mslam_b200_ctx* ctx, int n_from, int n_to)
+{
+    ctx->h_n2[0] = n_from;
+    ctx->h_n2[1] = n_to;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nfrom, &ctx->h_n2[0], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nto, &ctx->h_n2[1], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, const uint8_t* d_from, const int* d_n_from, const uint8_t* d_to,
+                               const int* d_n_to, int n_pairs, int capacity, int* d_out_a, int* d_out_b, int* d_out_dist,
+                               int* d_n_out)
+{
+    if(!ctx || !d_from || !d_to || !d_n_from || !d_n_to || !d_out_a || !d_out_b || !d_n_out || n_pairs < 1 ||
+       n_pairs > ctx->cfg.max_batch || capacity < 1 || capacity > ctx->desc_cap || (mode != 0 && mode != 1))
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    // query = `to`, train = `from` (orb_feature.cpp:96)
+    launch_knn2(st, d_to, d_n_to, d_from, d_n_from, n_pairs, capacity, ctx->d_key0, ctx->d_key1, &ctx->launches);
+    if(mode == 0)
+        launch_ratio_compact(st, ctx->d_key0, ctx->d_key1, d_n_to, d_n_from, n_pairs, capacity, ctx->cfg.ratio, d_out_a,
+                             d_out_b, d_out_dist, d_n_out, &ctx->launches);
+    else
+    {
+        launch_knn2(st, d_from, d_n_from, d_to, d_n_to, n_pairs, capacity, ctx->d_key0b, ctx->d_key1b, &ctx->launches);
+        launch_mutual_compact(st, ctx->d_key0, ctx->d_key0b, d_n_to, d_n_from, n_pairs, capacity, d_out_a, d_out_b,
+                              d_out_dist, d_n_out, &ctx->launches);
+    }
+    MSLAM_CUDA_OK(cudaGetLastError());
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_match_batch(mslam_b200_ctx* ctx, int mode, const uint8_t* from, const int* n_from, const uint8_t* to,
+                           const int* n_to, int n_pairs, int capacity, int* out_a, int* out_b, int* out_dist, int* n_out)
+{
+    if(!ctx || !from || !to || !n_from || !n_to || !out_a || !out_b || !n_out || n_pairs < 1 ||
+       n_pairs > ctx->cfg.max_batch || capacity < 1 || capacity > ctx->desc_cap)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    const size_t blk = (size_t)n_pairs * capacity;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mfrom, from, blk * 32, cudaMemcpyHostToDevice, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mto, to, blk * 32, cudaMemcpyHostToDevice, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nfrom, n_from, n_pairs * sizeof(int), cudaMemcpyHostToDevice, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nto, n_to, n_pairs * sizeof(int), cudaMemcpyHostToDevice, st));
+    int rc = mslam_b200_match_batch_dev(ctx, mode, ctx->d_mfrom, ctx->d_nfrom, ctx->d_mto, ctx->d_nto, n_pairs, capacity,
+                                        ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout);
+    if(rc)
+        return rc;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(out_a, ctx->d_out_a, blk * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(out_b, ctx->d_out_b, blk * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if(out_dist)
+        MSLAM_CUDA_OK(cudaMemcpyAsync(out_dist, ctx->d_out_d, blk * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(n_out, ctx->d_nout, n_pairs * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    return MSLAM_B200_OK;
+}
+
+static int match_single(mslam_b200_ctx* ctx, int mode, const uint8_t* from, int n_from, int from_stride, const uint8_t* to,
+                        int n_to, int to_stride, int* n_found)
+{
+    // results land in ctx->h_out_{a,b,d}; *n_found = count
+    *n_found = 0;
+    if(n_from < 0 || n_to < 0 || n_from > ctx->desc_cap || n_to > ctx->desc_cap || from_stride < 32 || to_stride < 32)
+        return MSLAM_B200_E_INVALID;
+    if(n_to < 1 || n_from < (mode == 0 ? 2 : 1))
+        return MSLAM_B200_OK; // the reference is undefined here (orb_feature.cpp:88-91,101); contract: no match
+    if(!from || !to)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    int rc = upload_desc(ctx, from, n_from, from_stride, ctx->d_mfrom);
+    if(rc)
+        return rc;
+    // d_raw is reused by the second upload: stream order makes that safe
+    rc = upload_desc(ctx, to, n_to, to_stride, ctx->d_mto);
+    if(rc)
+        return rc;
+    rc = upload_counts(ctx, n_from, n_to);
+    if(rc)
+        return rc;
+    const int cap = ctx->desc_cap;
+    rc = mslam_b200_match_batch_dev(ctx, mode, ctx->d_mfrom, ctx->d_nfrom, ctx->d_mto, ctx->d_nto, 1, cap, ctx->d_out_a,
+                                    ctx->d_out_b, ctx->d_out_d, ctx->d_nout);
+    if(rc)
+        return rc;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_nout, ctx->d_nout, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_out_a, ctx->d_out_a, (size_t)n_to * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_out_b, ctx->d_out_b, (size_t)n_to * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_out_d, ctx->d_out_d, (size_t)n_to * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    *n_found = ctx->h_nout[0];
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_match_knn_ratio(mslam_b200_ctx* ctx, const uint8_t* from, int n_from, int from_stride, const uint8_t* to,
+                               int n_to, int to_stride, uint64_t* out_from_idx, uint64_t* out_to_idx, int* out_dist,
+                               int capacity, int* n_out)
+{
+    if(!ctx || !n_out || capacity < 0 || (capacity > 0 && (!out_from_idx || !out_to_idx)))
+        return MSLAM_B200_E_INVALID;
+    int n = 0;
+    int rc = match_single(ctx, 0, from, n_from, from_stride, to, n_to, to_stride, &n);
+    if(rc)
+        return rc;
+    *n_out = n;
+    const int m = std::min(n, capacity);
+    for(int i = 0; i < m; ++i)
+    {
+        out_from_idx[i] = (uint64_t)ctx->h_out_a[i];
+        out_to_idx[i] = (uint64_t)ctx->h_out_b[i];
+        if(out_dist)
+            out_dist[i] = ctx->h_out_d[i];
+    }
+    return n > capacity ? MSLAM_B200_E_CAPACITY : MSLAM_B200_OK;
+}
+
+int mslam_b200_match_crosscheck(mslam_b200_ctx* ctx, const uint8_t* query, int n_query, int query_stride,
+                                const uint8_t* train, int n_train, int train_stride, int* out_query_idx, int* out_train_idx,
+                                int* out_dist, int capacity, int* n_out)
+{
+    if(!ctx || !n_out || capacity < 0 || (capacity > 0 && (!out_query_idx || !out_train_idx)))
+        return MSLAM_B200_E_INVALID;
+    int n = 0;
+    // match_single: "to" is the kNN query, "from" the train set
+    int rc = match_single(ctx, 1, train, n_train, train_stride, query, n_query, query_stride, &n);
+    if(rc)
+        return rc;
+    *n_out = n;
+    const int m = std::min(n, capacity);
+    for(int i = 0; i < m; ++i)
+    {
+        out_train_idx[i] = ctx->h_out_a[i];
+        out_query_idx[i] = ctx->h_out_b[i];
+        if(out_dist)
+            out_dist[i] = ctx->h_out_d[i];
+    }
+    return n > capacity ? MSLAM_B200_E_CAPACITY : MSLAM_B200_OK;
+}
+
+int mslam_b200_knn2(mslam_b200_ctx* ctx, const uint8_t* query, int n_query, int query_stride, const uint8_t* train,
+                    int n_train, int train_stride, int* idx0, int* dist0, int* idx1, int* dist1)
+{
+    if(!ctx || !idx0 || !dist0 || !idx1 || !dist1 || n_query < 0 || n_train < 0 || n_query > ctx->desc_cap ||
+       n_train > ctx->desc_cap || query_stride < 32 || train_stride < 32)
+        return MSLAM_B200_E_INVALID;
+    if(n_query == 0)
+        return MSLAM_B200_OK;
+    if(!query || (n_train > 0 && !train))
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    int rc = upload_desc(ctx, train, n_train, train_stride, ctx->d_mfrom);
+    if(rc)
+        return rc;
+    rc = upload_desc(ctx, query, n_query, query_stride, ctx->d_mto);
+    if(rc)
+        return rc;
+    rc = upload_counts(ctx, n_train, n_query);
+    if(rc)
+        return rc;
+    const int cap = ctx->desc_cap;
+    launch_knn2(st, ctx->d_mto, ctx->d_nto, ctx->d_mfrom, ctx->d_nfrom, 1, cap, ctx->d_key0, ctx->d_key1, &ctx->launches);
+    // unpack into the four int scratch arrays (out_a, out_b, out_d, key0b reinterpreted)
+    int* d_i1 = reinterpret_cast<int*>(ctx->d_key0b);
+    launch_unpack_knn(st, ctx->d_key0, ctx->d_key1, n_query, ctx->d_out_a, ctx->d_out_d, d_i1, ctx->d_out_b, &ctx->launches);
+    MSLAM_CUDA_OK(cudaMemcpyAsync(idx0, ctx->d_out_a, n_query * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(dist0, ctx->d_out_d, n_query * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(idx1, d_i1, n_query * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(dist1, ctx->d_out_b, n_query * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    return MSLAM_B200_OK;
+}
+
+// ---- keyframe database -------------------------------------------------------------------------------------------
+int mslam_b200_db_scores_dev(mslam_b200_ctx* ctx, const uint8_t* d_queries, const int* d_q_counts, int n_query_frames,
+                             int q_cap, const uint8_t* d_db, const int* d_k_counts, int n_keyframes, int k_cap, int* d_scores)
+{
+    if(!ctx || !d_queries || !d_q_counts || !d_db || !d_k_counts || !d_scores || n_query_frames < 1 ||
+       n_query_frames > 65535 || n_keyframes < 1 || q_cap < 1 || k_cap < 1 || (size_t)q_cap * 32 > 200 * 1024)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    MSLAM_CUDA_OK(launch_db_scores(ctx->stream, d_queries, d_q_counts, n_query_frames, q_cap, d_db, d_k_counts, n_keyframes,
+                                   k_cap, ctx->cfg.ratio, d_scores, ctx->sm_count, &ctx->launches));
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_topk_dev(mslam_b200_ctx* ctx, const int* d_scores, int n_query_frames, int n_keyframes, int id_base, int k,
+                           int* d_out_score, int* d_out_id)
+{
+    if(!ctx || !d_scores || !d_out_score || !d_out_id || n_query_frames < 1 || n_keyframes < 1 || k < 1 || id_base < 0)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    launch_topk(ctx->stream, d_scores, nullptr, 1, n_keyframes, n_query_frames, id_base, k, d_out_score, d_out_id,
+                &ctx->launches);
+    MSLAM_CUDA_OK(cudaGetLastError());
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_merge_topk_dev(mslam_b200_ctx* ctx, const int* d_scores, const int* d_ids, int n_lists, int n_query_frames,
+                                 int k, int* d_out_score, int* d_out_id)
+{
+    if(!ctx || !d_scores || !d_ids || !d_out_score || !d_out_id || n_lists < 1 || n_query_frames < 1 || k < 1)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    launch_topk(ctx->stream, d_scores, d_ids, n_lists, k, n_query_frames, 0, k, d_out_score, d_out_id, &ctx->launches);
+    MSLAM_CUDA_OK(cudaGetLastError());
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queries, const int* q_counts, int n_query_frames, int q_cap,
+                        const uint8_t* db, const int* k_counts, int n_keyframes, int k_cap, int id_base, int k,
+                        int* out_score, int* out_id, int* out_all_scores)
+{
+    if(!ctx || !queries || !q_counts || !db || !k_counts || !out_score || !out_id || n_query_frames < 1 ||
+       n_keyframes < 1 || k < 1)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    uint8_t *d_q = nullptr, *d_db = nullptr;
+    int *d_qc = nullptr, *d_kc = nullptr, *d_sc = nullptr, *d_os = nullptr, *d_oi = nullptr;
+    const size_t qb = (size_t)n_query_frames * q_cap * 32, kb = (size_t)n_keyframes * k_cap * 32;
+    const size_t sb = (size_t)n_query_frames * n_keyframes * sizeof(int), ob = (size_t)n_query_frames * k * sizeof(int);
+    int rc = MSLAM_B200_OK;
+    cudaError_t e;
+#define DBQ(expr)                                                                                                      \
+    if(rc == MSLAM_B200_OK && (e = (expr)) != cudaSuccess)                                                             \
+    rc = ctx_fail(ctx, e, #expr)
+    DBQ(cudaMalloc(&d_q, qb));
+    DBQ(cudaMalloc(&d_db, kb));
+    DBQ(cudaMalloc(&d_qc, n_query_frames * sizeof(int)));
+    DBQ(cudaMalloc(&d_kc, n_keyframes * sizeof(int)));
+    DBQ(cudaMalloc(&d_sc, sb));
+    DBQ(cudaMalloc(&d_os, ob));
+    DBQ(cudaMalloc(&d_oi, ob));
+    DBQ(cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, st));
+    DBQ(cudaMemcpyAsync(d_db, db, kb, cudaMemcpyHostToDevice, st));
+    DBQ(cudaMemcpyAsync(d_qc, q_counts, n_query_frames * sizeof(int), cudaMemcpyHostToDevice, st));
+    DBQ(cudaMemcpyAsync(d_kc, k_counts, n_keyframes * sizeof(int), cudaMemcpyHostToDevice, st));
+    if(rc == MSLAM_B200_OK)
+        rc = mslam_b200_db_scores_dev(ctx, d_q, d_qc, n_query_frames, q_cap, d_db, d_kc, n_keyframes, k_cap, d_sc);
+    if(rc == MSLAM_B200_OK)
+        rc = mslam_b200_db_topk_dev(ctx, d_sc, n_query_frames, n_keyframes, id_base, k, d_os, d_oi);
+    DBQ(cudaMemcpyAsync(out_score, d_os, ob, cudaMemcpyDeviceToHost, st));
+    DBQ(cudaMemcpyAsync(out_id, d_oi, ob, cudaMemcpyDeviceToHost, st));
+    if(out_all_scores)
+        DBQ(cudaMemcpyAsync(out_all_scores, d_sc, sb, cudaMemcpyDeviceToHost, st));
+    DBQ(cudaStreamSynchronize(st));
+#undef DBQ
+    void* frees[] = {d_q, d_db, d_qc, d_kc, d_sc, d_os, d_oi};
+    for(void* p : frees)
+        if(p)
+            cudaFree(p);
+    return rc;
+}
+
+int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out4)
+{
+    if(!ctx || !out4)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    MSLAM_CUDA_OK(measure_int_peaks(ctx->stream, ctx->sm_count, out4, &ctx->launches));
+    return MSLAM_B200_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,37 @@
+// kernels.h -- host-side launchers of the sm_100a kernels (orb_kernels.cu, match_kernels.cu).
+#pragma once
+#include "common.cuh"
+
+namespace mslam_b200
+{
+// ORB path
+void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const PipeParams& P, long long* launches);
+void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const short2* xtab, const short2* ytab,
+                    long long* launches);
+void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, long long* launches);
+void fast_tiles(int w, int h, int edge, int* tx, int* ty);
+void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCounters* ctr, unsigned* hist,
+                 const PipeParams& P, long long* launches);
+void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned* cand2, unsigned* keys, unsigned* keys2,
+                   LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P,
+                   long long* launches);
+void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
+                            const SelRec* sel, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int* out_counts,
+                            int out_cap, int n_slots, const PipeParams& P, long long* launches);
+// matching path
+void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
+                 unsigned* key0, unsigned* key1, long long* launches);
+void launch_ratio_compact(cudaStream_t st, const unsigned* key0, const unsigned* key1, const int* qn, const int* tn,
+                          int n_pairs, int cap, double ratio, int* out_a, int* out_b, int* out_d, int* n_out,
+                          long long* launches);
+void launch_mutual_compact(cudaStream_t st, const unsigned* key0_q, const unsigned* key0_t, const int* qn, const int* tn,
+                           int n_pairs, int cap, int* out_a, int* out_b, int* out_d, int* n_out, long long* launches);
+void launch_unpack_knn(cudaStream_t st, const unsigned* key0, const unsigned* key1, int n, int* idx0, int* d0, int* idx1,
+                       int* d1, long long* launches);
+cudaError_t launch_db_scores(cudaStream_t st, const uint8_t* queries, const int* q_counts, int nq_frames, int q_cap,
+                             const uint8_t* db, const int* k_counts, int n_keyframes, int k_cap, double ratio, int* scores,
+                             int sm_count, long long* launches);
+void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists, int per_list, int n_queries, int id_base,
+                 int k, int* out_score, int* out_id, long long* launches);
+cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long long* launches);
+} // namespace mslam_b200

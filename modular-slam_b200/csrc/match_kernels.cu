@@ -1,0 +1,540 @@
+// match_kernels.cu -- sm_100a kernels of the 256-bit Hamming matching path.
+//
+// Semantics are those of the reference matcher, OrbOpenCvMatcher::Pimpl::match
+// (src/lib/modular_slam/orb_feature.cpp:84-117): cv::BFMatcher(NORM_HAMMING).knnMatch(query = to, train = from, k = 2)
+// -- per query the two smallest distances, ties to the lower train index (cv::batchDistance) -- then the
+// 0.7 ratio test (orb_feature.cpp:101) and {fromIndex = trainIdx, toIndex = queryIdx} in ascending toIndex
+// (orb_feature.cpp:110-114).  Everything here is XOR + POPC on the integer pipes; no tensor cores.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace mslam_b200
+{
+
+constexpr unsigned kNoKey = 0xffffffffu;
+
+// 256-bit Hamming distance of two descriptors held as 2 x uint4
+__device__ __forceinline__ int ham256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) +
+           __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// =================================================================================================
+// K8  brute-force kNN (k = 2) for a batch of independent (query set, train set) pairs.
+//   Each thread owns QPT query descriptors in registers (8 x u32 each); the train set streams through
+//   shared memory in chunks and is read with broadcast 128-bit loads.  The running top-2 is kept as
+//   packed keys (distance << 16 | train index): two min/max per candidate give exactly "smallest
+//   distance, ties to the lower index" with no branches.
+//   Output: key0/key1 per query ([pair][cap]); kNoKey where the train set is too small.
+// =================================================================================================
+constexpr int KNN_THREADS = 128;
+constexpr int KNN_CHUNK = 512; // train descriptors per shared-memory chunk (16 KB)
+
+template <int QPT>
+__global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint8_t* __restrict__ q_base, const int* __restrict__ q_counts,
+                                                      const uint8_t* __restrict__ t_base, const int* __restrict__ t_counts,
+                                                      int cap, unsigned* __restrict__ key0, unsigned* __restrict__ key1)
+{
+    __shared__ uint4 s_t[KNN_CHUNK * 2];
+    const int p = blockIdx.y;
+    const int nq = min(q_counts[p], cap), nt = min(t_counts[p], cap);
+    const int q0 = blockIdx.x * (KNN_THREADS * QPT);
+    if(q0 >= nq)
+        return;
+    const uint4* qv = reinterpret_cast<const uint4*>(q_base + (long long)p * cap * 32);
+    const uint4* tv = reinterpret_cast<const uint4*>(t_base + (long long)p * cap * 32);
+    uint4 qa[QPT], qb[QPT];
+    unsigned k0[QPT], k1[QPT];
+#pragma unroll
+    for(int i = 0; i < QPT; ++i)
+    {
+        const int q = q0 + i * KNN_THREADS + threadIdx.x;
+        qa[i] = q < nq ? __ldg(qv + 2 * q) : make_uint4(0, 0, 0, 0);
+        qb[i] = q < nq ? __ldg(qv + 2 * q + 1) : make_uint4(0, 0, 0, 0);
+        k0[i] = kNoKey;
+        k1[i] = kNoKey;
+    }
+    for(int t0 = 0; t0 < nt; t0 += KNN_CHUNK)
+    {
+        const int nc = min(KNN_CHUNK, nt - t0);
+        __syncthreads();
+        for(int i = threadIdx.x; i < nc * 2; i += KNN_THREADS)
+            s_t[i] = __ldg(tv + 2 * t0 + i);
+        __syncthreads();
+#pragma unroll 4
+        for(int j = 0; j < nc; ++j)
+        {
+            const uint4 ta = s_t[2 * j], tb = s_t[2 * j + 1];
+#pragma unroll
+            for(int i = 0; i < QPT; ++i)
+            {
+                const unsigned key = ((unsigned)ham256(qa[i], qb[i], ta, tb) << 16) | (unsigned)(t0 + j);
+                k1[i] = min(k1[i], max(k0[i], key));
+                k0[i] = min(k0[i], key);
+            }
+        }
+    }
+#pragma unroll
+    for(int i = 0; i < QPT; ++i)
+    {
+        const int q = q0 + i * KNN_THREADS + threadIdx.x;
+        if(q < nq)
+        {
+            key0[(long long)p * cap + q] = k0[i];
+            key1[(long long)p * cap + q] = k1[i];
+        }
+    }
+}
+
+// block-wide exclusive scan of one flag per thread (256 threads); returns the offset, total in *total
+__device__ __forceinline__ int block_scan_flag(bool flag, int* total, int* s_warp /* >= 9 ints */)
+{
+    const unsigned bal = __ballot_sync(0xffffffffu, flag);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int within = __popc(bal & ((1u << lane) - 1u));
+    if(lane == 0)
+        s_warp[wid] = __popc(bal);
+    __syncthreads();
+    int off = 0, tot = 0;
+#pragma unroll
+    for(int w = 0; w < 8; ++w)
+    {
+        const int c = s_warp[w];
+        off += w < wid ? c : 0;
+        tot += c;
+    }
+    __syncthreads();
+    *total = tot;
+    return off + within;
+}
+
+// ratio test + ordered compaction: one CTA per pair, ascending query (= toIndex) order.
+//   keep iff (double)(float)d0 < ratio * (double)(float)d1          (orb_feature.cpp:101)
+__global__ void __launch_bounds__(256) k_ratio_compact(const unsigned* __restrict__ key0, const unsigned* __restrict__ key1,
+                                                       const int* __restrict__ q_counts, const int* __restrict__ t_counts,
+                                                       int cap, double ratio, int* __restrict__ out_a, int* __restrict__ out_b,
+                                                       int* __restrict__ out_d, int* __restrict__ n_out)
+{
+    __shared__ int s_warp[8];
+    const int p = blockIdx.x;
+    const int nq = min(q_counts[p], cap), nt = min(t_counts[p], cap);
+    int run = 0;
+    if(nt >= 2)
+        for(int base = 0; base < nq; base += 256)
+        {
+            const int q = base + threadIdx.x;
+            bool keep = false;
+            unsigned a = 0;
+            if(q < nq)
+            {
+                a = key0[(long long)p * cap + q];
+                const unsigned b = key1[(long long)p * cap + q];
+                keep = (double)(float)(a >> 16) < ratio * (double)(float)(b >> 16);
+            }
+            int tot;
+            const int pos = run + block_scan_flag(keep, &tot, s_warp);
+            if(keep)
+            {
+                out_a[(long long)p * cap + pos] = (int)(a & 0xffffu); // fromIndex = trainIdx
+                out_b[(long long)p * cap + pos] = q;                  // toIndex = queryIdx
+                if(out_d)
+                    out_d[(long long)p * cap + pos] = (int)(a >> 16);
+            }
+            run += tot;
+        }
+    if(threadIdx.x == 0)
+        n_out[p] = run;
+}
+
+// mutual-nearest-neighbour compaction (cv::BFMatcher crossCheck=true): key0_q from knn(query, train),
+// key0_t from knn(train, query); ascending query order.
+__global__ void __launch_bounds__(256) k_mutual_compact(const unsigned* __restrict__ key0_q, const unsigned* __restrict__ key0_t,
+                                                        const int* __restrict__ q_counts, const int* __restrict__ t_counts,
+                                                        int cap, int* __restrict__ out_a, int* __restrict__ out_b,
+                                                        int* __restrict__ out_d, int* __restrict__ n_out)
+{
+    __shared__ int s_warp[8];
+    const int p = blockIdx.x;
+    const int nq = min(q_counts[p], cap), nt = min(t_counts[p], cap);
+    int run = 0;
+    if(nt >= 1)
+        for(int base = 0; base < nq; base += 256)
+        {
+            const int q = base + threadIdx.x;
+            bool keep = false;
+            unsigned a = 0;
+            if(q < nq)
+            {
+                a = key0_q[(long long)p * cap + q];
+                const unsigned back = key0_t[(long long)p * cap + (a & 0xffffu)];
+                keep = (int)(back & 0xffffu) == q;
+            }
+            int tot;
+            const int pos = run + block_scan_flag(keep, &tot, s_warp);
+            if(keep)
+            {
+                out_a[(long long)p * cap + pos] = (int)(a & 0xffffu); // trainIdx
+                out_b[(long long)p * cap + pos] = q;                  // queryIdx
+                if(out_d)
+                    out_d[(long long)p * cap + pos] = (int)(a >> 16);
+            }
+            run += tot;
+        }
+    if(threadIdx.x == 0)
+        n_out[p] = run;
+}
+
+// unpack keys to (idx, dist) int arrays for the raw knn2 entry point
+__global__ void k_unpack_knn(const unsigned* __restrict__ key0, const unsigned* __restrict__ key1, int n, int* idx0, int* d0,
+                             int* idx1, int* d1)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if(i >= n)
+        return;
+    const unsigned a = key0[i], b = key1[i];
+    idx0[i] = a == kNoKey ? -1 : (int)(a & 0xffffu);
+    d0[i] = a == kNoKey ? -1 : (int)(a >> 16);
+    idx1[i] = b == kNoKey ? -1 : (int)(b & 0xffffu);
+    d1[i] = b == kNoKey ? -1 : (int)(b >> 16);
+}
+
+// =================================================================================================
+// K10  keyframe-database scoring:
+//   score[q][k] = | match(from = query frame q, to = keyframe k) |
+//   knn query role = keyframe descriptors (registers, DPT per thread), train role = the query frame's
+//   descriptors (whole frame resident in shared memory).  Only distances are needed, so the top-2 is
+//   two integers per descriptor; the ratio test is the integer form 10*d0 < 7*d1 when ratio == 0.7,
+//   else the double comparison.  One CTA walks KF_PER_CTA keyframes against one query frame.
+// =================================================================================================
+constexpr int DB_THREADS = 256;
+
+template <int DPT>
+__global__ void __launch_bounds__(DB_THREADS) k_db_scores(const uint8_t* __restrict__ queries, const int* __restrict__ q_counts,
+                                                          int q_cap, const uint8_t* __restrict__ db,
+                                                          const int* __restrict__ k_counts, int k_cap, int n_keyframes,
+                                                          int kf_per_cta, double ratio, int* __restrict__ scores)
+{
+    extern __shared__ uint4 s_q[]; // q_cap * 2
+    __shared__ int s_red[DB_THREADS / 32];
+    const int qf = blockIdx.y;
+    const int nfrom = min(q_counts[qf], q_cap);
+    const uint4* qv = reinterpret_cast<const uint4*>(queries + (long long)qf * q_cap * 32);
+    for(int i = threadIdx.x; i < nfrom * 2; i += DB_THREADS)
+        s_q[i] = __ldg(qv + i);
+    __syncthreads();
+    const bool int_ratio = ratio == 0.7;
+    const int kf0 = blockIdx.x * kf_per_cta, kf1 = min(kf0 + kf_per_cta, n_keyframes);
+    for(int kf = kf0; kf < kf1; ++kf)
+    {
+        const int nto = min(k_counts[kf], k_cap);
+        const uint4* kv = reinterpret_cast<const uint4*>(db + (long long)kf * k_cap * 32);
+        int cnt = 0;
+        if(nfrom >= 2)
+            for(int base = 0; base < nto; base += DB_THREADS * DPT)
+            {
+                uint4 da[DPT], dbb[DPT];
+                int d0[DPT], d1[DPT];
+#pragma unroll
+                for(int i = 0; i < DPT; ++i)
+                {
+                    const int d = base + i * DB_THREADS + threadIdx.x;
+                    da[i] = d < nto ? __ldg(kv + 2 * d) : make_uint4(0, 0, 0, 0);
+                    dbb[i] = d < nto ? __ldg(kv + 2 * d + 1) : make_uint4(0, 0, 0, 0);
+                    d0[i] = 1 << 20;
+                    d1[i] = 1 << 20;
+                }
+#pragma unroll 2
+                for(int j = 0; j < nfrom; ++j)
+                {
+                    const uint4 ta = s_q[2 * j], tb = s_q[2 * j + 1];
+#pragma unroll
+                    for(int i = 0; i < DPT; ++i)
+                    {
+                        const int d = ham256(da[i], dbb[i], ta, tb);
+                        d1[i] = min(d1[i], max(d0[i], d));
+                        d0[i] = min(d0[i], d);
+                    }
+                }
+#pragma unroll
+                for(int i = 0; i < DPT; ++i)
+                {
+                    const int d = base + i * DB_THREADS + threadIdx.x;
+                    const bool pass = int_ratio ? (10 * d0[i] < 7 * d1[i])
+                                                : ((double)(float)d0[i] < ratio * (double)(float)d1[i]);
+                    cnt += (d < nto) && pass;
+                }
+            }
+#pragma unroll
+        for(int o = 16; o > 0; o >>= 1)
+            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if((threadIdx.x & 31) == 0)
+            s_red[threadIdx.x >> 5] = cnt;
+        __syncthreads();
+        if(threadIdx.x == 0)
+        {
+            int t = 0;
+#pragma unroll
+            for(int w = 0; w < DB_THREADS / 32; ++w)
+                t += s_red[w];
+            scores[(long long)qf * n_keyframes + kf] = t;
+        }
+        __syncthreads();
+    }
+}
+
+// per query frame: top-k of n entries by (score desc, id asc).  Entry e of query q is read through
+// (list = e / per_list, j = e % per_list) at  ((list * list_stride_q) + q) * per_list + j  so the same kernel
+// serves a plain score row (n_lists = 1, ids implicit = id_base + j) and the all-gathered shard lists.
+__global__ void __launch_bounds__(256) k_topk(const int* __restrict__ scores, const int* __restrict__ ids, int n_lists,
+                                              int per_list, int n_queries, int id_base, int k, int* __restrict__ out_score,
+                                              int* __restrict__ out_id)
+{
+    __shared__ unsigned long long s_best[8];
+    __shared__ unsigned long long s_last;
+    const int q = blockIdx.x;
+    const int n = n_lists * per_list;
+    unsigned long long last = ~0ull; // strictly-below bound for the next pick
+    for(int r = 0; r < k; ++r)
+    {
+        unsigned long long best = 0; // 0 = nothing (valid keys are > 0 because score+1 >= 1 sits in the high word)
+        for(int e = threadIdx.x; e < n; e += 256)
+        {
+            const int list = e / per_list, j = e - list * per_list;
+            const long long at = ((long long)list * n_queries + q) * per_list + j;
+            const int sc = scores[at];
+            const int id = ids ? ids[at] : id_base + j;
+            if(sc < 0 || id < 0)
+                continue;
+            const unsigned long long key = ((unsigned long long)(unsigned)(sc + 1) << 32) | (0xffffffffu - (unsigned)id);
+            if(key < last && key > best)
+                best = key;
+        }
+#pragma unroll
+        for(int o = 16; o > 0; o >>= 1)
+        {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other > best ? other : best;
+        }
+        if((threadIdx.x & 31) == 0)
+            s_best[threadIdx.x >> 5] = best;
+        __syncthreads();
+        if(threadIdx.x == 0)
+        {
+            unsigned long long m = 0;
+#pragma unroll
+            for(int w = 0; w < 8; ++w)
+                m = s_best[w] > m ? s_best[w] : m;
+            s_last = m;
+            out_score[(long long)q * k + r] = m ? (int)(m >> 32) - 1 : -1;
+            out_id[(long long)q * k + r] = m ? (int)(0xffffffffu - (unsigned)(m & 0xffffffffu)) : -1;
+        }
+        __syncthreads();
+        last = s_last; // 0 once exhausted: no key is < 0, so every further pick is (-1, -1)
+        __syncthreads();
+    }
+}
+
+// =================================================================================================
+// integer-pipe roofline probes (register-only, all SMs)
+// =================================================================================================
+__global__ void __launch_bounds__(256) k_peak_popc(unsigned* out, int iters)
+{
+    unsigned v[8];
+#pragma unroll
+    for(int i = 0; i < 8; ++i)
+        v[i] = threadIdx.x * 2654435761u + i * 40503u + blockIdx.x;
+    for(int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for(int i = 0; i < 8; ++i)
+            v[i] = __popc(v[i]) + 0x01010101u * (unsigned)i; // POPC feeds the next POPC; the add keeps chains apart
+    }
+    unsigned s = 0;
+#pragma unroll
+    for(int i = 0; i < 8; ++i)
+        s ^= v[i];
+    if(s == 0x12345u)
+        out[0] = s;
+}
+
+__global__ void __launch_bounds__(256) k_peak_lop3(unsigned* out, int iters, unsigned a, unsigned b)
+{
+    unsigned v[8];
+#pragma unroll
+    for(int i = 0; i < 8; ++i)
+        v[i] = threadIdx.x * 2654435761u + i * 40503u + blockIdx.x;
+    for(int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for(int i = 0; i < 8; ++i)
+            v[i] = v[i] ^ (a & v[(i + 1) & 7]); // one LOP3 per result (3-input function)
+    }
+    unsigned s = 0;
+#pragma unroll
+    for(int i = 0; i < 8; ++i)
+        s ^= v[i];
+    if(s == 0x12345u)
+        out[0] = s;
+}
+
+// the plain pair sequence: 8 x (xor, popc) + adds, 4 pairs per iteration, operands in registers
+__global__ void __launch_bounds__(256) k_peak_pairs(unsigned* out, int iters)
+{
+    unsigned q[8], t[8];
+#pragma unroll
+    for(int i = 0; i < 8; ++i)
+    {
+        q[i] = threadIdx.x * 2654435761u + i * 40503u;
+        t[i] = blockIdx.x * 2246822519u + i * 3266489917u;
+    }
+    unsigned best = 0xffffffffu;
+    for(int it = 0; it < iters; ++it)
+    {
+        unsigned d = 0;
+#pragma unroll
+        for(int i = 0; i < 8; ++i)
+            d += __popc(q[i] ^ t[i] ^ (unsigned)it); // 3-input xor = one LOP3
+        best = min(best, d);
+        t[0] += d; // keep a train operand data-dependent so the loop cannot be collapsed
+    }
+    if(best == 0x12345u)
+        out[0] = best;
+}
+
+__global__ void k_clock_probe(long long* out)
+{
+    // SM cycles and nanoseconds across a fixed spin, for the MHz estimate
+    const long long c0 = clock64();
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    unsigned v = threadIdx.x;
+    for(int i = 0; i < 200000; ++i)
+        v = v * 1664525u + 1013904223u;
+    const long long c1 = clock64();
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+    if(threadIdx.x == 0 && blockIdx.x == 0)
+    {
+        out[0] = c1 - c0;
+        out[1] = (long long)(t1 - t0);
+        out[2] = v;
+    }
+}
+
+// =================================================================================================
+// launchers
+// =================================================================================================
+void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
+                 unsigned* key0, unsigned* key1, long long* launches)
+{
+    constexpr int QPT = 2;
+    dim3 grd((cap + KNN_THREADS * QPT - 1) / (KNN_THREADS * QPT), n_pairs);
+    k_knn2<QPT><<<grd, KNN_THREADS, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+    ++*launches;
+}
+
+void launch_ratio_compact(cudaStream_t st, const unsigned* key0, const unsigned* key1, const int* qn, const int* tn,
+                          int n_pairs, int cap, double ratio, int* out_a, int* out_b, int* out_d, int* n_out,
+                          long long* launches)
+{
+    k_ratio_compact<<<n_pairs, 256, 0, st>>>(key0, key1, qn, tn, cap, ratio, out_a, out_b, out_d, n_out);
+    ++*launches;
+}
+
+void launch_mutual_compact(cudaStream_t st, const unsigned* key0_q, const unsigned* key0_t, const int* qn, const int* tn,
+                           int n_pairs, int cap, int* out_a, int* out_b, int* out_d, int* n_out, long long* launches)
+{
+    k_mutual_compact<<<n_pairs, 256, 0, st>>>(key0_q, key0_t, qn, tn, cap, out_a, out_b, out_d, n_out);
+    ++*launches;
+}
+
+void launch_unpack_knn(cudaStream_t st, const unsigned* key0, const unsigned* key1, int n, int* idx0, int* d0, int* idx1,
+                       int* d1, long long* launches)
+{
+    k_unpack_knn<<<(n + 255) / 256, 256, 0, st>>>(key0, key1, n, idx0, d0, idx1, d1);
+    ++*launches;
+}
+
+cudaError_t launch_db_scores(cudaStream_t st, const uint8_t* queries, const int* q_counts, int nq_frames, int q_cap,
+                             const uint8_t* db, const int* k_counts, int n_keyframes, int k_cap, double ratio, int* scores,
+                             int sm_count, long long* launches)
+{
+    constexpr int DPT = 4;
+    const size_t smem = (size_t)q_cap * 32;
+    static size_t configured = 0;
+    if(smem > configured)
+    {
+        cudaError_t e =
+            cudaFuncSetAttribute(k_db_scores<DPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if(e != cudaSuccess)
+            return e;
+        configured = smem;
+    }
+    // enough CTAs to fill the machine a few times over, but long enough walks to amortise the query-frame load
+    int kf_per_cta = 8;
+    while(kf_per_cta > 1 && (long long)((n_keyframes + kf_per_cta - 1) / kf_per_cta) * nq_frames < 4LL * sm_count)
+        kf_per_cta >>= 1;
+    dim3 grd((n_keyframes + kf_per_cta - 1) / kf_per_cta, nq_frames);
+    k_db_scores<DPT><<<grd, DB_THREADS, smem, st>>>(queries, q_counts, q_cap, db, k_counts, k_cap, n_keyframes, kf_per_cta,
+                                                    ratio, scores);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists, int per_list, int n_queries, int id_base,
+                 int k, int* out_score, int* out_id, long long* launches)
+{
+    k_topk<<<n_queries, 256, 0, st>>>(scores, ids, n_lists, per_list, n_queries, id_base, k, out_score, out_id);
+    ++*launches;
+}
+
+cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long long* launches)
+{
+    unsigned* d_out = nullptr;
+    long long* d_clk = nullptr;
+    cudaError_t e = cudaMalloc(&d_out, 64);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaMalloc(&d_clk, 64);
+    if(e != cudaSuccess)
+        return e;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int grid = sm_count * 8, iters = 4096;
+    float ms[3] = {0, 0, 0};
+    for(int which = 0; which < 3; ++which)
+    {
+        for(int rep = 0; rep < 3; ++rep) // last repetition is the one kept (warm clocks)
+        {
+            cudaEventRecord(e0, st);
+            if(which == 0)
+                k_peak_popc<<<grid, 256, 0, st>>>(d_out, iters);
+            else if(which == 1)
+                k_peak_lop3<<<grid, 256, 0, st>>>(d_out, iters, 0x9e3779b9u, 0x7f4a7c15u);
+            else
+                k_peak_pairs<<<grid, 256, 0, st>>>(d_out, iters);
+            cudaEventRecord(e1, st);
+            cudaEventSynchronize(e1);
+            cudaEventElapsedTime(&ms[which], e0, e1);
+            ++*launches;
+        }
+    }
+    k_clock_probe<<<1, 32, 0, st>>>(d_clk);
+    ++*launches;
+    long long h_clk[3] = {0, 1, 0};
+    e = cudaMemcpyAsync(h_clk, d_clk, sizeof(h_clk), cudaMemcpyDeviceToHost, st);
+    cudaStreamSynchronize(st);
+    const double threads = (double)grid * 256.0;
+    out4[0] = threads * iters * 8.0 / (ms[0] * 1e-3);
+    out4[1] = threads * iters * 8.0 / (ms[1] * 1e-3);
+    out4[2] = threads * iters / (ms[2] * 1e-3);
+    out4[3] = h_clk[1] > 0 ? (double)h_clk[0] / (double)h_clk[1] * 1e3 : 0.0;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d_out);
+    cudaFree(d_clk);
+    return e == cudaSuccess ? cudaGetLastError() : e;
+}
+
+} // namespace mslam_b200

@@ -1,0 +1,269 @@
+"""ctypes wrapper round oracle/liborb_oracle.so -- TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this
+module.  The product (modular-slam_b200) never does.  See the header of orb_oracle.c for what the
+oracle restates (reference: src/lib/modular_slam/orb_feature.cpp:33-65,84-117; frame.cpp:6-27) and how
+it is pinned.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liborb_oracle.so")
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "orb_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return _SO
+
+
+class Params(C.Structure):
+    _fields_ = [("nfeatures", C.c_int), ("nlevels", C.c_int), ("fast_threshold", C.c_int), ("edge", C.c_int),
+                ("scale_factor", C.c_float)]
+
+
+class Dumps(C.Structure):
+    _fields_ = [("pyr", C.c_void_p), ("blurred", C.c_void_p), ("n_fast", C.c_void_p), ("n_cut1", C.c_void_p)]
+
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4")])
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        try:
+            _lib = C.CDLL(_SO)
+        except OSError:
+            build(force=True)
+            _lib = C.CDLL(_SO)
+        _lib.orc_harris.restype = C.c_float
+        _lib.orc_fast_atan2.restype = C.c_float
+        _lib.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        _lib.orc_ic_angle.restype = C.c_float
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def default_params(nfeatures=1000, nlevels=8, scale_factor=1.2, fast_threshold=20, edge=31):
+    return Params(nfeatures, nlevels, fast_threshold, edge, scale_factor)
+
+
+def level_geometry(W, H, nlevels=8, scale_factor=1.2):
+    w = np.zeros(nlevels, np.int32)
+    h = np.zeros(nlevels, np.int32)
+    s = np.zeros(nlevels, np.float32)
+    lib().orc_level_geometry(W, H, nlevels, C.c_float(scale_factor), _p(w), _p(h), _p(s))
+    return w, h, s
+
+
+def features_per_level(nfeatures=1000, nlevels=8, scale_factor=1.2):
+    n = np.zeros(nlevels, np.int32)
+    lib().orc_features_per_level(nfeatures, nlevels, C.c_float(scale_factor), _p(n))
+    return n
+
+
+def gray(rgb):
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    out = np.empty(rgb.shape[:-1], np.uint8)
+    lib().orc_gray(_p(rgb), C.c_long(out.size), _p(out))
+    return out
+
+
+def resize_coeffs(src, dst):
+    ofs = np.zeros(dst, np.int32)
+    a1 = np.zeros(dst, np.int32)
+    lib().orc_resize_coeffs(src, dst, _p(ofs), _p(a1))
+    return ofs, a1
+
+
+def resize_exact(img, dw, dh):
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_exact(_p(img), img.shape[1], img.shape[0], _p(out), dw, dh)
+    return out
+
+
+def fast_score_map(img, thr=20):
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty_like(img)
+    lib().orc_fast_score_map(_p(img), img.shape[1], img.shape[0], thr, _p(out))
+    return out
+
+
+def fast_nms_border(score, edge=31):
+    score = np.ascontiguousarray(score, np.uint8)
+    cap = score.size // 4 + 16
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orc_fast_nms_border(_p(score), score.shape[1], score.shape[0], edge, _p(out), cap)
+    return out[:n].copy()
+
+
+def harris(img, x, y):
+    img = np.ascontiguousarray(img, np.uint8)
+    return np.float32(lib().orc_harris(_p(img), img.shape[1], int(x), int(y)))
+
+
+def ic_angle(img, x, y):
+    img = np.ascontiguousarray(img, np.uint8)
+    return np.float32(lib().orc_ic_angle(_p(img), img.shape[1], int(x), int(y)))
+
+
+def fast_atan2(y, x):
+    return np.float32(lib().orc_fast_atan2(float(y), float(x)))
+
+
+def blur7(img):
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty_like(img)
+    lib().orc_blur7(_p(img), img.shape[1], img.shape[0], _p(out))
+    return out
+
+
+def describe(blurred, cx, cy, angle_deg):
+    blurred = np.ascontiguousarray(blurred, np.uint8)
+    out = np.empty(32, np.uint8)
+    lib().orc_describe(_p(blurred), blurred.shape[1], int(cx), int(cy), C.c_float(angle_deg), _p(out))
+    return out
+
+
+def orb_detect_gray(gray_img, params=None, cap=None, dumps=False):
+    """-> (keypoints[KP_DTYPE], descriptors[N,32]) in canonical (octave, y, x) order.
+    dumps=True additionally returns a dict with pyramid levels, blurred levels, n_fast, n_cut1."""
+    g = np.ascontiguousarray(gray_img, np.uint8)
+    H, W = g.shape
+    prm = params or default_params()
+    cap = cap or max(4 * prm.nfeatures, 64)
+    kps = np.zeros(cap, KP_DTYPE)
+    desc = np.zeros((cap, 32), np.uint8)
+    d = None
+    extra = None
+    if dumps:
+        w, h, _ = level_geometry(W, H, prm.nlevels, prm.scale_factor)
+        tot = int((w.astype(np.int64) * h).sum())
+        pyr = np.zeros(tot, np.uint8)
+        blr = np.zeros(tot, np.uint8)
+        nf = np.zeros(prm.nlevels, np.int32)
+        nc = np.zeros(prm.nlevels, np.int32)
+        d = Dumps(_p(pyr).value, _p(blr).value, _p(nf).value, _p(nc).value)
+        extra = (w, h, pyr, blr, nf, nc)
+    n = lib().orc_orb_detect_gray(_p(g), W, H, C.byref(prm), _p(kps), _p(desc), cap, C.byref(d) if d else None)
+    if n > cap:
+        return orb_detect_gray(g, prm, cap=n, dumps=dumps)
+    if not dumps:
+        return kps[:n].copy(), desc[:n].copy()
+    w, h, pyr, blr, nf, nc = extra
+    offs = np.concatenate([[0], np.cumsum(w.astype(np.int64) * h)])
+    out = {
+        "pyr": [pyr[offs[l]:offs[l + 1]].reshape(h[l], w[l]) for l in range(prm.nlevels)],
+        "blurred": [blr[offs[l]:offs[l + 1]].reshape(h[l], w[l]) for l in range(prm.nlevels)],
+        "n_fast": nf, "n_cut1": nc,
+    }
+    return kps[:n].copy(), desc[:n].copy(), out
+
+
+def orb_detect_rgb(rgb, params=None, cap=None):
+    """OrbOpenCvDetector::detect restated (gray conversion in memory order, then ORB)."""
+    return orb_detect_gray(gray(rgb), params, cap)
+
+
+def orb_detect_rgb_batch(frames, params=None, cap=None, nthreads=1):
+    frames = np.ascontiguousarray(frames, np.uint8)
+    B, H, W, _ = frames.shape
+    prm = params or default_params()
+    cap = cap or 2 * prm.nfeatures
+    kps = np.zeros((B, cap), KP_DTYPE)
+    desc = np.zeros((B, cap, 32), np.uint8)
+    counts = np.zeros(B, np.int32)
+    lib().orc_orb_detect_rgb_batch(_p(frames), B, W, H, C.byref(prm), _p(kps), _p(desc), cap, _p(counts), nthreads)
+    assert (counts <= cap).all(), "oracle batch capacity exceeded"
+    return kps, desc, counts
+
+
+def _desc_view(d):
+    d = np.asarray(d)
+    assert d.dtype == np.uint8 and d.ndim == 2 and d.shape[1] >= 32
+    if d.strides[1] != 1:
+        d = np.ascontiguousarray(d)
+    return d, d.strides[0]
+
+
+def knn2(query, train):
+    q, qs = _desc_view(query)
+    t, ts = _desc_view(train)
+    nq, nt = q.shape[0], t.shape[0]
+    out = np.zeros((4, nq), np.int32)
+    lib().orc_knn2(_p(q), nq, qs, _p(t), nt, ts, _p(out[0]), _p(out[1]), _p(out[2]), _p(out[3]))
+    return out[0], out[1], out[2], out[3]  # idx0, d0, idx1, d1
+
+
+def match_ratio(frm, to, ratio=0.7):
+    """OrbOpenCvMatcher::match(from, to) -> (fromIndex[int64], toIndex[int64], dist[int32])."""
+    f, fs = _desc_view(frm) if len(frm) else (np.zeros((0, 32), np.uint8), 32)
+    t, ts = _desc_view(to) if len(to) else (np.zeros((0, 32), np.uint8), 32)
+    nt = t.shape[0]
+    fi = np.zeros(max(nt, 1), np.int64)
+    ti = np.zeros(max(nt, 1), np.int64)
+    di = np.zeros(max(nt, 1), np.int32)
+    n = lib().orc_match_ratio(_p(f), f.shape[0], fs, _p(t), nt, ts, C.c_double(ratio), _p(fi), _p(ti), _p(di))
+    return fi[:n].copy(), ti[:n].copy(), di[:n].copy()
+
+
+def match_crosscheck(query, train):
+    q, qs = _desc_view(query) if len(query) else (np.zeros((0, 32), np.uint8), 32)
+    t, ts = _desc_view(train) if len(train) else (np.zeros((0, 32), np.uint8), 32)
+    nq = q.shape[0]
+    qi = np.zeros(max(nq, 1), np.int32)
+    ti = np.zeros(max(nq, 1), np.int32)
+    di = np.zeros(max(nq, 1), np.int32)
+    n = lib().orc_match_crosscheck(_p(q), nq, qs, _p(t), t.shape[0], ts, _p(qi), _p(ti), _p(di))
+    return qi[:n].copy(), ti[:n].copy(), di[:n].copy()
+
+
+def db_scores(queries, q_counts, db, k_counts, nthreads=1):
+    """queries [Q, qcap, 32], db [K, kcap, 32] -> scores [Q, K] (int32)."""
+    queries = np.ascontiguousarray(queries, np.uint8)
+    db = np.ascontiguousarray(db, np.uint8)
+    qc = np.ascontiguousarray(q_counts, np.int32)
+    kc = np.ascontiguousarray(k_counts, np.int32)
+    Q, qcap, _ = queries.shape
+    K, kcap, _ = db.shape
+    out = np.zeros((Q, K), np.int32)
+    lib().orc_db_scores(_p(queries), Q, _p(qc), qcap, _p(db), K, _p(kc), kcap, _p(out), nthreads)
+    return out
+
+
+def db_topk(scores, k, id_base=0):
+    scores = np.ascontiguousarray(scores, np.int32)
+    Q, K = scores.shape
+    os_ = np.zeros((Q, k), np.int32)
+    oi = np.zeros((Q, k), np.int32)
+    lib().orc_db_topk(_p(scores), Q, K, id_base, k, _p(os_), _p(oi))
+    return os_, oi
+
+
+def match_ratio_batch(frm, nfrom, to, nto, nthreads=1):
+    frm = np.ascontiguousarray(frm, np.uint8)
+    to = np.ascontiguousarray(to, np.uint8)
+    P, cap, _ = frm.shape
+    assert to.shape == frm.shape
+    nf = np.ascontiguousarray(nfrom, np.int32)
+    nt = np.ascontiguousarray(nto, np.int32)
+    fi = np.zeros((P, cap), np.int64)
+    ti = np.zeros((P, cap), np.int64)
+    di = np.zeros((P, cap), np.int32)
+    cnt = np.zeros(P, np.int32)
+    lib().orc_match_ratio_batch(_p(frm), _p(nf), _p(to), _p(nt), P, cap, _p(fi), _p(ti), _p(di), _p(cnt), nthreads)
+    return fi, ti, di, cnt
