@@ -77,8 +77,9 @@ static void level_geometry(int W, int H, int nlevels, float scale_factor, int* w
     {
         const float s = (float)pow((double)scale_factor, (double)l);
         scale[l] = s;
-        w[l] = (int)lrintf((float)W / s);
-        h[l] = (int)lrintf((float)H / s);
+        const float inv = 1.f / s; // cv::ORB multiplies by the f32 reciprocal (237 rows -> 198 at level 1, not 197)
+        w[l] = (int)lrintf((float)W * inv);
+        h[l] = (int)lrintf((float)H * inv);
     }
 }
 

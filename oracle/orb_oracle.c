@@ -52,8 +52,11 @@ ORC_API void orc_level_geometry(int W, int H, int nlevels, float scale_factor, i
     {
         float s = (float)pow((double)scale_factor, (double)l);
         scale[l] = s;
-        w[l] = cv_round_f((float)W / s);
-        h[l] = cv_round_f((float)H / s);
+        /* orb.cpp: float inv_scale = 1.f / scale; Size sz(cvRound(cols * inv_scale), cvRound(rows * inv_scale)).
+         * Pinned by tests/golden/synthetic.npz (237 rows -> 198 at level 1; a division would give 197). */
+        float inv = 1.f / s;
+        w[l] = cv_round_f((float)W * inv);
+        h[l] = cv_round_f((float)H * inv);
     }
 }
 

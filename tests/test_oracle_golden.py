@@ -99,7 +99,7 @@ def test_level_geometry_and_budget(oracle):
     w, h, s = oracle.level_geometry(640, 480)
     assert list(zip(w.tolist(), h.tolist())) == [(640, 480), (533, 400), (444, 333), (370, 278), (309, 231), (257, 193),
                                                  (214, 161), (179, 134)]
-    assert [x.tobytes().hex() for x in s.astype(">f4")] == ["3f800000", "3f99999a", "3fb851ec", "3fdd2f1c", "4004b5de",
+    assert ["%08x" % v for v in s.view(np.uint32)] == ["3f800000", "3f99999a", "3fb851ec", "3fdd2f1c", "4004b5de",
                                                             "401f40a5", "403f1a60", "406552da"]
     assert oracle.features_per_level(1000).tolist() == [217, 181, 151, 126, 105, 87, 73, 60]
     assert oracle.features_per_level(2000).tolist() == [434, 362, 302, 251, 209, 175, 145, 122]
