@@ -1,0 +1,393 @@
+#!/usr/bin/env python
+"""bench.py -- the headline benchmark of BASELINE.json: ORB extract + match frames/s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5] [--impl reference]
+
+N > 1 is launched by the driver under torch.distributed.run (one rank per GPU).
+
+A *step* is one pass of the hot path over one batch of synthetic input:
+  c2 (default, the config BASELINE.json's metric is quoted on): 64 independent 640x480 sequences, frame t of each:
+     detect (1000 kp, 8 levels) + kNN/ratio match of the current frame against the previous frame of its sequence.
+  c3: 1280x720, 2000 kp, cross-checked matching, batch 32.     c4: 1920x1080, 4000 kp, batch 16.
+  c5: keyframe-database scoring (reported as descriptor pairs/s): DB shard per GPU, per-query top-k, NCCL all-gather merge.
+Frames are sharded across GPUs as independent replicas (no data-path collective) -> weak scaling.
+
+value   : whole-job frames/s with the inputs resident in HBM when the timed region starts (device entry points).
+e2e     : the same metric through the host entry points of the C ABI (what the C++ plugin adapter calls): HOST frames in,
+          HOST keypoints / descriptors / matches out, H2D + D2H inside the timed region.
+roofline: the dominant kernel group of the step, algorithmic bytes / CUDA-event duration measured live.
+cpu_baseline: the CPU oracle port (oracle/orb_oracle.c, OpenMP over frames) timed on this box's host cores on a bounded
+          sample of the same workload.  `--impl reference` times that CPU path alone (the reference cannot be compiled here:
+          it needs OpenCV/Eigen/Boost headers) and prints the same JSON line with "impl": "reference".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as graft  # noqa: E402
+
+WORKLOADS = {
+    # name: (W, H, nfeatures, frames per GPU per step, match mode (0 ratio, 1 cross-check), label)
+    "c2": (640, 480, 1000, 64, 0, "configs[1]: synthetic 640x480 stream, 64-frame batch, ORB 1000 kp / 8 levels + kNN ratio match"),
+    "c3": (1280, 720, 2000, 32, 1, "configs[2]: synthetic 1280x720, ORB 2000 kp / 8 levels + cross-checked match"),
+    "c4": (1920, 1080, 4000, 16, 0, "configs[3]: synthetic 1920x1080, ORB 4000 kp / 8 levels + kNN ratio match"),
+}
+N_TIMESTEPS = 4  # distinct input batches rotated through the timed region (together larger than the 126 MB L2 for c2..c4)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(self.idx)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, r[5:9]):
+                if v.strip().lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_inputs(pkg, W, H, n_seq, rank, steps_needed):
+    """frames[t] for t = 0..N_TIMESTEPS (t = 0 primes the 'previous frame'); seeded per rank"""
+    T = min(N_TIMESTEPS, max(steps_needed, 1)) + 1
+    bases = None
+    out = []
+    for t in range(T):
+        fr, bases = pkg.synth.frame_batch(W, H, n_seq, t, seed=1234 + 100003 * rank, bases=bases)
+        out.append(fr)
+    return out
+
+
+def algorithmic_bytes_per_frame(w, h, W, H, n_kp):
+    """3WH input + pyramid write + blurred pyramid write + N*56 out"""
+    px = int((w.astype(np.int64) * h).sum())
+    return 3 * W * H + 2 * px + n_kp * 56, px
+
+
+def cpu_port_time(pkg, O, frames_prev, frames_cur, nfeat, mode, threads):
+    """one bounded sample of the workload on the CPU oracle port: detect both batches' current frame + match"""
+    prm = O.default_params(nfeat)
+    t0 = time.perf_counter()
+    kp1, d1, c1 = O.orb_detect_rgb_batch(frames_cur, prm, cap=2 * nfeat, nthreads=threads)
+    t_det = time.perf_counter() - t0
+    kp0, d0, c0 = O.orb_detect_rgb_batch(frames_prev, prm, cap=2 * nfeat, nthreads=threads)  # untimed: previous frame
+    t1 = time.perf_counter()
+    if mode == 0:
+        O.match_ratio_batch(d1, c1, d0, c0, nthreads=threads)
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(lambda p: O.match_crosscheck(d0[p, :c0[p]], d1[p, :c1[p]]), range(len(c0))))
+    t_match = time.perf_counter() - t1
+    return t_det + t_match, t_det, t_match
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU path alone (oracle port: the reference itself cannot be compiled in this image)"""
+    if rank != 0:
+        return
+    pkg = graft.load_package()
+    from oracle import oracle as O
+    W, H, nfeat, _, mode, label = WORKLOADS[args.workload if args.workload in WORKLOADS else "c2"]
+    threads = os.cpu_count() or 1
+    n_sample = max(threads, 8)  # frames per step: one per host thread
+    n_sample = min(n_sample, 64)
+    fr = make_inputs(pkg, W, H, n_sample, 0, 1)
+    for _ in range(args.warmup):
+        cpu_port_time(pkg, O, fr[0], fr[1], nfeat, mode, threads)
+    t = [cpu_port_time(pkg, O, fr[0], fr[1], nfeat, mode, threads)[0] for _ in range(args.steps)]
+    total = float(np.sum(t))
+    v = n_sample * args.steps / total
+    line = {"metric": "ORB extract+match frames/sec", "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
+            "config": {"workload": label, "frame": [W, H], "nfeatures": nfeat, "nlevels": 8, "batch_per_step": n_sample},
+            "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port",
+                             "sample": f"{n_sample} frames per step (detect + match vs previous frame), OpenMP over frames"},
+            "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+    if args.workload == "c5":
+        import bench_db
+        return bench_db.main(args, rank, world, local)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = graft.load_package()
+    W, H, nfeat, B, mode, label = WORKLOADS[args.workload]
+    frames = make_inputs(pkg, W, H, B, rank, args.steps)
+    T = len(frames) - 1
+    stream = torch.cuda.Stream()  # a real (non-default) stream: the context runs on it, torch events see it
+    torch.cuda.set_stream(stream)
+    ctx = pkg.Context(device=local, max_width=W, max_height=H, max_batch=B, nfeatures=nfeat, stream=stream.cuda_stream)
+    cap = ctx.kp_cap
+    w, h, sc, n_l = ctx.level_geometry(W, H)
+    bytes_per_frame, pyr_px = algorithmic_bytes_per_frame(w, h, W, H, nfeat)
+
+    # ---- device-resident inputs and outputs --------------------------------------------------------------------------
+    d_frames = [torch.from_numpy(f).cuda() for f in frames]
+    d_kp = [torch.zeros((B, cap, 6), dtype=torch.float32, device="cuda") for _ in range(2)]
+    d_desc = [torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda") for _ in range(2)]
+    d_cnt = [torch.zeros(B, dtype=torch.int32, device="cuda") for _ in range(2)]
+    d_ma = torch.zeros((B, cap), dtype=torch.int32, device="cuda")
+    d_mb = torch.zeros_like(d_ma)
+    d_md = torch.zeros_like(d_ma)
+    d_mn = torch.zeros(B, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+
+    def step_dev(t, cur):
+        prev = cur ^ 1
+        ctx.detect_batch_dev(d_frames[t], B, W, H, d_kp[cur], d_desc[cur], cap, d_cnt[cur])
+        # matcher->match(first = current frame, second = previous frame / keyframe)  rgbd_feature_frontend.cpp:237
+        ctx.match_batch_dev(mode, d_desc[cur], d_cnt[cur], d_desc[prev], d_cnt[prev], B, cap, d_ma, d_mb, d_md, d_mn)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # prime "previous frame", warm up
+    ctx.detect_batch_dev(d_frames[0], B, W, H, d_kp[0], d_desc[0], cap, d_cnt[0])
+    cur = 1
+    for i in range(args.warmup):
+        step_dev(1 + i % T, cur)
+        cur ^= 1
+    barrier()
+    n_matches_check = int(d_mn.sum().item())
+    n_kp_check = int(d_cnt[cur ^ 1].sum().item())
+
+    # ---- timed region: K steps, inputs resident in HBM ---------------------------------------------------------------
+    ctx.enable_stage_timing(True)
+    launches0 = ctx.launch_count
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for i in range(args.steps):
+        step_dev(1 + i % T, cur)
+        cur ^= 1
+    e1.record(stream)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    gpu_launches = ctx.launch_count - launches0
+    stage = ctx.stage_times()
+    ctx.enable_stage_timing(False)
+    if world > 1:
+        tt = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    frames_total = B * args.steps * world
+    value = frames_total / (ms_total * 1e-3)
+
+    # ---- end to end through the host entry points (pinned host buffers) ------------------------------------------------
+    h_frames = [pkg.pinned_empty(f.shape, np.uint8) for f in frames]
+    for hf, f in zip(h_frames, frames):
+        hf[...] = f
+    h_kp = [pkg.pinned_empty((B, cap), pkg.KP_DTYPE) for _ in range(2)]
+    h_desc = [pkg.pinned_empty((B, cap, 32), np.uint8) for _ in range(2)]
+    h_cnt = [pkg.pinned_empty((B,), np.int32) for _ in range(2)]
+    h_m = [pkg.pinned_empty((B, cap), np.int32) for _ in range(3)] + [pkg.pinned_empty((B,), np.int32)]
+
+    def step_host(t, cur):
+        prev = cur ^ 1
+        ctx.detect_batch(h_frames[t], cap, out=(h_kp[cur], h_desc[cur], h_cnt[cur]))
+        ctx.match_batch(mode, h_desc[cur], h_cnt[cur], h_desc[prev], h_cnt[prev], out=tuple(h_m))
+
+    ctx.detect_batch(h_frames[0], cap, out=(h_kp[0], h_desc[0], h_cnt[0]))
+    cur = 1
+    for i in range(args.warmup):
+        step_host(1 + i % T, cur)
+        cur ^= 1
+    barrier()
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for i in range(args.steps):
+        step_host(1 + i % T, cur)
+        cur ^= 1
+    e1.record(stream)
+    barrier()
+    e2e_ms = max(e0.elapsed_time(e1), 0.0)
+    e2e_wall = (time.perf_counter() - t0) * 1e3
+    e2e_ms = max(e2e_ms, e2e_wall)  # host entry points are synchronous: wall clock is the honest figure
+    if world > 1:
+        tt = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt.item())
+    e2e_value = frames_total / (e2e_ms * 1e-3)
+    h2d = int(B * W * H * 3 + 2 * B * cap * 32 + 2 * B * 4)
+    d2h = int(B * cap * (24 + 32) + 2 * B * 4 + 3 * B * cap * 4 + B * 4)
+    # host results must equal the device-resident run's
+    assert int(h_m[3].sum()) > 0 and int(h_cnt[cur ^ 1].sum()) >= B * nfeat // 2
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel group ---------------------------------------------------------------------------
+    pk, pk_kind = peaks()
+    det_stages = {k: v for k, v in stage.items() if v[1] > 0}
+    dom = max(det_stages, key=lambda k: det_stages[k][0])
+    per_launch_bytes = {  # algorithmic bytes one bracketed interval of the stage moves, per batch of B frames
+        "gray": B * (3 * W * H + W * H),
+        "resize": B * (2 * pyr_px - W * H - int(w[-1]) * int(h[-1])),
+        "fast": B * pyr_px,
+        "blur": B * 2 * pyr_px,
+        "select": B * nfeat * 8 * 4,
+        "describe": B * nfeat * 56,
+    }
+    roofs = {}
+    for k, (ms, n_iv, n_l) in det_stages.items():
+        avg_ms = ms / n_iv
+        entry = {"ms_per_step": avg_ms, "launches_per_step": n_l / n_iv, "share": ms / ms_total}
+        if k in per_launch_bytes:
+            ach = per_launch_bytes[k] / (avg_ms * 1e-3) / 1e9
+            entry.update({"bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"]})
+        elif k == "knn":
+            pairs = B * float(nfeat) ** 2 * (2 if mode == 1 else 1)
+            entry.update({"bound": "int-pipe (popc)", "achieved": pairs / (avg_ms * 1e-3) / 1e9, "unit": "Gpair/s"})
+        roofs[k] = entry
+    d = roofs[dom]
+    if "frac" in d:
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": d["achieved"], "peak": d["peak"], "unit": "GB/s", "frac": d["frac"],
+                    "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({pk_kind})",
+                    "algorithmic_bytes_per_launch_group": per_launch_bytes[dom]}
+    else:
+        ip = ctx.measure_int_peaks()
+        peak_pairs = ip["popc32_per_s"] / 8.0 / 1e9
+        roofline = {"bound": "int-pipe (popc); not hbm/tensor: 8 POPC.32 per 256-bit pair", "kernel": dom, "achieved": d["achieved"],
+                    "peak": peak_pairs, "unit": "Gpair/s", "frac": d["achieved"] / peak_pairs, "traffic": None,
+                    "peak_source": "register-only POPC loop measured in this run (mslam_b200_measure_int_peaks)"}
+    whole = bytes_per_frame * B * args.steps / (ms_total * 1e-3) / 1e9
+    roofline["whole_step_hbm"] = {"achieved": whole, "frac": whole / pk["hbm_gbs"], "bytes_per_frame": bytes_per_frame}
+    roofline["stages"] = roofs
+
+    # ---- CPU baseline on a bounded sample ------------------------------------------------------------------------------------
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import oracle as O
+        threads = os.cpu_count() or 1
+        ns = min(B, max(8, threads))
+        t_one, t_det, t_match = cpu_port_time(pkg, O, frames[0][:ns], frames[1][:ns], nfeat, mode, threads)
+        reps = int(max(1, min(20, args.cpu_seconds / max(t_one, 1e-3))))
+        ts = [cpu_port_time(pkg, O, frames[0][:ns], frames[1][:ns], nfeat, mode, threads) for _ in range(reps)]
+        best = min(x[0] for x in ts)
+        t1 = cpu_port_time(pkg, O, frames[0][:ns], frames[1][:ns], nfeat, mode, 1)[0] if ns <= 16 else None
+        cpu = {"value": ns / best, "unit": "frames/s", "cores": threads, "kind": "port",
+               "sample": f"{ns} frames (detect + match vs previous frame) x {reps} repetitions, best; OpenMP over frames",
+               "detect_ms_per_frame_per_thread": float(np.median([x[1] for x in ts])) / ns * min(threads, ns) * 1e3,
+               "match_ms_per_pair_per_thread": float(np.median([x[2] for x in ts])) / ns * min(threads, ns) * 1e3}
+        if t1:
+            cpu["single_thread_frames_per_s"] = ns / t1
+        try:  # informational: OpenCV itself (the library the reference calls), if importable on this box
+            import cv2
+            cv2.setNumThreads(threads)
+            orb, bf = cv2.ORB_create(nfeat), cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=(mode == 1))
+            g0, g1 = O.gray(frames[0][0]), O.gray(frames[1][0])
+            k0, q0 = orb.detectAndCompute(g0, None)
+            best_cv = 1e9
+            for _ in range(5):
+                tc = time.perf_counter()
+                k1, q1 = orb.detectAndCompute(O.gray(frames[1][0]), None)
+                (bf.match(q0, q1) if mode == 1 else bf.knnMatch(q0, q1, 2))
+                best_cv = min(best_cv, time.perf_counter() - tc)
+            cpu["cv2_frames_per_s"] = 1.0 / best_cv
+            cpu["cv2_version"] = cv2.__version__
+        except Exception as ex:  # pragma: no cover
+            cpu["cv2_frames_per_s"] = None
+            cpu["cv2_note"] = str(ex)[:80]
+
+    line = {"metric": "ORB extract+match frames/sec", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": label, "frame": [W, H], "nfeatures": nfeat, "nlevels": 8, "batch_per_gpu": B,
+                       "match": "crosscheck" if mode else "knn2+ratio0.7", "parallelism": f"frame-batch replicas x{world}",
+                       "l2": f"inputs rotate over {T} distinct batches ({T * B * W * H * 3 / 1e6:.0f} MB/GPU) + pyramids; "
+                             "working set per step > L2 is not guaranteed for c2 (59 MB frames + 2x61 MB pyramids = 181 MB > 126 MB)",
+                       "keypoints_per_batch_check": n_kp_check, "matches_per_batch_check": n_matches_check},
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

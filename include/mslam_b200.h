@@ -185,10 +185,32 @@ typedef enum mslam_b200_stage
 } mslam_b200_stage;
 /* copy an intermediate of the LAST detect call (frame index in that batch, level) to host memory */
 MSLAM_B200_API int mslam_b200_debug_read(mslam_b200_ctx* ctx, int stage, int frame, int level, void* out, size_t bytes);
+/* Per-stage device timing (tracing aid for bench.py's roofline): when enabled, every stage of the detect / match
+ * entry points is bracketed by CUDA events on the context's stream.  mslam_b200_stage_times synchronises the
+ * stream, folds the recorded intervals into per-stage totals since the last call and resets them. */
+typedef enum mslam_b200_timed_stage
+{
+    MSLAM_B200_T_GRAY = 0,     /* toGrayScale -> level 0 */
+    MSLAM_B200_T_RESIZE = 1,   /* chained INTER_LINEAR_EXACT levels 1..n-1 */
+    MSLAM_B200_T_FAST = 2,     /* FAST-9 score + NMS + border filter, all levels */
+    MSLAM_B200_T_SELECT = 3,   /* retainBest x2 + Harris */
+    MSLAM_B200_T_BLUR = 4,     /* 7x7 float blur, all levels */
+    MSLAM_B200_T_DESCRIBE = 5, /* IC angle + rBRIEF */
+    MSLAM_B200_T_KNN = 6,      /* brute-force Hamming kNN (k = 2) */
+    MSLAM_B200_T_COMPACT = 7,  /* ratio test / mutual check + ordered compaction */
+    MSLAM_B200_T_DB = 8,       /* keyframe-database scoring */
+    MSLAM_B200_T_COUNT = 9
+} mslam_b200_timed_stage;
+MSLAM_B200_API int mslam_b200_enable_stage_timing(mslam_b200_ctx* ctx, int enable);
+/* total_ms[MSLAM_B200_T_COUNT], intervals[MSLAM_B200_T_COUNT] (number of bracketed intervals), launches[..] (kernel
+ * launches inside them) */
+MSLAM_B200_API int mslam_b200_stage_times(mslam_b200_ctx* ctx, double* total_ms, long long* intervals,
+                                          long long* launches);
 /* integer-pipe roofline denominators, measured on the context's device with register-only loops over all SMs:
- * out[0] = POPC.32 results/s, out[1] = LOP3 (xor) results/s, out[2] = 256-bit pair evaluations/s of the plain
- * 8x(xor,popc,add) sequence, out[3] = SM clock (MHz) the loops ran at (from clock64/globaltimer). */
-MSLAM_B200_API int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out4);
+ * out[0] = POPC.32 results/s, out[1] = LOP3 results/s, out[2] = 256-bit pair evaluations/s of the plain
+ * 8x(xor,popc,add) + top-2 sequence, out[3] = SM clock (MHz) the loops ran at (from clock64/globaltimer),
+ * out[4] = pair evaluations/s of the carry-save sequence the matcher uses (8 xor, 8 lop3, 4 popc) + top-2. */
+MSLAM_B200_API int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out5);
 
 #ifdef __cplusplus
 }

@@ -311,7 +311,22 @@ class Context:
                                                          _ptr(d_out_score), _ptr(d_out_id)), "db_merge_topk_dev")
 
     # -- measurement ------------------------------------------------------------------------------------------------------
+    STAGES = ("gray", "resize", "fast", "select", "blur", "describe", "knn", "compact", "db")
+
+    def enable_stage_timing(self, on=True):
+        self._chk(library().mslam_b200_enable_stage_timing(self._h, int(bool(on))), "enable_stage_timing")
+
+    def stage_times(self):
+        """-> {stage: (total_ms, intervals, kernel launches)} since the last call"""
+        n = len(self.STAGES)
+        ms = np.zeros(n, np.float64)
+        iv = np.zeros(n, np.int64)
+        ln = np.zeros(n, np.int64)
+        self._chk(library().mslam_b200_stage_times(self._h, _ptr(ms), _ptr(iv), _ptr(ln)), "stage_times")
+        return {s: (float(ms[i]), int(iv[i]), int(ln[i])) for i, s in enumerate(self.STAGES)}
+
     def measure_int_peaks(self):
-        out = np.zeros(4, np.float64)
+        out = np.zeros(8, np.float64)
         self._chk(library().mslam_b200_measure_int_peaks(self._h, _ptr(out)), "measure_int_peaks")
-        return {"popc32_per_s": out[0], "lop3_per_s": out[1], "plain_pairs_per_s": out[2], "sm_mhz": out[3]}
+        return {"popc32_per_s": float(out[0]), "lop3_per_s": float(out[1]), "plain_pairs_per_s": float(out[2]),
+                "sm_mhz": float(out[3]), "csa_pairs_per_s": float(out[4])}

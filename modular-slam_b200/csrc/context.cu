@@ -46,6 +46,7 @@ struct mslam_b200_ctx
     mslam_b200_keypoint* d_kp = nullptr;
     uint8_t* d_desc = nullptr;
     int* d_counts = nullptr;
+    unsigned* d_pat = nullptr; // rBRIEF pattern, transposed (256 words)
     // ---- pinned host staging ----
     int* h_counts = nullptr;
     int* h_err = nullptr;
@@ -56,6 +57,37 @@ struct mslam_b200_ctx
     unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
     int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
     int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
+    // ---- per-stage event timing (mslam_b200_enable_stage_timing) ----
+    bool timing = false;
+    std::vector<cudaEvent_t> ev_pool; // pairs: [2i] start, [2i+1] stop
+    std::vector<int> ev_stage;        // stage of pair i
+    std::vector<long long> ev_launches;
+    size_t ev_used = 0;               // pairs in use
+    double t_ms[MSLAM_B200_T_COUNT] = {0};
+    long long t_n[MSLAM_B200_T_COUNT] = {0}, t_l[MSLAM_B200_T_COUNT] = {0};
+};
+
+// RAII bracket of one timed stage; no-op unless timing is enabled
+struct StageTimer
+{
+    mslam_b200_ctx* c;
+    long long l0;
+    int pair = -1;
+    StageTimer(mslam_b200_ctx* ctx, int stage) : c(ctx), l0(ctx->launches)
+    {
+        if(!c->timing || c->ev_used >= c->ev_stage.size())
+            return;
+        pair = (int)c->ev_used++;
+        c->ev_stage[pair] = stage;
+        cudaEventRecord(c->ev_pool[2 * pair], c->stream);
+    }
+    ~StageTimer()
+    {
+        if(pair < 0)
+            return;
+        cudaEventRecord(c->ev_pool[2 * pair + 1], c->stream);
+        c->ev_launches[pair] = c->launches - l0;
+    }
 };
 
 static int ctx_fail(mslam_b200_ctx* ctx, cudaError_t e, const char* what)
@@ -282,7 +314,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout};
+                   ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat};
     for(void* p : dev)
         if(p)
             cudaFree(p);
@@ -290,6 +322,8 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     for(void* p : host)
         if(p)
             cudaFreeHost(p);
+    for(cudaEvent_t e : ctx->ev_pool)
+        cudaEventDestroy(e);
     if(ctx->own_stream && ctx->stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -371,6 +405,12 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaMalloc(&ctx->d_kp, B * (size_t)ctx->kp_cap * sizeof(mslam_b200_keypoint)));
     CREATE_OK(cudaMalloc(&ctx->d_desc, B * (size_t)ctx->kp_cap * 32));
     CREATE_OK(cudaMalloc(&ctx->d_counts, B * sizeof(int)));
+    {
+        unsigned pat[256];
+        brief_pattern_transposed(pat);
+        CREATE_OK(cudaMalloc(&ctx->d_pat, sizeof(pat)));
+        CREATE_OK(cudaMemcpy(ctx->d_pat, pat, sizeof(pat), cudaMemcpyHostToDevice));
+    }
     CREATE_OK(cudaHostAlloc(&ctx->h_counts, B * sizeof(int), cudaHostAllocDefault));
     CREATE_OK(cudaHostAlloc(&ctx->h_err, B * sizeof(int), cudaHostAllocDefault));
     // matcher
@@ -448,8 +488,14 @@ int mslam_b200_level_geometry(mslam_b200_ctx* ctx, int width, int height, int* w
 static int run_pyramid(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames)
 {
     ctx->P.n_frames = n_frames;
-    launch_gray(ctx->stream, d_bgr, ctx->d_pyr, ctx->P, &ctx->launches);
-    launch_pyramid(ctx->stream, ctx->d_pyr, ctx->P, ctx->d_xtab, ctx->d_ytab, &ctx->launches);
+    {
+        StageTimer t(ctx, MSLAM_B200_T_GRAY);
+        launch_gray(ctx->stream, d_bgr, ctx->d_pyr, ctx->P, &ctx->launches);
+    }
+    {
+        StageTimer t(ctx, MSLAM_B200_T_RESIZE);
+        launch_pyramid(ctx->stream, ctx->d_pyr, ctx->P, ctx->d_xtab, ctx->d_ytab, &ctx->launches);
+    }
     return MSLAM_B200_OK;
 }
 
@@ -466,12 +512,24 @@ int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n
     MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
     run_pyramid(ctx, d_bgr, n_frames);
     const PipeParams& P = ctx->P;
-    launch_fast(st, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, &ctx->launches);
-    launch_select(st, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist, ctx->d_sel,
-                  ctx->d_err, P, &ctx->launches);
-    launch_blur(st, ctx->d_pyr, ctx->d_blur, P, &ctx->launches);
-    launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, d_kp, d_desc, d_counts, capacity,
-                           std::min(capacity, ctx->kp_cap * P.nlevels), P, &ctx->launches);
+    {
+        StageTimer t(ctx, MSLAM_B200_T_FAST);
+        launch_fast(st, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, &ctx->launches);
+    }
+    {
+        StageTimer t(ctx, MSLAM_B200_T_SELECT);
+        launch_select(st, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
+                      ctx->d_sel, ctx->d_err, P, &ctx->launches);
+    }
+    {
+        StageTimer t(ctx, MSLAM_B200_T_BLUR);
+        launch_blur(st, ctx->d_pyr, ctx->d_blur, P, &ctx->launches);
+    }
+    {
+        StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
+        launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, d_kp, d_desc, d_counts, capacity,
+                               std::min(capacity, ctx->kp_cap * P.nlevels), P, &ctx->launches);
+    }
     ctx->last_frames = n_frames;
     MSLAM_CUDA_OK(cudaGetLastError());
     return MSLAM_B200_OK;
@@ -581,7 +639,7 @@ int mslam_b200_describe(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int 
     MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_sel, sel.data(), sel.size() * sizeof(SelRec), cudaMemcpyHostToDevice, st));
     run_pyramid(ctx, ctx->d_bgr, 1);
     launch_blur(st, ctx->d_pyr, ctx->d_blur, ctx->P, &ctx->launches);
-    launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,
+    launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,
                            std::max(n_kp, 1), ctx->P, &ctx->launches);
     std::vector<mslam_b200_keypoint> hk((size_t)std::max(n_kp, 1));
     std::vector<uint8_t> hd((size_t)std::max(n_kp, 1) * 32);
@@ -681,15 +739,20 @@ int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, const uint8_t* d_f
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     cudaStream_t st = ctx->stream;
     // query = `to`, train = `from` (orb_feature.cpp:96)
-    launch_knn2(st, d_to, d_n_to, d_from, d_n_from, n_pairs, capacity, ctx->d_key0, ctx->d_key1, &ctx->launches);
-    if(mode == 0)
-        launch_ratio_compact(st, ctx->d_key0, ctx->d_key1, d_n_to, d_n_from, n_pairs, capacity, ctx->cfg.ratio, d_out_a,
-                             d_out_b, d_out_dist, d_n_out, &ctx->launches);
-    else
     {
-        launch_knn2(st, d_from, d_n_from, d_to, d_n_to, n_pairs, capacity, ctx->d_key0b, ctx->d_key1b, &ctx->launches);
-        launch_mutual_compact(st, ctx->d_key0, ctx->d_key0b, d_n_to, d_n_from, n_pairs, capacity, d_out_a, d_out_b,
-                              d_out_dist, d_n_out, &ctx->launches);
+        StageTimer t(ctx, MSLAM_B200_T_KNN);
+        launch_knn2(st, d_to, d_n_to, d_from, d_n_from, n_pairs, capacity, ctx->d_key0, ctx->d_key1, ctx->sm_count, &ctx->launches);
+        if(mode == 1)
+            launch_knn2(st, d_from, d_n_from, d_to, d_n_to, n_pairs, capacity, ctx->d_key0b, ctx->d_key1b, ctx->sm_count, &ctx->launches);
+    }
+    {
+        StageTimer t(ctx, MSLAM_B200_T_COMPACT);
+        if(mode == 0)
+            launch_ratio_compact(st, ctx->d_key0, ctx->d_key1, d_n_to, d_n_from, n_pairs, capacity, ctx->cfg.ratio, d_out_a,
+                                 d_out_b, d_out_dist, d_n_out, &ctx->launches);
+        else
+            launch_mutual_compact(st, ctx->d_key0, ctx->d_key0b, d_n_to, d_n_from, n_pairs, capacity, d_out_a, d_out_b,
+                                  d_out_dist, d_n_out, &ctx->launches);
     }
     MSLAM_CUDA_OK(cudaGetLastError());
     return MSLAM_B200_OK;
@@ -825,7 +888,7 @@ int mslam_b200_knn2(mslam_b200_ctx* ctx, const uint8_t* query, int n_query, int 
     if(rc)
         return rc;
     const int cap = ctx->desc_cap;
-    launch_knn2(st, ctx->d_mto, ctx->d_nto, ctx->d_mfrom, ctx->d_nfrom, 1, cap, ctx->d_key0, ctx->d_key1, &ctx->launches);
+    launch_knn2(st, ctx->d_mto, ctx->d_nto, ctx->d_mfrom, ctx->d_nfrom, 1, cap, ctx->d_key0, ctx->d_key1, ctx->sm_count, &ctx->launches);
     // unpack into the four int scratch arrays (out_a, out_b, out_d, key0b reinterpreted)
     int* d_i1 = reinterpret_cast<int*>(ctx->d_key0b);
     launch_unpack_knn(st, ctx->d_key0, ctx->d_key1, n_query, ctx->d_out_a, ctx->d_out_d, d_i1, ctx->d_out_b, &ctx->launches);
@@ -845,6 +908,7 @@ int mslam_b200_db_scores_dev(mslam_b200_ctx* ctx, const uint8_t* d_queries, cons
        n_query_frames > 65535 || n_keyframes < 1 || q_cap < 1 || k_cap < 1 || (size_t)q_cap * 32 > 200 * 1024)
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    StageTimer t(ctx, MSLAM_B200_T_DB);
     MSLAM_CUDA_OK(launch_db_scores(ctx->stream, d_queries, d_q_counts, n_query_frames, q_cap, d_db, d_k_counts, n_keyframes,
                                    k_cap, ctx->cfg.ratio, d_scores, ctx->sm_count, &ctx->launches));
     return MSLAM_B200_OK;
@@ -919,7 +983,57 @@ int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queries, const int* 
     return rc;
 }
 
-int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out4)
+int mslam_b200_enable_stage_timing(mslam_b200_ctx* ctx, int enable)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if(enable && ctx->ev_pool.empty())
+    {
+        const size_t pairs = 8192;
+        ctx->ev_pool.resize(2 * pairs);
+        for(size_t i = 0; i < 2 * pairs; ++i)
+            MSLAM_CUDA_OK(cudaEventCreate(&ctx->ev_pool[i]));
+        ctx->ev_stage.assign(pairs, 0);
+        ctx->ev_launches.assign(pairs, 0);
+    }
+    ctx->timing = enable != 0;
+    ctx->ev_used = 0;
+    for(int i = 0; i < MSLAM_B200_T_COUNT; ++i)
+        ctx->t_ms[i] = 0, ctx->t_n[i] = 0, ctx->t_l[i] = 0;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_stage_times(mslam_b200_ctx* ctx, double* total_ms, long long* intervals, long long* launches)
+{
+    if(!ctx || !total_ms)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    for(size_t i = 0; i < ctx->ev_used; ++i)
+    {
+        float ms = 0.f;
+        MSLAM_CUDA_OK(cudaEventElapsedTime(&ms, ctx->ev_pool[2 * i], ctx->ev_pool[2 * i + 1]));
+        const int s = ctx->ev_stage[i];
+        ctx->t_ms[s] += ms;
+        ctx->t_n[s] += 1;
+        ctx->t_l[s] += ctx->ev_launches[i];
+    }
+    ctx->ev_used = 0;
+    for(int i = 0; i < MSLAM_B200_T_COUNT; ++i)
+    {
+        total_ms[i] = ctx->t_ms[i];
+        if(intervals)
+            intervals[i] = ctx->t_n[i];
+        if(launches)
+            launches[i] = ctx->t_l[i];
+        ctx->t_ms[i] = 0, ctx->t_n[i] = 0, ctx->t_l[i] = 0;
+    }
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out4 /* 5 values */)
 {
     if(!ctx || !out4)
         return MSLAM_B200_E_INVALID;

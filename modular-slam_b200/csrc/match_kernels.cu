@@ -13,11 +13,34 @@ namespace mslam_b200
 
 constexpr unsigned kNoKey = 0xffffffffu;
 
-// 256-bit Hamming distance of two descriptors held as 2 x uint4
+// three-input logic on the ALU pipe (one LOP3 each)
+__device__ __forceinline__ unsigned xor3(unsigned a, unsigned b, unsigned c)
+{
+    unsigned r;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ unsigned maj3(unsigned a, unsigned b, unsigned c)
+{
+    unsigned r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+
+// 256-bit Hamming distance of two descriptors held as 2 x uint4.
+// POPC runs on the XU pipe at 16 results/clk/SM -- a quarter of the ALU pipe's LOP3 rate (measured:
+// mslam_b200_measure_int_peaks) -- so the eight XOR words are first compressed with four carry-save adders
+// (x0+x1+x2 = s + 2c per bit position): sum(popc(x0..x6)) = popc(s2) + 2 popc(s3) + 4 popc(c3), and only 4 POPC
+// (instead of 8) are issued per pair.  Exact integer arithmetic; nothing is approximated.
 __device__ __forceinline__ int ham256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
 {
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) +
-           __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+    const unsigned x0 = a0.x ^ b0.x, x1 = a0.y ^ b0.y, x2 = a0.z ^ b0.z, x3 = a0.w ^ b0.w;
+    const unsigned x4 = a1.x ^ b1.x, x5 = a1.y ^ b1.y, x6 = a1.z ^ b1.z, x7 = a1.w ^ b1.w;
+    const unsigned s0 = xor3(x0, x1, x2), c0 = maj3(x0, x1, x2);
+    const unsigned s1 = xor3(x3, x4, x5), c1 = maj3(x3, x4, x5);
+    const unsigned s2 = xor3(s0, s1, x6), c2 = maj3(s0, s1, x6);
+    const unsigned s3 = xor3(c0, c1, c2), c3 = maj3(c0, c1, c2);
+    return (__popc(s2) + __popc(x7)) + 2 * (__popc(s3) + 2 * __popc(c3));
 }
 
 // =================================================================================================
@@ -28,10 +51,9 @@ __device__ __forceinline__ int ham256(const uint4& a0, const uint4& a1, const ui
 //   distance, ties to the lower index" with no branches.
 //   Output: key0/key1 per query ([pair][cap]); kNoKey where the train set is too small.
 // =================================================================================================
-constexpr int KNN_THREADS = 128;
 constexpr int KNN_CHUNK = 512; // train descriptors per shared-memory chunk (16 KB)
 
-template <int QPT>
+template <int QPT, int KNN_THREADS>
 __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint8_t* __restrict__ q_base, const int* __restrict__ q_counts,
                                                       const uint8_t* __restrict__ t_base, const int* __restrict__ t_counts,
                                                       int cap, unsigned* __restrict__ key0, unsigned* __restrict__ key1)
@@ -62,7 +84,7 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint8_t* __restrict_
         for(int i = threadIdx.x; i < nc * 2; i += KNN_THREADS)
             s_t[i] = __ldg(tv + 2 * t0 + i);
         __syncthreads();
-#pragma unroll 4
+#pragma unroll(QPT == 1 ? 4 : 2)
         for(int j = 0; j < nc; ++j)
         {
             const uint4 ta = s_t[2 * j], tb = s_t[2 * j + 1];
@@ -344,11 +366,12 @@ __global__ void __launch_bounds__(256) k_peak_popc(unsigned* out, int iters)
 #pragma unroll
     for(int i = 0; i < 8; ++i)
         v[i] = threadIdx.x * 2654435761u + i * 40503u + blockIdx.x;
+#pragma unroll 8
     for(int it = 0; it < iters; ++it)
     {
 #pragma unroll
         for(int i = 0; i < 8; ++i)
-            v[i] = __popc(v[i]) + 0x01010101u * (unsigned)i; // POPC feeds the next POPC; the add keeps chains apart
+            v[i] = __popc(v[i]) * 0x01010101u + (unsigned)i; // POPC feeds the next POPC; the IMAD (fma pipe) keeps chains apart
     }
     unsigned s = 0;
 #pragma unroll
@@ -364,6 +387,7 @@ __global__ void __launch_bounds__(256) k_peak_lop3(unsigned* out, int iters, uns
 #pragma unroll
     for(int i = 0; i < 8; ++i)
         v[i] = threadIdx.x * 2654435761u + i * 40503u + blockIdx.x;
+#pragma unroll 8
     for(int it = 0; it < iters; ++it)
     {
 #pragma unroll
@@ -378,27 +402,34 @@ __global__ void __launch_bounds__(256) k_peak_lop3(unsigned* out, int iters, uns
         out[0] = s;
 }
 
-// the plain pair sequence: 8 x (xor, popc) + adds, 4 pairs per iteration, operands in registers
+// the pair sequence of the matcher with operands in registers: 8 x xor, then either 8 POPC + adds (CSA = false) or the
+// carry-save form ham256 uses (CSA = true).  All eight train words change every iteration through an IMAD (fma pipe,
+// otherwise idle) so that nothing can be hoisted out of the loop.
+template <bool CSA>
 __global__ void __launch_bounds__(256) k_peak_pairs(unsigned* out, int iters)
 {
-    unsigned q[8], t[8];
-#pragma unroll
-    for(int i = 0; i < 8; ++i)
-    {
-        q[i] = threadIdx.x * 2654435761u + i * 40503u;
-        t[i] = blockIdx.x * 2246822519u + i * 3266489917u;
-    }
-    unsigned best = 0xffffffffu;
+    uint4 qa, qb, ta, tb;
+    qa = make_uint4(threadIdx.x * 2654435761u, threadIdx.x * 40503u + 1u, threadIdx.x + 7u, threadIdx.x * 3u);
+    qb = make_uint4(qa.x ^ 0x9e3779b9u, qa.y + 11u, qa.z * 5u, qa.w ^ 0x7f4a7c15u);
+    ta = make_uint4(blockIdx.x * 2246822519u, blockIdx.x + 3u, blockIdx.x * 7u + 1u, blockIdx.x ^ 0x55555555u);
+    tb = make_uint4(ta.x + 1u, ta.y * 3u, ta.z ^ 0x33333333u, ta.w + 5u);
+    unsigned best = 0xffffffffu, second = 0xffffffffu;
+#pragma unroll 4
     for(int it = 0; it < iters; ++it)
     {
-        unsigned d = 0;
-#pragma unroll
-        for(int i = 0; i < 8; ++i)
-            d += __popc(q[i] ^ t[i] ^ (unsigned)it); // 3-input xor = one LOP3
-        best = min(best, d);
-        t[0] += d; // keep a train operand data-dependent so the loop cannot be collapsed
+        unsigned d;
+        if(CSA)
+            d = (unsigned)ham256(qa, qb, ta, tb);
+        else
+            d = __popc(qa.x ^ ta.x) + __popc(qa.y ^ ta.y) + __popc(qa.z ^ ta.z) + __popc(qa.w ^ ta.w) + __popc(qb.x ^ tb.x) +
+                __popc(qb.y ^ tb.y) + __popc(qb.z ^ tb.z) + __popc(qb.w ^ tb.w);
+        const unsigned key = (d << 16) | (unsigned)(it & 0xffff);
+        second = min(second, max(best, key));
+        best = min(best, key);
+        ta.x = ta.x * 3u + d; ta.y = ta.y * 5u + d; ta.z = ta.z * 7u + d; ta.w = ta.w * 9u + d;
+        tb.x = tb.x * 11u + d; tb.y = tb.y * 13u + d; tb.z = tb.z * 17u + d; tb.w = tb.w * 19u + d;
     }
-    if(best == 0x12345u)
+    if((best ^ second) == 0x12345u)
         out[0] = best;
 }
 
@@ -425,11 +456,22 @@ __global__ void k_clock_probe(long long* out)
 // launchers
 // =================================================================================================
 void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
-                 unsigned* key0, unsigned* key1, long long* launches)
+                 unsigned* key0, unsigned* key1, int sm_count, long long* launches)
 {
-    constexpr int QPT = 2;
-    dim3 grd((cap + KNN_THREADS * QPT - 1) / (KNN_THREADS * QPT), n_pairs);
-    k_knn2<QPT><<<grd, KNN_THREADS, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+    // Work granularity: the kernel is compute-bound on the integer pipes, so what matters is an even split over the
+    // 148 SMs.  Few frame pairs -> 64 queries per CTA (many small CTAs, all co-resident, < 2 % imbalance at 64 pairs x
+    // 1000 queries); lots of work -> 256 queries per CTA (fewer shared-memory refills of the train set).
+    const long long small_ctas = (long long)((cap + 63) / 64) * n_pairs;
+    if(small_ctas <= 24LL * sm_count)
+    {
+        dim3 grd((cap + 63) / 64, n_pairs);
+        k_knn2<1, 64><<<grd, 64, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+    }
+    else
+    {
+        dim3 grd((cap + 255) / 256, n_pairs);
+        k_knn2<2, 128><<<grd, 128, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+    }
     ++*launches;
 }
 
@@ -488,7 +530,7 @@ void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists
     ++*launches;
 }
 
-cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long long* launches)
+cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4 /* 5 values */, long long* launches)
 {
     unsigned* d_out = nullptr;
     long long* d_clk = nullptr;
@@ -502,8 +544,8 @@ cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long 
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     const int grid = sm_count * 8, iters = 4096;
-    float ms[3] = {0, 0, 0};
-    for(int which = 0; which < 3; ++which)
+    float ms[4] = {0, 0, 0, 0};
+    for(int which = 0; which < 4; ++which)
     {
         for(int rep = 0; rep < 3; ++rep) // last repetition is the one kept (warm clocks)
         {
@@ -512,8 +554,10 @@ cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long 
                 k_peak_popc<<<grid, 256, 0, st>>>(d_out, iters);
             else if(which == 1)
                 k_peak_lop3<<<grid, 256, 0, st>>>(d_out, iters, 0x9e3779b9u, 0x7f4a7c15u);
+            else if(which == 2)
+                k_peak_pairs<false><<<grid, 256, 0, st>>>(d_out, iters);
             else
-                k_peak_pairs<<<grid, 256, 0, st>>>(d_out, iters);
+                k_peak_pairs<true><<<grid, 256, 0, st>>>(d_out, iters);
             cudaEventRecord(e1, st);
             cudaEventSynchronize(e1);
             cudaEventElapsedTime(&ms[which], e0, e1);
@@ -530,6 +574,7 @@ cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long 
     out4[1] = threads * iters * 8.0 / (ms[1] * 1e-3);
     out4[2] = threads * iters / (ms[2] * 1e-3);
     out4[3] = h_clk[1] > 0 ? (double)h_clk[0] / (double)h_clk[1] * 1e3 : 0.0;
+    out4[4] = threads * iters / (ms[3] * 1e-3);
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     cudaFree(d_out);

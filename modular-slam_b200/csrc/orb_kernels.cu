@@ -11,10 +11,6 @@
 namespace mslam_b200
 {
 
-__constant__ int8_t c_pattern[256 * 4] = {
-#include "brief_pattern.inc"
-};
-
 // =================================================================================================
 // K1  gray : interleaved 3-channel u8 -> level 0      (frame.cpp:15-19)
 //   g = (u8) min(255.f, .299f*c0 + .587f*c1 + .114f*c2)  three rounded products, two rounded adds,
@@ -597,6 +593,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                          const uint8_t* __restrict__ blur,
                                                          const LevelCounters* __restrict__ ctr, const SelRec* __restrict__ sel,
+                                                         const unsigned* __restrict__ pat_t,
                                                          mslam_b200_keypoint* __restrict__ out_kp, uint8_t* __restrict__ out_desc,
                                                          int* __restrict__ out_counts, int out_cap)
 {
@@ -622,22 +619,22 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     const SelRec rec = sel[((long long)b * P.nlevels + l) * P.kp_cap + r];
     const int x = (rec.yx_score >> 8) & 0xfff, y = rec.yx_score >> 20;
     const long long plane = L.img_off + (long long)b * L.img_frame_stride;
+    const int pitch = L.pitch;
 
-    // ---- intensity centroid ----
+    // ---- intensity centroid: the warp walks the 31 rows of the disc, lane = column (coalesced 31-byte row reads) ----
     int m10 = 0, m01 = 0;
-    if(lane < 31)
     {
-        const int v = lane - 15, av = v < 0 ? -v : v;
-        const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * av)) & 15ull); // u_max[|v|]
-        const uint8_t* row = pyr + plane + (long long)(y + v) * L.pitch + x;
-        int s = 0;
-        for(int u = -d; u <= d; ++u)
+        const int u = lane - 15, au = u < 0 ? -u : u;
+        const uint8_t* c = pyr + plane + (long long)y * pitch + x + u;
+#pragma unroll
+        for(int v = -15; v <= 15; ++v)
         {
-            const int val = __ldg(row + u);
-            s += val;
+            const int av = v < 0 ? -v : v;
+            const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * av)) & 15ull); // u_max[|v|]
+            const int val = (lane < 31 && au <= d) ? (int)__ldg(c + v * pitch) : 0;
             m10 += u * val;
+            m01 += v * val;
         }
-        m01 = v * s;
     }
 #pragma unroll
     for(int o = 16; o > 0; o >>= 1)
@@ -647,7 +644,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     }
     const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    // ---- rotated BRIEF ----
+    // ---- rotated BRIEF: lane i produces descriptor byte i ----
     const float kx = __fmul_rn((float)x, L.scale), ky = __fmul_rn((float)y, L.scale);
     const int cx = __float2int_rn(__fmul_rn(kx, L.inv_scale)), cy = __float2int_rn(__fmul_rn(ky, L.inv_scale));
     float ca = 0.f, sa = 0.f;
@@ -659,19 +656,20 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     }
     ca = __shfl_sync(0xffffffffu, ca, 0);
     sa = __shfl_sync(0xffffffffu, sa, 0);
-    const uint8_t* centre = blur + plane + (long long)cy * L.pitch + cx;
+    const uint8_t* centre = blur + plane + (long long)cy * pitch + cx;
     unsigned byte = 0;
 #pragma unroll
     for(int j = 0; j < 8; ++j)
     {
-        const int8_t* t = c_pattern + (lane * 8 + j) * 4;
-        const float px0 = (float)t[0], py0 = (float)t[1], px1 = (float)t[2], py1 = (float)t[3];
+        const unsigned t = __ldg(pat_t + j * 32 + lane); // test (lane * 8 + j): x0 | y0 << 8 | x1 << 16 | y1 << 24 (int8 each)
+        const float px0 = (float)(int)(signed char)(t & 255u), py0 = (float)(int)(signed char)((t >> 8) & 255u),
+                    px1 = (float)(int)(signed char)((t >> 16) & 255u), py1 = (float)(int)(signed char)(t >> 24);
         const int x0 = __float2int_rn(__fsub_rn(__fmul_rn(px0, ca), __fmul_rn(py0, sa)));
         const int y0 = __float2int_rn(__fadd_rn(__fmul_rn(px0, sa), __fmul_rn(py0, ca)));
         const int x1 = __float2int_rn(__fsub_rn(__fmul_rn(px1, ca), __fmul_rn(py1, sa)));
         const int y1 = __float2int_rn(__fadd_rn(__fmul_rn(px1, sa), __fmul_rn(py1, ca)));
-        const int v0 = __ldg(centre + (long long)y0 * L.pitch + x0);
-        const int v1 = __ldg(centre + (long long)y1 * L.pitch + x1);
+        const int v0 = __ldg(centre + y0 * pitch + x0);
+        const int v1 = __ldg(centre + y1 * pitch + x1);
         byte |= (unsigned)(v0 < v1) << j;
     }
     out_desc[((long long)b * out_cap + slot) * 32 + lane] = (uint8_t)byte;
@@ -686,6 +684,21 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
         kp.octave = l;
         out_kp[(long long)b * out_cap + slot] = kp;
     }
+}
+
+// rBRIEF pattern, transposed for the warp-per-keypoint kernel: word j * 32 + lane = test lane * 8 + j
+void brief_pattern_transposed(unsigned* out256)
+{
+    static const int8_t pat[256 * 4] = {
+#include "brief_pattern.inc"
+    };
+    for(int lane = 0; lane < 32; ++lane)
+        for(int j = 0; j < 8; ++j)
+        {
+            const int8_t* t = pat + (lane * 8 + j) * 4;
+            out256[j * 32 + lane] = (unsigned)(uint8_t)t[0] | ((unsigned)(uint8_t)t[1] << 8) | ((unsigned)(uint8_t)t[2] << 16) |
+                                    ((unsigned)(uint8_t)t[3] << 24);
+        }
 }
 
 // =================================================================================================
@@ -762,12 +775,12 @@ void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned
 }
 
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
-                            const SelRec* sel, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int* out_counts,
+                            const SelRec* sel, const unsigned* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int* out_counts,
                             int out_cap, int n_slots, const PipeParams& P, long long* launches)
 {
     const int slots = n_slots < 1 ? 1 : n_slots;
-    k_orient_describe<<<dim3((slots + 7) / 8, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, out_kp, out_desc,
-                                                                         out_counts, out_cap);
+    k_orient_describe<<<dim3((slots + 7) / 8, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, pat_t, out_kp,
+                                                                         out_desc, out_counts, out_cap);
     ++*launches;
 }
 
