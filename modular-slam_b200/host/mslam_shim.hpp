@@ -1,0 +1,91 @@
+// mslam_shim.hpp -- layout-compatible stand-ins for the reference types that cross the plugin boundary.
+//
+// The reference headers (modular_slam/frontend/feature/feature_interface.hpp, orb_feature.hpp, types/rgb_frame.hpp,
+// types/basic_types.hpp) pull in Eigen, Boost and OpenCV, none of which exist in this build image.  When they ARE
+// available, compile the adapter with -DMSLAM_B200_WITH_REFERENCE_HEADERS -I<modular_slam include dir> and this shim
+// is skipped; the static_asserts in orb_b200_plugin.cpp hold for both.
+//
+// Layouts follow (x86-64, Eigen 3.4):
+//   Id = std::uint64_t                                              types/basic_types.hpp:12
+//   Vector2 = Eigen::Vector2d  -> 16 bytes, 16-byte aligned         types/basic_types.hpp:14
+//   Keypoint { Id id; Vector2 coordinates; }          = 32 bytes   feature_interface.hpp:18-22
+//   KeypointDescriptor<u8, 32> { Keypoint; array<u8,32> } = 64 bytes, descriptor at +32   feature_interface.hpp:24-29
+//   DescriptorMatch { size_t fromIndex, toIndex; }    = 16 bytes   feature_interface.hpp:37-41
+//   Size { int width, height; }                                    types/basic_types.hpp:23-27
+//   RgbFrame { std::vector<uint8_t> data; Size size; }              types/rgb_frame.hpp:12-16
+#pragma once
+#include <array>
+#include <cstddef>
+#include <cstdint>
+#include <memory>
+#include <vector>
+
+namespace mslam
+{
+using Id = std::uint64_t;
+
+// Eigen::Vector2d stand-in: two doubles, 16-byte aligned, Eigen-style accessors
+struct alignas(16) Vector2
+{
+    double v[2];
+    double& x() { return v[0]; }
+    double& y() { return v[1]; }
+    double x() const { return v[0]; }
+    double y() const { return v[1]; }
+    double& operator[](int i) { return v[i]; }
+    double operator[](int i) const { return v[i]; }
+};
+
+struct Size
+{
+    int width;
+    int height;
+};
+
+struct RgbFrame
+{
+    std::vector<std::uint8_t> data;
+    Size size;
+};
+
+struct Keypoint
+{
+    Id id;
+    Vector2 coordinates;
+};
+
+template <typename DescriptorType, int Length = 32>
+struct KeypointDescriptor
+{
+    Keypoint keypoint;
+    std::array<DescriptorType, Length> descriptor;
+};
+
+struct DescriptorMatch
+{
+    std::size_t fromIndex;
+    std::size_t toIndex;
+};
+
+template <typename SensorData, typename DescriptorType, int Length>
+class IFeatureDetector
+{
+  public:
+    virtual std::vector<KeypointDescriptor<DescriptorType, Length>> detect(const SensorData& sensorData) = 0;
+    virtual ~IFeatureDetector() {}
+};
+
+template <typename DescriptorType, int Length>
+class IFeatureMatcher
+{
+  public:
+    virtual std::vector<DescriptorMatch>
+    match(const std::vector<KeypointDescriptor<DescriptorType, Length>>& firstDescriptors,
+          const std::vector<KeypointDescriptor<DescriptorType, Length>>& secondDescriptors) = 0;
+    virtual ~IFeatureMatcher() {}
+};
+
+using IOrbFeatureDetector = IFeatureDetector<RgbFrame, std::uint8_t, 32>;
+using IOrbMatcher = IFeatureMatcher<std::uint8_t, 32>;
+using OrbKeypoint = KeypointDescriptor<std::uint8_t, 32>;
+} // namespace mslam

@@ -1,0 +1,93 @@
+// orb_b200_plugin.hpp -- the drop-in plugin classes: modular-slam's own detector / matcher interfaces implemented on
+// the B200 C ABI (include/mslam_b200.h).
+//
+//   mslam::OrbB200Detector  replaces  mslam::OrbOpenCvDetector   (orb_feature.hpp:19-31, orb_feature.cpp:19-72)
+//   mslam::OrbB200Matcher   replaces  mslam::OrbOpenCvMatcher    (orb_feature.hpp:33-47, orb_feature.cpp:74-117)
+//
+// Both are constructed the way the reference apps construct theirs (std::make_shared<...>(), rgbd_slam.cpp:74-76) or
+// through the boost::dll factory aliases exported by the plugin library (plugin_loader.hpp:19-25):
+//   orbDetectorFactory : std::unique_ptr<mslam::IOrbFeatureDetector>()
+//   orbMatcherFactory  : std::unique_ptr<mslam::IOrbMatcher>()
+// Error behaviour mirrors the reference: no exceptions out of detect()/match(); an empty vector means "nothing"
+// (a CUDA failure is logged to stderr once per object and also yields an empty vector).  Constructors throw
+// std::runtime_error when no CUDA device / context can be created -- there is no CPU fallback.
+#pragma once
+#ifdef MSLAM_B200_WITH_REFERENCE_HEADERS
+#include "modular_slam/orb_feature.hpp"
+#else
+#include "mslam_shim.hpp"
+#endif
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/mslam_b200.h"
+
+namespace mslam
+{
+
+// parameters the reference hard-codes (cv::ORB::create(1000), ratio 0.7); overridable through plugin_config.json
+struct OrbB200Options
+{
+    int device = 0;
+    int maxWidth = 1920, maxHeight = 1080;
+    int nfeatures = 1000;
+    int nlevels = 8;
+    float scaleFactor = 1.2f;
+    int fastThreshold = 20;
+    double ratio = 0.7;
+    int maxDescriptors = 0; // matcher capacity per side; 0 = derived from nfeatures
+};
+
+// one context shared by the detector and the matcher of a process (one CUDA stream, one set of HBM buffers)
+class OrbB200Context;
+
+class OrbB200Detector : public IOrbFeatureDetector
+{
+  public:
+    OrbB200Detector();
+    explicit OrbB200Detector(const OrbB200Options& options);
+    ~OrbB200Detector() override;
+    std::vector<OrbKeypoint> detect(const RgbFrame& sensorData) override;
+    // batched variant for callers that hold several frames (independent sequences); same results frame by frame
+    std::vector<std::vector<OrbKeypoint>> detectBatch(const std::vector<const RgbFrame*>& frames);
+
+  private:
+    std::shared_ptr<OrbB200Context> ctx;
+    std::vector<mslam_b200_keypoint> kpBuf;
+    std::vector<std::uint8_t> descBuf;
+};
+
+class OrbB200Matcher : public IOrbMatcher
+{
+  public:
+    OrbB200Matcher();
+    explicit OrbB200Matcher(const OrbB200Options& options);
+    ~OrbB200Matcher() override;
+    std::vector<DescriptorMatch> match(const std::vector<OrbKeypoint>& firstDescriptors,
+                                       const std::vector<OrbKeypoint>& secondDescriptors) override;
+
+  private:
+    std::shared_ptr<OrbB200Context> ctx;
+    std::vector<std::uint64_t> fromBuf, toBuf;
+};
+
+// ---- plugin_config.json (test/plugin_config.json:1-11 is the only schema hint in the reference) ----------------------
+//   {"plugins":[{"library":"libmslam_b200_plugin.so",
+//                "factoryMethods":{"featureDetector":"orbDetectorFactory","featureMatcher":"orbMatcherFactory"},
+//                "parameters":{"nfeatures":1000,"nlevels":8,"scaleFactor":1.2,"fastThreshold":20,"ratio":0.7,
+//                              "device":0,"maxWidth":1920,"maxHeight":1080}}]}
+struct PluginEntry
+{
+    std::string library;
+    std::string detectorFactory, matcherFactory; // factoryMethods.featureDetector / .featureMatcher
+    OrbB200Options options;
+};
+// returns false (and fills *error) on malformed input
+bool parsePluginConfig(const std::string& jsonText, std::vector<PluginEntry>* out, std::string* error);
+// options used by the default constructors / factories; set from the environment variable MSLAM_B200_PLUGIN_CONFIG
+// (path to a plugin_config.json) on first use, or explicitly here
+void setDefaultOrbB200Options(const OrbB200Options& options);
+OrbB200Options defaultOrbB200Options();
+
+} // namespace mslam

@@ -1,0 +1,112 @@
+// plugin_host_test.cpp -- a stand-in for the reference's side of the plugin boundary, used by tests/:
+// loads the plugin the way mslam::loadFactoryMethod does (plugin_loader.hpp:19-25: boost::dll::import_alias reads the
+// exported alias variable and calls the function it points to), then drives IFeatureDetector::detect /
+// IFeatureMatcher::match exactly as RgbdFeatureFrontend does (rgbd_feature_frontend.cpp:187,237).
+//
+//   plugin_host_test symbols <plugin.so>
+//   plugin_host_test config  <plugin_config.json>
+//   plugin_host_test run     <plugin.so> <frame0.raw> <frame1.raw> <W> <H> <out.bin>
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+
+#include "orb_b200_plugin.hpp"
+
+template <typename BlockType>
+using BlockFactoryCreator = std::unique_ptr<BlockType>(); // plugin_loader.hpp:13-14
+
+template <typename BlockType>
+static BlockFactoryCreator<BlockType>* loadFactoryMethod(void* lib, const char* name)
+{
+    // import_alias<T>(lib, name): the symbol is a variable holding the function's address
+    void* sym = dlsym(lib, name);
+    if(!sym)
+        return nullptr;
+    return *reinterpret_cast<BlockFactoryCreator<BlockType>**>(sym);
+}
+
+static bool readFile(const char* path, std::vector<std::uint8_t>* out)
+{
+    std::ifstream in(path, std::ios::binary);
+    if(!in)
+        return false;
+    out->assign(std::istreambuf_iterator<char>(in), std::istreambuf_iterator<char>());
+    return true;
+}
+
+int main(int argc, char** argv)
+{
+    if(argc >= 3 && !std::strcmp(argv[1], "config"))
+    {
+        std::ifstream in(argv[2]);
+        std::stringstream ss;
+        ss << in.rdbuf();
+        std::vector<mslam::PluginEntry> entries;
+        std::string err;
+        if(!in || !mslam::parsePluginConfig(ss.str(), &entries, &err))
+        {
+            std::printf("error: %s\n", err.c_str());
+            return 2;
+        }
+        for(const auto& e : entries)
+            std::printf("library=%s detector=%s matcher=%s nfeatures=%d nlevels=%d scaleFactor=%.3f fastThreshold=%d ratio=%.3f\n",
+                        e.library.c_str(), e.detectorFactory.c_str(), e.matcherFactory.c_str(), e.options.nfeatures,
+                        e.options.nlevels, e.options.scaleFactor, e.options.fastThreshold, e.options.ratio);
+        return 0;
+    }
+    if(argc < 3)
+    {
+        std::fprintf(stderr, "usage: see the header of plugin_host_test.cpp\n");
+        return 64;
+    }
+    void* lib = dlopen(argv[2], RTLD_NOW | RTLD_LOCAL);
+    if(!lib)
+    {
+        std::fprintf(stderr, "dlopen: %s\n", dlerror());
+        return 3;
+    }
+    auto* makeDetector = loadFactoryMethod<mslam::IOrbFeatureDetector>(lib, "orbDetectorFactory");
+    auto* makeMatcher = loadFactoryMethod<mslam::IOrbMatcher>(lib, "orbMatcherFactory");
+    if(!makeDetector || !makeMatcher)
+    {
+        std::fprintf(stderr, "factory aliases missing\n");
+        return 4;
+    }
+    if(!std::strcmp(argv[1], "symbols"))
+    {
+        std::printf("aliases ok: orbDetectorFactory orbMatcherFactory\n");
+        return 0;
+    }
+    if(std::strcmp(argv[1], "run") || argc < 8)
+        return 64;
+    mslam::RgbFrame f0, f1;
+    f0.size = f1.size = mslam::Size{std::atoi(argv[5]), std::atoi(argv[6])};
+    if(!readFile(argv[3], &f0.data) || !readFile(argv[4], &f1.data))
+        return 5;
+    try
+    {
+        std::shared_ptr<mslam::IOrbFeatureDetector> detector = makeDetector(); // unique_ptr -> shared_ptr, as the apps hold them
+        std::shared_ptr<mslam::IOrbMatcher> matcher = makeMatcher();
+        const std::vector<mslam::OrbKeypoint> k0 = detector->detect(f0);
+        const std::vector<mslam::OrbKeypoint> k1 = detector->detect(f1);
+        const std::vector<mslam::DescriptorMatch> m = matcher->match(k0, k1);
+        const std::vector<mslam::DescriptorMatch> none = matcher->match({}, k1);
+        std::ofstream out(argv[7], std::ios::binary);
+        const std::uint64_t hdr[4] = {k0.size(), k1.size(), m.size(), none.size()};
+        out.write(reinterpret_cast<const char*>(hdr), sizeof(hdr));
+        out.write(reinterpret_cast<const char*>(k0.data()), (std::streamsize)(k0.size() * sizeof(mslam::OrbKeypoint)));
+        out.write(reinterpret_cast<const char*>(k1.data()), (std::streamsize)(k1.size() * sizeof(mslam::OrbKeypoint)));
+        out.write(reinterpret_cast<const char*>(m.data()), (std::streamsize)(m.size() * sizeof(mslam::DescriptorMatch)));
+        std::printf("detect %zu + %zu keypoints, %zu matches\n", k0.size(), k1.size(), m.size());
+    }
+    catch(const std::exception& e)
+    {
+        std::fprintf(stderr, "plugin failed: %s\n", e.what());
+        return 6;
+    }
+    return 0;
+}

@@ -1,0 +1,80 @@
+"""The C++17 plugin adapter (modular-slam_b200/host): boost::dll-style factory aliases, plugin_config.json reader and --
+on the GPU -- the reference's own call sequence (detect, detect, match) through the plugin, compared with the oracle."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as graft
+
+LIB = os.path.join(graft.PKG_DIR, "lib")
+PLUGIN = os.path.join(LIB, "libmslam_b200_plugin.so")
+DRIVER = os.path.join(LIB, "plugin_host_test")
+
+
+@pytest.fixture(scope="module")
+def built():
+    if not (os.path.exists(PLUGIN) and os.path.exists(DRIVER)):
+        graft.build()
+    return DRIVER
+
+
+def test_factory_aliases_load_like_boost_dll_import_alias(built):
+    out = subprocess.run([built, "symbols", PLUGIN], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert "orbDetectorFactory" in out.stdout and "orbMatcherFactory" in out.stdout
+    # the aliases live in section "boostdll", as BOOST_DLL_ALIAS puts them (boost/dll/alias.hpp; test/dummy.cpp:11)
+    sec = subprocess.run(["readelf", "-S", "-W", PLUGIN], capture_output=True, text=True).stdout
+    assert "boostdll" in sec
+
+
+def test_plugin_config_reader(built, tmp_path):
+    cfg = {"plugins": [{"library": "libmslam_b200_plugin.so",
+                        "factoryMethods": {"featureDetector": "orbDetectorFactory", "featureMatcher": "orbMatcherFactory",
+                                           "loopDetection": "", "loopClosure": ""},
+                        "parameters": {"nfeatures": 2000, "nlevels": 8, "scaleFactor": 1.2, "fastThreshold": 20, "ratio": 0.7}}]}
+    p = tmp_path / "plugin_config.json"
+    p.write_text(json.dumps(cfg, indent=4))
+    out = subprocess.run([built, "config", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "detector=orbDetectorFactory matcher=orbMatcherFactory nfeatures=2000 nlevels=8 scaleFactor=1.200" in out.stdout
+    # the reference's own fixture schema (test/plugin_config.json:1-11) parses too: empty names, no parameters
+    p.write_text('{"plugins": [{"library": "", "factoryMethods": {"loopDetection": "", "loopClosure": ""}}]}')
+    out = subprocess.run([built, "config", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0 and "nfeatures=1000" in out.stdout and "ratio=0.700" in out.stdout
+    for bad in ('{"plugins": 3}', '{"plugins": [{"parameters": {"nlevels": 99}}]}', '{"plugins": [', "[]"):
+        p.write_text(bad)
+        assert subprocess.run([built, "config", str(p)], capture_output=True, text=True).returncode == 2, bad
+
+
+@pytest.mark.gpu
+def test_reference_call_sequence_through_the_plugin(built, oracle, bundled, tmp_path):
+    f0, f1 = tmp_path / "f0.raw", tmp_path / "f1.raw"
+    bundled["bgr0"].tofile(f0)
+    bundled["bgr1"].tofile(f1)
+    cfgp = tmp_path / "plugin_config.json"
+    cfgp.write_text(json.dumps({"plugins": [{"library": PLUGIN, "parameters": {"maxWidth": 640, "maxHeight": 480}}]}))
+    outp = tmp_path / "out.bin"
+    env = dict(os.environ, MSLAM_B200_PLUGIN_CONFIG=str(cfgp))
+    out = subprocess.run([built, "run", PLUGIN, str(f0), str(f1), "640", "480", str(outp)], capture_output=True, text=True,
+                         env=env)
+    assert out.returncode == 0, out.stdout + out.stderr
+    raw = outp.read_bytes()
+    n0, n1, nm, nnone = np.frombuffer(raw[:32], np.uint64).astype(int)
+    rec = np.dtype({"names": ["id", "coordinates", "descriptor"], "formats": ["<u8", ("<f8", (2,)), ("u1", (32,))],
+                    "offsets": [0, 16, 32], "itemsize": 64})
+    k0 = np.frombuffer(raw, rec, n0, 32)
+    k1 = np.frombuffer(raw, rec, n1, 32 + 64 * n0)
+    m = np.frombuffer(raw, np.dtype([("fromIndex", "<u8"), ("toIndex", "<u8")]), nm, 32 + 64 * (n0 + n1))
+    assert nnone == 0
+    for k, i in ((k0, 0), (k1, 1)):
+        okp, odesc = oracle.orb_detect_rgb(bundled[f"bgr{i}"])
+        assert len(k) == len(okp) == 1000
+        assert (k["coordinates"][:, 0] == okp["x"].astype(np.float64)).all()
+        assert (k["coordinates"][:, 1] == okp["y"].astype(np.float64)).all()
+        assert (k["descriptor"] == odesc).all()
+    fi, ti, _ = oracle.match_ratio(k0["descriptor"], k1["descriptor"])
+    assert nm == len(fi) == 693
+    assert (m["fromIndex"].astype(np.int64) == fi).all() and (m["toIndex"].astype(np.int64) == ti).all()
