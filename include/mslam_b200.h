@@ -71,7 +71,12 @@ typedef struct mslam_b200_config
     double ratio;       /* Lowe ratio of the kNN matcher, compared exactly as the reference does:
                            (double)(float)d0 < ratio * (double)(float)d1 */
     void* stream;       /* optional cudaStream_t to run on (e.g. the caller's); NULL => context-owned stream */
+    int flags;          /* MSLAM_B200_FLAG_* */
+    int reserved;
 } mslam_b200_config;
+/* run every kernel of detect on the one context stream (default: the pyramid chain, FAST + selection and the blur run on
+ * three forked streams that join before the describe kernel, so that small levels and latency-bound stages overlap) */
+#define MSLAM_B200_FLAG_SERIAL 1
 
 /* what cv::KeyPoint carries out of detectAndCompute (the reference interface keeps only pt, orb_feature.cpp:52-58) */
 typedef struct mslam_b200_keypoint

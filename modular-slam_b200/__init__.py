@@ -7,6 +7,6 @@ __graft_entry__.load_package() (the directory name carries a hyphen).
 """
 from .capi import (Context, Config, MslamB200Error, KP_DTYPE, LIB_PATH, library, default_config, pinned_empty,  # noqa: F401
                    OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM, STAGE_PYRAMID, STAGE_BLURRED, STAGE_N_FAST,
-                   STAGE_N_CUT1, STAGE_N_FINAL)
+                   STAGE_N_CUT1, STAGE_N_FINAL, FLAG_SERIAL)
 from .frontend import OrbB200Detector, OrbB200Matcher, RgbFrame  # noqa: F401
 from . import synth  # noqa: F401

@@ -22,7 +22,11 @@ class Config(C.Structure):
     _fields_ = [("struct_size", C.c_int), ("device", C.c_int), ("max_width", C.c_int), ("max_height", C.c_int),
                 ("max_batch", C.c_int), ("nfeatures", C.c_int), ("nlevels", C.c_int), ("scale_factor", C.c_float),
                 ("fast_threshold", C.c_int), ("edge_threshold", C.c_int), ("max_keypoints", C.c_int),
-                ("max_descriptors", C.c_int), ("ratio", C.c_double), ("stream", C.c_void_p)]
+                ("max_descriptors", C.c_int), ("ratio", C.c_double), ("stream", C.c_void_p), ("flags", C.c_int),
+                ("reserved", C.c_int)]
+
+
+FLAG_SERIAL = 1
 
 
 class MslamB200Error(RuntimeError):

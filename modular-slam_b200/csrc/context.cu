@@ -57,6 +57,10 @@ struct mslam_b200_ctx
     unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
     int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
     int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
+    // ---- forked streams of the detect pipeline ----
+    cudaStream_t aux[2] = {nullptr, nullptr};
+    cudaEvent_t ev_level[kMaxLevels] = {nullptr};
+    cudaEvent_t ev_join[2] = {nullptr, nullptr};
     // ---- per-stage event timing (mslam_b200_enable_stage_timing) ----
     bool timing = false;
     std::vector<cudaEvent_t> ev_pool; // pairs: [2i] start, [2i+1] stop
@@ -73,19 +77,20 @@ struct StageTimer
     mslam_b200_ctx* c;
     long long l0;
     int pair = -1;
-    StageTimer(mslam_b200_ctx* ctx, int stage) : c(ctx), l0(ctx->launches)
+    cudaStream_t st;
+    StageTimer(mslam_b200_ctx* ctx, int stage, cudaStream_t on = nullptr) : c(ctx), l0(ctx->launches), st(on ? on : ctx->stream)
     {
         if(!c->timing || c->ev_used >= c->ev_stage.size())
             return;
         pair = (int)c->ev_used++;
         c->ev_stage[pair] = stage;
-        cudaEventRecord(c->ev_pool[2 * pair], c->stream);
+        cudaEventRecord(c->ev_pool[2 * pair], st);
     }
     ~StageTimer()
     {
         if(pair < 0)
             return;
-        cudaEventRecord(c->ev_pool[2 * pair + 1], c->stream);
+        cudaEventRecord(c->ev_pool[2 * pair + 1], st);
         c->ev_launches[pair] = c->launches - l0;
     }
 };
@@ -324,6 +329,19 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
             cudaFreeHost(p);
     for(cudaEvent_t e : ctx->ev_pool)
         cudaEventDestroy(e);
+    for(int i = 0; i < 2; ++i)
+    {
+        if(ctx->aux[i])
+        {
+            cudaStreamSynchronize(ctx->aux[i]);
+            cudaStreamDestroy(ctx->aux[i]);
+        }
+        if(ctx->ev_join[i])
+            cudaEventDestroy(ctx->ev_join[i]);
+    }
+    for(int i = 0; i < kMaxLevels; ++i)
+        if(ctx->ev_level[i])
+            cudaEventDestroy(ctx->ev_level[i]);
     if(ctx->own_stream && ctx->stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -376,6 +394,13 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
         CREATE_OK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
         ctx->own_stream = true;
     }
+    for(int i = 0; i < 2; ++i)
+    {
+        CREATE_OK(cudaStreamCreateWithFlags(&ctx->aux[i], cudaStreamNonBlocking));
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
+    }
+    for(int i = 0; i < kMaxLevels; ++i)
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_level[i], cudaEventDisableTiming));
     Geometry g;
     build_geometry(c, ctx->kp_cap, c.max_width, c.max_height, &g);
     const size_t B = (size_t)c.max_batch;
@@ -494,7 +519,7 @@ static int run_pyramid(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames)
     }
     {
         StageTimer t(ctx, MSLAM_B200_T_RESIZE);
-        launch_pyramid(ctx->stream, ctx->d_pyr, ctx->P, ctx->d_xtab, ctx->d_ytab, &ctx->launches);
+        launch_pyramid(ctx->stream, ctx->d_pyr, ctx->P, ctx->d_xtab, ctx->d_ytab, 1, ctx->P.nlevels, &ctx->launches);
     }
     return MSLAM_B200_OK;
 }
@@ -510,25 +535,82 @@ int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n
         return rc;
     cudaStream_t st = ctx->stream;
     MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
-    run_pyramid(ctx, d_bgr, n_frames);
-    const PipeParams& P = ctx->P;
+    const int n_slots = std::min(capacity, ctx->kp_cap * ctx->P.nlevels);
+    if(ctx->cfg.flags & MSLAM_B200_FLAG_SERIAL)
     {
-        StageTimer t(ctx, MSLAM_B200_T_FAST);
-        launch_fast(st, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, &ctx->launches);
-    }
-    {
-        StageTimer t(ctx, MSLAM_B200_T_SELECT);
-        launch_select(st, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
-                      ctx->d_sel, ctx->d_err, P, &ctx->launches);
-    }
-    {
-        StageTimer t(ctx, MSLAM_B200_T_BLUR);
-        launch_blur(st, ctx->d_pyr, ctx->d_blur, P, &ctx->launches);
-    }
-    {
+        run_pyramid(ctx, d_bgr, n_frames);
+        const PipeParams& P = ctx->P;
+        {
+            StageTimer t(ctx, MSLAM_B200_T_FAST);
+            launch_fast(st, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, 0, P.nlevels, &ctx->launches);
+        }
+        {
+            StageTimer t(ctx, MSLAM_B200_T_SELECT);
+            launch_select(st, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
+                          ctx->d_sel, ctx->d_err, P, &ctx->launches);
+        }
+        {
+            StageTimer t(ctx, MSLAM_B200_T_BLUR);
+            launch_blur(st, ctx->d_pyr, ctx->d_blur, P, 0, P.nlevels, &ctx->launches);
+        }
         StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
         launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, d_kp, d_desc, d_counts, capacity,
-                               std::min(capacity, ctx->kp_cap * P.nlevels), P, &ctx->launches);
+                               n_slots, P, &ctx->launches);
+    }
+    else
+    {
+        // Dependency graph of one batch:  gray -> L1 -> L2 -> ... (chained resize, main stream)
+        //   FAST(l) and blur(l) need only level l; select needs every FAST; describe needs select and every blur.
+        // The chain, FAST + select (aux 0) and the blur (aux 1) run on three streams that fork at the level events and
+        // join before describe, so the latency-bound pieces (small levels, the one-CTA-per-level selection) hide
+        // under the throughput-bound ones.
+        ctx->P.n_frames = n_frames;
+        const PipeParams& P = ctx->P;
+        cudaStream_t s_fast = ctx->aux[0], s_blur = ctx->aux[1];
+        const int nl = P.nlevels, l_split = std::min(2, nl); // levels < l_split get their own FAST launch
+        {
+            StageTimer t(ctx, MSLAM_B200_T_GRAY);
+            launch_gray(st, d_bgr, ctx->d_pyr, P, &ctx->launches);
+        }
+        MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[0], st));
+        for(int l = 1; l < nl; ++l)
+        {
+            {
+                StageTimer t(ctx, MSLAM_B200_T_RESIZE);
+                launch_pyramid(st, ctx->d_pyr, P, ctx->d_xtab, ctx->d_ytab, l, l + 1, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[l], st));
+        }
+        for(int l = 0; l < l_split; ++l)
+        {
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_fast, ctx->ev_level[l], 0));
+            StageTimer t(ctx, MSLAM_B200_T_FAST, s_fast);
+            launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, l, l + 1, &ctx->launches);
+        }
+        if(l_split < nl)
+        {
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_fast, ctx->ev_level[nl - 1], 0));
+            StageTimer t(ctx, MSLAM_B200_T_FAST, s_fast);
+            launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, l_split, nl, &ctx->launches);
+        }
+        {
+            StageTimer t(ctx, MSLAM_B200_T_SELECT, s_fast);
+            launch_select(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
+                          ctx->d_sel, ctx->d_err, P, &ctx->launches);
+        }
+        MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[0], s_fast));
+        for(int l = 0; l < nl; ++l)
+        {
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_blur, ctx->ev_level[l], 0));
+            StageTimer t(ctx, MSLAM_B200_T_BLUR, s_blur);
+            launch_blur(s_blur, ctx->d_pyr, ctx->d_blur, P, l, l + 1, &ctx->launches);
+        }
+        MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[1], s_blur));
+        MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[0], 0));
+        MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[1], 0));
+        StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
+        launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, d_kp, d_desc, d_counts, capacity,
+                               n_slots, P, &ctx->launches);
     }
     ctx->last_frames = n_frames;
     MSLAM_CUDA_OK(cudaGetLastError());
@@ -638,7 +720,7 @@ int mslam_b200_describe(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int 
     MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_ctr, ctr.data(), nl * sizeof(LevelCounters), cudaMemcpyHostToDevice, st));
     MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_sel, sel.data(), sel.size() * sizeof(SelRec), cudaMemcpyHostToDevice, st));
     run_pyramid(ctx, ctx->d_bgr, 1);
-    launch_blur(st, ctx->d_pyr, ctx->d_blur, ctx->P, &ctx->launches);
+    launch_blur(st, ctx->d_pyr, ctx->d_blur, ctx->P, 0, ctx->P.nlevels, &ctx->launches);
     launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,
                            std::max(n_kp, 1), ctx->P, &ctx->launches);
     std::vector<mslam_b200_keypoint> hk((size_t)std::max(n_kp, 1));

@@ -7,11 +7,12 @@ namespace mslam_b200
 // ORB path
 void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const PipeParams& P, long long* launches);
 void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const short2* xtab, const short2* ytab,
-                    long long* launches);
-void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, long long* launches);
+                    int l_begin, int l_end, long long* launches);
+void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, int l_begin, int l_end,
+                 long long* launches);
 void fast_tiles(int w, int h, int edge, int* tx, int* ty);
 void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCounters* ctr, unsigned* hist,
-                 const PipeParams& P, long long* launches);
+                 const PipeParams& P, int l_begin, int l_end, long long* launches);
 void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned* cand2, unsigned* keys, unsigned* keys2,
                    LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P,
                    long long* launches);

@@ -109,7 +109,8 @@ __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src,
 //   row pass  acc = k0*p[x-3]; acc = fma(k_j, p[x-3+j], acc)  j = 1..6
 //   col pass  acc = k3*r[y];   acc = fma(k_{3+i}, r[y+i] + r[y-i], acc)  i = 1..3 ; out = sat_u8(rint(acc))
 // =================================================================================================
-constexpr int BT_W = 64, BT_H = 16;
+constexpr int BT_W = 128, BT_H = 32;            // output tile
+constexpr int BT_PW = BT_W + 8, BT_PH = BT_H + 6; // staged pixels (4-byte aligned 3-px halo)
 
 __device__ __forceinline__ int reflect101(int p, int n)
 {
@@ -120,102 +121,235 @@ __device__ __forceinline__ int reflect101(int p, int n)
     return p;
 }
 
+// exact u8 -> f32 without the XU pipe's I2F: 0x4B000000 | b is the float 8388608 + b
+__device__ __forceinline__ float byte_to_float(unsigned word, int i)
+{
+    return __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 + i)), 8388608.f);
+}
+
+// A thread produces 4 horizontally adjacent pixels in both passes; the row pass keeps its f32 results in shared
+// memory (float4), the column pass rounds with the 1.5 * 2^23 magic add (round-to-nearest-even, like cvRound) and
+// packs 4 bytes per store.
 __global__ void __launch_bounds__(256) k_blur(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int pitch,
                                               long long fs, int w, int h)
 {
-    __shared__ uint8_t s_in[BT_H + 6][BT_W + 8];
-    __shared__ float s_mid[BT_H + 6][BT_W];
+    __shared__ __align__(16) uint8_t s_in[BT_PH][BT_PW];
+    __shared__ __align__(16) float s_mid[BT_PH][BT_W];
     const float k0 = __int_as_float(0x3d8fafb1), k1 = __int_as_float(0x3e06387e), k2 = __int_as_float(0x3e434a39),
                 k3 = __int_as_float(0x3e5d4ae0);
     const float kk[7] = {k0, k1, k2, k3, k2, k1, k0};
     const int tx0 = blockIdx.x * BT_W, ty0 = blockIdx.y * BT_H;
     const uint8_t* img = src + (long long)blockIdx.z * fs;
-    for(int i = threadIdx.x; i < (BT_H + 6) * (BT_W + 6); i += 256)
+    for(int i = threadIdx.x; i < BT_PH * (BT_PW / 4); i += 256)
     {
-        const int ry = i / (BT_W + 6), rx = i - ry * (BT_W + 6);
-        const int gy = reflect101(ty0 - 3 + ry, h), gx = reflect101(tx0 - 3 + rx, w);
-        s_in[ry][rx] = __ldg(img + (long long)gy * pitch + gx);
+        const int r = i / (BT_PW / 4), c = i - r * (BT_PW / 4);
+        const int gy = reflect101(ty0 - 3 + r, h), gx = tx0 - 4 + 4 * c;
+        const uint8_t* row = img + (long long)gy * pitch;
+        unsigned v;
+        if(gx >= 0 && gx + 3 < w)
+            v = __ldg(reinterpret_cast<const unsigned*>(row + gx));
+        else
+            v = (unsigned)__ldg(row + reflect101(gx, w)) | ((unsigned)__ldg(row + reflect101(gx + 1, w)) << 8) |
+                ((unsigned)__ldg(row + reflect101(gx + 2, w)) << 16) | ((unsigned)__ldg(row + reflect101(gx + 3, w)) << 24);
+        reinterpret_cast<unsigned*>(&s_in[r][0])[c] = v;
     }
     __syncthreads();
-    for(int i = threadIdx.x; i < (BT_H + 6) * BT_W; i += 256)
+    // row pass: acc = k0 * p[x-3]; acc = fma(k_j, p[x-3+j], acc)
+    for(int i = threadIdx.x; i < BT_PH * (BT_W / 4); i += 256)
     {
-        const int ry = i / BT_W, x = i - ry * BT_W;
-        float acc = __fmul_rn(kk[0], (float)s_in[ry][x]);
+        const int r = i / (BT_W / 4), g = i - r * (BT_W / 4);
+        const unsigned* wrow = reinterpret_cast<const unsigned*>(&s_in[r][0]) + g;
+        const unsigned wa = wrow[0], wb = wrow[1], wc = wrow[2]; // staged x = 4g .. 4g + 11  <->  output x - 4 .. x + 7
+        const float p[10] = {byte_to_float(wa, 1), byte_to_float(wa, 2), byte_to_float(wa, 3), byte_to_float(wb, 0),
+                             byte_to_float(wb, 1), byte_to_float(wb, 2), byte_to_float(wb, 3), byte_to_float(wc, 0),
+                             byte_to_float(wc, 1), byte_to_float(wc, 2)};
+        float o[4];
 #pragma unroll
-        for(int j = 1; j < 7; ++j)
-            acc = __fmaf_rn(kk[j], (float)s_in[ry][x + j], acc);
-        s_mid[ry][x] = acc;
+        for(int q = 0; q < 4; ++q)
+        {
+            float acc = __fmul_rn(kk[0], p[q]);
+#pragma unroll
+            for(int j = 1; j < 7; ++j)
+                acc = __fmaf_rn(kk[j], p[q + j], acc);
+            o[q] = acc;
+        }
+        *reinterpret_cast<float4*>(&s_mid[r][4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
     }
     __syncthreads();
-    for(int i = threadIdx.x; i < BT_H * BT_W; i += 256)
+    // column pass: acc = k3 * r[y]; acc = fma(k_{3+i}, r[y+i] + r[y-i], acc); out = sat_u8(rint(acc))
+    for(int i = threadIdx.x; i < BT_H * (BT_W / 4); i += 256)
     {
-        const int y = i / BT_W, x = i - y * BT_W;
-        if(tx0 + x >= w || ty0 + y >= h)
+        const int y = i / (BT_W / 4), g = i - y * (BT_W / 4);
+        const int gx = tx0 + 4 * g, gy = ty0 + y;
+        if(gx >= w || gy >= h)
             continue;
-        float acc = __fmul_rn(k3, s_mid[y + 3][x]);
+        float4 m[7];
 #pragma unroll
-        for(int j = 1; j <= 3; ++j)
-            acc = __fmaf_rn(kk[3 + j], __fadd_rn(s_mid[y + 3 + j][x], s_mid[y + 3 - j][x]), acc);
-        int v = __float2int_rn(acc);
-        v = min(max(v, 0), 255);
-        dst[(long long)blockIdx.z * fs + (long long)(ty0 + y) * pitch + tx0 + x] = (uint8_t)v;
+        for(int j = 0; j < 7; ++j)
+            m[j] = *reinterpret_cast<const float4*>(&s_mid[y + j][4 * g]);
+        const float* mf = reinterpret_cast<const float*>(m);
+        unsigned bits[4];
+#pragma unroll
+        for(int q = 0; q < 4; ++q)
+        {
+            float acc = __fmul_rn(k3, mf[3 * 4 + q]);
+#pragma unroll
+            for(int j = 1; j <= 3; ++j)
+                acc = __fmaf_rn(kk[3 + j], __fadd_rn(mf[(3 + j) * 4 + q], mf[(3 - j) * 4 + q]), acc);
+            // 0 <= acc < 256 (weights sum to 1 within rounding), so the low byte of acc + 1.5 * 2^23 is rint(acc)
+            bits[q] = __float_as_uint(__fadd_rn(acc, 12582912.f));
+        }
+        const unsigned lo = __byte_perm(bits[0], bits[1], 0x0040), hi = __byte_perm(bits[2], bits[3], 0x0040);
+        *reinterpret_cast<unsigned*>(dst + (long long)blockIdx.z * fs + (long long)gy * pitch + gx) =
+            __byte_perm(lo, hi, 0x5410);
     }
 }
 
 // =================================================================================================
-// K3  FAST-9/16 + 3x3 strict NMS + border filter (items 3, 4) on one level of the whole batch.
-//   One CTA = 64x16 interior pixels.  Pixels are staged once in shared memory (4-px halo, 32-bit
-//   aligned loads); every position first runs the two-pixel high-speed rejects, then the exact
-//   16-bit bright/dark ring masks (9 contiguous set bits); corner positions are queued and only
-//   those get the exact cornerScore (max over the 16 arcs of the arc minimum, minus 1).
-//   Survivors of the NMS are appended to the level's candidate list (one global atomic per CTA) and
-//   counted into the level's 256-bin score histogram that retainBest's first cut needs.
+// K3  FAST-9/16 + 3x3 strict NMS + border filter (items 3, 4), any range of levels in one launch.
+//
+//   One CTA scores a 128 x 32 block of positions (assigned interior 124 x 30, the rest is the 1-px halo the NMS
+//   needs plus 4-byte alignment), pixels staged once in shared memory (136 x 38).
+//   Phase A, corner classification, is branch-free byte-SIMD: a thread owns 4 horizontally adjacent centres x 4
+//   rows.  For each of the 16 ring offsets the 4 ring pixels are one PRMT of two staged words; "ring > centre + t"
+//   and "ring < centre - t" are the carry-outs of byte-wise additions, evaluated for 4 pixels at once with one
+//   7-bit add and one majority LOP3 each (bit 7 of every byte carries the answer).  The "9 contiguous" test is
+//   bit-sliced over the 16 masks: a3_k = m_k & m_k+1 & m_k+2, a9_k = a3_k & a3_k+3 & a3_k+6, any = OR a9_k -- 40 LOP3
+//   per side per 4 pixels, no divergence however dense the corners are.
+//   Phase B scores only the corners, compacted CTA-wide into a queue: cornerScore = max over the 16 arcs of the arc
+//   minimum of |centre - ring| on the bright or the dark side, minus 1.  Both sides run through ONE packed u16x2
+//   max/min network (lane 0 = ring value, lane 1 = 255 - ring value; VIMNMX.U16x2), with the arc maxima built from
+//   block prefix/suffix maxima (28 + 16 ops) instead of 16 independent 9-element reductions.
+//   Phase C walks the same queue for the strict 3x3 NMS and the border filter; survivors go to the level's
+//   candidate list (one global atomic per CTA) and its 256-bin score histogram (first retainBest cut).
 // =================================================================================================
-constexpr int FT_W = 64, FT_H = 16;
-constexpr int FS_W = FT_W + 8, FS_H = FT_H + 8; // staged pixels
-constexpr int SC_W = FT_W + 2, SC_H = FT_H + 2; // scored positions
-constexpr int SC_P = 68;                        // score row pitch
+constexpr int FS_SW = 128, FS_SH = 32;          // scored positions per CTA
+constexpr int FS_IW = FS_SW - 4, FS_IH = FS_SH - 2; // assigned interior
+constexpr int FS_PW = FS_SW + 8, FS_PH = FS_SH + 6; // staged pixels
+constexpr int FS_PWW = FS_PW / 4;               // staged words per row (34)
 
-__device__ __forceinline__ bool has_run9(unsigned m)
+__device__ __forceinline__ unsigned lop3_maj_a_nb_c(unsigned a, unsigned b, unsigned c)
 {
-    unsigned x = m | (m << 16);
-    x &= x >> 1;
-    x &= x >> 2;
-    x &= x >> 4;
-    x &= x >> 1;
-    return x != 0;
+    unsigned r; // majority(a, ~b, c)
+    asm("lop3.b32 %0, %1, %2, %3, 0xB2;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ unsigned and3(unsigned a, unsigned b, unsigned c)
+{
+    unsigned r;
+    asm("lop3.b32 %0, %1, %2, %3, 0x80;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ unsigned or3(unsigned a, unsigned b, unsigned c)
+{
+    unsigned r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xFE;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
 }
 
-__global__ void __launch_bounds__(256) k_fast(const __grid_constant__ PipeParams P, int l, const uint8_t* __restrict__ pyr,
-                                              unsigned* __restrict__ cand, LevelCounters* __restrict__ ctr,
-                                              unsigned* __restrict__ hist)
+// bit 7 of each byte of the result: does the pixel have 9 contiguous set masks among m[0..15] (cyclic)?
+__device__ __forceinline__ unsigned any_run9(const unsigned (&m)[16])
 {
-    __shared__ __align__(16) uint8_t s_px[FS_H][FS_W];
-    __shared__ __align__(4) uint8_t s_sc[SC_H][SC_P];
-    __shared__ unsigned short s_q[SC_H * SC_W];
-    __shared__ unsigned s_out[FT_W * FT_H / 4];
+    unsigned a3[16];
+#pragma unroll
+    for(int k = 0; k < 16; ++k)
+        a3[k] = and3(m[k], m[(k + 1) & 15], m[(k + 2) & 15]);
+    unsigned a9[16];
+#pragma unroll
+    for(int k = 0; k < 16; ++k)
+        a9[k] = and3(a3[k], a3[(k + 3) & 15], a3[(k + 6) & 15]);
+    const unsigned o0 = or3(a9[0], a9[1], a9[2]), o1 = or3(a9[3], a9[4], a9[5]), o2 = or3(a9[6], a9[7], a9[8]),
+                   o3 = or3(a9[9], a9[10], a9[11]), o4 = or3(a9[12], a9[13], a9[14]);
+    return or3(or3(o0, o1, o2), or3(o3, o4, a9[15]), 0u);
+}
+
+// the 4 pixels starting dx (in -3..3) bytes from the start of word w0, out of the row's three staged words
+__device__ __forceinline__ unsigned ring4(unsigned wm, unsigned w0, unsigned wp, int dx)
+{
+    switch(dx)
+    {
+    case -3: return __byte_perm(wm, w0, 0x4321);
+    case -2: return __byte_perm(wm, w0, 0x5432);
+    case -1: return __byte_perm(wm, w0, 0x6543);
+    case 1: return __byte_perm(w0, wp, 0x4321);
+    case 2: return __byte_perm(w0, wp, 0x5432);
+    case 3: return __byte_perm(w0, wp, 0x6543);
+    default: return w0;
+    }
+}
+
+// exact cornerScore of a pixel known to be a FAST corner
+__device__ __forceinline__ int corner_score(const uint8_t* c /* centre in the staged tile */)
+{
+    constexpr int S = FS_PW;
+    const int v = c[0];
+    const int ring[16] = {c[3 * S],      c[3 * S + 1],  c[2 * S + 2],  c[S + 3],  c[3],  c[-S + 3], c[-2 * S + 2], c[-3 * S + 1],
+                          c[-3 * S],     c[-3 * S - 1], c[-2 * S - 2], c[-S - 3], c[-3], c[S - 3],  c[2 * S - 2],  c[3 * S - 1]};
+    unsigned x[16]; // lane 0 = ring value, lane 1 = 255 - ring value
+#pragma unroll
+    for(int k = 0; k < 16; ++k)
+        x[k] = (unsigned)ring[k] * 0xFFFF0001u + 0x00FF0000u;
+    unsigned pa[8], sa[8], pb[8], sb[8]; // prefix / suffix maxima of the two half rings
+    pa[0] = x[0], pb[0] = x[8], sa[7] = x[7], sb[7] = x[15];
+#pragma unroll
+    for(int i = 1; i < 8; ++i)
+    {
+        pa[i] = __vmaxu2(pa[i - 1], x[i]);
+        pb[i] = __vmaxu2(pb[i - 1], x[8 + i]);
+        sa[7 - i] = __vmaxu2(sa[8 - i], x[7 - i]);
+        sb[7 - i] = __vmaxu2(sb[8 - i], x[15 - i]);
+    }
+    // arc k..k+8: k < 8 -> suffix of A from k + prefix of B to k ; k = 8 + j -> suffix of B from j + prefix of A to j
+    unsigned m = 0xffffffffu;
+#pragma unroll
+    for(int k = 0; k < 8; ++k)
+    {
+        m = __vminu2(m, __vmaxu2(sa[k], pb[k]));
+        m = __vminu2(m, __vmaxu2(sb[k], pa[k]));
+    }
+    const int bright = v - (int)(m & 0xffffu);            // centre above the whole arc
+    const int dark = 255 - (int)(m >> 16) - v;            // centre below the whole arc
+    return max(bright, dark) - 1;
+}
+
+__global__ void __launch_bounds__(256) k_fast(const __grid_constant__ PipeParams P, int l_begin, int l_end,
+                                              const uint8_t* __restrict__ pyr, unsigned* __restrict__ cand,
+                                              LevelCounters* __restrict__ ctr, unsigned* __restrict__ hist)
+{
+    __shared__ __align__(16) uint8_t s_px[FS_PH][FS_PW];
+    __shared__ __align__(16) uint8_t s_sc[FS_SH][FS_SW];
+    __shared__ unsigned short s_q[FS_SH * FS_SW];
+    __shared__ unsigned s_out[FS_IW * FS_IH / 4 + 64];
     __shared__ int s_qn, s_on;
     __shared__ unsigned s_base;
 
+    // which level does this tile belong to?
+    int l = l_begin;
+    int tile = (int)blockIdx.x + P.lv[l_begin].tile_base;
+    while(l + 1 < l_end && tile >= P.lv[l + 1].tile_base)
+        ++l;
     const LevelDesc& L = P.lv[l];
-    const int b = blockIdx.z;
-    const int tid = threadIdx.x;
+    tile -= L.tile_base;
+    const int ty = tile / L.tiles_x, tx = tile - ty * L.tiles_x;
+    const int b = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int edge = P.edge, thr = P.fast_thr;
-    const int ox0 = (edge & ~3) + FT_W * blockIdx.x, oy0 = edge + FT_H * blockIdx.y; // first interior pixel of the tile
-    const int hx0 = ox0 - 4, hy0 = oy0 - 4;                                           // first staged pixel
+    const int sx0 = ((edge - 1) & ~3) + FS_IW * tx; // first scored column (multiple of 4)
+    const int sy0 = edge - 1 + FS_IH * ty;          // first scored row
+    const int px0 = sx0 - 4, py0 = sy0 - 3;         // first staged pixel
     const uint8_t* img = pyr + L.img_off + (long long)b * L.img_frame_stride;
 
-    for(int i = tid; i < FS_H * (FS_W / 4); i += 256)
+    for(int i = tid; i < FS_PH * FS_PWW; i += 256)
     {
-        const int r = i / (FS_W / 4), c = i - r * (FS_W / 4);
-        const int gy = hy0 + r, gx = hx0 + 4 * c;
+        const int r = i / FS_PWW, c = i - r * FS_PWW;
+        const int gy = py0 + r, gx = px0 + 4 * c;
         unsigned v = 0;
         if(gy < L.h && gx < L.pitch)
             v = __ldg(reinterpret_cast<const unsigned*>(img + (long long)gy * L.pitch + gx));
         reinterpret_cast<unsigned*>(&s_px[r][0])[c] = v;
     }
-    for(int i = tid; i < SC_H * SC_P / 4; i += 256)
-        reinterpret_cast<unsigned*>(&s_sc[0][0])[i] = 0;
+    for(int i = tid; i < FS_SH * FS_SW / 16; i += 256)
+        reinterpret_cast<uint4*>(&s_sc[0][0])[i] = make_uint4(0, 0, 0, 0);
     if(tid == 0)
     {
         s_qn = 0;
@@ -223,101 +357,126 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ PipeParams
     }
     __syncthreads();
 
-    // ---- corner test on every scored position ----
-    for(int i = tid; i < SC_H * SC_W; i += 256)
+    // ---- phase A: classify 4 rows x 4 pixels per thread ----
+    unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row 4 * warp + row is a corner
     {
-        const int sy = i / SC_W, sx = i - sy * SC_W;
-        const int x = ox0 - 1 + sx, y = oy0 - 1 + sy;
-        if(x < edge - 1 || x > L.w - edge || y > L.h - edge)
-            continue;
-        const uint8_t* c = &s_px[sy + 3][sx + 3];
-        const int v = c[0], hi = v + thr, lo = v - thr;
-        const int p0 = c[3 * FS_W], p8 = c[-3 * FS_W];
-        bool br = (p0 > hi) | (p8 > hi), dk = (p0 < lo) | (p8 < lo);
-        if(!(br | dk))
-            continue;
-        const int p4 = c[3], p12 = c[-3];
-        br &= (p4 > hi) | (p12 > hi);
-        dk &= (p4 < lo) | (p12 < lo);
-        if(!(br | dk))
-            continue;
-        const int r1 = c[3 * FS_W + 1], r2 = c[2 * FS_W + 2], r3 = c[FS_W + 3], r5 = c[-FS_W + 3], r6 = c[-2 * FS_W + 2],
-                  r7 = c[-3 * FS_W + 1], r9 = c[-3 * FS_W - 1], r10 = c[-2 * FS_W - 2], r11 = c[-FS_W - 3],
-                  r13 = c[FS_W - 3], r14 = c[2 * FS_W - 2], r15 = c[3 * FS_W - 1];
-        const int ring[16] = {p0, r1, r2, r3, p4, r5, r6, r7, p8, r9, r10, r11, p12, r13, r14, r15};
-        unsigned mb = 0, md = 0;
+        const unsigned t4 = (unsigned)thr * 0x01010101u;
+        const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[4 * warp][0]) + lane;
+        unsigned wm[10], w0[10], wp[10]; // staged rows 4 * warp .. 4 * warp + 9, words lane, lane + 1, lane + 2
 #pragma unroll
-        for(int k = 0; k < 16; ++k)
+        for(int r = 0; r < 10; ++r)
         {
-            mb |= (unsigned)(ring[k] > hi) << k;
-            md |= (unsigned)(ring[k] < lo) << k;
+            wm[r] = wbase[r * FS_PWW];
+            w0[r] = wbase[r * FS_PWW + 1];
+            wp[r] = wbase[r * FS_PWW + 2];
         }
-        if(has_run9(mb) || has_run9(md))
-            s_q[atomicAdd(&s_qn, 1)] = (unsigned short)i;
+#pragma unroll
+        for(int row = 0; row < 4; ++row)
+        {
+            const unsigned C = w0[row + 3];
+            const unsigned H = __vaddus4(C, t4), Lo = __vsubus4(C, t4);
+            const unsigned nH7 = ~H & 0x7f7f7f7fu;
+            const unsigned K = (Lo & 0x7f7f7f7fu) + 0x7f7f7f7fu;
+            unsigned mb[16], md[16];
+            // ring offsets (dx, dy), k = 0..15, as in cv::FAST's 16-pixel circle
+            constexpr int DX[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
+            constexpr int DY[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+#pragma unroll
+            for(int k = 0; k < 16; ++k)
+            {
+                const int r = row + 3 + DY[k];
+                const unsigned R = ring4(wm[r], w0[r], wp[r], DX[k]);
+                const unsigned r7 = R & 0x7f7f7f7fu;
+                mb[k] = lop3_maj_a_nb_c(R, H, r7 + nH7);  // bit 7: R > centre + t
+                md[k] = lop3_maj_a_nb_c(Lo, R, K - r7);   // bit 7: R < centre - t
+            }
+            const unsigned f = (any_run9(mb) | any_run9(md)) & 0x80808080u;
+            // gather the four bit-7 flags into a nibble
+            flags16 |= (((f >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
+        }
+    }
+    // only positions that can matter: inside the image interior +- 1 (the NMS halo)
+    {
+        unsigned keep = 0;
+        const int x = sx0 + 4 * lane;
+#pragma unroll
+        for(int row = 0; row < 4; ++row)
+        {
+            const int y = sy0 + 4 * warp + row;
+            const bool yok = y <= L.h - edge; // y >= edge - 1 by construction
+#pragma unroll
+            for(int j = 0; j < 4; ++j)
+                if(yok && x + j >= edge - 1 && x + j <= L.w - edge)
+                    keep |= 1u << (4 * row + j);
+        }
+        flags16 &= keep;
+    }
+    // warp-aggregated append to the CTA's corner queue
+    {
+        const int cnt = __popc(flags16);
+        int incl = cnt;
+#pragma unroll
+        for(int o = 1; o < 32; o <<= 1)
+        {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if(lane >= o)
+                incl += t;
+        }
+        int wbase_q = 0;
+        if(lane == 31)
+            wbase_q = atomicAdd(&s_qn, incl);
+        wbase_q = __shfl_sync(0xffffffffu, wbase_q, 31);
+        int pos = wbase_q + incl - cnt;
+        unsigned f = flags16;
+        while(f)
+        {
+            const int bit = __ffs(f) - 1;
+            f &= f - 1;
+            s_q[pos++] = (unsigned short)((4 * warp + (bit >> 2)) * FS_SW + 4 * lane + (bit & 3));
+        }
     }
     __syncthreads();
 
-    // ---- exact cornerScore for the queued corners ----
+    // ---- phase B: exact cornerScore of the queued corners ----
     const int nq = s_qn;
     for(int j = tid; j < nq; j += 256)
     {
         const int i = s_q[j];
-        const int sy = i / SC_W, sx = i - sy * SC_W;
-        const uint8_t* c = &s_px[sy + 3][sx + 3];
-        const int v = c[0];
-        int mn[16], mx[16];
-        {
-            const int ring[16] = {c[3 * FS_W],      c[3 * FS_W + 1],  c[2 * FS_W + 2],  c[FS_W + 3],
-                                  c[3],             c[-FS_W + 3],     c[-2 * FS_W + 2], c[-3 * FS_W + 1],
-                                  c[-3 * FS_W],     c[-3 * FS_W - 1], c[-2 * FS_W - 2], c[-FS_W - 3],
-                                  c[-3],            c[FS_W - 3],      c[2 * FS_W - 2],  c[3 * FS_W - 1]};
-            // sliding window of 9 over the cyclic ring: 2 -> 4 -> 8 -> 9
-            int a2[16], b2[16], a4[16], b4[16];
-#pragma unroll
-            for(int k = 0; k < 16; ++k)
-            {
-                a2[k] = min(ring[k], ring[(k + 1) & 15]);
-                b2[k] = max(ring[k], ring[(k + 1) & 15]);
-            }
-#pragma unroll
-            for(int k = 0; k < 16; ++k)
-            {
-                a4[k] = min(a2[k], a2[(k + 2) & 15]);
-                b4[k] = max(b2[k], b2[(k + 2) & 15]);
-            }
-#pragma unroll
-            for(int k = 0; k < 16; ++k)
-            {
-                mn[k] = min(min(a4[k], a4[(k + 4) & 15]), ring[(k + 8) & 15]);
-                mx[k] = max(max(b4[k], b4[(k + 4) & 15]), ring[(k + 8) & 15]);
-            }
-        }
-        int best_min = mn[0], best_max = mx[0]; // max over arcs of arc-min ; min over arcs of arc-max
-#pragma unroll
-        for(int k = 1; k < 16; ++k)
-        {
-            best_min = max(best_min, mn[k]);
-            best_max = min(best_max, mx[k]);
-        }
-        const int score = max(best_min - v, v - best_max) - 1; // >= thr because the position is a corner
-        s_sc[sy][sx] = (uint8_t)score;
+        const int sy = i / FS_SW, sx = i - sy * FS_SW;
+        s_sc[sy][sx] = (uint8_t)corner_score(&s_px[sy + 3][sx + 4]);
     }
     __syncthreads();
 
-    // ---- 3x3 strict NMS + border filter ----
-    for(int i = tid; i < FT_W * FT_H; i += 256)
+    // ---- phase C: 3x3 strict NMS + border filter over the queue ----
+    for(int j0 = 0; j0 < nq; j0 += 256)
     {
-        const int oy = i / FT_W, ox = i - oy * FT_W;
-        const uint8_t* s = &s_sc[oy + 1][ox + 1];
-        const int v = s[0];
-        if(v == 0)
-            continue;
-        const int x = ox0 + ox, y = oy0 + oy;
-        if(x < edge || x >= L.w - edge || y >= L.h - edge)
-            continue;
-        if(v > s[-1] && v > s[1] && v > s[-SC_P - 1] && v > s[-SC_P] && v > s[-SC_P + 1] && v > s[SC_P - 1] &&
-           v > s[SC_P] && v > s[SC_P + 1])
-            s_out[atomicAdd(&s_on, 1)] = ((unsigned)y << 20) | ((unsigned)x << 8) | (unsigned)v;
+        const int j = j0 + tid;
+        bool keep = false;
+        unsigned rec = 0;
+        if(j < nq)
+        {
+            const int i = s_q[j];
+            const int sy = i / FS_SW, sx = i - sy * FS_SW;
+            const int x = sx0 + sx, y = sy0 + sy;
+            if(sx >= 2 && sx < FS_SW - 2 && sy >= 1 && sy < FS_SH - 1 && x >= edge && x < L.w - edge && y < L.h - edge)
+            {
+                const uint8_t* s = &s_sc[sy][sx];
+                const int v = s[0];
+                keep = v > s[-1] && v > s[1] && v > s[-FS_SW - 1] && v > s[-FS_SW] && v > s[-FS_SW + 1] && v > s[FS_SW - 1] &&
+                       v > s[FS_SW] && v > s[FS_SW + 1];
+                rec = ((unsigned)y << 20) | ((unsigned)x << 8) | (unsigned)v;
+            }
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        if(bal)
+        {
+            int wb = 0;
+            if(lane == 0)
+                wb = atomicAdd(&s_on, __popc(bal));
+            wb = __shfl_sync(0xffffffffu, wb, 0);
+            if(keep)
+                s_out[wb + __popc(bal & ((1u << lane) - 1u))] = rec;
+        }
     }
     __syncthreads();
     const int n_out = s_on;
@@ -721,9 +880,9 @@ void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const Pipe
 }
 
 void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const short2* xtab, const short2* ytab,
-                    long long* launches)
+                    int l_begin, int l_end, long long* launches)
 {
-    for(int l = 1; l < P.nlevels; ++l)
+    for(int l = l_begin < 1 ? 1 : l_begin; l < l_end; ++l)
     {
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
         dim3 blk(32, 8);
@@ -734,9 +893,10 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
     }
 }
 
-void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, long long* launches)
+void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, int l_begin, int l_end,
+                 long long* launches)
 {
-    for(int l = 0; l < P.nlevels; ++l)
+    for(int l = l_begin; l < l_end; ++l)
     {
         const LevelDesc& L = P.lv[l];
         dim3 grd((L.w + BT_W - 1) / BT_W, (L.h + BT_H - 1) / BT_H, P.n_frames);
@@ -747,23 +907,25 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
 
 void fast_tiles(int w, int h, int edge, int* tx, int* ty)
 {
-    const int ox0 = edge & ~3;
+    const int ox0 = ((edge - 1) & ~3) + 2; // first assigned interior column of tile 0
     const int wi = w - edge - ox0, hi = h - 2 * edge;
-    *tx = wi > 0 ? (wi + FT_W - 1) / FT_W : 0;
-    *ty = hi > 0 ? (hi + FT_H - 1) / FT_H : 0;
+    *tx = wi > 0 ? (wi + FS_IW - 1) / FS_IW : 0;
+    *ty = hi > 0 ? (hi + FS_IH - 1) / FS_IH : 0;
+    if(*tx == 0 || *ty == 0)
+        *tx = *ty = 0;
 }
 
+// levels [l_begin, l_end) in one launch
 void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCounters* ctr, unsigned* hist,
-                 const PipeParams& P, long long* launches)
+                 const PipeParams& P, int l_begin, int l_end, long long* launches)
 {
-    for(int l = 0; l < P.nlevels; ++l)
-    {
-        const LevelDesc& L = P.lv[l];
-        if(L.tiles_x <= 0 || L.tiles_y <= 0)
-            continue;
-        k_fast<<<dim3(L.tiles_x, L.tiles_y, P.n_frames), 256, 0, st>>>(P, l, pyr, cand, ctr, hist);
-        ++*launches;
-    }
+    int tiles = 0;
+    for(int l = l_begin; l < l_end; ++l)
+        tiles += P.lv[l].tiles_x * P.lv[l].tiles_y;
+    if(tiles <= 0)
+        return;
+    k_fast<<<dim3(tiles, P.n_frames), 256, 0, st>>>(P, l_begin, l_end, pyr, cand, ctr, hist);
+    ++*launches;
 }
 
 void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned* cand2, unsigned* keys, unsigned* keys2,
