@@ -96,6 +96,8 @@ MSLAM_B200_API int mslam_b200_create(const mslam_b200_config* cfg, mslam_b200_ct
 MSLAM_B200_API void mslam_b200_destroy(mslam_b200_ctx* ctx);
 MSLAM_B200_API int mslam_b200_set_stream(mslam_b200_ctx* ctx, void* cuda_stream);
 MSLAM_B200_API int mslam_b200_synchronize(mslam_b200_ctx* ctx);
+/* change mslam_b200_config::flags of a live context (synchronises first) */
+MSLAM_B200_API int mslam_b200_set_flags(mslam_b200_ctx* ctx, int flags);
 /* text of the last CUDA error seen by this context ("" if none) */
 MSLAM_B200_API const char* mslam_b200_last_cuda_error(mslam_b200_ctx* ctx);
 /* number of kernels this library has launched on the context since creation (bench.py "gpu_launches") */

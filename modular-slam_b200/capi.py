@@ -145,6 +145,9 @@ class Context:
     def set_stream(self, stream_handle):
         self._chk(library().mslam_b200_set_stream(self._h, C.c_void_p(stream_handle or 0)), "set_stream")
 
+    def set_flags(self, flags):
+        self._chk(library().mslam_b200_set_flags(self._h, int(flags)), "set_flags")
+
     def synchronize(self):
         self._chk(library().mslam_b200_synchronize(self._h), "synchronize")
 

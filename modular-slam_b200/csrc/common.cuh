@@ -32,7 +32,8 @@ struct LevelDesc
 struct PipeParams
 {
     int nlevels, n_frames, W, H;
-    int edge, fast_thr, kp_cap, pad0;
+    int edge, fast_thr, kp_cap;
+    int frame0; // first frame (absolute index in the context's batch buffers) this launch covers; n_frames from there
     long long cand_frame_stride; // elements per frame in the candidate arrays
     int total_fast_tiles, pad1;
     LevelDesc lv[kMaxLevels];

@@ -14,6 +14,8 @@
 
 using namespace mslam_b200;
 
+constexpr int kMaxChunks = 4; // host detect_batch: chunks in flight through copy-in / kernels / copy-out
+
 struct mslam_b200_ctx
 {
     mslam_b200_config cfg;
@@ -57,6 +59,9 @@ struct mslam_b200_ctx
     unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
     int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
     int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
+    // ---- copy engines of the host entry points (chunked H2D / compute / D2H pipeline) ----
+    cudaStream_t copy[2] = {nullptr, nullptr};
+    cudaEvent_t ev_h2d[kMaxChunks] = {nullptr}, ev_done[kMaxChunks + 1] = {nullptr};
     // ---- forked streams of the detect pipeline ----
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t ev_level[kMaxLevels] = {nullptr};
@@ -342,6 +347,18 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     for(int i = 0; i < kMaxLevels; ++i)
         if(ctx->ev_level[i])
             cudaEventDestroy(ctx->ev_level[i]);
+    for(int i = 0; i < 2; ++i)
+        if(ctx->copy[i])
+        {
+            cudaStreamSynchronize(ctx->copy[i]);
+            cudaStreamDestroy(ctx->copy[i]);
+        }
+    for(int i = 0; i < kMaxChunks; ++i)
+        if(ctx->ev_h2d[i])
+            cudaEventDestroy(ctx->ev_h2d[i]);
+    for(int i = 0; i <= kMaxChunks; ++i)
+        if(ctx->ev_done[i])
+            cudaEventDestroy(ctx->ev_done[i]);
     if(ctx->own_stream && ctx->stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -401,6 +418,12 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     }
     for(int i = 0; i < kMaxLevels; ++i)
         CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_level[i], cudaEventDisableTiming));
+    for(int i = 0; i < 2; ++i)
+        CREATE_OK(cudaStreamCreateWithFlags(&ctx->copy[i], cudaStreamNonBlocking));
+    for(int i = 0; i < kMaxChunks; ++i)
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming));
+    for(int i = 0; i <= kMaxChunks; ++i)
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
     Geometry g;
     build_geometry(c, ctx->kp_cap, c.max_width, c.max_height, &g);
     const size_t B = (size_t)c.max_batch;
@@ -491,6 +514,15 @@ int mslam_b200_synchronize(mslam_b200_ctx* ctx)
     return MSLAM_B200_OK;
 }
 
+int mslam_b200_set_flags(mslam_b200_ctx* ctx, int flags)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    ctx->cfg.flags = flags;
+    return MSLAM_B200_OK;
+}
+
 int mslam_b200_level_geometry(mslam_b200_ctx* ctx, int width, int height, int* w, int* h, float* scale, int* n_per_level)
 {
     if(!ctx || width < 1 || height < 1)
@@ -524,17 +556,13 @@ static int run_pyramid(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames)
     return MSLAM_B200_OK;
 }
 
-int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames, int width, int height,
-                                mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity, int* d_counts)
+// enqueue the detect pipeline for frames [frame0, frame0 + n_frames) of the batch buffers (geometry already set, the
+// zero block already cleared); outputs are indexed by absolute frame
+static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, int n_frames, mslam_b200_keypoint* d_kp,
+                        uint8_t* d_desc, int capacity, int* d_counts)
 {
-    if(!ctx || !d_bgr || !d_kp || !d_desc || !d_counts || n_frames < 1 || n_frames > ctx->cfg.max_batch || capacity < 1)
-        return MSLAM_B200_E_INVALID;
-    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
-    int rc = set_geometry(ctx, width, height);
-    if(rc)
-        return rc;
     cudaStream_t st = ctx->stream;
-    MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
+    ctx->P.frame0 = frame0;
     const int n_slots = std::min(capacity, ctx->kp_cap * ctx->P.nlevels);
     if(ctx->cfg.flags & MSLAM_B200_FLAG_SERIAL)
     {
@@ -612,9 +640,22 @@ int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n
         launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, d_kp, d_desc, d_counts, capacity,
                                n_slots, P, &ctx->launches);
     }
-    ctx->last_frames = n_frames;
     MSLAM_CUDA_OK(cudaGetLastError());
     return MSLAM_B200_OK;
+}
+
+int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames, int width, int height,
+                                mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity, int* d_counts)
+{
+    if(!ctx || !d_bgr || !d_kp || !d_desc || !d_counts || n_frames < 1 || n_frames > ctx->cfg.max_batch || capacity < 1)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    int rc = set_geometry(ctx, width, height);
+    if(rc)
+        return rc;
+    MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, ctx->stream));
+    ctx->last_frames = n_frames;
+    return detect_range(ctx, d_bgr, 0, n_frames, d_kp, d_desc, capacity, d_counts);
 }
 
 int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
@@ -628,28 +669,59 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
     cudaStream_t st = ctx->stream;
     const size_t row = (size_t)width * 3, frame_bytes = row * height;
     for(int i = 0; i < n_frames; ++i)
-    {
         if(!frames[i])
             return MSLAM_B200_E_INVALID;
-        if((size_t)stride_bytes == row)
-            MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_bgr + i * frame_bytes, frames[i], frame_bytes, cudaMemcpyHostToDevice, st));
-        else
-            MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * frame_bytes, row, frames[i], (size_t)stride_bytes, row,
-                                            (size_t)height, cudaMemcpyHostToDevice, st));
-    }
-    const int icap = ctx->kp_cap;
-    int rc = mslam_b200_detect_batch_dev(ctx, ctx->d_bgr, n_frames, width, height, ctx->d_kp, ctx->d_desc, icap,
-                                         ctx->d_counts);
+    int rc = set_geometry(ctx, width, height);
     if(rc)
         return rc;
-    const int ncopy = std::min(capacity, icap);
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_counts, ctx->d_counts, n_frames * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_err, ctx->d_err, n_frames * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpy2DAsync(out_kp, (size_t)capacity * sizeof(mslam_b200_keypoint), ctx->d_kp,
-                                    (size_t)icap * sizeof(mslam_b200_keypoint), (size_t)ncopy * sizeof(mslam_b200_keypoint),
-                                    (size_t)n_frames, cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpy2DAsync(out_desc, (size_t)capacity * 32, ctx->d_desc, (size_t)icap * 32, (size_t)ncopy * 32,
-                                    (size_t)n_frames, cudaMemcpyDeviceToHost, st));
+    // The batch is cut into chunks that flow through three engines at once: chunk c+1 is copied in (copy stream) while
+    // chunk c runs through the kernels (context stream + its forks) and chunk c-1's results are copied out (second
+    // copy stream).  Per-frame scratch in HBM is indexed by absolute frame, so chunks never touch each other's data.
+    const int icap = ctx->kp_cap, ncopy = std::min(capacity, icap);
+    const int nchunks = n_frames >= 2 * kMaxChunks ? kMaxChunks : 1;
+    const int per = (n_frames + nchunks - 1) / nchunks;
+    cudaStream_t s_in = ctx->copy[0], s_out = ctx->copy[1];
+    MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
+    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_done[kMaxChunks], st)); // "previous work on the context stream is ordered"
+    MSLAM_CUDA_OK(cudaStreamWaitEvent(s_in, ctx->ev_done[kMaxChunks], 0));
+    for(int c = 0; c < nchunks; ++c)
+    {
+        const int b0 = c * per, b1 = std::min(n_frames, b0 + per);
+        bool contiguous = (size_t)stride_bytes == row;
+        for(int i = b0 + 1; i < b1 && contiguous; ++i)
+            contiguous = frames[i] == frames[i - 1] + frame_bytes;
+        if(contiguous && b1 > b0)
+            MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_bgr + b0 * frame_bytes, frames[b0], (size_t)(b1 - b0) * frame_bytes,
+                                          cudaMemcpyHostToDevice, s_in));
+        else
+            for(int i = b0; i < b1; ++i)
+                MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * frame_bytes, row, frames[i], (size_t)stride_bytes, row,
+                                                (size_t)height, cudaMemcpyHostToDevice, s_in));
+        MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_h2d[c], s_in));
+    }
+    for(int c = 0; c < nchunks; ++c)
+    {
+        const int b0 = c * per, b1 = std::min(n_frames, b0 + per);
+        if(b1 <= b0)
+            continue;
+        MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_h2d[c], 0));
+        rc = detect_range(ctx, ctx->d_bgr, b0, b1 - b0, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
+        if(rc)
+            return rc;
+        MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_done[c], st));
+        MSLAM_CUDA_OK(cudaStreamWaitEvent(s_out, ctx->ev_done[c], 0));
+        MSLAM_CUDA_OK(cudaMemcpy2DAsync(out_kp + (size_t)b0 * capacity, (size_t)capacity * sizeof(mslam_b200_keypoint),
+                                        ctx->d_kp + (size_t)b0 * icap, (size_t)icap * sizeof(mslam_b200_keypoint),
+                                        (size_t)ncopy * sizeof(mslam_b200_keypoint), (size_t)(b1 - b0), cudaMemcpyDeviceToHost,
+                                        s_out));
+        MSLAM_CUDA_OK(cudaMemcpy2DAsync(out_desc + (size_t)b0 * capacity * 32, (size_t)capacity * 32,
+                                        ctx->d_desc + (size_t)b0 * icap * 32, (size_t)icap * 32, (size_t)ncopy * 32,
+                                        (size_t)(b1 - b0), cudaMemcpyDeviceToHost, s_out));
+    }
+    ctx->last_frames = n_frames;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_counts, ctx->d_counts, n_frames * sizeof(int), cudaMemcpyDeviceToHost, s_out));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_err, ctx->d_err, n_frames * sizeof(int), cudaMemcpyDeviceToHost, s_out));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(s_out));
     MSLAM_CUDA_OK(cudaStreamSynchronize(st));
     rc = MSLAM_B200_OK;
     for(int i = 0; i < n_frames; ++i)
@@ -719,6 +791,7 @@ int mslam_b200_describe(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int 
     MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
     MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_ctr, ctr.data(), nl * sizeof(LevelCounters), cudaMemcpyHostToDevice, st));
     MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_sel, sel.data(), sel.size() * sizeof(SelRec), cudaMemcpyHostToDevice, st));
+    ctx->P.frame0 = 0;
     run_pyramid(ctx, ctx->d_bgr, 1);
     launch_blur(st, ctx->d_pyr, ctx->d_blur, ctx->P, 0, ctx->P.nlevels, &ctx->launches);
     launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,

@@ -331,7 +331,7 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ PipeParams
     const LevelDesc& L = P.lv[l];
     tile -= L.tile_base;
     const int ty = tile / L.tiles_x, tx = tile - ty * L.tiles_x;
-    const int b = blockIdx.y;
+    const int b = blockIdx.y + P.frame0;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int edge = P.edge, thr = P.fast_thr;
     const int sx0 = ((edge - 1) & ~3) + FS_IW * tx; // first scored column (multiple of 4)
@@ -568,7 +568,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
 {
     __shared__ unsigned s_hist[256];
     __shared__ unsigned s_cnt, s_thr, s_k;
-    const int l = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const int l = blockIdx.x, b = blockIdx.y + P.frame0, tid = threadIdx.x;
     const LevelDesc& L = P.lv[l];
     LevelCounters* C = ctr + (long long)b * P.nlevels + l;
     unsigned* c1 = cand + (long long)b * P.cand_frame_stride + L.cand_off;
@@ -758,7 +758,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
 {
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
-    const int b = blockIdx.y;
+    const int b = blockIdx.y + P.frame0;
     int base = 0, l = -1, r = 0;
     for(int i = 0; i < P.nlevels; ++i)
     {
@@ -870,11 +870,13 @@ void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const Pipe
     if((P.W & 15) == 0 && (reinterpret_cast<uintptr_t>(d_bgr) & 15) == 0)
     {
         const int n = (P.W >> 4) * P.H;
-        k_gray16<<<dim3((n + 255) / 256, P.n_frames), 256, 0, st>>>(d_bgr, in_fs, pyr + L0.img_off, L0.img_frame_stride,
+        k_gray16<<<dim3((n + 255) / 256, P.n_frames), 256, 0, st>>>(d_bgr + P.frame0 * in_fs, in_fs,
+                                                                    pyr + L0.img_off + P.frame0 * L0.img_frame_stride, L0.img_frame_stride,
                                                                     L0.pitch, P.W, P.H);
     }
     else
-        k_gray1<<<dim3((P.W + 255) / 256, P.H, P.n_frames), 256, 0, st>>>(d_bgr, in_fs, pyr + L0.img_off,
+        k_gray1<<<dim3((P.W + 255) / 256, P.H, P.n_frames), 256, 0, st>>>(d_bgr + P.frame0 * in_fs, in_fs,
+                                                                          pyr + L0.img_off + P.frame0 * L0.img_frame_stride,
                                                                           L0.img_frame_stride, L0.pitch, P.W, P.H);
     ++*launches;
 }
@@ -887,8 +889,9 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
         dim3 blk(32, 8);
         dim3 grd((D.w + 127) / 128, (D.h + 7) / 8, P.n_frames);
-        k_resize<<<grd, blk, 0, st>>>(pyr + S.img_off, S.pitch, S.img_frame_stride, S.w, S.h, pyr + D.img_off, D.pitch,
-                                      D.img_frame_stride, D.w, D.h, xtab + D.xtab_off, ytab + D.ytab_off);
+        k_resize<<<grd, blk, 0, st>>>(pyr + S.img_off + P.frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride, S.w, S.h,
+                                      pyr + D.img_off + P.frame0 * D.img_frame_stride, D.pitch, D.img_frame_stride, D.w, D.h,
+                                      xtab + D.xtab_off, ytab + D.ytab_off);
         ++*launches;
     }
 }
@@ -900,7 +903,8 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
     {
         const LevelDesc& L = P.lv[l];
         dim3 grd((L.w + BT_W - 1) / BT_W, (L.h + BT_H - 1) / BT_H, P.n_frames);
-        k_blur<<<grd, 256, 0, st>>>(pyr + L.img_off, blur + L.img_off, L.pitch, L.img_frame_stride, L.w, L.h);
+        const long long off = L.img_off + P.frame0 * L.img_frame_stride;
+        k_blur<<<grd, 256, 0, st>>>(pyr + off, blur + off, L.pitch, L.img_frame_stride, L.w, L.h);
         ++*launches;
     }
 }
