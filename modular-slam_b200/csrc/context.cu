@@ -48,7 +48,7 @@ struct mslam_b200_ctx
     mslam_b200_keypoint* d_kp = nullptr;
     uint8_t* d_desc = nullptr;
     int* d_counts = nullptr;
-    unsigned* d_pat = nullptr; // rBRIEF pattern, transposed (256 words)
+    float4* d_pat = nullptr; // rBRIEF pattern as floats, transposed (256 x float4)
     // ---- pinned host staging ----
     int* h_counts = nullptr;
     int* h_err = nullptr;
@@ -193,7 +193,7 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
         LevelDesc& L = P.lv[l];
         L.w = std::max(w[l], 1);
         L.h = std::max(h[l], 1);
-        L.pitch = (int)align_up((size_t)L.w, 64);
+        L.pitch = (int)align_up((size_t)L.w + 8, 64); // room for the 4 reflect-101 padding columns + aligned over-reads
         L.n_keep = nl[l];
         L.scale = sc[l];
         L.inv_scale = 1.f / sc[l];
@@ -454,7 +454,7 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaMalloc(&ctx->d_desc, B * (size_t)ctx->kp_cap * 32));
     CREATE_OK(cudaMalloc(&ctx->d_counts, B * sizeof(int)));
     {
-        unsigned pat[256];
+        float pat[1024];
         brief_pattern_transposed(pat);
         CREATE_OK(cudaMalloc(&ctx->d_pat, sizeof(pat)));
         CREATE_OK(cudaMemcpy(ctx->d_pat, pat, sizeof(pat), cudaMemcpyHostToDevice));

@@ -17,10 +17,10 @@ void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned
                    LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P,
                    long long* launches);
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
-                            const SelRec* sel, const unsigned* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc,
+                            const SelRec* sel, const float4* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc,
                             int* out_counts,
                             int out_cap, int n_slots, const PipeParams& P, long long* launches);
-void brief_pattern_transposed(unsigned* out256);
+void brief_pattern_transposed(float* out1024);
 // matching path
 void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
                  unsigned* key0, unsigned* key1, int sm_count, long long* launches);

@@ -16,6 +16,15 @@ namespace mslam_b200
 //   g = (u8) min(255.f, .299f*c0 + .587f*c1 + .114f*c2)  three rounded products, two rounded adds,
 //   truncating cast; weights in MEMORY order.  HBM-bound: 3 B read + 1 B written per pixel.
 // =================================================================================================
+__device__ __forceinline__ int reflect101(int p, int n)
+{
+    if(n == 1)
+        return 0;
+    while(p < 0 || p >= n)
+        p = p < 0 ? -p : 2 * n - 2 - p;
+    return p;
+}
+
 __device__ __forceinline__ unsigned gray_px(unsigned c0, unsigned c1, unsigned c2)
 {
     float v = __fadd_rn(__fadd_rn(__fmul_rn(0.299f, (float)c0), __fmul_rn(0.587f, (float)c1)),
@@ -52,8 +61,10 @@ __global__ void __launch_bounds__(256) k_gray16(const uint8_t* __restrict__ bgr,
         }
         o[q] = r;
     }
-    *reinterpret_cast<uint4*>(out + (long long)blockIdx.y * out_fs + (long long)y * pitch + c * 16) =
-        make_uint4(o[0], o[1], o[2], o[3]);
+    uint8_t* dst = out + (long long)blockIdx.y * out_fs + (long long)y * pitch + c * 16;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+    if(c == cpr - 1) // reflect-101 padding columns W .. W+3 = pixels W-2, W-3, W-4, W-5 (read by the blur's row pass)
+        *reinterpret_cast<unsigned*>(dst + 16) = __byte_perm(o[3], o[2], 0x7012);
 }
 
 // generic width: one pixel per thread
@@ -65,7 +76,12 @@ __global__ void __launch_bounds__(256) k_gray1(const uint8_t* __restrict__ bgr, 
     if(x >= W)
         return;
     const uint8_t* p = bgr + (long long)blockIdx.z * in_fs + ((long long)y * W + x) * 3;
-    out[(long long)blockIdx.z * out_fs + (long long)y * pitch + x] = (uint8_t)gray_px(p[0], p[1], p[2]);
+    const uint8_t g = (uint8_t)gray_px(p[0], p[1], p[2]);
+    uint8_t* row = out + (long long)blockIdx.z * out_fs + (long long)y * pitch;
+    row[x] = g;
+    for(int px = W; px < W + 4; ++px) // reflect-101 padding columns (read by the blur's row pass)
+        if(reflect101(px, W) == x)
+            row[px] = g;
 }
 
 // =================================================================================================
@@ -79,7 +95,7 @@ __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src,
 {
     const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    if(x4 >= dw || y >= dh)
+    if(x4 >= dw + 4 || y >= dh) // columns dw .. dw+3 are the reflect-101 padding the blur's row pass reads
         return;
     const short2 ty = __ldg(ytab + y);
     const int y0 = ty.x, y1 = min(y0 + 1, sh - 1);
@@ -91,9 +107,9 @@ __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src,
     for(int i = 0; i < 4; ++i)
     {
         const int x = x4 + i;
-        if(x < dw)
+        if(x < dw + 4)
         {
-            const short2 tx = __ldg(xtab + x);
+            const short2 tx = __ldg(xtab + (x < dw ? x : reflect101(x, dw)));
             const int i0 = tx.x, i1 = min(i0 + 1, sw - 1);
             const unsigned a1 = (unsigned)tx.y, a0 = 256u - a1;
             const unsigned h0 = a0 * __ldg(r0 + i0) + a1 * __ldg(r0 + i1);
@@ -109,17 +125,7 @@ __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src,
 //   row pass  acc = k0*p[x-3]; acc = fma(k_j, p[x-3+j], acc)  j = 1..6
 //   col pass  acc = k3*r[y];   acc = fma(k_{3+i}, r[y+i] + r[y-i], acc)  i = 1..3 ; out = sat_u8(rint(acc))
 // =================================================================================================
-constexpr int BT_W = 128, BT_H = 32;            // output tile
-constexpr int BT_PW = BT_W + 8, BT_PH = BT_H + 6; // staged pixels (4-byte aligned 3-px halo)
-
-__device__ __forceinline__ int reflect101(int p, int n)
-{
-    if(n == 1)
-        return 0;
-    while(p < 0 || p >= n)
-        p = p < 0 ? -p : 2 * n - 2 - p;
-    return p;
-}
+constexpr int BT_W = 128, BT_H = 32; // one warp: 128 columns (4 per lane) x 32 rows
 
 // exact u8 -> f32 without the XU pipe's I2F: 0x4B000000 | b is the float 8388608 + b
 __device__ __forceinline__ float byte_to_float(unsigned word, int i)
@@ -127,81 +133,106 @@ __device__ __forceinline__ float byte_to_float(unsigned word, int i)
     return __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 + i)), 8388608.f);
 }
 
-// A thread produces 4 horizontally adjacent pixels in both passes; the row pass keeps its f32 results in shared
-// memory (float4), the column pass rounds with the 1.5 * 2^23 magic add (round-to-nearest-even, like cvRound) and
-// packs 4 bytes per store.
-__global__ void __launch_bounds__(256) k_blur(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int pitch,
+// the three aligned words covering source pixels x-4 .. x+7 of one row.  The producers pad every pyramid row with its
+// reflect-101 columns w .. w+3, so only the left border needs care: for x = 0 pixels -3, -2, -1 are pixels 3, 2, 1.
+struct Row12
+{
+    unsigned a, b, c;
+};
+__device__ __forceinline__ Row12 blur_load(const uint8_t* __restrict__ row, int x)
+{
+    Row12 r;
+    const unsigned* wp = reinterpret_cast<const unsigned*>(row + x);
+    r.b = __ldg(wp), r.c = __ldg(wp + 1);
+    r.a = x > 0 ? __ldg(wp - 1) : __byte_perm(r.b, 0u, 0x1230);
+    return r;
+}
+
+// row pass for the 4 pixels x .. x+3:  acc = k0 * p[x-3]; acc = fma(k_j, p[x-3+j], acc)
+__device__ __forceinline__ void blur_row4(const Row12& wd, float (&o)[4])
+{
+    const float kk[7] = {__int_as_float(0x3d8fafb1), __int_as_float(0x3e06387e), __int_as_float(0x3e434a39),
+                         __int_as_float(0x3e5d4ae0), __int_as_float(0x3e434a39), __int_as_float(0x3e06387e),
+                         __int_as_float(0x3d8fafb1)};
+    const float p[10] = {byte_to_float(wd.a, 1), byte_to_float(wd.a, 2), byte_to_float(wd.a, 3), byte_to_float(wd.b, 0),
+                         byte_to_float(wd.b, 1), byte_to_float(wd.b, 2), byte_to_float(wd.b, 3), byte_to_float(wd.c, 0),
+                         byte_to_float(wd.c, 1), byte_to_float(wd.c, 2)};
+#pragma unroll
+    for(int q = 0; q < 4; ++q)
+    {
+        float acc = __fmul_rn(kk[0], p[q]);
+#pragma unroll
+        for(int j = 1; j < 7; ++j)
+            acc = __fmaf_rn(kk[j], p[q + j], acc);
+        o[q] = acc;
+    }
+}
+
+// A lane owns a 4-pixel-wide column strip and walks down 32 rows: the row pass of each new source row goes into a
+// 7-deep register ring, the column pass reads the ring -- no shared memory, no barriers, every source byte is read
+// once per 32-row band (+6 halo rows).  Source rows are fetched 7 rows ahead of their use (software pipeline), so the
+// walk is not bound by memory latency.  Rounding is the 1.5 * 2^23 magic add (round-to-nearest-even, like cvRound).
+__global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int pitch,
                                               long long fs, int w, int h)
 {
-    __shared__ __align__(16) uint8_t s_in[BT_PH][BT_PW];
-    __shared__ __align__(16) float s_mid[BT_PH][BT_W];
-    const float k0 = __int_as_float(0x3d8fafb1), k1 = __int_as_float(0x3e06387e), k2 = __int_as_float(0x3e434a39),
-                k3 = __int_as_float(0x3e5d4ae0);
-    const float kk[7] = {k0, k1, k2, k3, k2, k1, k0};
-    const int tx0 = blockIdx.x * BT_W, ty0 = blockIdx.y * BT_H;
+    const float k1 = __int_as_float(0x3e434a39), k2 = __int_as_float(0x3e06387e), k3 = __int_as_float(0x3d8fafb1),
+                kc = __int_as_float(0x3e5d4ae0); // kernel[3 + 1], [3 + 2], [3 + 3], [3]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x = (blockIdx.x * 32 + lane) * 4;
+    const int y0 = (blockIdx.y * 4 + warp) * BT_H;
+    if(x >= w || y0 >= h)
+        return;
     const uint8_t* img = src + (long long)blockIdx.z * fs;
-    for(int i = threadIdx.x; i < BT_PH * (BT_PW / 4); i += 256)
+    uint8_t* out = dst + (long long)blockIdx.z * fs;
+    const int rows = min(BT_H, h - y0);
+    float r[7][4];
+    Row12 cur[7], nxt[7];
     {
-        const int r = i / (BT_PW / 4), c = i - r * (BT_PW / 4);
-        const int gy = reflect101(ty0 - 3 + r, h), gx = tx0 - 4 + 4 * c;
-        const uint8_t* row = img + (long long)gy * pitch;
-        unsigned v;
-        if(gx >= 0 && gx + 3 < w)
-            v = __ldg(reinterpret_cast<const unsigned*>(row + gx));
-        else
-            v = (unsigned)__ldg(row + reflect101(gx, w)) | ((unsigned)__ldg(row + reflect101(gx + 1, w)) << 8) |
-                ((unsigned)__ldg(row + reflect101(gx + 2, w)) << 16) | ((unsigned)__ldg(row + reflect101(gx + 3, w)) << 24);
-        reinterpret_cast<unsigned*>(&s_in[r][0])[c] = v;
+        Row12 pre[6];
+#pragma unroll
+        for(int s = 0; s < 6; ++s)
+            pre[s] = blur_load(img + (long long)reflect101(y0 - 3 + s, h) * pitch, x);
+#pragma unroll
+        for(int k = 0; k < 7; ++k)
+            cur[k] = blur_load(img + (long long)reflect101(y0 + 3 + k, h) * pitch, x);
+#pragma unroll
+        for(int s = 0; s < 6; ++s)
+            blur_row4(pre[s], r[s]);
     }
-    __syncthreads();
-    // row pass: acc = k0 * p[x-3]; acc = fma(k_j, p[x-3+j], acc)
-    for(int i = threadIdx.x; i < BT_PH * (BT_W / 4); i += 256)
+    for(int i0 = 0; i0 < rows; i0 += 7)
     {
-        const int r = i / (BT_W / 4), g = i - r * (BT_W / 4);
-        const unsigned* wrow = reinterpret_cast<const unsigned*>(&s_in[r][0]) + g;
-        const unsigned wa = wrow[0], wb = wrow[1], wc = wrow[2]; // staged x = 4g .. 4g + 11  <->  output x - 4 .. x + 7
-        const float p[10] = {byte_to_float(wa, 1), byte_to_float(wa, 2), byte_to_float(wa, 3), byte_to_float(wb, 0),
-                             byte_to_float(wb, 1), byte_to_float(wb, 2), byte_to_float(wb, 3), byte_to_float(wc, 0),
-                             byte_to_float(wc, 1), byte_to_float(wc, 2)};
-        float o[4];
-#pragma unroll
-        for(int q = 0; q < 4; ++q)
+        if(i0 + 7 < rows)
         {
-            float acc = __fmul_rn(kk[0], p[q]);
 #pragma unroll
-            for(int j = 1; j < 7; ++j)
-                acc = __fmaf_rn(kk[j], p[q + j], acc);
-            o[q] = acc;
+            for(int k = 0; k < 7; ++k)
+                nxt[k] = blur_load(img + (long long)reflect101(y0 + 3 + i0 + 7 + k, h) * pitch, x);
         }
-        *reinterpret_cast<float4*>(&s_mid[r][4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
-    }
-    __syncthreads();
-    // column pass: acc = k3 * r[y]; acc = fma(k_{3+i}, r[y+i] + r[y-i], acc); out = sat_u8(rint(acc))
-    for(int i = threadIdx.x; i < BT_H * (BT_W / 4); i += 256)
-    {
-        const int y = i / (BT_W / 4), g = i - y * (BT_W / 4);
-        const int gx = tx0 + 4 * g, gy = ty0 + y;
-        if(gx >= w || gy >= h)
-            continue;
-        float4 m[7];
 #pragma unroll
-        for(int j = 0; j < 7; ++j)
-            m[j] = *reinterpret_cast<const float4*>(&s_mid[y + j][4 * g]);
-        const float* mf = reinterpret_cast<const float*>(m);
-        unsigned bits[4];
-#pragma unroll
-        for(int q = 0; q < 4; ++q)
+        for(int k = 0; k < 7; ++k)
         {
-            float acc = __fmul_rn(k3, mf[3 * 4 + q]);
+            const int i = i0 + k;
+            if(i < rows)
+            {
+                // ring slot (k + j) % 7 holds source row y - 3 + j of output row y = y0 + i
+                blur_row4(cur[k], r[(k + 6) % 7]);
+                unsigned bits[4];
 #pragma unroll
-            for(int j = 1; j <= 3; ++j)
-                acc = __fmaf_rn(kk[3 + j], __fadd_rn(mf[(3 + j) * 4 + q], mf[(3 - j) * 4 + q]), acc);
-            // 0 <= acc < 256 (weights sum to 1 within rounding), so the low byte of acc + 1.5 * 2^23 is rint(acc)
-            bits[q] = __float_as_uint(__fadd_rn(acc, 12582912.f));
+                for(int q = 0; q < 4; ++q)
+                {
+                    float acc = __fmul_rn(kc, r[(k + 3) % 7][q]);
+                    acc = __fmaf_rn(k1, __fadd_rn(r[(k + 4) % 7][q], r[(k + 2) % 7][q]), acc);
+                    acc = __fmaf_rn(k2, __fadd_rn(r[(k + 5) % 7][q], r[(k + 1) % 7][q]), acc);
+                    acc = __fmaf_rn(k3, __fadd_rn(r[(k + 6) % 7][q], r[k % 7][q]), acc);
+                    // 0 <= acc < 256 (weights sum to 1 within rounding): the low byte of acc + 1.5 * 2^23 is rint(acc)
+                    bits[q] = __float_as_uint(__fadd_rn(acc, 12582912.f));
+                }
+                const unsigned lo = __byte_perm(bits[0], bits[1], 0x0040), hi = __byte_perm(bits[2], bits[3], 0x0040);
+                *reinterpret_cast<unsigned*>(out + (long long)(y0 + i) * pitch + x) = __byte_perm(lo, hi, 0x5410);
+            }
         }
-        const unsigned lo = __byte_perm(bits[0], bits[1], 0x0040), hi = __byte_perm(bits[2], bits[3], 0x0040);
-        *reinterpret_cast<unsigned*>(dst + (long long)blockIdx.z * fs + (long long)gy * pitch + gx) =
-            __byte_perm(lo, hi, 0x5410);
+#pragma unroll
+        for(int k = 0; k < 7; ++k)
+            cur[k] = nxt[k];
     }
 }
 
@@ -312,7 +343,7 @@ __device__ __forceinline__ int corner_score(const uint8_t* c /* centre in the st
     return max(bright, dark) - 1;
 }
 
-__global__ void __launch_bounds__(256) k_fast(const __grid_constant__ PipeParams P, int l_begin, int l_end,
+__global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, int l_begin, int l_end,
                                               const uint8_t* __restrict__ pyr, unsigned* __restrict__ cand,
                                               LevelCounters* __restrict__ ctr, unsigned* __restrict__ hist)
 {
@@ -752,7 +783,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                          const uint8_t* __restrict__ blur,
                                                          const LevelCounters* __restrict__ ctr, const SelRec* __restrict__ sel,
-                                                         const unsigned* __restrict__ pat_t,
+                                                         const float4* __restrict__ pat_t,
                                                          mslam_b200_keypoint* __restrict__ out_kp, uint8_t* __restrict__ out_desc,
                                                          int* __restrict__ out_counts, int out_cap)
 {
@@ -810,25 +841,29 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     if(lane == 0)
     {
         const float ang = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
-        ca = (float)cos((double)ang);
-        sa = (float)sin((double)ang);
+        double sd, cd;
+        sincos((double)ang, &sd, &cd); // (float)cos((double)ang), (float)sin((double)ang) of OpenCV, one range reduction
+        ca = (float)cd;
+        sa = (float)sd;
     }
     ca = __shfl_sync(0xffffffffu, ca, 0);
     sa = __shfl_sync(0xffffffffu, sa, 0);
+    // cvRound(v) = low bits of (v + 1.5 * 2^23) - 0x4B400000 (round-to-nearest-even, |v| < 2^22); the two subtractions
+    // are folded into the base pointer:  iy * pitch + ix = by * pitch + bx - 0x4B400000 * (pitch + 1)  (mod 2^32)
+    const unsigned kfold = 0x4B400000u * (unsigned)(pitch + 1);
     const uint8_t* centre = blur + plane + (long long)cy * pitch + cx;
     unsigned byte = 0;
 #pragma unroll
     for(int j = 0; j < 8; ++j)
     {
-        const unsigned t = __ldg(pat_t + j * 32 + lane); // test (lane * 8 + j): x0 | y0 << 8 | x1 << 16 | y1 << 24 (int8 each)
-        const float px0 = (float)(int)(signed char)(t & 255u), py0 = (float)(int)(signed char)((t >> 8) & 255u),
-                    px1 = (float)(int)(signed char)((t >> 16) & 255u), py1 = (float)(int)(signed char)(t >> 24);
-        const int x0 = __float2int_rn(__fsub_rn(__fmul_rn(px0, ca), __fmul_rn(py0, sa)));
-        const int y0 = __float2int_rn(__fadd_rn(__fmul_rn(px0, sa), __fmul_rn(py0, ca)));
-        const int x1 = __float2int_rn(__fsub_rn(__fmul_rn(px1, ca), __fmul_rn(py1, sa)));
-        const int y1 = __float2int_rn(__fadd_rn(__fmul_rn(px1, sa), __fmul_rn(py1, ca)));
-        const int v0 = __ldg(centre + y0 * pitch + x0);
-        const int v1 = __ldg(centre + y1 * pitch + x1);
+        const float4 t = __ldg(pat_t + j * 32 + lane); // test (lane * 8 + j): x0, y0, x1, y1
+        const unsigned bx0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.x, ca), __fmul_rn(t.y, sa)), 12582912.f));
+        const unsigned by0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.x, sa), __fmul_rn(t.y, ca)), 12582912.f));
+        const unsigned bx1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.z, ca), __fmul_rn(t.w, sa)), 12582912.f));
+        const unsigned by1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.z, sa), __fmul_rn(t.w, ca)), 12582912.f));
+        const int o0 = (int)(by0 * (unsigned)pitch + bx0 - kfold), o1 = (int)(by1 * (unsigned)pitch + bx1 - kfold);
+        const int v0 = __ldg(centre + o0);
+        const int v1 = __ldg(centre + o1);
         byte |= (unsigned)(v0 < v1) << j;
     }
     out_desc[((long long)b * out_cap + slot) * 32 + lane] = (uint8_t)byte;
@@ -845,19 +880,16 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     }
 }
 
-// rBRIEF pattern, transposed for the warp-per-keypoint kernel: word j * 32 + lane = test lane * 8 + j
-void brief_pattern_transposed(unsigned* out256)
+// rBRIEF pattern as floats, transposed for the warp-per-keypoint kernel: entry j * 32 + lane = test lane * 8 + j
+void brief_pattern_transposed(float* out1024)
 {
     static const int8_t pat[256 * 4] = {
 #include "brief_pattern.inc"
     };
     for(int lane = 0; lane < 32; ++lane)
         for(int j = 0; j < 8; ++j)
-        {
-            const int8_t* t = pat + (lane * 8 + j) * 4;
-            out256[j * 32 + lane] = (unsigned)(uint8_t)t[0] | ((unsigned)(uint8_t)t[1] << 8) | ((unsigned)(uint8_t)t[2] << 16) |
-                                    ((unsigned)(uint8_t)t[3] << 24);
-        }
+            for(int c = 0; c < 4; ++c)
+                out1024[(j * 32 + lane) * 4 + c] = (float)pat[(lane * 8 + j) * 4 + c];
 }
 
 // =================================================================================================
@@ -888,7 +920,7 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
     {
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
         dim3 blk(32, 8);
-        dim3 grd((D.w + 127) / 128, (D.h + 7) / 8, P.n_frames);
+        dim3 grd((D.w + 4 + 127) / 128, (D.h + 7) / 8, P.n_frames);
         k_resize<<<grd, blk, 0, st>>>(pyr + S.img_off + P.frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride, S.w, S.h,
                                       pyr + D.img_off + P.frame0 * D.img_frame_stride, D.pitch, D.img_frame_stride, D.w, D.h,
                                       xtab + D.xtab_off, ytab + D.ytab_off);
@@ -902,9 +934,9 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
     for(int l = l_begin; l < l_end; ++l)
     {
         const LevelDesc& L = P.lv[l];
-        dim3 grd((L.w + BT_W - 1) / BT_W, (L.h + BT_H - 1) / BT_H, P.n_frames);
+        dim3 grd((L.w + BT_W - 1) / BT_W, (L.h + 4 * BT_H - 1) / (4 * BT_H), P.n_frames);
         const long long off = L.img_off + P.frame0 * L.img_frame_stride;
-        k_blur<<<grd, 256, 0, st>>>(pyr + off, blur + off, L.pitch, L.img_frame_stride, L.w, L.h);
+        k_blur<<<grd, 128, 0, st>>>(pyr + off, blur + off, L.pitch, L.img_frame_stride, L.w, L.h);
         ++*launches;
     }
 }
@@ -941,7 +973,7 @@ void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned
 }
 
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
-                            const SelRec* sel, const unsigned* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int* out_counts,
+                            const SelRec* sel, const float4* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int* out_counts,
                             int out_cap, int n_slots, const PipeParams& P, long long* launches)
 {
     const int slots = n_slots < 1 ? 1 : n_slots;
