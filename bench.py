@@ -135,6 +135,8 @@ def run_reference(args, rank, world):
         return
     pkg = graft.load_package()
     from oracle import oracle as O
+    if args.workload == "c5":
+        return run_reference_db(args, pkg, O)
     W, H, nfeat, _, mode, label = WORKLOADS[args.workload if args.workload in WORKLOADS else "c2"]
     threads = os.cpu_count() or 1
     n_sample = max(threads, 8)  # frames per step: one per host thread
@@ -154,6 +156,32 @@ def run_reference(args, rank, world):
             "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def run_reference_db(args, pkg, O):
+    """--impl reference --workload c5: the CPU oracle's keyframe-DB scoring on a bounded sample per step"""
+    threads = os.cpu_count() or 1
+    n, nk = 1000, 8 * threads
+    q = np.random.default_rng(2).integers(0, 256, (1, n, 32), dtype=np.uint8)
+    db = pkg.synth.descriptor_db(nk, n, seed=1)
+    qc, kc = np.full(1, n, np.int32), np.full(nk, n, np.int32)
+    for _ in range(args.warmup):
+        O.db_scores(q, qc, db, kc, nthreads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        O.db_topk(O.db_scores(q, qc, db, kc, nthreads=threads), 10)
+    total = time.perf_counter() - t0
+    v = float(nk) * n * n * args.steps / total
+    print(json.dumps({"metric": "DB Hamming descriptor-pair evaluations/sec", "value": v, "unit": "descriptor pairs/s",
+                      "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
+                      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 (xor/popc)",
+                      "data": "synthetic", "impl": "reference",
+                      "config": {"workload": "configs[4]: loop-candidate verification (CPU sample)", "descriptors_per_frame": n,
+                                 "query_frames_per_step": 1, "keyframes_per_step": nk},
+                      "cpu_baseline": {"value": v, "unit": "descriptor pairs/s", "cores": threads, "kind": "port",
+                                       "sample": f"1 query frame x {nk} keyframes x {n}^2 pairs per step, OpenMP over keyframes"},
+                      "e2e": {"value": v, "unit": "descriptor pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}))
 
 
 def main():

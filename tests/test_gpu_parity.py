@@ -300,6 +300,25 @@ def test_db_sharded_merge_equals_single(pkg, ctx, oracle):
     assert (os_.cpu().numpy() == whole_s).all() and (oi.cpu().numpy() == whole_i).all()
 
 
+def test_sharded_keyframe_db_host_class(pkg, ctx, oracle):
+    """ShardedKeyframeDb at world 1 (device tensors in/out) == oracle; the N > 1 exchange is covered by tests/test_sharded_db.py"""
+    import torch
+    from modular_slam_b200.keyframe_db import ShardedKeyframeDb
+    rng = np.random.default_rng(3)
+    Q, K, n, k = 4, 30, 200, 3
+    q = rng.integers(0, 256, (Q, n, 32), dtype=np.uint8)
+    db = pkg.synth.descriptor_db(K, n, seed=12)
+    pkg.synth.plant_copies(db, q, frac=0.2, seed=1)
+    qc, kc = np.full(Q, n, np.int32), np.full(K, n, np.int32)
+    kdb = ShardedKeyframeDb(ctx)
+    kdb.load_shard(torch.from_numpy(db).cuda(), torch.from_numpy(kc).cuda(), id_base=500)
+    torch.cuda.synchronize()
+    s, ids = kdb.query(torch.from_numpy(q).cuda(), torch.from_numpy(qc).cuda(), k)
+    ctx.synchronize()
+    rs, rid = oracle.db_topk(oracle.db_scores(q, qc, db, kc, nthreads=4), k, id_base=500)
+    assert (s.cpu().numpy() == rs).all() and (ids.cpu().numpy() == rid).all()
+
+
 # ---- the reference-facing mirror -------------------------------------------------------------------------------------
 def test_frontend_mirror_reads_like_the_reference(pkg, bundled):
     det = pkg.OrbB200Detector(max_width=640, max_height=480)
