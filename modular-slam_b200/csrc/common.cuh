@@ -21,6 +21,7 @@ struct LevelDesc
     int cand_cap;    // capacity of this level's candidate list (upper bound of strict 3x3 maxima)
     int tiles_x, tiles_y; // FAST tiling of the interior
     int tile_base;   // first FAST tile index of this level inside the fused launch
+    int blur_xblocks, blur_warp_base; // blur: 128-px column blocks per row band; first warp index of the level
     long long img_off;          // bytes
     long long img_frame_stride; // bytes
     long long cand_off;         // elements, within one frame's candidate block
@@ -36,6 +37,7 @@ struct PipeParams
     int frame0; // first frame (absolute index in the context's batch buffers) this launch covers; n_frames from there
     long long cand_frame_stride; // elements per frame in the candidate arrays
     int total_fast_tiles, pad1;
+    int one, minus_one; // +1 / -1 as run-time values (IMAD pipe steering in k_fast)
     LevelDesc lv[kMaxLevels];
 };
 

@@ -179,13 +179,15 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
     P.edge = cfg.edge_threshold;
     P.fast_thr = cfg.fast_threshold;
     P.kp_cap = kp_cap;
+    P.one = 1;
+    P.minus_one = -1;
     int w[kMaxLevels], h[kMaxLevels], nl[kMaxLevels];
     float sc[kMaxLevels];
     level_geometry(W, H, cfg.nlevels, cfg.scale_factor, w, h, sc);
     features_per_level(cfg.nfeatures, cfg.nlevels, cfg.scale_factor, nl);
     size_t off = 0;
     long long coff = 0;
-    int toff_x = 0, toff_y = 0, tiles = 0;
+    int toff_x = 0, toff_y = 0, tiles = 0, bwarps = 0;
     g->xtab.clear();
     g->ytab.clear();
     for(int l = 0; l < cfg.nlevels; ++l)
@@ -207,6 +209,10 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
         fast_tiles(L.w, L.h, cfg.edge_threshold, &L.tiles_x, &L.tiles_y);
         L.tile_base = tiles;
         tiles += L.tiles_x * L.tiles_y;
+        int bw = 0;
+        blur_warps(L.w, L.h, &L.blur_xblocks, &bw);
+        L.blur_warp_base = bwarps;
+        bwarps += bw;
         L.xtab_off = toff_x;
         L.ytab_off = toff_y;
         if(l > 0)
@@ -627,11 +633,17 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
                           ctx->d_sel, ctx->d_err, P, &ctx->launches);
         }
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[0], s_fast));
-        for(int l = 0; l < nl; ++l)
+        for(int l = 0; l < l_split; ++l)
         {
             MSLAM_CUDA_OK(cudaStreamWaitEvent(s_blur, ctx->ev_level[l], 0));
             StageTimer t(ctx, MSLAM_B200_T_BLUR, s_blur);
             launch_blur(s_blur, ctx->d_pyr, ctx->d_blur, P, l, l + 1, &ctx->launches);
+        }
+        if(l_split < nl)
+        {
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_blur, ctx->ev_level[nl - 1], 0));
+            StageTimer t(ctx, MSLAM_B200_T_BLUR, s_blur);
+            launch_blur(s_blur, ctx->d_pyr, ctx->d_blur, P, l_split, nl, &ctx->launches);
         }
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[1], s_blur));
         MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[0], 0));

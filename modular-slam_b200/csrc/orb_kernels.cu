@@ -168,25 +168,37 @@ __device__ __forceinline__ void blur_row4(const Row12& wd, float (&o)[4])
     }
 }
 
-// A lane owns a 4-pixel-wide column strip and walks down 32 rows: the row pass of each new source row goes into a
-// 7-deep register ring, the column pass reads the ring -- no shared memory, no barriers, every source byte is read
-// once per 32-row band (+6 halo rows).  Source rows are fetched 7 rows ahead of their use (software pipeline), so the
-// walk is not bound by memory latency.  Rounding is the 1.5 * 2^23 magic add (round-to-nearest-even, like cvRound).
-__global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int pitch,
-                                              long long fs, int w, int h)
+// A lane owns a 4-pixel-wide column strip and walks down a band of BT_H rows: the row pass of each new source row goes
+// into a 7-deep register ring, the column pass reads the ring -- no shared memory, no barriers, every source byte is
+// read once per band (+6 halo rows).  Source rows sit in a 7-slot register buffer that is refilled right after a slot
+// is consumed, i.e. they are fetched 7 rows ahead of their use, so the walk is not bound by memory latency.
+// One launch covers every level of every frame: warp w of the grid is (level, column block, band) through the
+// per-level warp offsets in LevelDesc, so that small levels do not leave the machine idle.
+// Rounding is the 1.5 * 2^23 magic add (round-to-nearest-even, like cvRound / saturate_cast<uchar>(float)).
+__global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipeParams P, int l_begin, int l_end,
+                                                 const uint8_t* __restrict__ src, uint8_t* __restrict__ dst)
 {
     const float k1 = __int_as_float(0x3e434a39), k2 = __int_as_float(0x3e06387e), k3 = __int_as_float(0x3d8fafb1),
                 kc = __int_as_float(0x3e5d4ae0); // kernel[3 + 1], [3 + 2], [3 + 3], [3]
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int x = (blockIdx.x * 32 + lane) * 4;
-    const int y0 = (blockIdx.y * 4 + warp) * BT_H;
+    const int lane = threadIdx.x & 31;
+    int wg = blockIdx.x * 4 + (threadIdx.x >> 5) + P.lv[l_begin].blur_warp_base;
+    int l = l_begin;
+    while(l + 1 < l_end && wg >= P.lv[l + 1].blur_warp_base)
+        ++l;
+    const LevelDesc& L = P.lv[l];
+    wg -= L.blur_warp_base;
+    const int band = wg / L.blur_xblocks, xb = wg - band * L.blur_xblocks;
+    const int w = L.w, h = L.h, pitch = L.pitch;
+    const int x = (xb * 32 + lane) * 4;
+    const int y0 = band * BT_H;
     if(x >= w || y0 >= h)
         return;
-    const uint8_t* img = src + (long long)blockIdx.z * fs;
-    uint8_t* out = dst + (long long)blockIdx.z * fs;
+    const long long plane = L.img_off + (long long)(blockIdx.y + P.frame0) * L.img_frame_stride;
+    const uint8_t* img = src + plane;
+    uint8_t* out = dst + plane;
     const int rows = min(BT_H, h - y0);
     float r[7][4];
-    Row12 cur[7], nxt[7];
+    Row12 buf[7];
     {
         Row12 pre[6];
 #pragma unroll
@@ -194,19 +206,13 @@ __global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ src, u
             pre[s] = blur_load(img + (long long)reflect101(y0 - 3 + s, h) * pitch, x);
 #pragma unroll
         for(int k = 0; k < 7; ++k)
-            cur[k] = blur_load(img + (long long)reflect101(y0 + 3 + k, h) * pitch, x);
+            buf[k] = blur_load(img + (long long)reflect101(y0 + 3 + k, h) * pitch, x);
 #pragma unroll
         for(int s = 0; s < 6; ++s)
             blur_row4(pre[s], r[s]);
     }
     for(int i0 = 0; i0 < rows; i0 += 7)
     {
-        if(i0 + 7 < rows)
-        {
-#pragma unroll
-            for(int k = 0; k < 7; ++k)
-                nxt[k] = blur_load(img + (long long)reflect101(y0 + 3 + i0 + 7 + k, h) * pitch, x);
-        }
 #pragma unroll
         for(int k = 0; k < 7; ++k)
         {
@@ -214,7 +220,9 @@ __global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ src, u
             if(i < rows)
             {
                 // ring slot (k + j) % 7 holds source row y - 3 + j of output row y = y0 + i
-                blur_row4(cur[k], r[(k + 6) % 7]);
+                blur_row4(buf[k], r[(k + 6) % 7]);
+                if(i + 7 < rows)
+                    buf[k] = blur_load(img + (long long)reflect101(y0 + 3 + i + 7, h) * pitch, x);
                 unsigned bits[4];
 #pragma unroll
                 for(int q = 0; q < 4; ++q)
@@ -230,9 +238,6 @@ __global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ src, u
                 *reinterpret_cast<unsigned*>(out + (long long)(y0 + i) * pitch + x) = __byte_perm(lo, hi, 0x5410);
             }
         }
-#pragma unroll
-        for(int k = 0; k < 7; ++k)
-            cur[k] = nxt[k];
     }
 }
 
@@ -392,6 +397,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row 4 * warp + row is a corner
     {
         const unsigned t4 = (unsigned)thr * 0x01010101u;
+        const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
         const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[4 * warp][0]) + lane;
         unsigned wm[10], w0[10], wp[10]; // staged rows 4 * warp .. 4 * warp + 9, words lane, lane + 1, lane + 2
 #pragma unroll
@@ -418,8 +424,10 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
                 const int r = row + 3 + DY[k];
                 const unsigned R = ring4(wm[r], w0[r], wp[r], DX[k]);
                 const unsigned r7 = R & 0x7f7f7f7fu;
-                mb[k] = lop3_maj_a_nb_c(R, H, r7 + nH7);  // bit 7: R > centre + t
-                md[k] = lop3_maj_a_nb_c(Lo, R, K - r7);   // bit 7: R < centre - t
+                // the two byte-lane additions go through IMAD with multipliers the compiler cannot see (+1 / -1 from the
+                // parameter block): they issue on the FMA pipe, which idles while the ALU pipe is the one that binds here
+                mb[k] = lop3_maj_a_nb_c(R, H, r7 * one + nH7);  // bit 7: R > centre + t
+                md[k] = lop3_maj_a_nb_c(Lo, R, r7 * mone + K);  // bit 7: R < centre - t
             }
             const unsigned f = (any_run9(mb) | any_run9(md)) & 0x80808080u;
             // gather the four bit-7 flags into a nibble
@@ -590,6 +598,36 @@ __device__ float harris_response(const uint8_t* __restrict__ img, int pitch, int
 }
 
 constexpr int SEL_THREADS = 256;
+constexpr int SEL_RANK_SMEM = 2048; // final (y, x) ranking runs out of shared memory up to this many survivors
+
+// Block-wide "k-th largest bin" over a 256-bin histogram, one bin per thread (bin = tid):
+//   S[v] = sum of bins >= v.  The unique v with S[v] >= k > S[v + 1] is written to *s_thr and k - S[v + 1] to *s_k.
+// Requires 1 <= k <= S[0].  Two barriers; replaces a 256-step serial walk by one thread.
+__device__ __forceinline__ void suffix_select(unsigned hval, unsigned k, unsigned* s_w /* 8 */, unsigned* s_thr, unsigned* s_k)
+{
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    unsigned sfx = hval;
+#pragma unroll
+    for(int o = 1; o < 32; o <<= 1)
+    {
+        const unsigned t = __shfl_down_sync(0xffffffffu, sfx, o);
+        if(lane + o < 32)
+            sfx += t;
+    }
+    if(lane == 0)
+        s_w[wid] = sfx;
+    __syncthreads();
+#pragma unroll
+    for(int w = 1; w < 8; ++w)
+        sfx += (w > wid) ? s_w[w] : 0u;
+    const unsigned next = sfx - hval;
+    if(sfx >= k && next < k)
+    {
+        *s_thr = (unsigned)tid;
+        *s_k = k - next;
+    }
+    __syncthreads();
+}
 
 __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                         unsigned* __restrict__ cand, unsigned* __restrict__ cand2,
@@ -598,6 +636,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
                                                         SelRec* __restrict__ sel, int* __restrict__ err)
 {
     __shared__ unsigned s_hist[256];
+    __shared__ unsigned s_w[8];
+    __shared__ unsigned s_rank[SEL_RANK_SMEM];
     __shared__ unsigned s_cnt, s_thr, s_k;
     const int l = blockIdx.x, b = blockIdx.y + P.frame0, tid = threadIdx.x;
     const LevelDesc& L = P.lv[l];
@@ -620,25 +660,14 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
     unsigned thr1 = 0;
     if(n > kcut1)
     {
-        s_hist[tid] = hist[((long long)b * P.nlevels + l) * 256 + tid];
-        __syncthreads();
-        if(tid == 0)
+        if(kcut1 == 0)
+            thr1 = 256; // keep nothing
+        else
         {
-            unsigned cum = 0, t = 256; // t = 256 => keep nothing (kcut1 == 0)
-            if(kcut1 > 0)
-                for(int v = 255; v >= 0; --v)
-                {
-                    cum += s_hist[v];
-                    if(cum >= kcut1)
-                    {
-                        t = (unsigned)v;
-                        break;
-                    }
-                }
-            s_thr = t;
+            // the histogram counts every NMS survivor (>= n > kcut1 entries), so the k-th largest exists
+            suffix_select(hist[((long long)b * P.nlevels + l) * 256 + tid], kcut1, s_w, &s_thr, &s_k);
+            thr1 = s_thr;
         }
-        __syncthreads();
-        thr1 = s_thr;
     }
     if(tid == 0)
         s_cnt = 0;
@@ -669,9 +698,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
             thrkey = 0xffffffffu; // keep nothing (handled below)
         else
         {
-            unsigned prefix = 0, mask = 0;
-            if(tid == 0)
-                s_k = kcut2;
+            unsigned prefix = 0, mask = 0, krem = kcut2;
             for(int shift = 24; shift >= 0; shift -= 8)
             {
                 s_hist[tid] = 0;
@@ -683,22 +710,11 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
                         atomicAdd(&s_hist[(k >> shift) & 255u], 1u);
                 }
                 __syncthreads();
-                if(tid == 0)
-                {
-                    unsigned cum = 0, k = s_k;
-                    int v = 255;
-                    for(; v > 0; --v)
-                    {
-                        if(cum + s_hist[v] >= k)
-                            break;
-                        cum += s_hist[v];
-                    }
-                    s_k = k - cum;
-                    s_thr = (unsigned)v;
-                }
-                __syncthreads();
+                // by induction at least krem keys carry the current prefix, so the digit exists
+                suffix_select(s_hist[tid], krem, s_w, &s_thr, &s_k);
                 prefix |= s_thr << shift;
                 mask |= 255u << shift;
+                krem = s_k;
                 __syncthreads();
             }
             thrkey = prefix;
@@ -729,12 +745,26 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
     }
     // ---- canonical order: rank by (y, x) ----
     SelRec* out = sel + ((long long)b * P.nlevels + l) * P.kp_cap;
+    const bool in_smem = nf <= (unsigned)SEL_RANK_SMEM;
+    if(in_smem)
+    {
+        for(unsigned i = tid; i < nf; i += SEL_THREADS)
+            s_rank[i] = c1[i] >> 8;
+        __syncthreads();
+    }
     for(unsigned i = tid; i < nf; i += SEL_THREADS)
     {
         const unsigned rec = c1[i], me = rec >> 8;
         unsigned rank = 0;
-        for(unsigned j = 0; j < nf; ++j)
-            rank += (c1[j] >> 8) < me;
+        if(in_smem)
+        {
+#pragma unroll 4
+            for(unsigned j = 0; j < nf; ++j)
+                rank += s_rank[j] < me;
+        }
+        else
+            for(unsigned j = 0; j < nf; ++j)
+                rank += (c1[j] >> 8) < me;
         if(rank < (unsigned)P.kp_cap)
         {
             SelRec r;
@@ -928,17 +958,23 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
     }
 }
 
+void blur_warps(int w, int h, int* xblocks, int* warps)
+{
+    *xblocks = (w + BT_W - 1) / BT_W;
+    *warps = *xblocks * ((h + BT_H - 1) / BT_H);
+}
+
+// levels [l_begin, l_end) of every frame in one launch
 void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, int l_begin, int l_end,
                  long long* launches)
 {
+    int warps = 0;
     for(int l = l_begin; l < l_end; ++l)
-    {
-        const LevelDesc& L = P.lv[l];
-        dim3 grd((L.w + BT_W - 1) / BT_W, (L.h + 4 * BT_H - 1) / (4 * BT_H), P.n_frames);
-        const long long off = L.img_off + P.frame0 * L.img_frame_stride;
-        k_blur<<<grd, 128, 0, st>>>(pyr + off, blur + off, L.pitch, L.img_frame_stride, L.w, L.h);
-        ++*launches;
-    }
+        warps += P.lv[l].blur_xblocks * ((P.lv[l].h + BT_H - 1) / BT_H);
+    if(warps <= 0)
+        return;
+    k_blur<<<dim3((warps + 3) / 4, P.n_frames), 128, 0, st>>>(P, l_begin, l_end, pyr, blur);
+    ++*launches;
 }
 
 void fast_tiles(int w, int h, int edge, int* tx, int* ty)
