@@ -26,6 +26,7 @@ struct LevelDesc
     long long img_frame_stride; // bytes
     long long cand_off;         // elements, within one frame's candidate block
     int xtab_off, ytab_off;     // offsets into the resize tap tables (short2 {ofs, alpha1})
+    int qtab_off, rs_quads;     // resize quad table (uint4 per 4 output columns); rs_quads = 0 => generic kernel
     float scale;                // (float)pow((double)scaleFactor, l)
     float inv_scale;            // 1.f / scale
 };

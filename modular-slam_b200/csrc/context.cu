@@ -36,6 +36,7 @@ struct mslam_b200_ctx
     uint8_t* d_blur = nullptr; // same layout
     size_t pyr_bytes = 0, bgr_bytes = 0;
     short2 *d_xtab = nullptr, *d_ytab = nullptr;
+    uint4* d_qtab = nullptr; // resize quad table (k_resize_quads)
     int tab_cap = 0;
     unsigned *d_cand = nullptr, *d_cand2 = nullptr, *d_keys = nullptr, *d_keys2 = nullptr;
     long long cand_elems = 0; // per frame
@@ -160,6 +161,51 @@ static void resize_taps(int src, int dst, short2* tab)
     }
 }
 
+static int reflect101_host(int p, int n)
+{
+    if(n == 1)
+        return 0;
+    while(p < 0 || p >= n)
+        p = p < 0 ? -p : 2 * n - 2 - p;
+    return p;
+}
+
+// Quad table of k_resize_quads for one level: entry q covers output columns 4q .. 4q+3 (columns >= dw are the
+// reflect-101 padding the blur reads).  {x: first source byte of the 8-byte window, y: PRMT selectors (pixels 0,1 |
+// pixels 2,3 << 16), z: alpha1 of pixels 0,1, w: alpha1 of pixels 2,3}.  Returns false when a quad's taps do not fit
+// the window (scale factors > 2), in which case the level uses the generic kernel.
+static bool resize_quads(const short2* xtab, int dw, std::vector<uint4>* out)
+{
+    const int nq = (dw + 4 + 3) / 4;
+    for(int q = 0; q < nq; ++q)
+    {
+        int i0[4], a1[4], base = 1 << 30;
+        for(int j = 0; j < 4; ++j)
+        {
+            const int x = 4 * q + j;
+            const short2 t = xtab[x < dw ? x : reflect101_host(x, dw)];
+            i0[j] = t.x;
+            a1[j] = t.y;
+            base = std::min(base, i0[j]);
+        }
+        unsigned sel[4];
+        for(int j = 0; j < 4; ++j)
+        {
+            const int o = i0[j] - base;
+            if(o + 1 > 7)
+                return false;
+            sel[j] = (unsigned)o | ((unsigned)(o + 1) << 4);
+        }
+        uint4 e;
+        e.x = (unsigned)base;
+        e.y = (sel[0] | (sel[1] << 8)) | ((sel[2] | (sel[3] << 8)) << 16);
+        e.z = (unsigned)a1[0] | ((unsigned)a1[1] << 16);
+        e.w = (unsigned)a1[2] | ((unsigned)a1[3] << 16);
+        out->push_back(e);
+    }
+    return true;
+}
+
 struct Geometry
 {
     PipeParams P;
@@ -167,6 +213,7 @@ struct Geometry
     long long cand_elems;
     int tab_elems;
     std::vector<short2> xtab, ytab;
+    std::vector<uint4> qtab;
 };
 
 static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int H, Geometry* g)
@@ -189,13 +236,14 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
     long long coff = 0;
     int toff_x = 0, toff_y = 0, tiles = 0, bwarps = 0;
     g->xtab.clear();
+    g->qtab.clear();
     g->ytab.clear();
     for(int l = 0; l < cfg.nlevels; ++l)
     {
         LevelDesc& L = P.lv[l];
         L.w = std::max(w[l], 1);
         L.h = std::max(h[l], 1);
-        L.pitch = (int)align_up((size_t)L.w + 8, 64); // room for the 4 reflect-101 padding columns + aligned over-reads
+        L.pitch = (int)align_up((size_t)L.w + 12, 64); // the 4 reflect-101 padding columns + aligned over-reads (resize window: 12 B)
         L.n_keep = nl[l];
         L.scale = sc[l];
         L.inv_scale = 1.f / sc[l];
@@ -221,6 +269,15 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
             g->ytab.resize(toff_y + L.h);
             resize_taps(P.lv[l - 1].w, L.w, g->xtab.data() + toff_x);
             resize_taps(P.lv[l - 1].h, L.h, g->ytab.data() + toff_y);
+            L.qtab_off = (int)g->qtab.size();
+            const size_t before = g->qtab.size();
+            if(resize_quads(g->xtab.data() + toff_x, L.w, &g->qtab))
+                L.rs_quads = (int)(g->qtab.size() - before);
+            else
+            {
+                g->qtab.resize(before);
+                L.rs_quads = 0;
+            }
             toff_x += L.w;
             toff_y += L.h;
         }
@@ -248,6 +305,9 @@ static int set_geometry(mslam_b200_ctx* ctx, int W, int H)
                                       ctx->stream));
         MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_ytab, g.ytab.data(), g.ytab.size() * sizeof(short2), cudaMemcpyHostToDevice,
                                       ctx->stream));
+        if(!g.qtab.empty())
+            MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_qtab, g.qtab.data(), g.qtab.size() * sizeof(uint4), cudaMemcpyHostToDevice,
+                                          ctx->stream));
         MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream)); // the host vectors die with this scope
     }
     ctx->P = g.P;
@@ -327,7 +387,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     cudaSetDevice(ctx->cfg.device);
     if(ctx->stream)
         cudaStreamSynchronize(ctx->stream);
-    void* dev[] = {ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
+    void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
                    ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat};
@@ -442,6 +502,7 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaMalloc(&ctx->d_blur, ctx->pyr_bytes));
     CREATE_OK(cudaMalloc(&ctx->d_xtab, ctx->tab_cap * sizeof(short2)));
     CREATE_OK(cudaMalloc(&ctx->d_ytab, ctx->tab_cap * sizeof(short2)));
+    CREATE_OK(cudaMalloc(&ctx->d_qtab, ctx->tab_cap * sizeof(uint4))); // <= (w + 7) / 4 quads per level, far below tab_cap
     const size_t cand_bytes = B * (size_t)ctx->cand_elems * sizeof(unsigned);
     CREATE_OK(cudaMalloc(&ctx->d_cand, cand_bytes));
     CREATE_OK(cudaMalloc(&ctx->d_cand2, cand_bytes));
@@ -557,7 +618,7 @@ static int run_pyramid(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames)
     }
     {
         StageTimer t(ctx, MSLAM_B200_T_RESIZE);
-        launch_pyramid(ctx->stream, ctx->d_pyr, ctx->P, ctx->d_xtab, ctx->d_ytab, 1, ctx->P.nlevels, &ctx->launches);
+        launch_pyramid(ctx->stream, ctx->d_pyr, ctx->P, ctx->d_xtab, ctx->d_ytab, ctx->d_qtab, ctx->sm_count, 1, ctx->P.nlevels, &ctx->launches);
     }
     return MSLAM_B200_OK;
 }
@@ -611,7 +672,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         {
             {
                 StageTimer t(ctx, MSLAM_B200_T_RESIZE);
-                launch_pyramid(st, ctx->d_pyr, P, ctx->d_xtab, ctx->d_ytab, l, l + 1, &ctx->launches);
+                launch_pyramid(st, ctx->d_pyr, P, ctx->d_xtab, ctx->d_ytab, ctx->d_qtab, ctx->sm_count, l, l + 1, &ctx->launches);
             }
             MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[l], st));
         }

@@ -7,7 +7,7 @@ namespace mslam_b200
 // ORB path
 void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const PipeParams& P, long long* launches);
 void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const short2* xtab, const short2* ytab,
-                    int l_begin, int l_end, long long* launches);
+                    const uint4* qtab, int sm_count, int l_begin, int l_end, long long* launches);
 void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, int l_begin, int l_end,
                  long long* launches);
 void fast_tiles(int w, int h, int edge, int* tx, int* ty);

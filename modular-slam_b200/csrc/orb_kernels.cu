@@ -87,11 +87,123 @@ __global__ void __launch_bounds__(256) k_gray1(const uint8_t* __restrict__ bgr, 
 // =================================================================================================
 // K2  resize : level l-1 -> level l, cv::resize INTER_LINEAR_EXACT (item 2)
 //   per axis the host precomputes (ofs, alpha1) in IEEE double; horizontal pass in 8.8 fixed point,
-//   vertical pass (a0*h0 + a1*h1 + 32768) >> 16.  4 output pixels per thread, 32-bit stores.
+//   vertical pass (a0*h0 + a1*h1 + 32768) >> 16.
+//
+//   k_resize_quads (the fast path): a lane owns 4 adjacent output columns and walks down a band of output rows.
+//   Everything that depends on x only is decoded once per lane from one uint4 of the per-level quad table
+//   (ResizeQuad): the source byte the quad's window starts at, two PRMT selectors that pull the (left, right) taps of
+//   two pixels each out of the 8-byte window, and the four alpha1.  Per SOURCE row a lane then issues 3 aligned 32-bit
+//   loads, 2 funnel shifts, 2 PRMT and 4 IDP.2A (h = a0*p[i] + a1*p[i+1], both taps in one instruction); consecutive
+//   output rows share their source rows (1.2 new source rows per output row), so the horizontal pass is never
+//   repeated.  Per OUTPUT row: 8 IMAD, 3 PRMT, one 32-bit store.  ~10 instructions per pixel against ~60 for the
+//   per-pixel table walk of k_resize_generic, which stays as the fallback for scale factors whose 4-pixel footprint
+//   does not fit the 8-byte window.
 // =================================================================================================
-__global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src, int spitch, long long sfs, int sw, int sh,
-                                                uint8_t* __restrict__ dst, int dpitch, long long dfs, int dw, int dh,
-                                                const short2* __restrict__ xtab, const short2* __restrict__ ytab)
+constexpr int RS_BAND_MAX = 16; // output rows per warp (chosen per launch: short bands when the level alone cannot fill the machine)
+
+struct Row3
+{
+    unsigned a, b, c;
+};
+__device__ __forceinline__ Row3 resize_load(const uint8_t* __restrict__ row, int wi)
+{
+    const unsigned* p = reinterpret_cast<const unsigned*>(row) + wi;
+    Row3 r;
+    r.a = __ldg(p), r.b = __ldg(p + 1), r.c = __ldg(p + 2);
+    return r;
+}
+__device__ __forceinline__ void resize_hrow(const Row3& W, int sh, unsigned selA, unsigned selB, unsigned w0, unsigned w1,
+                                            unsigned w2, unsigned w3, unsigned (&h)[4])
+{
+    const unsigned S0 = __funnelshift_r(W.a, W.b, sh), S1 = __funnelshift_r(W.b, W.c, sh);
+    const unsigned pA = __byte_perm(S0, S1, selA), pB = __byte_perm(S0, S1, selB);
+    h[0] = __dp2a_lo(w0, pA, 0u);
+    h[1] = __dp2a_hi(w1, pA, 0u);
+    h[2] = __dp2a_lo(w2, pB, 0u);
+    h[3] = __dp2a_hi(w3, pB, 0u);
+}
+
+// The band's source rows form one contiguous run r_first .. r_last; the lane streams through them in order with the raw
+// words of the next RS_AHEAD rows already in flight, keeps the horizontal pass of the last two rows, and emits every
+// output row whose lower tap row has just been produced.  The per-row (ofs, alpha1) of the band sit in lanes 0..15 of
+// one coalesced load and are broadcast with shuffles, so no load sits on the row-to-row dependency chain.
+constexpr int RS_AHEAD = 4;
+
+__global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict__ src, int spitch, long long sfs, int sh_rows,
+                                                      uint8_t* __restrict__ dst, int dpitch, long long dfs, int dh, int nquads,
+                                                      int xblocks, int rs_band, const uint4* __restrict__ qtab,
+                                                      const short2* __restrict__ ytab)
+{
+    static_assert(RS_BAND_MAX <= 32, "one lane per output row of the band");
+    const int lane = threadIdx.x & 31;
+    const int wg = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int band = wg / xblocks, xb = wg - band * xblocks;
+    const int yb = band * rs_band;
+    if(yb >= dh) // warp-uniform
+        return;
+    const int quad_raw = xb * 32 + lane;
+    const bool live = quad_raw < nquads;
+    const int quad = live ? quad_raw : nquads - 1; // dead lanes shadow the last quad (they must stay for the shuffles)
+    const uint4 q = __ldg(qtab + quad);
+    const int wi = (int)(q.x >> 2), sh = (int)(q.x & 3u) * 8;
+    const unsigned selA = q.y & 0xffffu, selB = q.y >> 16;
+    const unsigned a10 = q.z & 0xffffu, a11 = q.z >> 16, a12 = q.w & 0xffffu, a13 = q.w >> 16;
+    const unsigned w0 = (256u - a10) | (a10 << 16), w1 = (256u - a11) | (a11 << 16), w2 = (256u - a12) | (a12 << 16),
+                   w3 = (256u - a13) | (a13 << 16);
+    const uint8_t* simg = src + (long long)blockIdx.y * sfs;
+    uint8_t* dimg = dst + (long long)blockIdx.y * dfs + 4 * quad;
+    const int ye = min(yb + rs_band, dh);
+    const short2 ty_lane = __ldg(ytab + min(yb + lane, dh - 1));
+    const int r_first = __shfl_sync(0xffffffffu, (int)ty_lane.x, 0);
+    const int r_last = min(__shfl_sync(0xffffffffu, (int)ty_lane.x, ye - 1 - yb) + 1, sh_rows - 1);
+
+    Row3 buf[RS_AHEAD];
+#pragma unroll
+    for(int k = 0; k < RS_AHEAD; ++k)
+        buf[k] = resize_load(simg + (long long)min(r_first + k, r_last) * spitch, wi);
+    unsigned hP[4] = {0, 0, 0, 0}, hC[4] = {0, 0, 0, 0};
+    int y = yb;
+    int n0 = r_first;                                    // taps of output row y
+    unsigned b1 = (unsigned)__shfl_sync(0xffffffffu, (int)ty_lane.y, 0);
+    for(int r0 = r_first; r0 <= r_last; r0 += RS_AHEAD)
+    {
+#pragma unroll
+        for(int k = 0; k < RS_AHEAD; ++k)
+        {
+            const int r = r0 + k;
+            if(r <= r_last) // warp-uniform
+            {
+#pragma unroll
+                for(int j = 0; j < 4; ++j)
+                    hP[j] = hC[j];
+                resize_hrow(buf[k], sh, selA, selB, w0, w1, w2, w3, hC);
+                if(r + RS_AHEAD <= r_last)
+                    buf[k] = resize_load(simg + (long long)(r + RS_AHEAD) * spitch, wi);
+                // emit the output rows whose second tap row min(n0 + 1, last source row) is r
+                while(y < ye && min(n0 + 1, sh_rows - 1) == r)
+                {
+                    const unsigned b0 = 256u - b1;
+                    unsigned v[4];
+#pragma unroll
+                    for(int j = 0; j < 4; ++j)
+                        v[j] = b0 * (n0 == r ? hC[j] : hP[j]) + b1 * hC[j] + 32768u; // result byte = bits 16..23
+                    const unsigned lo = __byte_perm(v[0], v[1], 0x0062), hi = __byte_perm(v[2], v[3], 0x0062);
+                    if(live)
+                        *reinterpret_cast<unsigned*>(dimg + (long long)y * dpitch) = __byte_perm(lo, hi, 0x5410);
+                    ++y;
+                    const int src_lane = min(y, ye - 1) - yb;
+                    n0 = __shfl_sync(0xffffffffu, (int)ty_lane.x, src_lane);
+                    b1 = (unsigned)__shfl_sync(0xffffffffu, (int)ty_lane.y, src_lane);
+                }
+            }
+        }
+    }
+}
+
+// fallback: 4 output pixels per thread, per-pixel table walk
+__global__ void __launch_bounds__(256) k_resize_generic(const uint8_t* __restrict__ src, int spitch, long long sfs, int sw, int sh,
+                                                        uint8_t* __restrict__ dst, int dpitch, long long dfs, int dw, int dh,
+                                                        const short2* __restrict__ xtab, const short2* __restrict__ ytab)
 {
     const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
@@ -944,16 +1056,34 @@ void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const Pipe
 }
 
 void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const short2* xtab, const short2* ytab,
-                    int l_begin, int l_end, long long* launches)
+                    const uint4* qtab, int sm_count, int l_begin, int l_end, long long* launches)
 {
     for(int l = l_begin < 1 ? 1 : l_begin; l < l_end; ++l)
     {
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
-        dim3 blk(32, 8);
-        dim3 grd((D.w + 4 + 127) / 128, (D.h + 7) / 8, P.n_frames);
-        k_resize<<<grd, blk, 0, st>>>(pyr + S.img_off + P.frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride, S.w, S.h,
-                                      pyr + D.img_off + P.frame0 * D.img_frame_stride, D.pitch, D.img_frame_stride, D.w, D.h,
-                                      xtab + D.xtab_off, ytab + D.ytab_off);
+        if(D.rs_quads > 0)
+        {
+            // the shortest band that still keeps the launch within one wave of resident warps: a warp's walk is a serial
+            // chain (~90 instructions per row), so small levels want many short walks rather than few long ones
+            const int xblocks = (D.rs_quads + 31) / 32;
+            int rs_band = 2;
+            while(rs_band < RS_BAND_MAX &&
+                  (long long)xblocks * ((D.h + rs_band - 1) / rs_band) * P.n_frames > (long long)sm_count * 64)
+                rs_band *= 2;
+            const int bands = (D.h + rs_band - 1) / rs_band;
+            k_resize_quads<<<dim3((xblocks * bands + 3) / 4, P.n_frames), 128, 0, st>>>(
+                pyr + S.img_off + P.frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride, S.h,
+                pyr + D.img_off + P.frame0 * D.img_frame_stride, D.pitch, D.img_frame_stride, D.h, D.rs_quads, xblocks, rs_band,
+                qtab + D.qtab_off, ytab + D.ytab_off);
+        }
+        else
+        {
+            dim3 blk(32, 8);
+            dim3 grd((D.w + 4 + 127) / 128, (D.h + 7) / 8, P.n_frames);
+            k_resize_generic<<<grd, blk, 0, st>>>(pyr + S.img_off + P.frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride,
+                                                  S.w, S.h, pyr + D.img_off + P.frame0 * D.img_frame_stride, D.pitch,
+                                                  D.img_frame_stride, D.w, D.h, xtab + D.xtab_off, ytab + D.ytab_off);
+        }
         ++*launches;
     }
 }
