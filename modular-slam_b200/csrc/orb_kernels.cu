@@ -426,17 +426,21 @@ __device__ __forceinline__ unsigned ring4(unsigned wm, unsigned w0, unsigned wp,
     }
 }
 
-// exact cornerScore of a pixel known to be a FAST corner
-__device__ __forceinline__ int corner_score(const uint8_t* c /* centre in the staged tile */)
+// exact cornerScore of TWO pixels known to be FAST corners, one per u16 lane of a packed min/max network.
+// Each corner is read in the domain in which it is "centre above the whole arc": the raw tile for a corner whose arc is
+// darker than the centre, the complemented tile (255 - pixel) for a corner whose arc is brighter (phase A knows which;
+// the other side cannot win: two 9-arcs of a 16-ring always overlap).  In that domain
+//   score = centre - min over the 16 arcs (max over the 9 ring pixels of the arc) - 1,
+// with the arc maxima built from prefix/suffix maxima of the two half rings (28 + 32 VIMNMX.U16x2 for both corners).
+__device__ __forceinline__ unsigned corner_score2(const uint8_t* ca, const uint8_t* cb)
 {
     constexpr int S = FS_PW;
-    const int v = c[0];
-    const int ring[16] = {c[3 * S],      c[3 * S + 1],  c[2 * S + 2],  c[S + 3],  c[3],  c[-S + 3], c[-2 * S + 2], c[-3 * S + 1],
-                          c[-3 * S],     c[-3 * S - 1], c[-2 * S - 2], c[-S - 3], c[-3], c[S - 3],  c[2 * S - 2],  c[3 * S - 1]};
-    unsigned x[16]; // lane 0 = ring value, lane 1 = 255 - ring value
+    constexpr int OFF[16] = {3 * S,  3 * S + 1,  2 * S + 2,  S + 3,  3,  -S + 3, -2 * S + 2, -3 * S + 1,
+                             -3 * S, -3 * S - 1, -2 * S - 2, -S - 3, -3, S - 3,  2 * S - 2,  3 * S - 1};
+    unsigned x[16];
 #pragma unroll
     for(int k = 0; k < 16; ++k)
-        x[k] = (unsigned)ring[k] * 0xFFFF0001u + 0x00FF0000u;
+        x[k] = (unsigned)cb[OFF[k]] * 65536u + (unsigned)ca[OFF[k]]; // IMAD: fma pipe
     unsigned pa[8], sa[8], pb[8], sb[8]; // prefix / suffix maxima of the two half rings
     pa[0] = x[0], pb[0] = x[8], sa[7] = x[7], sb[7] = x[15];
 #pragma unroll
@@ -455,9 +459,8 @@ __device__ __forceinline__ int corner_score(const uint8_t* c /* centre in the st
         m = __vminu2(m, __vmaxu2(sa[k], pb[k]));
         m = __vminu2(m, __vmaxu2(sb[k], pa[k]));
     }
-    const int bright = v - (int)(m & 0xffffu);            // centre above the whole arc
-    const int dark = 255 - (int)(m >> 16) - v;            // centre below the whole arc
-    return max(bright, dark) - 1;
+    const unsigned v = (unsigned)cb[0] * 65536u + (unsigned)ca[0];
+    return v - m - 0x00010001u; // both lanes are >= fast_thr - ... > 0: no borrow crosses the lanes
 }
 
 __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, int l_begin, int l_end,
@@ -465,6 +468,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
                                               LevelCounters* __restrict__ ctr, unsigned* __restrict__ hist)
 {
     __shared__ __align__(16) uint8_t s_px[FS_PH][FS_PW];
+    __shared__ __align__(16) uint8_t s_pxc[FS_PH][FS_PW]; // 255 - pixel (phase B reads bright-arc corners here)
     __shared__ __align__(16) uint8_t s_sc[FS_SH][FS_SW];
     __shared__ unsigned short s_q[FS_SH * FS_SW];
     __shared__ unsigned s_out[FS_IW * FS_IH / 4 + 64];
@@ -487,14 +491,30 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     const int px0 = sx0 - 4, py0 = sy0 - 3;         // first staged pixel
     const uint8_t* img = pyr + L.img_off + (long long)b * L.img_frame_stride;
 
-    for(int i = tid; i < FS_PH * FS_PWW; i += 256)
     {
-        const int r = i / FS_PWW, c = i - r * FS_PWW;
-        const int gy = py0 + r, gx = px0 + 4 * c;
-        unsigned v = 0;
-        if(gy < L.h && gx < L.pitch)
-            v = __ldg(reinterpret_cast<const unsigned*>(img + (long long)gy * L.pitch + gx));
-        reinterpret_cast<unsigned*>(&s_px[r][0])[c] = v;
+        // all of the thread's tile words are requested before the first one is stored: one exposed load latency per CTA
+        constexpr int NLD = (FS_PH * FS_PWW + 255) / 256;
+        unsigned v[NLD];
+#pragma unroll
+        for(int k = 0; k < NLD; ++k)
+        {
+            const int i = tid + 256 * k;
+            const int r = i / FS_PWW, c = i - r * FS_PWW;
+            const int gy = py0 + r, gx = px0 + 4 * c;
+            v[k] = 0;
+            if(i < FS_PH * FS_PWW && gy < L.h && gx < L.pitch)
+                v[k] = __ldg(reinterpret_cast<const unsigned*>(img + (long long)gy * L.pitch + gx));
+        }
+#pragma unroll
+        for(int k = 0; k < NLD; ++k)
+        {
+            const int i = tid + 256 * k;
+            if(i < FS_PH * FS_PWW)
+            {
+                reinterpret_cast<unsigned*>(&s_px[0][0])[i] = v[k];
+                reinterpret_cast<unsigned*>(&s_pxc[0][0])[i] = ~v[k];
+            }
+        }
     }
     for(int i = tid; i < FS_SH * FS_SW / 16; i += 256)
         reinterpret_cast<uint4*>(&s_sc[0][0])[i] = make_uint4(0, 0, 0, 0);
@@ -507,6 +527,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
 
     // ---- phase A: classify 4 rows x 4 pixels per thread ----
     unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row 4 * warp + row is a corner
+    unsigned bright16 = 0; // ... and its arc is brighter than the centre
     {
         const unsigned t4 = (unsigned)thr * 0x01010101u;
         const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
@@ -541,9 +562,10 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
                 mb[k] = lop3_maj_a_nb_c(R, H, r7 * one + nH7);  // bit 7: R > centre + t
                 md[k] = lop3_maj_a_nb_c(Lo, R, r7 * mone + K);  // bit 7: R < centre - t
             }
-            const unsigned f = (any_run9(mb) | any_run9(md)) & 0x80808080u;
+            const unsigned fb = any_run9(mb) & 0x80808080u, f = fb | (any_run9(md) & 0x80808080u);
             // gather the four bit-7 flags into a nibble
             flags16 |= (((f >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
+            bright16 |= (((fb >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
         }
     }
     // only positions that can matter: inside the image interior +- 1 (the NMS halo)
@@ -583,18 +605,23 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         {
             const int bit = __ffs(f) - 1;
             f &= f - 1;
-            s_q[pos++] = (unsigned short)((4 * warp + (bit >> 2)) * FS_SW + 4 * lane + (bit & 3));
+            s_q[pos++] = (unsigned short)(((4 * warp + (bit >> 2)) * FS_SW + 4 * lane + (bit & 3)) | ((bright16 >> bit & 1u) << 12));
         }
     }
     __syncthreads();
 
     // ---- phase B: exact cornerScore of the queued corners ----
     const int nq = s_qn;
-    for(int j = tid; j < nq; j += 256)
+    for(int j = 2 * tid; j < nq; j += 512)
     {
-        const int i = s_q[j];
-        const int sy = i / FS_SW, sx = i - sy * FS_SW;
-        s_sc[sy][sx] = (uint8_t)corner_score(&s_px[sy + 3][sx + 4]);
+        const unsigned ea = s_q[j], eb = s_q[min(j + 1, nq - 1)];
+        const int ia = ea & 0xfff, ib = eb & 0xfff;
+        const int ya = ia / FS_SW, xa = ia - ya * FS_SW, yb = ib / FS_SW, xb = ib - yb * FS_SW;
+        const uint8_t* ta = (ea & 0x1000u) ? &s_pxc[0][0] : &s_px[0][0];
+        const uint8_t* tb = (eb & 0x1000u) ? &s_pxc[0][0] : &s_px[0][0];
+        const unsigned sc = corner_score2(ta + (ya + 3) * FS_PW + xa + 4, tb + (yb + 3) * FS_PW + xb + 4);
+        s_sc[ya][xa] = (uint8_t)(sc & 0xffu);
+        s_sc[yb][xb] = (uint8_t)(sc >> 16);
     }
     __syncthreads();
 
@@ -606,7 +633,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         unsigned rec = 0;
         if(j < nq)
         {
-            const int i = s_q[j];
+            const int i = s_q[j] & 0xfff;
             const int sy = i / FS_SW, sx = i - sy * FS_SW;
             const int x = sx0 + sx, y = sy0 + sy;
             if(sx >= 2 && sx < FS_SW - 2 && sy >= 1 && sy < FS_SH - 1 && x >= edge && x < L.w - edge && y < L.h - edge)
@@ -922,6 +949,12 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
     return a;
 }
 
+constexpr int OD_SLOTS = 32; // keypoints per CTA: 8 warps x 4 rounds
+
+// One CTA takes 32 consecutive output slots of one frame.  Phase 0: thread i finds (level, rank) of slot i.  Phase 1: a
+// warp per keypoint computes the intensity-centroid angle.  Phase 2: the 32 double-precision sincos of the CTA run in
+// the 32 lanes of ONE warp (as one warp-per-keypoint step they would cost every warp ~240 issue slots for a single
+// active lane).  Phase 3: a warp per keypoint evaluates the 256 rotated tests, lane i -> descriptor byte i.
 __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                          const uint8_t* __restrict__ blur,
                                                          const LevelCounters* __restrict__ ctr, const SelRec* __restrict__ sel,
@@ -929,35 +962,54 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
                                                          mslam_b200_keypoint* __restrict__ out_kp, uint8_t* __restrict__ out_desc,
                                                          int* __restrict__ out_counts, int out_cap)
 {
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
+    __shared__ int s_l[OD_SLOTS];
+    __shared__ unsigned s_yx[OD_SLOTS];
+    __shared__ float s_resp[OD_SLOTS], s_ang[OD_SLOTS], s_cos[OD_SLOTS], s_sin[OD_SLOTS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int b = blockIdx.y + P.frame0;
-    int base = 0, l = -1, r = 0;
-    for(int i = 0; i < P.nlevels; ++i)
+    const int slot0 = blockIdx.x * OD_SLOTS;
+    // ---- phase 0: slot -> (level, rank) ----
+    if(threadIdx.x < OD_SLOTS)
     {
-        const int c = min((int)ctr[(long long)b * P.nlevels + i].n_final, P.kp_cap);
-        if(l < 0 && slot < base + c)
+        const int slot = slot0 + threadIdx.x;
+        int base = 0, l = -1, r = 0;
+        for(int i = 0; i < P.nlevels; ++i)
         {
-            l = i;
-            r = slot - base;
+            const int c = min((int)ctr[(long long)b * P.nlevels + i].n_final, P.kp_cap);
+            if(l < 0 && slot < base + c)
+            {
+                l = i;
+                r = slot - base;
+            }
+            base += c;
         }
-        base += c;
+        if(slot == 0)
+            out_counts[b] = base;
+        if(slot >= out_cap)
+            l = -1;
+        s_l[threadIdx.x] = l;
+        if(l >= 0)
+        {
+            const SelRec rec = sel[((long long)b * P.nlevels + l) * P.kp_cap + r];
+            s_yx[threadIdx.x] = rec.yx_score;
+            s_resp[threadIdx.x] = rec.response;
+        }
     }
-    if(slot == 0 && lane == 0)
-        out_counts[b] = base;
-    if(l < 0 || slot >= out_cap)
-        return;
-    const LevelDesc& L = P.lv[l];
-    const SelRec rec = sel[((long long)b * P.nlevels + l) * P.kp_cap + r];
-    const int x = (rec.yx_score >> 8) & 0xfff, y = rec.yx_score >> 20;
-    const long long plane = L.img_off + (long long)b * L.img_frame_stride;
-    const int pitch = L.pitch;
-
-    // ---- intensity centroid: the warp walks the 31 rows of the disc, lane = column (coalesced 31-byte row reads) ----
-    int m10 = 0, m01 = 0;
+    __syncthreads();
+    // ---- phase 1: intensity centroid, the warp walks the 31 rows of the disc, lane = column ----
+#pragma unroll 1
+    for(int rnd = 0; rnd < OD_SLOTS / 8; ++rnd)
     {
+        const int s = rnd * 8 + warp;
+        const int l = s_l[s];
+        if(l < 0) // warp-uniform
+            continue;
+        const LevelDesc& L = P.lv[l];
+        const int x = (s_yx[s] >> 8) & 0xfff, y = s_yx[s] >> 20;
+        const int pitch = L.pitch;
         const int u = lane - 15, au = u < 0 ? -u : u;
-        const uint8_t* c = pyr + plane + (long long)y * pitch + x + u;
+        const uint8_t* c = pyr + L.img_off + (long long)b * L.img_frame_stride + (long long)y * pitch + x + u;
+        int m10 = 0, m01 = 0;
 #pragma unroll
         for(int v = -15; v <= 15; ++v)
         {
@@ -967,58 +1019,71 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
             m10 += u * val;
             m01 += v * val;
         }
-    }
 #pragma unroll
-    for(int o = 16; o > 0; o >>= 1)
-    {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        for(int o = 16; o > 0; o >>= 1)
+        {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        }
+        if(lane == 0)
+            s_ang[s] = fast_atan2_deg((float)m01, (float)m10);
     }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-    // ---- rotated BRIEF: lane i produces descriptor byte i ----
-    const float kx = __fmul_rn((float)x, L.scale), ky = __fmul_rn((float)y, L.scale);
-    const int cx = __float2int_rn(__fmul_rn(kx, L.inv_scale)), cy = __float2int_rn(__fmul_rn(ky, L.inv_scale));
-    float ca = 0.f, sa = 0.f;
-    if(lane == 0)
+    __syncthreads();
+    // ---- phase 2: (float)cos((double)a), (float)sin((double)a) of OpenCV, one keypoint per lane ----
+    if(warp == 0 && s_l[lane] >= 0)
     {
-        const float ang = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
+        const float ang = __fmul_rn(s_ang[lane], (float)(3.1415926535897932384626433832795 / 180.f));
         double sd, cd;
-        sincos((double)ang, &sd, &cd); // (float)cos((double)ang), (float)sin((double)ang) of OpenCV, one range reduction
-        ca = (float)cd;
-        sa = (float)sd;
+        sincos((double)ang, &sd, &cd);
+        s_cos[lane] = (float)cd;
+        s_sin[lane] = (float)sd;
     }
-    ca = __shfl_sync(0xffffffffu, ca, 0);
-    sa = __shfl_sync(0xffffffffu, sa, 0);
-    // cvRound(v) = low bits of (v + 1.5 * 2^23) - 0x4B400000 (round-to-nearest-even, |v| < 2^22); the two subtractions
-    // are folded into the base pointer:  iy * pitch + ix = by * pitch + bx - 0x4B400000 * (pitch + 1)  (mod 2^32)
-    const unsigned kfold = 0x4B400000u * (unsigned)(pitch + 1);
-    const uint8_t* centre = blur + plane + (long long)cy * pitch + cx;
-    unsigned byte = 0;
+    __syncthreads();
+    // ---- phase 3: rotated BRIEF, lane i produces descriptor byte i ----
+#pragma unroll 1
+    for(int rnd = 0; rnd < OD_SLOTS / 8; ++rnd)
+    {
+        const int s = rnd * 8 + warp;
+        const int l = s_l[s];
+        if(l < 0)
+            continue;
+        const int slot = slot0 + s;
+        const LevelDesc& L = P.lv[l];
+        const int x = (s_yx[s] >> 8) & 0xfff, y = s_yx[s] >> 20;
+        const int pitch = L.pitch;
+        const float ca = s_cos[s], sa = s_sin[s];
+        const float kx = __fmul_rn((float)x, L.scale), ky = __fmul_rn((float)y, L.scale);
+        const int cx = __float2int_rn(__fmul_rn(kx, L.inv_scale)), cy = __float2int_rn(__fmul_rn(ky, L.inv_scale));
+        // cvRound(v) = low bits of (v + 1.5 * 2^23) - 0x4B400000 (round-to-nearest-even, |v| < 2^22); the two subtractions
+        // are folded into the base pointer:  iy * pitch + ix = by * pitch + bx - 0x4B400000 * (pitch + 1)  (mod 2^32)
+        const unsigned kfold = 0x4B400000u * (unsigned)(pitch + 1);
+        const uint8_t* centre = blur + L.img_off + (long long)b * L.img_frame_stride + (long long)cy * pitch + cx;
+        unsigned byte = 0;
 #pragma unroll
-    for(int j = 0; j < 8; ++j)
-    {
-        const float4 t = __ldg(pat_t + j * 32 + lane); // test (lane * 8 + j): x0, y0, x1, y1
-        const unsigned bx0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.x, ca), __fmul_rn(t.y, sa)), 12582912.f));
-        const unsigned by0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.x, sa), __fmul_rn(t.y, ca)), 12582912.f));
-        const unsigned bx1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.z, ca), __fmul_rn(t.w, sa)), 12582912.f));
-        const unsigned by1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.z, sa), __fmul_rn(t.w, ca)), 12582912.f));
-        const int o0 = (int)(by0 * (unsigned)pitch + bx0 - kfold), o1 = (int)(by1 * (unsigned)pitch + bx1 - kfold);
-        const int v0 = __ldg(centre + o0);
-        const int v1 = __ldg(centre + o1);
-        byte |= (unsigned)(v0 < v1) << j;
-    }
-    out_desc[((long long)b * out_cap + slot) * 32 + lane] = (uint8_t)byte;
-    if(lane == 0)
-    {
-        mslam_b200_keypoint kp;
-        kp.x = kx;
-        kp.y = ky;
-        kp.size = __fmul_rn(31.f, L.scale);
-        kp.angle = angle;
-        kp.response = rec.response;
-        kp.octave = l;
-        out_kp[(long long)b * out_cap + slot] = kp;
+        for(int j = 0; j < 8; ++j)
+        {
+            const float4 t = __ldg(pat_t + j * 32 + lane); // test (lane * 8 + j): x0, y0, x1, y1
+            const unsigned bx0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.x, ca), __fmul_rn(t.y, sa)), 12582912.f));
+            const unsigned by0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.x, sa), __fmul_rn(t.y, ca)), 12582912.f));
+            const unsigned bx1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.z, ca), __fmul_rn(t.w, sa)), 12582912.f));
+            const unsigned by1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.z, sa), __fmul_rn(t.w, ca)), 12582912.f));
+            const int o0 = (int)(by0 * (unsigned)pitch + bx0 - kfold), o1 = (int)(by1 * (unsigned)pitch + bx1 - kfold);
+            const int v0 = __ldg(centre + o0);
+            const int v1 = __ldg(centre + o1);
+            byte |= (unsigned)(v0 < v1) << j;
+        }
+        out_desc[((long long)b * out_cap + slot) * 32 + lane] = (uint8_t)byte;
+        if(lane == 0)
+        {
+            mslam_b200_keypoint kp;
+            kp.x = kx;
+            kp.y = ky;
+            kp.size = __fmul_rn(31.f, L.scale);
+            kp.angle = s_ang[s];
+            kp.response = s_resp[s];
+            kp.octave = l;
+            out_kp[(long long)b * out_cap + slot] = kp;
+        }
     }
 }
 
@@ -1143,7 +1208,7 @@ void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* 
                             int out_cap, int n_slots, const PipeParams& P, long long* launches)
 {
     const int slots = n_slots < 1 ? 1 : n_slots;
-    k_orient_describe<<<dim3((slots + 7) / 8, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, pat_t, out_kp,
+    k_orient_describe<<<dim3((slots + OD_SLOTS - 1) / OD_SLOTS, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, pat_t, out_kp,
                                                                          out_desc, out_counts, out_cap);
     ++*launches;
 }
