@@ -58,6 +58,7 @@ struct mslam_b200_ctx
     uint8_t *d_mfrom = nullptr, *d_mto = nullptr, *d_raw = nullptr;
     int *d_nfrom = nullptr, *d_nto = nullptr;
     unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
+    unsigned *d_part0 = nullptr, *d_part1 = nullptr; // per-slice partial top-2 keys of the small-batch kNN
     int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
     int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
     // ---- copy engines of the host entry points (chunked H2D / compute / D2H pipeline) ----
@@ -390,7 +391,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat};
+                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat};
     for(void* p : dev)
         if(p)
             cudaFree(p);
@@ -539,6 +540,8 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaMalloc(&ctx->d_key1, B * dc * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_key0b, B * dc * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_key1b, B * dc * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_part0, kKnnMaxSlices * B * dc * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_part1, kKnnMaxSlices * B * dc * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_out_a, B * dc * sizeof(int)));
     CREATE_OK(cudaMalloc(&ctx->d_out_b, B * dc * sizeof(int)));
     CREATE_OK(cudaMalloc(&ctx->d_out_d, B * dc * sizeof(int)));
@@ -969,9 +972,9 @@ int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, const uint8_t* d_f
     // query = `to`, train = `from` (orb_feature.cpp:96)
     {
         StageTimer t(ctx, MSLAM_B200_T_KNN);
-        launch_knn2(st, d_to, d_n_to, d_from, d_n_from, n_pairs, capacity, ctx->d_key0, ctx->d_key1, ctx->sm_count, &ctx->launches);
+        launch_knn2(st, d_to, d_n_to, d_from, d_n_from, n_pairs, capacity, ctx->d_key0, ctx->d_key1, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
         if(mode == 1)
-            launch_knn2(st, d_from, d_n_from, d_to, d_n_to, n_pairs, capacity, ctx->d_key0b, ctx->d_key1b, ctx->sm_count, &ctx->launches);
+            launch_knn2(st, d_from, d_n_from, d_to, d_n_to, n_pairs, capacity, ctx->d_key0b, ctx->d_key1b, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
     }
     {
         StageTimer t(ctx, MSLAM_B200_T_COMPACT);
@@ -1116,7 +1119,7 @@ int mslam_b200_knn2(mslam_b200_ctx* ctx, const uint8_t* query, int n_query, int 
     if(rc)
         return rc;
     const int cap = ctx->desc_cap;
-    launch_knn2(st, ctx->d_mto, ctx->d_nto, ctx->d_mfrom, ctx->d_nfrom, 1, cap, ctx->d_key0, ctx->d_key1, ctx->sm_count, &ctx->launches);
+    launch_knn2(st, ctx->d_mto, ctx->d_nto, ctx->d_mfrom, ctx->d_nfrom, 1, cap, ctx->d_key0, ctx->d_key1, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
     // unpack into the four int scratch arrays (out_a, out_b, out_d, key0b reinterpreted)
     int* d_i1 = reinterpret_cast<int*>(ctx->d_key0b);
     launch_unpack_knn(st, ctx->d_key0, ctx->d_key1, n_query, ctx->d_out_a, ctx->d_out_d, d_i1, ctx->d_out_b, &ctx->launches);

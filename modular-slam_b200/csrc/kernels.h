@@ -23,8 +23,9 @@ void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* 
                             int out_cap, int n_slots, const PipeParams& P, long long* launches);
 void brief_pattern_transposed(float* out1024);
 // matching path
+constexpr int kKnnMaxSlices = 8; // train-set slices of the small-batch kNN (scratch: kKnnMaxSlices x [pair][cap] keys)
 void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
-                 unsigned* key0, unsigned* key1, int sm_count, long long* launches);
+                 unsigned* key0, unsigned* key1, unsigned* part0, unsigned* part1, int sm_count, long long* launches);
 void launch_ratio_compact(cudaStream_t st, const unsigned* key0, const unsigned* key1, const int* qn, const int* tn,
                           int n_pairs, int cap, double ratio, int* out_a, int* out_b, int* out_d, int* n_out,
                           long long* launches);

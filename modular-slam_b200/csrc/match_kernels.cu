@@ -5,6 +5,8 @@
 // -- per query the two smallest distances, ties to the lower train index (cv::batchDistance) -- then the
 // 0.7 ratio test (orb_feature.cpp:101) and {fromIndex = trainIdx, toIndex = queryIdx} in ascending toIndex
 // (orb_feature.cpp:110-114).  Everything here is XOR + POPC on the integer pipes; no tensor cores.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -58,9 +60,14 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint8_t* __restrict_
                                                       const uint8_t* __restrict__ t_base, const int* __restrict__ t_counts,
                                                       int cap, unsigned* __restrict__ key0, unsigned* __restrict__ key1)
 {
+    // blockIdx.z = slice of the train set (gridDim.z slices; partial top-2 lists are merged by k_merge_keys)
     __shared__ uint4 s_t[KNN_CHUNK * 2];
     const int p = blockIdx.y;
-    const int nq = min(q_counts[p], cap), nt = min(t_counts[p], cap);
+    const int nq = min(q_counts[p], cap), nt_all = min(t_counts[p], cap);
+    const int per = (nt_all + (int)gridDim.z - 1) / (int)gridDim.z;
+    const int t_begin = min((int)blockIdx.z * per, nt_all), nt = min(t_begin + per, nt_all);
+    key0 += (long long)blockIdx.z * gridDim.y * cap;
+    key1 += (long long)blockIdx.z * gridDim.y * cap;
     const int q0 = blockIdx.x * (KNN_THREADS * QPT);
     if(q0 >= nq)
         return;
@@ -77,7 +84,7 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint8_t* __restrict_
         k0[i] = kNoKey;
         k1[i] = kNoKey;
     }
-    for(int t0 = 0; t0 < nt; t0 += KNN_CHUNK)
+    for(int t0 = t_begin; t0 < nt; t0 += KNN_CHUNK)
     {
         const int nc = min(KNN_CHUNK, nt - t0);
         __syncthreads();
@@ -107,6 +114,27 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint8_t* __restrict_
             key1[(long long)p * cap + q] = k1[i];
         }
     }
+}
+
+// merge the per-slice top-2 lists ([slice][pair][cap]) into the final one: the two smallest of all 2 * slices keys
+__global__ void __launch_bounds__(256) k_merge_keys(const unsigned* __restrict__ part0, const unsigned* __restrict__ part1,
+                                                    int slices, long long n, unsigned* __restrict__ key0,
+                                                    unsigned* __restrict__ key1)
+{
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if(i >= n)
+        return;
+    unsigned a = kNoKey, b = kNoKey;
+    for(int s = 0; s < slices; ++s)
+    {
+        const unsigned x = part0[s * n + i], y = part1[s * n + i];
+        b = min(b, max(a, x));
+        a = min(a, x);
+        b = min(b, max(a, y));
+        a = min(a, y);
+    }
+    key0[i] = a;
+    key1[i] = b;
 }
 
 // block-wide exclusive scan of one flag per thread (256 threads); returns the offset, total in *total
@@ -456,16 +484,36 @@ __global__ void k_clock_probe(long long* out)
 // launchers
 // =================================================================================================
 void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
-                 unsigned* key0, unsigned* key1, int sm_count, long long* launches)
+                 unsigned* key0, unsigned* key1, unsigned* part0, unsigned* part1, int sm_count, long long* launches)
 {
-    // Work granularity: the kernel is compute-bound on the integer pipes, so what matters is an even split over the
-    // 148 SMs.  Few frame pairs -> 64 queries per CTA (many small CTAs, all co-resident, < 2 % imbalance at 64 pairs x
-    // 1000 queries); lots of work -> 256 queries per CTA (fewer shared-memory refills of the train set).
+    // Work granularity: the kernel is compute-bound on the integer pipes, so what matters is enough warps on every SM and
+    // an even split over the 148 SMs.  Few frame pairs -> 64 queries per CTA and the train set cut into slices (grid z)
+    // until there are ~50 warps per SM, partial top-2 lists merged by a second tiny kernel; lots of work -> 256 queries
+    // per CTA (fewer shared-memory refills of the train set), no slicing.
     const long long small_ctas = (long long)((cap + 63) / 64) * n_pairs;
     if(small_ctas <= 24LL * sm_count)
     {
-        dim3 grd((cap + 63) / 64, n_pairs);
-        k_knn2<1, 64><<<grd, 64, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+        static int forced = -1;
+        if(forced < 0)
+        {
+            const char* e = getenv("MSLAM_KNN_SLICES");
+            forced = e ? atoi(e) : 0;
+        }
+        int slices = 1;
+        while(slices < 4 && small_ctas * slices < 28LL * sm_count && cap / (slices * 2) >= 128)
+            slices *= 2;
+        if(forced > 0)
+            slices = forced < kKnnMaxSlices ? forced : kKnnMaxSlices;
+        dim3 grd((cap + 63) / 64, n_pairs, slices);
+        if(slices == 1)
+            k_knn2<1, 64><<<grd, 64, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+        else
+        {
+            k_knn2<1, 64><<<grd, 64, 0, st>>>(q, qn, t, tn, cap, part0, part1);
+            const long long n = (long long)n_pairs * cap;
+            k_merge_keys<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part0, part1, slices, n, key0, key1);
+            ++*launches;
+        }
     }
     else
     {
