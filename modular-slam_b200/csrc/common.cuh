@@ -38,6 +38,7 @@ struct PipeParams
     int frame0; // first frame (absolute index in the context's batch buffers) this launch covers; n_frames from there
     long long cand_frame_stride; // elements per frame in the candidate arrays
     int total_fast_tiles, pad1;
+    int blur_band;      // rows one warp of k_blur walks
     int one, minus_one; // +1 / -1 as run-time values (IMAD pipe steering in k_fast)
     LevelDesc lv[kMaxLevels];
 };

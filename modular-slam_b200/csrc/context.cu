@@ -228,6 +228,7 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
     P.fast_thr = cfg.fast_threshold;
     P.kp_cap = kp_cap;
     P.one = 1;
+    P.blur_band = blur_band_rows();
     P.minus_one = -1;
     int w[kMaxLevels], h[kMaxLevels], nl[kMaxLevels];
     float sc[kMaxLevels];

@@ -12,6 +12,7 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
                  long long* launches);
 void fast_tiles(int w, int h, int edge, int* tx, int* ty);
 void blur_warps(int w, int h, int* xblocks, int* warps);
+int blur_band_rows();
 void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCounters* ctr, unsigned* hist,
                  const PipeParams& P, int l_begin, int l_end, long long* launches);
 void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned* cand2, unsigned* keys, unsigned* keys2,

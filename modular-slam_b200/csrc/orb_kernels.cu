@@ -5,6 +5,8 @@
 // the arithmetic contract is restated next to every kernel.
 // All float stages use explicit round-to-nearest intrinsics so that nvcc can never contract them into
 // FMAs (the reference path is non-FMA float except the 7x7 blur, which is an explicit FMA chain).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -33,6 +35,21 @@ __device__ __forceinline__ unsigned gray_px(unsigned c0, unsigned c1, unsigned c
     return __float2uint_rz(v);
 }
 
+// exact u8 -> f32 without the XU pipe's I2F: 0x4B000000 | b is the float 8388608 + b
+__device__ __forceinline__ float byte_to_float(unsigned word, int i)
+{
+    return __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 + i)), 8388608.f);
+}
+
+// gray_px with the conversions kept off the XU pipe (I2F / F2I run at a quarter of the FMA rate and made the kernel
+// XU-bound): bytes enter through PRMT + FSUB, and the truncating cast is the low byte of (v + 2^23) rounded toward zero.
+__device__ __forceinline__ unsigned gray_px_fast(float c0, float c1, float c2)
+{
+    float v = __fadd_rn(__fadd_rn(__fmul_rn(0.299f, c0), __fmul_rn(0.587f, c1)), __fmul_rn(0.114f, c2));
+    v = v < 255.f ? v : 255.f;
+    return __float_as_uint(__fadd_rz(v, 8388608.f)); // bits 0..7 = (int)v for 0 <= v <= 255
+}
+
 // 16 pixels (48 B in, 16 B out) per thread with 128-bit accesses.  Requires W % 16 == 0.
 __global__ void __launch_bounds__(256) k_gray16(const uint8_t* __restrict__ bgr, long long in_fs, uint8_t* __restrict__ out,
                                                 long long out_fs, int pitch, int W, int H)
@@ -49,17 +66,15 @@ __global__ void __launch_bounds__(256) k_gray16(const uint8_t* __restrict__ bgr,
 #pragma unroll
     for(int q = 0; q < 4; ++q)
     {
-        unsigned r = 0;
+        unsigned g[4];
 #pragma unroll
         for(int i = 0; i < 4; ++i)
         {
             const int k = 3 * (q * 4 + i);
-            const unsigned c0 = (w[k >> 2] >> ((k & 3) * 8)) & 255u;
-            const unsigned c1 = (w[(k + 1) >> 2] >> (((k + 1) & 3) * 8)) & 255u;
-            const unsigned c2 = (w[(k + 2) >> 2] >> (((k + 2) & 3) * 8)) & 255u;
-            r |= gray_px(c0, c1, c2) << (8 * i);
+            g[i] = gray_px_fast(byte_to_float(w[k >> 2], k & 3), byte_to_float(w[(k + 1) >> 2], (k + 1) & 3),
+                                byte_to_float(w[(k + 2) >> 2], (k + 2) & 3));
         }
-        o[q] = r;
+        o[q] = __byte_perm(__byte_perm(g[0], g[1], 0x0040), __byte_perm(g[2], g[3], 0x0040), 0x5410);
     }
     uint8_t* dst = out + (long long)blockIdx.y * out_fs + (long long)y * pitch + c * 16;
     *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
@@ -237,13 +252,7 @@ __global__ void __launch_bounds__(256) k_resize_generic(const uint8_t* __restric
 //   row pass  acc = k0*p[x-3]; acc = fma(k_j, p[x-3+j], acc)  j = 1..6
 //   col pass  acc = k3*r[y];   acc = fma(k_{3+i}, r[y+i] + r[y-i], acc)  i = 1..3 ; out = sat_u8(rint(acc))
 // =================================================================================================
-constexpr int BT_W = 128, BT_H = 32; // one warp: 128 columns (4 per lane) x 32 rows
-
-// exact u8 -> f32 without the XU pipe's I2F: 0x4B000000 | b is the float 8388608 + b
-__device__ __forceinline__ float byte_to_float(unsigned word, int i)
-{
-    return __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 + i)), 8388608.f);
-}
+constexpr int BT_W = 128; // one warp: 128 columns (4 per lane) x PipeParams::blur_band rows
 
 // the three aligned words covering source pixels x-4 .. x+7 of one row.  The producers pad every pyramid row with its
 // reflect-101 columns w .. w+3, so only the left border needs care: for x = 0 pixels -3, -2, -1 are pixels 3, 2, 1.
@@ -256,13 +265,16 @@ __device__ __forceinline__ Row12 blur_load(const uint8_t* __restrict__ row, int 
     Row12 r;
     const unsigned* wp = reinterpret_cast<const unsigned*>(row + x);
     r.b = __ldg(wp), r.c = __ldg(wp + 1);
-    r.a = x > 0 ? __ldg(wp - 1) : __byte_perm(r.b, 0u, 0x1230);
-    return r;
+    r.a = __ldg(wp - (x > 0)); // x = 0: placeholder, blur_row4 reflects pixels 3, 2, 1 out of r.b when it consumes the row
+    return r;                  // (nothing may depend on a loaded value here: the loads are prefetches)
 }
 
 // row pass for the 4 pixels x .. x+3:  acc = k0 * p[x-3]; acc = fma(k_j, p[x-3+j], acc)
-__device__ __forceinline__ void blur_row4(const Row12& wd, float (&o)[4])
+__device__ __forceinline__ void blur_row4(const Row12& wd_in, bool left_edge, float (&o)[4])
 {
+    Row12 wd = wd_in;
+    if(left_edge)
+        wd.a = __byte_perm(wd.b, 0u, 0x1230);
     const float kk[7] = {__int_as_float(0x3d8fafb1), __int_as_float(0x3e06387e), __int_as_float(0x3e434a39),
                          __int_as_float(0x3e5d4ae0), __int_as_float(0x3e434a39), __int_as_float(0x3e06387e),
                          __int_as_float(0x3d8fafb1)};
@@ -302,13 +314,13 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
     const int band = wg / L.blur_xblocks, xb = wg - band * L.blur_xblocks;
     const int w = L.w, h = L.h, pitch = L.pitch;
     const int x = (xb * 32 + lane) * 4;
-    const int y0 = band * BT_H;
+    const int y0 = band * P.blur_band;
     if(x >= w || y0 >= h)
         return;
     const long long plane = L.img_off + (long long)(blockIdx.y + P.frame0) * L.img_frame_stride;
     const uint8_t* img = src + plane;
     uint8_t* out = dst + plane;
-    const int rows = min(BT_H, h - y0);
+    const int rows = min(P.blur_band, h - y0);
     float r[7][4];
     Row12 buf[7];
     {
@@ -321,7 +333,7 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
             buf[k] = blur_load(img + (long long)reflect101(y0 + 3 + k, h) * pitch, x);
 #pragma unroll
         for(int s = 0; s < 6; ++s)
-            blur_row4(pre[s], r[s]);
+            blur_row4(pre[s], x == 0, r[s]);
     }
     for(int i0 = 0; i0 < rows; i0 += 7)
     {
@@ -332,7 +344,7 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
             if(i < rows)
             {
                 // ring slot (k + j) % 7 holds source row y - 3 + j of output row y = y0 + i
-                blur_row4(buf[k], r[(k + 6) % 7]);
+                blur_row4(buf[k], x == 0, r[(k + 6) % 7]);
                 if(i + 7 < rows)
                     buf[k] = blur_load(img + (long long)reflect101(y0 + 3 + i + 7, h) * pitch, x);
                 unsigned bits[4];
@@ -695,23 +707,37 @@ __device__ __forceinline__ float funkey(unsigned k)
 
 __device__ float harris_response(const uint8_t* __restrict__ img, int pitch, int x, int y)
 {
-    int a = 0, b = 0, c = 0;
-    // rows y-4 .. y+4, columns x-4 .. x+4; three-row sliding window
-    int r0[9], r1[9], r2[9];
-    const uint8_t* p = img + (long long)(y - 4) * pitch + (x - 4);
+    // rows y-4 .. y+4, columns x-4 .. x+4.  All 27 aligned words of the window are requested before the first one is
+    // used (one exposed memory latency per keypoint instead of one per row), then a three-row sliding window.
+    const int off8 = ((x - 4) & 3) * 8;
+    const unsigned* p = reinterpret_cast<const unsigned*>(img + (long long)(y - 4) * pitch + ((x - 4) & ~3));
+    const int pw = pitch >> 2; // pitch is a multiple of 64
+    unsigned w[9][3];
 #pragma unroll
-    for(int j = 0; j < 9; ++j)
+    for(int r = 0; r < 9; ++r)
     {
-        r0[j] = __ldg(p + j);
-        r1[j] = __ldg(p + pitch + j);
+        w[r][0] = __ldg(p + r * pw);
+        w[r][1] = __ldg(p + r * pw + 1);
+        w[r][2] = __ldg(p + r * pw + 2);
     }
+    int a = 0, b = 0, c = 0;
+    int r0[9], r1[9], r2[9];
+    auto unpack = [&](int r, int (&o)[9]) {
+        const unsigned v0 = __funnelshift_r(w[r][0], w[r][1], off8), v1 = __funnelshift_r(w[r][1], w[r][2], off8);
+#pragma unroll
+        for(int j = 0; j < 4; ++j)
+        {
+            o[j] = (int)((v0 >> (8 * j)) & 255u);
+            o[4 + j] = (int)((v1 >> (8 * j)) & 255u);
+        }
+        o[8] = (int)((w[r][2] >> off8) & 255u);
+    };
+    unpack(0, r0);
+    unpack(1, r1);
 #pragma unroll
     for(int row = 0; row < 7; ++row)
     {
-        const uint8_t* q = p + (long long)(row + 2) * pitch;
-#pragma unroll
-        for(int j = 0; j < 9; ++j)
-            r2[j] = __ldg(q + j);
+        unpack(row + 2, r2);
 #pragma unroll
         for(int j = 1; j < 8; ++j)
         {
@@ -1153,8 +1179,22 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
     }
 }
 
+int blur_band_rows()
+{
+    static int band = 0;
+    if(band == 0)
+    {
+        const char* e = getenv("MSLAM_BLUR_BAND");
+        band = e ? atoi(e) : 32;
+        if(band < 7)
+            band = 32;
+    }
+    return band;
+}
+
 void blur_warps(int w, int h, int* xblocks, int* warps)
 {
+    const int BT_H = blur_band_rows();
     *xblocks = (w + BT_W - 1) / BT_W;
     *warps = *xblocks * ((h + BT_H - 1) / BT_H);
 }
@@ -1165,7 +1205,7 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
 {
     int warps = 0;
     for(int l = l_begin; l < l_end; ++l)
-        warps += P.lv[l].blur_xblocks * ((P.lv[l].h + BT_H - 1) / BT_H);
+        warps += P.lv[l].blur_xblocks * ((P.lv[l].h + P.blur_band - 1) / P.blur_band);
     if(warps <= 0)
         return;
     k_blur<<<dim3((warps + 3) / 4, P.n_frames), 128, 0, st>>>(P, l_begin, l_end, pyr, blur);
