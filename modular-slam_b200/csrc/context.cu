@@ -646,7 +646,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         {
             StageTimer t(ctx, MSLAM_B200_T_SELECT);
             launch_select(st, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
-                          ctx->d_sel, ctx->d_err, P, &ctx->launches);
+                          ctx->d_sel, ctx->d_err, P, ctx->sm_count, &ctx->launches);
         }
         {
             StageTimer t(ctx, MSLAM_B200_T_BLUR);
@@ -695,7 +695,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         {
             StageTimer t(ctx, MSLAM_B200_T_SELECT, s_fast);
             launch_select(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
-                          ctx->d_sel, ctx->d_err, P, &ctx->launches);
+                          ctx->d_sel, ctx->d_err, P, ctx->sm_count, &ctx->launches);
         }
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[0], s_fast));
         for(int l = 0; l < l_split; ++l)

@@ -16,7 +16,7 @@ int blur_band_rows();
 void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCounters* ctr, unsigned* hist,
                  const PipeParams& P, int l_begin, int l_end, long long* launches);
 void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned* cand2, unsigned* keys, unsigned* keys2,
-                   LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P,
+                   LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P, int sm_count,
                    long long* launches);
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
                             const SelRec* sel, const float4* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc,

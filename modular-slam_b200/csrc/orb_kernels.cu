@@ -762,12 +762,12 @@ __device__ float harris_response(const uint8_t* __restrict__ img, int pitch, int
     return __fmul_rn(t, s4);
 }
 
-constexpr int SEL_THREADS = 256;
 constexpr int SEL_RANK_SMEM = 2048; // final (y, x) ranking runs out of shared memory up to this many survivors
 
 // Block-wide "k-th largest bin" over a 256-bin histogram, one bin per thread (bin = tid):
 //   S[v] = sum of bins >= v.  The unique v with S[v] >= k > S[v + 1] is written to *s_thr and k - S[v + 1] to *s_k.
-// Requires 1 <= k <= S[0].  Two barriers; replaces a 256-step serial walk by one thread.
+// Requires 1 <= k <= S[0].  Two barriers; replaces a 256-step serial walk by one thread.  The CTA may have more than
+// 256 threads: the extra warps pass hval = 0 and only meet the barriers.
 __device__ __forceinline__ void suffix_select(unsigned hval, unsigned k, unsigned* s_w /* 8 */, unsigned* s_thr, unsigned* s_k)
 {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -779,14 +779,14 @@ __device__ __forceinline__ void suffix_select(unsigned hval, unsigned k, unsigne
         if(lane + o < 32)
             sfx += t;
     }
-    if(lane == 0)
+    if(lane == 0 && wid < 8)
         s_w[wid] = sfx;
     __syncthreads();
 #pragma unroll
     for(int w = 1; w < 8; ++w)
         sfx += (w > wid) ? s_w[w] : 0u;
     const unsigned next = sfx - hval;
-    if(sfx >= k && next < k)
+    if(tid < 256 && sfx >= k && next < k)
     {
         *s_thr = (unsigned)tid;
         *s_k = k - next;
@@ -794,6 +794,7 @@ __device__ __forceinline__ void suffix_select(unsigned hval, unsigned k, unsigne
     __syncthreads();
 }
 
+template <int SEL_THREADS>
 __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                         unsigned* __restrict__ cand, unsigned* __restrict__ cand2,
                                                         unsigned* __restrict__ keys, unsigned* __restrict__ keys2,
@@ -830,7 +831,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
         else
         {
             // the histogram counts every NMS survivor (>= n > kcut1 entries), so the k-th largest exists
-            suffix_select(hist[((long long)b * P.nlevels + l) * 256 + tid], kcut1, s_w, &s_thr, &s_k);
+            suffix_select(tid < 256 ? hist[((long long)b * P.nlevels + l) * 256 + tid] : 0u, kcut1, s_w, &s_thr, &s_k);
             thr1 = s_thr;
         }
     }
@@ -866,7 +867,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
             unsigned prefix = 0, mask = 0, krem = kcut2;
             for(int shift = 24; shift >= 0; shift -= 8)
             {
-                s_hist[tid] = 0;
+                if(tid < 256)
+                    s_hist[tid] = 0;
                 __syncthreads();
                 for(unsigned i = tid; i < m; i += SEL_THREADS)
                 {
@@ -876,7 +878,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
                 }
                 __syncthreads();
                 // by induction at least krem keys carry the current prefix, so the digit exists
-                suffix_select(s_hist[tid], krem, s_w, &s_thr, &s_k);
+                suffix_select(tid < 256 ? s_hist[tid] : 0u, krem, s_w, &s_thr, &s_k);
                 prefix |= s_thr << shift;
                 mask |= 255u << shift;
                 krem = s_k;
@@ -1236,10 +1238,14 @@ void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCount
 }
 
 void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned* cand2, unsigned* keys, unsigned* keys2,
-                   LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P,
+                   LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P, int sm_count,
                    long long* launches)
 {
-    k_select<<<dim3(P.nlevels, P.n_frames), SEL_THREADS, 0, st>>>(P, pyr, cand, cand2, keys, keys2, ctr, hist, sel, err);
+    // one CTA per (frame, level): with few of them the longest one (level 0) is the critical path, so it gets 1024 threads
+    if((long long)P.nlevels * P.n_frames <= 2LL * sm_count)
+        k_select<1024><<<dim3(P.nlevels, P.n_frames), 1024, 0, st>>>(P, pyr, cand, cand2, keys, keys2, ctr, hist, sel, err);
+    else
+        k_select<256><<<dim3(P.nlevels, P.n_frames), 256, 0, st>>>(P, pyr, cand, cand2, keys, keys2, ctr, hist, sel, err);
     ++*launches;
 }
 
