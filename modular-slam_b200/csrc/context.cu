@@ -50,6 +50,7 @@ struct mslam_b200_ctx
     uint8_t* d_desc = nullptr;
     int* d_counts = nullptr;
     float4* d_pat = nullptr; // rBRIEF pattern as floats, transposed (256 x float4)
+    uint2* d_icw = nullptr;  // intensity-centroid byte weights (ic_weight_table)
     // ---- pinned host staging ----
     int* h_counts = nullptr;
     int* h_err = nullptr;
@@ -392,7 +393,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat};
+                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw};
     for(void* p : dev)
         if(p)
             cudaFree(p);
@@ -527,6 +528,10 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
         brief_pattern_transposed(pat);
         CREATE_OK(cudaMalloc(&ctx->d_pat, sizeof(pat)));
         CREATE_OK(cudaMemcpy(ctx->d_pat, pat, sizeof(pat), cudaMemcpyHostToDevice));
+        std::vector<unsigned> icw(4 * 31 * 9 * 2);
+        ic_weight_table(icw.data());
+        CREATE_OK(cudaMalloc(&ctx->d_icw, icw.size() * sizeof(unsigned)));
+        CREATE_OK(cudaMemcpy(ctx->d_icw, icw.data(), icw.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
     }
     CREATE_OK(cudaHostAlloc(&ctx->h_counts, B * sizeof(int), cudaHostAllocDefault));
     CREATE_OK(cudaHostAlloc(&ctx->h_err, B * sizeof(int), cudaHostAllocDefault));
@@ -653,7 +658,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
             launch_blur(st, ctx->d_pyr, ctx->d_blur, P, 0, P.nlevels, &ctx->launches);
         }
         StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
-        launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, d_kp, d_desc, d_counts, capacity,
+        launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_icw, d_kp, d_desc, d_counts, capacity,
                                n_slots, P, &ctx->launches);
     }
     else
@@ -714,7 +719,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[0], 0));
         MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[1], 0));
         StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
-        launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, d_kp, d_desc, d_counts, capacity,
+        launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_icw, d_kp, d_desc, d_counts, capacity,
                                n_slots, P, &ctx->launches);
     }
     MSLAM_CUDA_OK(cudaGetLastError());
@@ -871,7 +876,7 @@ int mslam_b200_describe(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int 
     ctx->P.frame0 = 0;
     run_pyramid(ctx, ctx->d_bgr, 1);
     launch_blur(st, ctx->d_pyr, ctx->d_blur, ctx->P, 0, ctx->P.nlevels, &ctx->launches);
-    launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,
+    launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_icw, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,
                            std::max(n_kp, 1), ctx->P, &ctx->launches);
     std::vector<mslam_b200_keypoint> hk((size_t)std::max(n_kp, 1));
     std::vector<uint8_t> hd((size_t)std::max(n_kp, 1) * 32);

@@ -19,9 +19,9 @@ void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned
                    LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P, int sm_count,
                    long long* launches);
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
-                            const SelRec* sel, const float4* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc,
-                            int* out_counts,
-                            int out_cap, int n_slots, const PipeParams& P, long long* launches);
+                            const SelRec* sel, const float4* pat_t, const uint2* ic_w, mslam_b200_keypoint* out_kp,
+                            uint8_t* out_desc, int* out_counts, int out_cap, int n_slots, const PipeParams& P, long long* launches);
+void ic_weight_table(unsigned* out /* 4 * 31 * 9 * 2 */);
 void brief_pattern_transposed(float* out1024);
 // matching path
 constexpr int kKnnMaxSlices = 8; // train-set slices of the small-batch kNN (scratch: kKnnMaxSlices x [pair][cap] keys)

@@ -978,6 +978,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 }
 
 constexpr int OD_SLOTS = 32; // keypoints per CTA: 8 warps x 4 rounds
+constexpr int IC_WORDS = 31 * 9; // aligned words covering the 31 x 31 orientation patch (any alignment)
 
 // One CTA takes 32 consecutive output slots of one frame.  Phase 0: thread i finds (level, rank) of slot i.  Phase 1: a
 // warp per keypoint computes the intensity-centroid angle.  Phase 2: the 32 double-precision sincos of the CTA run in
@@ -986,7 +987,7 @@ constexpr int OD_SLOTS = 32; // keypoints per CTA: 8 warps x 4 rounds
 __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                          const uint8_t* __restrict__ blur,
                                                          const LevelCounters* __restrict__ ctr, const SelRec* __restrict__ sel,
-                                                         const float4* __restrict__ pat_t,
+                                                         const float4* __restrict__ pat_t, const uint2* __restrict__ ic_w,
                                                          mslam_b200_keypoint* __restrict__ out_kp, uint8_t* __restrict__ out_desc,
                                                          int* __restrict__ out_counts, int out_cap)
 {
@@ -1024,7 +1025,10 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
         }
     }
     __syncthreads();
-    // ---- phase 1: intensity centroid, the warp walks the 31 rows of the disc, lane = column ----
+    // ---- phase 1: intensity centroid.  The 31 x 31 disc is read as 31 rows x 9 ALIGNED words (279 words, lane i takes
+    // words i, i + 32, ...); every word meets two packed signed-byte weight words -- u * inside(u, v) and
+    // v * inside(u, v) for its four columns, tabulated per alignment of the patch -- in two IDP.4A instructions:
+    // m10 += sum u * I, m01 += sum v * I.  9 word loads per lane instead of 31 predicated byte loads.
 #pragma unroll 1
     for(int rnd = 0; rnd < OD_SLOTS / 8; ++rnd)
     {
@@ -1035,17 +1039,22 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
         const LevelDesc& L = P.lv[l];
         const int x = (s_yx[s] >> 8) & 0xfff, y = s_yx[s] >> 20;
         const int pitch = L.pitch;
-        const int u = lane - 15, au = u < 0 ? -u : u;
-        const uint8_t* c = pyr + L.img_off + (long long)b * L.img_frame_stride + (long long)y * pitch + x + u;
+        const int al = (x - 15) & 3;
+        const uint8_t* base = pyr + L.img_off + (long long)b * L.img_frame_stride + (long long)(y - 15) * pitch + ((x - 15) & ~3);
+        const uint2* wtab = ic_w + al * IC_WORDS;
         int m10 = 0, m01 = 0;
 #pragma unroll
-        for(int v = -15; v <= 15; ++v)
+        for(int it = 0; it < (IC_WORDS + 31) / 32; ++it)
         {
-            const int av = v < 0 ? -v : v;
-            const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * av)) & 15ull); // u_max[|v|]
-            const int val = (lane < 31 && au <= d) ? (int)__ldg(c + v * pitch) : 0;
-            m10 += u * val;
-            m01 += v * val;
+            const int i = lane + 32 * it;
+            if(i < IC_WORDS)
+            {
+                const int r = i / 9, k = i - 9 * r;
+                const unsigned word = __ldg(reinterpret_cast<const unsigned*>(base + r * pitch) + k);
+                const uint2 wgt = __ldg(wtab + i);
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(word), "r"(wgt.x));
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m01) : "r"(word), "r"(wgt.y));
+            }
         }
 #pragma unroll
         for(int o = 16; o > 0; o >>= 1)
@@ -1113,6 +1122,32 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
             out_kp[(long long)b * out_cap + slot] = kp;
         }
     }
+}
+
+// intensity-centroid weights: for alignment a = (x - 15) & 3, word (row r, k) of the aligned window holds columns
+// u = 4k + j - a - 15 (j = byte) of row v = r - 15; weight bytes are u resp. v inside the radius-15 disc
+// (|u| <= u_max[|v|], OpenCV's umax table), 0 outside.  out: 4 * IC_WORDS * {wu, wv}.
+void ic_weight_table(unsigned* out)
+{
+    static const int umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+    for(int a = 0; a < 4; ++a)
+        for(int r = 0; r < 31; ++r)
+            for(int k = 0; k < 9; ++k)
+            {
+                unsigned wu = 0, wv = 0;
+                const int v = r - 15, av = v < 0 ? -v : v;
+                for(int j = 0; j < 4; ++j)
+                {
+                    const int u = 4 * k + j - a - 15, au = u < 0 ? -u : u;
+                    if(au <= umax[av])
+                    {
+                        wu |= (unsigned)(u & 0xff) << (8 * j);
+                        wv |= (unsigned)(v & 0xff) << (8 * j);
+                    }
+                }
+                out[((a * 31 + r) * 9 + k) * 2] = wu;
+                out[((a * 31 + r) * 9 + k) * 2 + 1] = wv;
+            }
 }
 
 // rBRIEF pattern as floats, transposed for the warp-per-keypoint kernel: entry j * 32 + lane = test lane * 8 + j
@@ -1250,11 +1285,11 @@ void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned
 }
 
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
-                            const SelRec* sel, const float4* pat_t, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int* out_counts,
-                            int out_cap, int n_slots, const PipeParams& P, long long* launches)
+                            const SelRec* sel, const float4* pat_t, const uint2* ic_w, mslam_b200_keypoint* out_kp,
+                            uint8_t* out_desc, int* out_counts, int out_cap, int n_slots, const PipeParams& P, long long* launches)
 {
     const int slots = n_slots < 1 ? 1 : n_slots;
-    k_orient_describe<<<dim3((slots + OD_SLOTS - 1) / OD_SLOTS, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, pat_t, out_kp,
+    k_orient_describe<<<dim3((slots + OD_SLOTS - 1) / OD_SLOTS, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, pat_t, ic_w, out_kp,
                                                                          out_desc, out_counts, out_cap);
     ++*launches;
 }
