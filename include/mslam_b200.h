@@ -181,6 +181,31 @@ MSLAM_B200_API int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queri
                                        int n_keyframes, int k_cap, int id_base, int k, int* out_score, int* out_id,
                                        int* out_all_scores /* may be NULL; [n_query_frames][n_keyframes] */);
 
+/* ---- RGB-D association: SURVEY 8(f) row f2 ------------------------------------------------------------------------ */
+/* Replaces pointsFromRgbdKeypoints / reconstructPoint (src/lib/modular_slam/rgbd_feature_frontend.cpp:101-138) with
+ * getDepth / isDepthValid (include/modular_slam/types/depth_frame.hpp:20-30), the step RgbdFeatureFrontend::track runs
+ * on the matcher's output (rgbd_feature_frontend.cpp:292-293).  CameraParameters (sensors/camera_parameters.hpp:7-12). */
+typedef struct mslam_b200_camera
+{
+    double cx, cy;  /* principalPoint */
+    double fx, fy;  /* focal */
+    float factor;   /* depth unit -> metres */
+    int reserved;
+} mslam_b200_camera;
+/* Device variant, batched: kp [n_pairs][kp_cap] as detect wrote them; d_index [n_pairs][cap] picks keypoints (e.g. the
+ * fromIndex list of match_batch_dev; NULL = identity), d_counts [n_pairs]; depth [n_pairs][height][width] u16.
+ * Outputs d_xyz [n_pairs][cap][3] double (camera frame) and d_valid [n_pairs][cap] (0 where the reference returns
+ * std::nullopt: depth <= FLT_EPSILON; also 0 for a pixel outside the frame, where the reference reads out of bounds). */
+MSLAM_B200_API int mslam_b200_backproject_dev(mslam_b200_ctx* ctx, const mslam_b200_keypoint* d_kp, int kp_cap,
+                                              const int* d_index, const int* d_counts, int n_pairs, int cap,
+                                              const uint16_t* d_depth, int width, int height, const mslam_b200_camera* cam,
+                                              double* d_xyz, uint8_t* d_valid);
+/* Host variant, one frame: xy = &keypoints[0].keypoint.coordinates (two doubles, stride_bytes = sizeof(OrbKeypoint) = 64
+ * for the reference's records); DepthFrame::data in `depth`.  out_xyz [n][3], out_valid [n]. */
+MSLAM_B200_API int mslam_b200_backproject(mslam_b200_ctx* ctx, const double* xy, int n, int stride_bytes,
+                                          const uint16_t* depth, int width, int height, const mslam_b200_camera* cam,
+                                          double* out_xyz, uint8_t* out_valid);
+
 /* ---- measurement / parity aids ------------------------------------------------------------------------------- */
 typedef enum mslam_b200_stage
 {

@@ -29,6 +29,12 @@ class Config(C.Structure):
 FLAG_SERIAL = 1
 
 
+class Camera(C.Structure):
+    """mslam_b200_camera == mslam::CameraParameters (sensors/camera_parameters.hpp:7-12)"""
+    _fields_ = [("cx", C.c_double), ("cy", C.c_double), ("fx", C.c_double), ("fy", C.c_double), ("factor", C.c_float),
+                ("reserved", C.c_int)]
+
+
 class MslamB200Error(RuntimeError):
     def __init__(self, status, what, detail=""):
         self.status = status
@@ -316,6 +322,26 @@ class Context:
     def db_merge_topk_dev(self, d_scores, d_ids, n_lists, n_q, k, d_out_score, d_out_id):
         self._chk(library().mslam_b200_db_merge_topk_dev(self._h, _ptr(d_scores), _ptr(d_ids), n_lists, n_q, k,
                                                          _ptr(d_out_score), _ptr(d_out_id)), "db_merge_topk_dev")
+
+    # -- RGB-D association -----------------------------------------------------------------------------
+    def backproject(self, xy, depth, camera):
+        """pointsFromRgbdKeypoints: xy [n, 2] float64 rows (any row stride that is a multiple of 8), depth [H, W] u16
+        -> (xyz [n, 3] f64, valid [n] u8)"""
+        xy = np.asarray(xy, np.float64)
+        assert xy.ndim == 2 and xy.shape[1] == 2 and (xy.shape[0] == 0 or xy.strides[1] == 8)
+        depth = np.ascontiguousarray(depth, np.uint16)
+        n = xy.shape[0]
+        xyz = np.zeros((n, 3), np.float64)
+        valid = np.zeros(n, np.uint8)
+        self._chk(library().mslam_b200_backproject(self._h, _ptr(xy) if n else None, n, xy.strides[0] if n else 16, _ptr(depth),
+                                                   depth.shape[1], depth.shape[0], C.byref(camera), _ptr(xyz), _ptr(valid)),
+                  "backproject")
+        return xyz, valid
+
+    def backproject_dev(self, d_kp, kp_cap, d_index, d_counts, n_pairs, cap, d_depth, width, height, camera, d_xyz, d_valid):
+        self._chk(library().mslam_b200_backproject_dev(self._h, _ptr(d_kp), kp_cap, _ptr(d_index), _ptr(d_counts), n_pairs,
+                                                       cap, _ptr(d_depth), width, height, C.byref(camera), _ptr(d_xyz),
+                                                       _ptr(d_valid)), "backproject_dev")
 
     # -- measurement ------------------------------------------------------------------------------------------------------
     STAGES = ("gray", "resize", "fast", "select", "blur", "describe", "knn", "compact", "db")

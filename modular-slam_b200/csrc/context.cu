@@ -1220,6 +1220,66 @@ int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queries, const int* 
     return rc;
 }
 
+// ---- RGB-D association ------------------------------------------------------------------------------
+static bool camera_ok(const mslam_b200_camera* cam)
+{
+    return cam && cam->fx != 0.0 && cam->fy != 0.0;
+}
+
+int mslam_b200_backproject_dev(mslam_b200_ctx* ctx, const mslam_b200_keypoint* d_kp, int kp_cap, const int* d_index,
+                               const int* d_counts, int n_pairs, int cap, const uint16_t* d_depth, int width, int height,
+                               const mslam_b200_camera* cam, double* d_xyz, uint8_t* d_valid)
+{
+    if(!ctx || !d_kp || !d_counts || !d_depth || !d_xyz || !d_valid || !camera_ok(cam) || kp_cap < 1 || n_pairs < 1 ||
+       n_pairs > 65535 || cap < 1 || width < 1 || height < 1)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    launch_backproject(ctx->stream, d_kp, kp_cap, d_index, d_counts, n_pairs, cap, d_depth, width, height, *cam, d_xyz, d_valid,
+                       &ctx->launches);
+    MSLAM_CUDA_OK(cudaGetLastError());
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_backproject(mslam_b200_ctx* ctx, const double* xy, int n, int stride_bytes, const uint16_t* depth, int width,
+                           int height, const mslam_b200_camera* cam, double* out_xyz, uint8_t* out_valid)
+{
+    if(!ctx || n < 0 || !camera_ok(cam) || width < 1 || height < 1 || stride_bytes < 16 || (stride_bytes & 7))
+        return MSLAM_B200_E_INVALID;
+    if(n == 0)
+        return MSLAM_B200_OK;
+    if(!xy || !depth || !out_xyz || !out_valid)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    double *d_xy = nullptr, *d_xyz = nullptr;
+    uint16_t* d_depth = nullptr;
+    uint8_t* d_valid = nullptr;
+    const size_t depth_bytes = (size_t)width * height * sizeof(uint16_t);
+    int rc = MSLAM_B200_OK;
+    cudaError_t e;
+#define BPQ(expr)                                                                                                      \
+    if(rc == MSLAM_B200_OK && (e = (expr)) != cudaSuccess)                                                             \
+    rc = ctx_fail(ctx, e, #expr)
+    BPQ(cudaMalloc(&d_xy, (size_t)n * 16));
+    BPQ(cudaMalloc(&d_xyz, (size_t)n * 24));
+    BPQ(cudaMalloc(&d_depth, depth_bytes));
+    BPQ(cudaMalloc(&d_valid, (size_t)n));
+    BPQ(cudaMemcpy2DAsync(d_xy, 16, xy, (size_t)stride_bytes, 16, (size_t)n, cudaMemcpyHostToDevice, st));
+    BPQ(cudaMemcpyAsync(d_depth, depth, depth_bytes, cudaMemcpyHostToDevice, st));
+    if(rc == MSLAM_B200_OK)
+        launch_backproject_xy(st, d_xy, n, d_depth, width, height, *cam, d_xyz, d_valid, &ctx->launches);
+    BPQ(cudaGetLastError());
+    BPQ(cudaMemcpyAsync(out_xyz, d_xyz, (size_t)n * 24, cudaMemcpyDeviceToHost, st));
+    BPQ(cudaMemcpyAsync(out_valid, d_valid, (size_t)n, cudaMemcpyDeviceToHost, st));
+    BPQ(cudaStreamSynchronize(st));
+#undef BPQ
+    void* frees[] = {d_xy, d_xyz, d_depth, d_valid};
+    for(void* p : frees)
+        if(p)
+            cudaFree(p);
+    return rc;
+}
+
 int mslam_b200_enable_stage_timing(mslam_b200_ctx* ctx, int enable)
 {
     if(!ctx)

@@ -39,5 +39,11 @@ cudaError_t launch_db_scores(cudaStream_t st, const uint8_t* queries, const int*
                              int sm_count, long long* launches);
 void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists, int per_list, int n_queries, int id_base,
                  int k, int* out_score, int* out_id, long long* launches);
+// RGB-D association (rgbd_kernels.cu)
+void launch_backproject(cudaStream_t st, const mslam_b200_keypoint* kp, int kp_cap, const int* index, const int* counts,
+                        int n_pairs, int cap, const uint16_t* depth, int width, int height, const mslam_b200_camera& cam,
+                        double* xyz, uint8_t* valid, long long* launches);
+void launch_backproject_xy(cudaStream_t st, const double* xy, int n, const uint16_t* depth, int width, int height,
+                           const mslam_b200_camera& cam, double* xyz, uint8_t* valid, long long* launches);
 cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long long* launches);
 } // namespace mslam_b200

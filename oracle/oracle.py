@@ -267,3 +267,22 @@ def match_ratio_batch(frm, nfrom, to, nto, nthreads=1):
     cnt = np.zeros(P, np.int32)
     lib().orc_match_ratio_batch(_p(frm), _p(nf), _p(to), _p(nt), P, cap, _p(fi), _p(ti), _p(di), _p(cnt), nthreads)
     return fi, ti, di, cnt
+
+
+# TUM intrinsics the reference's file provider hard-codes (rgbd_file_provider.cpp:140-142)
+TUM_CAMERA = dict(cx=319.5, cy=239.5, fx=525.0, fy=525.0, factor=np.float32(1.0) / np.float32(5000.0))
+
+
+def backproject(xy, depth, cx, cy, fx, fy, factor):
+    """pointsFromRgbdKeypoints: xy [n, 2] float64 (any row stride), depth [H, W] uint16 -> (xyz [n, 3] f64, valid [n] u8)"""
+    xy = np.asarray(xy, np.float64)
+    assert xy.ndim == 2 and xy.shape[1] == 2 and (xy.shape[0] == 0 or xy.strides[1] == 8)
+    depth = np.ascontiguousarray(depth, np.uint16)
+    n = xy.shape[0]
+    xyz = np.zeros((max(n, 1), 3), np.float64)
+    valid = np.zeros(max(n, 1), np.uint8)
+    if n:
+        lib().orc_backproject(C.c_void_p(xy.ctypes.data), n, xy.strides[0], _p(depth), depth.shape[1], depth.shape[0],
+                              C.c_double(cx), C.c_double(cy), C.c_double(fx), C.c_double(fy), C.c_float(factor), _p(xyz),
+                              _p(valid))
+    return xyz[:n], valid[:n]

@@ -732,3 +732,37 @@ ORC_API void orc_match_ratio_batch(const uint8_t* from, const int* nfrom, const 
         counts[p] = orc_match_ratio(from + (size_t)p * cap * 32, nfrom[p], 32, to + (size_t)p * cap * 32, nto[p], 32, 0.7,
                                     from_idx + (size_t)p * cap, to_idx + (size_t)p * cap, dist + (size_t)p * cap);
 }
+
+/* ---- depth back-projection ---------------------------------------------------------------------
+ * pointsFromRgbdKeypoints / reconstructPoint (src/lib/modular_slam/rgbd_feature_frontend.cpp:101-138) with getDepth /
+ * isDepthValid (include/modular_slam/types/depth_frame.hpp:20-30):
+ *   imgPoint = coordinates.cast<int>()  (truncation);  depth = (float)data[w * y + x] * factor  (one f32 product);
+ *   nullopt unless depth > FLT_EPSILON;  z = depth;  x = (u - cx) * z * (1.0 / fx),  y likewise -- IEEE double, left to
+ *   right, no FMA (this file is compiled with -ffp-contract=off).  xy: n records of two doubles, stride in bytes.
+ * Parity unpinned: the reference holds no golden vector for this step and cannot be built here; the arithmetic is
+ * restated from the lines cited. */
+ORC_API void orc_backproject(const uint8_t* xy, int n, int stride_bytes, const uint16_t* depth, int width, int height,
+                             double cx, double cy, double fx, double fy, float factor, double* out_xyz, uint8_t* out_valid)
+{
+    const double inv_fx = 1.0 / fx, inv_fy = 1.0 / fy;
+    for(int i = 0; i < n; ++i)
+    {
+        const double* c = (const double*)(xy + (size_t)i * stride_bytes);
+        const double u = c[0], v = c[1];
+        out_xyz[3 * i] = out_xyz[3 * i + 1] = out_xyz[3 * i + 2] = 0.0;
+        out_valid[i] = 0;
+        if(!(u > -2147483648.0 && u < 2147483647.0 && v > -2147483648.0 && v < 2147483647.0))
+            continue;
+        const int xi = (int)u, yi = (int)v;
+        if(xi < 0 || yi < 0 || xi >= width || yi >= height)
+            continue; /* the reference reads out of bounds here */
+        const float d = (float)(int)depth[(size_t)width * yi + xi] * factor;
+        if(!(d > 1.1920928955078125e-07f))
+            continue;
+        const double z = (double)d;
+        out_xyz[3 * i] = (u - cx) * z * inv_fx;
+        out_xyz[3 * i + 1] = (v - cy) * z * inv_fy;
+        out_xyz[3 * i + 2] = z;
+        out_valid[i] = 1;
+    }
+}

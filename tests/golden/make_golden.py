@@ -67,6 +67,11 @@ def main():
     out["cross_q1_t0"] = cv_cross(descs[1], descs[0])
     out["knn2_q1_t0"] = cv_knn2(descs[1], descs[0])
     np.savez_compressed(os.path.join(HERE, "bundled.npz"), **out)
+    # the bundled depth frames (data/depth, 16-bit PNG as the reference's RgbdFileProvider reads them with IMREAD_UNCHANGED,
+    # rgbd_file_provider.cpp:95) for the back-projection step; kept in a separate file so bundled.npz stays untouched
+    np.savez_compressed(os.path.join(HERE, "depth.npz"),
+                        depth0=cv2.imread("/root/reference/data/depth/0000.png", cv2.IMREAD_UNCHANGED),
+                        depth1=cv2.imread("/root/reference/data/depth/0001.png", cv2.IMREAD_UNCHANGED))
 
     rng = np.random.default_rng(20261104)
     syn = {"cv2_version": np.array(cv2.__version__)}
