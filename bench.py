@@ -376,6 +376,13 @@ def main():
         roofline = {"bound": "int-pipe (popc); not hbm/tensor: 8 POPC.32 per 256-bit pair", "kernel": dom, "achieved": d["achieved"],
                     "peak": peak_pairs, "unit": "Gpair/s", "frac": d["achieved"] / peak_pairs, "traffic": None,
                     "peak_source": "register-only POPC loop measured in this run (mslam_b200_measure_int_peaks)"}
+    try:  # measured DRAM traffic of the dominant stage, from the committed ncu --set full capture of this workload
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if tr.get("workload") == args.workload and dom in tr["bytes_per_step"]:
+            roofline["traffic"] = tr["bytes_per_step"][dom]
+            roofline["traffic_source"] = "profiles/ncu_traffic.json (ncu --set full, dram read + write bytes per step, cold L2)"
+    except (OSError, ValueError, KeyError):
+        pass
     whole = bytes_per_frame * B * args.steps / (ms_total * 1e-3) / 1e9
     roofline["whole_step_hbm"] = {"achieved": whole, "frac": whole / pk["hbm_gbs"], "bytes_per_frame": bytes_per_frame}
     roofline["stages"] = roofs
