@@ -20,6 +20,7 @@ struct LevelDesc
     int n_keep;      // cv::ORB nfeaturesPerLevel[l]
     int cand_cap;    // capacity of this level's candidate list (upper bound of strict 3x3 maxima)
     int tiles_x, tiles_y; // FAST tiling of the interior
+    int tile_sh;          // scored rows per FAST tile (32 or 64)
     int tile_base;   // first FAST tile index of this level inside the fused launch
     int blur_xblocks, blur_warp_base; // blur: 128-px column blocks per row band; first warp index of the level
     long long img_off;          // bytes

@@ -257,7 +257,7 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
         L.cand_cap = (wi > 0 && hi > 0) ? ((wi + 1) / 2) * ((hi + 1) / 2) : 0;
         L.cand_off = coff;
         coff += (long long)align_up((size_t)L.cand_cap, 4);
-        fast_tiles(L.w, L.h, cfg.edge_threshold, &L.tiles_x, &L.tiles_y);
+        fast_tiles(L.w, L.h, cfg.edge_threshold, &L.tiles_x, &L.tiles_y, &L.tile_sh);
         L.tile_base = tiles;
         tiles += L.tiles_x * L.tiles_y;
         int bw = 0;

@@ -383,9 +383,9 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
 //   Phase C walks the same queue for the strict 3x3 NMS and the border filter; survivors go to the level's
 //   candidate list (one global atomic per CTA) and its 256-bin score histogram (first retainBest cut).
 // =================================================================================================
-constexpr int FS_SW = 128, FS_SH = 32;          // scored positions per CTA
-constexpr int FS_IW = FS_SW - 4, FS_IH = FS_SH - 2; // assigned interior
-constexpr int FS_PW = FS_SW + 8, FS_PH = FS_SH + 6; // staged pixels
+constexpr int FS_SW = 128, FS_SH_MAX = 64;      // scored positions per CTA: 128 x (32 | 64), LevelDesc::tile_sh rows
+constexpr int FS_IW = FS_SW - 4;                // assigned interior: 124 x (tile_sh - 2)
+constexpr int FS_PW = FS_SW + 8, FS_PH_MAX = FS_SH_MAX + 6; // staged pixels
 constexpr int FS_PWW = FS_PW / 4;               // staged words per row (34)
 
 __device__ __forceinline__ unsigned lop3_maj_a_nb_c(unsigned a, unsigned b, unsigned c)
@@ -444,46 +444,49 @@ __device__ __forceinline__ unsigned ring4(unsigned wm, unsigned w0, unsigned wp,
 // the other side cannot win: two 9-arcs of a 16-ring always overlap).  In that domain
 //   score = centre - min over the 16 arcs (max over the 9 ring pixels of the arc) - 1,
 // with the arc maxima built from prefix/suffix maxima of the two half rings (28 + 32 VIMNMX.U16x2 for both corners).
-__device__ __forceinline__ unsigned corner_score2(const uint8_t* ca, const uint8_t* cb)
+__device__ __forceinline__ unsigned corner_score2(const uint8_t* ca, const uint8_t* cb, unsigned bright_a, unsigned bright_b)
 {
     constexpr int S = FS_PW;
     constexpr int OFF[16] = {3 * S,  3 * S + 1,  2 * S + 2,  S + 3,  3,  -S + 3, -2 * S + 2, -3 * S + 1,
                              -3 * S, -3 * S - 1, -2 * S - 2, -S - 3, -3, S - 3,  2 * S - 2,  3 * S - 1};
+    // lane value = pixel (arc darker than the centre) or 255 - pixel (arc brighter): p * (+-1) + (0 | 255), both lanes
+    // through two IMADs (fma pipe); exact modulo 2^32 because every lane result lies in 0..255
+    const unsigned sa = bright_a ? 0xffffffffu : 1u, sb = bright_b ? 0xffff0000u : 0x00010000u;
+    const unsigned kk = (bright_a ? 255u : 0u) + (bright_b ? 255u << 16 : 0u);
     unsigned x[16];
 #pragma unroll
     for(int k = 0; k < 16; ++k)
-        x[k] = (unsigned)cb[OFF[k]] * 65536u + (unsigned)ca[OFF[k]]; // IMAD: fma pipe
-    unsigned pa[8], sa[8], pb[8], sb[8]; // prefix / suffix maxima of the two half rings
-    pa[0] = x[0], pb[0] = x[8], sa[7] = x[7], sb[7] = x[15];
+        x[k] = (unsigned)cb[OFF[k]] * sb + ((unsigned)ca[OFF[k]] * sa + kk);
+    unsigned pa[8], sfa[8], pb[8], sfb[8]; // prefix / suffix maxima of the two half rings
+    pa[0] = x[0], pb[0] = x[8], sfa[7] = x[7], sfb[7] = x[15];
 #pragma unroll
     for(int i = 1; i < 8; ++i)
     {
         pa[i] = __vmaxu2(pa[i - 1], x[i]);
         pb[i] = __vmaxu2(pb[i - 1], x[8 + i]);
-        sa[7 - i] = __vmaxu2(sa[8 - i], x[7 - i]);
-        sb[7 - i] = __vmaxu2(sb[8 - i], x[15 - i]);
+        sfa[7 - i] = __vmaxu2(sfa[8 - i], x[7 - i]);
+        sfb[7 - i] = __vmaxu2(sfb[8 - i], x[15 - i]);
     }
     // arc k..k+8: k < 8 -> suffix of A from k + prefix of B to k ; k = 8 + j -> suffix of B from j + prefix of A to j
     unsigned m = 0xffffffffu;
 #pragma unroll
     for(int k = 0; k < 8; ++k)
     {
-        m = __vminu2(m, __vmaxu2(sa[k], pb[k]));
-        m = __vminu2(m, __vmaxu2(sb[k], pa[k]));
+        m = __vminu2(m, __vmaxu2(sfa[k], pb[k]));
+        m = __vminu2(m, __vmaxu2(sfb[k], pa[k]));
     }
-    const unsigned v = (unsigned)cb[0] * 65536u + (unsigned)ca[0];
-    return v - m - 0x00010001u; // both lanes are >= fast_thr - ... > 0: no borrow crosses the lanes
+    const unsigned v = (unsigned)cb[0] * sb + ((unsigned)ca[0] * sa + kk);
+    return v - m - 0x00010001u; // both lanes are >= fast_thr - 1 >= 0: no borrow crosses the lanes
 }
 
 __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, int l_begin, int l_end,
                                               const uint8_t* __restrict__ pyr, unsigned* __restrict__ cand,
                                               LevelCounters* __restrict__ ctr, unsigned* __restrict__ hist)
 {
-    __shared__ __align__(16) uint8_t s_px[FS_PH][FS_PW];
-    __shared__ __align__(16) uint8_t s_pxc[FS_PH][FS_PW]; // 255 - pixel (phase B reads bright-arc corners here)
-    __shared__ __align__(16) uint8_t s_sc[FS_SH][FS_SW];
-    __shared__ unsigned short s_q[FS_SH * FS_SW];
-    __shared__ unsigned s_out[FS_IW * FS_IH / 4 + 64];
+    __shared__ __align__(16) uint8_t s_px[FS_PH_MAX][FS_PW];
+    __shared__ __align__(16) uint8_t s_sc[FS_SH_MAX][FS_SW];
+    __shared__ unsigned short s_q[FS_SH_MAX * FS_SW];
+    __shared__ unsigned s_out[FS_IW * (FS_SH_MAX - 2) / 4 + 64];
     __shared__ int s_qn, s_on;
     __shared__ unsigned s_base;
 
@@ -499,13 +502,14 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int edge = P.edge, thr = P.fast_thr;
     const int sx0 = ((edge - 1) & ~3) + FS_IW * tx; // first scored column (multiple of 4)
-    const int sy0 = edge - 1 + FS_IH * ty;          // first scored row
+    const int SH = L.tile_sh, PH = SH + 6;         // scored / staged rows of this level's tiles
+    const int sy0 = edge - 1 + (SH - 2) * ty;       // first scored row
     const int px0 = sx0 - 4, py0 = sy0 - 3;         // first staged pixel
     const uint8_t* img = pyr + L.img_off + (long long)b * L.img_frame_stride;
 
     {
         // all of the thread's tile words are requested before the first one is stored: one exposed load latency per CTA
-        constexpr int NLD = (FS_PH * FS_PWW + 255) / 256;
+        constexpr int NLD = (FS_PH_MAX * FS_PWW + 255) / 256;
         unsigned v[NLD];
 #pragma unroll
         for(int k = 0; k < NLD; ++k)
@@ -514,21 +518,20 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
             const int r = i / FS_PWW, c = i - r * FS_PWW;
             const int gy = py0 + r, gx = px0 + 4 * c;
             v[k] = 0;
-            if(i < FS_PH * FS_PWW && gy < L.h && gx < L.pitch)
+            if(i < PH * FS_PWW && gy < L.h && gx < L.pitch)
                 v[k] = __ldg(reinterpret_cast<const unsigned*>(img + (long long)gy * L.pitch + gx));
         }
 #pragma unroll
         for(int k = 0; k < NLD; ++k)
         {
             const int i = tid + 256 * k;
-            if(i < FS_PH * FS_PWW)
+            if(i < PH * FS_PWW)
             {
                 reinterpret_cast<unsigned*>(&s_px[0][0])[i] = v[k];
-                reinterpret_cast<unsigned*>(&s_pxc[0][0])[i] = ~v[k];
             }
         }
     }
-    for(int i = tid; i < FS_SH * FS_SW / 16; i += 256)
+    for(int i = tid; i < SH * FS_SW / 16; i += 256)
         reinterpret_cast<uint4*>(&s_sc[0][0])[i] = make_uint4(0, 0, 0, 0);
     if(tid == 0)
     {
@@ -537,13 +540,17 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     }
     __syncthreads();
 
-    // ---- phase A: classify 4 rows x 4 pixels per thread ----
+    // ---- phase A: classify 4 rows x 4 pixels per thread and pass (32 rows per pass) ----
+#pragma unroll 1
+    for(int pass = 0; pass < SH / 32; ++pass)
+    {
+    const int rb = 32 * pass + 4 * warp; // first scored row of this thread's group
     unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row 4 * warp + row is a corner
     unsigned bright16 = 0; // ... and its arc is brighter than the centre
     {
         const unsigned t4 = (unsigned)thr * 0x01010101u;
         const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
-        const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[4 * warp][0]) + lane;
+        const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[rb][0]) + lane;
         unsigned wm[10], w0[10], wp[10]; // staged rows 4 * warp .. 4 * warp + 9, words lane, lane + 1, lane + 2
 #pragma unroll
         for(int r = 0; r < 10; ++r)
@@ -580,21 +587,14 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
             bright16 |= (((fb >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
         }
     }
-    // only positions that can matter: inside the image interior +- 1 (the NMS halo)
+    // only positions that can matter: inside the image interior +- 1 (the NMS halo):
+    //   edge - 1 <= x <= w - edge (a nibble, the same for the 4 rows) and y <= h - edge (y >= edge - 1 by construction)
     {
-        unsigned keep = 0;
         const int x = sx0 + 4 * lane;
-#pragma unroll
-        for(int row = 0; row < 4; ++row)
-        {
-            const int y = sy0 + 4 * warp + row;
-            const bool yok = y <= L.h - edge; // y >= edge - 1 by construction
-#pragma unroll
-            for(int j = 0; j < 4; ++j)
-                if(yok && x + j >= edge - 1 && x + j <= L.w - edge)
-                    keep |= 1u << (4 * row + j);
-        }
-        flags16 &= keep;
+        const int jlo = max(0, edge - 1 - x), jhi = min(3, L.w - edge - x);
+        const unsigned nib = jlo <= jhi ? ((0xfu >> (3 - jhi)) & (0xfu << jlo) & 0xfu) : 0u;
+        const int nrows = min(4, max(0, L.h - edge - (sy0 + rb) + 1));
+        flags16 &= (nib * 0x1111u) & ((1u << (4 * nrows)) - 1u);
     }
     // warp-aggregated append to the CTA's corner queue
     {
@@ -617,9 +617,10 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         {
             const int bit = __ffs(f) - 1;
             f &= f - 1;
-            s_q[pos++] = (unsigned short)(((4 * warp + (bit >> 2)) * FS_SW + 4 * lane + (bit & 3)) | ((bright16 >> bit & 1u) << 12));
+            s_q[pos++] = (unsigned short)(((rb + (bit >> 2)) * FS_SW + 4 * lane + (bit & 3)) | ((bright16 >> bit & 1u) << 13));
         }
     }
+    } // passes
     __syncthreads();
 
     // ---- phase B: exact cornerScore of the queued corners ----
@@ -627,11 +628,9 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     for(int j = 2 * tid; j < nq; j += 512)
     {
         const unsigned ea = s_q[j], eb = s_q[min(j + 1, nq - 1)];
-        const int ia = ea & 0xfff, ib = eb & 0xfff;
+        const int ia = ea & 0x1fff, ib = eb & 0x1fff;
         const int ya = ia / FS_SW, xa = ia - ya * FS_SW, yb = ib / FS_SW, xb = ib - yb * FS_SW;
-        const uint8_t* ta = (ea & 0x1000u) ? &s_pxc[0][0] : &s_px[0][0];
-        const uint8_t* tb = (eb & 0x1000u) ? &s_pxc[0][0] : &s_px[0][0];
-        const unsigned sc = corner_score2(ta + (ya + 3) * FS_PW + xa + 4, tb + (yb + 3) * FS_PW + xb + 4);
+        const unsigned sc = corner_score2(&s_px[ya + 3][xa + 4], &s_px[yb + 3][xb + 4], ea & 0x2000u, eb & 0x2000u);
         s_sc[ya][xa] = (uint8_t)(sc & 0xffu);
         s_sc[yb][xb] = (uint8_t)(sc >> 16);
     }
@@ -645,10 +644,10 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         unsigned rec = 0;
         if(j < nq)
         {
-            const int i = s_q[j] & 0xfff;
+            const int i = s_q[j] & 0x1fff;
             const int sy = i / FS_SW, sx = i - sy * FS_SW;
             const int x = sx0 + sx, y = sy0 + sy;
-            if(sx >= 2 && sx < FS_SW - 2 && sy >= 1 && sy < FS_SH - 1 && x >= edge && x < L.w - edge && y < L.h - edge)
+            if(sx >= 2 && sx < FS_SW - 2 && sy >= 1 && sy < SH - 1 && x >= edge && x < L.w - edge && y < L.h - edge)
             {
                 const uint8_t* s = &s_sc[sy][sx];
                 const int v = s[0];
@@ -1249,12 +1248,16 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
     ++*launches;
 }
 
-void fast_tiles(int w, int h, int edge, int* tx, int* ty)
+void fast_tiles(int w, int h, int edge, int* tx, int* ty, int* tile_sh)
 {
     const int ox0 = ((edge - 1) & ~3) + 2; // first assigned interior column of tile 0
     const int wi = w - edge - ox0, hi = h - 2 * edge;
+    // tall tiles (64 scored rows) halve the per-tile fixed cost and the halo share; short ones waste fewer rows on levels
+    // whose interior is only a few tiles high
+    const int sh = hi > 150 ? 64 : 32;
+    *tile_sh = sh;
     *tx = wi > 0 ? (wi + FS_IW - 1) / FS_IW : 0;
-    *ty = hi > 0 ? (hi + FS_IH - 1) / FS_IH : 0;
+    *ty = hi > 0 ? (hi + (sh - 2) - 1) / (sh - 2) : 0;
     if(*tx == 0 || *ty == 0)
         *tx = *ty = 0;
 }
