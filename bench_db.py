@@ -187,6 +187,9 @@ def main(args, rank, world, local):
                 "peak_source": "register-only POPC.32 loop over all SMs, measured in this run (mslam_b200_measure_int_peaks)",
                 "pairs_per_s_per_gpu": per_gpu_pairs, "kernel_ms_per_launch": db_ms,
                 "frac_of_measured_csa_sequence_peak": per_gpu_pairs / ip["csa_pairs_per_s"],
+                "frac_of_alu_pipe_bound": per_gpu_pairs * 19.0 / ip["lop3_3reg_per_s"],
+                "alu_pipe_bound": "19 ALU-pipe instructions per pair (8 XOR + 8 carry-save LOP3 + 3 VIMNMX of the top-2 update) against "
+                                  "the 3-register LOP3 rate measured in this run (= 64 lanes/clk/SM)",
                 "note": "the kernel issues 4 POPC + 8 LOP3 carry-save per pair instead of 8 POPC, so the ALU pipe (LOP3/VIMNMX) "
                         "is its binding pipe; csa_sequence_peak is the same instruction sequence run register-only",
                 "hbm_bytes_per_launch_algorithmic": kf_local * n * 32 + qb * n * 32,

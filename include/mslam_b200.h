@@ -241,8 +241,9 @@ MSLAM_B200_API int mslam_b200_stage_times(mslam_b200_ctx* ctx, double* total_ms,
 /* integer-pipe roofline denominators, measured on the context's device with register-only loops over all SMs:
  * out[0] = POPC.32 results/s, out[1] = LOP3 results/s, out[2] = 256-bit pair evaluations/s of the plain
  * 8x(xor,popc,add) + top-2 sequence, out[3] = SM clock (MHz) the loops ran at (from clock64/globaltimer),
- * out[4] = pair evaluations/s of the carry-save sequence the matcher uses (8 xor, 8 lop3, 4 popc) + top-2. */
-MSLAM_B200_API int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out5);
+ * out[4] = pair evaluations/s of the carry-save sequence the matcher uses (8 xor, 8 lop3, 4 popc) + top-2,
+ * out[5] = LOP3 results/s when all three operands are live registers (12 independent chains per thread). */
+MSLAM_B200_API int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out6);
 
 #ifdef __cplusplus
 }

@@ -362,4 +362,4 @@ class Context:
         out = np.zeros(8, np.float64)
         self._chk(library().mslam_b200_measure_int_peaks(self._h, _ptr(out)), "measure_int_peaks")
         return {"popc32_per_s": float(out[0]), "lop3_per_s": float(out[1]), "plain_pairs_per_s": float(out[2]),
-                "sm_mhz": float(out[3]), "csa_pairs_per_s": float(out[4])}
+                "sm_mhz": float(out[3]), "csa_pairs_per_s": float(out[4]), "lop3_3reg_per_s": float(out[5])}

@@ -430,6 +430,29 @@ __global__ void __launch_bounds__(256) k_peak_lop3(unsigned* out, int iters, uns
         out[0] = s;
 }
 
+// 3-register-operand LOP3 (what the bit-sliced FAST test and the carry-save adders issue): 12 independent chains per
+// thread, every instruction reads three different live registers
+__global__ void __launch_bounds__(256) k_peak_lop3r(unsigned* out, int iters)
+{
+    unsigned v[12];
+#pragma unroll
+    for(int i = 0; i < 12; ++i)
+        v[i] = threadIdx.x * 2654435761u + i * 40503u + blockIdx.x;
+#pragma unroll 4
+    for(int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for(int i = 0; i < 12; ++i)
+            v[i] = maj3(v[i], v[(i + 4) % 12], v[(i + 8) % 12]) ^ 0u; // majority of three registers, one LOP3
+    }
+    unsigned s = 0;
+#pragma unroll
+    for(int i = 0; i < 12; ++i)
+        s ^= v[i];
+    if(s == 0x12345u)
+        out[0] = s;
+}
+
 // the pair sequence of the matcher with operands in registers: 8 x xor, then either 8 POPC + adds (CSA = false) or the
 // carry-save form ham256 uses (CSA = true).  All eight train words change every iteration through an IMAD (fma pipe,
 // otherwise idle) so that nothing can be hoisted out of the loop.
@@ -592,8 +615,8 @@ cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4 /* 5 v
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     const int grid = sm_count * 8, iters = 4096;
-    float ms[4] = {0, 0, 0, 0};
-    for(int which = 0; which < 4; ++which)
+    float ms[5] = {0, 0, 0, 0, 0};
+    for(int which = 0; which < 5; ++which)
     {
         for(int rep = 0; rep < 3; ++rep) // last repetition is the one kept (warm clocks)
         {
@@ -604,8 +627,10 @@ cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4 /* 5 v
                 k_peak_lop3<<<grid, 256, 0, st>>>(d_out, iters, 0x9e3779b9u, 0x7f4a7c15u);
             else if(which == 2)
                 k_peak_pairs<false><<<grid, 256, 0, st>>>(d_out, iters);
-            else
+            else if(which == 3)
                 k_peak_pairs<true><<<grid, 256, 0, st>>>(d_out, iters);
+            else
+                k_peak_lop3r<<<grid, 256, 0, st>>>(d_out, iters);
             cudaEventRecord(e1, st);
             cudaEventSynchronize(e1);
             cudaEventElapsedTime(&ms[which], e0, e1);
@@ -623,6 +648,7 @@ cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4 /* 5 v
     out4[2] = threads * iters / (ms[2] * 1e-3);
     out4[3] = h_clk[1] > 0 ? (double)h_clk[0] / (double)h_clk[1] * 1e3 : 0.0;
     out4[4] = threads * iters / (ms[3] * 1e-3);
+    out4[5] = threads * iters * 12.0 / (ms[4] * 1e-3);
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     cudaFree(d_out);
