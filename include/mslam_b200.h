@@ -206,6 +206,71 @@ MSLAM_B200_API int mslam_b200_backproject(mslam_b200_ctx* ctx, const double* xy,
                                           const uint16_t* depth, int width, int height, const mslam_b200_camera* cam,
                                           double* out_xyz, uint8_t* out_valid);
 
+/* ---- second detector: DistributedOrbOpenCvDetector, SURVEY 8(f) row f1 ---------------------------------------- */
+/* Replaces DistributedOrbOpenCvDetector::detect (src/lib/modular_slam/distributed_cv_feature.cpp:1189-1222: toGrayScale,
+ * then OrbExtractorPimpl::extract :719-809), the detector the Viewer app wires in (src/app/viewer/viewer.cpp:183):
+ * chained cv::resize INTER_LINEAR pyramid (:830-841), cv::FAST per 64-px cell with threshold 20 then 7 (:843-939), quad-tree
+ * keypoint distribution (:941-1106), intensity-centroid angle (:543-570), fixed-point 7x7 Gaussian blur (:797-798) and
+ * rotated BRIEF with the polynomial cos/sin (:456-503, :572-629).  Keypoints come out in the reference's order (level,
+ * then the tree's final list order), so index i is the reference's Keypoint::id (:1201-1210).
+ * It is a separate handle: its pyramid geometry differs from cv::ORB's (round(W / scale_l), float product-chain scales). */
+typedef struct mslam_b200_dist mslam_b200_dist;
+/* Defaults = orb_params("orb", 1.2f, 8, 20, 7) and OrbExtractorPimpl(params, 1000)  (distributed_cv_feature.cpp:1184-1186) */
+typedef struct mslam_b200_dist_config
+{
+    int struct_size;        /* = sizeof(mslam_b200_dist_config) */
+    int device;
+    int max_width;          /* largest frame the handle accepts */
+    int max_height;
+    int max_batch;
+    int nlevels;            /* orb_params::num_levels_ */
+    float scale_factor;     /* orb_params::scale_factor_ */
+    int ini_fast_threshold; /* orb_params::ini_fast_thr_ */
+    int min_fast_threshold; /* orb_params::min_fast_thr_ */
+    int min_size;           /* OrbExtractorPimpl::min_size_: a tree node stops splitting at area * scale^2 <= min_size */
+    int max_keypoints;      /* per-frame capacity inside the handle; 0 => the tree's own upper bound for max_width x max_height */
+    void* stream;           /* optional cudaStream_t; NULL => handle-owned stream */
+    int flags;
+    int reserved;
+} mslam_b200_dist_config;
+MSLAM_B200_API void mslam_b200_dist_default_config(mslam_b200_dist_config* cfg);
+MSLAM_B200_API int mslam_b200_dist_create(const mslam_b200_dist_config* cfg, mslam_b200_dist** out);
+MSLAM_B200_API void mslam_b200_dist_destroy(mslam_b200_dist* d);
+MSLAM_B200_API int mslam_b200_dist_synchronize(mslam_b200_dist* d);
+MSLAM_B200_API const char* mslam_b200_dist_last_cuda_error(mslam_b200_dist* d);
+MSLAM_B200_API long long mslam_b200_dist_launch_count(mslam_b200_dist* d);
+/* per-frame keypoint capacity the handle was created with (size outputs with it) */
+MSLAM_B200_API int mslam_b200_dist_keypoint_capacity(mslam_b200_dist* d);
+/* per-level sizes / scales for a frame size (compute_image_pyramid, :830-841); arrays of nlevels */
+MSLAM_B200_API int mslam_b200_dist_level_geometry(mslam_b200_dist* d, int width, int height, int* w, int* h, float* scale);
+/* One frame (host pointers, synchronous).  `bgr` is RgbFrame::data; keypoint.response is the FAST score, .size is
+ * (float)(unsigned)(31 * scale_l), x / y are level coordinates times scale_l (:1117-1130).  MSLAM_B200_E_CAPACITY if the
+ * count exceeds `capacity` (n_out still reports it).  Frames whose smallest level is under 38 px on a side are
+ * MSLAM_B200_E_INVALID (the reference's unsigned border arithmetic underflows there). */
+MSLAM_B200_API int mslam_b200_dist_detect(mslam_b200_dist* d, const uint8_t* bgr, int width, int height, int stride_bytes,
+                                          mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out);
+/* A batch of independent frames of one size; outputs [n_frames][capacity], counts [n_frames] */
+MSLAM_B200_API int mslam_b200_dist_detect_batch(mslam_b200_dist* d, const uint8_t* const* frames, int n_frames, int width,
+                                                int height, int stride_bytes, mslam_b200_keypoint* out_kp,
+                                                uint8_t* out_desc, int capacity, int* n_out);
+/* Device-resident variant (asynchronous on the handle's stream): d_bgr [n_frames][height][width][3] dense */
+MSLAM_B200_API int mslam_b200_dist_detect_batch_dev(mslam_b200_dist* d, const uint8_t* d_bgr, int n_frames, int width,
+                                                    int height, mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity,
+                                                    int* d_counts);
+typedef enum mslam_b200_dist_stage
+{
+    MSLAM_B200_DIST_PYRAMID = 0, /* u8 level image, dense w_l*h_l */
+    MSLAM_B200_DIST_BLURRED = 1, /* u8 blurred level image */
+    MSLAM_B200_DIST_N_FAST = 2,  /* int: keypts_to_distribute of the level */
+    MSLAM_B200_DIST_N_TREE = 3,  /* int: keypoints the tree kept on the level */
+    MSLAM_B200_DIST_PASSES = 4   /* int: passes of the tree's while(true) loop */
+} mslam_b200_dist_stage;
+/* copy an intermediate of the LAST detect call (frame index in that batch, level) to host memory */
+MSLAM_B200_API int mslam_b200_dist_debug_read(mslam_b200_dist* d, int stage, int frame, int level, void* out, size_t bytes);
+/* per-stage device time of the calls since the last read: ms[6] = gray, resize, fast cells, tree, blur, describe
+ * (CUDA events on the handle's stream; enable = 0/1 switches the bracketing, ms may be NULL) */
+MSLAM_B200_API int mslam_b200_dist_stage_times(mslam_b200_dist* d, int enable, double* ms6);
+
 /* ---- measurement / parity aids ------------------------------------------------------------------------------- */
 typedef enum mslam_b200_stage
 {

@@ -363,3 +363,131 @@ class Context:
         self._chk(library().mslam_b200_measure_int_peaks(self._h, _ptr(out)), "measure_int_peaks")
         return {"popc32_per_s": float(out[0]), "lop3_per_s": float(out[1]), "plain_pairs_per_s": float(out[2]),
                 "sm_mhz": float(out[3]), "csa_pairs_per_s": float(out[4]), "lop3_3reg_per_s": float(out[5])}
+
+
+# ---- second detector: DistributedOrbOpenCvDetector (include/mslam_b200.h, "second detector") ---------------------------
+DIST_PYRAMID, DIST_BLURRED, DIST_N_FAST, DIST_N_TREE, DIST_PASSES = 0, 1, 2, 3, 4
+
+
+class DistConfig(C.Structure):
+    _fields_ = [("struct_size", C.c_int), ("device", C.c_int), ("max_width", C.c_int), ("max_height", C.c_int),
+                ("max_batch", C.c_int), ("nlevels", C.c_int), ("scale_factor", C.c_float),
+                ("ini_fast_threshold", C.c_int), ("min_fast_threshold", C.c_int), ("min_size", C.c_int),
+                ("max_keypoints", C.c_int), ("stream", C.c_void_p), ("flags", C.c_int), ("reserved", C.c_int)]
+
+
+def dist_default_config(**kw):
+    cfg = DistConfig()
+    lib = library()
+    lib.mslam_b200_dist_default_config.restype = None
+    lib.mslam_b200_dist_default_config(C.byref(cfg))
+    for k, v in kw.items():
+        if not hasattr(cfg, k):
+            raise TypeError(f"unknown config field {k}")
+        setattr(cfg, k, v)
+    return cfg
+
+
+class DistContext:
+    """Owns one mslam_b200_dist handle (DistributedOrbOpenCvDetector on one CUDA device / stream)."""
+
+    def __init__(self, **cfg_kw):
+        self._h = None
+        self.cfg = dist_default_config(**cfg_kw)
+        lib = library()
+        lib.mslam_b200_dist_destroy.argtypes = [C.c_void_p]
+        lib.mslam_b200_dist_destroy.restype = None
+        lib.mslam_b200_dist_last_cuda_error.restype = C.c_char_p
+        lib.mslam_b200_dist_last_cuda_error.argtypes = [C.c_void_p]
+        lib.mslam_b200_dist_launch_count.restype = C.c_longlong
+        lib.mslam_b200_dist_launch_count.argtypes = [C.c_void_p]
+        h = C.c_void_p()
+        rc = lib.mslam_b200_dist_create(C.byref(self.cfg), C.byref(h))
+        if rc:
+            raise MslamB200Error(rc, "mslam_b200_dist_create")
+        self._h = h
+        self.kp_cap = lib.mslam_b200_dist_keypoint_capacity(h)
+
+    def close(self):
+        if self._h is not None:
+            library().mslam_b200_dist_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc, what):
+        if rc:
+            raise MslamB200Error(rc, what, library().mslam_b200_dist_last_cuda_error(self._h).decode())
+
+    @property
+    def launch_count(self):
+        return int(library().mslam_b200_dist_launch_count(self._h))
+
+    def synchronize(self):
+        self._check(library().mslam_b200_dist_synchronize(self._h), "mslam_b200_dist_synchronize")
+
+    def level_geometry(self, W, H):
+        n = self.cfg.nlevels
+        w, h, s = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float32)
+        self._check(library().mslam_b200_dist_level_geometry(self._h, W, H, _ptr(w), _ptr(h), _ptr(s)),
+                    "mslam_b200_dist_level_geometry")
+        return w, h, s
+
+    def detect(self, bgr, capacity=None):
+        """one frame [H, W, 3] u8 -> (keypoints[KP_DTYPE], descriptors [n, 32]) in the reference's order"""
+        bgr = np.ascontiguousarray(bgr, np.uint8)
+        H, W, _ = bgr.shape
+        cap = capacity or self.kp_cap
+        kp = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        rc = library().mslam_b200_dist_detect(self._h, _ptr(bgr), W, H, W * 3, _ptr(kp), _ptr(desc), cap, C.byref(n))
+        self._check(rc, "mslam_b200_dist_detect")
+        return kp[:n.value].copy(), desc[:n.value].copy()
+
+    def detect_batch(self, frames, capacity=None):
+        """frames [B, H, W, 3] u8 (host) -> (kp [B, cap], desc [B, cap, 32], counts [B])"""
+        frames = np.ascontiguousarray(frames, np.uint8)
+        B, H, W, _ = frames.shape
+        cap = capacity or self.kp_cap
+        kp = np.zeros((B, cap), KP_DTYPE)
+        desc = np.zeros((B, cap, 32), np.uint8)
+        counts = np.zeros(B, np.int32)
+        ptrs = (C.c_void_p * B)(*[frames[i].ctypes.data for i in range(B)])
+        rc = library().mslam_b200_dist_detect_batch(self._h, ptrs, B, W, H, W * 3, _ptr(kp), _ptr(desc), cap, _ptr(counts))
+        self._check(rc, "mslam_b200_dist_detect_batch")
+        return kp, desc, counts
+
+    def detect_batch_dev(self, d_bgr, n_frames, W, H, d_kp, d_desc, capacity, d_counts):
+        """device tensors in / out, asynchronous on the handle's stream"""
+        rc = library().mslam_b200_dist_detect_batch_dev(self._h, _ptr(d_bgr), n_frames, W, H, _ptr(d_kp), _ptr(d_desc),
+                                                        capacity, _ptr(d_counts))
+        self._check(rc, "mslam_b200_dist_detect_batch_dev")
+
+    def debug_image(self, stage, frame, level, W, H):
+        w, h, _ = self.level_geometry(W, H)
+        out = np.zeros((h[level], w[level]), np.uint8)
+        self._check(library().mslam_b200_dist_debug_read(self._h, stage, frame, level, _ptr(out), C.c_size_t(out.size)),
+                    "mslam_b200_dist_debug_read")
+        return out
+
+    def debug_count(self, stage, frame, level):
+        v = np.zeros(1, np.int32)
+        self._check(library().mslam_b200_dist_debug_read(self._h, stage, frame, level, _ptr(v), C.c_size_t(4)),
+                    "mslam_b200_dist_debug_read")
+        return int(v[0])
+
+    def stage_times(self, enable=True):
+        ms = np.zeros(6, np.float64)
+        self._check(library().mslam_b200_dist_stage_times(self._h, int(enable), _ptr(ms)), "mslam_b200_dist_stage_times")
+        return dict(zip(("gray", "resize", "fast", "tree", "blur", "describe"), ms.tolist()))

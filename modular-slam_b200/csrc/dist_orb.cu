@@ -1,0 +1,1317 @@
+// dist_orb.cu -- the second detector of the reference, DistributedOrbOpenCvDetector, built B200-first.
+//
+// Reference: src/lib/modular_slam/distributed_cv_feature.cpp (a stella_vslam-derived extractor).  What it computes:
+//   toGrayScale (frame.cpp:6-27) -> chained cv::resize INTER_LINEAR pyramid (:830-841) -> cv::FAST with non-max suppression
+//   on every 64-px cell (+6 px overlap) inside a 19-px border, threshold 20, then 7 if the cell came back empty (:843-939)
+//   -> quad-tree distribution of the level's keypoints, one keypoint per final node, maximum response (:941-1106)
+//   -> intensity-centroid angle on the unblurred level (:543-570) -> cv::GaussianBlur 7x7 sigma 2 on u8 (fixed point,
+//   :797-798) -> 256 rotated BRIEF tests with polynomial cos/sin (:456-503, :572-629) -> coordinates * scale_l (:1117-1130).
+//
+// How it is mapped to the GPU (one launch per stage covers every frame of the batch and every level):
+//   k_dist_resize   level l-1 -> l, 11-bit fixed-point bilinear taps from per-level tables (tables built on the host in
+//                   IEEE double / float exactly as OpenCV builds them); 4 output pixels per thread
+//   k_dist_fast     one CTA per (frame, level, cell): the cell's 70x70 tile in shared memory, a queue of the pixels that
+//                   pass the 4-compass-point test, exact cornerScore of the queued pixels in one packed-s16x2 min/max
+//                   network (both polarities at once), strict 3x3 NMS inside the cell, threshold fallback, one atomic
+//                   per cell to append the survivors to the (frame, level) list
+//   k_dist_tree     one CTA per (frame, level).  The reference's std::list surgery is replaced by an order-key
+//                   formulation: every keypoint's path through the tree is a pure function of the node geometry, a
+//                   pass of the reference divides exactly the divisible nodes of one depth, and the final list order
+//                   is (depth descending, key ascending) with key_{d+1} = (nodes_d - 1 - key_d) * 4 + (3 - child)
+//                   (children are pushed to the FRONT of the list in order 0..3, which reverses the order every depth).
+//                   Per-depth occupancy counters in shared memory, the loop's "list size unchanged" exit reproduced
+//                   (created == divided), per-leaf argmax by atomicMax on (score, arrival order), block scan for the
+//                   output rank.
+//   k_dist_gauss    64x32 tiles, 8.8 horizontal / 16.16 vertical fixed point, REFLECT_101
+//   k_dist_describe one warp per keypoint: moments with lane = patch column, cv::fastAtan2, polynomial cos/sin in
+//                   separately rounded f32, lane = descriptor byte
+// All integer stages are exact by construction; every float operation is an explicit round-to-nearest intrinsic
+// (the library is also compiled with -fmad=false).
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <set>
+#include <utility>
+#include <vector>
+
+#include "kernels.h"
+
+using namespace mslam_b200;
+
+namespace
+{
+constexpr int kBorder = 19;   // orb_patch_radius_ (:695)
+constexpr int kCell = 64;     // cell_size (:854)
+constexpr int kFastOrg = 22;  // first pixel cv::FAST can report in a cell that starts at the border: 19 + 3
+constexpr int kMaxInit = 64;  // initial tree nodes supported (round(aspect ratio))
+constexpr int kTreeThreads = 1024;
+constexpr int kTreeSmemBudget = 200 * 1024;
+constexpr unsigned kFlag = 0x80000000u;
+
+struct DistLevel
+{
+    int w, h, pitch;
+    int ncx, ncy, cell_base;  // FAST cells
+    int gtx, gty, gtile_base; // blur tiles
+    int cand_cap, sel_cap;
+    int sel_off;              // elements, within one frame's selection block
+    int ninit_x, ninit_y;
+    int depth;                // deepest depth a node can have (all nodes there stop by area)
+    int tree_slots;           // sum over depths 0..depth of ninit * 4^d
+    int tree_in_smem;
+    int xtab_off, ytab_off;
+    long long img_off, img_frame_stride;
+    long long cand_off;       // elements, within one frame's candidate block
+    long long tree_off;       // words, within one frame's global tree scratch (levels that do not fit in smem)
+    double delta_x, delta_y;
+    float scale, size;
+};
+
+struct DistParams
+{
+    int nlevels, n_frames, W, H;
+    int ini_thr, min_thr;
+    unsigned min_size;
+    int kp_cap;               // per-frame keypoint capacity of the handle
+    int total_cells, total_gtiles;
+    int sel_frame_stride, pad;
+    long long cand_frame_stride, tree_frame_stride;
+    DistLevel lv[kMaxLevels];
+};
+
+struct DistCounters
+{
+    unsigned n_fast, n_tree, passes, err;
+};
+
+__device__ __align__(16) const signed char g_pairs[256 * 4] = {
+#include "brief_pattern.inc"
+};
+
+// =================================================================================================
+// resize: cv::resize INTER_LINEAR, CV_8UC1 (OpenCV resize.cpp HResizeLinear / VResizeLinear, 11-bit coefficients)
+// =================================================================================================
+struct XTap
+{
+    int ofs;
+    unsigned a; // a0 | a1 << 16
+};
+struct YTap
+{
+    int sy0, sy1; // clamped source rows
+    unsigned b;   // b0 | b1 << 16
+    int pad;
+};
+
+__global__ void __launch_bounds__(256) k_dist_resize(const uint8_t* __restrict__ src, int spitch, long long sfs, int sw,
+                                                     uint8_t* __restrict__ dst, int dpitch, long long dfs, int dw, int dh,
+                                                     const XTap* __restrict__ xt, const YTap* __restrict__ yt)
+{
+    const int x4 = (blockIdx.x * 64 + (threadIdx.x & 63)) * 4;
+    const int y = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if(x4 >= dw || y >= dh)
+        return;
+    const YTap Y = yt[y];
+    const uint8_t* s0 = src + blockIdx.z * sfs + (long long)Y.sy0 * spitch;
+    const uint8_t* s1 = src + blockIdx.z * sfs + (long long)Y.sy1 * spitch;
+    const int b0 = Y.b & 0xffff, b1 = Y.b >> 16;
+    unsigned out = 0;
+#pragma unroll
+    for(int i = 0; i < 4; ++i)
+    {
+        const int x = x4 + i < dw ? x4 + i : dw - 1;
+        const XTap X = xt[x];
+        const int a0 = X.a & 0xffff, a1 = X.a >> 16;
+        const int sx1 = X.ofs + 1 < sw ? X.ofs + 1 : X.ofs;
+        const int r0 = s0[X.ofs] * a0 + s0[sx1] * a1;
+        const int r1 = s1[X.ofs] * a0 + s1[sx1] * a1;
+        const unsigned o = (unsigned)((((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2);
+        out |= (o & 0xff) << (8 * i);
+    }
+    *reinterpret_cast<unsigned*>(dst + blockIdx.z * dfs + (long long)y * dpitch + x4) = out; // pitch covers the tail
+}
+
+// =================================================================================================
+// FAST per cell (cv::FAST(cell, thr, true), :915-922)
+// =================================================================================================
+constexpr int FT_PITCH = 72; // tile row pitch (70 used)
+constexpr int FS_PITCH = 68; // score row pitch (66 used: 64 + zero ring)
+
+__device__ __forceinline__ int level_of_cell(const DistParams& P, int idx)
+{
+    int l = 0;
+    while(l + 1 < P.nlevels && idx >= P.lv[l + 1].cell_base)
+        ++l;
+    return l;
+}
+__device__ __forceinline__ int level_of_gtile(const DistParams& P, int idx)
+{
+    int l = 0;
+    while(l + 1 < P.nlevels && idx >= P.lv[l + 1].gtile_base)
+        ++l;
+    return l;
+}
+
+// exact cornerScore<16> of a pixel known to sit >= 3 px inside the tile: max over the 16 arcs of 9 contiguous ring
+// pixels of min(v - p) and of min(p - v), minus one.  d and -d ride in the two s16 halves of one register.
+__device__ __forceinline__ int corner_best(const uint8_t* __restrict__ c)
+{
+    const int v = c[0];
+    unsigned e[25];
+    const int off[16] = {3 * FT_PITCH,      3 * FT_PITCH + 1,  2 * FT_PITCH + 2,  FT_PITCH + 3,  3,  -FT_PITCH + 3,
+                         -2 * FT_PITCH + 2, -3 * FT_PITCH + 1, -3 * FT_PITCH,     -3 * FT_PITCH - 1, -2 * FT_PITCH - 2,
+                         -FT_PITCH - 3,     -3,                FT_PITCH - 3,      2 * FT_PITCH - 2,  3 * FT_PITCH - 1};
+#pragma unroll
+    for(int k = 0; k < 16; ++k)
+    {
+        const int d = v - (int)c[off[k]];
+        e[k] = ((unsigned)d & 0xffffu) | ((unsigned)(-d) << 16);
+    }
+#pragma unroll
+    for(int k = 16; k < 25; ++k)
+        e[k] = e[k - 16];
+    unsigned m2[24], m4[22], best = 0x80008000u; // (-32768, -32768)
+#pragma unroll
+    for(int k = 0; k < 24; ++k)
+        m2[k] = __vmins2(e[k], e[k + 1]);
+#pragma unroll
+    for(int k = 0; k < 22; ++k)
+        m4[k] = __vmins2(m2[k], m2[k + 2]);
+#pragma unroll
+    for(int k = 0; k < 16; ++k)
+    {
+        const unsigned m8 = __vmins2(m4[k], m4[k + 4]);
+        best = __vmaxs2(best, __vmins2(m8, e[k + 8]));
+    }
+    const int lo = (int)(short)(best & 0xffff), hi = (int)(short)(best >> 16);
+    return lo > hi ? lo : hi;
+}
+
+__global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
+                                                   unsigned* __restrict__ cand, DistCounters* __restrict__ ctr)
+{
+    __shared__ __align__(16) uint8_t tile[70 * FT_PITCH];
+    __shared__ __align__(16) uint8_t sc[66 * FS_PITCH];
+    __shared__ unsigned short q[4096];
+    __shared__ unsigned surv[1024];
+    __shared__ int s_nq, s_ns, s_base;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int l = level_of_cell(P, blockIdx.x);
+    const DistLevel& L = P.lv[l];
+    const int frame = blockIdx.y;
+    const int c = blockIdx.x - L.cell_base;
+    const int ci = c / L.ncx, cj = c - ci * L.ncx;
+    const int x0 = kFastOrg + kCell * cj, y0 = kFastOrg + kCell * ci;
+    const int cw = min(kCell, L.w - kFastOrg - x0), ch = min(kCell, L.h - kFastOrg - y0);
+    const uint8_t* img = pyr + L.img_off + frame * L.img_frame_stride + (long long)(y0 - 3) * L.pitch + (x0 - 3);
+    const int tw = cw + 6, th = ch + 6;
+    for(int i = tid; i < th * tw; i += 256)
+    {
+        const int r = i / tw, cc = i - r * tw;
+        tile[r * FT_PITCH + cc] = __ldg(img + (long long)r * L.pitch + cc);
+    }
+    int thr = P.ini_thr;
+    int ns = 0;
+    for(int attempt = 0; attempt < 2; ++attempt)
+    {
+        for(int i = tid; i < 66 * FS_PITCH / 4; i += 256)
+            reinterpret_cast<unsigned*>(sc)[i] = 0;
+        if(tid == 0)
+            s_nq = 0, s_ns = 0;
+        __syncthreads();
+        // phase A: the 4-compass-point test (a 9-arc of the 16-ring always holds two of ring pixels 0, 4, 8, 12)
+#pragma unroll 4
+        for(int i = 0; i < 16; ++i)
+        {
+            const int ly = (tid >> 6) + 4 * i, lx = tid & 63;
+            bool pass = false;
+            if(lx < cw && ly < ch)
+            {
+                const uint8_t* p = tile + (ly + 3) * FT_PITCH + lx + 3;
+                const int v = p[0];
+                const int d0 = v - p[3 * FT_PITCH], d8 = v - p[-3 * FT_PITCH], d4 = v - p[3], d12 = v - p[-3];
+                const int dark = (d0 > thr) + (d8 > thr) + (d4 > thr) + (d12 > thr);
+                const int bright = (d0 < -thr) + (d8 < -thr) + (d4 < -thr) + (d12 < -thr);
+                pass = dark >= 2 || bright >= 2;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if(m)
+            {
+                int base = 0;
+                if(lane == 0)
+                    base = atomicAdd(&s_nq, __popc(m));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if(pass)
+                    q[base + __popc(m & ((1u << lane) - 1))] = (unsigned short)(ly << 8 | lx);
+            }
+        }
+        __syncthreads();
+        // phase B: exact score of the queued pixels
+        const int nq = s_nq;
+        for(int i = tid; i < nq; i += 256)
+        {
+            const int ly = q[i] >> 8, lx = q[i] & 255;
+            const int best = corner_best(tile + (ly + 3) * FT_PITCH + lx + 3);
+            if(best > thr)
+                sc[(ly + 1) * FS_PITCH + lx + 1] = (uint8_t)(best - 1);
+        }
+        __syncthreads();
+        // phase C: strict 3x3 non-max suppression inside the cell
+        for(int i = tid; i < nq; i += 256)
+        {
+            const int ly = q[i] >> 8, lx = q[i] & 255;
+            const uint8_t* s = sc + (ly + 1) * FS_PITCH + lx + 1;
+            const int v = s[0];
+            if(v && v > s[-1] && v > s[1] && v > s[-FS_PITCH - 1] && v > s[-FS_PITCH] && v > s[-FS_PITCH + 1] &&
+               v > s[FS_PITCH - 1] && v > s[FS_PITCH] && v > s[FS_PITCH + 1])
+            {
+                const int k = atomicAdd(&s_ns, 1);
+                // coordinates relative to the border origin, as keypts_to_distribute holds them (:928-931)
+                surv[k] = (unsigned)(y0 + ly - kBorder) << 20 | (unsigned)(x0 + lx - kBorder) << 8 | (unsigned)v;
+            }
+        }
+        __syncthreads();
+        ns = s_ns;
+        if(ns > 0 || thr == P.min_thr)
+            break;
+        thr = P.min_thr; // keypts_in_cell.empty() -> second cv::FAST with min_fast_thr_ (:919-923)
+        __syncthreads();
+    }
+    if(ns == 0)
+        return;
+    if(tid == 0)
+        s_base = (int)atomicAdd(&ctr[frame * P.nlevels + l].n_fast, (unsigned)ns);
+    __syncthreads();
+    unsigned* out = cand + frame * P.cand_frame_stride + L.cand_off;
+    for(int i = tid; i < ns; i += 256)
+        if(s_base + i < L.cand_cap)
+            out[s_base + i] = surv[i];
+}
+
+// =================================================================================================
+// quad-tree distribution (:941-1106), order-key formulation -- see the file header
+// =================================================================================================
+struct Walk
+{
+    int bx, by, ex, ey;
+    int depth, key, off, nslots;
+};
+
+__device__ __forceinline__ bool area_stops(int bx, int by, int ex, int ey, float s, unsigned min_size)
+{
+    const unsigned area = (unsigned)((ex - bx) * (ey - by)); // orb_extractor_node::size()
+    return __fmul_rn(__fmul_rn((float)area, s), s) <= (float)min_size;
+}
+
+// place a keypoint in its initial node (initialize_nodes, :1032-1041)
+__device__ __forceinline__ void walk_init(const DistLevel& L, int x, int y, Walk& w)
+{
+    const int ninit = L.ninit_x * L.ninit_y;
+    unsigned ix = (unsigned)((double)(float)x / L.delta_x), iy = (unsigned)((double)(float)y / L.delta_y);
+    unsigned i0 = ix + iy * (unsigned)L.ninit_x;
+    if(i0 >= (unsigned)ninit)
+        i0 = ninit - 1, ix = i0 % L.ninit_x, iy = i0 / L.ninit_x;
+    w.bx = (int)(L.delta_x * ix), w.by = (int)(L.delta_y * iy);
+    w.ex = (int)(L.delta_x * (ix + 1)), w.ey = (int)(L.delta_y * (iy + 1));
+    w.depth = 0, w.key = (int)i0, w.off = 0, w.nslots = ninit;
+}
+
+// one divide_node step (:306-355): returns the child index and moves w into the child
+__device__ __forceinline__ void walk_down(int x, int y, Walk& w)
+{
+    const int cx = w.bx + ((w.ex - w.bx + 1) >> 1), cy = w.by + ((w.ey - w.by + 1) >> 1); // cvCeil(len / 2.0)
+    int ci = 0;
+    if(cx <= x)
+        ci += 1, w.bx = cx;
+    else
+        w.ex = cx;
+    if(cy <= y)
+        ci += 2, w.by = cy;
+    else
+        w.ey = cy;
+    w.key = (w.nslots - 1 - w.key) * 4 + (3 - ci);
+    w.off += w.nslots;
+    w.nslots *= 4;
+    w.depth += 1;
+}
+
+// walk from the root towards depth `target`; stops early at a node that is final (one keypoint, or small area).
+// Returns true when the walk arrived at `target` through divided nodes only.
+__device__ __forceinline__ bool walk_to(const DistLevel& L, const unsigned* cnt, int x, int y, int target, Walk& w)
+{
+    walk_init(L, x, y, w);
+    while(w.depth < target)
+    {
+        const unsigned c = cnt[w.off + w.key];
+        if((c & ~kFlag) == 1u || (c & kFlag))
+            return false;
+        walk_down(x, y, w);
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constant__ DistParams P, const unsigned* __restrict__ cand,
+                                                           DistCounters* __restrict__ ctr, unsigned* __restrict__ sel,
+                                                           unsigned* __restrict__ gtree)
+{
+    extern __shared__ unsigned s_dyn[];
+    __shared__ unsigned s_created, s_divided;
+    __shared__ unsigned s_warp[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int l = blockIdx.x, frame = blockIdx.y;
+    const DistLevel& L = P.lv[l];
+    DistCounters* C = ctr + frame * P.nlevels + l;
+    const int n = (int)min(C->n_fast, (unsigned)L.cand_cap);
+    if(n == 0)
+        return; // n_tree and passes stay 0
+    if(C->n_fast > (unsigned)L.cand_cap && tid == 0)
+        C->err = 1;
+    unsigned* cnt = L.tree_in_smem ? s_dyn : gtree + frame * P.tree_frame_stride + L.tree_off;
+    unsigned* best = cnt + L.tree_slots;
+    for(int i = tid; i < 2 * L.tree_slots; i += kTreeThreads)
+        cnt[i] = 0;
+    __syncthreads();
+    const unsigned* list = cand + frame * P.cand_frame_stride + L.cand_off;
+    const int ninit = L.ninit_x * L.ninit_y;
+    const float s = L.scale;
+
+    // depth 0: occupancy of the initial nodes
+    for(int k = tid; k < n; k += kTreeThreads)
+    {
+        const unsigned r = list[k];
+        const int x = (r >> 8) & 0xfff, y = r >> 20;
+        Walk w;
+        walk_init(L, x, y, w);
+        const unsigned old = atomicAdd(&cnt[w.key], 1u);
+        if(old == 0 && area_stops(w.bx, w.by, w.ex, w.ey, s, P.min_size))
+            atomicOr(&cnt[w.key], kFlag);
+    }
+    __syncthreads();
+
+    // pass p divides every divisible node of depth p (the reference's while(true) body, :954-976)
+    int t_end = L.depth, passes = 0;
+    bool broke = false;
+    int off_p = 0, nslots_p = ninit;
+    for(int p = 0; p < L.depth; ++p)
+    {
+        if(tid == 0)
+            s_created = 0, s_divided = 0;
+        __syncthreads();
+        unsigned created = 0, divided = 0;
+        for(int k = tid; k < n; k += kTreeThreads)
+        {
+            const unsigned r = list[k];
+            const int x = (r >> 8) & 0xfff, y = r >> 20;
+            Walk w;
+            if(!walk_to(L, cnt, x, y, p, w))
+                continue;
+            const unsigned c = cnt[w.off + w.key];
+            if((c & ~kFlag) == 1u || (c & kFlag))
+                continue;
+            walk_down(x, y, w);
+            const unsigned old = atomicAdd(&cnt[w.off + w.key], 1u);
+            if((old & ~kFlag) == 0)
+            {
+                ++created;
+                if(area_stops(w.bx, w.by, w.ex, w.ey, s, P.min_size))
+                    atomicOr(&cnt[w.off + w.key], kFlag);
+            }
+        }
+        for(int i = tid; i < nslots_p; i += kTreeThreads)
+        {
+            const unsigned c = cnt[off_p + i];
+            divided += (c & ~kFlag) >= 2u && !(c & kFlag);
+        }
+        created = __reduce_add_sync(0xffffffffu, created);
+        divided = __reduce_add_sync(0xffffffffu, divided);
+        if(lane == 0 && (created | divided))
+        {
+            atomicAdd(&s_created, created);
+            atomicAdd(&s_divided, divided);
+        }
+        __syncthreads();
+        const unsigned tc = s_created, td = s_divided;
+        ++passes;
+        off_p += nslots_p;
+        nslots_p *= 4;
+        if(tc == td) // nodes.size() == prev_size (:972): also when every divided node had exactly one non-empty child
+        {
+            t_end = p + 1;
+            broke = true;
+            break;
+        }
+        __syncthreads();
+    }
+    if(!broke)
+        ++passes; // every pass changed the list: the reference runs one more, which finds every node stopped by area
+    __syncthreads();
+
+    // final nodes: per node the keypoint of maximum response, first in arrival order on ties (:1079-1106).
+    // arrival order = cell-major raster (cells rows x cols, raster inside the cell), 24 bits.
+    for(int k = tid; k < n; k += kTreeThreads)
+    {
+        const unsigned r = list[k];
+        const int x = (r >> 8) & 0xfff, y = r >> 20;
+        Walk w;
+        walk_to(L, cnt, x, y, t_end, w);
+        const int cj = (x - 3) >> 6, ci = (y - 3) >> 6;
+        const unsigned ord = (unsigned)(ci * L.ncx + cj) << 12 | (unsigned)((y - 3) & 63) << 6 | (unsigned)((x - 3) & 63);
+        atomicMax(&best[w.off + w.key], (r & 0xffu) << 24 | (0xffffffu - ord));
+    }
+    __syncthreads();
+
+    // final list order: depth t_end first, then the final nodes of depth t_end - 1, ... , depth 0; key ascending
+    int total_seq = 0;
+    {
+        int ns = ninit;
+        for(int d = 0; d <= t_end; ++d, ns *= 4)
+            total_seq += ns;
+    }
+    const int per = (total_seq + kTreeThreads - 1) / kTreeThreads;
+    const int q0 = min(tid * per, total_seq), q1 = min(q0 + per, total_seq);
+    // depth / offset of sequence position q0
+    int d = t_end, ns_d = ninit, off_d = 0, seq_d = 0;
+    for(int e = 0; e < t_end; ++e)
+        off_d += ns_d, ns_d *= 4;
+    while(d > 0 && q0 >= seq_d + ns_d)
+    {
+        seq_d += ns_d;
+        ns_d >>= 2;
+        off_d -= ns_d;
+        --d;
+    }
+    int mine = 0;
+    {
+        int dd = d, nsd = ns_d, offd = off_d, seqd = seq_d;
+        for(int qq = q0; qq < q1; ++qq)
+        {
+            while(qq >= seqd + nsd)
+                seqd += nsd, nsd >>= 2, offd -= nsd, --dd;
+            const unsigned c = cnt[offd + (qq - seqd)];
+            const unsigned m = c & ~kFlag;
+            mine += m > 0 && (dd == t_end || m == 1u || (c & kFlag));
+        }
+    }
+    // block exclusive scan of `mine`
+    int incl = mine;
+#pragma unroll
+    for(int o = 1; o < 32; o <<= 1)
+    {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if(lane >= o)
+            incl += v;
+    }
+    if(lane == 31)
+        s_warp[wid] = (unsigned)incl;
+    __syncthreads();
+    if(wid == 0)
+    {
+        int v = (int)s_warp[lane], iv = v;
+#pragma unroll
+        for(int o = 1; o < 32; o <<= 1)
+        {
+            const int u = __shfl_up_sync(0xffffffffu, iv, o);
+            if(lane >= o)
+                iv += u;
+        }
+        s_warp[lane] = (unsigned)(iv - v);
+        if(lane == 31)
+            s_created = (unsigned)iv; // total
+    }
+    __syncthreads();
+    int pos = (int)s_warp[wid] + incl - mine;
+    const int total = (int)s_created;
+    unsigned* out = sel + (long long)frame * P.sel_frame_stride + L.sel_off;
+    {
+        int dd = d, nsd = ns_d, offd = off_d, seqd = seq_d;
+        for(int qq = q0; qq < q1; ++qq)
+        {
+            while(qq >= seqd + nsd)
+                seqd += nsd, nsd >>= 2, offd -= nsd, --dd;
+            const unsigned c = cnt[offd + (qq - seqd)];
+            const unsigned m = c & ~kFlag;
+            if(m > 0 && (dd == t_end || m == 1u || (c & kFlag)))
+            {
+                const unsigned b = best[offd + (qq - seqd)];
+                const unsigned ord = 0xffffffu - (b & 0xffffffu);
+                const int cell = ord >> 12, ci = cell / L.ncx, cj = cell - ci * L.ncx;
+                const int y = ci * 64 + ((ord >> 6) & 63) + 3 + kBorder, x = cj * 64 + (ord & 63) + 3 + kBorder;
+                if(pos < L.sel_cap)
+                    out[pos] = (unsigned)y << 20 | (unsigned)x << 8 | (b >> 24); // absolute level coordinates
+                ++pos;
+            }
+        }
+    }
+    if(tid == 0)
+    {
+        C->n_tree = (unsigned)min(total, L.sel_cap);
+        C->passes = (unsigned)passes;
+        if(total > L.sel_cap)
+            C->err = 2;
+    }
+}
+
+// =================================================================================================
+// cv::GaussianBlur(7x7, sigma 2) on u8: OpenCV's fixed-point path, kernel [18 34 48 56 48 34 18] / 256
+// =================================================================================================
+__device__ __forceinline__ int reflect101_d(int p, int n)
+{
+    if(n == 1)
+        return 0;
+    while(p < 0 || p >= n)
+        p = p < 0 ? -p : 2 * n - 2 - p;
+    return p;
+}
+
+__global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
+                                                    uint8_t* __restrict__ blur)
+{
+    __shared__ uint8_t in[38][72];
+    __shared__ unsigned short hs[38][64];
+    const int tid = threadIdx.x;
+    const int l = level_of_gtile(P, blockIdx.x);
+    const DistLevel& L = P.lv[l];
+    const int t = blockIdx.x - L.gtile_base;
+    const int ty = t / L.gtx, tx = t - ty * L.gtx;
+    const int x0 = tx * 64, y0 = ty * 32;
+    const uint8_t* img = pyr + L.img_off + blockIdx.y * L.img_frame_stride;
+    for(int i = tid; i < 38 * 70; i += 256)
+    {
+        const int r = i / 70, c = i - r * 70;
+        const int sy = reflect101_d(y0 + r - 3, L.h), sx = reflect101_d(x0 + c - 3, L.w);
+        in[r][c] = __ldg(img + (long long)sy * L.pitch + sx);
+    }
+    __syncthreads();
+    for(int i = tid; i < 38 * 64; i += 256)
+    {
+        const int r = i >> 6, c = i & 63;
+        const uint8_t* p = &in[r][c];
+        hs[r][c] = (unsigned short)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
+    }
+    __syncthreads();
+    uint8_t* dst = blur + L.img_off + blockIdx.y * L.img_frame_stride;
+    for(int i = tid; i < 32 * 16; i += 256)
+    {
+        const int y = i >> 4, xq = (i & 15) * 4;
+        if(y0 + y >= L.h || x0 + xq >= L.w)
+            continue;
+        unsigned o = 0;
+#pragma unroll
+        for(int j = 0; j < 4; ++j)
+        {
+            const int x = xq + j;
+            const unsigned v = 18u * (hs[y][x] + hs[y + 6][x]) + 34u * (hs[y + 1][x] + hs[y + 5][x]) +
+                               48u * (hs[y + 2][x] + hs[y + 4][x]) + 56u * hs[y + 3][x];
+            o |= ((v + 32768u) >> 16) << (8 * j);
+        }
+        *reinterpret_cast<unsigned*>(dst + (long long)(y0 + y) * L.pitch + x0 + xq) = o;
+    }
+}
+
+// =================================================================================================
+// orientation + descriptor (:543-570, :572-629): one warp per keypoint
+// =================================================================================================
+__device__ __forceinline__ float poly_cos(float v)
+{
+    const float c1 = 0.99940307f, c2 = -0.49558072f, c3 = 0.03679168f;
+    const float v2 = __fmul_rn(v, v);
+    return __fadd_rn(c1, __fmul_rn(v2, __fadd_rn(c2, __fmul_rn(c3, v2))));
+}
+__device__ __forceinline__ float util_cos(float v)
+{
+    const float PI = 3.14159265358979f;
+    const float PI_2 = __fdiv_rn(PI, 2.0f), TWO_PI = __fmul_rn(2.0f, PI), INV_TWO_PI = __fdiv_rn(1.0f, TWO_PI),
+                THREE_PI_2 = __fmul_rn(3.0f, PI_2);
+    v = __fsub_rn(v, __fmul_rn((float)(int)floorf(__fmul_rn(v, INV_TWO_PI)), TWO_PI));
+    v = (0.0f < v) ? v : -v;
+    if(v < PI_2)
+        return poly_cos(v);
+    else if(v < PI)
+        return -poly_cos(__fsub_rn(PI, v));
+    else if(v < THREE_PI_2)
+        return -poly_cos(__fsub_rn(v, PI));
+    else
+        return poly_cos(__fsub_rn(TWO_PI, v));
+}
+
+__global__ void __launch_bounds__(256) k_dist_describe(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
+                                                       const uint8_t* __restrict__ blur, const DistCounters* __restrict__ ctr,
+                                                       const unsigned* __restrict__ sel, mslam_b200_keypoint* __restrict__ out_kp,
+                                                       uint8_t* __restrict__ out_desc, int* __restrict__ out_counts, int out_cap)
+{
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int frame = blockIdx.y;
+    const DistCounters* C = ctr + frame * P.nlevels;
+    int l = 0, base = 0, total = 0;
+    {
+        int acc = 0;
+        bool found = false;
+        for(int i = 0; i < P.nlevels; ++i)
+        {
+            const int n = (int)C[i].n_tree;
+            if(!found && g < acc + n)
+                l = i, base = acc, found = true;
+            acc += n;
+        }
+        total = acc;
+    }
+    if(g == 0 && lane == 0)
+        out_counts[frame] = total;
+    if(g >= total || g >= out_cap)
+        return;
+    const DistLevel& L = P.lv[l];
+    const unsigned r = sel[(long long)frame * P.sel_frame_stride + L.sel_off + (g - base)];
+    const int x = (r >> 8) & 0xfff, y = r >> 20;
+    const uint8_t* img = pyr + L.img_off + frame * L.img_frame_stride;
+    // intensity-centroid moments over the radius-15 disc, lane = column u
+    int m10 = 0, m01 = 0;
+    {
+        const int u = lane - 15;
+        const int au = u < 0 ? -u : u;
+        // u_max of orb_impl::orb_impl (:521-541), packed 4 bits per |v| (v = 0..15): 15 15 15 15 14 14 14 13 13 12 11 10 9 8 6 3
+        const unsigned long long umax = 0x3689ABCDDEEEFFFFull;
+        if(lane < 31)
+        {
+            const uint8_t* c = img + (long long)y * L.pitch + x + u;
+#pragma unroll 1
+            for(int v = -15; v <= 15; ++v)
+            {
+                const int av = v < 0 ? -v : v;
+                if(au <= (int)((umax >> (4 * av)) & 15))
+                {
+                    const int val = __ldg(c + (long long)v * L.pitch);
+                    m10 += u * val;
+                    m01 += v * val;
+                }
+            }
+        }
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+    // keypt.angle * M_PI / 180.0 in double, then float (:574)
+    const float rad = (float)((double)angle * 3.14159265358979323846 / 180.0);
+    const float ca = util_cos(rad), sa = util_cos(__fsub_rn(__fdiv_rn(3.14159265358979f, 2.0f), rad));
+    const uint8_t* bc = blur + L.img_off + frame * L.img_frame_stride + (long long)y * L.pitch + x;
+    unsigned byte = 0;
+#pragma unroll
+    for(int b = 0; b < 8; ++b)
+    {
+        const char4 p = reinterpret_cast<const char4*>(g_pairs)[lane * 8 + b];
+        const float x0 = (float)p.x, y0 = (float)p.y, x1 = (float)p.z, y1 = (float)p.w;
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
+        const int v0 = __ldg(bc + (long long)r0 * L.pitch + c0), v1 = __ldg(bc + (long long)r1 * L.pitch + c1);
+        byte |= (unsigned)(v0 < v1) << b;
+    }
+    out_desc[((long long)frame * out_cap + g) * 32 + lane] = (uint8_t)byte;
+    if(lane == 0)
+    {
+        mslam_b200_keypoint k;
+        const float px = (float)x, py = (float)y;
+        k.x = l == 0 ? px : __fmul_rn(px, L.scale);
+        k.y = l == 0 ? py : __fmul_rn(py, L.scale);
+        k.size = L.size;
+        k.angle = angle;
+        k.response = (float)(r & 0xff);
+        k.octave = l;
+        out_kp[(long long)frame * out_cap + g] = k;
+    }
+}
+
+// =================================================================================================
+// host side
+// =================================================================================================
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// cv::resize INTER_LINEAR coefficient tables (OpenCV resize.cpp), built exactly as OpenCV builds them
+void linear_taps_x(int src, int dst, XTap* t)
+{
+    const double inv_scale = (double)dst / (double)src, scale = 1.0 / inv_scale;
+    for(int d = 0; d < dst; ++d)
+    {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= (float)s;
+        if(s < 0)
+            f = 0.f, s = 0;
+        if(s >= src - 1)
+            f = 0.f, s = src - 1;
+        t[d].ofs = s;
+        t[d].a = (unsigned)lrintf((1.f - f) * 2048.f) | (unsigned)lrintf(f * 2048.f) << 16;
+    }
+}
+void linear_taps_y(int src, int dst, YTap* t)
+{
+    const double inv_scale = (double)dst / (double)src, scale = 1.0 / inv_scale;
+    for(int d = 0; d < dst; ++d)
+    {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        const int s = (int)std::floor(f);
+        f -= (float)s;
+        t[d].sy0 = std::min(std::max(s, 0), src - 1);
+        t[d].sy1 = std::min(std::max(s + 1, 0), src - 1);
+        t[d].b = (unsigned)lrintf((1.f - f) * 2048.f) | (unsigned)lrintf(f * 2048.f) << 16;
+        t[d].pad = 0;
+    }
+}
+
+struct DistGeometry
+{
+    DistParams P;
+    size_t pyr_bytes;
+    long long cand_elems, tree_words;
+    int sel_elems, kp_bound;
+    size_t tree_smem;
+    std::vector<XTap> xtab;
+    std::vector<YTap> ytab;
+    bool ok;
+};
+
+void build_dist_geometry(const mslam_b200_dist_config& cfg, int W, int H, DistGeometry* g)
+{
+    DistParams& P = g->P;
+    memset(&P, 0, sizeof(P));
+    g->ok = false;
+    g->xtab.clear();
+    g->ytab.clear();
+    P.nlevels = cfg.nlevels;
+    P.W = W, P.H = H;
+    P.ini_thr = cfg.ini_fast_threshold;
+    P.min_thr = cfg.min_fast_threshold;
+    P.min_size = (unsigned)cfg.min_size;
+    size_t off = 0, tree_smem = 0;
+    long long coff = 0, toff = 0;
+    int cells = 0, gtiles = 0, soff = 0, xo = 0, yo = 0;
+    float s = 1.0f;
+    for(int l = 0; l < cfg.nlevels; ++l)
+    {
+        DistLevel& L = P.lv[l];
+        if(l > 0)
+            s = cfg.scale_factor * s; // orb_params::calc_scale_factors (:413-421)
+        L.scale = s;
+        L.size = (float)(unsigned)(31 * s); // fast_patch_size_ * scale_factor, truncated (:931)
+        const double sc = (double)s;
+        L.w = l == 0 ? W : (int)std::round(W * 1.0 / sc); // compute_image_pyramid (:835-836)
+        L.h = l == 0 ? H : (int)std::round(H * 1.0 / sc);
+        if(L.w < 2 * kBorder || L.h < 2 * kBorder)
+            return; // the reference's unsigned border arithmetic underflows
+        L.pitch = (int)align_up((size_t)L.w + 4, 64);
+        L.img_off = (long long)off;
+        L.img_frame_stride = (long long)align_up((size_t)L.pitch * L.h, 256);
+        off += (size_t)L.img_frame_stride * cfg.max_batch;
+        // cells: the region cv::FAST can report in, [22, w-22) x [22, h-22), in 64-px steps
+        const int rw = L.w - 2 * kFastOrg, rh = L.h - 2 * kFastOrg;
+        L.ncx = rw > 0 ? (rw + kCell - 1) / kCell : 0;
+        L.ncy = rh > 0 ? (rh + kCell - 1) / kCell : 0;
+        if(L.ncx == 0 || L.ncy == 0)
+            L.ncx = L.ncy = 0;
+        L.cell_base = cells;
+        cells += L.ncx * L.ncy;
+        int cap = 0;
+        for(int i = 0; i < L.ncy; ++i)
+            for(int j = 0; j < L.ncx; ++j)
+            {
+                const int cw = std::min(kCell, rw - j * kCell), ch = std::min(kCell, rh - i * kCell);
+                cap += ((cw + 1) / 2) * ((ch + 1) / 2); // strict 3x3 maxima
+            }
+        L.cand_cap = cap;
+        L.cand_off = coff;
+        coff += (long long)align_up((size_t)cap, 4);
+        L.gtx = (L.w + 63) / 64, L.gty = (L.h + 31) / 32;
+        L.gtile_base = gtiles;
+        gtiles += L.gtx * L.gty;
+        // tree geometry (initialize_nodes, :989-1011)
+        const int tw = L.w - 2 * kBorder, th = L.h - 2 * kBorder;
+        L.ninit_x = L.ninit_y = 1;
+        L.delta_x = tw, L.delta_y = th;
+        L.depth = 0;
+        if(tw > 0 && th > 0)
+        {
+            const double ratio = (double)tw / th;
+            if(ratio > 1)
+            {
+                L.ninit_x = (int)(unsigned)std::round(ratio);
+                L.delta_x = (double)tw / (unsigned)L.ninit_x;
+                L.delta_y = th;
+            }
+            else
+            {
+                L.ninit_y = (int)(unsigned)std::round(1 / ratio);
+                L.delta_x = tw; // max_x - min_y in the reference (:1018); min_x == min_y == 19
+                L.delta_y = (double)th / (unsigned)L.ninit_y;
+            }
+            if(L.ninit_x * L.ninit_y > kMaxInit)
+                return;
+            // deepest depth: descend the distinct node shapes until every one stops by area
+            std::set<std::pair<int, int>> shapes;
+            for(int iy = 0; iy < L.ninit_y; ++iy)
+                for(int ix = 0; ix < L.ninit_x; ++ix)
+                    shapes.insert({(int)(L.delta_x * (ix + 1)) - (int)(L.delta_x * ix), (int)(L.delta_y * (iy + 1)) - (int)(L.delta_y * iy)});
+            int depth = 0;
+            for(;; ++depth)
+            {
+                std::set<std::pair<int, int>> next;
+                for(const auto& sh : shapes)
+                {
+                    const unsigned area = (unsigned)(sh.first * sh.second);
+                    if((float)area * s * s <= (float)P.min_size)
+                        continue;
+                    const int hx = (sh.first + 1) / 2, hy = (sh.second + 1) / 2;
+                    const int xs[2] = {hx, sh.first - hx}, ys[2] = {hy, sh.second - hy};
+                    for(int a = 0; a < 2; ++a)
+                        for(int b = 0; b < 2; ++b)
+                            next.insert({xs[a], ys[b]});
+                }
+                if(next.empty() || depth >= 11)
+                    break;
+                shapes.swap(next);
+            }
+            L.depth = depth;
+        }
+        long long slots = 0, ns = (long long)L.ninit_x * L.ninit_y;
+        for(int d = 0; d <= L.depth; ++d, ns *= 4)
+            slots += ns;
+        if(slots > (1 << 24))
+            return;
+        L.tree_slots = (int)slots;
+        L.tree_in_smem = (size_t)slots * 8 <= (size_t)kTreeSmemBudget;
+        L.tree_off = toff;
+        if(L.tree_in_smem)
+            tree_smem = std::max(tree_smem, (size_t)slots * 8);
+        else
+            toff += 2 * slots;
+        long long deepest = (long long)L.ninit_x * L.ninit_y;
+        for(int d = 0; d < L.depth; ++d)
+            deepest *= 4;
+        L.sel_cap = (int)std::min<long long>(deepest, L.cand_cap);
+        L.sel_off = soff;
+        soff += (int)align_up((size_t)L.sel_cap, 4);
+        L.xtab_off = xo, L.ytab_off = yo;
+        if(l > 0)
+        {
+            g->xtab.resize(xo + L.w);
+            g->ytab.resize(yo + L.h);
+            linear_taps_x(P.lv[l - 1].w, L.w, g->xtab.data() + xo);
+            linear_taps_y(P.lv[l - 1].h, L.h, g->ytab.data() + yo);
+            xo += L.w, yo += L.h;
+        }
+    }
+    P.total_cells = cells;
+    P.total_gtiles = gtiles;
+    P.cand_frame_stride = std::max<long long>(coff, 4);
+    P.tree_frame_stride = toff;
+    P.sel_frame_stride = std::max(soff, 4);
+    g->pyr_bytes = off;
+    g->cand_elems = P.cand_frame_stride;
+    g->tree_words = toff;
+    g->sel_elems = P.sel_frame_stride;
+    g->kp_bound = soff;
+    g->tree_smem = tree_smem;
+    g->ok = true;
+}
+} // namespace
+
+struct mslam_b200_dist
+{
+    mslam_b200_dist_config cfg;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    long long launches = 0;
+    char err[512] = {0};
+    int geo_w = 0, geo_h = 0;
+    DistParams P;
+    size_t tree_smem = 0, tree_smem_max = 0;
+    int kp_cap = 0;
+    uint8_t *d_bgr = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
+    size_t pyr_bytes = 0;
+    XTap* d_xtab = nullptr;
+    YTap* d_ytab = nullptr;
+    int xtab_cap = 0, ytab_cap = 0;
+    unsigned *d_cand = nullptr, *d_sel = nullptr, *d_tree = nullptr;
+    long long cand_elems = 0, tree_words = 0;
+    int sel_elems = 0;
+    DistCounters* d_ctr = nullptr;
+    mslam_b200_keypoint* d_kp = nullptr;
+    uint8_t* d_desc = nullptr;
+    int* d_counts = nullptr;
+    int* h_counts = nullptr;
+    DistCounters* h_ctr = nullptr;
+    int last_frames = 0;
+    bool timing = false;
+    cudaEvent_t ev[7] = {nullptr};
+    double t_ms[6] = {0};
+};
+
+static int dist_fail(mslam_b200_dist* ctx, cudaError_t e, const char* what)
+{
+    if(ctx)
+        snprintf(ctx->err, sizeof(ctx->err), "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+    return MSLAM_B200_E_CUDA;
+}
+#define DIST_CUDA_OK(expr)                                                                                             \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        cudaError_t e__ = (expr);                                                                                      \
+        if(e__ != cudaSuccess)                                                                                         \
+            return dist_fail(ctx, e__, #expr);                                                                         \
+    } while(0)
+
+static int dist_set_geometry(mslam_b200_dist* ctx, int W, int H)
+{
+    if(W == ctx->geo_w && H == ctx->geo_h)
+        return MSLAM_B200_OK;
+    if(W < 1 || H < 1 || W > ctx->cfg.max_width || H > ctx->cfg.max_height || W > 4095 || H > 4095)
+        return MSLAM_B200_E_INVALID;
+    DistGeometry g;
+    build_dist_geometry(ctx->cfg, W, H, &g);
+    if(!g.ok)
+        return MSLAM_B200_E_INVALID;
+    if(g.pyr_bytes > ctx->pyr_bytes || g.cand_elems > ctx->cand_elems || g.tree_words > ctx->tree_words ||
+       g.sel_elems > ctx->sel_elems || (int)g.xtab.size() > ctx->xtab_cap || (int)g.ytab.size() > ctx->ytab_cap ||
+       g.tree_smem > ctx->tree_smem_max)
+        return MSLAM_B200_E_INVALID;
+    if(!g.xtab.empty())
+    {
+        DIST_CUDA_OK(cudaMemcpyAsync(ctx->d_xtab, g.xtab.data(), g.xtab.size() * sizeof(XTap), cudaMemcpyHostToDevice, ctx->stream));
+        DIST_CUDA_OK(cudaMemcpyAsync(ctx->d_ytab, g.ytab.data(), g.ytab.size() * sizeof(YTap), cudaMemcpyHostToDevice, ctx->stream));
+        DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->P = g.P;
+    ctx->P.kp_cap = ctx->kp_cap;
+    ctx->tree_smem = g.tree_smem;
+    ctx->geo_w = W, ctx->geo_h = H;
+    return MSLAM_B200_OK;
+}
+
+extern "C" {
+
+void mslam_b200_dist_default_config(mslam_b200_dist_config* cfg)
+{
+    if(!cfg)
+        return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->struct_size = (int)sizeof(*cfg);
+    cfg->max_width = 640;
+    cfg->max_height = 480;
+    cfg->max_batch = 1;
+    cfg->nlevels = 8;
+    cfg->scale_factor = 1.2f;
+    cfg->ini_fast_threshold = 20;
+    cfg->min_fast_threshold = 7;
+    cfg->min_size = 1000;
+}
+
+void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
+{
+    if(!ctx)
+        return;
+    cudaSetDevice(ctx->cfg.device);
+    if(ctx->stream)
+        cudaStreamSynchronize(ctx->stream);
+    void* dev[] = {ctx->d_bgr, ctx->d_pyr, ctx->d_blur, ctx->d_xtab, ctx->d_ytab, ctx->d_cand, ctx->d_sel, ctx->d_tree,
+                   ctx->d_ctr, ctx->d_kp,  ctx->d_desc, ctx->d_counts};
+    for(void* p : dev)
+        if(p)
+            cudaFree(p);
+    if(ctx->h_counts)
+        cudaFreeHost(ctx->h_counts);
+    if(ctx->h_ctr)
+        cudaFreeHost(ctx->h_ctr);
+    for(cudaEvent_t e : ctx->ev)
+        if(e)
+            cudaEventDestroy(e);
+    if(ctx->own_stream && ctx->stream)
+        cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist** out)
+{
+    if(!cfg_in || !out || cfg_in->struct_size != (int)sizeof(mslam_b200_dist_config))
+        return MSLAM_B200_E_INVALID;
+    *out = nullptr;
+    const mslam_b200_dist_config& c = *cfg_in;
+    if(c.max_width < 2 * kBorder || c.max_height < 2 * kBorder || c.max_width > 4095 || c.max_height > 4095 || c.max_batch < 1 ||
+       c.nlevels < 1 || c.nlevels > kMaxLevels || !(c.scale_factor > 1.f) || c.ini_fast_threshold < 1 ||
+       c.ini_fast_threshold > 254 || c.min_fast_threshold < 1 || c.min_fast_threshold > c.ini_fast_threshold || c.min_size < 1)
+        return MSLAM_B200_E_INVALID;
+    int ndev = 0;
+    if(cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || c.device < 0 || c.device >= ndev)
+        return MSLAM_B200_E_CUDA; // no CPU fallback
+    mslam_b200_dist* ctx = new(std::nothrow) mslam_b200_dist;
+    if(!ctx)
+        return MSLAM_B200_E_NOMEM;
+    ctx->cfg = c;
+    DistGeometry g;
+    build_dist_geometry(c, c.max_width, c.max_height, &g);
+    if(!g.ok)
+    {
+        delete ctx;
+        return MSLAM_B200_E_INVALID;
+    }
+    ctx->kp_cap = c.max_keypoints > 0 ? c.max_keypoints : g.kp_bound;
+    auto fail = [&](int rc) {
+        mslam_b200_dist_destroy(ctx);
+        return rc;
+    };
+#define CREATE_OK(expr)                                                                                                \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        if((expr) != cudaSuccess)                                                                                      \
+            return fail(MSLAM_B200_E_CUDA);                                                                            \
+    } while(0)
+    CREATE_OK(cudaSetDevice(c.device));
+    if(c.stream)
+        ctx->stream = (cudaStream_t)c.stream;
+    else
+    {
+        CREATE_OK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        ctx->own_stream = true;
+    }
+    for(auto& e : ctx->ev)
+        CREATE_OK(cudaEventCreate(&e));
+    const size_t B = (size_t)c.max_batch;
+    // a little slack on the geometry-dependent sizes: level sizes are monotone in (W, H) but row pitches round up
+    ctx->pyr_bytes = g.pyr_bytes + 4096;
+    ctx->cand_elems = g.cand_elems + 64;
+    ctx->tree_words = g.tree_words;
+    ctx->sel_elems = g.sel_elems + 64;
+    ctx->xtab_cap = (int)g.xtab.size() + 16;
+    ctx->ytab_cap = (int)g.ytab.size() + 16;
+    ctx->tree_smem_max = g.tree_smem;
+    CREATE_OK(cudaMalloc(&ctx->d_bgr, B * c.max_width * c.max_height * 3));
+    CREATE_OK(cudaMalloc(&ctx->d_pyr, ctx->pyr_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_blur, ctx->pyr_bytes));
+    CREATE_OK(cudaMemset(ctx->d_pyr, 0, ctx->pyr_bytes));
+    CREATE_OK(cudaMemset(ctx->d_blur, 0, ctx->pyr_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_xtab, ctx->xtab_cap * sizeof(XTap)));
+    CREATE_OK(cudaMalloc(&ctx->d_ytab, ctx->ytab_cap * sizeof(YTap)));
+    CREATE_OK(cudaMalloc(&ctx->d_cand, B * ctx->cand_elems * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_sel, B * ctx->sel_elems * sizeof(unsigned)));
+    if(ctx->tree_words > 0)
+        CREATE_OK(cudaMalloc(&ctx->d_tree, B * ctx->tree_words * sizeof(unsigned)));
+    CREATE_OK(cudaMalloc(&ctx->d_ctr, B * kMaxLevels * sizeof(DistCounters)));
+    CREATE_OK(cudaMalloc(&ctx->d_kp, B * ctx->kp_cap * sizeof(mslam_b200_keypoint)));
+    CREATE_OK(cudaMalloc(&ctx->d_desc, B * ctx->kp_cap * 32));
+    CREATE_OK(cudaMalloc(&ctx->d_counts, B * sizeof(int)));
+    CREATE_OK(cudaMallocHost(&ctx->h_counts, B * sizeof(int)));
+    CREATE_OK(cudaMallocHost(&ctx->h_ctr, B * kMaxLevels * sizeof(DistCounters)));
+    ctx->tree_smem_max = kTreeSmemBudget; // any level that fits the budget runs from shared memory
+    CREATE_OK(cudaFuncSetAttribute(k_dist_tree, cudaFuncAttributeMaxDynamicSharedMemorySize, kTreeSmemBudget));
+#undef CREATE_OK
+    *out = ctx;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_dist_synchronize(mslam_b200_dist* ctx)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    return MSLAM_B200_OK;
+}
+
+const char* mslam_b200_dist_last_cuda_error(mslam_b200_dist* ctx) { return ctx ? ctx->err : ""; }
+long long mslam_b200_dist_launch_count(mslam_b200_dist* ctx) { return ctx ? ctx->launches : 0; }
+int mslam_b200_dist_keypoint_capacity(mslam_b200_dist* ctx) { return ctx ? ctx->kp_cap : 0; }
+
+int mslam_b200_dist_level_geometry(mslam_b200_dist* ctx, int width, int height, int* w, int* h, float* scale)
+{
+    if(!ctx || width < 1 || height < 1)
+        return MSLAM_B200_E_INVALID;
+    DistGeometry g;
+    build_dist_geometry(ctx->cfg, width, height, &g);
+    if(!g.ok)
+        return MSLAM_B200_E_INVALID;
+    for(int l = 0; l < ctx->cfg.nlevels; ++l)
+    {
+        if(w) w[l] = g.P.lv[l].w;
+        if(h) h[l] = g.P.lv[l].h;
+        if(scale) scale[l] = g.P.lv[l].scale;
+    }
+    return MSLAM_B200_OK;
+}
+
+// enqueue the whole detector for n_frames frames already in d_bgr
+static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, mslam_b200_keypoint* d_kp, uint8_t* d_desc,
+                    int capacity, int* d_counts)
+{
+    DistParams& P = ctx->P;
+    P.n_frames = n_frames;
+    cudaStream_t st = ctx->stream;
+    const bool tm = ctx->timing;
+    DIST_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, (size_t)n_frames * P.nlevels * sizeof(DistCounters), st));
+    if(tm)
+        cudaEventRecord(ctx->ev[0], st);
+    {
+        // toGrayScale into level 0 (k_gray16 / k_gray1 of the ORB path; same RgbFrame layout, frame.cpp:6-27)
+        PipeParams G;
+        memset(&G, 0, sizeof(G));
+        G.nlevels = 1, G.n_frames = n_frames, G.W = P.W, G.H = P.H, G.frame0 = 0;
+        G.lv[0].w = P.W, G.lv[0].h = P.H, G.lv[0].pitch = P.lv[0].pitch;
+        G.lv[0].img_off = P.lv[0].img_off, G.lv[0].img_frame_stride = P.lv[0].img_frame_stride;
+        launch_gray(st, d_bgr, ctx->d_pyr, G, &ctx->launches);
+    }
+    if(tm)
+        cudaEventRecord(ctx->ev[1], st);
+    for(int l = 1; l < P.nlevels; ++l)
+    {
+        const DistLevel &S = P.lv[l - 1], &D = P.lv[l];
+        k_dist_resize<<<dim3((D.w + 255) / 256, (D.h + 3) / 4, n_frames), 256, 0, st>>>(
+            ctx->d_pyr + S.img_off, S.pitch, S.img_frame_stride, S.w, ctx->d_pyr + D.img_off, D.pitch, D.img_frame_stride, D.w,
+            D.h, ctx->d_xtab + D.xtab_off, ctx->d_ytab + D.ytab_off);
+        ++ctx->launches;
+    }
+    if(tm)
+        cudaEventRecord(ctx->ev[2], st);
+    if(P.total_cells > 0)
+    {
+        k_dist_fast<<<dim3(P.total_cells, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_cand, ctx->d_ctr);
+        ++ctx->launches;
+    }
+    if(tm)
+        cudaEventRecord(ctx->ev[3], st);
+    k_dist_tree<<<dim3(P.nlevels, n_frames), kTreeThreads, ctx->tree_smem, st>>>(P, ctx->d_cand, ctx->d_ctr, ctx->d_sel, ctx->d_tree);
+    ++ctx->launches;
+    if(tm)
+        cudaEventRecord(ctx->ev[4], st);
+    k_dist_gauss<<<dim3(P.total_gtiles, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_blur);
+    ++ctx->launches;
+    if(tm)
+        cudaEventRecord(ctx->ev[5], st);
+    const int slots = std::min(capacity, ctx->kp_cap);
+    k_dist_describe<<<dim3((std::max(slots, 1) + 7) / 8, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel,
+                                                                                  d_kp, d_desc, d_counts, capacity);
+    ++ctx->launches;
+    if(tm)
+        cudaEventRecord(ctx->ev[6], st);
+    DIST_CUDA_OK(cudaGetLastError());
+    if(tm)
+    {
+        DIST_CUDA_OK(cudaEventSynchronize(ctx->ev[6]));
+        for(int i = 0; i < 6; ++i)
+        {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]);
+            ctx->t_ms[i] += ms;
+        }
+    }
+    ctx->last_frames = n_frames;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_dist_detect_batch_dev(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, int width, int height,
+                                     mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity, int* d_counts)
+{
+    if(!ctx || !d_bgr || !d_kp || !d_desc || !d_counts || n_frames < 1 || n_frames > ctx->cfg.max_batch || capacity < 1)
+        return MSLAM_B200_E_INVALID;
+    DIST_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    const int rc = dist_set_geometry(ctx, width, height);
+    if(rc)
+        return rc;
+    return dist_run(ctx, d_bgr, n_frames, d_kp, d_desc, capacity, d_counts);
+}
+
+int mslam_b200_dist_detect_batch(mslam_b200_dist* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
+                                 int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(!ctx || !frames || !n_out || n_frames < 1 || n_frames > ctx->cfg.max_batch || capacity < 0 ||
+       (capacity > 0 && (!out_kp || !out_desc)) || stride_bytes < 3 * width)
+        return MSLAM_B200_E_INVALID;
+    for(int i = 0; i < n_frames; ++i)
+        if(!frames[i])
+            return MSLAM_B200_E_INVALID;
+    DIST_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    int rc = dist_set_geometry(ctx, width, height);
+    if(rc)
+        return rc;
+    const size_t fbytes = (size_t)width * height * 3;
+    for(int i = 0; i < n_frames; ++i)
+        DIST_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * fbytes, (size_t)width * 3, frames[i], (size_t)stride_bytes, (size_t)width * 3,
+                                       height, cudaMemcpyHostToDevice, ctx->stream));
+    rc = dist_run(ctx, ctx->d_bgr, n_frames, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
+    if(rc)
+        return rc;
+    DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_counts, ctx->d_counts, n_frames * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_ctr, ctx->d_ctr, (size_t)n_frames * ctx->P.nlevels * sizeof(DistCounters),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    rc = MSLAM_B200_OK;
+    for(int i = 0; i < n_frames * ctx->P.nlevels; ++i)
+        if(ctx->h_ctr[i].err)
+            rc = MSLAM_B200_E_CAPACITY; // an internal list overflowed (cannot happen: capacities are upper bounds)
+    for(int i = 0; i < n_frames; ++i)
+    {
+        const int n = ctx->h_counts[i];
+        n_out[i] = n;
+        if(n > capacity || n > ctx->kp_cap)
+            rc = MSLAM_B200_E_CAPACITY;
+        const int m = std::min(n, std::min(capacity, ctx->kp_cap));
+        if(m > 0)
+        {
+            DIST_CUDA_OK(cudaMemcpyAsync(out_kp + (size_t)i * capacity, ctx->d_kp + (size_t)i * ctx->kp_cap,
+                                         (size_t)m * sizeof(mslam_b200_keypoint), cudaMemcpyDeviceToHost, ctx->stream));
+            DIST_CUDA_OK(cudaMemcpyAsync(out_desc + (size_t)i * capacity * 32, ctx->d_desc + (size_t)i * ctx->kp_cap * 32, (size_t)m * 32,
+                                         cudaMemcpyDeviceToHost, ctx->stream));
+        }
+    }
+    DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    return rc;
+}
+
+int mslam_b200_dist_detect(mslam_b200_dist* ctx, const uint8_t* bgr, int width, int height, int stride_bytes,
+                           mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    const uint8_t* frames[1] = {bgr};
+    return mslam_b200_dist_detect_batch(ctx, frames, 1, width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
+}
+
+int mslam_b200_dist_debug_read(mslam_b200_dist* ctx, int stage, int frame, int level, void* out, size_t bytes)
+{
+    if(!ctx || !out || frame < 0 || frame >= ctx->cfg.max_batch || level < 0 || ctx->geo_w == 0 || level >= ctx->P.nlevels)
+        return MSLAM_B200_E_INVALID;
+    DIST_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    const DistLevel& L = ctx->P.lv[level];
+    if(stage == MSLAM_B200_DIST_PYRAMID || stage == MSLAM_B200_DIST_BLURRED)
+    {
+        if(bytes < (size_t)L.w * L.h)
+            return MSLAM_B200_E_INVALID;
+        const uint8_t* src = (stage == MSLAM_B200_DIST_PYRAMID ? ctx->d_pyr : ctx->d_blur) + L.img_off + frame * L.img_frame_stride;
+        DIST_CUDA_OK(cudaMemcpy2D(out, L.w, src, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+        return MSLAM_B200_OK;
+    }
+    if(stage >= MSLAM_B200_DIST_N_FAST && stage <= MSLAM_B200_DIST_PASSES)
+    {
+        if(bytes < sizeof(int))
+            return MSLAM_B200_E_INVALID;
+        DistCounters c;
+        DIST_CUDA_OK(cudaMemcpy(&c, ctx->d_ctr + frame * ctx->P.nlevels + level, sizeof(c), cudaMemcpyDeviceToHost));
+        *(int*)out = (int)(stage == MSLAM_B200_DIST_N_FAST ? c.n_fast : stage == MSLAM_B200_DIST_N_TREE ? c.n_tree : c.passes);
+        return MSLAM_B200_OK;
+    }
+    return MSLAM_B200_E_INVALID;
+}
+
+int mslam_b200_dist_stage_times(mslam_b200_dist* ctx, int enable, double* ms6)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if(ms6)
+        for(int i = 0; i < 6; ++i)
+            ms6[i] = ctx->t_ms[i];
+    for(double& v : ctx->t_ms)
+        v = 0;
+    ctx->timing = enable != 0;
+    return MSLAM_B200_OK;
+}
+
+} // extern "C"

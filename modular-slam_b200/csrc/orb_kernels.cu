@@ -947,34 +947,6 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
 //   (non-FMA f32 polynomial), then the 256 rotated BRIEF tests on the BLURRED level; lane i produces
 //   descriptor byte i.
 // =================================================================================================
-__device__ __forceinline__ float fast_atan2_deg(float y, float x)
-{
-    const float p1 = __int_as_float(0x4265226f), p3 = __int_as_float(0xc19556ee), p5 = __int_as_float(0x410e9fbf),
-                p7 = __int_as_float(0xc0228ad9);
-    const float eps = 2.2204460492503131e-16f; // (float)DBL_EPSILON
-    const float ax = fabsf(x), ay = fabsf(y);
-    float a, c, c2;
-    if(ax >= ay)
-    {
-        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
-        c2 = __fmul_rn(c, c);
-        a = __fmul_rn(
-            __fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
-    }
-    else
-    {
-        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
-        c2 = __fmul_rn(c, c);
-        a = __fsub_rn(
-            90.f,
-            __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
-    }
-    if(x < 0)
-        a = __fsub_rn(180.f, a);
-    if(y < 0)
-        a = __fsub_rn(360.f, a);
-    return a;
-}
 
 constexpr int OD_SLOTS = 32; // keypoints per CTA: 8 warps x 4 rounds
 constexpr int IC_WORDS = 31 * 9; // aligned words covering the 31 x 31 orientation patch (any alignment)

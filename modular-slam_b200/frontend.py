@@ -53,3 +53,20 @@ class OrbB200Matcher:
         out = np.zeros(len(fi), DESCRIPTOR_MATCH_DTYPE)
         out["fromIndex"], out["toIndex"] = fi, ti
         return out
+
+
+class DistributedOrbB200Detector:
+    """drop-in for mslam::DistributedOrbOpenCvDetector (distributed_cv_feature.cpp:1181-1222): Keypoint::id = index"""
+
+    def __init__(self, ctx=None, **cfg):
+        from .capi import DistContext
+        self.ctx = ctx or DistContext(**cfg)
+
+    def detect(self, frame: RgbFrame):
+        kp, desc = self.ctx.detect(frame.data.reshape(frame.height, frame.width, 3))
+        out = np.zeros(len(kp), ORB_KEYPOINT_DTYPE)
+        out["id"] = np.arange(len(kp), dtype=np.uint64)  # distributed_cv_feature.cpp:1201-1205
+        out["coordinates"][:, 0] = kp["x"]
+        out["coordinates"][:, 1] = kp["y"]
+        out["descriptor"] = desc
+        return out

@@ -16,8 +16,8 @@ _SO = os.path.join(_HERE, "liborb_oracle.so")
 
 
 def build(force=False):
-    src = os.path.join(_HERE, "orb_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.c", "dist_orb_oracle.c")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(s) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
     return _SO
 
@@ -50,6 +50,10 @@ def lib():
         _lib.orc_fast_atan2.restype = C.c_float
         _lib.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
         _lib.orc_ic_angle.restype = C.c_float
+        _lib.orc_dist_cos.restype = C.c_float
+        _lib.orc_dist_cos.argtypes = [C.c_float]
+        _lib.orc_dist_sin.restype = C.c_float
+        _lib.orc_dist_sin.argtypes = [C.c_float]
     return _lib
 
 
@@ -286,3 +290,140 @@ def backproject(xy, depth, cx, cy, fx, fy, factor):
                               C.c_double(cx), C.c_double(cy), C.c_double(fx), C.c_double(fy), C.c_float(factor), _p(xyz),
                               _p(valid))
     return xyz[:n], valid[:n]
+
+
+# ---- DistributedOrbOpenCvDetector (distributed_cv_feature.cpp), SURVEY 8(f) f1: dist_orb_oracle.c -----------------------
+class DistParams(C.Structure):
+    _fields_ = [("nlevels", C.c_int), ("ini_fast_thr", C.c_int), ("min_fast_thr", C.c_int), ("min_size", C.c_int),
+                ("scale_factor", C.c_float)]
+
+
+class DistDumps(C.Structure):
+    _fields_ = [("pyr", C.c_void_p), ("blurred", C.c_void_p), ("n_fast", C.c_void_p), ("n_tree", C.c_void_p),
+                ("passes", C.c_void_p)]
+
+
+def dist_default_params(nlevels=8, ini_fast_thr=20, min_fast_thr=7, min_size=1000, scale_factor=1.2):
+    """orb_params("orb", 1.2f, 8, 20, 7) + OrbExtractorPimpl(params, 1000)  (distributed_cv_feature.cpp:1184-1186)"""
+    return DistParams(nlevels, ini_fast_thr, min_fast_thr, min_size, scale_factor)
+
+
+def dist_level_geometry(W, H, nlevels=8, scale_factor=1.2):
+    w = np.zeros(nlevels, np.int32)
+    h = np.zeros(nlevels, np.int32)
+    s = np.zeros(nlevels, np.float32)
+    lib().orc_dist_level_geometry(W, H, nlevels, C.c_float(scale_factor), _p(w), _p(h), _p(s))
+    return w, h, s
+
+
+def resize_linear(img, dw, dh):
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_linear(_p(img), img.shape[1], img.shape[0], _p(out), dw, dh)
+    return out
+
+
+def fast_subimage(img, thr):
+    """cv::FAST(img, thr, nonmax=True) -> [n, 3] (x, y, score), raster order"""
+    img = np.ascontiguousarray(img, np.uint8)
+    cap = img.size // 4 + 16
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orc_fast_subimage(_p(img), img.shape[1], img.shape[1], img.shape[0], thr, _p(out), cap)
+    return out[:n].copy()
+
+
+def dist_fast_cells(img, ini_thr=20, min_thr=7):
+    img = np.ascontiguousarray(img, np.uint8)
+    cap = img.size // 4 + 64
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orc_dist_fast_cells(_p(img), img.shape[1], img.shape[0], ini_thr, min_thr, _p(out), cap)
+    return out[:n].copy()
+
+
+def dist_tree(xys, w, h, scale_factor, min_size=1000):
+    """distribute_keypoints_via_tree on a level of size (w, h) -> (kept indices in list order, passes)"""
+    xys = np.ascontiguousarray(xys, np.int32)
+    n = len(xys)
+    out = np.empty(max(n, 1), np.int32)
+    passes = C.c_int(0)
+    if n == 0:
+        return out[:0], 0
+    m = lib().orc_dist_tree(_p(xys), n, 19, w - 19, 19, h - 19, C.c_float(scale_factor), C.c_uint(min_size), _p(out),
+                            C.byref(passes))
+    return out[:m].copy(), passes.value
+
+
+def gauss7_u8(img):
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty_like(img)
+    lib().orc_gauss7_u8(_p(img), img.shape[1], img.shape[0], _p(out))
+    return out
+
+
+def dist_cos(v):
+    return np.float32(lib().orc_dist_cos(C.c_float(v)))
+
+
+def dist_sin(v):
+    return np.float32(lib().orc_dist_sin(C.c_float(v)))
+
+
+def dist_describe(blurred, cx, cy, angle_deg):
+    blurred = np.ascontiguousarray(blurred, np.uint8)
+    out = np.empty(32, np.uint8)
+    lib().orc_dist_describe(_p(blurred), blurred.shape[1], int(cx), int(cy), C.c_float(angle_deg), _p(out))
+    return out
+
+
+def dist_umax():
+    u = np.zeros(16, np.int32)
+    lib().orc_dist_umax(_p(u))
+    return u
+
+
+def dist_detect_gray(gray_img, params=None, cap=16384, dumps=False):
+    """-> (keypoints[KP_DTYPE], descriptors[N,32]) in the reference's order (level, tree list order)"""
+    g = np.ascontiguousarray(gray_img, np.uint8)
+    H, W = g.shape
+    prm = params or dist_default_params()
+    kps = np.zeros(cap, KP_DTYPE)
+    desc = np.zeros((cap, 32), np.uint8)
+    d = None
+    if dumps:
+        w, h, _ = dist_level_geometry(W, H, prm.nlevels, prm.scale_factor)
+        tot = int((w.astype(np.int64) * h).sum())
+        pyr = np.zeros(tot, np.uint8)
+        blr = np.zeros(tot, np.uint8)
+        nf = np.zeros(prm.nlevels, np.int32)
+        nt = np.zeros(prm.nlevels, np.int32)
+        ps = np.zeros(prm.nlevels, np.int32)
+        d = DistDumps(_p(pyr).value, _p(blr).value, _p(nf).value, _p(nt).value, _p(ps).value)
+    n = lib().orc_dist_detect_gray(_p(g), W, H, C.byref(prm), _p(kps), _p(desc), cap, C.byref(d) if d else None)
+    if n > cap:
+        return dist_detect_gray(g, prm, cap=n, dumps=dumps)
+    if not dumps:
+        return kps[:n].copy(), desc[:n].copy()
+    offs = np.concatenate([[0], np.cumsum(w.astype(np.int64) * h)])
+    out = {
+        "pyr": [pyr[offs[l]:offs[l + 1]].reshape(h[l], w[l]) for l in range(prm.nlevels)],
+        "blurred": [blr[offs[l]:offs[l + 1]].reshape(h[l], w[l]) for l in range(prm.nlevels)],
+        "n_fast": nf, "n_tree": nt, "passes": ps,
+    }
+    return kps[:n].copy(), desc[:n].copy(), out
+
+
+def dist_detect_rgb(rgb, params=None, cap=16384):
+    """DistributedOrbOpenCvDetector::detect restated (toGrayScale in memory order, then extract)"""
+    return dist_detect_gray(gray(rgb), params, cap)
+
+
+def dist_detect_rgb_batch(frames, params=None, cap=16384, nthreads=1):
+    frames = np.ascontiguousarray(frames, np.uint8)
+    B, H, W, _ = frames.shape
+    prm = params or dist_default_params()
+    kps = np.zeros((B, cap), KP_DTYPE)
+    desc = np.zeros((B, cap, 32), np.uint8)
+    counts = np.zeros(B, np.int32)
+    lib().orc_dist_detect_rgb_batch(_p(frames), B, W, H, C.byref(prm), _p(kps), _p(desc), cap, _p(counts), nthreads)
+    assert (counts <= cap).all(), "oracle batch capacity exceeded"
+    return kps, desc, counts

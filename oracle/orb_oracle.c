@@ -183,6 +183,9 @@ static inline int fast_score_px(const uint8_t* p, int stride, int thr)
     return best > thr ? best - 1 : 0;
 }
 
+/* the per-pixel score, for dist_orb_oracle.c (cv::FAST on sub-images) */
+ORC_API int orc_fast_score_px(const uint8_t* p, int stride, int thr) { return fast_score_px(p, stride, thr); }
+
 ORC_API void orc_fast_score_map(const uint8_t* img, int w, int h, int thr, uint8_t* score)
 {
     memset(score, 0, (size_t)w * h);

@@ -1,0 +1,130 @@
+"""GPU parity tests of the second detector (DistributedOrbOpenCvDetector), through the C ABI
+(mslam_b200_dist_*) against oracle/dist_orb_oracle.c.  Bar: bit-exact at every stage -- pyramid levels, blurred levels,
+per-level candidate / kept counts and tree passes -- and bit-exact keypoints (x, y, size, angle, response, octave as raw
+bytes) and descriptors IN THE REFERENCE'S ORDER (index i is the reference's Keypoint::id).  Nothing reads /root/reference."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_frame(pkg, oracle, ctx, bgr, frame=0, kp=None, desc=None, what=""):
+    H, W, _ = bgr.shape
+    okp, odesc, dumps = oracle.dist_detect_gray(oracle.gray(bgr), dumps=True)
+    w, h, s = ctx.level_geometry(W, H)
+    ow, oh, osc = oracle.dist_level_geometry(W, H)
+    assert (w == ow).all() and (h == oh).all() and s.tobytes() == osc.tobytes()
+    for l in range(8):
+        got = ctx.debug_image(pkg.DIST_PYRAMID, frame, l, W, H)
+        assert (got == dumps["pyr"][l]).all(), f"{what} pyramid level {l}: {(got != dumps['pyr'][l]).sum()} px differ"
+        assert ctx.debug_count(pkg.DIST_N_FAST, frame, l) == dumps["n_fast"][l], f"{what} n_fast level {l}"
+        assert ctx.debug_count(pkg.DIST_N_TREE, frame, l) == dumps["n_tree"][l], f"{what} n_tree level {l}"
+        if dumps["n_fast"][l] > 0:
+            assert ctx.debug_count(pkg.DIST_PASSES, frame, l) == dumps["passes"][l], f"{what} passes level {l}"
+        if dumps["n_tree"][l] > 0:  # the reference blurs only levels that kept keypoints (:789-799)
+            got = ctx.debug_image(pkg.DIST_BLURRED, frame, l, W, H)
+            assert (got == dumps["blurred"][l]).all(), f"{what} blurred level {l}"
+    if kp is not None:
+        assert len(kp) == len(okp), f"{what}: {len(kp)} keypoints vs oracle {len(okp)}"
+        if kp.tobytes() != okp.tobytes():
+            bad = [i for i in range(len(kp)) if kp[i].tobytes() != okp[i].tobytes()]
+            raise AssertionError(f"{what}: {len(bad)} keypoints differ, first {bad[0]}: {kp[bad[0]]} vs {okp[bad[0]]}")
+        nbad = int((desc != odesc).any(axis=1).sum())
+        assert nbad == 0, f"{what}: {nbad}/{len(desc)} descriptors differ"
+    return okp, odesc
+
+
+def test_bundled_frames_bit_exact_in_reference_order(pkg, oracle, bundled):
+    with pkg.DistContext(max_width=640, max_height=480, max_batch=2) as ctx:
+        for name in ("bgr0", "bgr1"):
+            kp, desc = ctx.detect(bundled[name])
+            assert len(kp) > 1000
+            _check_frame(pkg, oracle, ctx, bundled[name], 0, kp, desc, name)
+
+
+@pytest.mark.parametrize("W,H", [(640, 480), (1280, 720), (1920, 1080), (311, 237), (480, 640), (333, 500), (160, 140)])
+def test_synthetic_sizes_bit_exact(pkg, oracle, W, H):
+    frames, _ = pkg.synth.frame_batch(W, H, 1, 0, seed=W + H)
+    with pkg.DistContext(max_width=W, max_height=H, max_batch=1) as ctx:
+        kp, desc = ctx.detect(frames[0])
+        _check_frame(pkg, oracle, ctx, frames[0], 0, kp, desc, f"{W}x{H}")
+
+
+def test_noise_frame_many_candidates(pkg, oracle):
+    rng = np.random.default_rng(11)
+    bgr = rng.integers(0, 256, (480, 640, 3), dtype=np.uint8)
+    with pkg.DistContext(max_width=640, max_height=480) as ctx:
+        kp, desc = ctx.detect(bgr)
+        _check_frame(pkg, oracle, ctx, bgr, 0, kp, desc, "noise")
+
+
+def test_low_contrast_uses_the_threshold_fallback(pkg, oracle):
+    """contrast between 7 and 20: no corner at ini_fast_thr_, so every cell is redone at min_fast_thr_ (:919-923)"""
+    rng = np.random.default_rng(5)
+    g = (120 + rng.integers(0, 14, (480, 640))).astype(np.uint8)
+    bgr = np.repeat(g[:, :, None], 3, axis=2)
+    with pkg.DistContext(max_width=640, max_height=480) as ctx:
+        kp, desc = ctx.detect(bgr)
+        okp, _ = _check_frame(pkg, oracle, ctx, bgr, 0, kp, desc, "low contrast")
+        assert len(okp) > 0 and okp["response"].max() < 20
+
+
+def test_flat_frame_has_no_keypoints(pkg, oracle):
+    bgr = np.full((240, 320, 3), 77, np.uint8)
+    with pkg.DistContext(max_width=320, max_height=240) as ctx:
+        kp, desc = ctx.detect(bgr)
+        assert len(kp) == 0 and len(desc) == 0
+
+
+def test_batch_of_frames_equals_single_frames(pkg, oracle):
+    frames, _ = pkg.synth.frame_batch(640, 480, 5, 1, seed=77)
+    with pkg.DistContext(max_width=640, max_height=480, max_batch=5) as ctx:
+        kp, desc, counts = ctx.detect_batch(frames)
+        for i in range(5):
+            _check_frame(pkg, oracle, ctx, frames[i], i, kp[i, :counts[i]], desc[i, :counts[i]], f"frame {i}")
+
+
+def test_device_entry_point(pkg, oracle):
+    import torch
+    frames, _ = pkg.synth.frame_batch(640, 480, 3, 0, seed=9)
+    with pkg.DistContext(max_width=640, max_height=480, max_batch=3) as ctx:
+        cap = ctx.kp_cap
+        d_bgr = torch.from_numpy(frames).cuda()
+        d_kp = torch.zeros((3, cap, 6), dtype=torch.float32, device="cuda")
+        d_desc = torch.zeros((3, cap, 32), dtype=torch.uint8, device="cuda")
+        d_n = torch.zeros(3, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        ctx.detect_batch_dev(d_bgr, 3, 640, 480, d_kp, d_desc, cap, d_n)
+        ctx.synchronize()
+        n = d_n.cpu().numpy()
+        kp = d_kp.cpu().numpy().view(np.uint8).reshape(3, cap, 24).copy().view(pkg.KP_DTYPE).reshape(3, cap)
+        desc = d_desc.cpu().numpy()
+        for i in range(3):
+            okp, odesc = oracle.dist_detect_rgb(frames[i])
+            assert n[i] == len(okp)
+            assert kp[i, :n[i]].tobytes() == okp.tobytes() and (desc[i, :n[i]] == odesc).all()
+
+
+def test_frontend_class_sets_ids(pkg, oracle, bundled):
+    det = pkg.DistributedOrbB200Detector(max_width=640, max_height=480)
+    out = det.detect(pkg.RgbFrame(bundled["bgr0"], 640, 480))
+    okp, odesc = oracle.dist_detect_rgb(bundled["bgr0"])
+    assert (out["id"] == np.arange(len(okp))).all()
+    assert (out["coordinates"][:, 0] == okp["x"].astype(np.float64)).all()
+    assert (out["coordinates"][:, 1] == okp["y"].astype(np.float64)).all()
+    assert (out["descriptor"] == odesc).all()
+    det.ctx.close()
+
+
+def test_capacity_and_invalid_sizes(pkg):
+    frames, _ = pkg.synth.frame_batch(640, 480, 1, 0, seed=3)
+    with pkg.DistContext(max_width=640, max_height=480) as ctx:
+        with pytest.raises(pkg.MslamB200Error) as e:
+            ctx.detect(frames[0], capacity=10)
+        assert e.value.status == pkg.E_CAPACITY
+        with pytest.raises(pkg.MslamB200Error) as e:
+            ctx.detect(np.zeros((481, 640, 3), np.uint8))  # larger than the handle
+        assert e.value.status == pkg.E_INVALID
+        with pytest.raises(pkg.MslamB200Error) as e:
+            ctx.detect(np.zeros((100, 100, 3), np.uint8))  # level 7 is 28 px: the reference's border arithmetic underflows
+        assert e.value.status == pkg.E_INVALID
