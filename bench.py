@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- the headline benchmark of BASELINE.json: ORB extract + match frames/s.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5|dist] [--impl reference]
 
 N > 1 is launched by the driver under torch.distributed.run (one rank per GPU).
 
@@ -9,6 +9,7 @@ A *step* is one pass of the hot path over one batch of synthetic input:
   c2 (default, the config BASELINE.json's metric is quoted on): 64 independent 640x480 sequences, frame t of each:
      detect (1000 kp, 8 levels) + kNN/ratio match of the current frame against the previous frame of its sequence.
   c3: 1280x720, 2000 kp, cross-checked matching, batch 32.     c4: 1920x1080, 4000 kp, batch 16.
+  dist: the Viewer's wiring -- DistributedOrb detector + kNN ratio match, 640x480 x 64 (bench_dist.py).
   c5: keyframe-database scoring (reported as descriptor pairs/s): DB shard per GPU, per-query top-k, NCCL all-gather merge.
 Frames are sharded across GPUs as independent replicas (no data-path collective) -> weak scaling.
 
@@ -137,6 +138,9 @@ def run_reference(args, rank, world):
     from oracle import oracle as O
     if args.workload == "c5":
         return run_reference_db(args, pkg, O)
+    if args.workload == "dist":
+        import bench_dist
+        return bench_dist.run_reference(args)
     W, H, nfeat, _, mode, label = WORKLOADS[args.workload if args.workload in WORKLOADS else "c2"]
     threads = os.cpu_count() or 1
     n_sample = max(threads, 8)  # frames per step: one per host thread
@@ -204,6 +208,9 @@ def main():
     if args.workload == "c5":
         import bench_db
         return bench_db.main(args, rank, world, local)
+    if args.workload == "dist":
+        import bench_dist
+        return bench_dist.main(args, rank, world, local)
 
     import torch
     import torch.distributed as dist

@@ -1,0 +1,254 @@
+#!/usr/bin/env python
+"""bench_dist.py -- `bench.py --workload dist`: the reference Viewer's wiring (src/app/viewer/viewer.cpp:182-184):
+DistributedOrbOpenCvDetector + OrbOpenCvMatcher, SURVEY.md section 8(f) row f1.
+
+Workload: 64 independent 640x480 sequences per GPU; a *step* = distributed-ORB detect of frame t of every sequence
+(8 levels, FAST 20 -> 7 per 64-px cell, quad-tree distribution with min_size 1000: ~3,000 keypoints per frame on the
+synthetic frames) + kNN(2) / 0.7-ratio match of the current against the previous frame of the same sequence.
+metric = frames/s (same metric as the default workload; the detector differs).
+value / e2e / roofline / cpu_baseline: as in bench.py; the CPU baseline is oracle/dist_orb_oracle.c + the oracle matcher,
+OpenMP over frames, on a bounded sample.
+"""
+import json
+import os
+import time
+
+import numpy as np
+
+import __graft_entry__ as graft
+
+W, H, B = 640, 480, 64
+LABEL = ("SURVEY 8(f) f1: synthetic 640x480 stream, 64-frame batch, DistributedOrb detector (8 levels, FAST 20/7 per cell, "
+         "quad-tree min_size 1000) + kNN ratio match")
+METRIC = "ORB extract+match frames/sec"
+
+
+def cpu_time(O, prev, cur, threads, cap):
+    t0 = time.perf_counter()
+    kp1, d1, c1 = O.dist_detect_rgb_batch(cur, cap=cap, nthreads=threads)
+    t_det = time.perf_counter() - t0
+    kp0, d0, c0 = O.dist_detect_rgb_batch(prev, cap=cap, nthreads=threads)  # untimed: the previous frame
+    t1 = time.perf_counter()
+    O.match_ratio_batch(d1, c1, d0, c0, nthreads=threads)
+    t_match = time.perf_counter() - t1
+    return t_det + t_match, t_det, t_match
+
+
+def run_reference(args):
+    """--impl reference --workload dist: the CPU path alone (oracle port; the reference cannot be compiled here)"""
+    from bench import make_inputs
+    pkg = graft.load_package()
+    from oracle import oracle as O
+    threads = os.cpu_count() or 1
+    ns = min(max(threads, 8), 64)
+    fr = make_inputs(pkg, W, H, ns, 0, 1)
+    for _ in range(min(args.warmup, 3)):
+        cpu_time(O, fr[0], fr[1], threads, 6144)
+    t = [cpu_time(O, fr[0], fr[1], threads, 6144)[0] for _ in range(args.steps)]
+    total = float(np.sum(t))
+    v = ns * args.steps / total
+    print(json.dumps({"metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+                      "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True,
+                      "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
+                      "config": {"workload": LABEL, "frame": [W, H], "nlevels": 8, "batch_per_step": ns},
+                      "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port",
+                                       "sample": f"{ns} frames per step (detect + match vs previous frame), OpenMP over frames"},
+                      "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}))
+
+
+def main(args, rank, world, local):
+    import torch
+    import torch.distributed as dist
+    from bench import ClockSampler, make_inputs, peaks
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = graft.load_package()
+    frames = make_inputs(pkg, W, H, B, rank, args.steps)
+    T = len(frames) - 1
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    det = pkg.DistContext(device=local, max_width=W, max_height=H, max_batch=B, stream=stream.cuda_stream)
+    cap = det.kp_cap
+    # the matcher of the ORB context (OrbOpenCvMatcher's replacement); its detector side is not used here
+    ctx = pkg.Context(device=local, max_width=W, max_height=H, max_batch=B, nfeatures=1000, max_descriptors=cap,
+                      stream=stream.cuda_stream)
+    w, h, sc = det.level_geometry(W, H)
+    pyr_px = int((w.astype(np.int64) * h).sum())
+
+    d_frames = [torch.from_numpy(f).cuda() for f in frames]
+    d_kp = [torch.zeros((B, cap, 6), dtype=torch.float32, device="cuda") for _ in range(2)]
+    d_desc = [torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda") for _ in range(2)]
+    d_cnt = [torch.zeros(B, dtype=torch.int32, device="cuda") for _ in range(2)]
+    d_ma = torch.zeros((B, cap), dtype=torch.int32, device="cuda")
+    d_mb, d_md = torch.zeros_like(d_ma), torch.zeros_like(d_ma)
+    d_mn = torch.zeros(B, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+
+    def step_dev(t, cur):
+        prev = cur ^ 1
+        det.detect_batch_dev(d_frames[t], B, W, H, d_kp[cur], d_desc[cur], cap, d_cnt[cur])
+        ctx.match_batch_dev(0, d_desc[cur], d_cnt[cur], d_desc[prev], d_cnt[prev], B, cap, d_ma, d_mb, d_md, d_mn)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    det.detect_batch_dev(d_frames[0], B, W, H, d_kp[0], d_desc[0], cap, d_cnt[0])
+    cur = 1
+    for i in range(args.warmup):
+        step_dev(1 + i % T, cur)
+        cur ^= 1
+    barrier()
+    n_kp_check = int(d_cnt[cur ^ 1].sum().item())
+    n_matches_check = int(d_mn.sum().item())
+
+    l0 = det.launch_count + ctx.launch_count
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for i in range(args.steps):
+        step_dev(1 + i % T, cur)
+        cur ^= 1
+    e1.record(stream)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    gpu_launches = det.launch_count + ctx.launch_count - l0
+
+    # per-stage pass (CUDA events round every stage on the handle's stream)
+    det.stage_times(True)
+    ctx.enable_stage_timing(True)
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record(stream)
+    for i in range(args.steps):
+        step_dev(1 + i % T, cur)
+        cur ^= 1
+    e3.record(stream)
+    torch.cuda.synchronize()
+    ms_staged = e2.elapsed_time(e3)
+    st_det = det.stage_times(False)
+    st_m = ctx.stage_times()
+    ctx.enable_stage_timing(False)
+    if world > 1:
+        tt = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    frames_total = B * args.steps * world
+    value = frames_total / (ms_total * 1e-3)
+
+    # ---- end to end through the host entry points ------------------------------------------------------------------------
+    h_frames = [pkg.pinned_empty(f.shape, np.uint8) for f in frames]
+    for hf, f in zip(h_frames, frames):
+        hf[...] = f
+    h_kp = [pkg.pinned_empty((B, cap), pkg.KP_DTYPE) for _ in range(2)]
+    h_desc = [pkg.pinned_empty((B, cap, 32), np.uint8) for _ in range(2)]
+    h_cnt = [pkg.pinned_empty((B,), np.int32) for _ in range(2)]
+    h_m = [pkg.pinned_empty((B, cap), np.int32) for _ in range(3)] + [pkg.pinned_empty((B,), np.int32)]
+
+    def step_host(t, cur):
+        prev = cur ^ 1
+        det.detect_batch(h_frames[t], cap, out=(h_kp[cur], h_desc[cur], h_cnt[cur]))
+        ctx.match_batch(0, h_desc[cur], h_cnt[cur], h_desc[prev], h_cnt[prev], out=tuple(h_m))
+
+    det.detect_batch(h_frames[0], cap, out=(h_kp[0], h_desc[0], h_cnt[0]))
+    cur = 1
+    for i in range(args.warmup):
+        step_host(1 + i % T, cur)
+        cur ^= 1
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step_host(1 + i % T, cur)
+        cur ^= 1
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    if world > 1:
+        tt = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt.item())
+    e2e_value = frames_total / (e2e_ms * 1e-3)
+    kp_mean = float(h_cnt[cur ^ 1].mean())
+    h2d = int(B * W * H * 3 + 2 * B * cap * 32 + 2 * B * 4)
+    d2h = int(B * kp_mean * (24 + 32) + 2 * B * 4 + 3 * B * cap * 4 + B * 4)
+    assert int(h_m[3].sum()) > 0 and int(h_cnt[cur ^ 1].sum()) == n_kp_check or T > 1
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    pk, pk_kind = peaks()
+    n_kp = n_kp_check / B
+    bytes_per_frame = 3 * W * H + 2 * pyr_px + int(n_kp * 56)
+    per_stage_bytes = {"gray": B * 4 * W * H, "resize": B * (2 * pyr_px - W * H - int(w[-1]) * int(h[-1])), "fast": B * pyr_px,
+                      "blur": B * 2 * pyr_px, "describe": int(B * n_kp * 56)}
+    roofs = {}
+    for k, ms in st_det.items():
+        avg = ms / args.steps
+        e = {"ms_per_step": avg, "share": ms / ms_staged}
+        if k in per_stage_bytes and avg > 0:
+            ach = per_stage_bytes[k] / (avg * 1e-3) / 1e9
+            e.update({"bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"]})
+        roofs[k] = e
+    for k in ("knn", "compact"):
+        ms = st_m[k][0]
+        e = {"ms_per_step": ms / args.steps, "share": ms / ms_staged}
+        if k == "knn" and ms > 0:
+            e.update({"bound": "int-pipe (popc)", "achieved": B * n_kp * n_kp / (ms / args.steps * 1e-3) / 1e9, "unit": "Gpair/s"})
+        roofs[k] = e
+    dom = max((k for k in roofs if "frac" in roofs[k]), key=lambda k: roofs[k]["ms_per_step"])
+    d = roofs[dom]
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": d["achieved"], "peak": d["peak"], "unit": "GB/s", "frac": d["frac"],
+                "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({pk_kind})",
+                "algorithmic_bytes_per_launch_group": per_stage_bytes[dom]}
+    try:
+        tr = json.load(open(os.path.join(graft.ROOT, "profiles", "ncu_traffic_dist.json")))
+        if dom in tr["bytes_per_step"]:
+            roofline["traffic"] = tr["bytes_per_step"][dom]
+            roofline["traffic_source"] = "profiles/ncu_traffic_dist.json (ncu --set full, dram read + write bytes per step)"
+    except (OSError, ValueError, KeyError):
+        pass
+    whole = bytes_per_frame * B * args.steps / (ms_total * 1e-3) / 1e9
+    roofline["whole_step_hbm"] = {"achieved": whole, "frac": whole / pk["hbm_gbs"], "bytes_per_frame": bytes_per_frame}
+    roofline["stages"] = roofs
+    roofline["measured_in"] = (f"a second pass of the same {args.steps} steps with CUDA events round every stage "
+                               f"({ms_staged / args.steps:.4f} ms/step vs {ms_total / args.steps:.4f} ms/step in the timed region)")
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import oracle as O
+        threads = os.cpu_count() or 1
+        ns = min(B, max(8, threads))
+        t_one = cpu_time(O, frames[0][:ns], frames[1][:ns], threads, cap)[0]
+        reps = int(max(1, min(20, args.cpu_seconds / max(t_one, 1e-3))))
+        ts = [cpu_time(O, frames[0][:ns], frames[1][:ns], threads, cap) for _ in range(reps)]
+        best = min(x[0] for x in ts)
+        cpu = {"value": ns / best, "unit": "frames/s", "cores": threads, "kind": "port",
+               "sample": f"{ns} frames (detect + match vs previous frame) x {reps} repetitions, best; OpenMP over frames",
+               "detect_ms_per_frame_per_thread": float(np.median([x[1] for x in ts])) / ns * min(threads, ns) * 1e3,
+               "match_ms_per_pair_per_thread": float(np.median([x[2] for x in ts])) / ns * min(threads, ns) * 1e3}
+    line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": LABEL, "frame": [W, H], "nlevels": 8, "batch_per_gpu": B, "match": "knn2+ratio0.7",
+                       "parallelism": f"frame-batch replicas x{world}", "keypoint_capacity": cap,
+                       "l2": f"inputs rotate over {T} distinct batches ({T * B * W * H * 3 / 1e6:.0f} MB/GPU) + 2 pyramids",
+                       "keypoints_per_batch_check": n_kp_check, "matches_per_batch_check": n_matches_check},
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line))
+    det.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()

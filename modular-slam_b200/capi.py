@@ -455,15 +455,21 @@ class DistContext:
         self._check(rc, "mslam_b200_dist_detect")
         return kp[:n.value].copy(), desc[:n.value].copy()
 
-    def detect_batch(self, frames, capacity=None):
-        """frames [B, H, W, 3] u8 (host) -> (kp [B, cap], desc [B, cap, 32], counts [B])"""
-        frames = np.ascontiguousarray(frames, np.uint8)
+    def detect_batch(self, frames, capacity=None, out=None):
+        """frames [B, H, W, 3] u8 (host) -> (kp [B, cap], desc [B, cap, 32], counts [B]); out = preallocated triple"""
+        if not (isinstance(frames, np.ndarray) and frames.dtype == np.uint8 and frames.flags.c_contiguous):
+            frames = np.ascontiguousarray(frames, np.uint8)
         B, H, W, _ = frames.shape
         cap = capacity or self.kp_cap
-        kp = np.zeros((B, cap), KP_DTYPE)
-        desc = np.zeros((B, cap, 32), np.uint8)
-        counts = np.zeros(B, np.int32)
-        ptrs = (C.c_void_p * B)(*[frames[i].ctypes.data for i in range(B)])
+        if out is None:
+            kp = np.zeros((B, cap), KP_DTYPE)
+            desc = np.zeros((B, cap, 32), np.uint8)
+            counts = np.zeros(B, np.int32)
+        else:
+            kp, desc, counts = out
+            assert kp.shape == (B, cap) and desc.shape == (B, cap, 32) and counts.shape == (B,)
+        base, fs = frames.ctypes.data, frames.strides[0]
+        ptrs = (C.c_void_p * B)(*[base + i * fs for i in range(B)])
         rc = library().mslam_b200_dist_detect_batch(self._h, ptrs, B, W, H, W * 3, _ptr(kp), _ptr(desc), cap, _ptr(counts))
         self._check(rc, "mslam_b200_dist_detect_batch")
         return kp, desc, counts

@@ -196,6 +196,53 @@ std::vector<std::vector<OrbKeypoint>> OrbB200Detector::detectBatch(const std::ve
     return result;
 }
 
+// ---- second detector ---------------------------------------------------------------------------------------------
+DistributedOrbB200Detector::DistributedOrbB200Detector() : DistributedOrbB200Detector(defaultOrbB200Options()) {}
+
+DistributedOrbB200Detector::DistributedOrbB200Detector(const OrbB200Options& o)
+{
+    mslam_b200_dist_config cfg;
+    mslam_b200_dist_default_config(&cfg);
+    cfg.device = o.device;
+    cfg.max_width = o.maxWidth;
+    cfg.max_height = o.maxHeight;
+    cfg.max_batch = 1;
+    cfg.nlevels = o.nlevels;
+    cfg.scale_factor = o.scaleFactor;
+    cfg.ini_fast_threshold = o.iniFastThreshold;
+    cfg.min_fast_threshold = o.minFastThreshold;
+    cfg.min_size = o.minSize;
+    const int rc = mslam_b200_dist_create(&cfg, &handle);
+    if(rc != MSLAM_B200_OK)
+        throw std::runtime_error(std::string("mslam_b200_dist_create failed: ") + mslam_b200_status_string(rc) +
+                                 " (the B200 plugin has no CPU fallback)");
+    capacity = mslam_b200_dist_keypoint_capacity(handle);
+    kpBuf.resize((size_t)capacity);
+    descBuf.resize((size_t)capacity * MSLAM_B200_DESC_BYTES);
+}
+
+DistributedOrbB200Detector::~DistributedOrbB200Detector() { mslam_b200_dist_destroy(handle); }
+
+std::vector<OrbKeypoint> DistributedOrbB200Detector::detect(const RgbFrame& sensorData)
+{
+    std::vector<OrbKeypoint> result;
+    const int w = sensorData.size.width, h = sensorData.size.height;
+    if(w <= 0 || h <= 0 || sensorData.data.size() < (size_t)w * h * 3)
+        return result;
+    int n = 0;
+    const int rc = mslam_b200_dist_detect(handle, sensorData.data.data(), w, h, 3 * w, kpBuf.data(), descBuf.data(), capacity, &n);
+    if(rc != MSLAM_B200_OK && rc != MSLAM_B200_E_CAPACITY)
+    {
+        if(!reported)
+            std::fprintf(stderr, "[mslam_b200 plugin] distributed detect: %s %s\n", mslam_b200_status_string(rc),
+                         mslam_b200_dist_last_cuda_error(handle));
+        reported = true;
+        return result;
+    }
+    fillKeypoints(kpBuf.data(), descBuf.data(), n < capacity ? n : capacity, &result); // id = index (:1201-1205)
+    return result;
+}
+
 // ---- matcher -------------------------------------------------------------------------------------------------------
 OrbB200Matcher::OrbB200Matcher() : OrbB200Matcher(defaultOrbB200Options()) {}
 

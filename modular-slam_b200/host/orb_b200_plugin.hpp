@@ -3,11 +3,14 @@
 //
 //   mslam::OrbB200Detector  replaces  mslam::OrbOpenCvDetector   (orb_feature.hpp:19-31, orb_feature.cpp:19-72)
 //   mslam::OrbB200Matcher   replaces  mslam::OrbOpenCvMatcher    (orb_feature.hpp:33-47, orb_feature.cpp:74-117)
+//   mslam::DistributedOrbB200Detector  replaces  mslam::DistributedOrbOpenCvDetector
+//                                      (distributed_cv_feature.hpp:10-21, distributed_cv_feature.cpp:1181-1222; viewer.cpp:183)
 //
 // Both are constructed the way the reference apps construct theirs (std::make_shared<...>(), rgbd_slam.cpp:74-76) or
 // through the boost::dll factory aliases exported by the plugin library (plugin_loader.hpp:19-25):
 //   orbDetectorFactory : std::unique_ptr<mslam::IOrbFeatureDetector>()
 //   orbMatcherFactory  : std::unique_ptr<mslam::IOrbMatcher>()
+//   distributedOrbDetectorFactory : std::unique_ptr<mslam::IOrbFeatureDetector>()
 // Error behaviour mirrors the reference: no exceptions out of detect()/match(); an empty vector means "nothing"
 // (a CUDA failure is logged to stderr once per object and also yields an empty vector).  Constructors throw
 // std::runtime_error when no CUDA device / context can be created -- there is no CPU fallback.
@@ -37,6 +40,9 @@ struct OrbB200Options
     int fastThreshold = 20;
     double ratio = 0.7;
     int maxDescriptors = 0; // matcher capacity per side; 0 = derived from nfeatures
+    // DistributedOrbB200Detector only: orb_params("orb", 1.2f, 8, 20, 7), OrbExtractorPimpl(params, 1000)
+    // (distributed_cv_feature.cpp:1184-1186); it also reads device, maxWidth, maxHeight, nlevels, scaleFactor
+    int iniFastThreshold = 20, minFastThreshold = 7, minSize = 1000;
 };
 
 // one context shared by the detector and the matcher of a process (one CUDA stream, one set of HBM buffers)
@@ -54,6 +60,25 @@ class OrbB200Detector : public IOrbFeatureDetector
 
   private:
     std::shared_ptr<OrbB200Context> ctx;
+    std::vector<mslam_b200_keypoint> kpBuf;
+    std::vector<std::uint8_t> descBuf;
+};
+
+// Keypoints come back in the reference's order and Keypoint::id = index (distributed_cv_feature.cpp:1201-1210).
+class DistributedOrbB200Detector : public IOrbFeatureDetector
+{
+  public:
+    DistributedOrbB200Detector();
+    explicit DistributedOrbB200Detector(const OrbB200Options& options);
+    ~DistributedOrbB200Detector() override;
+    DistributedOrbB200Detector(const DistributedOrbB200Detector&) = delete;
+    DistributedOrbB200Detector& operator=(const DistributedOrbB200Detector&) = delete;
+    std::vector<OrbKeypoint> detect(const RgbFrame& sensorData) override;
+
+  private:
+    mslam_b200_dist* handle = nullptr;
+    int capacity = 0;
+    bool reported = false;
     std::vector<mslam_b200_keypoint> kpBuf;
     std::vector<std::uint8_t> descBuf;
 };

@@ -34,6 +34,11 @@ std::unique_ptr<IOrbFeatureDetector> createOrbB200Detector()
     return std::unique_ptr<IOrbFeatureDetector>(new OrbB200Detector());
 }
 
+std::unique_ptr<IOrbFeatureDetector> createDistributedOrbB200Detector()
+{
+    return std::unique_ptr<IOrbFeatureDetector>(new DistributedOrbB200Detector());
+}
+
 std::unique_ptr<IOrbMatcher> createOrbB200Matcher()
 {
     return std::unique_ptr<IOrbMatcher>(new OrbB200Matcher());
@@ -270,6 +275,9 @@ bool parsePluginConfig(const std::string& jsonText, std::vector<PluginEntry>* ou
             v = o.fastThreshold; if(!numberField(*prm, "fastThreshold", 1, 254, &v, &err)) return false;  o.fastThreshold = (int)v;
             v = o.ratio;         if(!numberField(*prm, "ratio", 1e-6, 1e6, &v, &err)) return false;       o.ratio = v;
             v = o.maxDescriptors; if(!numberField(*prm, "maxDescriptors", 0, 65535, &v, &err)) return false; o.maxDescriptors = (int)v;
+            v = o.iniFastThreshold; if(!numberField(*prm, "iniFastThreshold", 1, 254, &v, &err)) return false; o.iniFastThreshold = (int)v;
+            v = o.minFastThreshold; if(!numberField(*prm, "minFastThreshold", 1, 254, &v, &err)) return false; o.minFastThreshold = (int)v;
+            v = o.minSize;       if(!numberField(*prm, "minSize", 1, 1e9, &v, &err)) return false;         o.minSize = (int)v;
         }
         out->push_back(entry);
     }
@@ -281,3 +289,5 @@ bool parsePluginConfig(const std::string& jsonText, std::vector<PluginEntry>* ou
 // the aliases loadFactoryMethod<IOrbFeatureDetector>(lib, "orbDetectorFactory") / <IOrbMatcher>(lib, "orbMatcherFactory") import
 MSLAM_B200_DLL_ALIAS(mslam::createOrbB200Detector, orbDetectorFactory)
 MSLAM_B200_DLL_ALIAS(mslam::createOrbB200Matcher, orbMatcherFactory)
+// the detector the reference's Viewer wires in (viewer.cpp:183), as a second alias of the same interface
+MSLAM_B200_DLL_ALIAS(mslam::createDistributedOrbB200Detector, distributedOrbDetectorFactory)

@@ -5,7 +5,7 @@
 //
 //   plugin_host_test symbols <plugin.so>
 //   plugin_host_test config  <plugin_config.json>
-//   plugin_host_test run     <plugin.so> <frame0.raw> <frame1.raw> <W> <H> <out.bin>
+//   plugin_host_test run     <plugin.so> <frame0.raw> <frame1.raw> <W> <H> <out.bin> [detector alias]
 #include <dlfcn.h>
 
 #include <cstdio>
@@ -69,16 +69,17 @@ int main(int argc, char** argv)
         std::fprintf(stderr, "dlopen: %s\n", dlerror());
         return 3;
     }
-    auto* makeDetector = loadFactoryMethod<mslam::IOrbFeatureDetector>(lib, "orbDetectorFactory");
+    const char* detectorAlias = (argc >= 9 && !std::strcmp(argv[1], "run")) ? argv[8] : "orbDetectorFactory";
+    auto* makeDetector = loadFactoryMethod<mslam::IOrbFeatureDetector>(lib, detectorAlias);
     auto* makeMatcher = loadFactoryMethod<mslam::IOrbMatcher>(lib, "orbMatcherFactory");
-    if(!makeDetector || !makeMatcher)
+    if(!makeDetector || !makeMatcher || !loadFactoryMethod<mslam::IOrbFeatureDetector>(lib, "distributedOrbDetectorFactory"))
     {
         std::fprintf(stderr, "factory aliases missing\n");
         return 4;
     }
     if(!std::strcmp(argv[1], "symbols"))
     {
-        std::printf("aliases ok: orbDetectorFactory orbMatcherFactory\n");
+        std::printf("aliases ok: orbDetectorFactory orbMatcherFactory distributedOrbDetectorFactory\n");
         return 0;
     }
     if(std::strcmp(argv[1], "run") || argc < 8)

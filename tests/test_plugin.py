@@ -25,6 +25,7 @@ def test_factory_aliases_load_like_boost_dll_import_alias(built):
     out = subprocess.run([built, "symbols", PLUGIN], capture_output=True, text=True)
     assert out.returncode == 0, out.stderr
     assert "orbDetectorFactory" in out.stdout and "orbMatcherFactory" in out.stdout
+    assert "distributedOrbDetectorFactory" in out.stdout
     # the aliases live in section "boostdll", as BOOST_DLL_ALIAS puts them (boost/dll/alias.hpp; test/dummy.cpp:11)
     sec = subprocess.run(["readelf", "-S", "-W", PLUGIN], capture_output=True, text=True).stdout
     assert "boostdll" in sec
@@ -77,4 +78,39 @@ def test_reference_call_sequence_through_the_plugin(built, oracle, bundled, tmp_
         assert (k["descriptor"] == odesc).all()
     fi, ti, _ = oracle.match_ratio(k0["descriptor"], k1["descriptor"])
     assert nm == len(fi) == 693
+    assert (m["fromIndex"].astype(np.int64) == fi).all() and (m["toIndex"].astype(np.int64) == ti).all()
+
+
+@pytest.mark.gpu
+def test_distributed_detector_through_the_plugin(built, oracle, bundled, tmp_path):
+    """the Viewer's wiring (viewer.cpp:182-184): DistributedOrb detector + Orb matcher, loaded by alias"""
+    f0, f1 = tmp_path / "f0.raw", tmp_path / "f1.raw"
+    bundled["bgr0"].tofile(f0)
+    bundled["bgr1"].tofile(f1)
+    cfgp = tmp_path / "plugin_config.json"
+    cfgp.write_text(json.dumps({"plugins": [{"library": PLUGIN,
+                                             "factoryMethods": {"featureDetector": "distributedOrbDetectorFactory",
+                                                                "featureMatcher": "orbMatcherFactory"},
+                                             "parameters": {"maxWidth": 640, "maxHeight": 480, "maxDescriptors": 4096}}]}))
+    outp = tmp_path / "out.bin"
+    env = dict(os.environ, MSLAM_B200_PLUGIN_CONFIG=str(cfgp))
+    out = subprocess.run([built, "run", PLUGIN, str(f0), str(f1), "640", "480", str(outp), "distributedOrbDetectorFactory"],
+                         capture_output=True, text=True, env=env)
+    assert out.returncode == 0, out.stdout + out.stderr
+    raw = outp.read_bytes()
+    n0, n1, nm, nnone = np.frombuffer(raw[:32], np.uint64).astype(int)
+    rec = np.dtype({"names": ["id", "coordinates", "descriptor"], "formats": ["<u8", ("<f8", (2,)), ("u1", (32,))],
+                    "offsets": [0, 16, 32], "itemsize": 64})
+    k0 = np.frombuffer(raw, rec, n0, 32)
+    k1 = np.frombuffer(raw, rec, n1, 32 + 64 * n0)
+    m = np.frombuffer(raw, np.dtype([("fromIndex", "<u8"), ("toIndex", "<u8")]), nm, 32 + 64 * (n0 + n1))
+    for k, i in ((k0, 0), (k1, 1)):
+        okp, odesc = oracle.dist_detect_rgb(bundled[f"bgr{i}"])
+        assert len(k) == len(okp) > 1000
+        assert (k["id"] == np.arange(len(k))).all()  # distributed_cv_feature.cpp:1201-1205
+        assert (k["coordinates"][:, 0] == okp["x"].astype(np.float64)).all()
+        assert (k["coordinates"][:, 1] == okp["y"].astype(np.float64)).all()
+        assert (k["descriptor"] == odesc).all()
+    fi, ti, _ = oracle.match_ratio(k0["descriptor"], k1["descriptor"])
+    assert nm == len(fi) > 100
     assert (m["fromIndex"].astype(np.int64) == fi).all() and (m["toIndex"].astype(np.int64) == ti).all()
