@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(256) k_dist_resize(const uint8_t* __restrict__
 // =================================================================================================
 // FAST per cell (cv::FAST(cell, thr, true), :915-922)
 // =================================================================================================
-constexpr int FT_PITCH = 72; // tile row pitch (70 used)
+constexpr int FT_PITCH = 80; // tile row pitch: 19 aligned words cover the 70 columns of a cell at any alignment
 constexpr int FS_PITCH = 68; // score row pitch (66 used: 64 + zero ring)
 
 __device__ __forceinline__ int level_of_cell(const DistParams& P, int idx)
@@ -192,7 +192,7 @@ __device__ __forceinline__ int corner_best(const uint8_t* __restrict__ c)
 __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
                                                    unsigned* __restrict__ cand, DistCounters* __restrict__ ctr)
 {
-    __shared__ __align__(16) uint8_t tile[70 * FT_PITCH];
+    __shared__ __align__(16) uint8_t tile[70 * FT_PITCH + 16];
     __shared__ __align__(16) uint8_t sc[66 * FS_PITCH];
     __shared__ unsigned short q[4096];
     __shared__ unsigned surv[1024];
@@ -206,13 +206,15 @@ __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistP
     const int ci = c / L.ncx, cj = c - ci * L.ncx;
     const int x0 = kFastOrg + kCell * cj, y0 = kFastOrg + kCell * ci;
     const int cw = min(kCell, L.w - kFastOrg - x0), ch = min(kCell, L.h - kFastOrg - y0);
-    const uint8_t* img = pyr + L.img_off + frame * L.img_frame_stride + (long long)(y0 - 3) * L.pitch + (x0 - 3);
-    const int tw = cw + 6, th = ch + 6;
-    for(int i = tid; i < th * tw; i += 256)
-    {
-        const int r = i / tw, cc = i - r * tw;
-        tile[r * FT_PITCH + cc] = __ldg(img + (long long)r * L.pitch + cc);
-    }
+    // the tile starts at column x0 - 3 = 19 + 64 cj; rows are fetched as aligned words from column 16 + 64 cj, so the
+    // tile's column 0 sits at byte 3 of a shared-memory row (T below)
+    const uint8_t* img = pyr + L.img_off + frame * L.img_frame_stride + (long long)(y0 - 3) * L.pitch + (x0 - 6);
+    const int th = ch + 6, nwords = (cw + 12) >> 2;
+    for(int r = tid >> 5; r < th; r += 8)
+        if(lane < nwords)
+            reinterpret_cast<unsigned*>(tile + r * FT_PITCH)[lane] =
+                __ldg(reinterpret_cast<const unsigned*>(img + (long long)r * L.pitch) + lane);
+    const uint8_t* T = tile + 3;
     int thr = P.ini_thr;
     int ns = 0;
     for(int attempt = 0; attempt < 2; ++attempt)
@@ -230,7 +232,7 @@ __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistP
             bool pass = false;
             if(lx < cw && ly < ch)
             {
-                const uint8_t* p = tile + (ly + 3) * FT_PITCH + lx + 3;
+                const uint8_t* p = T + (ly + 3) * FT_PITCH + lx + 3;
                 const int v = p[0];
                 const int d0 = v - p[3 * FT_PITCH], d8 = v - p[-3 * FT_PITCH], d4 = v - p[3], d12 = v - p[-3];
                 const int dark = (d0 > thr) + (d8 > thr) + (d4 > thr) + (d12 > thr);
@@ -254,7 +256,7 @@ __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistP
         for(int i = tid; i < nq; i += 256)
         {
             const int ly = q[i] >> 8, lx = q[i] & 255;
-            const int best = corner_best(tile + (ly + 3) * FT_PITCH + lx + 3);
+            const int best = corner_best(T + (ly + 3) * FT_PITCH + lx + 3);
             if(best > thr)
                 sc[(ly + 1) * FS_PITCH + lx + 1] = (uint8_t)(best - 1);
         }
@@ -569,7 +571,7 @@ __device__ __forceinline__ int reflect101_d(int p, int n)
 __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
                                                     uint8_t* __restrict__ blur)
 {
-    __shared__ uint8_t in[38][72];
+    __shared__ __align__(16) uint8_t in[38][76];
     __shared__ unsigned short hs[38][64];
     const int tid = threadIdx.x;
     const int l = level_of_gtile(P, blockIdx.x);
@@ -578,17 +580,28 @@ __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ Dist
     const int ty = t / L.gtx, tx = t - ty * L.gtx;
     const int x0 = tx * 64, y0 = ty * 32;
     const uint8_t* img = pyr + L.img_off + blockIdx.y * L.img_frame_stride;
-    for(int i = tid; i < 38 * 70; i += 256)
+    // shared row r holds columns x0 - 4 .. x0 + 71 of source row reflect(y0 + r - 3): 19 aligned words when the tile
+    // is clear of the left / right image border, byte-wise with REFLECT_101 otherwise
+    if(x0 >= 4 && x0 + 72 <= L.w)
     {
-        const int r = i / 70, c = i - r * 70;
-        const int sy = reflect101_d(y0 + r - 3, L.h), sx = reflect101_d(x0 + c - 3, L.w);
-        in[r][c] = __ldg(img + (long long)sy * L.pitch + sx);
+        const int lane = tid & 31;
+        for(int r = tid >> 5; r < 38; r += 8)
+            if(lane < 19)
+                reinterpret_cast<unsigned*>(&in[r][0])[lane] = __ldg(
+                    reinterpret_cast<const unsigned*>(img + (long long)reflect101_d(y0 + r - 3, L.h) * L.pitch + x0 - 4) + lane);
     }
+    else
+        for(int i = tid; i < 38 * 70; i += 256)
+        {
+            const int r = i / 70, c = i - r * 70;
+            const int sy = reflect101_d(y0 + r - 3, L.h), sx = reflect101_d(x0 + c - 3, L.w);
+            in[r][c + 1] = __ldg(img + (long long)sy * L.pitch + sx);
+        }
     __syncthreads();
     for(int i = tid; i < 38 * 64; i += 256)
     {
         const int r = i >> 6, c = i & 63;
-        const uint8_t* p = &in[r][c];
+        const uint8_t* p = &in[r][c + 1];
         hs[r][c] = (unsigned short)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
     }
     __syncthreads();
@@ -676,18 +689,18 @@ __global__ void __launch_bounds__(256) k_dist_describe(const __grid_constant__ D
         const unsigned long long umax = 0x3689ABCDDEEEFFFFull;
         if(lane < 31)
         {
-            const uint8_t* c = img + (long long)y * L.pitch + x + u;
+            // the disc is symmetric (u_max[|v|] >= |u|  <=>  |v| <= u_max[|u|]), so column u spans rows -vm .. vm
+            const int vm = (int)((umax >> (4 * au)) & 15);
+            const uint8_t* c = img + (long long)(y - vm) * L.pitch + x + u;
+            int sum = 0;
 #pragma unroll 1
-            for(int v = -15; v <= 15; ++v)
+            for(int v = -vm; v <= vm; ++v, c += L.pitch)
             {
-                const int av = v < 0 ? -v : v;
-                if(au <= (int)((umax >> (4 * av)) & 15))
-                {
-                    const int val = __ldg(c + (long long)v * L.pitch);
-                    m10 += u * val;
-                    m01 += v * val;
-                }
+                const int val = __ldg(c);
+                sum += val;
+                m01 += v * val;
             }
+            m10 = u * sum;
         }
         m10 = __reduce_add_sync(0xffffffffu, m10);
         m01 = __reduce_add_sync(0xffffffffu, m01);
@@ -946,6 +959,8 @@ struct mslam_b200_dist
     int last_frames = 0;
     bool timing = false;
     cudaEvent_t ev[7] = {nullptr};
+    cudaStream_t aux = nullptr; // forked stream of the blur
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     double t_ms[6] = {0};
 };
 
@@ -1027,6 +1042,15 @@ void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
     for(cudaEvent_t e : ctx->ev)
         if(e)
             cudaEventDestroy(e);
+    if(ctx->ev_fork)
+        cudaEventDestroy(ctx->ev_fork);
+    if(ctx->ev_join)
+        cudaEventDestroy(ctx->ev_join);
+    if(ctx->aux)
+    {
+        cudaStreamSynchronize(ctx->aux);
+        cudaStreamDestroy(ctx->aux);
+    }
     if(ctx->own_stream && ctx->stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -1077,6 +1101,9 @@ int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist
     }
     for(auto& e : ctx->ev)
         CREATE_OK(cudaEventCreate(&e));
+    CREATE_OK(cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
     const size_t B = (size_t)c.max_batch;
     // a little slack on the geometry-dependent sizes: level sizes are monotone in (W, H) but row pitches round up
     ctx->pyr_bytes = g.pyr_bytes + 4096;
@@ -1171,6 +1198,16 @@ static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, ms
     }
     if(tm)
         cudaEventRecord(ctx->ev[2], st);
+    // the blur depends on the pyramid only: unless stages are being timed it runs on a forked stream beside FAST + tree
+    cudaStream_t bs = tm ? st : ctx->aux;
+    if(!tm)
+    {
+        DIST_CUDA_OK(cudaEventRecord(ctx->ev_fork, st));
+        DIST_CUDA_OK(cudaStreamWaitEvent(ctx->aux, ctx->ev_fork, 0));
+        k_dist_gauss<<<dim3(P.total_gtiles, n_frames), 256, 0, bs>>>(P, ctx->d_pyr, ctx->d_blur);
+        ++ctx->launches;
+        DIST_CUDA_OK(cudaEventRecord(ctx->ev_join, ctx->aux));
+    }
     if(P.total_cells > 0)
     {
         k_dist_fast<<<dim3(P.total_cells, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_cand, ctx->d_ctr);
@@ -1181,11 +1218,14 @@ static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, ms
     k_dist_tree<<<dim3(P.nlevels, n_frames), kTreeThreads, ctx->tree_smem, st>>>(P, ctx->d_cand, ctx->d_ctr, ctx->d_sel, ctx->d_tree);
     ++ctx->launches;
     if(tm)
+    {
         cudaEventRecord(ctx->ev[4], st);
-    k_dist_gauss<<<dim3(P.total_gtiles, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_blur);
-    ++ctx->launches;
-    if(tm)
+        k_dist_gauss<<<dim3(P.total_gtiles, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_blur);
+        ++ctx->launches;
         cudaEventRecord(ctx->ev[5], st);
+    }
+    else
+        DIST_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
     const int slots = std::min(capacity, ctx->kp_cap);
     k_dist_describe<<<dim3((std::max(slots, 1) + 7) / 8, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel,
                                                                                   d_kp, d_desc, d_counts, capacity);
