@@ -85,6 +85,60 @@ class IFeatureMatcher
     virtual ~IFeatureMatcher() {}
 };
 
+// ---- sensor side (rgbd_file_b200_provider.hpp): types/timestamp.hpp:7-10, sensors/camera_parameters.hpp:7-12,
+// types/depth_frame.hpp:12-17, types/rgbd_frame.hpp:13-19, slam_component.hpp:9-23, sensors/data_provider.hpp:10-17
+struct Timestamp
+{
+    double timePoint;
+};
+
+struct CameraParameters
+{
+    Vector2 principalPoint;
+    Vector2 focal;
+    float factor;
+};
+
+struct DepthFrame
+{
+    std::vector<std::uint16_t> data;
+    Size size;
+    CameraParameters cameraParameters;
+};
+
+struct RgbdFrame
+{
+    Timestamp timestamp;
+    RgbFrame rgb;
+    DepthFrame depth;
+};
+
+class ParametersHandlerInterface; // parameters/parameters_handler.hpp:79-95 (not used by the provider)
+
+class SlamComponent
+{
+  public:
+    SlamComponent(std::shared_ptr<ParametersHandlerInterface> handler = nullptr) : parametersHandler{handler} {}
+    void setParameterHandler(std::shared_ptr<ParametersHandlerInterface> newParameterHendler)
+    {
+        parametersHandler = std::move(newParameterHendler);
+    }
+    virtual bool init() { return true; }
+    virtual ~SlamComponent() {}
+
+  protected:
+    std::shared_ptr<ParametersHandlerInterface> parametersHandler;
+};
+
+template <typename DataType>
+class DataProviderInterface : public SlamComponent
+{
+  public:
+    virtual bool init() = 0;
+    virtual bool fetch() = 0;
+    virtual std::shared_ptr<DataType> recentData() const = 0;
+};
+
 using IOrbFeatureDetector = IFeatureDetector<RgbFrame, std::uint8_t, 32>;
 using IOrbMatcher = IFeatureMatcher<std::uint8_t, 32>;
 using OrbKeypoint = KeypointDescriptor<std::uint8_t, 32>;

@@ -5,6 +5,7 @@
 //
 //   plugin_host_test symbols <plugin.so>
 //   plugin_host_test config  <plugin_config.json>
+//   plugin_host_test provider <associations.txt> <out.bin> [batch size]   (RgbdFileB200Provider; batch > 0 => fetchBatch, pinned)
 //   plugin_host_test run     <plugin.so> <frame0.raw> <frame1.raw> <W> <H> <out.bin> [detector alias]
 #include <dlfcn.h>
 
@@ -15,6 +16,7 @@
 #include <string>
 
 #include "orb_b200_plugin.hpp"
+#include "rgbd_file_b200_provider.hpp"
 
 template <typename BlockType>
 using BlockFactoryCreator = std::unique_ptr<BlockType>(); // plugin_loader.hpp:13-14
@@ -56,6 +58,52 @@ int main(int argc, char** argv)
             std::printf("library=%s detector=%s matcher=%s nfeatures=%d nlevels=%d scaleFactor=%.3f fastThreshold=%d ratio=%.3f\n",
                         e.library.c_str(), e.detectorFactory.c_str(), e.matcherFactory.c_str(), e.options.nfeatures,
                         e.options.nlevels, e.options.scaleFactor, e.options.fastThreshold, e.options.ratio);
+        return 0;
+    }
+    if(argc >= 4 && !std::strcmp(argv[1], "provider"))
+    {
+        // the way the reference apps build their provider (rgbd_slam.cpp:66-70): readTumRgbdDataset + tumRgbdCameraParams
+        mslam::RgbdFileB200Provider provider(mslam::readTumRgbdDataset(argv[2]), mslam::tumRgbdCameraParams());
+        if(!provider.init())
+        {
+            std::printf("init failed\n");
+            return 7;
+        }
+        const int batch = argc >= 5 ? std::atoi(argv[4]) : 0;
+        std::ofstream out(argv[3], std::ios::binary);
+        int frames = 0;
+        auto dump = [&out](int w, int h, double ts, const std::uint8_t* rgb, const std::uint16_t* depth, float factor) {
+            const double hdr[4] = {(double)w, (double)h, ts, (double)factor};
+            out.write(reinterpret_cast<const char*>(hdr), sizeof(hdr));
+            out.write(reinterpret_cast<const char*>(rgb), (std::streamsize)((size_t)w * h * 3));
+            out.write(reinterpret_cast<const char*>(depth), (std::streamsize)((size_t)w * h * 2));
+        };
+        if(batch > 0)
+        {
+            for(;;)
+            {
+                const mslam::RgbdFileB200Provider::Batch b = provider.fetchBatch(batch);
+                if(b.count == 0)
+                    break;
+                for(int i = 0; i < b.count; ++i, ++frames)
+                    dump(b.width, b.height, b.timestamps[(size_t)i], b.rgb[(size_t)i], b.depth[(size_t)i], mslam::tumRgbdCameraParams().factor);
+            }
+        }
+        else
+        {
+            while(provider.fetch())
+            {
+                const std::shared_ptr<mslam::RgbdFrame> f = provider.recentData();
+                if(f->depth.size.width != f->rgb.size.width || f->depth.size.height != f->rgb.size.height)
+                    return 8;
+                dump(f->rgb.size.width, f->rgb.size.height, f->timestamp.timePoint, f->rgb.data.data(), f->depth.data.data(),
+                     f->depth.cameraParameters.factor);
+                ++frames;
+            }
+            if(provider.recentData() != nullptr)
+                return 9; // the reference resets recentFrame when the sequence ends (rgbd_file_provider.cpp:57-61)
+        }
+        std::printf("frames=%d position=%zu\n", frames, provider.position());
         return 0;
     }
     if(argc < 3)
