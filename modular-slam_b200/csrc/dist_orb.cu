@@ -49,6 +49,7 @@ constexpr int kMaxInit = 64;  // initial tree nodes supported (round(aspect rati
 constexpr int kTreeThreads = 1024;
 constexpr int kTreeSmemBudget = 200 * 1024;
 constexpr unsigned kFlag = 0x80000000u;
+constexpr int kDistChunks = 4; // host detect_batch: chunks in flight through copy-in / kernels / copy-out
 
 struct DistLevel
 {
@@ -76,7 +77,8 @@ struct DistParams
     unsigned min_size;
     int kp_cap;               // per-frame keypoint capacity of the handle
     int total_cells, total_gtiles;
-    int sel_frame_stride, pad;
+    int sel_frame_stride;
+    int frame0;               // first frame (absolute index in the handle's per-frame buffers) a launch covers
     long long cand_frame_stride, tree_frame_stride;
     DistLevel lv[kMaxLevels];
 };
@@ -154,39 +156,42 @@ __device__ __forceinline__ int level_of_gtile(const DistParams& P, int idx)
     return l;
 }
 
+// Both polarities of a ring difference ride in the two 16-bit halves of one register, biased by +256 so that they stay
+// positive: lo = (v - p) + 256, hi = (p - v) + 256.  Because lo + hi * 65536 = [v' + (512 - v') * 65536] + p * 0xFFFF with
+// v' = v + 256, one IMAD per ring pixel builds the pair from a per-pixel base.
+__device__ __forceinline__ unsigned pair_base(int v) { return (unsigned)(v + 256) + ((unsigned)(256 - v) << 16); }
+__device__ __forceinline__ unsigned pair_of(unsigned base, unsigned p) { return base + p * 0xFFFFu; }
+
 // exact cornerScore<16> of a pixel known to sit >= 3 px inside the tile: max over the 16 arcs of 9 contiguous ring
-// pixels of min(v - p) and of min(p - v), minus one.  d and -d ride in the two s16 halves of one register.
+// pixels of min(v - p) and of min(p - v), minus one (the caller subtracts it).
 __device__ __forceinline__ int corner_best(const uint8_t* __restrict__ c)
 {
-    const int v = c[0];
+    const unsigned base = pair_base(c[0]);
     unsigned e[25];
     const int off[16] = {3 * FT_PITCH,      3 * FT_PITCH + 1,  2 * FT_PITCH + 2,  FT_PITCH + 3,  3,  -FT_PITCH + 3,
                          -2 * FT_PITCH + 2, -3 * FT_PITCH + 1, -3 * FT_PITCH,     -3 * FT_PITCH - 1, -2 * FT_PITCH - 2,
                          -FT_PITCH - 3,     -3,                FT_PITCH - 3,      2 * FT_PITCH - 2,  3 * FT_PITCH - 1};
 #pragma unroll
     for(int k = 0; k < 16; ++k)
-    {
-        const int d = v - (int)c[off[k]];
-        e[k] = ((unsigned)d & 0xffffu) | ((unsigned)(-d) << 16);
-    }
+        e[k] = pair_of(base, c[off[k]]);
 #pragma unroll
     for(int k = 16; k < 25; ++k)
         e[k] = e[k - 16];
-    unsigned m2[24], m4[22], best = 0x80008000u; // (-32768, -32768)
+    unsigned m2[24], m4[22], best = 0; // biased values are >= 1
 #pragma unroll
     for(int k = 0; k < 24; ++k)
-        m2[k] = __vmins2(e[k], e[k + 1]);
+        m2[k] = __vminu2(e[k], e[k + 1]);
 #pragma unroll
     for(int k = 0; k < 22; ++k)
-        m4[k] = __vmins2(m2[k], m2[k + 2]);
+        m4[k] = __vminu2(m2[k], m2[k + 2]);
 #pragma unroll
     for(int k = 0; k < 16; ++k)
     {
-        const unsigned m8 = __vmins2(m4[k], m4[k + 4]);
-        best = __vmaxs2(best, __vmins2(m8, e[k + 8]));
+        const unsigned m8 = __vminu2(m4[k], m4[k + 4]);
+        best = __vmaxu2(best, __vminu2(m8, e[k + 8]));
     }
-    const int lo = (int)(short)(best & 0xffff), hi = (int)(short)(best >> 16);
-    return lo > hi ? lo : hi;
+    const int lo = (int)(best & 0xffff), hi = (int)(best >> 16);
+    return (lo > hi ? lo : hi) - 256;
 }
 
 __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
@@ -201,7 +206,7 @@ __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistP
     const int tid = threadIdx.x, lane = tid & 31;
     const int l = level_of_cell(P, blockIdx.x);
     const DistLevel& L = P.lv[l];
-    const int frame = blockIdx.y;
+    const int frame = P.frame0 + blockIdx.y;
     const int c = blockIdx.x - L.cell_base;
     const int ci = c / L.ncx, cj = c - ci * L.ncx;
     const int x0 = kFastOrg + kCell * cj, y0 = kFastOrg + kCell * ci;
@@ -233,11 +238,14 @@ __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistP
             if(lx < cw && ly < ch)
             {
                 const uint8_t* p = T + (ly + 3) * FT_PITCH + lx + 3;
-                const int v = p[0];
-                const int d0 = v - p[3 * FT_PITCH], d8 = v - p[-3 * FT_PITCH], d4 = v - p[3], d12 = v - p[-3];
-                const int dark = (d0 > thr) + (d8 > thr) + (d4 > thr) + (d12 > thr);
-                const int bright = (d0 < -thr) + (d8 < -thr) + (d4 < -thr) + (d12 < -thr);
-                pass = dark >= 2 || bright >= 2;
+                const unsigned base = pair_base(p[0]);
+                const unsigned a = pair_of(base, p[3 * FT_PITCH]), b = pair_of(base, p[-3 * FT_PITCH]);
+                const unsigned c4 = pair_of(base, p[3]), d12 = pair_of(base, p[-3]);
+                // second largest of the four, per polarity: two of the four compass differences exceed thr
+                const unsigned second = __vmaxu2(__vmaxu2(__vminu2(a, b), __vminu2(c4, d12)),
+                                                 __vminu2(__vmaxu2(a, b), __vmaxu2(c4, d12)));
+                const unsigned lim = (unsigned)(thr + 256);
+                pass = (second & 0xffffu) > lim || (second >> 16) > lim;
             }
             const unsigned m = __ballot_sync(0xffffffffu, pass);
             if(m)
@@ -363,7 +371,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
     __shared__ unsigned s_created, s_divided;
     __shared__ unsigned s_warp[32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int l = blockIdx.x, frame = blockIdx.y;
+    const int l = blockIdx.y, frame = P.frame0 + blockIdx.x; // level-major launch order: the big levels start first
     const DistLevel& L = P.lv[l];
     DistCounters* C = ctr + frame * P.nlevels + l;
     const int n = (int)min(C->n_fast, (unsigned)L.cand_cap);
@@ -579,7 +587,7 @@ __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ Dist
     const int t = blockIdx.x - L.gtile_base;
     const int ty = t / L.gtx, tx = t - ty * L.gtx;
     const int x0 = tx * 64, y0 = ty * 32;
-    const uint8_t* img = pyr + L.img_off + blockIdx.y * L.img_frame_stride;
+    const uint8_t* img = pyr + L.img_off + (P.frame0 + blockIdx.y) * L.img_frame_stride;
     // shared row r holds columns x0 - 4 .. x0 + 71 of source row reflect(y0 + r - 3): 19 aligned words when the tile
     // is clear of the left / right image border, byte-wise with REFLECT_101 otherwise
     if(x0 >= 4 && x0 + 72 <= L.w)
@@ -605,7 +613,7 @@ __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ Dist
         hs[r][c] = (unsigned short)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
     }
     __syncthreads();
-    uint8_t* dst = blur + L.img_off + blockIdx.y * L.img_frame_stride;
+    uint8_t* dst = blur + L.img_off + (P.frame0 + blockIdx.y) * L.img_frame_stride;
     for(int i = tid; i < 32 * 16; i += 256)
     {
         const int y = i >> 4, xq = (i & 15) * 4;
@@ -657,7 +665,7 @@ __global__ void __launch_bounds__(256) k_dist_describe(const __grid_constant__ D
 {
     const int lane = threadIdx.x & 31;
     const int g = blockIdx.x * 8 + (threadIdx.x >> 5);
-    const int frame = blockIdx.y;
+    const int frame = P.frame0 + blockIdx.y;
     const DistCounters* C = ctr + frame * P.nlevels;
     int l = 0, base = 0, total = 0;
     {
@@ -960,6 +968,8 @@ struct mslam_b200_dist
     bool timing = false;
     cudaEvent_t ev[7] = {nullptr};
     cudaStream_t aux = nullptr; // forked stream of the blur
+    cudaStream_t copy[2] = {nullptr, nullptr}; // copy-in / copy-out engines of the host entry point
+    cudaEvent_t ev_h2d[kDistChunks] = {nullptr}, ev_done[kDistChunks] = {nullptr}, ev_cnt[kDistChunks] = {nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     double t_ms[6] = {0};
 };
@@ -1042,6 +1052,16 @@ void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
     for(cudaEvent_t e : ctx->ev)
         if(e)
             cudaEventDestroy(e);
+    for(int i = 0; i < kDistChunks; ++i)
+        for(cudaEvent_t e : {ctx->ev_h2d[i], ctx->ev_done[i], ctx->ev_cnt[i]})
+            if(e)
+                cudaEventDestroy(e);
+    for(int i = 0; i < 2; ++i)
+        if(ctx->copy[i])
+        {
+            cudaStreamSynchronize(ctx->copy[i]);
+            cudaStreamDestroy(ctx->copy[i]);
+        }
     if(ctx->ev_fork)
         cudaEventDestroy(ctx->ev_fork);
     if(ctx->ev_join)
@@ -1102,6 +1122,14 @@ int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist
     for(auto& e : ctx->ev)
         CREATE_OK(cudaEventCreate(&e));
     CREATE_OK(cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
+    for(int i = 0; i < 2; ++i)
+        CREATE_OK(cudaStreamCreateWithFlags(&ctx->copy[i], cudaStreamNonBlocking));
+    for(int i = 0; i < kDistChunks; ++i)
+    {
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming));
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_cnt[i], cudaEventDisableTiming));
+    }
     CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
     const size_t B = (size_t)c.max_batch;
@@ -1167,21 +1195,22 @@ int mslam_b200_dist_level_geometry(mslam_b200_dist* ctx, int width, int height, 
 }
 
 // enqueue the whole detector for n_frames frames already in d_bgr
-static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, mslam_b200_keypoint* d_kp, uint8_t* d_desc,
-                    int capacity, int* d_counts)
+static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int frame0, int n_frames, mslam_b200_keypoint* d_kp,
+                    uint8_t* d_desc, int capacity, int* d_counts)
 {
     DistParams& P = ctx->P;
     P.n_frames = n_frames;
+    P.frame0 = frame0;
     cudaStream_t st = ctx->stream;
     const bool tm = ctx->timing;
-    DIST_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, (size_t)n_frames * P.nlevels * sizeof(DistCounters), st));
+    DIST_CUDA_OK(cudaMemsetAsync(ctx->d_ctr + (size_t)frame0 * P.nlevels, 0, (size_t)n_frames * P.nlevels * sizeof(DistCounters), st));
     if(tm)
         cudaEventRecord(ctx->ev[0], st);
     {
         // toGrayScale into level 0 (k_gray16 / k_gray1 of the ORB path; same RgbFrame layout, frame.cpp:6-27)
         PipeParams G;
         memset(&G, 0, sizeof(G));
-        G.nlevels = 1, G.n_frames = n_frames, G.W = P.W, G.H = P.H, G.frame0 = 0;
+        G.nlevels = 1, G.n_frames = n_frames, G.W = P.W, G.H = P.H, G.frame0 = frame0;
         G.lv[0].w = P.W, G.lv[0].h = P.H, G.lv[0].pitch = P.lv[0].pitch;
         G.lv[0].img_off = P.lv[0].img_off, G.lv[0].img_frame_stride = P.lv[0].img_frame_stride;
         launch_gray(st, d_bgr, ctx->d_pyr, G, &ctx->launches);
@@ -1192,7 +1221,8 @@ static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, ms
     {
         const DistLevel &S = P.lv[l - 1], &D = P.lv[l];
         k_dist_resize<<<dim3((D.w + 255) / 256, (D.h + 3) / 4, n_frames), 256, 0, st>>>(
-            ctx->d_pyr + S.img_off, S.pitch, S.img_frame_stride, S.w, ctx->d_pyr + D.img_off, D.pitch, D.img_frame_stride, D.w,
+            ctx->d_pyr + S.img_off + frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride, S.w,
+            ctx->d_pyr + D.img_off + frame0 * D.img_frame_stride, D.pitch, D.img_frame_stride, D.w,
             D.h, ctx->d_xtab + D.xtab_off, ctx->d_ytab + D.ytab_off);
         ++ctx->launches;
     }
@@ -1215,7 +1245,7 @@ static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, ms
     }
     if(tm)
         cudaEventRecord(ctx->ev[3], st);
-    k_dist_tree<<<dim3(P.nlevels, n_frames), kTreeThreads, ctx->tree_smem, st>>>(P, ctx->d_cand, ctx->d_ctr, ctx->d_sel, ctx->d_tree);
+    k_dist_tree<<<dim3(n_frames, P.nlevels), kTreeThreads, ctx->tree_smem, st>>>(P, ctx->d_cand, ctx->d_ctr, ctx->d_sel, ctx->d_tree);
     ++ctx->launches;
     if(tm)
     {
@@ -1256,7 +1286,7 @@ int mslam_b200_dist_detect_batch_dev(mslam_b200_dist* ctx, const uint8_t* d_bgr,
     const int rc = dist_set_geometry(ctx, width, height);
     if(rc)
         return rc;
-    return dist_run(ctx, d_bgr, n_frames, d_kp, d_desc, capacity, d_counts);
+    return dist_run(ctx, d_bgr, 0, n_frames, d_kp, d_desc, capacity, d_counts);
 }
 
 int mslam_b200_dist_detect_batch(mslam_b200_dist* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
@@ -1272,36 +1302,59 @@ int mslam_b200_dist_detect_batch(mslam_b200_dist* ctx, const uint8_t* const* fra
     int rc = dist_set_geometry(ctx, width, height);
     if(rc)
         return rc;
+    // chunked pipeline: copy-in of chunk c+1 (copy engine 1) overlaps the kernels of chunk c, and the copy-out of chunk c
+    // (copy engine 2, exact sizes once its counts are on the host) overlaps the kernels of chunk c+1
     const size_t fbytes = (size_t)width * height * 3;
-    for(int i = 0; i < n_frames; ++i)
-        DIST_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * fbytes, (size_t)width * 3, frames[i], (size_t)stride_bytes, (size_t)width * 3,
-                                       height, cudaMemcpyHostToDevice, ctx->stream));
-    rc = dist_run(ctx, ctx->d_bgr, n_frames, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
-    if(rc)
-        return rc;
-    DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_counts, ctx->d_counts, n_frames * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_ctr, ctx->d_ctr, (size_t)n_frames * ctx->P.nlevels * sizeof(DistCounters),
-                                 cudaMemcpyDeviceToHost, ctx->stream));
-    DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
-    rc = MSLAM_B200_OK;
-    for(int i = 0; i < n_frames * ctx->P.nlevels; ++i)
-        if(ctx->h_ctr[i].err)
-            rc = MSLAM_B200_E_CAPACITY; // an internal list overflowed (cannot happen: capacities are upper bounds)
-    for(int i = 0; i < n_frames; ++i)
+    const int nchunks = ctx->timing ? 1 : std::min(kDistChunks, std::max(1, n_frames / 4));
+    const int nl = ctx->P.nlevels;
+    int bounds[kDistChunks + 1];
+    for(int c = 0; c <= nchunks; ++c)
+        bounds[c] = (int)((long long)n_frames * c / nchunks);
+    for(int c = 0; c < nchunks; ++c)
     {
-        const int n = ctx->h_counts[i];
-        n_out[i] = n;
-        if(n > capacity || n > ctx->kp_cap)
-            rc = MSLAM_B200_E_CAPACITY;
-        const int m = std::min(n, std::min(capacity, ctx->kp_cap));
-        if(m > 0)
+        for(int i = bounds[c]; i < bounds[c + 1]; ++i)
+            DIST_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * fbytes, (size_t)width * 3, frames[i], (size_t)stride_bytes,
+                                           (size_t)width * 3, height, cudaMemcpyHostToDevice, ctx->copy[0]));
+        DIST_CUDA_OK(cudaEventRecord(ctx->ev_h2d[c], ctx->copy[0]));
+    }
+    for(int c = 0; c < nchunks; ++c)
+    {
+        DIST_CUDA_OK(cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d[c], 0));
+        rc = dist_run(ctx, ctx->d_bgr, bounds[c], bounds[c + 1] - bounds[c], ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
+        if(rc)
+            return rc;
+        DIST_CUDA_OK(cudaEventRecord(ctx->ev_done[c], ctx->stream));
+        DIST_CUDA_OK(cudaStreamWaitEvent(ctx->copy[1], ctx->ev_done[c], 0));
+        DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_counts + bounds[c], ctx->d_counts + bounds[c], (bounds[c + 1] - bounds[c]) * sizeof(int),
+                                     cudaMemcpyDeviceToHost, ctx->copy[1]));
+        DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_ctr + (size_t)bounds[c] * nl, ctx->d_ctr + (size_t)bounds[c] * nl,
+                                     (size_t)(bounds[c + 1] - bounds[c]) * nl * sizeof(DistCounters), cudaMemcpyDeviceToHost, ctx->copy[1]));
+        DIST_CUDA_OK(cudaEventRecord(ctx->ev_cnt[c], ctx->copy[1]));
+    }
+    rc = MSLAM_B200_OK;
+    for(int c = 0; c < nchunks; ++c)
+    {
+        DIST_CUDA_OK(cudaEventSynchronize(ctx->ev_cnt[c]));
+        for(int i = bounds[c] * nl; i < bounds[c + 1] * nl; ++i)
+            if(ctx->h_ctr[i].err)
+                rc = MSLAM_B200_E_CAPACITY; // an internal list overflowed (cannot happen: capacities are upper bounds)
+        for(int i = bounds[c]; i < bounds[c + 1]; ++i)
         {
-            DIST_CUDA_OK(cudaMemcpyAsync(out_kp + (size_t)i * capacity, ctx->d_kp + (size_t)i * ctx->kp_cap,
-                                         (size_t)m * sizeof(mslam_b200_keypoint), cudaMemcpyDeviceToHost, ctx->stream));
-            DIST_CUDA_OK(cudaMemcpyAsync(out_desc + (size_t)i * capacity * 32, ctx->d_desc + (size_t)i * ctx->kp_cap * 32, (size_t)m * 32,
-                                         cudaMemcpyDeviceToHost, ctx->stream));
+            const int n = ctx->h_counts[i];
+            n_out[i] = n;
+            if(n > capacity || n > ctx->kp_cap)
+                rc = MSLAM_B200_E_CAPACITY;
+            const int m = std::min(n, std::min(capacity, ctx->kp_cap));
+            if(m > 0)
+            {
+                DIST_CUDA_OK(cudaMemcpyAsync(out_kp + (size_t)i * capacity, ctx->d_kp + (size_t)i * ctx->kp_cap,
+                                             (size_t)m * sizeof(mslam_b200_keypoint), cudaMemcpyDeviceToHost, ctx->copy[1]));
+                DIST_CUDA_OK(cudaMemcpyAsync(out_desc + (size_t)i * capacity * 32, ctx->d_desc + (size_t)i * ctx->kp_cap * 32,
+                                             (size_t)m * 32, cudaMemcpyDeviceToHost, ctx->copy[1]));
+            }
         }
     }
+    DIST_CUDA_OK(cudaStreamSynchronize(ctx->copy[1]));
     DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     return rc;
 }
