@@ -540,8 +540,27 @@ void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t
     }
     else
     {
-        dim3 grd((cap + 255) / 256, n_pairs);
-        k_knn2<2, 128><<<grd, 128, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+        // 256 queries per CTA (two per thread) halve the shared-memory traffic per pair, but leave only
+        // n_pairs * cap / 64 warps; below ~48 warps per SM one query per thread hides latency better (measured on the
+        // distributed-ORB workload, 64 pairs x ~3260 descriptors: 534 -> 704 Gpair/s)
+        static int mode = -1;
+        if(mode < 0)
+        {
+            const char* e = getenv("MSLAM_KNN_MODE");
+            mode = e ? atoi(e) : 0;
+        }
+        const long long warps2 = (long long)((cap + 255) / 256) * n_pairs * 4;
+        const bool one_per_thread = mode == 2 || (mode == 0 && warps2 < 48LL * sm_count);
+        if(one_per_thread)
+        {
+            dim3 grd((cap + 127) / 128, n_pairs);
+            k_knn2<1, 128><<<grd, 128, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+        }
+        else
+        {
+            dim3 grd((cap + 255) / 256, n_pairs);
+            k_knn2<2, 128><<<grd, 128, 0, st>>>(q, qn, t, tn, cap, key0, key1);
+        }
     }
     ++*launches;
 }
