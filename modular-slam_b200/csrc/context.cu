@@ -14,7 +14,8 @@
 
 using namespace mslam_b200;
 
-constexpr int kMaxChunks = 4; // host detect_batch: chunks in flight through copy-in / kernels / copy-out
+constexpr int kDefaultChunks = 4;
+constexpr int kMaxChunks = 8; // host detect_batch: most chunks in flight through copy-in / kernels / copy-out
 
 struct mslam_b200_ctx
 {
@@ -760,7 +761,13 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
     // chunk c runs through the kernels (context stream + its forks) and chunk c-1's results are copied out (second
     // copy stream).  Per-frame scratch in HBM is indexed by absolute frame, so chunks never touch each other's data.
     const int icap = ctx->kp_cap, ncopy = std::min(capacity, icap);
-    const int nchunks = n_frames >= 2 * kMaxChunks ? kMaxChunks : 1;
+    static int want_chunks = -1;
+    if(want_chunks < 0)
+    {
+        const char* e = getenv("MSLAM_B200_CHUNKS");
+        want_chunks = e ? std::max(1, std::min(kMaxChunks, atoi(e))) : kDefaultChunks;
+    }
+    const int nchunks = n_frames >= 8 ? std::min(want_chunks, n_frames / 2) : 1;
     const int per = (n_frames + nchunks - 1) / nchunks;
     cudaStream_t s_in = ctx->copy[0], s_out = ctx->copy[1];
     MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
