@@ -316,11 +316,13 @@ __device__ __forceinline__ bool area_stops(int bx, int by, int ex, int ey, float
     return __fmul_rn(__fmul_rn((float)area, s), s) <= (float)min_size;
 }
 
-// place a keypoint in its initial node (initialize_nodes, :1032-1041)
-__device__ __forceinline__ void walk_init(const DistLevel& L, int x, int y, Walk& w)
+// place a keypoint in its initial node (initialize_nodes, :1032-1041): ix = (unsigned)(pt.x / delta_x).  Only one axis
+// ever has more than one initial node; its quotients come from a per-CTA table filled once with the same double
+// division (init_tab[c] = (unsigned)((double)(float)c / delta)), so the walk itself is integer-only.
+__device__ __forceinline__ void walk_init(const DistLevel& L, const uint8_t* __restrict__ init_tab, int x, int y, Walk& w)
 {
     const int ninit = L.ninit_x * L.ninit_y;
-    unsigned ix = (unsigned)((double)(float)x / L.delta_x), iy = (unsigned)((double)(float)y / L.delta_y);
+    unsigned ix = L.ninit_x > 1 ? init_tab[x] : 0u, iy = L.ninit_y > 1 ? init_tab[y] : 0u;
     unsigned i0 = ix + iy * (unsigned)L.ninit_x;
     if(i0 >= (unsigned)ninit)
         i0 = ninit - 1, ix = i0 % L.ninit_x, iy = i0 / L.ninit_x;
@@ -350,9 +352,10 @@ __device__ __forceinline__ void walk_down(int x, int y, Walk& w)
 
 // walk from the root towards depth `target`; stops early at a node that is final (one keypoint, or small area).
 // Returns true when the walk arrived at `target` through divided nodes only.
-__device__ __forceinline__ bool walk_to(const DistLevel& L, const unsigned* cnt, int x, int y, int target, Walk& w)
+__device__ __forceinline__ bool walk_to(const DistLevel& L, const uint8_t* __restrict__ init_tab, const unsigned* cnt, int x, int y,
+                                        int target, Walk& w)
 {
-    walk_init(L, x, y, w);
+    walk_init(L, init_tab, x, y, w);
     while(w.depth < target)
     {
         const unsigned c = cnt[w.off + w.key];
@@ -370,6 +373,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
     extern __shared__ unsigned s_dyn[];
     __shared__ unsigned s_created, s_divided;
     __shared__ unsigned s_warp[32];
+    __shared__ uint8_t s_init[4096]; // initial-node index of a coordinate along the axis that has several initial nodes
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int l = blockIdx.y, frame = P.frame0 + blockIdx.x; // level-major launch order: the big levels start first
     const DistLevel& L = P.lv[l];
@@ -383,6 +387,12 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
     unsigned* best = cnt + L.tree_slots;
     for(int i = tid; i < 2 * L.tree_slots; i += kTreeThreads)
         cnt[i] = 0;
+    if(L.ninit_x * L.ninit_y > 1)
+    {
+        const double delta = L.ninit_x > 1 ? L.delta_x : L.delta_y;
+        for(int i = tid; i < 4096; i += kTreeThreads)
+            s_init[i] = (uint8_t)min(255u, (unsigned)((double)(float)i / delta));
+    }
     __syncthreads();
     const unsigned* list = cand + frame * P.cand_frame_stride + L.cand_off;
     const int ninit = L.ninit_x * L.ninit_y;
@@ -394,7 +404,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
         const unsigned r = list[k];
         const int x = (r >> 8) & 0xfff, y = r >> 20;
         Walk w;
-        walk_init(L, x, y, w);
+        walk_init(L, s_init, x, y, w);
         const unsigned old = atomicAdd(&cnt[w.key], 1u);
         if(old == 0 && area_stops(w.bx, w.by, w.ex, w.ey, s, P.min_size))
             atomicOr(&cnt[w.key], kFlag);
@@ -416,7 +426,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
             const unsigned r = list[k];
             const int x = (r >> 8) & 0xfff, y = r >> 20;
             Walk w;
-            if(!walk_to(L, cnt, x, y, p, w))
+            if(!walk_to(L, s_init, cnt, x, y, p, w))
                 continue;
             const unsigned c = cnt[w.off + w.key];
             if((c & ~kFlag) == 1u || (c & kFlag))
@@ -466,7 +476,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
         const unsigned r = list[k];
         const int x = (r >> 8) & 0xfff, y = r >> 20;
         Walk w;
-        walk_to(L, cnt, x, y, t_end, w);
+        walk_to(L, s_init, cnt, x, y, t_end, w);
         const int cj = (x - 3) >> 6, ci = (y - 3) >> 6;
         const unsigned ord = (unsigned)(ci * L.ncx + cj) << 12 | (unsigned)((y - 3) & 63) << 6 | (unsigned)((x - 3) & 63);
         atomicMax(&best[w.off + w.key], (r & 0xffu) << 24 | (0xffffffu - ord));
@@ -580,7 +590,7 @@ __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ Dist
                                                     uint8_t* __restrict__ blur)
 {
     __shared__ __align__(16) uint8_t in[38][76];
-    __shared__ unsigned short hs[38][64];
+    __shared__ __align__(16) unsigned hp[19][64]; // horizontally filtered rows, stored as row pairs
     const int tid = threadIdx.x;
     const int l = level_of_gtile(P, blockIdx.x);
     const DistLevel& L = P.lv[l];
@@ -606,27 +616,53 @@ __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ Dist
             in[r][c + 1] = __ldg(img + (long long)sy * L.pitch + sx);
         }
     __syncthreads();
-    for(int i = tid; i < 38 * 64; i += 256)
+    // horizontal pass, exact in 8.8: an item is (row pair, 4 columns); the 10 bytes a row needs come from three aligned
+    // words, every output is two IDP.4A over byte windows cut with PRMT.  Results are stored as row PAIRS -- word
+    // (rp, x) = h[2 rp][x] | h[2 rp + 1][x] << 16 -- so that the vertical pass can run on IDP.2A.
+    for(int i = tid; i < 19 * 16; i += 256)
     {
-        const int r = i >> 6, c = i & 63;
-        const uint8_t* p = &in[r][c + 1];
-        hs[r][c] = (unsigned short)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
+        const int rp = i >> 4, c = (i & 15) * 4;
+        unsigned h[2][4];
+#pragma unroll
+        for(int k = 0; k < 2; ++k)
+        {
+            const unsigned* w = reinterpret_cast<const unsigned*>(&in[2 * rp + k][c]);
+            const unsigned w0 = w[0], w1 = w[1], w2 = w[2];
+            const unsigned lo[4] = {__byte_perm(w0, w1, 0x4321), __byte_perm(w0, w1, 0x5432), __byte_perm(w0, w1, 0x6543), w1};
+            const unsigned hi[4] = {__byte_perm(w1, w2, 0x4321), __byte_perm(w1, w2, 0x5432), __byte_perm(w1, w2, 0x6543), w2};
+#pragma unroll
+            for(int j = 0; j < 4; ++j) // taps 18 34 48 56 | 48 34 18 0
+                h[k][j] = __dp4a(hi[j], 0x00122230u, __dp4a(lo[j], 0x38302212u, 0u));
+        }
+        *reinterpret_cast<uint4*>(&hp[rp][c]) =
+            make_uint4(h[0][0] | h[1][0] << 16, h[0][1] | h[1][1] << 16, h[0][2] | h[1][2] << 16, h[0][3] | h[1][3] << 16);
     }
     __syncthreads();
+    // vertical pass, exact in 16.16: output row y uses h rows y .. y+6 = row pairs (y >> 1) .. (y >> 1) + 3, with the tap
+    // pairs shifted by one row when y is odd
     uint8_t* dst = blur + L.img_off + (P.frame0 + blockIdx.y) * L.img_frame_stride;
     for(int i = tid; i < 32 * 16; i += 256)
     {
         const int y = i >> 4, xq = (i & 15) * 4;
         if(y0 + y >= L.h || x0 + xq >= L.w)
             continue;
+        const bool odd = y & 1;
+        const unsigned c0 = odd ? 0x30221200u : 0x38302212u; // (0 18 | 34 48)   or (18 34 | 48 56)
+        const unsigned c1 = odd ? 0x12223038u : 0x00122230u; // (56 48 | 34 18)  or (48 34 | 18 0)
+        const int rp = y >> 1;
+        const uint4 a = *reinterpret_cast<const uint4*>(&hp[rp][xq]), b = *reinterpret_cast<const uint4*>(&hp[rp + 1][xq]);
+        const uint4 c = *reinterpret_cast<const uint4*>(&hp[rp + 2][xq]), d = *reinterpret_cast<const uint4*>(&hp[rp + 3][xq]);
+        const unsigned pa[4] = {a.x, a.y, a.z, a.w}, pb[4] = {b.x, b.y, b.z, b.w}, pc[4] = {c.x, c.y, c.z, c.w},
+                       pd[4] = {d.x, d.y, d.z, d.w};
         unsigned o = 0;
 #pragma unroll
         for(int j = 0; j < 4; ++j)
         {
-            const int x = xq + j;
-            const unsigned v = 18u * (hs[y][x] + hs[y + 6][x]) + 34u * (hs[y + 1][x] + hs[y + 5][x]) +
-                               48u * (hs[y + 2][x] + hs[y + 4][x]) + 56u * hs[y + 3][x];
-            o |= ((v + 32768u) >> 16) << (8 * j);
+            unsigned v = __dp2a_lo(pa[j], c0, 32768u);
+            v = __dp2a_hi(pb[j], c0, v);
+            v = __dp2a_lo(pc[j], c1, v);
+            v = __dp2a_hi(pd[j], c1, v);
+            o |= (v >> 16) << (8 * j);
         }
         *reinterpret_cast<unsigned*>(dst + (long long)(y0 + y) * L.pitch + x0 + xq) = o;
     }
@@ -699,14 +735,19 @@ __global__ void __launch_bounds__(256) k_dist_describe(const __grid_constant__ D
         {
             // the disc is symmetric (u_max[|v|] >= |u|  <=>  |v| <= u_max[|u|]), so column u spans rows -vm .. vm
             const int vm = (int)((umax >> (4 * au)) & 15);
-            const uint8_t* c = img + (long long)(y - vm) * L.pitch + x + u;
+            const uint8_t* c = img + (long long)y * L.pitch + x + u;
             int sum = 0;
-#pragma unroll 1
-            for(int v = -vm; v <= vm; ++v, c += L.pitch)
+            // all 31 rows unrolled and predicated, so that the loads of a lane are independent and in flight together
+#pragma unroll
+            for(int v = -15; v <= 15; ++v)
             {
-                const int val = __ldg(c);
-                sum += val;
-                m01 += v * val;
+                const int av = v < 0 ? -v : v;
+                if(av <= vm)
+                {
+                    const int val = __ldg(c + (long long)v * L.pitch);
+                    sum += val;
+                    m01 += v * val;
+                }
             }
             m10 = u * sum;
         }
