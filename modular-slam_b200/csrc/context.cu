@@ -768,14 +768,26 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
         want_chunks = e ? std::max(1, std::min(kMaxChunks, atoi(e))) : kDefaultChunks;
     }
     const int nchunks = n_frames >= 8 ? std::min(want_chunks, n_frames / 2) : 1;
-    const int per = (n_frames + nchunks - 1) / nchunks;
+    // chunk boundaries: the first chunk's copy-in and the last chunk's kernels are the only parts nothing overlaps, so
+    // with four chunks and a large batch those two are made small (1 : 3 : 3 : 1)
+    static int tapered = -1;
+    if(tapered < 0)
+    {
+        const char* e = getenv("MSLAM_B200_TAPER");
+        tapered = e ? atoi(e) : 1;
+    }
+    int bound[kMaxChunks + 1];
+    for(int c = 0; c <= nchunks; ++c)
+        bound[c] = (int)((long long)n_frames * c / nchunks);
+    if(tapered && nchunks == 4 && n_frames >= 32)
+        bound[1] = n_frames / 8, bound[2] = n_frames / 2, bound[3] = n_frames - n_frames / 8;
     cudaStream_t s_in = ctx->copy[0], s_out = ctx->copy[1];
     MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
     MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_done[kMaxChunks], st)); // "previous work on the context stream is ordered"
     MSLAM_CUDA_OK(cudaStreamWaitEvent(s_in, ctx->ev_done[kMaxChunks], 0));
     for(int c = 0; c < nchunks; ++c)
     {
-        const int b0 = c * per, b1 = std::min(n_frames, b0 + per);
+        const int b0 = bound[c], b1 = bound[c + 1];
         bool contiguous = (size_t)stride_bytes == row;
         for(int i = b0 + 1; i < b1 && contiguous; ++i)
             contiguous = frames[i] == frames[i - 1] + frame_bytes;
@@ -790,7 +802,7 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
     }
     for(int c = 0; c < nchunks; ++c)
     {
-        const int b0 = c * per, b1 = std::min(n_frames, b0 + per);
+        const int b0 = bound[c], b1 = bound[c + 1];
         if(b1 <= b0)
             continue;
         MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_h2d[c], 0));

@@ -8,13 +8,14 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _check_frame(pkg, oracle, ctx, bgr, frame=0, kp=None, desc=None, what=""):
+def _check_frame(pkg, oracle, ctx, bgr, frame=0, kp=None, desc=None, what="", params=None):
     H, W, _ = bgr.shape
-    okp, odesc, dumps = oracle.dist_detect_gray(oracle.gray(bgr), dumps=True)
+    okp, odesc, dumps = oracle.dist_detect_gray(oracle.gray(bgr), params, dumps=True)
+    nl = params.nlevels if params else 8
     w, h, s = ctx.level_geometry(W, H)
-    ow, oh, osc = oracle.dist_level_geometry(W, H)
+    ow, oh, osc = oracle.dist_level_geometry(W, H, nl, params.scale_factor if params else 1.2)
     assert (w == ow).all() and (h == oh).all() and s.tobytes() == osc.tobytes()
-    for l in range(8):
+    for l in range(nl):
         got = ctx.debug_image(pkg.DIST_PYRAMID, frame, l, W, H)
         assert (got == dumps["pyr"][l]).all(), f"{what} pyramid level {l}: {(got != dumps['pyr'][l]).sum()} px differ"
         assert ctx.debug_count(pkg.DIST_N_FAST, frame, l) == dumps["n_fast"][l], f"{what} n_fast level {l}"
@@ -48,6 +49,19 @@ def test_synthetic_sizes_bit_exact(pkg, oracle, W, H):
     with pkg.DistContext(max_width=W, max_height=H, max_batch=1) as ctx:
         kp, desc = ctx.detect(frames[0])
         _check_frame(pkg, oracle, ctx, frames[0], 0, kp, desc, f"{W}x{H}")
+
+
+@pytest.mark.parametrize("nlevels,sf,ini,mn,min_size,W,H", [(5, 1.5, 30, 10, 400, 640, 480), (3, 2.0, 12, 12, 5000, 800, 300),
+                                                            (8, 1.2, 20, 7, 150, 400, 400), (11, 1.1, 40, 5, 1000, 512, 384)])
+def test_non_default_parameters(pkg, oracle, nlevels, sf, ini, mn, min_size, W, H):
+    """orb_params / min_size other than the hard-coded ones, including an exact 2x pyramid and several initial tree nodes"""
+    frames, _ = pkg.synth.frame_batch(W, H, 1, 0, seed=nlevels * 100 + ini)
+    prm = oracle.dist_default_params(nlevels=nlevels, ini_fast_thr=ini, min_fast_thr=mn, min_size=min_size, scale_factor=sf)
+    with pkg.DistContext(max_width=W, max_height=H, nlevels=nlevels, scale_factor=sf, ini_fast_threshold=ini,
+                         min_fast_threshold=mn, min_size=min_size) as ctx:
+        kp, desc = ctx.detect(frames[0])
+        assert len(kp) > 0
+        _check_frame(pkg, oracle, ctx, frames[0], 0, kp, desc, f"{nlevels} levels x{sf}", params=prm)
 
 
 def test_noise_frame_many_candidates(pkg, oracle):
