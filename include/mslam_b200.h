@@ -121,6 +121,15 @@ MSLAM_B200_API int mslam_b200_detect(mslam_b200_ctx* ctx, const uint8_t* bgr, in
 MSLAM_B200_API int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width,
                                            int height, int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc,
                                            int capacity, int* n_out /* [n_frames] */);
+/* Pipelined form of mslam_b200_detect_batch for callers that stream batches: _begin enqueues the copy-in, the kernels
+ * and the copy-out of one batch and returns without waiting; _end waits for the OLDEST batch in flight and fills its
+ * n_out.  Up to two batches may be in flight, so the copy-in of batch t+1 (and t+2 once t has ended) overlaps the
+ * kernels and the copy-out of batch t -- the PCIe link never idles.  Frames and outputs must stay valid (and, for real
+ * overlap, be pinned: mslam_b200_host_alloc) until the matching _end.  mslam_b200_detect_batch == _begin + _end. */
+MSLAM_B200_API int mslam_b200_detect_batch_begin(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width,
+                                                 int height, int stride_bytes, mslam_b200_keypoint* out_kp,
+                                                 uint8_t* out_desc, int capacity, int* n_out);
+MSLAM_B200_API int mslam_b200_detect_batch_end(mslam_b200_ctx* ctx);
 /* Device-resident variant: d_bgr is [n_frames][height][width][3] dense in device memory; outputs are device arrays
  * [n_frames][capacity] (keypoints, descriptors) and [n_frames] (counts, un-clamped).  Asynchronous. */
 MSLAM_B200_API int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames, int width,
@@ -156,6 +165,11 @@ MSLAM_B200_API int mslam_b200_match_crosscheck(mslam_b200_ctx* ctx, const uint8_
 MSLAM_B200_API int mslam_b200_match_batch(mslam_b200_ctx* ctx, int mode, const uint8_t* from, const int* n_from,
                                           const uint8_t* to, const int* n_to, int n_pairs, int capacity, int* out_a,
                                           int* out_b, int* out_dist, int* n_out);
+/* pipelined form (one match batch in flight): _begin enqueues on the context stream, _end waits for the results */
+MSLAM_B200_API int mslam_b200_match_batch_begin(mslam_b200_ctx* ctx, int mode, const uint8_t* from, const int* n_from,
+                                                const uint8_t* to, const int* n_to, int n_pairs, int capacity, int* out_a,
+                                                int* out_b, int* out_dist, int* n_out);
+MSLAM_B200_API int mslam_b200_match_batch_end(mslam_b200_ctx* ctx);
 MSLAM_B200_API int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, const uint8_t* d_from, const int* d_n_from,
                                               const uint8_t* d_to, const int* d_n_to, int n_pairs, int capacity,
                                               int* d_out_a, int* d_out_b, int* d_out_dist, int* d_n_out);

@@ -203,6 +203,41 @@ class Context:
         self.last_status = rc
         return kp, desc, n
 
+    def detect_batch_begin(self, frames, capacity, out):
+        """pipelined detect_batch: enqueue one batch (frames [B, H, W, 3] u8, ideally pinned; out = (kp, desc, counts)
+        preallocated, ideally pinned) and return at once; up to two batches in flight.  Pair with detect_batch_end()."""
+        assert isinstance(frames, np.ndarray) and frames.dtype == np.uint8 and frames.ndim == 4 and frames.shape[3] == 3
+        B, H, W, _ = frames.shape
+        assert frames.strides[3] == 1 and frames.strides[2] == 3
+        ptrs = (C.c_void_p * B)(*[frames.ctypes.data + i * frames.strides[0] for i in range(B)])
+        kp, desc, n = out
+        rc = library().mslam_b200_detect_batch_begin(self._h, ptrs, B, W, H, frames.strides[1], _ptr(kp), _ptr(desc), capacity,
+                                                     _ptr(n))
+        self._chk(rc, "detect_batch_begin")
+        self._inflight = getattr(self, "_inflight", []) + [(frames, out)]  # keep the buffers alive until the end
+
+    def detect_batch_end(self, allow_capacity_error=False):
+        """wait for the oldest batch in flight -> its (kp, desc, counts)"""
+        rc = library().mslam_b200_detect_batch_end(self._h)
+        self._chk(rc, "detect_batch_end", allow=(E_CAPACITY,) if allow_capacity_error else ())
+        self.last_status = rc
+        _, out = self._inflight.pop(0)
+        return out
+
+    def match_batch_begin(self, mode, frm, n_from, to, n_to, out):
+        P, cap, _ = frm.shape
+        assert to.shape == frm.shape and frm.flags.c_contiguous and to.flags.c_contiguous
+        oa, ob, od, no = out
+        self._chk(library().mslam_b200_match_batch_begin(self._h, mode, _ptr(frm), _ptr(n_from), _ptr(to), _ptr(n_to), P, cap,
+                                                         _ptr(oa), _ptr(ob), _ptr(od), _ptr(no)), "match_batch_begin")
+        self._match_inflight = (frm, n_from, to, n_to, out)
+
+    def match_batch_end(self):
+        self._chk(library().mslam_b200_match_batch_end(self._h), "match_batch_end")
+        out = self._match_inflight[4]
+        self._match_inflight = None
+        return out
+
     def describe(self, bgr, kps):
         """descriptors (and angles) for GIVEN keypoints (x, y at level-0 scale, octave).  -> (kps', desc [N, 32])."""
         bgr = np.ascontiguousarray(bgr, np.uint8)

@@ -56,6 +56,17 @@ struct mslam_b200_ctx
     int* h_counts = nullptr;
     int* h_err = nullptr;
     int last_frames = 0;
+    // ---- host pipeline: up to two batches in flight (mslam_b200_detect_batch_begin / _end) ----
+    struct PendingBatch
+    {
+        bool active = false;
+        int n_frames = 0, capacity = 0;
+        int* n_out = nullptr;
+    } pend[2];
+    int pend_next = 0;
+    cudaEvent_t ev_slot_done[2] = {nullptr, nullptr}, ev_out_done = nullptr, ev_match_done = nullptr;
+    bool match_pending = false;
+    bool out_done_valid = false;
     // ---- HBM: matcher ----
     uint8_t *d_mfrom = nullptr, *d_mto = nullptr, *d_raw = nullptr;
     int *d_nfrom = nullptr, *d_nto = nullptr;
@@ -429,6 +440,9 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     for(int i = 0; i <= kMaxChunks; ++i)
         if(ctx->ev_done[i])
             cudaEventDestroy(ctx->ev_done[i]);
+    for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done, ctx->ev_match_done})
+        if(e)
+            cudaEventDestroy(e);
     if(ctx->own_stream && ctx->stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -501,7 +515,7 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     ctx->cand_elems = g.cand_elems;
     ctx->tab_cap = g.tab_elems + 64;
     ctx->bgr_bytes = B * c.max_width * c.max_height * 3;
-    CREATE_OK(cudaMalloc(&ctx->d_bgr, ctx->bgr_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_bgr, 2 * ctx->bgr_bytes)); // two pipeline slots
     CREATE_OK(cudaMalloc(&ctx->d_pyr, ctx->pyr_bytes));
     CREATE_OK(cudaMalloc(&ctx->d_blur, ctx->pyr_bytes));
     CREATE_OK(cudaMalloc(&ctx->d_xtab, ctx->tab_cap * sizeof(short2)));
@@ -534,8 +548,12 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
         CREATE_OK(cudaMalloc(&ctx->d_icw, icw.size() * sizeof(unsigned)));
         CREATE_OK(cudaMemcpy(ctx->d_icw, icw.data(), icw.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
     }
-    CREATE_OK(cudaHostAlloc(&ctx->h_counts, B * sizeof(int), cudaHostAllocDefault));
-    CREATE_OK(cudaHostAlloc(&ctx->h_err, B * sizeof(int), cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_counts, 2 * B * sizeof(int), cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_err, 2 * B * sizeof(int), cudaHostAllocDefault));
+    for(int i = 0; i < 2; ++i)
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_slot_done[i], cudaEventDisableTiming));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_out_done, cudaEventDisableTiming));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_match_done, cudaEventDisableTiming));
     // matcher
     const size_t dc = (size_t)ctx->desc_cap;
     CREATE_OK(cudaMalloc(&ctx->d_mfrom, B * dc * 32));
@@ -741,19 +759,12 @@ int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n
     return detect_range(ctx, d_bgr, 0, n_frames, d_kp, d_desc, capacity, d_counts);
 }
 
-int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
-                            int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+// enqueue one host batch into pipeline slot `slot` (copy-in, kernels, copy-out); nothing here waits for the GPU
+static int detect_batch_enqueue(mslam_b200_ctx* ctx, int slot, const uint8_t* const* frames, int n_frames, int width, int height,
+                                int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity)
 {
-    if(!ctx || !frames || !out_kp || !out_desc || !n_out || n_frames < 1 || n_frames > ctx->cfg.max_batch ||
-       capacity < 1 || width < 1 || height < 1 || stride_bytes < 3 * width || width > ctx->cfg.max_width ||
-       height > ctx->cfg.max_height)
-        return MSLAM_B200_E_INVALID;
-    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     cudaStream_t st = ctx->stream;
     const size_t row = (size_t)width * 3, frame_bytes = row * height;
-    for(int i = 0; i < n_frames; ++i)
-        if(!frames[i])
-            return MSLAM_B200_E_INVALID;
     int rc = set_geometry(ctx, width, height);
     if(rc)
         return rc;
@@ -782,9 +793,19 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
     if(tapered && nchunks == 4 && n_frames >= 32)
         bound[1] = n_frames / 8, bound[2] = n_frames / 2, bound[3] = n_frames - n_frames / 8;
     cudaStream_t s_in = ctx->copy[0], s_out = ctx->copy[1];
+    uint8_t* d_bgr = ctx->d_bgr + (size_t)slot * ctx->bgr_bytes;
+    const bool pipelined = ctx->pend[slot ^ 1].active;
+    // the previous batch's results must have left d_kp / d_desc / d_counts / d_err before this batch's kernels reuse them
+    if(ctx->out_done_valid)
+        MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_out_done, 0));
     MSLAM_CUDA_OK(cudaMemsetAsync(ctx->d_zero, 0, ctx->zero_bytes, st));
-    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_done[kMaxChunks], st)); // "previous work on the context stream is ordered"
-    MSLAM_CUDA_OK(cudaStreamWaitEvent(s_in, ctx->ev_done[kMaxChunks], 0));
+    if(!pipelined)
+    {
+        // earlier single-frame work on the context stream may still read this frame buffer (mslam_b200_describe); with a
+        // batch already in flight the only work queued since is that batch's, which lives in the other slot
+        MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_done[kMaxChunks], st));
+        MSLAM_CUDA_OK(cudaStreamWaitEvent(s_in, ctx->ev_done[kMaxChunks], 0));
+    }
     for(int c = 0; c < nchunks; ++c)
     {
         const int b0 = bound[c], b1 = bound[c + 1];
@@ -792,11 +813,11 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
         for(int i = b0 + 1; i < b1 && contiguous; ++i)
             contiguous = frames[i] == frames[i - 1] + frame_bytes;
         if(contiguous && b1 > b0)
-            MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_bgr + b0 * frame_bytes, frames[b0], (size_t)(b1 - b0) * frame_bytes,
+            MSLAM_CUDA_OK(cudaMemcpyAsync(d_bgr + b0 * frame_bytes, frames[b0], (size_t)(b1 - b0) * frame_bytes,
                                           cudaMemcpyHostToDevice, s_in));
         else
             for(int i = b0; i < b1; ++i)
-                MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * frame_bytes, row, frames[i], (size_t)stride_bytes, row,
+                MSLAM_CUDA_OK(cudaMemcpy2DAsync(d_bgr + i * frame_bytes, row, frames[i], (size_t)stride_bytes, row,
                                                 (size_t)height, cudaMemcpyHostToDevice, s_in));
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_h2d[c], s_in));
     }
@@ -806,7 +827,7 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
         if(b1 <= b0)
             continue;
         MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_h2d[c], 0));
-        rc = detect_range(ctx, ctx->d_bgr, b0, b1 - b0, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
+        rc = detect_range(ctx, d_bgr, b0, b1 - b0, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
         if(rc)
             return rc;
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_done[c], st));
@@ -820,17 +841,91 @@ int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, i
                                         (size_t)(b1 - b0), cudaMemcpyDeviceToHost, s_out));
     }
     ctx->last_frames = n_frames;
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_counts, ctx->d_counts, n_frames * sizeof(int), cudaMemcpyDeviceToHost, s_out));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_err, ctx->d_err, n_frames * sizeof(int), cudaMemcpyDeviceToHost, s_out));
-    MSLAM_CUDA_OK(cudaStreamSynchronize(s_out));
-    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
-    rc = MSLAM_B200_OK;
-    for(int i = 0; i < n_frames; ++i)
+    const size_t B = (size_t)ctx->cfg.max_batch;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_counts + slot * B, ctx->d_counts, n_frames * sizeof(int), cudaMemcpyDeviceToHost, s_out));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_err + slot * B, ctx->d_err, n_frames * sizeof(int), cudaMemcpyDeviceToHost, s_out));
+    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_slot_done[slot], s_out));
+    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_out_done, s_out));
+    ctx->out_done_valid = true;
+    return MSLAM_B200_OK;
+}
+
+// wait for the batch in `slot`, hand its counts to the caller
+static int detect_batch_finish(mslam_b200_ctx* ctx, int slot)
+{
+    mslam_b200_ctx::PendingBatch& pb = ctx->pend[slot];
+    pb.active = false;
+    MSLAM_CUDA_OK(cudaEventSynchronize(ctx->ev_slot_done[slot]));
+    const size_t B = (size_t)ctx->cfg.max_batch;
+    int rc = MSLAM_B200_OK;
+    for(int i = 0; i < pb.n_frames; ++i)
     {
-        n_out[i] = ctx->h_counts[i];
-        if(ctx->h_counts[i] > capacity || ctx->h_err[i])
+        const int n = ctx->h_counts[slot * B + i];
+        pb.n_out[i] = n;
+        if(n > pb.capacity || ctx->h_err[slot * B + i])
             rc = MSLAM_B200_E_CAPACITY;
     }
+    return rc;
+}
+
+static int detect_batch_args_ok(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
+                                int stride_bytes, const void* out_kp, const void* out_desc, int capacity, const int* n_out)
+{
+    if(!ctx || !frames || !out_kp || !out_desc || !n_out || n_frames < 1 || n_frames > ctx->cfg.max_batch ||
+       capacity < 1 || width < 1 || height < 1 || stride_bytes < 3 * width || width > ctx->cfg.max_width ||
+       height > ctx->cfg.max_height)
+        return 0;
+    for(int i = 0; i < n_frames; ++i)
+        if(!frames[i])
+            return 0;
+    return 1;
+}
+
+int mslam_b200_detect_batch_begin(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
+                                  int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(!detect_batch_args_ok(ctx, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity, n_out))
+        return MSLAM_B200_E_INVALID;
+    const int slot = ctx->pend_next;
+    if(ctx->pend[slot].active)
+        return MSLAM_B200_E_INVALID; // two batches are already in flight: call mslam_b200_detect_batch_end first
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    const int rc = detect_batch_enqueue(ctx, slot, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity);
+    if(rc)
+        return rc;
+    ctx->pend[slot].active = true;
+    ctx->pend[slot].n_frames = n_frames;
+    ctx->pend[slot].capacity = capacity;
+    ctx->pend[slot].n_out = n_out;
+    ctx->pend_next = slot ^ 1;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_detect_batch_end(mslam_b200_ctx* ctx)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    // the oldest batch in flight: the slot the next begin would take if it is busy, else the other one
+    int slot = ctx->pend_next;
+    if(!ctx->pend[slot].active)
+        slot ^= 1;
+    if(!ctx->pend[slot].active)
+        return MSLAM_B200_E_INVALID; // nothing in flight
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    return detect_batch_finish(ctx, slot);
+}
+
+int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
+                            int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(!detect_batch_args_ok(ctx, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity, n_out) ||
+       ctx->pend[0].active || ctx->pend[1].active)
+        return MSLAM_B200_E_INVALID;
+    int rc = mslam_b200_detect_batch_begin(ctx, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
+    if(rc)
+        return rc;
+    rc = mslam_b200_detect_batch_end(ctx);
+    MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     return rc;
 }
 
@@ -1014,11 +1109,11 @@ int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, const uint8_t* d_f
     return MSLAM_B200_OK;
 }
 
-int mslam_b200_match_batch(mslam_b200_ctx* ctx, int mode, const uint8_t* from, const int* n_from, const uint8_t* to,
-                           const int* n_to, int n_pairs, int capacity, int* out_a, int* out_b, int* out_dist, int* n_out)
+int mslam_b200_match_batch_begin(mslam_b200_ctx* ctx, int mode, const uint8_t* from, const int* n_from, const uint8_t* to,
+                                 const int* n_to, int n_pairs, int capacity, int* out_a, int* out_b, int* out_dist, int* n_out)
 {
     if(!ctx || !from || !to || !n_from || !n_to || !out_a || !out_b || !n_out || n_pairs < 1 ||
-       n_pairs > ctx->cfg.max_batch || capacity < 1 || capacity > ctx->desc_cap)
+       n_pairs > ctx->cfg.max_batch || capacity < 1 || capacity > ctx->desc_cap || ctx->match_pending)
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     cudaStream_t st = ctx->stream;
@@ -1036,8 +1131,26 @@ int mslam_b200_match_batch(mslam_b200_ctx* ctx, int mode, const uint8_t* from, c
     if(out_dist)
         MSLAM_CUDA_OK(cudaMemcpyAsync(out_dist, ctx->d_out_d, blk * sizeof(int), cudaMemcpyDeviceToHost, st));
     MSLAM_CUDA_OK(cudaMemcpyAsync(n_out, ctx->d_nout, n_pairs * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_match_done, st));
+    ctx->match_pending = true;
     return MSLAM_B200_OK;
+}
+
+int mslam_b200_match_batch_end(mslam_b200_ctx* ctx)
+{
+    if(!ctx || !ctx->match_pending)
+        return MSLAM_B200_E_INVALID;
+    ctx->match_pending = false;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    MSLAM_CUDA_OK(cudaEventSynchronize(ctx->ev_match_done));
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_match_batch(mslam_b200_ctx* ctx, int mode, const uint8_t* from, const int* n_from, const uint8_t* to,
+                           const int* n_to, int n_pairs, int capacity, int* out_a, int* out_b, int* out_dist, int* n_out)
+{
+    const int rc = mslam_b200_match_batch_begin(ctx, mode, from, n_from, to, n_to, n_pairs, capacity, out_a, out_b, out_dist, n_out);
+    return rc ? rc : mslam_b200_match_batch_end(ctx);
 }
 
 static int match_single(mslam_b200_ctx* ctx, int mode, const uint8_t* from, int n_from, int from_stride, const uint8_t* to,

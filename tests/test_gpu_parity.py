@@ -342,3 +342,46 @@ def test_launch_counter_counts(ctx, bundled):
     n0 = ctx.launch_count
     ctx.detect(bundled["bgr0"])
     assert ctx.launch_count - n0 >= 5
+
+
+def test_pipelined_host_batches_equal_blocking_calls(pkg):
+    """mslam_b200_detect_batch_begin / _end with two batches in flight + match_batch_begin / _end == the blocking calls"""
+    B, W, H = 8, 320, 240
+    batches, bases = [], None
+    for t in range(5):
+        fr, bases = pkg.synth.frame_batch(W, H, B, t, seed=21, bases=bases)
+        batches.append(fr)
+    with pkg.Context(max_width=W, max_height=H, max_batch=B, nfeatures=300) as ctx:
+        cap = ctx.kp_cap
+        ref = [ctx.detect_batch(f, cap) for f in batches]
+        ref_m = [ctx.match_batch(0, ref[t][1], ref[t][2], ref[t - 1][1], ref[t - 1][2]) for t in range(1, 5)]
+        hf = []
+        for f in batches:
+            h = pkg.pinned_empty(f.shape, np.uint8)
+            h[...] = f
+            hf.append(h)
+        outs = [(pkg.pinned_empty((B, cap), pkg.KP_DTYPE), pkg.pinned_empty((B, cap, 32), np.uint8), pkg.pinned_empty((B,), np.int32))
+                for _ in range(5)]
+        hm = [pkg.pinned_empty((B, cap), np.int32) for _ in range(3)] + [pkg.pinned_empty((B,), np.int32)]
+        ctx.detect_batch_begin(hf[0], cap, outs[0])
+        ctx.detect_batch_begin(hf[1], cap, outs[1])
+        with pytest.raises(pkg.MslamB200Error):  # a third batch does not fit
+            ctx.detect_batch_begin(hf[2], cap, outs[2])
+        with pytest.raises(pkg.MslamB200Error):  # and the blocking call refuses to jump the queue
+            ctx.detect_batch(batches[2], cap)
+        for t in range(5):
+            kp, desc, n = ctx.detect_batch_end()
+            if t + 2 < 5:
+                ctx.detect_batch_begin(hf[t + 2], cap, outs[t + 2])
+            assert (n == ref[t][2]).all()
+            for b in range(B):
+                assert kp[b, :n[b]].tobytes() == ref[t][0][b, :n[b]].tobytes() and (desc[b, :n[b]] == ref[t][1][b, :n[b]]).all()
+            if t >= 1:
+                ctx.match_batch_begin(0, outs[t][1], outs[t][2], outs[t - 1][1], outs[t - 1][2], tuple(hm))
+                oa, ob, od, no = ctx.match_batch_end()
+                ra, rb, rd, rn = ref_m[t - 1]
+                assert (no == rn).all()
+                for b in range(B):
+                    assert (oa[b, :no[b]] == ra[b, :rn[b]]).all() and (ob[b, :no[b]] == rb[b, :rn[b]]).all()
+        with pytest.raises(pkg.MslamB200Error):
+            ctx.detect_batch_end()  # nothing in flight
