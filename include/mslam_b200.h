@@ -267,6 +267,11 @@ MSLAM_B200_API int mslam_b200_dist_detect(mslam_b200_dist* d, const uint8_t* bgr
 MSLAM_B200_API int mslam_b200_dist_detect_batch(mslam_b200_dist* d, const uint8_t* const* frames, int n_frames, int width,
                                                 int height, int stride_bytes, mslam_b200_keypoint* out_kp,
                                                 uint8_t* out_desc, int capacity, int* n_out);
+/* pipelined form, as mslam_b200_detect_batch_begin / _end: up to two batches in flight, _end waits for the oldest */
+MSLAM_B200_API int mslam_b200_dist_detect_batch_begin(mslam_b200_dist* d, const uint8_t* const* frames, int n_frames,
+                                                      int width, int height, int stride_bytes, mslam_b200_keypoint* out_kp,
+                                                      uint8_t* out_desc, int capacity, int* n_out);
+MSLAM_B200_API int mslam_b200_dist_detect_batch_end(mslam_b200_dist* d);
 /* Device-resident variant (asynchronous on the handle's stream): d_bgr [n_frames][height][width][3] dense */
 MSLAM_B200_API int mslam_b200_dist_detect_batch_dev(mslam_b200_dist* d, const uint8_t* d_bgr, int n_frames, int width,
                                                     int height, mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity,

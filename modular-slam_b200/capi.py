@@ -509,6 +509,21 @@ class DistContext:
         self._check(rc, "mslam_b200_dist_detect_batch")
         return kp, desc, counts
 
+    def detect_batch_begin(self, frames, capacity, out):
+        """pipelined detect_batch (two batches in flight); frames / out should be pinned.  Pair with detect_batch_end()."""
+        assert isinstance(frames, np.ndarray) and frames.dtype == np.uint8 and frames.flags.c_contiguous
+        B, H, W, _ = frames.shape
+        kp, desc, counts = out
+        base, fs = frames.ctypes.data, frames.strides[0]
+        ptrs = (C.c_void_p * B)(*[base + i * fs for i in range(B)])
+        rc = library().mslam_b200_dist_detect_batch_begin(self._h, ptrs, B, W, H, W * 3, _ptr(kp), _ptr(desc), capacity, _ptr(counts))
+        self._check(rc, "mslam_b200_dist_detect_batch_begin")
+        self._inflight = getattr(self, "_inflight", []) + [(frames, out)]
+
+    def detect_batch_end(self):
+        self._check(library().mslam_b200_dist_detect_batch_end(self._h), "mslam_b200_dist_detect_batch_end")
+        return self._inflight.pop(0)[1]
+
     def detect_batch_dev(self, d_bgr, n_frames, W, H, d_kp, d_desc, capacity, d_counts):
         """device tensors in / out, asynchronous on the handle's stream"""
         rc = library().mslam_b200_dist_detect_batch_dev(self._h, _ptr(d_bgr), n_frames, W, H, _ptr(d_kp), _ptr(d_desc),

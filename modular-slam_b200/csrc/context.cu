@@ -64,7 +64,8 @@ struct mslam_b200_ctx
         int* n_out = nullptr;
     } pend[2];
     int pend_next = 0;
-    cudaEvent_t ev_slot_done[2] = {nullptr, nullptr}, ev_out_done = nullptr, ev_match_done = nullptr;
+    cudaEvent_t ev_slot_done[2] = {nullptr, nullptr}, ev_out_done = nullptr, ev_match_done = nullptr,
+                ev_match_in = nullptr, ev_match_k = nullptr;
     bool match_pending = false;
     bool out_done_valid = false;
     // ---- HBM: matcher ----
@@ -440,7 +441,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     for(int i = 0; i <= kMaxChunks; ++i)
         if(ctx->ev_done[i])
             cudaEventDestroy(ctx->ev_done[i]);
-    for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done, ctx->ev_match_done})
+    for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done, ctx->ev_match_done, ctx->ev_match_in, ctx->ev_match_k})
         if(e)
             cudaEventDestroy(e);
     if(ctx->own_stream && ctx->stream)
@@ -554,6 +555,8 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
         CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_slot_done[i], cudaEventDisableTiming));
     CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_out_done, cudaEventDisableTiming));
     CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_match_done, cudaEventDisableTiming));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_match_in, cudaEventDisableTiming));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_match_k, cudaEventDisableTiming));
     // matcher
     const size_t dc = (size_t)ctx->desc_cap;
     CREATE_OK(cudaMalloc(&ctx->d_mfrom, B * dc * 32));
@@ -1116,22 +1119,28 @@ int mslam_b200_match_batch_begin(mslam_b200_ctx* ctx, int mode, const uint8_t* f
        n_pairs > ctx->cfg.max_batch || capacity < 1 || capacity > ctx->desc_cap || ctx->match_pending)
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
-    cudaStream_t st = ctx->stream;
+    cudaStream_t st = ctx->stream, s_in = ctx->copy[0], s_out = ctx->copy[1];
     const size_t blk = (size_t)n_pairs * capacity;
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mfrom, from, blk * 32, cudaMemcpyHostToDevice, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mto, to, blk * 32, cudaMemcpyHostToDevice, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nfrom, n_from, n_pairs * sizeof(int), cudaMemcpyHostToDevice, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nto, n_to, n_pairs * sizeof(int), cudaMemcpyHostToDevice, st));
+    // descriptors go in on the copy-in engine and results come out on the copy-out engine, so that neither transfer
+    // stalls kernels of a detect batch queued on the context stream around this match
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mfrom, from, blk * 32, cudaMemcpyHostToDevice, s_in));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mto, to, blk * 32, cudaMemcpyHostToDevice, s_in));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nfrom, n_from, n_pairs * sizeof(int), cudaMemcpyHostToDevice, s_in));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nto, n_to, n_pairs * sizeof(int), cudaMemcpyHostToDevice, s_in));
+    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_match_in, s_in));
+    MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_match_in, 0));
     int rc = mslam_b200_match_batch_dev(ctx, mode, ctx->d_mfrom, ctx->d_nfrom, ctx->d_mto, ctx->d_nto, n_pairs, capacity,
                                         ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout);
     if(rc)
         return rc;
-    MSLAM_CUDA_OK(cudaMemcpyAsync(out_a, ctx->d_out_a, blk * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(out_b, ctx->d_out_b, blk * sizeof(int), cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_match_k, st));
+    MSLAM_CUDA_OK(cudaStreamWaitEvent(s_out, ctx->ev_match_k, 0));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(out_a, ctx->d_out_a, blk * sizeof(int), cudaMemcpyDeviceToHost, s_out));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(out_b, ctx->d_out_b, blk * sizeof(int), cudaMemcpyDeviceToHost, s_out));
     if(out_dist)
-        MSLAM_CUDA_OK(cudaMemcpyAsync(out_dist, ctx->d_out_d, blk * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(n_out, ctx->d_nout, n_pairs * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_match_done, st));
+        MSLAM_CUDA_OK(cudaMemcpyAsync(out_dist, ctx->d_out_d, blk * sizeof(int), cudaMemcpyDeviceToHost, s_out));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(n_out, ctx->d_nout, n_pairs * sizeof(int), cudaMemcpyDeviceToHost, s_out));
+    MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_match_done, s_out));
     ctx->match_pending = true;
     return MSLAM_B200_OK;
 }

@@ -1003,8 +1003,18 @@ struct mslam_b200_dist
     mslam_b200_keypoint* d_kp = nullptr;
     uint8_t* d_desc = nullptr;
     int* d_counts = nullptr;
-    int* h_counts = nullptr;
-    DistCounters* h_ctr = nullptr;
+    int* h_counts = nullptr;      // [2 slots][max_batch]
+    DistCounters* h_ctr = nullptr; // [2 slots][max_batch][kMaxLevels]
+    size_t bgr_bytes = 0;
+    struct PendingBatch
+    {
+        bool active = false;
+        int n_frames = 0, capacity = 0;
+        int* n_out = nullptr;
+    } pend[2];
+    int pend_next = 0;
+    cudaEvent_t ev_slot_done[2] = {nullptr, nullptr}, ev_out_done = nullptr;
+    bool out_done_valid = false;
     int last_frames = 0;
     bool timing = false;
     cudaEvent_t ev[7] = {nullptr};
@@ -1103,6 +1113,9 @@ void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
             cudaStreamSynchronize(ctx->copy[i]);
             cudaStreamDestroy(ctx->copy[i]);
         }
+    for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done})
+        if(e)
+            cudaEventDestroy(e);
     if(ctx->ev_fork)
         cudaEventDestroy(ctx->ev_fork);
     if(ctx->ev_join)
@@ -1182,7 +1195,8 @@ int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist
     ctx->xtab_cap = (int)g.xtab.size() + 16;
     ctx->ytab_cap = (int)g.ytab.size() + 16;
     ctx->tree_smem_max = g.tree_smem;
-    CREATE_OK(cudaMalloc(&ctx->d_bgr, B * c.max_width * c.max_height * 3));
+    ctx->bgr_bytes = B * c.max_width * c.max_height * 3;
+    CREATE_OK(cudaMalloc(&ctx->d_bgr, 2 * ctx->bgr_bytes)); // two pipeline slots
     CREATE_OK(cudaMalloc(&ctx->d_pyr, ctx->pyr_bytes));
     CREATE_OK(cudaMalloc(&ctx->d_blur, ctx->pyr_bytes));
     CREATE_OK(cudaMemset(ctx->d_pyr, 0, ctx->pyr_bytes));
@@ -1197,8 +1211,11 @@ int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist
     CREATE_OK(cudaMalloc(&ctx->d_kp, B * ctx->kp_cap * sizeof(mslam_b200_keypoint)));
     CREATE_OK(cudaMalloc(&ctx->d_desc, B * ctx->kp_cap * 32));
     CREATE_OK(cudaMalloc(&ctx->d_counts, B * sizeof(int)));
-    CREATE_OK(cudaMallocHost(&ctx->h_counts, B * sizeof(int)));
-    CREATE_OK(cudaMallocHost(&ctx->h_ctr, B * kMaxLevels * sizeof(DistCounters)));
+    CREATE_OK(cudaMallocHost(&ctx->h_counts, 2 * B * sizeof(int)));
+    CREATE_OK(cudaMallocHost(&ctx->h_ctr, 2 * B * kMaxLevels * sizeof(DistCounters)));
+    for(int i = 0; i < 2; ++i)
+        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_slot_done[i], cudaEventDisableTiming));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_out_done, cudaEventDisableTiming));
     ctx->tree_smem_max = kTreeSmemBudget; // any level that fits the budget runs from shared memory
     CREATE_OK(cudaFuncSetAttribute(k_dist_tree, cudaFuncAttributeMaxDynamicSharedMemorySize, kTreeSmemBudget));
 #undef CREATE_OK
@@ -1330,72 +1347,124 @@ int mslam_b200_dist_detect_batch_dev(mslam_b200_dist* ctx, const uint8_t* d_bgr,
     return dist_run(ctx, d_bgr, 0, n_frames, d_kp, d_desc, capacity, d_counts);
 }
 
-int mslam_b200_dist_detect_batch(mslam_b200_dist* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
-                                 int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+// Host batches flow through a chunked pipeline: copy-in of chunk c+1 (copy engine 1) overlaps the kernels of chunk c and
+// the copy-out of chunk c-1 (copy engine 2); with mslam_b200_dist_detect_batch_begin / _end two whole batches may be in
+// flight (two frame-buffer slots), so the copy-in of the next batch overlaps everything of the current one.
+static int dist_batch_args_ok(mslam_b200_dist* ctx, const uint8_t* const* frames, int n_frames, int width, int stride_bytes,
+                              const void* out_kp, const void* out_desc, int capacity, const int* n_out)
 {
     if(!ctx || !frames || !n_out || n_frames < 1 || n_frames > ctx->cfg.max_batch || capacity < 0 ||
        (capacity > 0 && (!out_kp || !out_desc)) || stride_bytes < 3 * width)
-        return MSLAM_B200_E_INVALID;
+        return 0;
     for(int i = 0; i < n_frames; ++i)
         if(!frames[i])
-            return MSLAM_B200_E_INVALID;
+            return 0;
+    return 1;
+}
+
+int mslam_b200_dist_detect_batch_begin(mslam_b200_dist* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
+                                       int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(!dist_batch_args_ok(ctx, frames, n_frames, width, stride_bytes, out_kp, out_desc, capacity, n_out))
+        return MSLAM_B200_E_INVALID;
+    const int slot = ctx->pend_next;
+    if(ctx->pend[slot].active)
+        return MSLAM_B200_E_INVALID; // two batches are already in flight
     DIST_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     int rc = dist_set_geometry(ctx, width, height);
     if(rc)
         return rc;
-    // chunked pipeline: copy-in of chunk c+1 (copy engine 1) overlaps the kernels of chunk c, and the copy-out of chunk c
-    // (copy engine 2, exact sizes once its counts are on the host) overlaps the kernels of chunk c+1
-    const size_t fbytes = (size_t)width * height * 3;
+    const size_t fbytes = (size_t)width * height * 3, B = (size_t)ctx->cfg.max_batch;
+    uint8_t* d_bgr = ctx->d_bgr + (size_t)slot * ctx->bgr_bytes;
     const int nchunks = ctx->timing ? 1 : std::min(kDistChunks, std::max(1, n_frames / 4));
-    const int nl = ctx->P.nlevels;
+    const int nl = ctx->P.nlevels, icap = ctx->kp_cap, ncopy = std::min(capacity, icap);
     int bounds[kDistChunks + 1];
     for(int c = 0; c <= nchunks; ++c)
         bounds[c] = (int)((long long)n_frames * c / nchunks);
+    // the previous batch's results must have left d_kp / d_desc / d_counts / d_ctr before this batch's kernels reuse them
+    if(ctx->out_done_valid)
+        DIST_CUDA_OK(cudaStreamWaitEvent(ctx->stream, ctx->ev_out_done, 0));
     for(int c = 0; c < nchunks; ++c)
     {
         for(int i = bounds[c]; i < bounds[c + 1]; ++i)
-            DIST_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr + i * fbytes, (size_t)width * 3, frames[i], (size_t)stride_bytes,
+            DIST_CUDA_OK(cudaMemcpy2DAsync(d_bgr + i * fbytes, (size_t)width * 3, frames[i], (size_t)stride_bytes,
                                            (size_t)width * 3, height, cudaMemcpyHostToDevice, ctx->copy[0]));
         DIST_CUDA_OK(cudaEventRecord(ctx->ev_h2d[c], ctx->copy[0]));
     }
     for(int c = 0; c < nchunks; ++c)
     {
+        const int b0 = bounds[c], nb = bounds[c + 1] - bounds[c];
         DIST_CUDA_OK(cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d[c], 0));
-        rc = dist_run(ctx, ctx->d_bgr, bounds[c], bounds[c + 1] - bounds[c], ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
+        rc = dist_run(ctx, d_bgr, b0, nb, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
         if(rc)
             return rc;
         DIST_CUDA_OK(cudaEventRecord(ctx->ev_done[c], ctx->stream));
         DIST_CUDA_OK(cudaStreamWaitEvent(ctx->copy[1], ctx->ev_done[c], 0));
-        DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_counts + bounds[c], ctx->d_counts + bounds[c], (bounds[c + 1] - bounds[c]) * sizeof(int),
-                                     cudaMemcpyDeviceToHost, ctx->copy[1]));
-        DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_ctr + (size_t)bounds[c] * nl, ctx->d_ctr + (size_t)bounds[c] * nl,
-                                     (size_t)(bounds[c + 1] - bounds[c]) * nl * sizeof(DistCounters), cudaMemcpyDeviceToHost, ctx->copy[1]));
-        DIST_CUDA_OK(cudaEventRecord(ctx->ev_cnt[c], ctx->copy[1]));
-    }
-    rc = MSLAM_B200_OK;
-    for(int c = 0; c < nchunks; ++c)
-    {
-        DIST_CUDA_OK(cudaEventSynchronize(ctx->ev_cnt[c]));
-        for(int i = bounds[c] * nl; i < bounds[c + 1] * nl; ++i)
-            if(ctx->h_ctr[i].err)
-                rc = MSLAM_B200_E_CAPACITY; // an internal list overflowed (cannot happen: capacities are upper bounds)
-        for(int i = bounds[c]; i < bounds[c + 1]; ++i)
+        DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_counts + slot * B + b0, ctx->d_counts + b0, nb * sizeof(int), cudaMemcpyDeviceToHost,
+                                     ctx->copy[1]));
+        DIST_CUDA_OK(cudaMemcpyAsync(ctx->h_ctr + (slot * B + b0) * kMaxLevels, ctx->d_ctr + (size_t)b0 * nl,
+                                     (size_t)nb * nl * sizeof(DistCounters), cudaMemcpyDeviceToHost, ctx->copy[1]));
+        if(ncopy > 0)
         {
-            const int n = ctx->h_counts[i];
-            n_out[i] = n;
-            if(n > capacity || n > ctx->kp_cap)
-                rc = MSLAM_B200_E_CAPACITY;
-            const int m = std::min(n, std::min(capacity, ctx->kp_cap));
-            if(m > 0)
-            {
-                DIST_CUDA_OK(cudaMemcpyAsync(out_kp + (size_t)i * capacity, ctx->d_kp + (size_t)i * ctx->kp_cap,
-                                             (size_t)m * sizeof(mslam_b200_keypoint), cudaMemcpyDeviceToHost, ctx->copy[1]));
-                DIST_CUDA_OK(cudaMemcpyAsync(out_desc + (size_t)i * capacity * 32, ctx->d_desc + (size_t)i * ctx->kp_cap * 32,
-                                             (size_t)m * 32, cudaMemcpyDeviceToHost, ctx->copy[1]));
-            }
+            // whole rows of the per-frame output blocks (the count is not known on the host yet)
+            DIST_CUDA_OK(cudaMemcpy2DAsync(out_kp + (size_t)b0 * capacity, (size_t)capacity * sizeof(mslam_b200_keypoint),
+                                           ctx->d_kp + (size_t)b0 * icap, (size_t)icap * sizeof(mslam_b200_keypoint),
+                                           (size_t)ncopy * sizeof(mslam_b200_keypoint), (size_t)nb, cudaMemcpyDeviceToHost, ctx->copy[1]));
+            DIST_CUDA_OK(cudaMemcpy2DAsync(out_desc + (size_t)b0 * capacity * 32, (size_t)capacity * 32,
+                                           ctx->d_desc + (size_t)b0 * icap * 32, (size_t)icap * 32, (size_t)ncopy * 32, (size_t)nb,
+                                           cudaMemcpyDeviceToHost, ctx->copy[1]));
         }
     }
-    DIST_CUDA_OK(cudaStreamSynchronize(ctx->copy[1]));
+    DIST_CUDA_OK(cudaEventRecord(ctx->ev_slot_done[slot], ctx->copy[1]));
+    DIST_CUDA_OK(cudaEventRecord(ctx->ev_out_done, ctx->copy[1]));
+    ctx->out_done_valid = true;
+    ctx->pend[slot].active = true;
+    ctx->pend[slot].n_frames = n_frames;
+    ctx->pend[slot].capacity = capacity;
+    ctx->pend[slot].n_out = n_out;
+    ctx->pend_next = slot ^ 1;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_dist_detect_batch_end(mslam_b200_dist* ctx)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    int slot = ctx->pend_next; // the oldest batch in flight
+    if(!ctx->pend[slot].active)
+        slot ^= 1;
+    if(!ctx->pend[slot].active)
+        return MSLAM_B200_E_INVALID;
+    DIST_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    mslam_b200_dist::PendingBatch& pb = ctx->pend[slot];
+    pb.active = false;
+    DIST_CUDA_OK(cudaEventSynchronize(ctx->ev_slot_done[slot]));
+    const size_t B = (size_t)ctx->cfg.max_batch;
+    const int nl = ctx->P.nlevels;
+    int rc = MSLAM_B200_OK;
+    for(int i = 0; i < pb.n_frames; ++i)
+    {
+        for(int l = 0; l < nl; ++l)
+            if(ctx->h_ctr[(slot * B + i) * kMaxLevels + l].err)
+                rc = MSLAM_B200_E_CAPACITY; // an internal list overflowed (cannot happen: capacities are upper bounds)
+        const int n = ctx->h_counts[slot * B + i];
+        pb.n_out[i] = n;
+        if(n > pb.capacity || n > ctx->kp_cap)
+            rc = MSLAM_B200_E_CAPACITY;
+    }
+    return rc;
+}
+
+int mslam_b200_dist_detect_batch(mslam_b200_dist* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
+                                 int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(!dist_batch_args_ok(ctx, frames, n_frames, width, stride_bytes, out_kp, out_desc, capacity, n_out) || ctx->pend[0].active ||
+       ctx->pend[1].active)
+        return MSLAM_B200_E_INVALID;
+    int rc = mslam_b200_dist_detect_batch_begin(ctx, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
+    if(rc)
+        return rc;
+    rc = mslam_b200_dist_detect_batch_end(ctx);
     DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     return rc;
 }

@@ -142,3 +142,34 @@ def test_capacity_and_invalid_sizes(pkg):
         with pytest.raises(pkg.MslamB200Error) as e:
             ctx.detect(np.zeros((100, 100, 3), np.uint8))  # level 7 is 28 px: the reference's border arithmetic underflows
         assert e.value.status == pkg.E_INVALID
+
+
+def test_pipelined_host_batches_equal_blocking_calls(pkg):
+    B, W, H = 8, 320, 240
+    batches, bases = [], None
+    for t in range(4):
+        fr, bases = pkg.synth.frame_batch(W, H, B, t, seed=33, bases=bases)
+        batches.append(fr)
+    with pkg.DistContext(max_width=W, max_height=H, max_batch=B) as ctx:
+        cap = ctx.kp_cap
+        ref = [ctx.detect_batch(f) for f in batches]
+        hf = []
+        for f in batches:
+            h = pkg.pinned_empty(f.shape, np.uint8)
+            h[...] = f
+            hf.append(h)
+        outs = [(pkg.pinned_empty((B, cap), pkg.KP_DTYPE), pkg.pinned_empty((B, cap, 32), np.uint8), pkg.pinned_empty((B,), np.int32))
+                for _ in range(4)]
+        ctx.detect_batch_begin(hf[0], cap, outs[0])
+        ctx.detect_batch_begin(hf[1], cap, outs[1])
+        with pytest.raises(pkg.MslamB200Error):
+            ctx.detect_batch_begin(hf[2], cap, outs[2])
+        for t in range(4):
+            kp, desc, n = ctx.detect_batch_end()
+            if t + 2 < 4:
+                ctx.detect_batch_begin(hf[t + 2], cap, outs[t + 2])
+            assert (n == ref[t][2]).all() and n.min() > 0
+            for b in range(B):
+                assert kp[b, :n[b]].tobytes() == ref[t][0][b, :n[b]].tobytes() and (desc[b, :n[b]] == ref[t][1][b, :n[b]]).all()
+        with pytest.raises(pkg.MslamB200Error):
+            ctx.detect_batch_end()
