@@ -1376,7 +1376,17 @@ int mslam_b200_dist_detect_batch_begin(mslam_b200_dist* ctx, const uint8_t* cons
         return rc;
     const size_t fbytes = (size_t)width * height * 3, B = (size_t)ctx->cfg.max_batch;
     uint8_t* d_bgr = ctx->d_bgr + (size_t)slot * ctx->bgr_bytes;
-    const int nchunks = ctx->timing ? 1 : std::min(kDistChunks, std::max(1, n_frames / 4));
+    // with another batch in flight the overlap comes from the batch pipeline itself; whole-batch launches then keep the
+    // kernels at their best occupancy (MSLAM_B200_DIST_CHUNKS overrides)
+    static int forced_chunks = -1;
+    if(forced_chunks < 0)
+    {
+        const char* e = getenv("MSLAM_B200_DIST_CHUNKS");
+        forced_chunks = e ? std::max(1, std::min(kDistChunks, atoi(e))) : 0;
+    }
+    const bool pipelined = ctx->pend[slot ^ 1].active;
+    int nchunks = forced_chunks ? forced_chunks : (pipelined ? 1 : kDistChunks);
+    nchunks = ctx->timing ? 1 : std::min(nchunks, std::max(1, n_frames / 4));
     const int nl = ctx->P.nlevels, icap = ctx->kp_cap, ncopy = std::min(capacity, icap);
     int bounds[kDistChunks + 1];
     for(int c = 0; c <= nchunks; ++c)
