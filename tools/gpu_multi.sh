@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 N=${N:-2}
 nvidia-smi -L > gpurun_out/smi_multi.txt
-for WL in c2 c5; do
+for WL in ${WLS:-c2 c5}; do
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
       bench.py --gpus $N --workload $WL --steps ${STEPS:-5} --warmup 3 --no-cpu-baseline > gpurun_out/bench_${WL}_n$N.log 2> gpurun_out/bench_${WL}_n$N.err
   echo "$WL N=$N rc=$?"; tail -1 gpurun_out/bench_${WL}_n$N.log | cut -c1-400; tail -3 gpurun_out/bench_${WL}_n$N.err
