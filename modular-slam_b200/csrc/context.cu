@@ -68,6 +68,16 @@ struct mslam_b200_ctx
                 ev_match_in = nullptr, ev_match_k = nullptr;
     bool match_pending = false;
     bool out_done_valid = false;
+    // ---- single-frame kernel graph ----
+    // one frame is ~16 small launches on three streams: enqueueing them costs more host time than they run for, so the
+    // single-frame calls replay a captured graph of the same launches (one per frame slot; re-captured on a new geometry)
+    struct FrameGraph
+    {
+        cudaGraphExec_t exec = nullptr;
+        int width = 0, height = 0, uses = 0;
+        long long launches = 0;
+    } graph1[2];
+    int graphs_enabled = -1; // -1: read MSLAM_B200_GRAPH on first use
     // ---- HBM: matcher ----
     uint8_t *d_mfrom = nullptr, *d_mto = nullptr, *d_raw = nullptr;
     int *d_nfrom = nullptr, *d_nto = nullptr;
@@ -444,6 +454,9 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done, ctx->ev_match_done, ctx->ev_match_in, ctx->ev_match_k})
         if(e)
             cudaEventDestroy(e);
+    for(auto& g : ctx->graph1)
+        if(g.exec)
+            cudaGraphExecDestroy(g.exec);
     if(ctx->own_stream && ctx->stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -763,6 +776,59 @@ int mslam_b200_detect_batch_dev(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n
 }
 
 // enqueue one host batch into pipeline slot `slot` (copy-in, kernels, copy-out); nothing here waits for the GPU
+// One frame through the kernels of detect_range, replayed from a captured graph once the geometry has been seen (the
+// first call of a geometry launches directly, which also performs any one-time kernel attribute set-up outside capture).
+// A capture that fails switches the graphs off for this context and the launches go out directly, as for batches.
+static int detect_one_graphed(mslam_b200_ctx* ctx, int slot, const uint8_t* d_bgr, int width, int height)
+{
+    cudaStream_t st = ctx->stream;
+    if(ctx->graphs_enabled < 0)
+    {
+        const char* e = getenv("MSLAM_B200_GRAPH");
+        ctx->graphs_enabled = e ? atoi(e) != 0 : 1;
+    }
+    auto& g = ctx->graph1[slot];
+    const bool usable = ctx->graphs_enabled && !ctx->timing && !(ctx->cfg.flags & MSLAM_B200_FLAG_SERIAL);
+    if(!usable)
+        return detect_range(ctx, d_bgr, 0, 1, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
+    if(g.width != width || g.height != height)
+    {
+        if(g.exec)
+            cudaGraphExecDestroy(g.exec);
+        g.exec = nullptr;
+        g.width = width, g.height = height, g.uses = 0;
+    }
+    if(!g.exec && g.uses++ >= 1)
+    {
+        const long long l0 = ctx->launches;
+        cudaGraph_t graph = nullptr;
+        bool ok = cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+        if(ok)
+        {
+            ok = detect_range(ctx, d_bgr, 0, 1, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts) == MSLAM_B200_OK;
+            ok = (cudaStreamEndCapture(st, &graph) == cudaSuccess) && ok && graph;
+        }
+        if(ok)
+            ok = cudaGraphInstantiate(&g.exec, graph, 0) == cudaSuccess;
+        if(graph)
+            cudaGraphDestroy(graph);
+        g.launches = ctx->launches - l0;
+        ctx->launches = l0; // nothing ran yet
+        if(!ok)
+        {
+            cudaGetLastError();
+            g.exec = nullptr;
+            ctx->graphs_enabled = 0;
+        }
+    }
+    if(!g.exec)
+        return detect_range(ctx, d_bgr, 0, 1, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
+    ctx->P.frame0 = 0, ctx->P.n_frames = 1;
+    MSLAM_CUDA_OK(cudaGraphLaunch(g.exec, st));
+    ctx->launches += g.launches;
+    return MSLAM_B200_OK;
+}
+
 static int detect_batch_enqueue(mslam_b200_ctx* ctx, int slot, const uint8_t* const* frames, int n_frames, int width, int height,
                                 int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity)
 {
@@ -830,7 +896,10 @@ static int detect_batch_enqueue(mslam_b200_ctx* ctx, int slot, const uint8_t* co
         if(b1 <= b0)
             continue;
         MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_h2d[c], 0));
-        rc = detect_range(ctx, d_bgr, b0, b1 - b0, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
+        if(n_frames == 1)
+            rc = detect_one_graphed(ctx, slot, d_bgr, width, height);
+        else
+            rc = detect_range(ctx, d_bgr, b0, b1 - b0, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
         if(rc)
             return rc;
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_done[c], st));

@@ -1015,6 +1015,14 @@ struct mslam_b200_dist
     int pend_next = 0;
     cudaEvent_t ev_slot_done[2] = {nullptr, nullptr}, ev_out_done = nullptr;
     bool out_done_valid = false;
+    // single-frame kernel graph (one per frame slot; the same launches as dist_run, replayed)
+    struct FrameGraph
+    {
+        cudaGraphExec_t exec = nullptr;
+        int width = 0, height = 0, uses = 0;
+        long long launches = 0;
+    } graph1[2];
+    int graphs_enabled = -1;
     int last_frames = 0;
     bool timing = false;
     cudaEvent_t ev[7] = {nullptr};
@@ -1113,6 +1121,9 @@ void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
             cudaStreamSynchronize(ctx->copy[i]);
             cudaStreamDestroy(ctx->copy[i]);
         }
+    for(auto& g : ctx->graph1)
+        if(g.exec)
+            cudaGraphExecDestroy(g.exec);
     for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done})
         if(e)
             cudaEventDestroy(e);
@@ -1335,6 +1346,57 @@ static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int frame0, int 
     return MSLAM_B200_OK;
 }
 
+// One frame through dist_run, replayed from a captured graph once its geometry has been seen (a frame is ~13 small
+// launches: enqueueing them costs more host time than they run for).  A failed capture switches the graphs off.
+static int dist_one_graphed(mslam_b200_dist* ctx, int slot, const uint8_t* d_bgr, int width, int height)
+{
+    if(ctx->graphs_enabled < 0)
+    {
+        const char* e = getenv("MSLAM_B200_GRAPH");
+        ctx->graphs_enabled = e ? atoi(e) != 0 : 1;
+    }
+    auto& g = ctx->graph1[slot];
+    if(!ctx->graphs_enabled || ctx->timing)
+        return dist_run(ctx, d_bgr, 0, 1, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
+    if(g.width != width || g.height != height)
+    {
+        if(g.exec)
+            cudaGraphExecDestroy(g.exec);
+        g.exec = nullptr;
+        g.width = width, g.height = height, g.uses = 0;
+    }
+    if(!g.exec && g.uses++ >= 1)
+    {
+        const long long l0 = ctx->launches;
+        cudaGraph_t graph = nullptr;
+        bool ok = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+        if(ok)
+        {
+            ok = dist_run(ctx, d_bgr, 0, 1, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts) == MSLAM_B200_OK;
+            ok = (cudaStreamEndCapture(ctx->stream, &graph) == cudaSuccess) && ok && graph;
+        }
+        if(ok)
+            ok = cudaGraphInstantiate(&g.exec, graph, 0) == cudaSuccess;
+        if(graph)
+            cudaGraphDestroy(graph);
+        g.launches = ctx->launches - l0;
+        ctx->launches = l0; // nothing ran yet
+        if(!ok)
+        {
+            cudaGetLastError();
+            g.exec = nullptr;
+            ctx->graphs_enabled = 0;
+        }
+    }
+    if(!g.exec)
+        return dist_run(ctx, d_bgr, 0, 1, ctx->d_kp, ctx->d_desc, ctx->kp_cap, ctx->d_counts);
+    ctx->P.n_frames = 1, ctx->P.frame0 = 0;
+    ctx->last_frames = 1;
+    DIST_CUDA_OK(cudaGraphLaunch(g.exec, ctx->stream));
+    ctx->launches += g.launches;
+    return MSLAM_B200_OK;
+}
+
 int mslam_b200_dist_detect_batch_dev(mslam_b200_dist* ctx, const uint8_t* d_bgr, int n_frames, int width, int height,
                                      mslam_b200_keypoint* d_kp, uint8_t* d_desc, int capacity, int* d_counts)
 {
@@ -1405,7 +1467,8 @@ int mslam_b200_dist_detect_batch_begin(mslam_b200_dist* ctx, const uint8_t* cons
     {
         const int b0 = bounds[c], nb = bounds[c + 1] - bounds[c];
         DIST_CUDA_OK(cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d[c], 0));
-        rc = dist_run(ctx, d_bgr, b0, nb, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
+        rc = n_frames == 1 ? dist_one_graphed(ctx, slot, d_bgr, width, height)
+                           : dist_run(ctx, d_bgr, b0, nb, ctx->d_kp, ctx->d_desc, icap, ctx->d_counts);
         if(rc)
             return rc;
         DIST_CUDA_OK(cudaEventRecord(ctx->ev_done[c], ctx->stream));

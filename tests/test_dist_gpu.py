@@ -173,3 +173,26 @@ def test_pipelined_host_batches_equal_blocking_calls(pkg):
                 assert kp[b, :n[b]].tobytes() == ref[t][0][b, :n[b]].tobytes() and (desc[b, :n[b]] == ref[t][1][b, :n[b]]).all()
         with pytest.raises(pkg.MslamB200Error):
             ctx.detect_batch_end()
+
+
+def test_single_frame_graph_replay_matches_oracle(pkg, oracle):
+    """Single-frame calls replay a captured kernel graph from the third call of a geometry on (per frame slot): a stream of
+    different frames, a geometry change in the middle and a return to the first geometry all stay bit-exact, and the
+    launch counter advances by the same amount for a replayed frame as for a directly launched one."""
+    W, H = 320, 240
+    frames, bases = [], None
+    for t in range(7):
+        fr, bases = pkg.synth.frame_batch(W, H, 1, t, seed=91, bases=bases)
+        frames.append(fr[0])
+    other, _ = pkg.synth.frame_batch(400, 300, 1, 0, seed=92)
+    with pkg.DistContext(max_width=400, max_height=300, max_batch=1) as ctx:
+        per_frame = []
+        for t, f in enumerate(frames):
+            l0 = ctx.launch_count
+            kp, desc = ctx.detect(f)
+            per_frame.append(ctx.launch_count - l0)
+            _check_frame(pkg, oracle, ctx, f, 0, kp, desc, f"frame {t}")
+            if t == 4:
+                kp, desc = ctx.detect(other[0])
+                _check_frame(pkg, oracle, ctx, other[0], 0, kp, desc, "other geometry")
+        assert len(set(per_frame)) == 1 and per_frame[0] >= 10

@@ -385,3 +385,32 @@ def test_pipelined_host_batches_equal_blocking_calls(pkg):
                     assert (oa[b, :no[b]] == ra[b, :rn[b]]).all() and (ob[b, :no[b]] == rb[b, :rn[b]]).all()
         with pytest.raises(pkg.MslamB200Error):
             ctx.detect_batch_end()  # nothing in flight
+
+
+def test_single_frame_graph_replay_matches_oracle(pkg, oracle, bundled):
+    """mslam_b200_detect replays a captured kernel graph from the third call of a geometry on (per frame slot): a stream
+    of different frames, a geometry change in the middle, a describe-only call and a batch in between all stay
+    bit-exact, and a replayed frame advances the launch counter like a directly launched one."""
+    W, H = 320, 240
+    frames, bases = [], None
+    for t in range(7):
+        fr, bases = pkg.synth.frame_batch(W, H, 1, t, seed=19, bases=bases)
+        frames.append(fr[0])
+    prm = oracle.default_params(500)
+    with pkg.Context(max_width=640, max_height=480, max_batch=2, nfeatures=500) as c:
+        per_frame = []
+        for t, f in enumerate(frames):
+            l0 = c.launch_count
+            kp, desc = c.detect(f)
+            per_frame.append(c.launch_count - l0)
+            okp, odesc = oracle.orb_detect_rgb(f, prm)
+            _assert_same_keypoints(kp, desc, okp, odesc, f"frame {t}")
+            if t == 3:
+                kp, desc = c.detect(bundled["bgr0"])
+                okp, odesc = oracle.orb_detect_rgb(bundled["bgr0"], prm)
+                _assert_same_keypoints(kp, desc, okp, odesc, "other geometry")
+            if t == 5:
+                kb, db, cnt = c.detect_batch(np.stack([frames[0], frames[1]]))
+                okp, odesc = oracle.orb_detect_rgb(frames[1], prm)
+                _assert_same_keypoints(kb[1, :cnt[1]], db[1, :cnt[1]], okp, odesc, "batch between replays")
+        assert len(set(per_frame)) == 1 and per_frame[0] >= 10
