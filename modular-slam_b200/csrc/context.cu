@@ -83,6 +83,8 @@ struct mslam_b200_ctx
     int *d_nfrom = nullptr, *d_nto = nullptr;
     unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
     unsigned *d_part0 = nullptr, *d_part1 = nullptr; // per-slice partial top-2 keys of the small-batch kNN
+    uint8_t *d_xa = nullptr, *d_xb = nullptr;        // +1/-1 int8 expansions of the two descriptor sets (knn_mma.cu)
+    int knn_mma = 1;                                 // MSLAM_KNN_MMA: 0 scalar kernel only, 1 by problem size, 2 always
     int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
     int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
     // ---- copy engines of the host entry points (chunked H2D / compute / D2H pipeline) ----
@@ -416,7 +418,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw};
+                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb};
     for(void* p : dev)
         if(p)
             cudaFree(p);
@@ -583,6 +585,13 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaMalloc(&ctx->d_key1b, B * dc * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_part0, kKnnMaxSlices * B * dc * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_part1, kKnnMaxSlices * B * dc * sizeof(unsigned)));
+    if(const char* e = getenv("MSLAM_KNN_MMA"))
+        ctx->knn_mma = atoi(e);
+    if(ctx->knn_mma)
+    {
+        CREATE_OK(cudaMalloc(&ctx->d_xa, knn_mma_bytes((int)B, (int)dc)));
+        CREATE_OK(cudaMalloc(&ctx->d_xb, knn_mma_bytes((int)B, (int)dc)));
+    }
     CREATE_OK(cudaMalloc(&ctx->d_out_a, B * dc * sizeof(int)));
     CREATE_OK(cudaMalloc(&ctx->d_out_b, B * dc * sizeof(int)));
     CREATE_OK(cudaMalloc(&ctx->d_out_d, B * dc * sizeof(int)));
@@ -1143,6 +1152,30 @@ static int upload_desc(mslam_b200_ctx* ctx, const uint8_t* src, int n, int strid
     return MSLAM_B200_OK;
 }
 
+// kNN (k = 2) of every query set against its train set -> packed keys; `both` also runs train against query (cross
+// check).  Large problems go to the tensor-core kernel (one int8 expansion of each set, shared by both directions), small
+// ones to the scalar kernel, whose one-warp-per-64-queries granularity fills the GPU better when there is little work.
+static int run_knn(mslam_b200_ctx* ctx, const uint8_t* d_q, const int* d_nq, const uint8_t* d_t, const int* d_nt, int n_pairs,
+                   int cap, bool both)
+{
+    cudaStream_t st = ctx->stream;
+    const long long ctas = (long long)((cap + 127) / 128) * n_pairs;
+    const bool mma = ctx->knn_mma == 2 || (ctx->knn_mma == 1 && cap >= 256 && ctas >= ctx->sm_count / 2);
+    if(mma)
+    {
+        launch_expand_pm1(st, d_q, d_nq, n_pairs, cap, ctx->d_xa, &ctx->launches);
+        launch_expand_pm1(st, d_t, d_nt, n_pairs, cap, ctx->d_xb, &ctx->launches);
+        MSLAM_CUDA_OK(launch_knn2_mma(st, ctx->d_xa, d_nq, ctx->d_xb, d_nt, n_pairs, cap, ctx->d_key0, ctx->d_key1, &ctx->launches));
+        if(both)
+            MSLAM_CUDA_OK(launch_knn2_mma(st, ctx->d_xb, d_nt, ctx->d_xa, d_nq, n_pairs, cap, ctx->d_key0b, ctx->d_key1b, &ctx->launches));
+        return MSLAM_B200_OK;
+    }
+    launch_knn2(st, d_q, d_nq, d_t, d_nt, n_pairs, cap, ctx->d_key0, ctx->d_key1, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
+    if(both)
+        launch_knn2(st, d_t, d_nt, d_q, d_nq, n_pairs, cap, ctx->d_key0b, ctx->d_key1b, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
+    return MSLAM_B200_OK;
+}
+
 static int upload_counts(mslam_b200_ctx* ctx, int n_from, int n_to)
 {
     ctx->h_n2[0] = n_from;
@@ -1164,9 +1197,9 @@ int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, const uint8_t* d_f
     // query = `to`, train = `from` (orb_feature.cpp:96)
     {
         StageTimer t(ctx, MSLAM_B200_T_KNN);
-        launch_knn2(st, d_to, d_n_to, d_from, d_n_from, n_pairs, capacity, ctx->d_key0, ctx->d_key1, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
-        if(mode == 1)
-            launch_knn2(st, d_from, d_n_from, d_to, d_n_to, n_pairs, capacity, ctx->d_key0b, ctx->d_key1b, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
+        const int rc = run_knn(ctx, d_to, d_n_to, d_from, d_n_from, n_pairs, capacity, mode == 1);
+        if(rc)
+            return rc;
     }
     {
         StageTimer t(ctx, MSLAM_B200_T_COMPACT);
@@ -1335,7 +1368,9 @@ int mslam_b200_knn2(mslam_b200_ctx* ctx, const uint8_t* query, int n_query, int 
     if(rc)
         return rc;
     const int cap = ctx->desc_cap;
-    launch_knn2(st, ctx->d_mto, ctx->d_nto, ctx->d_mfrom, ctx->d_nfrom, 1, cap, ctx->d_key0, ctx->d_key1, ctx->d_part0, ctx->d_part1, ctx->sm_count, &ctx->launches);
+    rc = run_knn(ctx, ctx->d_mto, ctx->d_nto, ctx->d_mfrom, ctx->d_nfrom, 1, cap, false);
+    if(rc)
+        return rc;
     // unpack into the four int scratch arrays (out_a, out_b, out_d, key0b reinterpreted)
     int* d_i1 = reinterpret_cast<int*>(ctx->d_key0b);
     launch_unpack_knn(st, ctx->d_key0, ctx->d_key1, n_query, ctx->d_out_a, ctx->d_out_d, d_i1, ctx->d_out_b, &ctx->launches);

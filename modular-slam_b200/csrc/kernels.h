@@ -27,6 +27,13 @@ void brief_pattern_transposed(float* out1024);
 constexpr int kKnnMaxSlices = 8; // train-set slices of the small-batch kNN (scratch: kKnnMaxSlices x [pair][cap] keys)
 void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
                  unsigned* key0, unsigned* key1, unsigned* part0, unsigned* part1, int sm_count, long long* launches);
+// tensor-core kNN (knn_mma.cu): descriptors expanded to +1/-1 int8 rows, then D = Q T^T on tcgen05 with a top-2 epilogue
+int knn_mma_pad(int cap);
+size_t knn_mma_bytes(int n_pairs, int cap);
+void launch_expand_pm1(cudaStream_t st, const uint8_t* desc, const int* counts, int n_pairs, int cap, uint8_t* out,
+                       long long* launches);
+cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, const uint8_t* xt, const int* tn, int n_pairs,
+                            int cap, unsigned* key0, unsigned* key1, long long* launches);
 void launch_ratio_compact(cudaStream_t st, const unsigned* key0, const unsigned* key1, const int* qn, const int* tn,
                           int n_pairs, int cap, double ratio, int* out_a, int* out_b, int* out_d, int* n_out,
                           long long* launches);
