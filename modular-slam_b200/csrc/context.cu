@@ -84,6 +84,8 @@ struct mslam_b200_ctx
     unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
     unsigned *d_part0 = nullptr, *d_part1 = nullptr; // per-slice partial top-2 keys of the small-batch kNN
     uint8_t *d_xa = nullptr, *d_xb = nullptr;        // +1/-1 int8 expansions of the two descriptor sets (knn_mma.cu)
+    uint8_t *d_xdb = nullptr, *d_xqf = nullptr;      // ... of a chunk of keyframes / of the query frames (DB scoring), lazily sized
+    size_t xdb_bytes = 0, xqf_bytes = 0;
     int knn_mma = 1;                                 // MSLAM_KNN_MMA: 0 scalar kernel only, 1 by problem size, 2 always
     int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
     int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
@@ -418,7 +420,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb};
+                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb, ctx->d_xdb, ctx->d_xqf};
     for(void* p : dev)
         if(p)
             cudaFree(p);
@@ -1159,12 +1161,11 @@ static int run_knn(mslam_b200_ctx* ctx, const uint8_t* d_q, const int* d_nq, con
                    int cap, bool both)
 {
     cudaStream_t st = ctx->stream;
-    const long long ctas = (long long)((cap + 127) / 128) * n_pairs;
+    const long long ctas = (long long)((cap + 255) / 256) * n_pairs;
     const bool mma = ctx->knn_mma == 2 || (ctx->knn_mma == 1 && cap >= 256 && ctas >= ctx->sm_count / 2);
     if(mma)
     {
-        launch_expand_pm1(st, d_q, d_nq, n_pairs, cap, ctx->d_xa, &ctx->launches);
-        launch_expand_pm1(st, d_t, d_nt, n_pairs, cap, ctx->d_xb, &ctx->launches);
+        launch_expand_pm1_x2(st, d_q, d_nq, ctx->d_xa, d_t, d_nt, ctx->d_xb, n_pairs, cap, &ctx->launches);
         MSLAM_CUDA_OK(launch_knn2_mma(st, ctx->d_xa, d_nq, ctx->d_xb, d_nt, n_pairs, cap, ctx->d_key0, ctx->d_key1, &ctx->launches));
         if(both)
             MSLAM_CUDA_OK(launch_knn2_mma(st, ctx->d_xb, d_nt, ctx->d_xa, d_nq, n_pairs, cap, ctx->d_key0b, ctx->d_key1b, &ctx->launches));
@@ -1391,6 +1392,43 @@ int mslam_b200_db_scores_dev(mslam_b200_ctx* ctx, const uint8_t* d_queries, cons
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     StageTimer t(ctx, MSLAM_B200_T_DB);
+    cudaStream_t st = ctx->stream;
+    // Large scorings go to the tensor-core kernel: the query frames and (a chunk at a time, bounded scratch) the keyframes
+    // are expanded to +1/-1 int8 rows, which costs ~0.2 % of the scoring itself.
+    const long long work = (long long)n_query_frames * n_keyframes * ((k_cap + 255) / 256);
+    if(ctx->knn_mma == 2 || (ctx->knn_mma == 1 && q_cap >= 256 && work >= 4LL * ctx->sm_count))
+    {
+        const size_t per_kf = (size_t)knn_mma_pad(k_cap) * 256, per_qf = (size_t)knn_mma_pad(q_cap) * 256;
+        const int kf_chunk = (int)std::min<size_t>(std::min<size_t>((size_t)n_keyframes, 65535), std::max<size_t>(1, ((size_t)4 << 30) / per_kf));
+        if(ctx->xdb_bytes < kf_chunk * per_kf || ctx->xqf_bytes < n_query_frames * per_qf)
+        {
+            MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+            if(ctx->xdb_bytes < kf_chunk * per_kf)
+            {
+                cudaFree(ctx->d_xdb);
+                ctx->d_xdb = nullptr, ctx->xdb_bytes = 0;
+                MSLAM_CUDA_OK(cudaMalloc(&ctx->d_xdb, kf_chunk * per_kf));
+                ctx->xdb_bytes = kf_chunk * per_kf;
+            }
+            if(ctx->xqf_bytes < n_query_frames * per_qf)
+            {
+                cudaFree(ctx->d_xqf);
+                ctx->d_xqf = nullptr, ctx->xqf_bytes = 0;
+                MSLAM_CUDA_OK(cudaMalloc(&ctx->d_xqf, n_query_frames * per_qf));
+                ctx->xqf_bytes = n_query_frames * per_qf;
+            }
+        }
+        MSLAM_CUDA_OK(cudaMemsetAsync(d_scores, 0, (size_t)n_query_frames * n_keyframes * sizeof(int), st));
+        launch_expand_pm1(st, d_queries, d_q_counts, n_query_frames, q_cap, ctx->d_xqf, &ctx->launches);
+        for(int kf0 = 0; kf0 < n_keyframes; kf0 += kf_chunk)
+        {
+            const int nk = std::min(kf_chunk, n_keyframes - kf0);
+            launch_expand_pm1(st, d_db + (size_t)kf0 * k_cap * 32, d_k_counts + kf0, nk, k_cap, ctx->d_xdb, &ctx->launches);
+            MSLAM_CUDA_OK(launch_db_scores_mma(st, ctx->d_xqf, d_q_counts, n_query_frames, q_cap, ctx->d_xdb, d_k_counts + kf0, nk,
+                                               k_cap, ctx->cfg.ratio, d_scores + kf0, n_keyframes, &ctx->launches));
+        }
+        return MSLAM_B200_OK;
+    }
     MSLAM_CUDA_OK(launch_db_scores(ctx->stream, d_queries, d_q_counts, n_query_frames, q_cap, d_db, d_k_counts, n_keyframes,
                                    k_cap, ctx->cfg.ratio, d_scores, ctx->sm_count, &ctx->launches));
     return MSLAM_B200_OK;

@@ -32,8 +32,13 @@ int knn_mma_pad(int cap);
 size_t knn_mma_bytes(int n_pairs, int cap);
 void launch_expand_pm1(cudaStream_t st, const uint8_t* desc, const int* counts, int n_pairs, int cap, uint8_t* out,
                        long long* launches);
+void launch_expand_pm1_x2(cudaStream_t st, const uint8_t* desc0, const int* counts0, uint8_t* out0, const uint8_t* desc1,
+                          const int* counts1, uint8_t* out1, int n_pairs, int cap, long long* launches);
 cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, const uint8_t* xt, const int* tn, int n_pairs,
                             int cap, unsigned* key0, unsigned* key1, long long* launches);
+cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const int* q_counts, int nq_frames, int q_cap,
+                                 const uint8_t* xdb, const int* k_counts, int n_keyframes, int k_cap, double ratio, int* scores,
+                                 int score_stride, long long* launches);
 void launch_ratio_compact(cudaStream_t st, const unsigned* key0, const unsigned* key1, const int* qn, const int* tn,
                           int n_pairs, int cap, double ratio, int* out_a, int* out_b, int* out_d, int* n_out,
                           long long* launches);

@@ -7,16 +7,17 @@
 // A 256-bit descriptor is expanded to 256 int8 values +1 / -1 (k_expand_pm1).  For two descriptors a, b
 //      dot(a, b) = (#equal bits) - (#different bits) = 256 - 2 * hamming(a, b)
 // exactly, in int32.  So the all-pairs distance matrix of a (query set, train set) pair is one int8 GEMM with K = 256:
-//      D[128 x 256] = Q[128 x 256] * T[256 x 256]^T        -> 8 tcgen05.mma.kind::i8 (M128 N256 K32) per tile
+//      D[128 x 128] = Q[128 x 256] * T[128 x 256]^T        -> 8 tcgen05.mma.kind::i8 (M128 N128 K32) per tile
 // and the packed result key of the scalar kernel, (hamming << 16) | train index, is one IMAD of the accumulator:
 //      key = D * (-32768) + (0x800000 + index).
 //
-// One CTA = one (frame pair, 128 queries): the query tile stays in shared memory, the train set streams through a
-// two-stage ring of 64 KB tiles (cp.async.bulk from the expanded copy in HBM/L2, completion on mbarriers), accumulators
-// are double-buffered in tensor memory (2 x 256 columns), and eight epilogue warps read them back with tcgen05.ld
-// (one query row per lane) and keep the running top-2 in registers.  Roles: warp 0 lane 0 = bulk-copy producer,
-// warp 1 lane 0 = MMA issuer, warps 2..9 = epilogue (warp w reads TMEM lanes 32 * (w % 4) .. + 31; the two warps of a
-// lane quarter split the 256 columns).
+// One CTA = one (frame pair, 256 queries): the two 128-row query tiles stay in shared memory (64 KB), the train set
+// streams through a four-stage ring of 128-descriptor tiles (32 KB each, cp.async.bulk from the expanded copy in HBM/L2,
+// completion on mbarriers -- three tiles in flight per SM cover the L2 latency), each train tile feeds 2 x 8 MMAs
+// (M128 N128 K32), accumulators are double-buffered in tensor memory (2 stages x 2 query tiles x 128 columns = all 512),
+// and eight epilogue warps read them back with tcgen05.ld (one query row per lane) and keep the running top-2 in
+// registers.  Roles: warp 0 lane 0 = bulk-copy producer, warp 1 lane 0 = MMA issuer, warps 2..9 = epilogue (warp w reads
+// TMEM lanes 32 * (w % 4) .. + 31 of query tile (w - 2) / 4).
 //
 // Shared-memory operand layout (and, so that a tile is one contiguous range, the layout of the expanded copy in
 // HBM): the no-swizzle K-major canonical layout -- core matrices of 8 rows x 16 bytes stored as 128 contiguous
@@ -30,14 +31,17 @@ namespace mslam_b200
 namespace
 {
 constexpr unsigned kNoKey = 0xffffffffu;
-constexpr int MMA_M = 128, MMA_N = 256;
+constexpr int MMA_M = 128, MMA_N = 128;
+constexpr int CTA_ROWS = 2 * MMA_M;          // queries per CTA (two MMA row tiles)
 constexpr int ROW_BYTES = 256;               // expanded descriptor: 256 x int8
-constexpr int A_BYTES = MMA_M * ROW_BYTES;   // 32 KB
-constexpr int B_BYTES = MMA_N * ROW_BYTES;   // 64 KB
-constexpr int STAGES = 2;
+constexpr int A_BYTES = CTA_ROWS * ROW_BYTES; // 64 KB
+constexpr int B_BYTES = MMA_N * ROW_BYTES;   // 32 KB
+constexpr int STAGES = 4;                    // train-tile ring
+constexpr int ACC_STAGES = 2;                // accumulator stages in tensor memory
 constexpr int BULK = 16384;                  // bytes per cp.async.bulk
 constexpr int MMA_THREADS = 64 + 256;        // producer warp + MMA warp + 8 epilogue warps
 constexpr int TMEM_COLS = 512;
+constexpr int PAD_ROWS = 256;                // rows of an expanded set are padded to a multiple of this
 constexpr int SMEM_BYTES = A_BYTES + STAGES * B_BYTES + 256;
 
 // instruction descriptor of tcgen05.mma.kind::i8: D = S32 (bits 4-5 = 2), A = B = signed 8 bit (bits 7-9, 10-12 = 1),
@@ -132,21 +136,6 @@ __device__ __forceinline__ void tmem_wait(uint32_t (&v)[32])
                  : "memory");
 }
 
-// running top-2 (smallest keys) as two independent chains, merged at the end
-struct Top2
-{
-    unsigned a0 = kNoKey, a1 = kNoKey, b0 = kNoKey, b1 = kNoKey;
-    __device__ __forceinline__ void push_a(unsigned key)
-    {
-        a1 = min(a1, max(a0, key));
-        a0 = min(a0, key);
-    }
-    __device__ __forceinline__ void push_b(unsigned key)
-    {
-        b1 = min(b1, max(b0, key));
-        b0 = min(b0, key);
-    }
-};
 __device__ __forceinline__ void merge2(unsigned& k0, unsigned& k1, unsigned o0, unsigned o1)
 {
     // two sorted pairs -> the two smallest of the four
@@ -155,42 +144,63 @@ __device__ __forceinline__ void merge2(unsigned& k0, unsigned& k1, unsigned o0, 
     k0 = lo;
 }
 
-// 32 accumulators (columns col0 .. col0 + 31 of the tile) -> keys -> top-2 chains.  MASKED: columns >= n_valid are
-// train descriptors that do not exist (last tile of a ragged set).
+// Running top-2 of one row over the 128 columns of a tile, two columns per register.
+// Inside a tile a key fits 16 bits: hamming (0..256) * 128 + column (0..127) <= 32895, so the even and the odd
+// columns run as the two halves of VIMNMX.U16x2 (the min/max unit is the busy pipe of this kernel: 1.5 operations per
+// accumulator instead of 3), and both halves of a register are produced by two IMADs on the FMA pipe, no packing:
+//      hamming * 128 + col = 16384 - 64 * D + col;   pk = D_even * -64 + C_even;   pk = D_odd * (-64 << 16) + pk
+// 0xffff marks "no candidate" (columns that do not exist in a ragged last tile).
+struct Top2x2
+{
+    unsigned k0 = 0xffffffffu, k1 = 0xffffffffu;
+    __device__ __forceinline__ void push(unsigned pk)
+    {
+        k1 = __vminu2(k1, __vmaxu2(k0, pk));
+        k0 = __vminu2(k0, pk);
+    }
+};
+__device__ __forceinline__ unsigned widen_key(unsigned k16, unsigned col_base)
+{
+    // 16-bit tile key -> (hamming << 16) | train index
+    return k16 == 0xffffu ? kNoKey : ((k16 >> 7) << 16) | (col_base + (k16 & 127u));
+}
+
+// 32 accumulators (columns col0 .. col0 + 31 of this warp's 128) -> 16 packed key pairs -> top-2 chains.
 template <bool MASKED>
-__device__ __forceinline__ void push32(Top2& t, const uint32_t (&v)[32], int col0, int n_valid)
+__device__ __forceinline__ void push32(Top2x2& t, const uint32_t (&v)[32], int col0, int n_valid)
 {
 #pragma unroll
-    for(int i = 0; i < 32; ++i)
+    for(int i = 0; i < 32; i += 2)
     {
-        // (256 - D) << 15 == hamming << 16 ; + local train index
-        unsigned key = (unsigned)((int)v[i] * -32768) + (0x800000u + (unsigned)(col0 + i));
+        const unsigned c = (16384u + (unsigned)(col0 + i)) | ((16384u + (unsigned)(col0 + i + 1)) << 16);
+        unsigned pk = v[i] * (unsigned)-64 + c;
+        pk = v[i + 1] * ((unsigned)-64 << 16) + pk;
         if(MASKED)
-            key = (col0 + i) < n_valid ? key : kNoKey;
-        if(i & 1)
-            t.push_b(key);
-        else
-            t.push_a(key);
+        {
+            pk |= (col0 + i) < n_valid ? 0u : 0x0000ffffu;
+            pk |= (col0 + i + 1) < n_valid ? 0u : 0xffff0000u;
+        }
+        t.push(pk);
     }
 }
 
-// One accumulator stage, this warp's half of the columns (128 columns = 4 loads of 32), double-buffered in registers.
+// One 128-column accumulator (4 loads of 32 columns), double-buffered in registers.
 template <bool MASKED>
-__device__ __forceinline__ void drain_half(Top2& t, uint32_t taddr, int col_begin, int n_valid)
+__device__ __forceinline__ void drain_half(Top2x2& t, uint32_t taddr, int n_valid)
 {
     uint32_t va[32], vb[32];
-    tmem_ld32(taddr + col_begin, va);
+    tmem_ld32(taddr, va);
     tmem_wait(va);
-    tmem_ld32(taddr + col_begin + 32, vb);
-    push32<MASKED>(t, va, col_begin, n_valid);
+    tmem_ld32(taddr + 32, vb);
+    push32<MASKED>(t, va, 0, n_valid);
     tmem_wait(vb);
-    tmem_ld32(taddr + col_begin + 64, va);
-    push32<MASKED>(t, vb, col_begin + 32, n_valid);
+    tmem_ld32(taddr + 64, va);
+    push32<MASKED>(t, vb, 32, n_valid);
     tmem_wait(va);
-    tmem_ld32(taddr + col_begin + 96, vb);
-    push32<MASKED>(t, va, col_begin + 64, n_valid);
+    tmem_ld32(taddr + 96, vb);
+    push32<MASKED>(t, va, 64, n_valid);
     tmem_wait(vb);
-    push32<MASKED>(t, vb, col_begin + 96, n_valid);
+    push32<MASKED>(t, vb, 96, n_valid);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -198,17 +208,23 @@ __device__ __forceinline__ void drain_half(Top2& t, uint32_t taddr, int col_begi
 // One thread = one 16-byte K chunk of one descriptor (16 descriptor bits).  Rows >= the set's count are left as they
 // are: they only ever reach accumulator rows that are not stored / columns that the epilogue masks.
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_expand_pm1(const uint8_t* __restrict__ desc, const int* __restrict__ counts, int cap,
-                                                    int cap_pad, uint8_t* __restrict__ out)
+struct ExpandSet
 {
+    const uint8_t* desc;
+    const int* counts;
+    uint8_t* out;
+};
+__global__ void __launch_bounds__(256) k_expand_pm1(ExpandSet s0, ExpandSet s1, int cap, int cap_pad)
+{
+    const ExpandSet s = blockIdx.z ? s1 : s0;
     const int p = blockIdx.y;
-    const int n = min(counts[p], cap);
-    const int gid = blockIdx.x * 256 + threadIdx.x; // (row, chunk): chunk fastest within a row's 16 chunks
-    const int row = gid >> 4, chunk = gid & 15;
+    const int n = min(s.counts[p], cap);
+    // (row % 8) fastest, then the K chunk, then the 8-row group: 8 consecutive lanes write one 128-byte core matrix
+    const int gid = blockIdx.x * 256 + threadIdx.x;
+    const int row = ((gid >> 7) << 3) | (gid & 7), chunk = (gid >> 3) & 15;
     if(row >= n)
         return;
-    const unsigned bits = reinterpret_cast<const unsigned short*>(desc + ((size_t)p * cap + row) * 32)[chunk];
-    uint4 o;
+    const unsigned bits = reinterpret_cast<const unsigned short*>(s.desc + ((size_t)p * cap + row) * 32)[chunk];
     unsigned w[4];
 #pragma unroll
     for(int i = 0; i < 4; ++i)
@@ -217,33 +233,47 @@ __global__ void __launch_bounds__(256) k_expand_pm1(const uint8_t* __restrict__ 
         const unsigned spread = (nib * 0x00204081u) & 0x01010101u; // bit b of the nibble -> byte b, value 0 / 1
         w[i] = ~(spread * 0xfeu);                                  // 1 -> 0x01 (+1), 0 -> 0xff (-1)
     }
-    o = make_uint4(w[0], w[1], w[2], w[3]);
-    uint8_t* dst = out + (size_t)p * cap_pad * ROW_BYTES + (size_t)(row >> 3) * 2048 + chunk * 128 + (row & 7) * 16;
-    *reinterpret_cast<uint4*>(dst) = o;
+    uint8_t* dst = s.out + (size_t)p * cap_pad * ROW_BYTES + (size_t)gid * 16;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// the kNN kernel.  grid = (ceil(cap / 128), n_pairs); 320 threads; one CTA per SM (all 512 TMEM columns).
+// the kNN kernel.  grid = (ceil(cap / 256), n_pairs); 320 threads; one CTA per SM (all 512 TMEM columns).
 // ---------------------------------------------------------------------------------------------------------------
+// DB = false: kNN of pair p = blockIdx.y (rows: set q of the pair, columns: set t of the pair) -> key0 / key1.
+// DB = true : keyframe-database scoring (k_db_scores of match_kernels.cu on the tensor cores): rows = descriptors of
+//             keyframe blockIdx.y (set q, capacity cap), columns = descriptors of query frame blockIdx.z (set t, capacity
+//             t_cap); a row counts when its two smallest distances pass the ratio test; the CTA adds its count to
+//             scores[query frame][keyframe] (zeroed by the launcher; integer adds commute, so the result is exact).
+struct DbArgs
+{
+    int t_cap, t_cap_pad, n_keyframes, int_ratio;
+    double ratio;
+    int* scores;
+};
+template <bool DB>
 __global__ void __launch_bounds__(MMA_THREADS, 1)
     k_knn2_mma(const uint8_t* __restrict__ xq, const int* __restrict__ q_counts, const uint8_t* __restrict__ xt,
-               const int* __restrict__ t_counts, int cap, int cap_pad, unsigned* __restrict__ key0, unsigned* __restrict__ key1)
+               const int* __restrict__ t_counts, int cap, int cap_pad, unsigned* __restrict__ key0, unsigned* __restrict__ key1,
+               DbArgs db)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    const int p = blockIdx.y;
-    const int nq = min(q_counts[p], cap), nt = min(t_counts[p], cap);
-    const int q0 = blockIdx.x * MMA_M;
-    if(q0 >= nq)
+    const int p = blockIdx.y;                 // row set
+    const int pt = DB ? blockIdx.z : p;       // column set
+    const int nq = min(q_counts[p], cap), nt = DB ? min(t_counts[pt], db.t_cap) : min(t_counts[pt], cap);
+    const int q0 = blockIdx.x * CTA_ROWS;
+    if(q0 >= nq || (DB && nt < 2))
         return; // whole CTA, before any barrier or allocation
+    const int t_pad = DB ? db.t_cap_pad : cap_pad;
     const int n_tiles = (nt + MMA_N - 1) / MMA_N;
+    const int n_row_tiles = nq - q0 > MMA_M ? 2 : 1; // the second query tile may be empty
     uint8_t* sA = smem;
     uint8_t* sB = smem + A_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_BYTES + STAGES * B_BYTES);
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 16);
-    __shared__ unsigned s_part[2][MMA_M];
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 24);
     const uint32_t bar_a = smem_u32(bars + 0);
-    const uint32_t bar_bfull = smem_u32(bars + 1), bar_bempty = smem_u32(bars + 3);   // [STAGES] each
-    const uint32_t bar_cfull = smem_u32(bars + 5), bar_cempty = smem_u32(bars + 7);   // accumulator stages
+    const uint32_t bar_bfull = smem_u32(bars + 1), bar_bempty = smem_u32(bars + 1 + STAGES);          // [STAGES] each
+    const uint32_t bar_cfull = smem_u32(bars + 1 + 2 * STAGES), bar_cempty = bar_cfull + 8 * ACC_STAGES; // [ACC_STAGES] each
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if(threadIdx.x == 0)
     {
@@ -252,6 +282,9 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
         {
             mbar_init(bar_bfull + 8 * s, 1);
             mbar_init(bar_bempty + 8 * s, 1);
+        }
+        for(int s = 0; s < ACC_STAGES; ++s)
+        {
             mbar_init(bar_cfull + 8 * s, 1);
             mbar_init(bar_cempty + 8 * s, 8); // one arrival per epilogue warp
         }
@@ -272,17 +305,18 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     {
         if(lane == 0)
         {
-            // ---- producer: query tile once, then the train tiles through the ring ----
+            // ---- producer: query tiles once, then the train tiles through the ring ----
             const uint8_t* a_src = xq + ((size_t)p * cap_pad + q0) * ROW_BYTES;
-            mbar_expect_tx(bar_a, A_BYTES);
-            for(int o = 0; o < A_BYTES; o += BULK)
+            const int a_bytes = n_row_tiles * MMA_M * ROW_BYTES;
+            mbar_expect_tx(bar_a, a_bytes);
+            for(int o = 0; o < a_bytes; o += BULK)
                 bulk_g2s(smem_u32(sA + o), a_src + o, BULK, bar_a);
             for(int it = 0; it < n_tiles; ++it)
             {
                 const int s = it % STAGES;
                 mbar_wait(bar_bempty + 8 * s, ((it / STAGES) & 1) ^ 1);
                 mbar_expect_tx(bar_bfull + 8 * s, B_BYTES);
-                const uint8_t* b_src = xt + ((size_t)p * cap_pad + (size_t)it * MMA_N) * ROW_BYTES;
+                const uint8_t* b_src = xt + ((size_t)pt * t_pad + (size_t)it * MMA_N) * ROW_BYTES;
                 for(int o = 0; o < B_BYTES; o += BULK)
                     bulk_g2s(smem_u32(sB + s * B_BYTES + o), b_src + o, BULK, bar_bfull + 8 * s);
             }
@@ -297,65 +331,70 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
             const uint32_t a_addr = smem_u32(sA);
             for(int it = 0; it < n_tiles; ++it)
             {
-                const int s = it % STAGES;
-                const uint32_t ph = (it / STAGES) & 1;
-                mbar_wait(bar_bfull + 8 * s, ph);
-                mbar_wait(bar_cempty + 8 * s, ph ^ 1);
+                const int s = it % STAGES, as = it % ACC_STAGES;
+                mbar_wait(bar_bfull + 8 * s, (it / STAGES) & 1);
+                mbar_wait(bar_cempty + 8 * as, ((it / ACC_STAGES) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t b_addr = smem_u32(sB + s * B_BYTES);
+                for(int a = 0; a < n_row_tiles; ++a)
+                {
 #pragma unroll
-                for(int k = 0; k < ROW_BYTES / 32; ++k)
-                    umma_i8(tmem + s * MMA_N, smem_desc(a_addr + k * 256), smem_desc(b_addr + k * 256), k > 0);
+                    for(int k = 0; k < ROW_BYTES / 32; ++k)
+                        umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
+                                smem_desc(b_addr + k * 256), k > 0);
+                }
                 umma_commit(bar_bempty + 8 * s); // the train tile may be overwritten once these MMAs have read it
-                umma_commit(bar_cfull + 8 * s);  // ... and the accumulator stage is complete
+                umma_commit(bar_cfull + 8 * as); // ... and the accumulator stage is complete
             }
         }
     }
     else
     {
-        // ---- epilogue: warp w owns TMEM lanes 32 * (w % 4) ..; the two warps of a quarter split the columns ----
-        const int quarter = warp & 3, half = (warp - 2) >> 2;
-        const int row = quarter * 32 + lane;
+        // ---- epilogue: warp w owns TMEM lanes 32 * (w % 4) .. of query tile a = (w - 2) / 4 ----
+        const int quarter = warp & 3, a = (warp - 2) >> 2;
+        const int row = a * MMA_M + quarter * 32 + lane;
+        const bool active = a < n_row_tiles;
         unsigned k0 = kNoKey, k1 = kNoKey;
         for(int it = 0; it < n_tiles; ++it)
         {
-            const int s = it % STAGES;
-            mbar_wait(bar_cfull + 8 * s, (it / STAGES) & 1);
+            const int as = it % ACC_STAGES;
+            mbar_wait(bar_cfull + 8 * as, (it / ACC_STAGES) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + s * MMA_N;
-            const int n_valid = nt - it * MMA_N; // >= 1
-            Top2 t;
-            if(n_valid >= MMA_N)
-                drain_half<false>(t, taddr, half * 128, n_valid);
-            else
-                drain_half<true>(t, taddr, half * 128, n_valid);
+            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (as * 2 + a) * MMA_N;
+            const int col_base = it * MMA_N;
+            const int n_valid = nt - col_base; // >= 1
+            Top2x2 t;
+            if(active)
+            {
+                if(n_valid >= MMA_N)
+                    drain_half<false>(t, taddr, n_valid);
+                else
+                    drain_half<true>(t, taddr, n_valid);
+            }
             tc_fence_before();
             __syncwarp();
             if(lane == 0)
-                mbar_arrive(bar_cempty + 8 * s);
-            unsigned t0 = t.a0, t1 = t.a1;
-            merge2(t0, t1, t.b0, t.b1);
-            const unsigned base = (unsigned)(it * MMA_N);
-            t0 = t0 == kNoKey ? t0 : t0 + base;
-            t1 = t1 == kNoKey ? t1 : t1 + base;
+                mbar_arrive(bar_cempty + 8 * as);
+            unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
+            merge2(t0, t1, widen_key(t.k0 >> 16, col_base), widen_key(t.k1 >> 16, col_base));
             merge2(k0, k1, t0, t1);
         }
-        // the upper-half warp hands its pair to the lower-half warp of the same lane quarter
-        if(half == 1)
+        const int q = q0 + row;
+        if(!DB)
         {
-            s_part[0][row] = k0;
-            s_part[1][row] = k1;
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory"); // the eight epilogue warps only
-        if(half == 0)
-        {
-            merge2(k0, k1, s_part[0][row], s_part[1][row]);
-            const int q = q0 + row;
-            if(q < nq)
+            if(active && q < nq)
             {
                 key0[(long long)p * cap + q] = k0;
                 key1[(long long)p * cap + q] = k1;
             }
+        }
+        else
+        {
+            const int d0 = (int)(k0 >> 16), d1 = (int)(k1 >> 16); // nt >= 2: both exist
+            const bool pass = db.int_ratio ? (10 * d0 < 7 * d1) : ((double)(float)d0 < db.ratio * (double)(float)d1);
+            const int cnt = __reduce_add_sync(0xffffffffu, (active && q < nq && pass) ? 1 : 0);
+            if(lane == 0 && cnt)
+                atomicAdd(db.scores + (long long)pt * db.n_keyframes + p, cnt);
         }
     }
     tc_fence_before();
@@ -370,7 +409,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
 
 int knn_mma_pad(int cap)
 {
-    return (cap + MMA_N - 1) / MMA_N * MMA_N;
+    return (cap + PAD_ROWS - 1) / PAD_ROWS * PAD_ROWS;
 }
 size_t knn_mma_bytes(int n_pairs, int cap)
 {
@@ -379,8 +418,16 @@ size_t knn_mma_bytes(int n_pairs, int cap)
 void launch_expand_pm1(cudaStream_t st, const uint8_t* desc, const int* counts, int n_pairs, int cap, uint8_t* out,
                        long long* launches)
 {
-    dim3 grd((cap * 16 + 255) / 256, n_pairs);
-    k_expand_pm1<<<grd, 256, 0, st>>>(desc, counts, cap, knn_mma_pad(cap), out);
+    const ExpandSet s{desc, counts, out};
+    dim3 grd(((cap + 7) / 8 * 128 + 255) / 256, n_pairs, 1);
+    k_expand_pm1<<<grd, 256, 0, st>>>(s, s, cap, knn_mma_pad(cap));
+    ++*launches;
+}
+void launch_expand_pm1_x2(cudaStream_t st, const uint8_t* desc0, const int* counts0, uint8_t* out0, const uint8_t* desc1,
+                          const int* counts1, uint8_t* out1, int n_pairs, int cap, long long* launches)
+{
+    dim3 grd(((cap + 7) / 8 * 128 + 255) / 256, n_pairs, 2);
+    k_expand_pm1<<<grd, 256, 0, st>>>(ExpandSet{desc0, counts0, out0}, ExpandSet{desc1, counts1, out1}, cap, knn_mma_pad(cap));
     ++*launches;
 }
 cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, const uint8_t* xt, const int* tn, int n_pairs,
@@ -389,14 +436,44 @@ cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, c
     static bool configured = false;
     if(!configured)
     {
-        cudaError_t e = cudaFuncSetAttribute(k_knn2_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         if(e != cudaSuccess)
             return e;
         configured = true;
     }
-    dim3 grd((cap + MMA_M - 1) / MMA_M, n_pairs);
-    k_knn2_mma<<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1);
+    dim3 grd((cap + CTA_ROWS - 1) / CTA_ROWS, n_pairs);
+    k_knn2_mma<false><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, DbArgs{});
     ++*launches;
     return cudaSuccess;
+}
+// xdb: expanded descriptors of keyframes [0, n_keyframes) of this call [n_keyframes][pad(k_cap)], xqueries: expanded query
+// frames [nq_frames][pad(q_cap)].  Adds into scores[q * score_stride + kf] -- the caller zeroes the score matrix.
+cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const int* q_counts, int nq_frames, int q_cap,
+                                 const uint8_t* xdb, const int* k_counts, int n_keyframes, int k_cap, double ratio, int* scores,
+                                 int score_stride, long long* launches)
+{
+    static bool configured = false;
+    if(!configured)
+    {
+        cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        if(e != cudaSuccess)
+            return e;
+        configured = true;
+    }
+    DbArgs db;
+    db.t_cap = q_cap, db.t_cap_pad = knn_mma_pad(q_cap), db.n_keyframes = score_stride, db.int_ratio = ratio == 0.7;
+    db.ratio = ratio, db.scores = scores;
+    // grid.y = keyframes (<= 65535 per launch), grid.z = query frames
+    for(int kf0 = 0; kf0 < n_keyframes; kf0 += 65535)
+    {
+        const int nk = n_keyframes - kf0 < 65535 ? n_keyframes - kf0 : 65535;
+        DbArgs d = db;
+        d.scores = scores + kf0;
+        dim3 grd((k_cap + CTA_ROWS - 1) / CTA_ROWS, nk, nq_frames);
+        k_knn2_mma<true><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
+                                                               xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
+        ++*launches;
+    }
+    return cudaGetLastError();
 }
 } // namespace mslam_b200

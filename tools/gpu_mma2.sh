@@ -1,7 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
 for m in 0 1; do
-  for wl in dist c5; do
+  for wl in c2 dist c5; do
     MSLAM_KNN_MMA=$m timeout 300 python bench.py --workload $wl --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_${wl}_mma$m.json 2> gpurun_out/bench_${wl}_mma$m.err
     python - <<PY
 import json
