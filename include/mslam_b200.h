@@ -77,6 +77,11 @@ typedef struct mslam_b200_config
 /* run every kernel of detect on the one context stream (default: the pyramid chain, FAST + selection and the blur run on
  * three forked streams that join before the describe kernel, so that small levels and latency-bound stages overlap) */
 #define MSLAM_B200_FLAG_SERIAL 1
+/* kNN / keyframe-DB scoring kernel choice.  Default: by problem size -- the tensor-core kernel (Hamming distances as an
+ * int8 GEMM on tcgen05, knn_mma.cu) for large problems, the scalar XOR + POPC kernel for small ones.  Both give the same
+ * bits; the flags force one of them (tests, A/B measurements).  Environment MSLAM_KNN_MMA=0|1|2 does the same at create. */
+#define MSLAM_B200_FLAG_KNN_SCALAR 2
+#define MSLAM_B200_FLAG_KNN_TENSOR 4
 
 /* what cv::KeyPoint carries out of detectAndCompute (the reference interface keeps only pt, orb_feature.cpp:52-58) */
 typedef struct mslam_b200_keypoint

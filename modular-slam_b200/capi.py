@@ -27,6 +27,8 @@ class Config(C.Structure):
 
 
 FLAG_SERIAL = 1
+FLAG_KNN_SCALAR = 2
+FLAG_KNN_TENSOR = 4
 
 
 class Camera(C.Structure):

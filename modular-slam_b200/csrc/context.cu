@@ -589,6 +589,10 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaMalloc(&ctx->d_part1, kKnnMaxSlices * B * dc * sizeof(unsigned)));
     if(const char* e = getenv("MSLAM_KNN_MMA"))
         ctx->knn_mma = atoi(e);
+    if(ctx->cfg.flags & MSLAM_B200_FLAG_KNN_SCALAR)
+        ctx->knn_mma = 0;
+    if(ctx->cfg.flags & MSLAM_B200_FLAG_KNN_TENSOR)
+        ctx->knn_mma = 2;
     if(ctx->knn_mma)
     {
         CREATE_OK(cudaMalloc(&ctx->d_xa, knn_mma_bytes((int)B, (int)dc)));
