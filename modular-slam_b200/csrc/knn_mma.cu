@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(256) k_expand_pm1(ExpandSet s0, ExpandSet s1, 
 // ---------------------------------------------------------------------------------------------------------------
 // DB = false: kNN of pair p = blockIdx.y (rows: set q of the pair, columns: set t of the pair) -> key0 / key1.
 // DB = true : keyframe-database scoring (k_db_scores of match_kernels.cu on the tensor cores): rows = descriptors of
-//             keyframe blockIdx.y (set q, capacity cap), columns = descriptors of query frame blockIdx.z (set t, capacity
+//             keyframe blockIdx.z (set q, capacity cap), columns = descriptors of query frame blockIdx.y (set t, capacity
 //             t_cap); a row counts when its two smallest distances pass the ratio test; the CTA adds its count to
 //             scores[query frame][keyframe] (zeroed by the launcher; integer adds commute, so the result is exact).
 struct DbArgs
@@ -258,8 +258,10 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                DbArgs db)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    const int p = blockIdx.y;                 // row set
-    const int pt = DB ? blockIdx.z : p;       // column set
+    // DB: the query frame is the faster grid dimension, so the CTAs that run together share one keyframe's rows (read from
+    // HBM once) while the query frames (a few MB) stay in L2
+    const int p = DB ? blockIdx.z : blockIdx.y; // row set
+    const int pt = DB ? blockIdx.y : p;         // column set
     const int nq = min(q_counts[p], cap), nt = DB ? min(t_counts[pt], db.t_cap) : min(t_counts[pt], cap);
     const int q0 = blockIdx.x * CTA_ROWS;
     if(q0 >= nq || (DB && nt < 2))
@@ -463,13 +465,13 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
     DbArgs db;
     db.t_cap = q_cap, db.t_cap_pad = knn_mma_pad(q_cap), db.n_keyframes = score_stride, db.int_ratio = ratio == 0.7;
     db.ratio = ratio, db.scores = scores;
-    // grid.y = keyframes (<= 65535 per launch), grid.z = query frames
+    // grid.y = query frames, grid.z = keyframes (<= 65535 per launch)
     for(int kf0 = 0; kf0 < n_keyframes; kf0 += 65535)
     {
         const int nk = n_keyframes - kf0 < 65535 ? n_keyframes - kf0 : 65535;
         DbArgs d = db;
         d.scores = scores + kf0;
-        dim3 grd((k_cap + CTA_ROWS - 1) / CTA_ROWS, nk, nq_frames);
+        dim3 grd((k_cap + CTA_ROWS - 1) / CTA_ROWS, nq_frames, nk);
         k_knn2_mma<true><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
                                                                xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
         ++*launches;
