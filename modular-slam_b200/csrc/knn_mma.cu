@@ -41,6 +41,7 @@ constexpr int ACC_STAGES = 2;                // accumulator stages in tensor mem
 constexpr int BULK = 16384;                  // bytes per cp.async.bulk
 constexpr int MMA_THREADS = 64 + 256;        // producer warp + MMA warp + 8 epilogue warps
 constexpr int TMEM_COLS = 512;
+constexpr int kDbGroup = 8;                   // query frames one DB-scoring CTA walks
 constexpr int PAD_ROWS = 256;                // rows of an expanded set are padded to a multiple of this
 constexpr int SMEM_BYTES = A_BYTES + STAGES * B_BYTES + 256;
 
@@ -248,6 +249,7 @@ __global__ void __launch_bounds__(256) k_expand_pm1(ExpandSet s0, ExpandSet s1, 
 struct DbArgs
 {
     int t_cap, t_cap_pad, n_keyframes, int_ratio;
+    int group, n_sets; // query frames per CTA, query frames in all
     double ratio;
     int* scores;
 };
@@ -260,14 +262,30 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     extern __shared__ __align__(128) uint8_t smem[];
     // DB: the query frame is the faster grid dimension, so the CTAs that run together share one keyframe's rows (read from
     // HBM once) while the query frames (a few MB) stay in L2
+    // ... and one CTA walks a group of db.group query frames against its resident keyframe rows: the pipeline (ring, tensor
+    // memory, barriers) is set up once per group instead of once per (keyframe, query frame)
     const int p = DB ? blockIdx.z : blockIdx.y; // row set
-    const int pt = DB ? blockIdx.y : p;         // column set
-    const int nq = min(q_counts[p], cap), nt = DB ? min(t_counts[pt], db.t_cap) : min(t_counts[pt], cap);
+    const int nq = min(q_counts[p], cap);
     const int q0 = blockIdx.x * CTA_ROWS;
-    if(q0 >= nq || (DB && nt < 2))
+    if(q0 >= nq)
         return; // whole CTA, before any barrier or allocation
-    const int t_pad = DB ? db.t_cap_pad : cap_pad;
-    const int n_tiles = (nt + MMA_N - 1) / MMA_N;
+    const int t_pad = DB ? db.t_cap_pad : cap_pad, t_cap = DB ? db.t_cap : cap;
+    const int pt_begin = DB ? blockIdx.y * db.group : p, pt_end = DB ? min(pt_begin + db.group, db.n_sets) : p + 1;
+    // the column sets of this CTA, in order; a set with fewer than 2 descriptors scores 0 in DB mode and is skipped.
+    // Every role walks the same sequence; `it` numbers the tiles of all sets consecutively (ring / accumulator phases).
+    auto for_each_tile = [&](auto&& set_begin, auto&& tile, auto&& set_end) {
+        for(int pt = pt_begin, it = 0; pt < pt_end; ++pt)
+        {
+            const int nt = min(t_counts[pt], t_cap);
+            if(DB && nt < 2)
+                continue;
+            const int n_tiles = (nt + MMA_N - 1) / MMA_N;
+            set_begin();
+            for(int j = 0; j < n_tiles; ++j, ++it)
+                tile(pt, nt, j, it);
+            set_end(pt);
+        }
+    };
     const int n_row_tiles = nq - q0 > MMA_M ? 2 : 1; // the second query tile may be empty
     uint8_t* sA = smem;
     uint8_t* sB = smem + A_BYTES;
@@ -313,15 +331,14 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
             mbar_expect_tx(bar_a, a_bytes);
             for(int o = 0; o < a_bytes; o += BULK)
                 bulk_g2s(smem_u32(sA + o), a_src + o, BULK, bar_a);
-            for(int it = 0; it < n_tiles; ++it)
-            {
-                const int s = it % STAGES;
-                mbar_wait(bar_bempty + 8 * s, ((it / STAGES) & 1) ^ 1);
-                mbar_expect_tx(bar_bfull + 8 * s, B_BYTES);
-                const uint8_t* b_src = xt + ((size_t)pt * t_pad + (size_t)it * MMA_N) * ROW_BYTES;
-                for(int o = 0; o < B_BYTES; o += BULK)
-                    bulk_g2s(smem_u32(sB + s * B_BYTES + o), b_src + o, BULK, bar_bfull + 8 * s);
-            }
+            for_each_tile([] {}, [&](int pt, int, int j, int it) {
+                    const int s = it % STAGES;
+                    mbar_wait(bar_bempty + 8 * s, ((it / STAGES) & 1) ^ 1);
+                    mbar_expect_tx(bar_bfull + 8 * s, B_BYTES);
+                    const uint8_t* b_src = xt + ((size_t)pt * t_pad + (size_t)j * MMA_N) * ROW_BYTES;
+                    for(int o = 0; o < B_BYTES; o += BULK)
+                        bulk_g2s(smem_u32(sB + s * B_BYTES + o), b_src + o, BULK, bar_bfull + 8 * s);
+                }, [](int) {});
         }
     }
     else if(warp == 1)
@@ -331,23 +348,22 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
             // ---- MMA issuer ----
             mbar_wait(bar_a, 0);
             const uint32_t a_addr = smem_u32(sA);
-            for(int it = 0; it < n_tiles; ++it)
-            {
-                const int s = it % STAGES, as = it % ACC_STAGES;
-                mbar_wait(bar_bfull + 8 * s, (it / STAGES) & 1);
-                mbar_wait(bar_cempty + 8 * as, ((it / ACC_STAGES) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t b_addr = smem_u32(sB + s * B_BYTES);
-                for(int a = 0; a < n_row_tiles; ++a)
-                {
+            for_each_tile([] {}, [&](int, int, int, int it) {
+                    const int s = it % STAGES, as = it % ACC_STAGES;
+                    mbar_wait(bar_bfull + 8 * s, (it / STAGES) & 1);
+                    mbar_wait(bar_cempty + 8 * as, ((it / ACC_STAGES) & 1) ^ 1);
+                    tc_fence_after();
+                    const uint32_t b_addr = smem_u32(sB + s * B_BYTES);
+                    for(int a = 0; a < n_row_tiles; ++a)
+                    {
 #pragma unroll
-                    for(int k = 0; k < ROW_BYTES / 32; ++k)
-                        umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
-                                smem_desc(b_addr + k * 256), k > 0);
-                }
-                umma_commit(bar_bempty + 8 * s); // the train tile may be overwritten once these MMAs have read it
-                umma_commit(bar_cfull + 8 * as); // ... and the accumulator stage is complete
-            }
+                        for(int k = 0; k < ROW_BYTES / 32; ++k)
+                            umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
+                                    smem_desc(b_addr + k * 256), k > 0);
+                    }
+                    umma_commit(bar_bempty + 8 * s); // the train tile may be overwritten once these MMAs have read it
+                    umma_commit(bar_cfull + 8 * as); // ... and the accumulator stage is complete
+                }, [](int) {});
         }
     }
     else
@@ -356,48 +372,51 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
         const int quarter = warp & 3, a = (warp - 2) >> 2;
         const int row = a * MMA_M + quarter * 32 + lane;
         const bool active = a < n_row_tiles;
-        unsigned k0 = kNoKey, k1 = kNoKey;
-        for(int it = 0; it < n_tiles; ++it)
-        {
-            const int as = it % ACC_STAGES;
-            mbar_wait(bar_cfull + 8 * as, (it / ACC_STAGES) & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (as * 2 + a) * MMA_N;
-            const int col_base = it * MMA_N;
-            const int n_valid = nt - col_base; // >= 1
-            Top2x2 t;
-            if(active)
-            {
-                if(n_valid >= MMA_N)
-                    drain_half<false>(t, taddr, n_valid);
-                else
-                    drain_half<true>(t, taddr, n_valid);
-            }
-            tc_fence_before();
-            __syncwarp();
-            if(lane == 0)
-                mbar_arrive(bar_cempty + 8 * as);
-            unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
-            merge2(t0, t1, widen_key(t.k0 >> 16, col_base), widen_key(t.k1 >> 16, col_base));
-            merge2(k0, k1, t0, t1);
-        }
         const int q = q0 + row;
-        if(!DB)
-        {
-            if(active && q < nq)
-            {
-                key0[(long long)p * cap + q] = k0;
-                key1[(long long)p * cap + q] = k1;
-            }
-        }
-        else
-        {
-            const int d0 = (int)(k0 >> 16), d1 = (int)(k1 >> 16); // nt >= 2: both exist
-            const bool pass = db.int_ratio ? (10 * d0 < 7 * d1) : ((double)(float)d0 < db.ratio * (double)(float)d1);
-            const int cnt = __reduce_add_sync(0xffffffffu, (active && q < nq && pass) ? 1 : 0);
-            if(lane == 0 && cnt)
-                atomicAdd(db.scores + (long long)pt * db.n_keyframes + p, cnt);
-        }
+        unsigned k0 = kNoKey, k1 = kNoKey;
+        for_each_tile(
+            [&] { k0 = kNoKey, k1 = kNoKey; },
+            [&](int, int nt, int j, int it) {
+                const int as = it % ACC_STAGES;
+                mbar_wait(bar_cfull + 8 * as, (it / ACC_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (as * 2 + a) * MMA_N;
+                const int col_base = j * MMA_N;
+                const int n_valid = nt - col_base; // >= 1
+                Top2x2 t;
+                if(active)
+                {
+                    if(n_valid >= MMA_N)
+                        drain_half<false>(t, taddr, n_valid);
+                    else
+                        drain_half<true>(t, taddr, n_valid);
+                }
+                tc_fence_before();
+                __syncwarp();
+                if(lane == 0)
+                    mbar_arrive(bar_cempty + 8 * as);
+                unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
+                merge2(t0, t1, widen_key(t.k0 >> 16, col_base), widen_key(t.k1 >> 16, col_base));
+                merge2(k0, k1, t0, t1);
+            },
+            [&](int pt) {
+                if(!DB)
+                {
+                    if(active && q < nq)
+                    {
+                        key0[(long long)p * cap + q] = k0;
+                        key1[(long long)p * cap + q] = k1;
+                    }
+                }
+                else
+                {
+                    const int d0 = (int)(k0 >> 16), d1 = (int)(k1 >> 16); // nt >= 2: both exist
+                    const bool pass = db.int_ratio ? (10 * d0 < 7 * d1) : ((double)(float)d0 < db.ratio * (double)(float)d1);
+                    const int cnt = __reduce_add_sync(0xffffffffu, (active && q < nq && pass) ? 1 : 0);
+                    if(lane == 0 && cnt)
+                        atomicAdd(db.scores + (long long)pt * db.n_keyframes + p, cnt);
+                }
+            });
     }
     tc_fence_before();
     __syncthreads();
@@ -465,13 +484,14 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
     DbArgs db;
     db.t_cap = q_cap, db.t_cap_pad = knn_mma_pad(q_cap), db.n_keyframes = score_stride, db.int_ratio = ratio == 0.7;
     db.ratio = ratio, db.scores = scores;
+    db.group = kDbGroup, db.n_sets = nq_frames;
     // grid.y = query frames, grid.z = keyframes (<= 65535 per launch)
     for(int kf0 = 0; kf0 < n_keyframes; kf0 += 65535)
     {
         const int nk = n_keyframes - kf0 < 65535 ? n_keyframes - kf0 : 65535;
         DbArgs d = db;
         d.scores = scores + kf0;
-        dim3 grd((k_cap + CTA_ROWS - 1) / CTA_ROWS, nq_frames, nk);
+        dim3 grd((k_cap + CTA_ROWS - 1) / CTA_ROWS, (nq_frames + kDbGroup - 1) / kDbGroup, nk);
         k_knn2_mma<true><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
                                                                xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
         ++*launches;
