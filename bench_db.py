@@ -264,7 +264,7 @@ def main(args, rank, world, local):
                          "GPU scores of the same sample checked equal"}
     line = {"metric": "DB Hamming descriptor-pair evaluations/sec", "value": value, "unit": "descriptor pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u32 (xor/popc)", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": ("s8 (+1/-1 int8 GEMM, int32 accumulate; exact)" if tensor_path else "u32 (xor/popc)"), "data": "synthetic",
             "config": {"workload": "configs[4]: loop-candidate verification, query frames x sharded keyframe-descriptor DB, kNN(2) + "
                                    "ratio 0.7 match count per (query frame, keyframe), per-query top-k, NCCL all-gather + merge",
                        "keyframes_per_gpu": kf_local, "keyframes_total": kf_local * world, "descriptors_per_frame": n,
