@@ -478,6 +478,9 @@ def main():
                        "keypoints_per_batch_check": n_kp_check, "matches_per_batch_check": n_matches_check},
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps,
+                    "h2d_gbs": h2d * args.steps / (e2e_ms * 1e-3) / 1e9,
+                    "pcie_note": "host->device GB/s this rate moves; a raw pinned copy of one batch measures 47-55 GB/s on these "
+                                 "boxes (tools/h2d_probe.py), so the pipelined e2e figure is bounded by PCIe, not by the kernels",
                     "mode": "pipelined host entry points (detect_batch_begin/_end, two batches in flight; pinned host buffers; "
                             "every step's frames cross PCIe and its keypoints / descriptors / matches come back inside the timed region)",
                     "synchronous": {"value": e2e_sync_value, "ms_per_step": e2e_sync_ms / args.steps,

@@ -147,8 +147,7 @@ __device__ __forceinline__ void merge2(unsigned& k0, unsigned& k1, unsigned o0, 
 
 // Running top-2 of one row over the 128 columns of a tile, two columns per register.
 // Inside a tile a key fits 16 bits: hamming (0..256) * 128 + column (0..127) <= 32895, so the even and the odd
-// columns run as the two halves of VIMNMX.U16x2 (the min/max unit is the busy pipe of this kernel: 1.5 operations per
-// accumulator instead of 3), and both halves of a register are produced by two IMADs on the FMA pipe, no packing:
+// columns run as the two halves of VIMNMX.U16x2 (1.5 ALU-pipe operations per accumulator instead of 3), and both halves of a register are produced by two IMADs on the FMA pipe, no packing:
 //      hamming * 128 + col = 16384 - 64 * D + col;   pk = D_even * -64 + C_even;   pk = D_odd * (-64 << 16) + pk
 // 0xffff marks "no candidate" (columns that do not exist in a ragged last tile).
 struct Top2x2
@@ -166,7 +165,7 @@ __device__ __forceinline__ unsigned widen_key(unsigned k16, unsigned col_base)
     return k16 == 0xffffu ? kNoKey : ((k16 >> 7) << 16) | (col_base + (k16 & 127u));
 }
 
-// 32 accumulators (columns col0 .. col0 + 31 of this warp's 128) -> 16 packed key pairs -> top-2 chains.
+// 32 accumulators (columns col0 .. col0 + 31 of the tile) -> 16 packed key pairs -> top-2 chains.
 template <bool MASKED>
 __device__ __forceinline__ void push32(Top2x2& t, const uint32_t (&v)[32], int col0, int n_valid)
 {
@@ -187,7 +186,7 @@ __device__ __forceinline__ void push32(Top2x2& t, const uint32_t (&v)[32], int c
 
 // One 128-column accumulator (4 loads of 32 columns), double-buffered in registers.
 template <bool MASKED>
-__device__ __forceinline__ void drain_half(Top2x2& t, uint32_t taddr, int n_valid)
+__device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_valid)
 {
     uint32_t va[32], vb[32];
     tmem_ld32(taddr, va);
@@ -387,9 +386,9 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                 if(active)
                 {
                     if(n_valid >= MMA_N)
-                        drain_half<false>(t, taddr, n_valid);
+                        drain_tile<false>(t, taddr, n_valid);
                     else
-                        drain_half<true>(t, taddr, n_valid);
+                        drain_tile<true>(t, taddr, n_valid);
                 }
                 tc_fence_before();
                 __syncwarp();
