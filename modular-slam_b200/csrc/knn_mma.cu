@@ -16,13 +16,14 @@
 // completion on mbarriers -- three tiles in flight per SM cover the L2 latency), each train tile feeds 2 x 8 MMAs
 // (M128 N128 K32), accumulators are double-buffered in tensor memory (2 stages x 2 query tiles x 128 columns = all 512),
 // and eight epilogue warps read them back with tcgen05.ld (one query row per lane) and keep the running top-2 in
-// registers.  Roles: warp 0 lane 0 = bulk-copy producer, warp 1 lane 0 = MMA issuer, warps 2..9 = epilogue (warp w reads
-// TMEM lanes 32 * (w % 4) .. + 31 of query tile (w - 2) / 4).
+// registers.  Roles: warps 0..7 = epilogue (warp w reads TMEM lanes 32 * (w % 4) .. + 31 of query tile w / 4), warp 8
+// lane 0 = bulk-copy producer, warp 9 lane 0 = MMA issuer.
 //
 // Shared-memory operand layout (and, so that a tile is one contiguous range, the layout of the expanded copy in
 // HBM): the no-swizzle K-major canonical layout -- core matrices of 8 rows x 16 bytes stored as 128 contiguous
 // bytes;  [row / 8][k_byte / 16][row % 8][k_byte % 16]  =>  K-direction core-matrix stride (LBO) 128 B, 8-row group
 // stride (SBO) 2048 B, and a K step of 32 bytes advances the descriptor start address by 256 B.
+#include <cstdio>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -39,7 +40,11 @@ constexpr int B_BYTES = MMA_N * ROW_BYTES;   // 32 KB
 constexpr int STAGES = 4;                    // train-tile ring
 constexpr int ACC_STAGES = 2;                // accumulator stages in tensor memory
 constexpr int BULK = 16384;                  // bytes per cp.async.bulk
-constexpr int MMA_THREADS = 64 + 256;        // producer warp + MMA warp + 8 epilogue warps
+constexpr int MMA_THREADS = 256 + 64;        // 8 epilogue warps + producer warp + MMA warp
+// The SMSP arbiter prefers the highest warp id among eligible warps: the two single-thread roles sit above the epilogue
+// warps so that an MMA or a bulk copy is issued the moment its barrier opens, not when the ALU-bound epilogue warps of
+// that SMSP happen to stall
+constexpr int kProducerWarp = 8, kMmaWarp = 9;
 constexpr int TMEM_COLS = 512;
 constexpr int kDbGroup = 8;                   // query frames one DB-scoring CTA walks
 constexpr int PAD_ROWS = 256;                // rows of an expanded set are padded to a multiple of this
@@ -245,10 +250,14 @@ __global__ void __launch_bounds__(256) k_expand_pm1(ExpandSet s0, ExpandSet s1, 
 //             keyframe blockIdx.z (set q, capacity cap), columns = descriptors of query frame blockIdx.y (set t, capacity
 //             t_cap); a row counts when its two smallest distances pass the ratio test; the CTA adds its count to
 //             scores[query frame][keyframe] (zeroed by the launcher; integer adds commute, so the result is exact).
+__device__ unsigned long long g_mma_clk[2]; // MSLAM_MMA_DEBUG & 32: sum of SM cycles / of nanoseconds over sampled CTAs
+
 struct DbArgs
 {
     int t_cap, t_cap_pad, n_keyframes, int_ratio;
     int group, n_sets; // query frames per CTA, query frames in all
+    int debug;         // timing experiments only (MSLAM_MMA_DEBUG; results are wrong): 1 = one K step per tile, 2 = epilogue
+                       // loads tensor memory but does not process, 4 = epilogue does not load at all
     double ratio;
     int* scores;
 };
@@ -268,6 +277,13 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     const int q0 = blockIdx.x * CTA_ROWS;
     if(q0 >= nq)
         return; // whole CTA, before any barrier or allocation
+    long long clk0 = 0;
+    unsigned long long ns0 = 0;
+    if((db.debug & 32) && threadIdx.x == 0)
+    {
+        clk0 = clock64();
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns0));
+    }
     const int t_pad = DB ? db.t_cap_pad : cap_pad, t_cap = DB ? db.t_cap : cap;
     const int pt_begin = DB ? blockIdx.y * db.group : p, pt_end = DB ? min(pt_begin + db.group, db.n_sets) : p + 1;
     // the column sets of this CTA, in order; a set with fewer than 2 descriptors scores 0 in DB mode and is skipped.
@@ -320,7 +336,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     tc_fence_after();
     const uint32_t tmem = *s_tmem;
 
-    if(warp == 0)
+    if(warp == kProducerWarp)
     {
         if(lane == 0)
         {
@@ -340,7 +356,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                 }, [](int) {});
         }
     }
-    else if(warp == 1)
+    else if(warp == kMmaWarp)
     {
         if(lane == 0)
         {
@@ -353,11 +369,12 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                     mbar_wait(bar_cempty + 8 * as, ((it / ACC_STAGES) & 1) ^ 1);
                     tc_fence_after();
                     const uint32_t b_addr = smem_u32(sB + s * B_BYTES);
-                    for(int a = 0; a < n_row_tiles; ++a)
+                    for(int a = 0; a < ((db.debug & 16) ? 1 : n_row_tiles); ++a)
                     {
 #pragma unroll
                         for(int k = 0; k < ROW_BYTES / 32; ++k)
-                            umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
+                            if(k == 0 || !(db.debug & 1))
+                                umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
                                     smem_desc(b_addr + k * 256), k > 0);
                     }
                     umma_commit(bar_bempty + 8 * s); // the train tile may be overwritten once these MMAs have read it
@@ -367,8 +384,8 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     }
     else
     {
-        // ---- epilogue: warp w owns TMEM lanes 32 * (w % 4) .. of query tile a = (w - 2) / 4 ----
-        const int quarter = warp & 3, a = (warp - 2) >> 2;
+        // ---- epilogue: warp w (0..7) owns TMEM lanes 32 * (w % 4) .. of query tile a = w / 4 ----
+        const int quarter = warp & 3, a = warp >> 2;
         const int row = a * MMA_M + quarter * 32 + lane;
         const bool active = a < n_row_tiles;
         const int q = q0 + row;
@@ -383,7 +400,34 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                 const int col_base = j * MMA_N;
                 const int n_valid = nt - col_base; // >= 1
                 Top2x2 t;
-                if(active)
+                if(db.debug & 8)
+                {
+                    // ALU work of the epilogue on whatever the registers hold, no tensor-memory load
+                    uint32_t va[32];
+#pragma unroll
+                    for(int i = 0; i < 32; ++i)
+                        va[i] = (uint32_t)(lane * 7 + i + it);
+                    if(active)
+                        for(int c = 0; c < MMA_N; c += 32)
+                        {
+                            push32<false>(t, va, 0, MMA_N);
+                            asm volatile("" : "+r"(va[0]), "+r"(va[1]));
+                        }
+                }
+                else if(db.debug & 6)
+                {
+                    if(active && (db.debug & 2))
+                    {
+                        uint32_t va[32];
+                        for(int c = 0; c < MMA_N; c += 32)
+                        {
+                            tmem_ld32(taddr + c, va);
+                            tmem_wait(va);
+                            t.k0 ^= va[0] ^ va[31];
+                        }
+                    }
+                }
+                else if(active)
                 {
                     if(n_valid >= MMA_N)
                         drain_tile<false>(t, taddr, n_valid);
@@ -419,6 +463,13 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     }
     tc_fence_before();
     __syncthreads();
+    if((db.debug & 32) && threadIdx.x == 0)
+    {
+        unsigned long long ns1;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns1));
+        atomicAdd(&g_mma_clk[0], (unsigned long long)(clock64() - clk0));
+        atomicAdd(&g_mma_clk[1], ns1 - ns0);
+    }
     if(warp == 0)
     {
         __syncwarp();
@@ -427,6 +478,16 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
 }
 } // namespace
 
+static int mma_debug()
+{
+    static int v = -1;
+    if(v < 0)
+    {
+        const char* e = getenv("MSLAM_MMA_DEBUG");
+        v = e ? atoi(e) : 0;
+    }
+    return v;
+}
 int knn_mma_pad(int cap)
 {
     return (cap + PAD_ROWS - 1) / PAD_ROWS * PAD_ROWS;
@@ -462,7 +523,9 @@ cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, c
         configured = true;
     }
     dim3 grd((cap + CTA_ROWS - 1) / CTA_ROWS, n_pairs);
-    k_knn2_mma<false><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, DbArgs{});
+    DbArgs none{};
+    none.debug = mma_debug();
+    k_knn2_mma<false><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, none);
     ++*launches;
     return cudaSuccess;
 }
@@ -484,6 +547,7 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
     db.t_cap = q_cap, db.t_cap_pad = knn_mma_pad(q_cap), db.n_keyframes = score_stride, db.int_ratio = ratio == 0.7;
     db.ratio = ratio, db.scores = scores;
     db.group = kDbGroup, db.n_sets = nq_frames;
+    db.debug = mma_debug();
     // grid.y = query frames, grid.z = keyframes (<= 65535 per launch)
     for(int kf0 = 0; kf0 < n_keyframes; kf0 += 65535)
     {
@@ -494,6 +558,16 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
         k_knn2_mma<true><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
                                                                xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
         ++*launches;
+    }
+    if(db.debug & 32)
+    {
+        unsigned long long h[2] = {0, 0};
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(h, g_mma_clk, sizeof(h));
+        fprintf(stderr, "k_knn2_mma: %.1f MHz SM clock inside the kernel (%llu cycles / %llu ns summed over CTAs)\n",
+                h[1] ? 1e3 * (double)h[0] / (double)h[1] : 0.0, h[0], h[1]);
+        unsigned long long z[2] = {0, 0};
+        cudaMemcpyToSymbol(g_mma_clk, z, sizeof(z));
     }
     return cudaGetLastError();
 }
