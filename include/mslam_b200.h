@@ -225,6 +225,44 @@ MSLAM_B200_API int mslam_b200_backproject(mslam_b200_ctx* ctx, const double* xy,
                                           const uint16_t* depth, int width, int height, const mslam_b200_camera* cam,
                                           double* out_xyz, uint8_t* out_valid);
 
+/* ---- RANSAC PnP: SURVEY 8(f) row f4 -------------------------------------------------------------------------------- */
+/* Replaces OpenCvRansacPnp::solvePnp (src/lib/modular_slam/cv_ransac_pnp.cpp:15-85), i.e. the call
+ *   cv::solvePnPRansac(objectPoints f32, imagePoints f32, cameraMatrix f32, noArray(), rvec, tvec, true, 100, 5.0, 0.99,
+ *                      inliers)                                                                        (:56-57)
+ * made by RgbdFeatureFrontend::track on the matcher's output (rgbd_feature_frontend.cpp:345-361).  All hypotheses of a
+ * frame are evaluated in parallel and a call covers a batch of frames (csrc/pnp_kernels.cu).  The minimal solver (P3P +
+ * a 4th point) and the random stream (a counter-based hash of seed / frame / hypothesis) differ from OpenCV's EPnP-on-5 +
+ * cv::RNG, so agreement with cv::solvePnPRansac is by tolerance (same inlier set on separable data, same
+ * least-squares pose over it), not by bits; `confidence` is accepted for interface parity and unused (no early exit:
+ * the hypotheses do not run one after another).  The extrinsic guess the reference passes only seeds OpenCV's final
+ * Levenberg-Marquardt fit; here the fit starts from the winning hypothesis, so no guess is taken. */
+typedef struct mslam_b200_pnp_params
+{
+    int struct_size;          /* = sizeof(mslam_b200_pnp_params) */
+    int iterations;           /* hypotheses per frame; reference: 100 (1..256) */
+    double reproj_error;      /* inlier threshold in pixels; reference: 5.0 (squared error <= reproj_error^2) */
+    double confidence;        /* reference: 0.99; unused */
+    unsigned int seed;        /* random stream; frame f of a batch call uses (seed, frame_base + f) */
+    int frame_base;
+    int refine_iterations;    /* Levenberg-Marquardt cap; default 30 */
+    int reserved;
+    double fx, fy, cx, cy;    /* narrowed to float like the reference's cameraMatrix (:52-53) */
+} mslam_b200_pnp_params;
+MSLAM_B200_API void mslam_b200_pnp_default_params(mslam_b200_pnp_params* p);
+/* Device variant: d_obj [n_frames][cap][3] f32 landmark positions (world), d_img [n_frames][cap][2] f32 pixels,
+ * d_counts [n_frames].  Outputs per frame: d_rvec_tvec [6] f64 (world->camera Rodrigues vector, translation),
+ * d_pose [7] f64 (the reference's result.pose: orientation quaternion w,x,y,z = R^-1 and position = -(R^-1 t), :65-77),
+ * d_inliers [cap] u8 (result.inliers, :79-82), d_info [4] i32 = {found, n_inliers, winning hypothesis, LM iterations}.
+ * found = 0 where the reference returns std::nullopt (and for n < 4, where cv::solvePnPRansac throws). */
+MSLAM_B200_API int mslam_b200_pnp_ransac_batch_dev(mslam_b200_ctx* ctx, const float* d_obj, const float* d_img,
+                                                   const int* d_counts, int n_frames, int cap,
+                                                   const mslam_b200_pnp_params* params, double* d_rvec_tvec, double* d_pose,
+                                                   uint8_t* d_inliers, int* d_info);
+/* Host variant (host in / host out, same layouts). */
+MSLAM_B200_API int mslam_b200_pnp_ransac_batch(mslam_b200_ctx* ctx, const float* obj, const float* img, const int* counts,
+                                               int n_frames, int cap, const mslam_b200_pnp_params* params,
+                                               double* rvec_tvec, double* pose, uint8_t* inliers, int* info);
+
 /* ---- second detector: DistributedOrbOpenCvDetector, SURVEY 8(f) row f1 ---------------------------------------- */
 /* Replaces DistributedOrbOpenCvDetector::detect (src/lib/modular_slam/distributed_cv_feature.cpp:1189-1222: toGrayScale,
  * then OrbExtractorPimpl::extract :719-809), the detector the Viewer app wires in (src/app/viewer/viewer.cpp:183):

@@ -37,6 +37,24 @@ class Camera(C.Structure):
                 ("reserved", C.c_int)]
 
 
+class PnpParams(C.Structure):
+    """mslam_b200_pnp_params: the arguments of cv::solvePnPRansac at cv_ransac_pnp.cpp:56-57 plus the camera matrix"""
+    _fields_ = [("struct_size", C.c_int), ("iterations", C.c_int), ("reproj_error", C.c_double), ("confidence", C.c_double),
+                ("seed", C.c_uint), ("frame_base", C.c_int), ("refine_iterations", C.c_int), ("reserved", C.c_int),
+                ("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double)]
+
+
+def pnp_params(fx, fy, cx, cy, **kw):
+    p = PnpParams()
+    library().mslam_b200_pnp_default_params(C.byref(p))
+    p.fx, p.fy, p.cx, p.cy = fx, fy, cx, cy
+    for k, v in kw.items():
+        if not hasattr(p, k):
+            raise TypeError(k)
+        setattr(p, k, v)
+    return p
+
+
 class MslamB200Error(RuntimeError):
     def __init__(self, status, what, detail=""):
         self.status = status
@@ -62,6 +80,7 @@ def library():
         lib.mslam_b200_destroy.argtypes = [C.c_void_p]
         lib.mslam_b200_destroy.restype = None
         lib.mslam_b200_default_config.restype = None
+        lib.mslam_b200_pnp_default_params.restype = None
         _lib = lib
     return _lib
 
@@ -379,6 +398,29 @@ class Context:
         self._chk(library().mslam_b200_backproject_dev(self._h, _ptr(d_kp), kp_cap, _ptr(d_index), _ptr(d_counts), n_pairs,
                                                        cap, _ptr(d_depth), width, height, C.byref(camera), _ptr(d_xyz),
                                                        _ptr(d_valid)), "backproject_dev")
+
+    # -- RANSAC PnP ------------------------------------------------------------------------------------
+    def pnp_ransac_batch(self, obj, img, counts, params):
+        """OpenCvRansacPnp::solvePnp for a batch of frames: obj [F, cap, 3] f32, img [F, cap, 2] f32, counts [F]
+        -> (rvec_tvec [F, 6] f64, pose [F, 7] f64 (qw qx qy qz px py pz), inliers [F, cap] u8, info [F, 4] i32 =
+        found, n_inliers, winning hypothesis, LM iterations)"""
+        obj = np.ascontiguousarray(obj, np.float32)
+        img = np.ascontiguousarray(img, np.float32)
+        counts = np.ascontiguousarray(counts, np.int32)
+        F, cap, _ = obj.shape
+        assert img.shape == (F, cap, 2) and counts.shape == (F,)
+        rt = np.zeros((F, 6), np.float64)
+        pose = np.zeros((F, 7), np.float64)
+        inl = np.zeros((F, cap), np.uint8)
+        info = np.zeros((F, 4), np.int32)
+        self._chk(library().mslam_b200_pnp_ransac_batch(self._h, _ptr(obj), _ptr(img), _ptr(counts), F, cap, C.byref(params),
+                                                        _ptr(rt), _ptr(pose), _ptr(inl), _ptr(info)), "pnp_ransac_batch")
+        return rt, pose, inl, info
+
+    def pnp_ransac_batch_dev(self, d_obj, d_img, d_counts, n_frames, cap, params, d_rt, d_pose, d_inliers, d_info):
+        self._chk(library().mslam_b200_pnp_ransac_batch_dev(self._h, _ptr(d_obj), _ptr(d_img), _ptr(d_counts), n_frames, cap,
+                                                            C.byref(params), _ptr(d_rt), _ptr(d_pose), _ptr(d_inliers),
+                                                            _ptr(d_info)), "pnp_ransac_batch_dev")
 
     # -- measurement ------------------------------------------------------------------------------------------------------
     STAGES = ("gray", "resize", "fast", "select", "blur", "describe", "knn", "compact", "db")

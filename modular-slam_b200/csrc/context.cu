@@ -1567,6 +1567,83 @@ int mslam_b200_backproject(mslam_b200_ctx* ctx, const double* xy, int n, int str
     return rc;
 }
 
+// ---- RANSAC PnP ----------------------------------------------------------------------------------------
+void mslam_b200_pnp_default_params(mslam_b200_pnp_params* p)
+{
+    if(!p)
+        return;
+    memset(p, 0, sizeof(*p));
+    p->struct_size = (int)sizeof(*p);
+    p->iterations = 100;    // cv_ransac_pnp.cpp:57
+    p->reproj_error = 5.0;
+    p->confidence = 0.99;
+    p->refine_iterations = 30;
+    p->fx = p->fy = 1.0;
+}
+
+static bool pnp_params_ok(const mslam_b200_pnp_params* p)
+{
+    return p && p->struct_size == (int)sizeof(*p) && p->iterations >= 1 && p->iterations <= pnp_max_hypotheses() &&
+           p->reproj_error > 0.0 && p->refine_iterations >= 0 && (float)p->fx != 0.f && (float)p->fy != 0.f;
+}
+
+int mslam_b200_pnp_ransac_batch_dev(mslam_b200_ctx* ctx, const float* d_obj, const float* d_img, const int* d_counts,
+                                    int n_frames, int cap, const mslam_b200_pnp_params* params, double* d_rvec_tvec,
+                                    double* d_pose, uint8_t* d_inliers, int* d_info)
+{
+    if(!ctx || !d_obj || !d_img || !d_counts || !d_rvec_tvec || !d_pose || !d_inliers || !d_info || n_frames < 1 || cap < 1 ||
+       !pnp_params_ok(params))
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    launch_pnp_ransac(ctx->stream, d_obj, d_img, d_counts, n_frames, cap, params->frame_base, (double)(float)params->fx,
+                      (double)(float)params->fy, (double)(float)params->cx, (double)(float)params->cy, params->iterations,
+                      params->reproj_error * params->reproj_error, params->seed, params->refine_iterations, d_rvec_tvec,
+                      d_pose, d_inliers, d_info, &ctx->launches);
+    MSLAM_CUDA_OK(cudaGetLastError());
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_pnp_ransac_batch(mslam_b200_ctx* ctx, const float* obj, const float* img, const int* counts, int n_frames,
+                                int cap, const mslam_b200_pnp_params* params, double* rvec_tvec, double* pose,
+                                uint8_t* inliers, int* info)
+{
+    if(!ctx || !obj || !img || !counts || !rvec_tvec || !pose || !inliers || !info || n_frames < 1 || cap < 1 ||
+       !pnp_params_ok(params))
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    const size_t F = (size_t)n_frames;
+    const size_t b_obj = F * cap * 3 * sizeof(float), b_img = F * cap * 2 * sizeof(float), b_cnt = F * sizeof(int);
+    const size_t b_rt = F * 6 * sizeof(double), b_pose = F * 7 * sizeof(double), b_inl = F * cap, b_info = F * 4 * sizeof(int);
+    // one allocation, 256-byte aligned sections
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t o_img = up(b_obj), o_cnt = o_img + up(b_img), o_rt = o_cnt + up(b_cnt), o_pose = o_rt + up(b_rt),
+                 o_inl = o_pose + up(b_pose), o_info = o_inl + up(b_inl), total = o_info + up(b_info);
+    uint8_t* d = nullptr;
+    int rc = MSLAM_B200_OK;
+    cudaError_t e;
+#define PNQ(expr)                                                                                                      \
+    if(rc == MSLAM_B200_OK && (e = (expr)) != cudaSuccess)                                                             \
+    rc = ctx_fail(ctx, e, #expr)
+    PNQ(cudaMalloc(&d, total));
+    PNQ(cudaMemcpyAsync(d, obj, b_obj, cudaMemcpyHostToDevice, st));
+    PNQ(cudaMemcpyAsync(d + o_img, img, b_img, cudaMemcpyHostToDevice, st));
+    PNQ(cudaMemcpyAsync(d + o_cnt, counts, b_cnt, cudaMemcpyHostToDevice, st));
+    if(rc == MSLAM_B200_OK)
+        rc = mslam_b200_pnp_ransac_batch_dev(ctx, (const float*)d, (const float*)(d + o_img), (const int*)(d + o_cnt), n_frames,
+                                             cap, params, (double*)(d + o_rt), (double*)(d + o_pose), d + o_inl,
+                                             (int*)(d + o_info));
+    PNQ(cudaMemcpyAsync(rvec_tvec, d + o_rt, b_rt, cudaMemcpyDeviceToHost, st));
+    PNQ(cudaMemcpyAsync(pose, d + o_pose, b_pose, cudaMemcpyDeviceToHost, st));
+    PNQ(cudaMemcpyAsync(inliers, d + o_inl, b_inl, cudaMemcpyDeviceToHost, st));
+    PNQ(cudaMemcpyAsync(info, d + o_info, b_info, cudaMemcpyDeviceToHost, st));
+    PNQ(cudaStreamSynchronize(st));
+#undef PNQ
+    if(d)
+        cudaFree(d);
+    return rc;
+}
+
 int mslam_b200_enable_stage_timing(mslam_b200_ctx* ctx, int enable)
 {
     if(!ctx)

@@ -57,5 +57,10 @@ void launch_backproject(cudaStream_t st, const mslam_b200_keypoint* kp, int kp_c
                         double* xyz, uint8_t* valid, long long* launches);
 void launch_backproject_xy(cudaStream_t st, const double* xy, int n, const uint16_t* depth, int width, int height,
                            const mslam_b200_camera& cam, double* xyz, uint8_t* valid, long long* launches);
+// RANSAC PnP (pnp_kernels.cu)
+void launch_pnp_ransac(cudaStream_t st, const float* obj, const float* img, const int* counts, int n_frames, int cap, int frame0,
+                       double fx, double fy, double cx, double cy, int iterations, double thr2, unsigned seed, int refine_iters,
+                       double* out_rt, double* out_pose, uint8_t* out_mask, int* out_info, long long* launches);
+int pnp_max_hypotheses();
 cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long long* launches);
 } // namespace mslam_b200

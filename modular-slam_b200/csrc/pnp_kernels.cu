@@ -1,0 +1,655 @@
+// pnp_kernels.cu -- SURVEY.md section 8(f) row f4: RANSAC PnP, batched over frames.
+//
+// Replaces OpenCvRansacPnp::solvePnp (src/lib/modular_slam/cv_ransac_pnp.cpp:15-85), i.e.
+//   cv::solvePnPRansac(obj f32, img f32, K f32, noArray(), rvec, tvec, true, 100, 5.0, 0.99, inliers)      (:56-57)
+// the consumer of the matcher's output in RgbdFeatureFrontend::track (rgbd_feature_frontend.cpp:345-361).
+//
+// cv::solvePnPRansac is a sequential loop (draw 5 points from cv::RNG, EPnP, count inliers, adapt the iteration count)
+// followed by a Levenberg-Marquardt fit over the inliers.  Here all hypotheses of a frame are evaluated at once by one
+// CTA, and a launch covers a whole batch of frames (one CTA per frame):
+//   phase 1  thread h < iterations: 4 distinct indices from a counter-based hash, Grunert's P3P on the first three
+//            (quartic in v = s3 / s1 from polynomial products, Ferrari roots + 2 Newton steps), triangle alignment
+//            -> (R, t) per real root, the 4th point picks the root;                          float64 throughout
+//   phase 2  warp per hypothesis, lanes over the points: squared reprojection error <= thr^2 (the test of
+//            PnPRansacCallback::computeError + findInliers), warp-shuffle count;
+//   phase 3  best = most inliers, lowest h on ties, >= 5 inliers (cv: goodCount > modelPoints - 1); inlier mask written;
+//   phase 4  Levenberg-Marquardt over the inliers from the best hypothesis: block-reduced 6x6 normal equations, thread 0
+//            solves (Gaussian elimination, partial pivoting), up to 8 damping retries per iteration, to convergence;
+//   phase 5  rvec = log(R), tvec, and the reference's sensor pose (orientation = R^-1 as a quaternion,
+//            position = -(R^-1 t), cv_ransac_pnp.cpp:65-77).
+// Every step mirrors oracle/pnp_oracle.py (same draws, same formulas); parity with OpenCV itself is by tolerance
+// (different minimal solver and random stream) -- DESIGN.md section 4e.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace mslam_b200
+{
+namespace
+{
+constexpr int PNP_THREADS = 256;
+constexpr int PNP_MAX_HYP = 256;
+
+__device__ __forceinline__ unsigned lowbias32(unsigned x)
+{
+    x ^= x >> 16;
+    x *= 0x7FEB352Du;
+    x ^= x >> 15;
+    x *= 0x846CA68Bu;
+    x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ int pnp_draw(unsigned seed, unsigned frame, unsigned hyp, unsigned j, int n)
+{
+    const unsigned r = lowbias32(seed ^ lowbias32(frame * 0x9E3779B9u + hyp * 0x85EBCA6Bu + j * 0xC2B2AE35u + 0x27D4EB2Fu));
+    return (int)(((unsigned long long)r * (unsigned long long)n) >> 32);
+}
+
+struct V3
+{
+    double x, y, z;
+};
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+
+struct Pose
+{
+    double R[9]; // row major
+    double t[3];
+};
+
+__device__ double cubic_largest_real_root(double p, double q, double r)
+{
+    const double Q = (p * p - 3.0 * q) / 9.0;
+    const double R = (2.0 * p * p * p - 9.0 * p * q + 27.0 * r) / 54.0;
+    const double Q3 = Q * Q * Q;
+    if(R * R < Q3)
+    {
+        const double th = acos(fmax(-1.0, fmin(1.0, R / sqrt(Q3))));
+        const double sq = -2.0 * sqrt(Q);
+        const double pi = 3.14159265358979323846;
+        const double y0 = sq * cos(th / 3.0), y1 = sq * cos((th + 2.0 * pi) / 3.0), y2 = sq * cos((th - 2.0 * pi) / 3.0);
+        return fmax(y0, fmax(y1, y2)) - p / 3.0;
+    }
+    const double A = -copysign(1.0, R) * cbrt(fabs(R) + sqrt(fmax(R * R - Q3, 0.0)));
+    const double B = A != 0.0 ? Q / A : 0.0;
+    return A + B - p / 3.0;
+}
+
+// real roots of c4 x^4 + ... + c0; returns how many were written to out[4]
+__device__ int quartic_real_roots(double c4, double c3, double c2, double c1, double c0, double* out)
+{
+    if(c4 == 0.0 || !isfinite(c4))
+        return 0;
+    const double a = c3 / c4, b = c2 / c4, c = c1 / c4, d = c0 / c4;
+    if(!(isfinite(a) && isfinite(b) && isfinite(c) && isfinite(d)))
+        return 0;
+    const double a2 = a * a;
+    const double y = cubic_largest_real_root(-b, a * c - 4.0 * d, 4.0 * b * d - a2 * d - c * c);
+    const double R2 = 0.25 * a2 - b + y;
+    const double scale = fabs(0.25 * a2) + fabs(b) + fabs(y) + 1e-300;
+    if(!(R2 >= -1e-12 * scale))
+        return 0;
+    double R = sqrt(fmax(R2, 0.0));
+    double D2, E2;
+    if(R > 1e-8 * sqrt(scale))
+    {
+        const double t = 0.25 * (4.0 * a * b - 8.0 * c - a2 * a) / R;
+        D2 = 0.75 * a2 - R * R - 2.0 * b + t;
+        E2 = 0.75 * a2 - R * R - 2.0 * b - t;
+    }
+    else
+    {
+        R = 0.0;
+        double w = y * y - 4.0 * d;
+        if(w < 0.0)
+            w = 0.0;
+        D2 = 0.75 * a2 - 2.0 * b + 2.0 * sqrt(w);
+        E2 = 0.75 * a2 - 2.0 * b - 2.0 * sqrt(w);
+    }
+    const double tol = 1e-10 * (fabs(0.75 * a2) + fabs(2.0 * b) + 1e-300);
+    int n = 0;
+    if(D2 >= -tol)
+    {
+        const double D = sqrt(fmax(D2, 0.0));
+        out[n++] = -0.25 * a + 0.5 * R + 0.5 * D;
+        out[n++] = -0.25 * a + 0.5 * R - 0.5 * D;
+    }
+    if(E2 >= -tol)
+    {
+        const double E = sqrt(fmax(E2, 0.0));
+        out[n++] = -0.25 * a - 0.5 * R + 0.5 * E;
+        out[n++] = -0.25 * a - 0.5 * R - 0.5 * E;
+    }
+    for(int i = 0; i < n; ++i)
+    {
+        double x = out[i];
+        for(int k = 0; k < 2; ++k)
+        {
+            const double f = (((x + a) * x + b) * x + c) * x + d;
+            const double fp = ((4.0 * x + 3.0 * a) * x + 2.0 * b) * x + c;
+            if(fp != 0.0)
+                x = x - f / fp;
+        }
+        out[i] = x;
+    }
+    return n;
+}
+
+// orthonormal frame of a triangle: columns e1, e2, e3 (B[r][c], row major)
+__device__ bool triad(V3 p0, V3 p1, V3 p2, double* B)
+{
+    V3 e1 = p1 - p0;
+    const double n1 = sqrt(dot(e1, e1));
+    if(n1 == 0.0)
+        return false;
+    e1 = e1 * (1.0 / n1);
+    V3 e3 = cross(e1, p2 - p0);
+    const double n3 = sqrt(dot(e3, e3));
+    if(n3 == 0.0)
+        return false;
+    e3 = e3 * (1.0 / n3);
+    const V3 e2 = cross(e3, e1);
+    B[0] = e1.x, B[1] = e2.x, B[2] = e3.x;
+    B[3] = e1.y, B[4] = e2.y, B[5] = e3.y;
+    B[6] = e1.z, B[7] = e2.z, B[8] = e3.z;
+    return true;
+}
+
+struct Cam
+{
+    double fx, fy, cx, cy;
+};
+
+__device__ __forceinline__ V3 load_obj(const float* __restrict__ obj, int i)
+{
+    return {(double)__ldg(obj + 3 * i), (double)__ldg(obj + 3 * i + 1), (double)__ldg(obj + 3 * i + 2)};
+}
+__device__ __forceinline__ V3 bearing(const float* __restrict__ img, int i, const Cam& K)
+{
+    const double bx = ((double)__ldg(img + 2 * i) - K.cx) / K.fx, by = ((double)__ldg(img + 2 * i + 1) - K.cy) / K.fy;
+    const double nn = sqrt(bx * bx + by * by + 1.0);
+    return {bx / nn, by / nn, 1.0 / nn};
+}
+__device__ __forceinline__ V3 transform(const double* R, const double* t, V3 X)
+{
+    return {R[0] * X.x + R[1] * X.y + R[2] * X.z + t[0], R[3] * X.x + R[4] * X.y + R[5] * X.z + t[1],
+            R[6] * X.x + R[7] * X.y + R[8] * X.z + t[2]};
+}
+__device__ __forceinline__ double err2(const double* R, const double* t, V3 X, double u0, double v0, const Cam& K)
+{
+    const V3 c = transform(R, t, X);
+    const double u = K.fx * (c.x / c.z) + K.cx, v = K.fy * (c.y / c.z) + K.cy;
+    const double du = u - u0, dv = v - v0;
+    return du * du + dv * dv;
+}
+
+// one hypothesis from points idx[0..3]; false if the sample yields no pose
+__device__ bool p3p_hypothesis(const float* __restrict__ obj, const float* __restrict__ img, const int* idx, const Cam& K,
+                               Pose& best)
+{
+    const V3 P0 = load_obj(obj, idx[0]), P1 = load_obj(obj, idx[1]), P2 = load_obj(obj, idx[2]), P3 = load_obj(obj, idx[3]);
+    const V3 f0 = bearing(img, idx[0], K), f1 = bearing(img, idx[1], K), f2 = bearing(img, idx[2], K);
+    const double a2 = dot(P1 - P2, P1 - P2), b2 = dot(P0 - P2, P0 - P2), c2 = dot(P0 - P1, P0 - P1);
+    if(a2 == 0.0 || b2 == 0.0 || c2 == 0.0)
+        return false;
+    const double ca = dot(f1, f2), cb = dot(f0, f2), cg = dot(f0, f1);
+    const double k1 = (a2 - c2) / b2, k2 = c2 / b2;
+    const double n2 = k1 - 1.0, n1 = -2.0 * k1 * cb, n0 = 1.0 + k1;
+    const double d1 = -2.0 * ca, d0 = 2.0 * cg;
+    const double NN[5] = {n0 * n0, 2.0 * n0 * n1, n1 * n1 + 2.0 * n0 * n2, 2.0 * n1 * n2, n2 * n2};
+    const double ND[5] = {n0 * d0, n0 * d1 + n1 * d0, n1 * d1 + n2 * d0, n2 * d1, 0.0};
+    const double DD[3] = {d0 * d0, 2.0 * d0 * d1, d1 * d1};
+    const double q0 = 1.0 - k2, q1 = 2.0 * k2 * cb, q2 = -k2;
+    const double DQ[5] = {DD[0] * q0, DD[0] * q1 + DD[1] * q0, DD[0] * q2 + DD[1] * q1 + DD[2] * q0, DD[1] * q2 + DD[2] * q1,
+                          DD[2] * q2};
+    double co[5];
+#pragma unroll
+    for(int i = 0; i < 5; ++i)
+        co[i] = NN[i] - 2.0 * cg * ND[i] + DQ[i];
+    double Bw[9];
+    if(!triad(P0, P1, P2, Bw))
+        return false;
+    double roots[4];
+    const int nr = quartic_real_roots(co[4], co[3], co[2], co[1], co[0], roots);
+    const double u3 = (double)__ldg(img + 2 * idx[3]), v3 = (double)__ldg(img + 2 * idx[3] + 1);
+    bool found = false;
+    double best_e = 0.0;
+    for(int k = 0; k < nr; ++k)
+    {
+        const double v = roots[k];
+        if(!(v > 0.0) || !isfinite(v))
+            continue;
+        const double den = d1 * v + d0;
+        if(fabs(den) < 1e-12)
+            continue;
+        const double u = ((n2 * v + n1) * v + n0) / den;
+        if(!(u > 0.0))
+            continue;
+        const double w = 1.0 + v * v - 2.0 * v * cb;
+        if(!(w > 0.0))
+            continue;
+        const double s1 = sqrt(b2 / w);
+        const V3 C0 = f0 * s1, C1 = f1 * (u * s1), C2 = f2 * (v * s1);
+        double Bc[9];
+        if(!triad(C0, C1, C2, Bc))
+            continue;
+        Pose p;
+#pragma unroll
+        for(int r = 0; r < 3; ++r)
+#pragma unroll
+            for(int c = 0; c < 3; ++c) // R = Bc Bw^T
+                p.R[3 * r + c] = Bc[3 * r] * Bw[3 * c] + Bc[3 * r + 1] * Bw[3 * c + 1] + Bc[3 * r + 2] * Bw[3 * c + 2];
+        const double zero[3] = {0.0, 0.0, 0.0};
+        const V3 RP0 = transform(p.R, zero, P0);
+        p.t[0] = C0.x - RP0.x, p.t[1] = C0.y - RP0.y, p.t[2] = C0.z - RP0.z;
+        const double e = err2(p.R, p.t, P3, u3, v3, K);
+        const double zc = transform(p.R, p.t, P3).z;
+        if(zc > 0.0 && (!found || e < best_e) && e < INFINITY)
+        {
+            found = true;
+            best_e = e;
+            best = p;
+        }
+    }
+    return found;
+}
+
+__device__ void rodrigues_exp(const double* w, double* R)
+{
+    const double th = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+    const double K[9] = {0.0, -w[2], w[1], w[2], 0.0, -w[0], -w[1], w[0], 0.0};
+    double A = 1.0, B = 0.0;
+    if(th >= 1e-12)
+    {
+        A = sin(th) / th;
+        B = (1.0 - cos(th)) / (th * th);
+    }
+#pragma unroll
+    for(int r = 0; r < 3; ++r)
+#pragma unroll
+        for(int c = 0; c < 3; ++c)
+        {
+            const double kk = K[3 * r] * K[c] + K[3 * r + 1] * K[3 + c] + K[3 * r + 2] * K[6 + c];
+            R[3 * r + c] = (r == c ? 1.0 : 0.0) + A * K[3 * r + c] + B * kk;
+        }
+}
+
+__device__ void rodrigues_log(const double* R, double* out)
+{
+    double c = 0.5 * (R[0] + R[4] + R[8] - 1.0);
+    c = fmax(-1.0, fmin(1.0, c));
+    const double th = acos(c);
+    const double r[3] = {R[7] - R[5], R[2] - R[6], R[3] - R[1]};
+    const double s = 0.5 * sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+    if(s < 1e-10)
+    {
+        if(c > 0.0)
+        {
+            out[0] = 0.5 * r[0], out[1] = 0.5 * r[1], out[2] = 0.5 * r[2];
+            return;
+        }
+        double d[3] = {sqrt(fmax((R[0] + 1.0) * 0.5, 0.0)), sqrt(fmax((R[4] + 1.0) * 0.5, 0.0)), sqrt(fmax((R[8] + 1.0) * 0.5, 0.0))};
+        if(R[1] < 0.0)
+            d[1] = -d[1];
+        if(R[2] < 0.0)
+            d[2] = -d[2];
+        const double n = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        const double k = n > 0.0 ? th / n : 0.0;
+        out[0] = d[0] * k, out[1] = d[1] * k, out[2] = d[2] * k;
+        return;
+    }
+    const double k = 0.5 * th / s;
+    out[0] = r[0] * k, out[1] = r[1] * k, out[2] = r[2] * k;
+}
+
+// rotation matrix (row major) -> unit quaternion (w, x, y, z), w >= 0
+__device__ void quat_from_R(const double* R, double* q)
+{
+    const double tr = R[0] + R[4] + R[8];
+    if(tr > 0.0)
+    {
+        const double s = sqrt(tr + 1.0) * 2.0;
+        q[0] = 0.25 * s, q[1] = (R[7] - R[5]) / s, q[2] = (R[2] - R[6]) / s, q[3] = (R[3] - R[1]) / s;
+    }
+    else if(R[0] > R[4] && R[0] > R[8])
+    {
+        const double s = sqrt(1.0 + R[0] - R[4] - R[8]) * 2.0;
+        q[0] = (R[7] - R[5]) / s, q[1] = 0.25 * s, q[2] = (R[1] + R[3]) / s, q[3] = (R[2] + R[6]) / s;
+    }
+    else if(R[4] > R[8])
+    {
+        const double s = sqrt(1.0 + R[4] - R[0] - R[8]) * 2.0;
+        q[0] = (R[2] - R[6]) / s, q[1] = (R[1] + R[3]) / s, q[2] = 0.25 * s, q[3] = (R[5] + R[7]) / s;
+    }
+    else
+    {
+        const double s = sqrt(1.0 + R[8] - R[0] - R[4]) * 2.0;
+        q[0] = (R[3] - R[1]) / s, q[1] = (R[2] + R[6]) / s, q[2] = (R[5] + R[7]) / s, q[3] = 0.25 * s;
+    }
+    if(q[0] < 0.0)
+        q[0] = -q[0], q[1] = -q[1], q[2] = -q[2], q[3] = -q[3];
+}
+
+// block-wide sum of NV doubles per thread; result in s_red[0..NV) (valid for all threads after the call)
+template <int NV>
+__device__ void block_sum(double* v, double* s_part /* [8][NV] */, double* s_red /* [NV] */)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for(int k = 0; k < NV; ++k)
+    {
+        double x = v[k];
+#pragma unroll
+        for(int o = 16; o > 0; o >>= 1)
+            x += __shfl_xor_sync(0xffffffffu, x, o);
+        if(lane == 0)
+            s_part[warp * NV + k] = x;
+    }
+    __syncthreads();
+    if(threadIdx.x < NV)
+    {
+        double x = 0.0;
+#pragma unroll
+        for(int w = 0; w < PNP_THREADS / 32; ++w)
+            x += s_part[w * NV + threadIdx.x];
+        s_red[threadIdx.x] = x;
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restrict__ obj_all, const float* __restrict__ img_all,
+                                                           const int* __restrict__ counts, int cap, int frame0, Cam K,
+                                                           int iterations, double thr2, unsigned seed, int refine_iters,
+                                                           double* __restrict__ out_rt, double* __restrict__ out_pose,
+                                                           uint8_t* __restrict__ out_mask, int* __restrict__ out_info)
+{
+    __shared__ Pose s_hyp[PNP_MAX_HYP];
+    __shared__ int s_cnt[PNP_MAX_HYP];
+    __shared__ double s_part[8 * 28], s_red[28];
+    __shared__ Pose s_cur, s_new;
+    __shared__ int s_best, s_flag;
+    __shared__ double s_dx[6];
+
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = min(max(counts[f], 0), cap);
+    const float* obj = obj_all + (long long)f * cap * 3;
+    const float* img = img_all + (long long)f * cap * 2;
+    uint8_t* mask = out_mask + (long long)f * cap;
+    int* info = out_info + 4 * f;
+    double* rt = out_rt + 6 * f;
+    double* pose = out_pose + 7 * f;
+
+    for(int i = tid; i < cap; i += PNP_THREADS)
+        mask[i] = 0;
+    if(n < 4)
+    {
+        if(tid == 0)
+            info[0] = 0, info[1] = 0, info[2] = -1, info[3] = 0;
+        if(tid < 6)
+            rt[tid] = 0.0;
+        if(tid < 7)
+            pose[tid] = tid == 0 ? 1.0 : 0.0;
+        return;
+    }
+    const int need = n >= 5 ? 5 : 4;
+
+    // ---- phase 1: one hypothesis per thread ----
+    for(int h = tid; h < iterations; h += PNP_THREADS)
+    {
+        int idx[4], got = 0;
+        for(unsigned j = 0; j < 64 && got < 4; ++j)
+        {
+            const int i = pnp_draw(seed, (unsigned)(frame0 + f), (unsigned)h, j, n);
+            bool dup = false;
+            for(int k = 0; k < got; ++k)
+                dup |= idx[k] == i;
+            if(!dup)
+                idx[got++] = i;
+        }
+        Pose p;
+        const bool ok = got == 4 && p3p_hypothesis(obj, img, idx, K, p);
+        if(ok)
+            s_hyp[h] = p;
+        s_cnt[h] = ok ? 0 : -1;
+    }
+    __syncthreads();
+
+    // ---- phase 2: inlier counts, warp per hypothesis ----
+    for(int h = warp; h < iterations; h += PNP_THREADS / 32)
+    {
+        if(s_cnt[h] < 0)
+            continue;
+        const Pose& p = s_hyp[h];
+        int c = 0;
+        for(int i = lane; i < n; i += 32)
+            c += err2(p.R, p.t, load_obj(obj, i), (double)__ldg(img + 2 * i), (double)__ldg(img + 2 * i + 1), K) <= thr2;
+        c = __reduce_add_sync(0xffffffffu, c);
+        if(lane == 0)
+            s_cnt[h] = c;
+    }
+    __syncthreads();
+
+    // ---- phase 3: best hypothesis (most inliers, lowest index) ----
+    if(warp == 0)
+    {
+        int bc = -1, bh = -1;
+        for(int h = lane; h < iterations; h += 32)
+            if(s_cnt[h] > bc)
+                bc = s_cnt[h], bh = h;
+#pragma unroll
+        for(int o = 16; o > 0; o >>= 1)
+        {
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, o), oh = __shfl_xor_sync(0xffffffffu, bh, o);
+            if(oc > bc || (oc == bc && oh >= 0 && (bh < 0 || oh < bh)))
+                bc = oc, bh = oh;
+        }
+        if(lane == 0)
+        {
+            s_best = bc >= need ? bh : -1;
+            if(bc >= need)
+                s_cur = s_hyp[bh];
+            info[0] = bc >= need;
+            info[1] = bc >= need ? bc : 0;
+            info[2] = bc >= need ? bh : -1;
+        }
+    }
+    __syncthreads();
+    if(s_best < 0)
+    {
+        if(tid == 0)
+            info[3] = 0;
+        if(tid < 6)
+            rt[tid] = 0.0;
+        if(tid < 7)
+            pose[tid] = tid == 0 ? 1.0 : 0.0;
+        return;
+    }
+    // inlier mask of the best hypothesis (kept in registers as well: point i = tid + 256 k)
+    for(int i = tid; i < n; i += PNP_THREADS)
+        mask[i] = err2(s_cur.R, s_cur.t, load_obj(obj, i), (double)__ldg(img + 2 * i), (double)__ldg(img + 2 * i + 1), K) <= thr2;
+    __syncthreads(); // mask[] is re-read below by the threads that wrote it (same thread, same index): no fence needed
+
+    // ---- phase 4: Levenberg-Marquardt over the inliers ----
+    auto cost_of = [&](const Pose& p) -> double {
+        double c[1] = {0.0};
+        for(int i = tid; i < n; i += PNP_THREADS)
+            if(mask[i])
+                c[0] += err2(p.R, p.t, load_obj(obj, i), (double)__ldg(img + 2 * i), (double)__ldg(img + 2 * i + 1), K);
+        block_sum<1>(c, s_part, s_red);
+        const double r = s_red[0];
+        __syncthreads();
+        return r;
+    };
+    double lam = 1e-3;
+    double cost = cost_of(s_cur);
+    int it = 0;
+    for(; it < refine_iters; ++it)
+    {
+        double acc[27]; // 21 upper-triangle entries of J^T J, then 6 of J^T r
+#pragma unroll
+        for(int k = 0; k < 27; ++k)
+            acc[k] = 0.0;
+        for(int i = tid; i < n; i += PNP_THREADS)
+        {
+            if(!mask[i])
+                continue;
+            const V3 c = transform(s_cur.R, s_cur.t, load_obj(obj, i));
+            const double iz = 1.0 / c.z, px = c.x * iz, py = c.y * iz;
+            const double ru = K.fx * px + K.cx - (double)__ldg(img + 2 * i), rv = K.fy * py + K.cy - (double)__ldg(img + 2 * i + 1);
+            const V3 ju = {K.fx * iz, 0.0, -K.fx * px * iz}, jv = {0.0, K.fy * iz, -K.fy * py * iz};
+            const V3 wu = cross(c, ju), wv = cross(c, jv);
+            const double Ju[6] = {wu.x, wu.y, wu.z, ju.x, ju.y, ju.z}, Jv[6] = {wv.x, wv.y, wv.z, jv.x, jv.y, jv.z};
+            int k = 0;
+#pragma unroll
+            for(int r = 0; r < 6; ++r)
+#pragma unroll
+                for(int cc = r; cc < 6; ++cc)
+                    acc[k++] += Ju[r] * Ju[cc] + Jv[r] * Jv[cc];
+#pragma unroll
+            for(int r = 0; r < 6; ++r)
+                acc[21 + r] += Ju[r] * ru + Jv[r] * rv;
+        }
+        block_sum<27>(acc, s_part, s_red);
+        double H[36], g[6];
+        {
+            int k = 0;
+            for(int r = 0; r < 6; ++r)
+                for(int cc = r; cc < 6; ++cc)
+                {
+                    H[6 * r + cc] = s_red[k];
+                    H[6 * cc + r] = s_red[k];
+                    ++k;
+                }
+            for(int r = 0; r < 6; ++r)
+                g[r] = s_red[21 + r];
+        }
+        __syncthreads();
+        bool improved = false;
+        double step = 0.0, drop = 0.0;
+        for(int tr = 0; tr < 8; ++tr)
+        {
+            if(tid == 0)
+            {
+                double A[36], b[6];
+                for(int k = 0; k < 36; ++k)
+                    A[k] = H[k];
+                for(int k = 0; k < 6; ++k)
+                {
+                    A[7 * k] += lam * H[7 * k] + 1e-12;
+                    b[k] = -g[k];
+                }
+                bool ok = true;
+                for(int col = 0; col < 6 && ok; ++col)
+                {
+                    int piv = col;
+                    for(int r = col + 1; r < 6; ++r)
+                        if(fabs(A[6 * r + col]) > fabs(A[6 * piv + col]))
+                            piv = r;
+                    if(A[6 * piv + col] == 0.0 || !isfinite(A[6 * piv + col]))
+                    {
+                        ok = false;
+                        break;
+                    }
+                    if(piv != col)
+                    {
+                        for(int k = 0; k < 6; ++k)
+                        {
+                            const double tmp = A[6 * col + k];
+                            A[6 * col + k] = A[6 * piv + k];
+                            A[6 * piv + k] = tmp;
+                        }
+                        const double tmp = b[col];
+                        b[col] = b[piv];
+                        b[piv] = tmp;
+                    }
+                    for(int r = col + 1; r < 6; ++r)
+                    {
+                        const double m = A[6 * r + col] / A[6 * col + col];
+                        for(int k = col; k < 6; ++k)
+                            A[6 * r + k] -= m * A[6 * col + k];
+                        b[r] -= m * b[col];
+                    }
+                }
+                if(ok)
+                {
+                    for(int r = 5; r >= 0; --r)
+                    {
+                        double x = b[r];
+                        for(int k = r + 1; k < 6; ++k)
+                            x -= A[6 * r + k] * s_dx[k];
+                        s_dx[r] = x / A[6 * r + r];
+                    }
+                    double dR[9];
+                    rodrigues_exp(s_dx, dR);
+                    for(int r = 0; r < 3; ++r)
+                    {
+                        for(int c = 0; c < 3; ++c)
+                            s_new.R[3 * r + c] = dR[3 * r] * s_cur.R[c] + dR[3 * r + 1] * s_cur.R[3 + c] + dR[3 * r + 2] * s_cur.R[6 + c];
+                        s_new.t[r] = dR[3 * r] * s_cur.t[0] + dR[3 * r + 1] * s_cur.t[1] + dR[3 * r + 2] * s_cur.t[2] + s_dx[3 + r];
+                    }
+                }
+                s_flag = ok;
+            }
+            __syncthreads();
+            const bool ok = s_flag != 0;
+            if(!ok)
+            {
+                lam *= 10.0;
+                __syncthreads();
+                continue;
+            }
+            const double cn = cost_of(s_new);
+            if(isfinite(cn) && cn <= cost)
+            {
+                step = 0.0;
+                for(int k = 0; k < 6; ++k)
+                    step = fmax(step, fabs(s_dx[k]));
+                drop = cost - cn;
+                cost = cn;
+                lam = fmax(lam * 0.1, 1e-12);
+                improved = true;
+                __syncthreads();
+                if(tid == 0)
+                    s_cur = s_new;
+                __syncthreads();
+                break;
+            }
+            lam *= 10.0;
+            __syncthreads();
+        }
+        if(!improved || step < 1e-13 || drop <= 1e-15 * fmax(cost, 1e-300))
+        {
+            ++it;
+            break;
+        }
+    }
+
+    // ---- phase 5: outputs ----
+    if(tid == 0)
+    {
+        info[3] = it;
+        rodrigues_log(s_cur.R, rt);
+        rt[3] = s_cur.t[0], rt[4] = s_cur.t[1], rt[5] = s_cur.t[2];
+        // sensor pose (cv_ransac_pnp.cpp:65-77): orientation = R^-1, position = -(R^-1 t)
+        const double Rt[9] = {s_cur.R[0], s_cur.R[3], s_cur.R[6], s_cur.R[1], s_cur.R[4], s_cur.R[7], s_cur.R[2], s_cur.R[5], s_cur.R[8]};
+        quat_from_R(Rt, pose);
+        for(int r = 0; r < 3; ++r)
+            pose[4 + r] = -(Rt[3 * r] * s_cur.t[0] + Rt[3 * r + 1] * s_cur.t[1] + Rt[3 * r + 2] * s_cur.t[2]);
+    }
+}
+} // namespace
+
+void launch_pnp_ransac(cudaStream_t st, const float* obj, const float* img, const int* counts, int n_frames, int cap, int frame0,
+                       double fx, double fy, double cx, double cy, int iterations, double thr2, unsigned seed, int refine_iters,
+                       double* out_rt, double* out_pose, uint8_t* out_mask, int* out_info, long long* launches)
+{
+    const Cam K{fx, fy, cx, cy};
+    k_pnp_ransac<<<n_frames, PNP_THREADS, 0, st>>>(obj, img, counts, cap, frame0, K, iterations, thr2, seed, refine_iters, out_rt,
+                                                   out_pose, out_mask, out_info);
+    if(launches)
+        ++*launches;
+}
+int pnp_max_hypotheses() { return PNP_MAX_HYP; }
+} // namespace mslam_b200

@@ -78,3 +78,35 @@ def plant_copies(db, queries, frac=0.01, flip_p=0.05, seed=3):
         db[kf] = np.packbits(bits ^ flips, axis=-1)
         planted[int(kf)] = q
     return planted
+
+
+def _rodrigues(w):
+    th = float(np.sqrt(w @ w))
+    K = np.array([[0.0, -w[2], w[1]], [w[2], 0.0, -w[0]], [-w[1], w[0], 0.0]])
+    if th < 1e-12:
+        return np.eye(3) + K
+    return np.eye(3) + (np.sin(th) / th) * K + ((1.0 - np.cos(th)) / (th * th)) * (K @ K)
+
+
+TUM_K = (525.0, 525.0, 319.5, 239.5)  # fx, fy, cx, cy of the reference's TUM camera (rgbd_file_provider.cpp tumRgbdCameraParams)
+
+
+def pnp_scene(seed, n=300, outlier_frac=0.3, noise=0.5, width=640, height=480, K=TUM_K):
+    """Landmark / pixel correspondences of one tracked frame (the input of OpenCvRansacPnp::solvePnp): n world points seen
+    by a camera at a random pose, pixel noise ~ N(0, noise), and outlier_frac of the pixels replaced by uniform ones.
+    -> obj [n, 3] f32, img [n, 2] f32, rvec [3], tvec [3] (world -> camera), outlier mask [n] bool"""
+    rng = np.random.default_rng(seed)
+    fx, fy, cx, cy = K
+    rv, tv = rng.normal(0, 0.15, 3), rng.normal(0, 0.3, 3)
+    R = _rodrigues(rv)
+    u, v, z = rng.uniform(20, width - 20, n), rng.uniform(20, height - 20, n), rng.uniform(0.8, 6.0, n)
+    Xc = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], 1)
+    X = (Xc - tv) @ R
+    x = np.stack([u, v], 1) + rng.normal(0, noise, (n, 2))
+    no = int(outlier_frac * n)
+    out = np.zeros(n, bool)
+    if no:
+        oi = rng.choice(n, no, replace=False)
+        x[oi] = np.stack([rng.uniform(0, width, no), rng.uniform(0, height, no)], 1)
+        out[oi] = True
+    return X.astype(np.float32), x.astype(np.float32), rv, tv, out
