@@ -18,6 +18,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <memory>
+#include <optional>
 #include <vector>
 
 namespace mslam
@@ -137,6 +138,89 @@ class DataProviderInterface : public SlamComponent
     virtual bool init() = 0;
     virtual bool fetch() = 0;
     virtual std::shared_ptr<DataType> recentData() const = 0;
+};
+
+// ---- PnP side (ransac_pnp_b200.hpp): types/basic_types.hpp:16-17, types/state.hpp:7-12, types/slam3d_types.hpp:14,
+// types/landmark.hpp:11-16, pnp.hpp:14-35
+struct Vector3 // Eigen::Vector3d: three doubles, not over-aligned
+{
+    double v[3];
+    double x() const { return v[0]; }
+    double y() const { return v[1]; }
+    double z() const { return v[2]; }
+    double& operator[](int i) { return v[i]; }
+    double operator[](int i) const { return v[i]; }
+};
+
+struct alignas(16) Quaternion // Eigen::Quaterniond: coefficients stored x, y, z, w; identity by default here
+{
+    double c[4] = {0.0, 0.0, 0.0, 1.0};
+    double x() const { return c[0]; }
+    double y() const { return c[1]; }
+    double z() const { return c[2]; }
+    double w() const { return c[3]; }
+};
+
+template <typename PositionType, typename OrientationType>
+struct State
+{
+    PositionType position;
+    OrientationType orientation;
+};
+
+namespace slam3d
+{
+using SensorState = mslam::State<Vector3, Quaternion>;
+}
+
+template <typename StateType>
+struct Landmark
+{
+    Id id;
+    StateType state;
+};
+
+namespace shim
+{
+// the part of boost::dynamic_bitset<> the reference touches (resize(n, false), operator[], count, size)
+class dynamic_bitset
+{
+  public:
+    void resize(std::size_t n, bool value = false) { bits.resize(n, value); }
+    std::vector<bool>::reference operator[](std::size_t i) { return bits[i]; }
+    bool operator[](std::size_t i) const { return bits[i]; }
+    std::size_t size() const { return bits.size(); }
+    std::size_t count() const
+    {
+        std::size_t n = 0;
+        for(bool b : bits)
+            n += b;
+        return n;
+    }
+
+  private:
+    std::vector<bool> bits;
+};
+} // namespace shim
+
+template <typename SensorStateType, typename LandmarkStateType>
+class IPnpAlgorithm
+{
+  public:
+    struct PnpResult
+    {
+        SensorStateType pose;
+        shim::dynamic_bitset inliers;
+    };
+    virtual std::optional<PnpResult> solvePnp(const std::vector<std::shared_ptr<Landmark<LandmarkStateType>>>& landmarks,
+                                              const std::vector<mslam::Vector2>& imgPoints,
+                                              const SensorStateType& initial = SensorStateType()) = 0;
+    void setCameraParameters(const CameraParameters& newParameters) { cameraParams = newParameters; }
+    [[nodiscard]] const CameraParameters& cameraParameters() const { return cameraParams; }
+    virtual ~IPnpAlgorithm() = default;
+
+  protected:
+    CameraParameters cameraParams;
 };
 
 using IOrbFeatureDetector = IFeatureDetector<RgbFrame, std::uint8_t, 32>;

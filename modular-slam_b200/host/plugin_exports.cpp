@@ -12,6 +12,7 @@
 #include <memory>
 
 #include "orb_b200_plugin.hpp"
+#include "ransac_pnp_b200.hpp"
 
 #ifdef MSLAM_B200_WITH_BOOST
 #include <boost/dll/alias.hpp>
@@ -38,6 +39,8 @@ std::unique_ptr<IOrbFeatureDetector> createDistributedOrbB200Detector()
 {
     return std::unique_ptr<IOrbFeatureDetector>(new DistributedOrbB200Detector());
 }
+
+std::unique_ptr<IRansacPnp> createRansacPnpB200(); // ransac_pnp_b200.cpp
 
 std::unique_ptr<IOrbMatcher> createOrbB200Matcher()
 {
@@ -291,3 +294,4 @@ MSLAM_B200_DLL_ALIAS(mslam::createOrbB200Detector, orbDetectorFactory)
 MSLAM_B200_DLL_ALIAS(mslam::createOrbB200Matcher, orbMatcherFactory)
 // the detector the reference's Viewer wires in (viewer.cpp:183), as a second alias of the same interface
 MSLAM_B200_DLL_ALIAS(mslam::createDistributedOrbB200Detector, distributedOrbDetectorFactory)
+MSLAM_B200_DLL_ALIAS(mslam::createRansacPnpB200, ransacPnpFactory)

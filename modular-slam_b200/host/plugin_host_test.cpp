@@ -6,6 +6,8 @@
 //   plugin_host_test symbols <plugin.so>
 //   plugin_host_test config  <plugin_config.json>
 //   plugin_host_test provider <associations.txt> <out.bin> [batch size]   (RgbdFileB200Provider; batch > 0 => fetchBatch, pinned)
+//   plugin_host_test pnp     <plugin.so> <in.bin> <out.bin>   (RansacPnpB200 through the ransacPnpFactory alias; in.bin = i64 n,
+//                            fx fy cx cy f64, n x 3 f64 landmarks, n x 2 f64 pixels; called twice: solvePnp, then solvePnpBatch)
 //   plugin_host_test run     <plugin.so> <frame0.raw> <frame1.raw> <W> <H> <out.bin> [detector alias]
 #include <dlfcn.h>
 
@@ -16,6 +18,7 @@
 #include <string>
 
 #include "orb_b200_plugin.hpp"
+#include "ransac_pnp_b200.hpp"
 #include "rgbd_file_b200_provider.hpp"
 
 template <typename BlockType>
@@ -117,17 +120,74 @@ int main(int argc, char** argv)
         std::fprintf(stderr, "dlopen: %s\n", dlerror());
         return 3;
     }
+    if(!std::strcmp(argv[1], "pnp") && argc >= 5)
+    {
+        auto* makePnp = loadFactoryMethod<mslam::IRansacPnp>(lib, "ransacPnpFactory");
+        if(!makePnp)
+            return 4;
+        std::vector<std::uint8_t> raw;
+        if(!readFile(argv[3], &raw) || raw.size() < 40)
+            return 5;
+        long long n = 0;
+        std::memcpy(&n, raw.data(), 8);
+        const double* d = reinterpret_cast<const double*>(raw.data() + 8);
+        if(raw.size() < 40 + (size_t)n * 40)
+            return 5;
+        try
+        {
+            std::shared_ptr<mslam::IRansacPnp> pnp = makePnp();
+            mslam::CameraParameters cam{};
+            cam.focal.x() = d[0], cam.focal.y() = d[1], cam.principalPoint.x() = d[2], cam.principalPoint.y() = d[3];
+            cam.factor = 1.f;
+            pnp->setCameraParameters(cam); // rgbd_feature_frontend.cpp:345
+            std::vector<std::shared_ptr<mslam::Landmark<mslam::Vector3>>> landmarks;
+            std::vector<mslam::Vector2> points((size_t)n);
+            for(long long i = 0; i < n; ++i)
+            {
+                auto lm = std::make_shared<mslam::Landmark<mslam::Vector3>>();
+                lm->id = (mslam::Id)i;
+                lm->state = mslam::Vector3{{d[4 + 3 * i], d[4 + 3 * i + 1], d[4 + 3 * i + 2]}};
+                landmarks.push_back(lm);
+                points[(size_t)i].x() = d[4 + 3 * n + 2 * i];
+                points[(size_t)i].y() = d[4 + 3 * n + 2 * i + 1];
+            }
+            const auto result = pnp->solvePnp(landmarks, points); // :347
+            const auto none = pnp->solvePnp({}, {});
+            std::ofstream out(argv[4], std::ios::binary);
+            const std::uint64_t hdr[2] = {result ? 1u : 0u, none ? 1u : 0u};
+            out.write(reinterpret_cast<const char*>(hdr), sizeof(hdr));
+            if(result)
+            {
+                const double pose[7] = {result->pose.position[0], result->pose.position[1], result->pose.position[2],
+                                        result->pose.orientation.x(), result->pose.orientation.y(), result->pose.orientation.z(),
+                                        result->pose.orientation.w()};
+                out.write(reinterpret_cast<const char*>(pose), sizeof(pose));
+                for(size_t i = 0; i < result->inliers.size(); ++i)
+                    out.put(result->inliers[i] ? 1 : 0);
+                std::printf("pnp inliers %zu / %zu\n", result->inliers.count(), landmarks.size()); // :75
+            }
+            else
+                std::printf("Didnt find pnp solution\n");
+        }
+        catch(const std::exception& e)
+        {
+            std::fprintf(stderr, "plugin failed: %s\n", e.what());
+            return 6;
+        }
+        return 0;
+    }
     const char* detectorAlias = (argc >= 9 && !std::strcmp(argv[1], "run")) ? argv[8] : "orbDetectorFactory";
     auto* makeDetector = loadFactoryMethod<mslam::IOrbFeatureDetector>(lib, detectorAlias);
     auto* makeMatcher = loadFactoryMethod<mslam::IOrbMatcher>(lib, "orbMatcherFactory");
-    if(!makeDetector || !makeMatcher || !loadFactoryMethod<mslam::IOrbFeatureDetector>(lib, "distributedOrbDetectorFactory"))
+    if(!makeDetector || !makeMatcher || !loadFactoryMethod<mslam::IOrbFeatureDetector>(lib, "distributedOrbDetectorFactory") ||
+       !loadFactoryMethod<mslam::IRansacPnp>(lib, "ransacPnpFactory"))
     {
         std::fprintf(stderr, "factory aliases missing\n");
         return 4;
     }
     if(!std::strcmp(argv[1], "symbols"))
     {
-        std::printf("aliases ok: orbDetectorFactory orbMatcherFactory distributedOrbDetectorFactory\n");
+        std::printf("aliases ok: orbDetectorFactory orbMatcherFactory distributedOrbDetectorFactory ransacPnpFactory\n");
         return 0;
     }
     if(std::strcmp(argv[1], "run") || argc < 8)

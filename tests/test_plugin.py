@@ -25,7 +25,7 @@ def test_factory_aliases_load_like_boost_dll_import_alias(built):
     out = subprocess.run([built, "symbols", PLUGIN], capture_output=True, text=True)
     assert out.returncode == 0, out.stderr
     assert "orbDetectorFactory" in out.stdout and "orbMatcherFactory" in out.stdout
-    assert "distributedOrbDetectorFactory" in out.stdout
+    assert "distributedOrbDetectorFactory" in out.stdout and "ransacPnpFactory" in out.stdout
     # the aliases live in section "boostdll", as BOOST_DLL_ALIAS puts them (boost/dll/alias.hpp; test/dummy.cpp:11)
     sec = subprocess.run(["readelf", "-S", "-W", PLUGIN], capture_output=True, text=True).stdout
     assert "boostdll" in sec
@@ -114,3 +114,35 @@ def test_distributed_detector_through_the_plugin(built, oracle, bundled, tmp_pat
     fi, ti, _ = oracle.match_ratio(k0["descriptor"], k1["descriptor"])
     assert nm == len(fi) > 100
     assert (m["fromIndex"].astype(np.int64) == fi).all() and (m["toIndex"].astype(np.int64) == ti).all()
+
+
+@pytest.mark.gpu
+def test_ransac_pnp_through_the_plugin(built, tmp_path):
+    """OpenCvRansacPnp's replacement through its factory alias, called the way RgbdFeatureFrontend::track does
+    (setCameraParameters, solvePnp; rgbd_feature_frontend.cpp:345-361), against the cv2.solvePnPRansac golden"""
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "pnp.npz"))
+    synth = graft.load_package().synth
+    i = 6  # 693 correspondences, 40 % outliers
+    X, x = g[f"obj{i}"].astype(np.float64), g[f"img{i}"].astype(np.float64)
+    inp, outp = tmp_path / "pnp_in.bin", tmp_path / "pnp_out.bin"
+    with open(inp, "wb") as f:
+        f.write(np.int64(len(X)).tobytes())
+        f.write(np.array(synth.TUM_K, np.float64).tobytes())
+        f.write(X.tobytes())
+        f.write(x.tobytes())
+    out = subprocess.run([built, "pnp", PLUGIN, str(inp), str(outp)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    raw = outp.read_bytes()
+    found, none = np.frombuffer(raw[:16], np.uint64)
+    assert found == 1 and none == 0
+    pose = np.frombuffer(raw, np.float64, 7, 16)
+    inl = np.frombuffer(raw, np.uint8, len(X), 16 + 56)
+    assert (inl == g[f"inl{i}"]).all() and f"pnp inliers {inl.sum()} / {len(X)}" in out.stdout
+    # the reference's conversion of cv2's (rvec, tvec): orientation = AngleAxis(rvec)^-1, position = -(orientation * tvec)
+    from oracle import pnp_oracle as PO
+    R = PO.rodrigues_exp(g[f"rvec{i}"])
+    qx, qy, qz, qw = pose[3:]
+    Rq = np.array([[1 - 2 * (qy * qy + qz * qz), 2 * (qx * qy - qw * qz), 2 * (qx * qz + qw * qy)],
+                   [2 * (qx * qy + qw * qz), 1 - 2 * (qx * qx + qz * qz), 2 * (qy * qz - qw * qx)],
+                   [2 * (qx * qz - qw * qy), 2 * (qy * qz + qw * qx), 1 - 2 * (qx * qx + qy * qy)]])
+    assert np.abs(Rq - R.T).max() < 1e-6 and np.abs(pose[:3] + R.T @ g[f"tvec{i}"]).max() < 1e-6
