@@ -134,6 +134,9 @@ def run_reference(args, rank, world):
     """--impl reference: the CPU path alone (oracle port: the reference itself cannot be compiled in this image)"""
     if rank != 0:
         return
+    if args.workload == "pnp":
+        import bench_pnp
+        return bench_pnp.run_reference(args)
     pkg = graft.load_package()
     from oracle import oracle as O
     if args.workload == "c5":
@@ -211,6 +214,9 @@ def main():
     if args.workload == "dist":
         import bench_dist
         return bench_dist.main(args, rank, world, local)
+    if args.workload == "pnp":
+        import bench_pnp
+        return bench_pnp.main(args, rank, world, local)
 
     import torch
     import torch.distributed as dist

@@ -10,8 +10,8 @@
 //   phase 1  thread h < iterations: 4 distinct indices from a counter-based hash, Grunert's P3P on the first three
 //            (quartic in v = s3 / s1 from polynomial products, Ferrari roots + 2 Newton steps), triangle alignment
 //            -> (R, t) per real root, the 4th point picks the root;                          float64 throughout
-//   phase 2  warp per hypothesis, lanes over the points: squared reprojection error <= thr^2 (the test of
-//            PnPRansacCallback::computeError + findInliers), warp-shuffle count;
+//   phase 2  inlier counts: squared reprojection error <= thr^2 (the test of PnPRansacCallback::computeError +
+//            findInliers, evaluated without the division); a warp takes two hypotheses x 256 points at a time;
 //   phase 3  best = most inliers, lowest h on ties, >= 5 inliers (cv: goodCount > modelPoints - 1); inlier mask written;
 //   phase 4  Levenberg-Marquardt over the inliers from the best hypothesis: block-reduced 6x6 normal equations, thread 0
 //            solves (Gaussian elimination, partial pivoting), up to 8 damping retries per iteration, to convergence;
@@ -26,7 +26,7 @@ namespace mslam_b200
 {
 namespace
 {
-constexpr int PNP_THREADS = 256;
+constexpr int PNP_THREADS = 512;
 constexpr int PNP_MAX_HYP = 256;
 
 __device__ __forceinline__ unsigned lowbias32(unsigned x)
@@ -185,6 +185,16 @@ __device__ __forceinline__ double err2(const double* R, const double* t, V3 X, d
     return du * du + dv * dv;
 }
 
+// the inlier test |proj(X) - (u0, v0)|^2 <= thr2 without the division: with c = R X + t,
+//   (fx c.x + (cx - u0) c.z)^2 + (fy c.y + (cy - v0) c.z)^2 <= thr2 c.z^2          (both sides multiplied by c.z^2 > 0)
+// c.z == 0 (where the projection is infinite) is never an inlier.  oracle/pnp_oracle.py::inlier_mask is the same sequence.
+__device__ __forceinline__ bool is_inlier(const double* R, const double* t, V3 X, double u0, double v0, const Cam& K, double thr2)
+{
+    const V3 c = transform(R, t, X);
+    const double a = K.fx * c.x + (K.cx - u0) * c.z, b = K.fy * c.y + (K.cy - v0) * c.z;
+    return c.z != 0.0 && a * a + b * b <= thr2 * (c.z * c.z);
+}
+
 // one hypothesis from points idx[0..3]; false if the sample yields no pose
 __device__ bool p3p_hypothesis(const float* __restrict__ obj, const float* __restrict__ img, const int* idx, const Cam& K,
                                Pose& best)
@@ -334,7 +344,7 @@ __device__ void quat_from_R(const double* R, double* q)
 
 // block-wide sum of NV doubles per thread; result in s_red[0..NV) (valid for all threads after the call)
 template <int NV>
-__device__ void block_sum(double* v, double* s_part /* [8][NV] */, double* s_red /* [NV] */)
+__device__ void block_sum(double* v, double* s_part /* [PNP_THREADS / 32][NV] */, double* s_red /* [NV] */)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -367,7 +377,7 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
 {
     __shared__ Pose s_hyp[PNP_MAX_HYP];
     __shared__ int s_cnt[PNP_MAX_HYP];
-    __shared__ double s_part[8 * 28], s_red[28];
+    __shared__ double s_part[(PNP_THREADS / 32) * 28], s_red[28];
     __shared__ Pose s_cur, s_new;
     __shared__ int s_best, s_flag;
     __shared__ double s_dx[6];
@@ -416,18 +426,39 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
     }
     __syncthreads();
 
-    // ---- phase 2: inlier counts, warp per hypothesis ----
-    for(int h = warp; h < iterations; h += PNP_THREADS / 32)
+    // ---- phase 2: inlier counts ----
+    // work item = (pair of hypotheses, chunk of 256 points): a warp loads each point of the chunk once (32 lanes x 8 points)
+    // and tests it against both poses held in registers; counts are accumulated with one shared-memory atomic per item
     {
-        if(s_cnt[h] < 0)
-            continue;
-        const Pose& p = s_hyp[h];
-        int c = 0;
-        for(int i = lane; i < n; i += 32)
-            c += err2(p.R, p.t, load_obj(obj, i), (double)__ldg(img + 2 * i), (double)__ldg(img + 2 * i + 1), K) <= thr2;
-        c = __reduce_add_sync(0xffffffffu, c);
-        if(lane == 0)
-            s_cnt[h] = c;
+        constexpr int CHUNK = 256;
+        const int n_pairs = (iterations + 1) >> 1, n_chunks = (n + CHUNK - 1) / CHUNK;
+        for(int item = warp; item < n_pairs * n_chunks; item += PNP_THREADS / 32)
+        {
+            const int pr = item / n_chunks, ch = item - pr * n_chunks;
+            const int h0 = 2 * pr, h1 = h0 + 1;
+            const bool ok0 = s_cnt[h0] >= 0, ok1 = h1 < iterations && s_cnt[h1] >= 0;
+            if(!ok0 && !ok1)
+                continue;
+            const Pose p0 = s_hyp[ok0 ? h0 : h1], p1 = s_hyp[ok1 ? h1 : h0];
+            int c0 = 0, c1 = 0;
+            const int i_end = min(n, (ch + 1) * CHUNK);
+            for(int i = ch * CHUNK + lane; i < i_end; i += 32)
+            {
+                const V3 X = load_obj(obj, i);
+                const double u0 = (double)__ldg(img + 2 * i), v0 = (double)__ldg(img + 2 * i + 1);
+                c0 += is_inlier(p0.R, p0.t, X, u0, v0, K, thr2);
+                c1 += is_inlier(p1.R, p1.t, X, u0, v0, K, thr2);
+            }
+            c0 = __reduce_add_sync(0xffffffffu, c0);
+            c1 = __reduce_add_sync(0xffffffffu, c1);
+            if(lane == 0)
+            {
+                if(ok0 && c0)
+                    atomicAdd(&s_cnt[h0], c0);
+                if(ok1 && c1)
+                    atomicAdd(&s_cnt[h1], c1);
+            }
+        }
     }
     __syncthreads();
 
@@ -468,7 +499,7 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
     }
     // inlier mask of the best hypothesis (kept in registers as well: point i = tid + 256 k)
     for(int i = tid; i < n; i += PNP_THREADS)
-        mask[i] = err2(s_cur.R, s_cur.t, load_obj(obj, i), (double)__ldg(img + 2 * i), (double)__ldg(img + 2 * i + 1), K) <= thr2;
+        mask[i] = is_inlier(s_cur.R, s_cur.t, load_obj(obj, i), (double)__ldg(img + 2 * i), (double)__ldg(img + 2 * i + 1), K, thr2);
     __syncthreads(); // mask[] is re-read below by the threads that wrote it (same thread, same index): no fence needed
 
     // ---- phase 4: Levenberg-Marquardt over the inliers ----

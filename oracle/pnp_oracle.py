@@ -18,7 +18,8 @@ and a different random stream, so parity with OpenCV is by tolerance, not by bit
     (quartic in v = s3 / s1 built by polynomial products, closed-form roots + 2 Newton steps), each real solution turned
     into (R, t) by aligning the two point triangles, the 4th point picks the solution;
   * score = number of points with squared reprojection error <= thr^2 (same test as PnPRansacCallback::computeError +
-    findInliers), best = most inliers, lowest h on ties, at least 5 inliers required (cv: goodCount > modelPoints - 1);
+    findInliers, written without the division: both sides times z^2), best = most inliers, lowest h on ties, at least
+    5 inliers required (cv: goodCount > modelPoints - 1);
   * Levenberg-Marquardt over the inliers of the best hypothesis, started from it, in float64, to convergence;
   * outputs: rvec = log(R) (Rodrigues vector), tvec, inlier mask of the best hypothesis.
 
@@ -193,6 +194,16 @@ def project_err2(R, t, X, x, fx, fy, cx, cy):
     return du * du + dv * dv
 
 
+def inlier_mask(R, t, X, x, fx, fy, cx, cy, thr2):
+    """|proj(X) - x|^2 <= thr2, both sides multiplied by z^2 (no division; z == 0 is never an inlier) -- the same operation
+    sequence as is_inlier() in csrc/pnp_kernels.cu"""
+    Xc = X @ R.T + t
+    z = Xc[:, 2]
+    a = fx * Xc[:, 0] + (cx - x[:, 0]) * z
+    b = fy * Xc[:, 1] + (cy - x[:, 1]) * z
+    return (z != 0.0) & (a * a + b * b <= thr2 * (z * z))
+
+
 def rodrigues_exp(w):
     th = math.sqrt(float(w @ w))
     K = np.array([[0.0, -w[2], w[1]], [w[2], 0.0, -w[0]], [-w[1], w[0], 0.0]])
@@ -297,14 +308,13 @@ def solve_pnp_ransac(obj, img, fx, fy, cx, cy, iters=100, reproj=5.0, seed=0, fr
                 pick, pick_e = (R, t), e
         if pick is None:
             continue
-        e2 = project_err2(pick[0], pick[1], X, x, fx, fy, cx, cy)
-        cnt = int((e2 <= thr2).sum())
+        cnt = int(inlier_mask(pick[0], pick[1], X, x, fx, fy, cx, cy, thr2).sum())
         if cnt > best[0]:
             best = (cnt, h, pick[0], pick[1])
     if best[0] < need:
         return fail
     _, h, R, t = best
-    mask = (project_err2(R, t, X, x, fx, fy, cx, cy) <= thr2).astype(np.uint8)
+    mask = inlier_mask(R, t, X, x, fx, fy, cx, cy, thr2).astype(np.uint8)
     sel = mask.astype(bool)
     R, t = refine(R, t, X[sel], x[sel], fx, fy, cx, cy, refine_iters)
     return True, rodrigues_log(R), t.copy(), mask, h, R, t
