@@ -342,6 +342,85 @@ __device__ void quat_from_R(const double* R, double* q)
         q[0] = -q[0], q[1] = -q[1], q[2] = -q[2], q[3] = -q[3];
 }
 
+// (H + lam diag(H) + 1e-12 I) dx = -g for the 6x6 normal equations of one Levenberg-Marquardt trial: Gaussian elimination
+// with partial pivoting on one thread.  Every index is a compile-time constant (the row exchange is a predicated swap
+// against each candidate row), so the 6x7 system lives in registers -- the same elimination with run-time indices sat
+// in local memory and made this serial step 40 % of the kernel's stall samples (profiles/r1_v12_pnp_source_lines.txt).
+// hg = 21 upper-triangle entries of H row by row, then the 6 of g.  false: a zero / non-finite pivot.
+__device__ __forceinline__ bool solve6_damped(const double* hg, double lam, double* dx)
+{
+    double A[6][7];
+    {
+        int k = 0;
+#pragma unroll
+        for(int r = 0; r < 6; ++r)
+#pragma unroll
+            for(int c = r; c < 6; ++c)
+            {
+                A[r][c] = hg[k];
+                A[c][r] = hg[k];
+                ++k;
+            }
+    }
+#pragma unroll
+    for(int r = 0; r < 6; ++r)
+    {
+        A[r][r] += lam * A[r][r] + 1e-12;
+        A[r][6] = -hg[21 + r];
+    }
+    bool ok = true;
+#pragma unroll
+    for(int col = 0; col < 6; ++col)
+    {
+        int piv = col;
+        double best = fabs(A[col][col]);
+#pragma unroll
+        for(int r = col + 1; r < 6; ++r)
+        {
+            const double v = fabs(A[r][col]);
+            if(v > best)
+                best = v, piv = r;
+        }
+#pragma unroll
+        for(int r = col + 1; r < 6; ++r)
+            if(piv == r)
+            {
+#pragma unroll
+                for(int k = col; k < 7; ++k)
+                {
+                    const double tmp = A[col][k];
+                    A[col][k] = A[r][k];
+                    A[r][k] = tmp;
+                }
+            }
+        ok = ok && A[col][col] != 0.0 && isfinite(A[col][col]);
+#pragma unroll
+        for(int r = col + 1; r < 6; ++r)
+        {
+            const double m = A[r][col] / A[col][col];
+#pragma unroll
+            for(int k = col + 1; k < 7; ++k)
+                A[r][k] -= m * A[col][k];
+        }
+    }
+    if(!ok)
+        return false;
+    double x[6];
+#pragma unroll
+    for(int r = 5; r >= 0; --r)
+    {
+        double v = A[r][6];
+#pragma unroll
+        for(int k = r + 1; k < 6; ++k)
+            v -= A[r][k] * x[k];
+        x[r] = v / A[r][r];
+    }
+#pragma unroll
+    for(int r = 0; r < 6; ++r)
+        dx[r] = x[r];
+    return true;
+}
+
 // block-wide sum of NV doubles per thread; result in s_red[0..NV) (valid for all threads after the call)
 template <int NV>
 __device__ void block_sum(double* v, double* s_part /* [PNP_THREADS / 32][NV] */, double* s_red /* [NV] */)
@@ -380,7 +459,7 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
     __shared__ double s_part[(PNP_THREADS / 32) * 28], s_red[28];
     __shared__ Pose s_cur, s_new;
     __shared__ int s_best, s_flag;
-    __shared__ double s_dx[6];
+    __shared__ double s_dx[6], s_H[28];
 
     const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(max(counts[f], 0), cap);
@@ -542,80 +621,22 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
             for(int r = 0; r < 6; ++r)
                 acc[21 + r] += Ju[r] * ru + Jv[r] * rv;
         }
-        block_sum<27>(acc, s_part, s_red);
-        double H[36], g[6];
-        {
-            int k = 0;
-            for(int r = 0; r < 6; ++r)
-                for(int cc = r; cc < 6; ++cc)
-                {
-                    H[6 * r + cc] = s_red[k];
-                    H[6 * cc + r] = s_red[k];
-                    ++k;
-                }
-            for(int r = 0; r < 6; ++r)
-                g[r] = s_red[21 + r];
-        }
-        __syncthreads();
+        block_sum<27>(acc, s_part, s_H); // s_H stays valid through the trials below (cost_of reduces into s_red)
         bool improved = false;
         double step = 0.0, drop = 0.0;
         for(int tr = 0; tr < 8; ++tr)
         {
             if(tid == 0)
             {
-                double A[36], b[6];
-                for(int k = 0; k < 36; ++k)
-                    A[k] = H[k];
-                for(int k = 0; k < 6; ++k)
-                {
-                    A[7 * k] += lam * H[7 * k] + 1e-12;
-                    b[k] = -g[k];
-                }
-                bool ok = true;
-                for(int col = 0; col < 6 && ok; ++col)
-                {
-                    int piv = col;
-                    for(int r = col + 1; r < 6; ++r)
-                        if(fabs(A[6 * r + col]) > fabs(A[6 * piv + col]))
-                            piv = r;
-                    if(A[6 * piv + col] == 0.0 || !isfinite(A[6 * piv + col]))
-                    {
-                        ok = false;
-                        break;
-                    }
-                    if(piv != col)
-                    {
-                        for(int k = 0; k < 6; ++k)
-                        {
-                            const double tmp = A[6 * col + k];
-                            A[6 * col + k] = A[6 * piv + k];
-                            A[6 * piv + k] = tmp;
-                        }
-                        const double tmp = b[col];
-                        b[col] = b[piv];
-                        b[piv] = tmp;
-                    }
-                    for(int r = col + 1; r < 6; ++r)
-                    {
-                        const double m = A[6 * r + col] / A[6 * col + col];
-                        for(int k = col; k < 6; ++k)
-                            A[6 * r + k] -= m * A[6 * col + k];
-                        b[r] -= m * b[col];
-                    }
-                }
+                const bool ok = solve6_damped(s_H, lam, s_dx);
                 if(ok)
                 {
-                    for(int r = 5; r >= 0; --r)
-                    {
-                        double x = b[r];
-                        for(int k = r + 1; k < 6; ++k)
-                            x -= A[6 * r + k] * s_dx[k];
-                        s_dx[r] = x / A[6 * r + r];
-                    }
                     double dR[9];
                     rodrigues_exp(s_dx, dR);
+#pragma unroll
                     for(int r = 0; r < 3; ++r)
                     {
+#pragma unroll
                         for(int c = 0; c < 3; ++c)
                             s_new.R[3 * r + c] = dR[3 * r] * s_cur.R[c] + dR[3 * r + 1] * s_cur.R[3 + c] + dR[3 * r + 2] * s_cur.R[6 + c];
                         s_new.t[r] = dR[3 * r] * s_cur.t[0] + dR[3 * r + 1] * s_cur.t[1] + dR[3 * r + 2] * s_cur.t[2] + s_dx[3 + r];
