@@ -22,6 +22,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <type_traits>
+
 namespace mslam_b200
 {
 namespace
@@ -343,82 +345,71 @@ __device__ void quat_from_R(const double* R, double* q)
 }
 
 // (H + lam diag(H) + 1e-12 I) dx = -g for the 6x6 normal equations of one Levenberg-Marquardt trial: Gaussian elimination
-// with partial pivoting on one thread.  Every index is a compile-time constant (the row exchange is a predicated swap
-// against each candidate row), so the 6x7 system lives in registers -- the same elimination with run-time indices sat
-// in local memory and made this serial step 40 % of the kernel's stall samples (profiles/r1_v12_pnp_source_lines.txt).
-// hg = 21 upper-triangle entries of H row by row, then the 6 of g.  false: a zero / non-finite pivot.
-__device__ __forceinline__ bool solve6_damped(const double* hg, double lam, double* dx)
+// with partial pivoting, run by one whole warp.  Lane r < 6 keeps row r of [A | b] in 7 registers; rows are never
+// exchanged -- the pivot of column c is the largest |A[r][c]| among the rows not used yet (lowest row on ties), its
+// row is broadcast with shuffles, and the back substitution visits the pivot lanes in reverse order.  The same
+// elimination on one thread needs 42 doubles: with run-time indices it sat in local memory and was 40 % of the kernel's
+// stall samples, fully unrolled it still spilled under the 128-register cap of a 512-thread CTA (27 % of the samples;
+// profiles/r1_v12_pnp_source_lines.txt).
+// hg = 21 upper-triangle entries of H row by row, then the 6 of g.  All 32 lanes must call; the result is uniform.
+// false: a zero / infinite pivot (a NaN elsewhere propagates into dx and the trial's cost, which rejects the trial too).
+__device__ __forceinline__ bool solve6_damped_warp(const double* hg, double lam, double (&x)[6])
 {
-    double A[6][7];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, r = lane < 6 ? lane : 5;
+    double a[7];
+#pragma unroll
+    for(int c = 0; c < 6; ++c)
     {
-        int k = 0;
-#pragma unroll
-        for(int r = 0; r < 6; ++r)
-#pragma unroll
-            for(int c = r; c < 6; ++c)
-            {
-                A[r][c] = hg[k];
-                A[c][r] = hg[k];
-                ++k;
-            }
+        const int lo = min(r, c), hi = max(r, c);
+        a[c] = hg[6 * lo - lo * (lo - 1) / 2 + hi - lo];
+        if(c == r)
+            a[c] += lam * a[c] + 1e-12;
     }
-#pragma unroll
-    for(int r = 0; r < 6; ++r)
-    {
-        A[r][r] += lam * A[r][r] + 1e-12;
-        A[r][6] = -hg[21 + r];
-    }
-    bool ok = true;
+    a[6] = -hg[21 + r];
+    bool ok = true, used = lane >= 6;
+    int order[6];
 #pragma unroll
     for(int col = 0; col < 6; ++col)
     {
-        int piv = col;
-        double best = fabs(A[col][col]);
+        double v = used ? -1.0 : fabs(a[col]);
+        int piv = lane;
 #pragma unroll
-        for(int r = col + 1; r < 6; ++r)
+        for(int o = 4; o > 0; o >>= 1)
         {
-            const double v = fabs(A[r][col]);
-            if(v > best)
-                best = v, piv = r;
+            const double ov = __shfl_xor_sync(full, v, o);
+            const int op = __shfl_xor_sync(full, piv, o);
+            if(ov > v || (ov == v && op < piv))
+                v = ov, piv = op;
         }
+        v = __shfl_sync(full, v, 0);
+        piv = __shfl_sync(full, piv, 0);
+        order[col] = piv;
+        ok = ok && v > 0.0 && v < INFINITY;
+        double prow[7];
 #pragma unroll
-        for(int r = col + 1; r < 6; ++r)
-            if(piv == r)
-            {
-#pragma unroll
-                for(int k = col; k < 7; ++k)
-                {
-                    const double tmp = A[col][k];
-                    A[col][k] = A[r][k];
-                    A[r][k] = tmp;
-                }
-            }
-        ok = ok && A[col][col] != 0.0 && isfinite(A[col][col]);
-#pragma unroll
-        for(int r = col + 1; r < 6; ++r)
+        for(int k = col; k < 7; ++k)
+            prow[k] = __shfl_sync(full, a[k], piv);
+        if(lane == piv)
+            used = true;
+        if(!used)
         {
-            const double m = A[r][col] / A[col][col];
+            const double m = a[col] / prow[col];
 #pragma unroll
             for(int k = col + 1; k < 7; ++k)
-                A[r][k] -= m * A[col][k];
+                a[k] -= m * prow[k];
         }
     }
-    if(!ok)
-        return false;
-    double x[6];
 #pragma unroll
-    for(int r = 5; r >= 0; --r)
+    for(int col = 5; col >= 0; --col)
     {
-        double v = A[r][6];
+        double v = a[6];
 #pragma unroll
-        for(int k = r + 1; k < 6; ++k)
-            v -= A[r][k] * x[k];
-        x[r] = v / A[r][r];
+        for(int k = col + 1; k < 6; ++k)
+            v -= a[k] * x[k];
+        x[col] = __shfl_sync(full, v / a[col], order[col]);
     }
-#pragma unroll
-    for(int r = 0; r < 6; ++r)
-        dx[r] = x[r];
-    return true;
+    return ok;
 }
 
 // block-wide sum of NV doubles per thread; result in s_red[0..NV) (valid for all threads after the call)
@@ -457,9 +448,11 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
     __shared__ Pose s_hyp[PNP_MAX_HYP];
     __shared__ int s_cnt[PNP_MAX_HYP];
     __shared__ double s_part[(PNP_THREADS / 32) * 28], s_red[28];
-    __shared__ Pose s_cur, s_new;
-    __shared__ int s_best, s_flag;
-    __shared__ double s_dx[6], s_H[28];
+    __shared__ Pose s_cur;
+    __shared__ int s_best;
+    __shared__ double s_H[28], s_tdx[7][6], s_tlam[7];
+    __shared__ Pose s_try[7];
+    __shared__ int s_tok[7];
 
     const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(max(counts[f], 0), cap);
@@ -624,53 +617,89 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
         block_sum<27>(acc, s_part, s_H); // s_H stays valid through the trials below (cost_of reduces into s_red)
         bool improved = false;
         double step = 0.0, drop = 0.0;
-        for(int tr = 0; tr < 8; ++tr)
-        {
-            if(tid == 0)
+        // The up-to-8 trials of an iteration differ only in the damping (lam, 10 lam, 100 lam, ...) and the first one that
+        // does not raise the cost is taken.  Trial 0 is accepted in every iteration but the last, where all eight are
+        // rejected (the fit has converged): it runs alone; trials 1..7 then run TOGETHER -- warp w solves trial w + 1,
+        // one pass over the inliers yields the seven costs -- and the first acceptable one in trial order is taken, so the
+        // outcome is that of the sequential loop (oracle/pnp_oracle.py::refine) in two rounds instead of eight.
+        auto run_trials = [&](auto nt_c) {
+            constexpr int NT = decltype(nt_c)::value;
+            if(warp < NT)
             {
-                const bool ok = solve6_damped(s_H, lam, s_dx);
-                if(ok)
+                double lk = lam; // damping of this warp's trial: every earlier trial multiplied it by 10
+                for(int k = 0; k < warp; ++k)
+                    lk *= 10.0;
+                double dx[6];
+                const bool ok = solve6_damped_warp(s_H, lk, dx);
+                if(lane == 0)
                 {
-                    double dR[9];
-                    rodrigues_exp(s_dx, dR);
+                    s_tok[warp] = ok;
+                    s_tlam[warp] = lk;
 #pragma unroll
-                    for(int r = 0; r < 3; ++r)
+                    for(int k = 0; k < 6; ++k)
+                        s_tdx[warp][k] = dx[k];
+                    Pose pn = s_cur;
+                    if(ok)
                     {
+                        double dR[9];
+                        rodrigues_exp(dx, dR);
 #pragma unroll
-                        for(int c = 0; c < 3; ++c)
-                            s_new.R[3 * r + c] = dR[3 * r] * s_cur.R[c] + dR[3 * r + 1] * s_cur.R[3 + c] + dR[3 * r + 2] * s_cur.R[6 + c];
-                        s_new.t[r] = dR[3 * r] * s_cur.t[0] + dR[3 * r + 1] * s_cur.t[1] + dR[3 * r + 2] * s_cur.t[2] + s_dx[3 + r];
+                        for(int r = 0; r < 3; ++r)
+                        {
+#pragma unroll
+                            for(int c = 0; c < 3; ++c)
+                                pn.R[3 * r + c] = dR[3 * r] * s_cur.R[c] + dR[3 * r + 1] * s_cur.R[3 + c] + dR[3 * r + 2] * s_cur.R[6 + c];
+                            pn.t[r] = dR[3 * r] * s_cur.t[0] + dR[3 * r + 1] * s_cur.t[1] + dR[3 * r + 2] * s_cur.t[2] + dx[3 + r];
+                        }
                     }
+                    s_try[warp] = pn;
                 }
-                s_flag = ok;
             }
             __syncthreads();
-            const bool ok = s_flag != 0;
-            if(!ok)
-            {
-                lam *= 10.0;
-                __syncthreads();
-                continue;
-            }
-            const double cn = cost_of(s_new);
-            if(isfinite(cn) && cn <= cost)
+            double c[NT];
+#pragma unroll
+            for(int k = 0; k < NT; ++k)
+                c[k] = 0.0;
+            for(int i = tid; i < n; i += PNP_THREADS)
+                if(mask[i])
+                {
+                    const V3 X = load_obj(obj, i);
+                    const double u0 = (double)__ldg(img + 2 * i), v0 = (double)__ldg(img + 2 * i + 1);
+#pragma unroll
+                    for(int k = 0; k < NT; ++k)
+                        c[k] += err2(s_try[k].R, s_try[k].t, X, u0, v0, K);
+                }
+            block_sum<NT>(c, s_part, s_red);
+            int pick = -1;
+            double cn = 0.0;
+#pragma unroll
+            for(int k = NT - 1; k >= 0; --k)
+                if(s_tok[k] && isfinite(s_red[k]) && s_red[k] <= cost)
+                    pick = k, cn = s_red[k];
+            if(pick >= 0)
             {
                 step = 0.0;
                 for(int k = 0; k < 6; ++k)
-                    step = fmax(step, fabs(s_dx[k]));
+                    step = fmax(step, fabs(s_tdx[pick][k]));
                 drop = cost - cn;
                 cost = cn;
-                lam = fmax(lam * 0.1, 1e-12);
+                lam = fmax(s_tlam[pick] * 0.1, 1e-12);
                 improved = true;
-                __syncthreads();
-                if(tid == 0)
-                    s_cur = s_new;
-                __syncthreads();
-                break;
             }
-            lam *= 10.0;
+            else
+                for(int k = 0; k < NT; ++k)
+                    lam *= 10.0;
             __syncthreads();
-        }
+            if(pick >= 0)
+            {
+                if(tid == 0)
+                    s_cur = s_try[pick];
+                __syncthreads();
+            }
+        };
+        run_trials(std::integral_constant<int, 1>());
+        if(!improved)
+            run_trials(std::integral_constant<int, 7>());
         if(!improved || step < 1e-13 || drop <= 1e-15 * fmax(cost, 1e-300))
         {
             ++it;
