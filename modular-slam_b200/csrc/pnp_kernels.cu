@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <cooperative_groups.h>
 #include <type_traits>
 
 namespace mslam_b200
@@ -30,6 +31,7 @@ namespace
 {
 constexpr int PNP_THREADS = 512;
 constexpr int PNP_MAX_HYP = 256;
+constexpr int PNP_CLUSTER = 2; // CTAs per frame: they share the inlier counting (phase 2), rank 0 carries on alone
 
 __device__ __forceinline__ unsigned lowbias32(unsigned x)
 {
@@ -439,7 +441,7 @@ __device__ void block_sum(double* v, double* s_part /* [PNP_THREADS / 32][NV] */
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restrict__ obj_all, const float* __restrict__ img_all,
+__global__ void __cluster_dims__(PNP_CLUSTER, 1, 1) __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restrict__ obj_all, const float* __restrict__ img_all,
                                                            const int* __restrict__ counts, int cap, int frame0, Cam K,
                                                            int iterations, double thr2, unsigned seed, int refine_iters,
                                                            double* __restrict__ out_rt, double* __restrict__ out_pose,
@@ -454,7 +456,10 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
     __shared__ Pose s_try[7];
     __shared__ int s_tok[7];
 
-    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int crank = (int)cluster.block_rank();
+    const int f = blockIdx.x / PNP_CLUSTER, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(max(counts[f], 0), cap);
     const float* obj = obj_all + (long long)f * cap * 3;
     const float* img = img_all + (long long)f * cap * 2;
@@ -463,10 +468,13 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
     double* rt = out_rt + 6 * f;
     double* pose = out_pose + 7 * f;
 
-    for(int i = tid; i < cap; i += PNP_THREADS)
-        mask[i] = 0;
+    if(crank == 0)
+        for(int i = tid; i < cap; i += PNP_THREADS)
+            mask[i] = 0;
     if(n < 4)
     {
+        if(crank != 0)
+            return;
         if(tid == 0)
             info[0] = 0, info[1] = 0, info[2] = -1, info[3] = 0;
         if(tid < 6)
@@ -496,7 +504,9 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
             s_hyp[h] = p;
         s_cnt[h] = ok ? 0 : -1;
     }
-    __syncthreads();
+    // every CTA of the frame's cluster has built the same hypotheses (one thread each: splitting them would not shorten
+    // the phase); nobody may add into rank 0's counts before rank 0 has initialised them
+    cluster.sync();
 
     // ---- phase 2: inlier counts ----
     // work item = (pair of hypotheses, chunk of 256 points): a warp loads each point of the chunk once (32 lanes x 8 points)
@@ -504,7 +514,7 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
     {
         constexpr int CHUNK = 256;
         const int n_pairs = (iterations + 1) >> 1, n_chunks = (n + CHUNK - 1) / CHUNK;
-        for(int item = warp; item < n_pairs * n_chunks; item += PNP_THREADS / 32)
+        for(int item = warp + (PNP_THREADS / 32) * crank; item < n_pairs * n_chunks; item += PNP_CLUSTER * (PNP_THREADS / 32))
         {
             const int pr = item / n_chunks, ch = item - pr * n_chunks;
             const int h0 = 2 * pr, h1 = h0 + 1;
@@ -533,6 +543,17 @@ __global__ void __launch_bounds__(PNP_THREADS) k_pnp_ransac(const float* __restr
         }
     }
     __syncthreads();
+    if(crank != 0)
+    {
+        // hand this CTA's share of the counts to rank 0 through distributed shared memory, then leave
+        int* cnt0 = cluster.map_shared_rank(s_cnt, 0);
+        for(int h = tid; h < iterations; h += PNP_THREADS)
+            if(s_cnt[h] > 0)
+                atomicAdd(cnt0 + h, s_cnt[h]);
+    }
+    cluster.sync();
+    if(crank != 0)
+        return;
 
     // ---- phase 3: best hypothesis (most inliers, lowest index) ----
     if(warp == 0)
@@ -727,7 +748,7 @@ void launch_pnp_ransac(cudaStream_t st, const float* obj, const float* img, cons
                        double* out_rt, double* out_pose, uint8_t* out_mask, int* out_info, long long* launches)
 {
     const Cam K{fx, fy, cx, cy};
-    k_pnp_ransac<<<n_frames, PNP_THREADS, 0, st>>>(obj, img, counts, cap, frame0, K, iterations, thr2, seed, refine_iters, out_rt,
+    k_pnp_ransac<<<PNP_CLUSTER * n_frames, PNP_THREADS, 0, st>>>(obj, img, counts, cap, frame0, K, iterations, thr2, seed, refine_iters, out_rt,
                                                    out_pose, out_mask, out_info);
     if(launches)
         ++*launches;
