@@ -419,15 +419,41 @@ template <int NV>
 __device__ void block_sum(double* v, double* s_part /* [PNP_THREADS / 32][NV] */, double* s_red /* [NV] */)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for(int k = 0; k < NV; ++k)
+    if constexpr(NV > 8)
     {
-        double x = v[k];
+        // many values: halve the value count at every butterfly stage (a lane keeps the half of the values its bit selects
+        // and sends the other half), 31 shuffles for up to 32 values instead of 5 per value; lane k ends with total k
+        static_assert(NV <= 32, "block_sum: at most 32 values");
+        double w[32];
+#pragma unroll
+        for(int k = 0; k < 32; ++k)
+            w[k] = k < NV ? v[k] : 0.0;
 #pragma unroll
         for(int o = 16; o > 0; o >>= 1)
-            x += __shfl_xor_sync(0xffffffffu, x, o);
-        if(lane == 0)
-            s_part[warp * NV + k] = x;
+        {
+            const bool hi = (lane & o) != 0;
+#pragma unroll
+            for(int k = 0; k < o; ++k)
+            {
+                const double send = hi ? w[k] : w[k + o], keep = hi ? w[k + o] : w[k];
+                w[k] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+            }
+        }
+        if(lane < NV)
+            s_part[warp * NV + lane] = w[0];
+    }
+    else
+    {
+#pragma unroll
+        for(int k = 0; k < NV; ++k)
+        {
+            double x = v[k];
+#pragma unroll
+            for(int o = 16; o > 0; o >>= 1)
+                x += __shfl_xor_sync(0xffffffffu, x, o);
+            if(lane == 0)
+                s_part[warp * NV + k] = x;
+        }
     }
     __syncthreads();
     if(threadIdx.x < NV)
