@@ -9,7 +9,7 @@ Workload: 64 independent sequences per GPU; a *step* = one solvePnp per sequence
   value        mslam_b200_pnp_ransac_batch_dev, inputs resident in HBM, CUDA events on the context's stream
   e2e          mslam_b200_pnp_ransac_batch: host correspondences in, host poses / inlier masks out, copies inside the timed region
   roofline     the kernel against HBM with its algorithmic bytes (20 B per correspondence in, cap + 124 B per frame out); it is
-               a float64-arithmetic / latency-bound kernel (one CTA per frame), so the fraction is small by construction
+               a float64-arithmetic / latency-bound kernel (a two-CTA cluster per frame), so the fraction is small by construction
   cpu_baseline cv2.solvePnPRansac (the very call the reference makes, OpenCV's python binding) over all host cores on a bounded
                sample; the numpy oracle (oracle/pnp_oracle.py) when cv2 is not importable
 """
@@ -194,8 +194,14 @@ def main(args, rank, world, local):
             "roofline": {"bound": "hbm", "kernel": "k_pnp_ransac", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / pk["hbm_gbs"], "traffic": None,
                          "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({pk_src})", "algorithmic_bytes_per_launch": alg_bytes,
-                         "note": "one CTA per frame; float64 P3P / reprojection arithmetic and the serial Levenberg-Marquardt tail bound "
-                                 "it, not bytes (DESIGN 4e): 64 CTAs on 148 SMs"}}
+                         "note": "a two-CTA cluster per frame; float64 P3P / reprojection arithmetic and the serial Levenberg-Marquardt tail bound "
+                                 "it, not bytes (DESIGN 4e): 128 CTAs on 148 SMs"}}
+    try:
+        tr = json.load(open(os.path.join(graft.ROOT, "profiles", "ncu_traffic_pnp.json")))
+        line["roofline"]["traffic"] = tr["bytes_per_launch"]
+        line["roofline"]["traffic_source"] = "profiles/ncu_traffic_pnp.json (ncu --set full, dram read + write bytes per launch)"
+    except (OSError, KeyError, ValueError):
+        pass
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         v, kind, sample = cpu_run(pkg, batches[0][0], batches[0][1], batches[0][2], threads, args.cpu_seconds)

@@ -5,16 +5,19 @@
 // the consumer of the matcher's output in RgbdFeatureFrontend::track (rgbd_feature_frontend.cpp:345-361).
 //
 // cv::solvePnPRansac is a sequential loop (draw 5 points from cv::RNG, EPnP, count inliers, adapt the iteration count)
-// followed by a Levenberg-Marquardt fit over the inliers.  Here all hypotheses of a frame are evaluated at once by one
-// CTA, and a launch covers a whole batch of frames (one CTA per frame):
+// followed by a Levenberg-Marquardt fit over the inliers.  Here all hypotheses of a frame are evaluated at once, and a
+// launch covers a whole batch of frames: a cluster of two 512-thread CTAs per frame, of which rank 1 only helps with
+// the inlier counting (phase 2) and leaves:
 //   phase 1  thread h < iterations: 4 distinct indices from a counter-based hash, Grunert's P3P on the first three
 //            (quartic in v = s3 / s1 from polynomial products, Ferrari roots + 2 Newton steps), triangle alignment
-//            -> (R, t) per real root, the 4th point picks the root;                          float64 throughout
+//            -> (R, t) per real root, the 4th point picks the root;  float64 throughout; both CTAs build all of them
 //   phase 2  inlier counts: squared reprojection error <= thr^2 (the test of PnPRansacCallback::computeError +
-//            findInliers, evaluated without the division); a warp takes two hypotheses x 256 points at a time;
+//            findInliers, evaluated without the division); a warp takes two hypotheses x 256 points at a time, the
+//            items alternate between the two CTAs, rank 1 adds its counts into rank 0's through distributed shared memory;
 //   phase 3  best = most inliers, lowest h on ties, >= 5 inliers (cv: goodCount > modelPoints - 1); inlier mask written;
-//   phase 4  Levenberg-Marquardt over the inliers from the best hypothesis: block-reduced 6x6 normal equations, thread 0
-//            solves (Gaussian elimination, partial pivoting), up to 8 damping retries per iteration, to convergence;
+//   phase 4  Levenberg-Marquardt over the inliers from the best hypothesis: block-reduced 6x6 normal equations (halving
+//            butterfly over the 27 sums), solved by one warp (row per lane, partial pivoting); the first damping trial of
+//            an iteration runs alone, trials 2..8 together (warp per damping, one pass for the seven costs);
 //   phase 5  rvec = log(R), tvec, and the reference's sensor pose (orientation = R^-1 as a quaternion,
 //            position = -(R^-1 t), cv_ransac_pnp.cpp:65-77).
 // Every step mirrors oracle/pnp_oracle.py (same draws, same formulas); parity with OpenCV itself is by tolerance
