@@ -84,6 +84,8 @@ struct mslam_b200_ctx
     unsigned *d_key0 = nullptr, *d_key1 = nullptr, *d_key0b = nullptr, *d_key1b = nullptr;
     unsigned *d_part0 = nullptr, *d_part1 = nullptr; // per-slice partial top-2 keys of the small-batch kNN
     uint8_t *d_xa = nullptr, *d_xb = nullptr;        // +1/-1 int8 expansions of the two descriptor sets (knn_mma.cu)
+    uint8_t* d_pnp = nullptr;                        // scratch of the host back-projection / RANSAC-PnP entry points, grow-only
+    size_t pnp_bytes = 0;
     uint8_t *d_xdb = nullptr, *d_xqf = nullptr;      // ... of a chunk of keyframes / of the query frames (DB scoring), lazily sized
     size_t xdb_bytes = 0, xqf_bytes = 0;
     int knn_mma = 1;                                 // MSLAM_KNN_MMA: 0 scalar kernel only, 1 by problem size, 2 always
@@ -420,7 +422,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb, ctx->d_xdb, ctx->d_xqf};
+                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb, ctx->d_xdb, ctx->d_xqf, ctx->d_pnp};
     for(void* p : dev)
         if(p)
             cudaFree(p);
@@ -1507,6 +1509,22 @@ int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queries, const int* 
     return rc;
 }
 
+// grow-only device scratch of the host convenience entry points (back-projection, RANSAC PnP): a per-call cudaMalloc /
+// cudaFree pair costs more than the kernels they feed
+static int host_scratch(mslam_b200_ctx* ctx, size_t bytes, uint8_t** out)
+{
+    if(ctx->pnp_bytes < bytes)
+    {
+        MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_pnp);
+        ctx->d_pnp = nullptr, ctx->pnp_bytes = 0;
+        MSLAM_CUDA_OK(cudaMalloc(&ctx->d_pnp, bytes));
+        ctx->pnp_bytes = bytes;
+    }
+    *out = ctx->d_pnp;
+    return MSLAM_B200_OK;
+}
+
 // ---- RGB-D association ------------------------------------------------------------------------------
 static bool camera_ok(const mslam_b200_camera* cam)
 {
@@ -1538,19 +1556,20 @@ int mslam_b200_backproject(mslam_b200_ctx* ctx, const double* xy, int n, int str
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     cudaStream_t st = ctx->stream;
-    double *d_xy = nullptr, *d_xyz = nullptr;
-    uint16_t* d_depth = nullptr;
-    uint8_t* d_valid = nullptr;
     const size_t depth_bytes = (size_t)width * height * sizeof(uint16_t);
-    int rc = MSLAM_B200_OK;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t o_xyz = up((size_t)n * 16), o_depth = o_xyz + up((size_t)n * 24), o_valid = o_depth + up(depth_bytes);
+    uint8_t* d = nullptr;
+    int rc = host_scratch(ctx, o_valid + up((size_t)n), &d);
+    if(rc != MSLAM_B200_OK)
+        return rc;
+    double *d_xy = (double*)d, *d_xyz = (double*)(d + o_xyz);
+    uint16_t* d_depth = (uint16_t*)(d + o_depth);
+    uint8_t* d_valid = d + o_valid;
     cudaError_t e;
 #define BPQ(expr)                                                                                                      \
     if(rc == MSLAM_B200_OK && (e = (expr)) != cudaSuccess)                                                             \
     rc = ctx_fail(ctx, e, #expr)
-    BPQ(cudaMalloc(&d_xy, (size_t)n * 16));
-    BPQ(cudaMalloc(&d_xyz, (size_t)n * 24));
-    BPQ(cudaMalloc(&d_depth, depth_bytes));
-    BPQ(cudaMalloc(&d_valid, (size_t)n));
     BPQ(cudaMemcpy2DAsync(d_xy, 16, xy, (size_t)stride_bytes, 16, (size_t)n, cudaMemcpyHostToDevice, st));
     BPQ(cudaMemcpyAsync(d_depth, depth, depth_bytes, cudaMemcpyHostToDevice, st));
     if(rc == MSLAM_B200_OK)
@@ -1560,10 +1579,6 @@ int mslam_b200_backproject(mslam_b200_ctx* ctx, const double* xy, int n, int str
     BPQ(cudaMemcpyAsync(out_valid, d_valid, (size_t)n, cudaMemcpyDeviceToHost, st));
     BPQ(cudaStreamSynchronize(st));
 #undef BPQ
-    void* frees[] = {d_xy, d_xyz, d_depth, d_valid};
-    for(void* p : frees)
-        if(p)
-            cudaFree(p);
     return rc;
 }
 
@@ -1620,12 +1635,13 @@ int mslam_b200_pnp_ransac_batch(mslam_b200_ctx* ctx, const float* obj, const flo
     const size_t o_img = up(b_obj), o_cnt = o_img + up(b_img), o_rt = o_cnt + up(b_cnt), o_pose = o_rt + up(b_rt),
                  o_inl = o_pose + up(b_pose), o_info = o_inl + up(b_inl), total = o_info + up(b_info);
     uint8_t* d = nullptr;
-    int rc = MSLAM_B200_OK;
+    int rc = host_scratch(ctx, total, &d);
+    if(rc != MSLAM_B200_OK)
+        return rc;
     cudaError_t e;
 #define PNQ(expr)                                                                                                      \
     if(rc == MSLAM_B200_OK && (e = (expr)) != cudaSuccess)                                                             \
     rc = ctx_fail(ctx, e, #expr)
-    PNQ(cudaMalloc(&d, total));
     PNQ(cudaMemcpyAsync(d, obj, b_obj, cudaMemcpyHostToDevice, st));
     PNQ(cudaMemcpyAsync(d + o_img, img, b_img, cudaMemcpyHostToDevice, st));
     PNQ(cudaMemcpyAsync(d + o_cnt, counts, b_cnt, cudaMemcpyHostToDevice, st));
@@ -1639,8 +1655,6 @@ int mslam_b200_pnp_ransac_batch(mslam_b200_ctx* ctx, const float* obj, const flo
     PNQ(cudaMemcpyAsync(info, d + o_info, b_info, cudaMemcpyDeviceToHost, st));
     PNQ(cudaStreamSynchronize(st));
 #undef PNQ
-    if(d)
-        cudaFree(d);
     return rc;
 }
 
