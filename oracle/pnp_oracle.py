@@ -275,7 +275,8 @@ def refine(R, t, X, x, fx, fy, cx, cy, iters=30):
                 improved = True
                 break
             lam *= 10.0
-        if not improved or step < 1e-13 or drop <= 1e-15 * max(cost, 1e-300):
+        # quadratic convergence: a step below 1e-10 is the last one that matters in float64 (same rule as the kernel)
+        if not improved or step < 1e-10 or drop <= 1e-15 * max(cost, 1e-300):
             break
     return R, t
 
