@@ -191,6 +191,21 @@ def run_reference_db(args, pkg, O):
                       "gpu_launches": 0}))
 
 
+def natural_frames(W, H, n_seq, n_batches=4):
+    """informational second input set: the reference's bundled TUM frame (tests/golden/tum/rgb/0000.png, a fixture of this
+    repo) as n_seq sequences -- sequence s is the frame rolled by (5 s, 3 s) pixels, frame t of it by a further (t, 0) --
+    so that the step also gets timed on natural-image statistics.  None if the file or an image decoder is missing."""
+    path = os.path.join(ROOT, "tests", "golden", "tum", "rgb", "0000.png")
+    try:
+        import cv2
+        img = cv2.imread(path, cv2.IMREAD_COLOR)
+    except ImportError:
+        return None
+    if img is None or img.shape != (H, W, 3):
+        return None
+    return [np.stack([np.roll(img, (3 * s, 5 * s + t), axis=(0, 1)) for s in range(n_seq)]) for t in range(n_batches)]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -303,6 +318,35 @@ def main():
     stage = ctx.stage_times()
     ctx.enable_stage_timing(False)
     ctx.set_flags(pkg.FLAG_SERIAL if args.serial else 0)
+    # ---- informational: the same K device-timed steps on natural-image input (rank 0, c2 only).  The synthetic textures
+    # have ~12x the FAST corner density of a real TUM frame (20.7 % of the pixels against 1.7 %), which is what the
+    # scoring / non-maximum-suppression phases of k_fast scale with ----------------------------------------------------
+    natural = None
+    nat = natural_frames(W, H, B) if (rank == 0 and args.workload == "c2") else None
+    if nat is not None:
+        d_nat = [torch.from_numpy(f).cuda() for f in nat]
+        ctx.detect_batch_dev(d_nat[0], B, W, H, d_kp[cur ^ 1], d_desc[cur ^ 1], cap, d_cnt[cur ^ 1])
+        def step_nat(t, c):
+            ctx.detect_batch_dev(d_nat[t], B, W, H, d_kp[c], d_desc[c], cap, d_cnt[c])
+            ctx.match_batch_dev(mode, d_desc[c], d_cnt[c], d_desc[c ^ 1], d_cnt[c ^ 1], B, cap, d_ma, d_mb, d_md, d_mn)
+        for i in range(args.warmup):
+            step_nat(1 + i % (len(d_nat) - 1), cur)
+            cur ^= 1
+        torch.cuda.synchronize()
+        e4, e5 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e4.record(stream)
+        for i in range(args.steps):
+            step_nat(1 + i % (len(d_nat) - 1), cur)
+            cur ^= 1
+        e5.record(stream)
+        torch.cuda.synchronize()
+        ms_nat = e4.elapsed_time(e5)
+        natural = {"frames_per_s": B * args.steps / (ms_nat * 1e-3), "ms_per_step": ms_nat / args.steps,
+                   "keypoints_per_batch_check": int(d_cnt[cur ^ 1].sum().item()), "matches_per_batch_check": int(d_mn.sum().item()),
+                   "input": "tests/golden/tum/rgb/0000.png (the reference's bundled TUM frame) rolled per sequence and per frame; one "
+                            "GPU, device-resident, same step as `value`; informational -- `value` stays on the synthetic stream "
+                            "BASELINE.json names, whose textures have ~12x this frame's FAST corner density"}
+        del d_nat
     if world > 1:
         tt = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -491,7 +535,8 @@ def main():
                             "every step's frames cross PCIe and its keypoints / descriptors / matches come back inside the timed region)",
                     "synchronous": {"value": e2e_sync_value, "ms_per_step": e2e_sync_ms / args.steps,
                                     "note": "one blocking detect_batch + one blocking match_batch per step"}},
-            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "natural_frames": natural}
     print(json.dumps(line))
     ctx.close()
     if world > 1:
