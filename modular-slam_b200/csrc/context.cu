@@ -86,6 +86,8 @@ struct mslam_b200_ctx
     uint8_t *d_xa = nullptr, *d_xb = nullptr;        // +1/-1 int8 expansions of the two descriptor sets (knn_mma.cu)
     uint8_t* d_pnp = nullptr;                        // scratch of the host back-projection / RANSAC-PnP entry points, grow-only
     size_t pnp_bytes = 0;
+    uint8_t* h_pnp = nullptr;                        // pinned staging of the RANSAC-PnP outputs, grow-only
+    size_t h_pnp_bytes = 0;
     uint8_t *d_xdb = nullptr, *d_xqf = nullptr;      // ... of a chunk of keyframes / of the query frames (DB scoring), lazily sized
     size_t xdb_bytes = 0, xqf_bytes = 0;
     int knn_mma = 1;                                 // MSLAM_KNN_MMA: 0 scalar kernel only, 1 by problem size, 2 always
@@ -426,7 +428,7 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     for(void* p : dev)
         if(p)
             cudaFree(p);
-    void* host[] = {ctx->h_counts, ctx->h_err, ctx->h_out_a, ctx->h_out_b, ctx->h_out_d, ctx->h_nout, ctx->h_n2};
+    void* host[] = {ctx->h_counts, ctx->h_err, ctx->h_out_a, ctx->h_out_b, ctx->h_out_d, ctx->h_nout, ctx->h_n2, ctx->h_pnp};
     for(void* p : host)
         if(p)
             cudaFreeHost(p);
@@ -1649,12 +1651,29 @@ int mslam_b200_pnp_ransac_batch(mslam_b200_ctx* ctx, const float* obj, const flo
         rc = mslam_b200_pnp_ransac_batch_dev(ctx, (const float*)d, (const float*)(d + o_img), (const int*)(d + o_cnt), n_frames,
                                              cap, params, (double*)(d + o_rt), (double*)(d + o_pose), d + o_inl,
                                              (int*)(d + o_info));
-    PNQ(cudaMemcpyAsync(rvec_tvec, d + o_rt, b_rt, cudaMemcpyDeviceToHost, st));
-    PNQ(cudaMemcpyAsync(pose, d + o_pose, b_pose, cudaMemcpyDeviceToHost, st));
-    PNQ(cudaMemcpyAsync(inliers, d + o_inl, b_inl, cudaMemcpyDeviceToHost, st));
-    PNQ(cudaMemcpyAsync(info, d + o_info, b_info, cudaMemcpyDeviceToHost, st));
+    // the four outputs are adjacent in the scratch block: one device->host copy into a pinned staging block, then plain
+    // host copies (four small DMA transfers cost more than the 72 KB they move)
+    const size_t b_out = total - o_rt;
+    if(rc == MSLAM_B200_OK && ctx->h_pnp_bytes < b_out)
+    {
+        if(ctx->h_pnp)
+            cudaFreeHost(ctx->h_pnp);
+        ctx->h_pnp = nullptr, ctx->h_pnp_bytes = 0;
+        PNQ(cudaHostAlloc((void**)&ctx->h_pnp, b_out, cudaHostAllocDefault));
+        if(rc == MSLAM_B200_OK)
+            ctx->h_pnp_bytes = b_out;
+    }
+    PNQ(cudaMemcpyAsync(ctx->h_pnp, d + o_rt, b_out, cudaMemcpyDeviceToHost, st));
     PNQ(cudaStreamSynchronize(st));
 #undef PNQ
+    if(rc == MSLAM_B200_OK)
+    {
+        const uint8_t* h = ctx->h_pnp;
+        memcpy(rvec_tvec, h, b_rt);
+        memcpy(pose, h + (o_pose - o_rt), b_pose);
+        memcpy(inliers, h + (o_inl - o_rt), b_inl);
+        memcpy(info, h + (o_info - o_rt), b_info);
+    }
     return rc;
 }
 
