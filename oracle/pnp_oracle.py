@@ -232,15 +232,16 @@ def rodrigues_log(R):
     return r * (0.5 * th / s)
 
 
-def refine(R, t, X, x, fx, fy, cx, cy, iters=30):
-    """Levenberg-Marquardt on the reprojection error; update Xc' = exp(w) Xc + dt"""
+def refine(R, t, X, x, fx, fy, cx, cy, iters=30, trace=None):
+    """Levenberg-Marquardt on the reprojection error; update Xc' = exp(w) Xc + dt.
+    trace (a list) receives one (iteration, trial, accepted) tuple per damping trial."""
     def cost_of(R, t):
         e = project_err2(R, t, X, x, fx, fy, cx, cy)
         return float(e.sum())
 
     lam = 1e-3
     cost = cost_of(R, t)
-    for _ in range(iters):
+    for it in range(iters):
         Xc = X @ R.T + t
         iz = 1.0 / Xc[:, 2]
         px, py = Xc[:, 0] * iz, Xc[:, 1] * iz
@@ -266,6 +267,8 @@ def refine(R, t, X, x, fx, fy, cx, cy, iters=30):
             dR = rodrigues_exp(dx[:3])
             Rn, tn = dR @ R, dR @ t + dx[3:]
             cn = cost_of(Rn, tn)
+            if trace is not None:
+                trace.append((it, _try, bool(math.isfinite(cn) and cn <= cost)))
             if math.isfinite(cn) and cn <= cost:
                 R, t = Rn, tn
                 step = float(np.abs(dx).max())
@@ -281,7 +284,7 @@ def refine(R, t, X, x, fx, fy, cx, cy, iters=30):
     return R, t
 
 
-def solve_pnp_ransac(obj, img, fx, fy, cx, cy, iters=100, reproj=5.0, seed=0, frame=0, refine_iters=30):
+def solve_pnp_ransac(obj, img, fx, fy, cx, cy, iters=100, reproj=5.0, seed=0, frame=0, refine_iters=30, trace=None):
     """-> (ok, rvec [3], tvec [3], inlier mask [n] u8, best hypothesis index, R, t)"""
     X = np.asarray(obj, np.float32).astype(np.float64).reshape(-1, 3)  # cv_ransac_pnp.cpp:20-30 narrows to float
     x = np.asarray(img, np.float32).astype(np.float64).reshape(-1, 2)  # :32-41
@@ -317,5 +320,5 @@ def solve_pnp_ransac(obj, img, fx, fy, cx, cy, iters=100, reproj=5.0, seed=0, fr
     _, h, R, t = best
     mask = inlier_mask(R, t, X, x, fx, fy, cx, cy, thr2).astype(np.uint8)
     sel = mask.astype(bool)
-    R, t = refine(R, t, X[sel], x[sel], fx, fy, cx, cy, refine_iters)
+    R, t = refine(R, t, X[sel], x[sel], fx, fy, cx, cy, refine_iters, trace)
     return True, rodrigues_log(R), t.copy(), mask, h, R, t

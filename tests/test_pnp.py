@@ -204,3 +204,32 @@ def test_gpu_batch_is_order_independent_and_repeatable(pkg, golden):
             s = ctx.pnp_ransac_batch(obj[k:k + 1], img[k:k + 1], cnt[k:k + 1], pkg.pnp_params(fx, fy, cx, cy, seed=3, frame_base=k))
             for x, y in zip(a, s):
                 assert x[k].tobytes() == y[0].tobytes()
+
+
+@pytest.mark.gpu
+def test_gpu_damping_retries_match_oracle(pkg, PO):
+    """noisy small scenes where the first damping trial of an iteration is rejected: the kernel evaluates trials 2..8
+    together (warp per damping) and must take the one the oracle's sequential loop takes"""
+    fx, fy, cx, cy = pkg.synth.TUM_K
+    spec = [(0, 30, 0.2, 3.0), (0, 12, 0.0, 4.0), (0, 60, 0.4, 2.5), (1, 30, 0.2, 3.0), (1, 12, 0.0, 4.0), (1, 60, 0.4, 2.5)]
+    scenes = [pkg.synth.pnp_scene(s, n, o, noise) for s, n, o, noise in spec]
+    cap = 64
+    obj, img = np.zeros((len(spec), cap, 3), np.float32), np.zeros((len(spec), cap, 2), np.float32)
+    cnt = np.array([n for _, n, _, _ in spec], np.int32)
+    for k, sc in enumerate(scenes):
+        obj[k, :cnt[k]], img[k, :cnt[k]] = sc[0], sc[1]
+    with pkg.Context(max_width=64, max_height=64, max_batch=1, nfeatures=100) as ctx:
+        rt, pose, inl, info = ctx.pnp_ransac_batch(obj, img, cnt, pkg.pnp_params(fx, fy, cx, cy, seed=7))
+    retried = 0
+    for k, sc in enumerate(scenes):
+        trace = []
+        ok, r, t, mask, h, _, _ = PO.solve_pnp_ransac(sc[0], sc[1], fx, fy, cx, cy, seed=7, frame=k, trace=trace)
+        assert bool(info[k, 0]) == ok
+        if not ok:
+            continue
+        retried += any(tr > 0 for _, tr, _ in trace)
+        assert info[k, 2] == h and (inl[k, :cnt[k]] == mask).all()
+        # (the iteration count is not compared: these late trials are accepted or rejected on the last bits of the cost,
+        # where the kernel's reduction tree and numpy's summation order may differ; the pose is what must agree)
+        assert np.abs(rt[k, :3] - r).max() <= TOL_ORACLE and np.abs(rt[k, 3:] - t).max() <= TOL_ORACLE, k
+    assert retried >= 3, "the scenes no longer exercise the damping retries"
