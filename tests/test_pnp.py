@@ -233,3 +233,25 @@ def test_gpu_damping_retries_match_oracle(pkg, PO):
         # where the kernel's reduction tree and numpy's summation order may differ; the pose is what must agree)
         assert np.abs(rt[k, :3] - r).max() <= TOL_ORACLE and np.abs(rt[k, 3:] - t).max() <= TOL_ORACLE, k
     assert retried >= 3, "the scenes no longer exercise the damping retries"
+
+
+@pytest.mark.gpu
+def test_gpu_full_size_batch_is_position_independent(pkg):
+    """BASELINE-sized batch (64 frames x 1000 correspondences, 50 % outliers): every frame is solved, close to the generating
+    pose, and a frame's result does not depend on where it sits in a batch (frame k alone with frame_base = k gives the
+    same bytes) -- the size-independent property of a launch that maps one two-CTA cluster to each frame"""
+    fx, fy, cx, cy = pkg.synth.TUM_K
+    F, n = 64, 1000
+    scenes = [pkg.synth.pnp_scene(5000 + i, n, 0.5, 0.7) for i in range(F)]
+    obj, img = np.stack([s[0] for s in scenes]), np.stack([s[1] for s in scenes])
+    cnt = np.full(F, n, np.int32)
+    with pkg.Context(max_width=64, max_height=64, max_batch=1, nfeatures=100) as ctx:
+        rt, pose, inl, info = ctx.pnp_ransac_batch(obj, img, cnt, pkg.pnp_params(fx, fy, cx, cy, seed=3))
+        assert (info[:, 0] == 1).all() and (info[:, 1] > 0.4 * n).all() and (info[:, 1] == inl.sum(axis=1)).all()
+        for k, s in enumerate(scenes):
+            assert np.abs(rt[k, :3] - s[2]).max() < 5e-3 and np.abs(rt[k, 3:] - s[3]).max() < 2e-2, k
+        for k in (0, 5, 63):
+            rt1, pose1, inl1, info1 = ctx.pnp_ransac_batch(obj[k:k + 1], img[k:k + 1], cnt[k:k + 1],
+                                                           pkg.pnp_params(fx, fy, cx, cy, seed=3, frame_base=k))
+            assert rt1.tobytes() == rt[k:k + 1].tobytes() and pose1.tobytes() == pose[k:k + 1].tobytes()
+            assert (inl1 == inl[k:k + 1]).all() and (info1 == info[k:k + 1]).all()
