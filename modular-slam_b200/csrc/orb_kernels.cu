@@ -511,15 +511,24 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         // all of the thread's tile words are requested before the first one is stored: one exposed load latency per CTA
         constexpr int NLD = (FS_PH_MAX * FS_PWW + 255) / 256;
         unsigned v[NLD];
+        // word i = tid + 256 k of the tile is (row r, word c): 256 = 7 * 34 + 18, so a step of k moves 7 rows and 18 words
+        // (one division per thread instead of one per word); rows past the tile / the image and words past the row pitch
+        // read as 0
+        static_assert(256 / FS_PWW == 7 && 256 % FS_PWW == 18, "staging walk assumes 34-word rows");
+        int r = tid / FS_PWW, c = tid - r * FS_PWW;
+        const int rows_ok = min(PH, L.h - py0);                    // staged rows that exist in the image
+        const int words_ok = (L.pitch - px0 + 3) >> 2;             // gx < pitch  <=>  c < words_ok
+        const unsigned* gp = reinterpret_cast<const unsigned*>(img + (long long)(py0 + r) * L.pitch + px0) + c;
+        const int row_words = L.pitch >> 2;                        // pitch is a multiple of 64
 #pragma unroll
         for(int k = 0; k < NLD; ++k)
         {
-            const int i = tid + 256 * k;
-            const int r = i / FS_PWW, c = i - r * FS_PWW;
-            const int gy = py0 + r, gx = px0 + 4 * c;
             v[k] = 0;
-            if(i < PH * FS_PWW && gy < L.h && gx < L.pitch)
-                v[k] = __ldg(reinterpret_cast<const unsigned*>(img + (long long)gy * L.pitch + gx));
+            if(r < rows_ok && c < words_ok)
+                v[k] = __ldg(gp);
+            c += 18, r += 7, gp += 7 * row_words + 18;
+            if(c >= FS_PWW)
+                c -= FS_PWW, r += 1, gp += row_words - FS_PWW;
         }
 #pragma unroll
         for(int k = 0; k < NLD; ++k)
