@@ -659,9 +659,12 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
             if(sx >= 2 && sx < FS_SW - 2 && sy >= 1 && sy < SH - 1 && x >= edge && x < L.w - edge && y < L.h - edge)
             {
                 const uint8_t* s = &s_sc[sy][sx];
+                // all eight neighbours are requested before the first comparison (no short-circuit chain of dependent
+                // shared-memory loads); strict maximum <=> v > max of the neighbours
                 const int v = s[0];
-                keep = v > s[-1] && v > s[1] && v > s[-FS_SW - 1] && v > s[-FS_SW] && v > s[-FS_SW + 1] && v > s[FS_SW - 1] &&
-                       v > s[FS_SW] && v > s[FS_SW + 1];
+                const int n0 = s[-FS_SW - 1], n1 = s[-FS_SW], n2 = s[-FS_SW + 1], n3 = s[-1], n4 = s[1], n5 = s[FS_SW - 1],
+                          n6 = s[FS_SW], n7 = s[FS_SW + 1];
+                keep = v > max(max(max(n0, n1), max(n2, n3)), max(max(n4, n5), max(n6, n7)));
                 rec = ((unsigned)y << 20) | ((unsigned)x << 8) | (unsigned)v;
             }
         }
