@@ -1,0 +1,1 @@
+#include "../../../mslam_eigen_shim.hpp"

@@ -1,0 +1,1 @@
+#include "../mslam_cv_shim.hpp"
