@@ -101,7 +101,9 @@ MSLAM_B200_API int mslam_b200_create(const mslam_b200_config* cfg, mslam_b200_ct
 MSLAM_B200_API void mslam_b200_destroy(mslam_b200_ctx* ctx);
 MSLAM_B200_API int mslam_b200_set_stream(mslam_b200_ctx* ctx, void* cuda_stream);
 MSLAM_B200_API int mslam_b200_synchronize(mslam_b200_ctx* ctx);
-/* change mslam_b200_config::flags of a live context (synchronises first) */
+/* change mslam_b200_config::flags of a live context (synchronises first): the kernel choice of the matcher follows the new
+ * flags from the next call on (expansion buffers are allocated if the tensor-core kernel becomes selectable), captured
+ * single-frame kernel graphs are dropped.  KNN_SCALAR | KNN_TENSOR together is MSLAM_B200_E_INVALID. */
 MSLAM_B200_API int mslam_b200_set_flags(mslam_b200_ctx* ctx, int flags);
 /* text of the last CUDA error seen by this context ("" if none) */
 MSLAM_B200_API const char* mslam_b200_last_cuda_error(mslam_b200_ctx* ctx);
@@ -199,6 +201,46 @@ MSLAM_B200_API int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queri
                                        int n_query_frames, int q_cap, const uint8_t* db, const int* k_counts,
                                        int n_keyframes, int k_cap, int id_base, int k, int* out_score, int* out_id,
                                        int* out_all_scores /* may be NULL; [n_query_frames][n_keyframes] */);
+
+/* ---- sharded keyframe database (SURVEY 8(b) "_db_build / _db_query: sharded, takes ncclComm_t or rank/size"; 8(e)) ---------
+ * Keyframes are sharded by contiguous id range, one shard per rank (one process per GPU), each shard resident in its rank's
+ * HBM as a caller-owned device array [n_local][k_cap][32] + counts; every rank sees all query frames.  A query runs
+ *   score the shard -> local top-k -> ONE ncclAllGather of the [2][n_query_frames][k] (score, id) block -> k-way merge
+ * on the context's stream with no host synchronisation in between, and leaves the same global top-k -- bit-identical to the
+ * single-GPU answer, (score desc, keyframe id asc) -- on every rank.  NCCL is bound at run time (dlopen libnccl.so.2, so a
+ * process that already holds PyTorch's NCCL shares it); without it the attach calls fail with MSLAM_B200_E_CUDA for
+ * world > 1 -- there is no fallback.  world == 1 needs no NCCL and no attach. */
+#define MSLAM_B200_NCCL_ID_BYTES 128
+/* contiguous id range [k0, k1) of `rank`: the first n_keyframes % world ranks hold one keyframe more */
+MSLAM_B200_API void mslam_b200_db_shard_range(long long n_keyframes, int rank, int world, long long* k0, long long* k1);
+/* ncclGetUniqueId: rank 0 calls this and hands the 128 bytes to every rank by any means (MPI, a file, torch.distributed) */
+MSLAM_B200_API int mslam_b200_nccl_unique_id(void* out_id128);
+/* join the database's communicator: ncclCommInitRank(world, id, rank) on the context's device (collective over all ranks) */
+MSLAM_B200_API int mslam_b200_db_attach(mslam_b200_ctx* ctx, int rank, int world, const void* nccl_unique_id);
+/* ... or use a communicator the caller already has (an ncclComm_t; checked against rank / world; not destroyed by detach) */
+MSLAM_B200_API int mslam_b200_db_attach_comm(mslam_b200_ctx* ctx, void* nccl_comm, int rank, int world);
+MSLAM_B200_API int mslam_b200_db_detach(mslam_b200_ctx* ctx);
+MSLAM_B200_API int mslam_b200_db_shard_info(mslam_b200_ctx* ctx, int* rank, int* world);
+/* Device pointers, asynchronous.  n_local may be 0 (an empty shard still takes part in the collective).  Every rank must
+ * call with the same n_query_frames and k.  d_out_score / d_out_id: [n_query_frames][k], (-1, -1) pads when the whole
+ * database holds fewer than k keyframes. */
+MSLAM_B200_API int mslam_b200_db_query_sharded_dev(mslam_b200_ctx* ctx, const uint8_t* d_queries, const int* d_q_counts,
+                                                   int n_query_frames, int q_cap, const uint8_t* d_db_shard,
+                                                   const int* d_k_counts, int n_local, int k_cap, int id_base, int k,
+                                                   int* d_out_score, int* d_out_id);
+/* Host query frames in, host top-k out (synchronous); the shard arguments are still device pointers (resident). */
+MSLAM_B200_API int mslam_b200_db_query_sharded(mslam_b200_ctx* ctx, const uint8_t* queries, const int* q_counts,
+                                               int n_query_frames, int q_cap, const uint8_t* d_db_shard,
+                                               const int* d_k_counts, int n_local, int k_cap, int id_base, int k,
+                                               int* out_score, int* out_id);
+
+/* A shard owned by the context, for callers without device allocations of their own (the C++ class
+ * mslam::ShardedKeyframeDbB200): _load_shard uploads host descriptors [n_local][k_cap][32] + counts once (replacing any
+ * previous shard; n_local may be 0), _query_loaded runs mslam_b200_db_query_sharded against it. */
+MSLAM_B200_API int mslam_b200_db_load_shard(mslam_b200_ctx* ctx, const uint8_t* db, const int* k_counts, int n_local, int k_cap,
+                                            int id_base);
+MSLAM_B200_API int mslam_b200_db_query_loaded(mslam_b200_ctx* ctx, const uint8_t* queries, const int* q_counts,
+                                              int n_query_frames, int q_cap, int k, int* out_score, int* out_id);
 
 /* ---- RGB-D association: SURVEY 8(f) row f2 ------------------------------------------------------------------------ */
 /* Replaces pointsFromRgbdKeypoints / reconstructPoint (src/lib/modular_slam/rgbd_feature_frontend.cpp:101-138) with

@@ -5,7 +5,7 @@ adapter implementing the reference's IFeatureDetector / IFeatureMatcher).  This 
 harness over the same C ABI used by tests/ and bench.py.  Imported as `modular_slam_b200` through
 __graft_entry__.load_package() (the directory name carries a hyphen).
 """
-from .capi import (Context, Config, Camera, PnpParams, pnp_params, MslamB200Error, KP_DTYPE, LIB_PATH, library, default_config, pinned_empty,  # noqa: F401
+from .capi import (Context, Config, Camera, PnpParams, pnp_params, MslamB200Error, KP_DTYPE, LIB_PATH, library, default_config, pinned_empty, db_shard_range, nccl_unique_id, NCCL_ID_BYTES,  # noqa: F401
                    OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM, STAGE_PYRAMID, STAGE_BLURRED, STAGE_N_FAST,
                    STAGE_N_CUT1, STAGE_N_FINAL, FLAG_SERIAL, FLAG_KNN_SCALAR, FLAG_KNN_TENSOR, DistContext, DistConfig, dist_default_config,
                    DIST_PYRAMID, DIST_BLURRED, DIST_N_FAST, DIST_N_TREE, DIST_PASSES)

@@ -81,6 +81,7 @@ def library():
         lib.mslam_b200_destroy.restype = None
         lib.mslam_b200_default_config.restype = None
         lib.mslam_b200_pnp_default_params.restype = None
+        lib.mslam_b200_db_shard_range.restype = None
         _lib = lib
     return _lib
 
@@ -103,6 +104,27 @@ def _ptr(a):
     if hasattr(a, "data_ptr"):
         return C.c_void_p(a.data_ptr())
     raise TypeError(type(a))
+
+
+NCCL_ID_BYTES = 128
+
+
+def db_shard_range(n_keyframes, rank, world):
+    """contiguous id range [k0, k1) of `rank` (mslam_b200_db_shard_range): the first n % world ranks hold one keyframe more"""
+    if world < 1 or not (0 <= rank < world) or n_keyframes < 0:
+        raise ValueError("bad shard request")
+    k0, k1 = C.c_longlong(0), C.c_longlong(0)
+    library().mslam_b200_db_shard_range(C.c_longlong(n_keyframes), rank, world, C.byref(k0), C.byref(k1))
+    return k0.value, k1.value
+
+
+def nccl_unique_id():
+    """ncclGetUniqueId through the library (rank 0 calls it and distributes the bytes) -> bytes[128]"""
+    buf = (C.c_char * NCCL_ID_BYTES)()
+    rc = library().mslam_b200_nccl_unique_id(buf)
+    if rc:
+        raise MslamB200Error(rc, "mslam_b200_nccl_unique_id", "(is libnccl.so.2 loadable?)")
+    return bytes(buf.raw)
 
 
 def default_config(**kw):
@@ -378,6 +400,40 @@ class Context:
     def db_merge_topk_dev(self, d_scores, d_ids, n_lists, n_q, k, d_out_score, d_out_id):
         self._chk(library().mslam_b200_db_merge_topk_dev(self._h, _ptr(d_scores), _ptr(d_ids), n_lists, n_q, k,
                                                          _ptr(d_out_score), _ptr(d_out_id)), "db_merge_topk_dev")
+
+    # -- sharded keyframe database (one shard per rank; NCCL all-gather + merge inside the library) ---------------------------
+    def db_attach(self, rank, world, unique_id=None):
+        """join the database communicator (collective): unique_id = the 128 bytes rank 0 got from nccl_unique_id()"""
+        buf = (C.c_char * NCCL_ID_BYTES).from_buffer_copy(bytes(unique_id)) if unique_id is not None else None
+        self._chk(library().mslam_b200_db_attach(self._h, rank, world, buf), "db_attach")
+
+    def db_attach_comm(self, nccl_comm, rank, world):
+        self._chk(library().mslam_b200_db_attach_comm(self._h, C.c_void_p(nccl_comm), rank, world), "db_attach_comm")
+
+    def db_detach(self):
+        self._chk(library().mslam_b200_db_detach(self._h), "db_detach")
+
+    def db_shard_info(self):
+        r, w = C.c_int(0), C.c_int(0)
+        self._chk(library().mslam_b200_db_shard_info(self._h, C.byref(r), C.byref(w)), "db_shard_info")
+        return r.value, w.value
+
+    def db_query_sharded_dev(self, d_queries, d_q_counts, n_q, q_cap, d_db, d_k_counts, n_local, k_cap, id_base, k, d_out_score,
+                             d_out_id):
+        self._chk(library().mslam_b200_db_query_sharded_dev(self._h, _ptr(d_queries), _ptr(d_q_counts), n_q, q_cap, _ptr(d_db),
+                                                            _ptr(d_k_counts), n_local, k_cap, id_base, k, _ptr(d_out_score),
+                                                            _ptr(d_out_id)), "db_query_sharded_dev")
+
+    def db_query_sharded(self, queries, q_counts, d_db, d_k_counts, n_local, k_cap, id_base, k):
+        """host query frames [Q, cap, 32] -> host (scores [Q, k], ids [Q, k]); the shard arguments are device pointers"""
+        queries = np.ascontiguousarray(queries, np.uint8)
+        qc = np.ascontiguousarray(q_counts, np.int32)
+        Q, qcap, _ = queries.shape
+        os_ = np.zeros((Q, k), np.int32)
+        oi = np.zeros((Q, k), np.int32)
+        self._chk(library().mslam_b200_db_query_sharded(self._h, _ptr(queries), _ptr(qc), Q, qcap, _ptr(d_db), _ptr(d_k_counts),
+                                                        n_local, k_cap, id_base, k, _ptr(os_), _ptr(oi)), "db_query_sharded")
+        return os_, oi
 
     # -- RGB-D association (SURVEY 8(f) f2) -----------------------------------------------------------------------------
     def backproject(self, xy, depth, camera):

@@ -11,6 +11,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "nccl_dyn.h"
 
 using namespace mslam_b200;
 
@@ -91,6 +92,18 @@ struct mslam_b200_ctx
     uint8_t *d_xdb = nullptr, *d_xqf = nullptr;      // ... of a chunk of keyframes / of the query frames (DB scoring), lazily sized
     size_t xdb_bytes = 0, xqf_bytes = 0;
     int knn_mma = 1;                                 // MSLAM_KNN_MMA: 0 scalar kernel only, 1 by problem size, 2 always
+    int knn_mma_env = -1;                            // what MSLAM_KNN_MMA said at create (-1: unset)
+    // ---- sharded keyframe database (mslam_b200_db_attach* / _db_query_sharded_dev) ----
+    ncclComm_t db_comm = nullptr;
+    bool db_own_comm = false;
+    int db_rank = 0, db_world = 1;
+    int* d_dbs = nullptr;                            // grow-only: [Q][n_local] scores | local top-k [2][Q][k] | gathered [world][2][Q][k]
+    size_t dbs_bytes = 0;
+    uint8_t* d_dbq = nullptr;                        // device copy of the host entry point's query frames / outputs, grow-only
+    size_t dbq_bytes = 0;
+    uint8_t* d_shard = nullptr;                      // context-owned resident shard (mslam_b200_db_load_shard): descriptors | counts
+    size_t shard_bytes = 0;
+    int shard_n = 0, shard_cap = 0, shard_id_base = 0;
     int *d_out_a = nullptr, *d_out_b = nullptr, *d_out_d = nullptr, *d_nout = nullptr;
     int *h_out_a = nullptr, *h_out_b = nullptr, *h_out_d = nullptr, *h_nout = nullptr, *h_n2 = nullptr;
     // ---- copy engines of the host entry points (chunked H2D / compute / D2H pipeline) ----
@@ -421,6 +434,13 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     cudaSetDevice(ctx->cfg.device);
     if(ctx->stream)
         cudaStreamSynchronize(ctx->stream);
+    mslam_b200_db_detach(ctx);
+    if(ctx->d_dbs)
+        cudaFree(ctx->d_dbs);
+    if(ctx->d_dbq)
+        cudaFree(ctx->d_dbq);
+    if(ctx->d_shard)
+        cudaFree(ctx->d_shard);
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
@@ -470,6 +490,24 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     delete ctx;
 }
 
+// kernel choice of the matcher from cfg.flags (and MSLAM_KNN_MMA as read at create); allocates the +1/-1 expansion buffers the
+// tensor-core kernel needs the first time it becomes selectable
+static int apply_knn_flags(mslam_b200_ctx* ctx)
+{
+    ctx->knn_mma = ctx->knn_mma_env >= 0 ? ctx->knn_mma_env : 1;
+    if(ctx->cfg.flags & MSLAM_B200_FLAG_KNN_SCALAR)
+        ctx->knn_mma = 0;
+    if(ctx->cfg.flags & MSLAM_B200_FLAG_KNN_TENSOR)
+        ctx->knn_mma = 2;
+    if(ctx->knn_mma && !ctx->d_xa)
+    {
+        const size_t bytes = knn_mma_bytes(ctx->cfg.max_batch, ctx->desc_cap);
+        MSLAM_CUDA_OK(cudaMalloc(&ctx->d_xa, bytes));
+        MSLAM_CUDA_OK(cudaMalloc(&ctx->d_xb, bytes));
+    }
+    return MSLAM_B200_OK;
+}
+
 int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
 {
     if(!cfg_in || !out_ctx || cfg_in->struct_size != (int)sizeof(mslam_b200_config))
@@ -510,6 +548,9 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     cudaDeviceProp prop;
     CREATE_OK(cudaGetDeviceProperties(&prop, c.device));
     ctx->sm_count = prop.multiProcessorCount;
+    // dynamic shared-memory opt-ins are per device: set them for THIS context's device (a process may hold one context per GPU)
+    CREATE_OK(configure_match_kernels());
+    CREATE_OK(configure_mma_kernels());
     if(c.stream)
         ctx->stream = (cudaStream_t)c.stream;
     else
@@ -592,15 +633,14 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaMalloc(&ctx->d_part0, kKnnMaxSlices * B * dc * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_part1, kKnnMaxSlices * B * dc * sizeof(unsigned)));
     if(const char* e = getenv("MSLAM_KNN_MMA"))
-        ctx->knn_mma = atoi(e);
-    if(ctx->cfg.flags & MSLAM_B200_FLAG_KNN_SCALAR)
-        ctx->knn_mma = 0;
-    if(ctx->cfg.flags & MSLAM_B200_FLAG_KNN_TENSOR)
-        ctx->knn_mma = 2;
-    if(ctx->knn_mma)
+        ctx->knn_mma_env = atoi(e);
     {
-        CREATE_OK(cudaMalloc(&ctx->d_xa, knn_mma_bytes((int)B, (int)dc)));
-        CREATE_OK(cudaMalloc(&ctx->d_xb, knn_mma_bytes((int)B, (int)dc)));
+        const int rc__ = apply_knn_flags(ctx);
+        if(rc__ != MSLAM_B200_OK)
+        {
+            mslam_b200_destroy(ctx);
+            return rc__;
+        }
     }
     CREATE_OK(cudaMalloc(&ctx->d_out_a, B * dc * sizeof(int)));
     CREATE_OK(cudaMalloc(&ctx->d_out_b, B * dc * sizeof(int)));
@@ -648,9 +688,19 @@ int mslam_b200_set_flags(mslam_b200_ctx* ctx, int flags)
 {
     if(!ctx)
         return MSLAM_B200_E_INVALID;
+    if((flags & MSLAM_B200_FLAG_KNN_SCALAR) && (flags & MSLAM_B200_FLAG_KNN_TENSOR))
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     ctx->cfg.flags = flags;
-    return MSLAM_B200_OK;
+    // the single-frame kernel graphs were captured under the old flags (MSLAM_B200_FLAG_SERIAL changes the stream structure)
+    for(auto& g : ctx->graph1)
+    {
+        if(g.exec)
+            cudaGraphExecDestroy(g.exec);
+        g = mslam_b200_ctx::FrameGraph{};
+    }
+    return apply_knn_flags(ctx);
 }
 
 int mslam_b200_level_geometry(mslam_b200_ctx* ctx, int width, int height, int* w, int* h, float* scale, int* n_per_level)
@@ -1448,7 +1498,7 @@ int mslam_b200_db_topk_dev(mslam_b200_ctx* ctx, const int* d_scores, int n_query
     if(!ctx || !d_scores || !d_out_score || !d_out_id || n_query_frames < 1 || n_keyframes < 1 || k < 1 || id_base < 0)
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
-    launch_topk(ctx->stream, d_scores, nullptr, 1, n_keyframes, n_query_frames, id_base, k, d_out_score, d_out_id,
+    launch_topk(ctx->stream, d_scores, nullptr, 1, n_keyframes, 0, n_query_frames, id_base, k, d_out_score, d_out_id,
                 &ctx->launches);
     MSLAM_CUDA_OK(cudaGetLastError());
     return MSLAM_B200_OK;
@@ -1460,7 +1510,8 @@ int mslam_b200_db_merge_topk_dev(mslam_b200_ctx* ctx, const int* d_scores, const
     if(!ctx || !d_scores || !d_ids || !d_out_score || !d_out_id || n_lists < 1 || n_query_frames < 1 || k < 1)
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
-    launch_topk(ctx->stream, d_scores, d_ids, n_lists, k, n_query_frames, 0, k, d_out_score, d_out_id, &ctx->launches);
+    launch_topk(ctx->stream, d_scores, d_ids, n_lists, k, (long long)n_query_frames * k, n_query_frames, 0, k, d_out_score, d_out_id,
+                &ctx->launches);
     MSLAM_CUDA_OK(cudaGetLastError());
     return MSLAM_B200_OK;
 }
@@ -1509,6 +1560,246 @@ int mslam_b200_db_query(mslam_b200_ctx* ctx, const uint8_t* queries, const int* 
         if(p)
             cudaFree(p);
     return rc;
+}
+
+// ---- sharded keyframe database: one shard per rank, per-query top-k all-gathered over NCCL and merged on the device ------------
+void mslam_b200_db_shard_range(long long n_keyframes, int rank, int world, long long* k0, long long* k1)
+{
+    long long a = 0, b = 0;
+    if(world >= 1 && rank >= 0 && rank < world && n_keyframes >= 0)
+    {
+        const long long base = n_keyframes / world, extra = n_keyframes % world;
+        a = rank * base + std::min<long long>(rank, extra);
+        b = a + base + (rank < extra ? 1 : 0);
+    }
+    if(k0)
+        *k0 = a;
+    if(k1)
+        *k1 = b;
+}
+
+static int nccl_fail(mslam_b200_ctx* ctx, int r, const char* what)
+{
+    NcclApi& api = nccl_api();
+    snprintf(ctx->err, sizeof(ctx->err), "%s: NCCL error %d (%s)", what, r, api.GetErrorString ? api.GetErrorString(r) : "?");
+    return MSLAM_B200_E_CUDA;
+}
+
+int mslam_b200_nccl_unique_id(void* out_id128)
+{
+    if(!out_id128)
+        return MSLAM_B200_E_INVALID;
+    NcclApi& api = nccl_api();
+    if(!api.ok())
+        return MSLAM_B200_E_CUDA;
+    ncclUniqueId id;
+    if(api.GetUniqueId(&id) != 0)
+        return MSLAM_B200_E_CUDA;
+    memcpy(out_id128, &id, sizeof(id));
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_detach(mslam_b200_ctx* ctx)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    if(ctx->db_comm)
+    {
+        cudaSetDevice(ctx->cfg.device);
+        cudaStreamSynchronize(ctx->stream);
+        if(ctx->db_own_comm)
+            nccl_api().CommDestroy(ctx->db_comm);
+    }
+    ctx->db_comm = nullptr, ctx->db_own_comm = false, ctx->db_rank = 0, ctx->db_world = 1;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_attach(mslam_b200_ctx* ctx, int rank, int world, const void* nccl_unique_id)
+{
+    if(!ctx || world < 1 || rank < 0 || rank >= world || (world > 1 && !nccl_unique_id))
+        return MSLAM_B200_E_INVALID;
+    mslam_b200_db_detach(ctx);
+    if(world > 1)
+    {
+        NcclApi& api = nccl_api();
+        if(!api.ok())
+        {
+            snprintf(ctx->err, sizeof(ctx->err), "%s", api.why);
+            return MSLAM_B200_E_CUDA; // no fallback: a sharded database without its collective is not a database
+        }
+        MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+        ncclUniqueId id;
+        memcpy(&id, nccl_unique_id, sizeof(id));
+        const int r = api.CommInitRank(&ctx->db_comm, world, id, rank);
+        if(r != 0)
+        {
+            ctx->db_comm = nullptr;
+            return nccl_fail(ctx, r, "ncclCommInitRank");
+        }
+        ctx->db_own_comm = true;
+    }
+    ctx->db_rank = rank, ctx->db_world = world;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_attach_comm(mslam_b200_ctx* ctx, void* nccl_comm, int rank, int world)
+{
+    if(!ctx || world < 1 || rank < 0 || rank >= world || (world > 1 && !nccl_comm))
+        return MSLAM_B200_E_INVALID;
+    mslam_b200_db_detach(ctx);
+    if(world > 1)
+    {
+        NcclApi& api = nccl_api();
+        if(!api.ok())
+        {
+            snprintf(ctx->err, sizeof(ctx->err), "%s", api.why);
+            return MSLAM_B200_E_CUDA;
+        }
+        int n = 0, me = -1;
+        if(api.CommCount((ncclComm_t)nccl_comm, &n) != 0 || api.CommUserRank((ncclComm_t)nccl_comm, &me) != 0 || n != world || me != rank)
+            return MSLAM_B200_E_INVALID; // the communicator is not the (rank, world) the caller says
+        ctx->db_comm = (ncclComm_t)nccl_comm;
+    }
+    ctx->db_rank = rank, ctx->db_world = world;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_shard_info(mslam_b200_ctx* ctx, int* rank, int* world)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    if(rank)
+        *rank = ctx->db_rank;
+    if(world)
+        *world = ctx->db_world;
+    return MSLAM_B200_OK;
+}
+
+// scores -> local top-k -> ncclAllGather -> k-way merge, all enqueued on the context stream: no host synchronisation
+// between them (scratch growth, on the first call of a shape, is the one exception)
+int mslam_b200_db_query_sharded_dev(mslam_b200_ctx* ctx, const uint8_t* d_queries, const int* d_q_counts, int n_query_frames,
+                                    int q_cap, const uint8_t* d_db_shard, const int* d_k_counts, int n_local, int k_cap,
+                                    int id_base, int k, int* d_out_score, int* d_out_id)
+{
+    if(!ctx || !d_queries || !d_q_counts || !d_out_score || !d_out_id || n_query_frames < 1 || n_query_frames > 65535 || q_cap < 1 ||
+       n_local < 0 || (n_local > 0 && (!d_db_shard || !d_k_counts || k_cap < 1)) || k < 1 || id_base < 0)
+        return MSLAM_B200_E_INVALID;
+    const int world = ctx->db_world;
+    if(world > 1 && !ctx->db_comm)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    const size_t qk = (size_t)n_query_frames * k;
+    const size_t n_sc = (size_t)n_query_frames * std::max(n_local, 1);
+    const size_t need = (n_sc + 2 * qk + (size_t)world * 2 * qk) * sizeof(int);
+    if(ctx->dbs_bytes < need)
+    {
+        MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(ctx->d_dbs);
+        ctx->d_dbs = nullptr, ctx->dbs_bytes = 0;
+        MSLAM_CUDA_OK(cudaMalloc(&ctx->d_dbs, need));
+        ctx->dbs_bytes = need;
+    }
+    int* d_sc = ctx->d_dbs;
+    int* d_local = d_sc + n_sc;        // [2][Q][k]: scores, then ids
+    int* d_gather = d_local + 2 * qk;  // [world][2][Q][k]
+    if(n_local > 0)
+    {
+        int rc = mslam_b200_db_scores_dev(ctx, d_queries, d_q_counts, n_query_frames, q_cap, d_db_shard, d_k_counts, n_local, k_cap, d_sc);
+        if(rc != MSLAM_B200_OK)
+            return rc;
+        rc = mslam_b200_db_topk_dev(ctx, d_sc, n_query_frames, n_local, id_base, k, d_local, d_local + qk);
+        if(rc != MSLAM_B200_OK)
+            return rc;
+    }
+    else // an empty shard still takes part in the collective: (-1, -1) pads
+        MSLAM_CUDA_OK(cudaMemsetAsync(d_local, 0xff, 2 * qk * sizeof(int), st));
+    if(world == 1)
+    {
+        MSLAM_CUDA_OK(cudaMemcpyAsync(d_out_score, d_local, qk * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        MSLAM_CUDA_OK(cudaMemcpyAsync(d_out_id, d_local + qk, qk * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        return MSLAM_B200_OK;
+    }
+    const int r = nccl_api().AllGather(d_local, d_gather, 2 * qk, kNcclInt32, ctx->db_comm, st);
+    if(r != 0)
+        return nccl_fail(ctx, r, "ncclAllGather");
+    launch_topk(st, d_gather, d_gather + qk, world, k, (long long)(2 * qk), n_query_frames, 0, k, d_out_score, d_out_id, &ctx->launches);
+    MSLAM_CUDA_OK(cudaGetLastError());
+    return MSLAM_B200_OK;
+}
+
+// host queries in, host top-k out; the shard stays resident on the device (loaded once by the caller)
+int mslam_b200_db_query_sharded(mslam_b200_ctx* ctx, const uint8_t* queries, const int* q_counts, int n_query_frames, int q_cap,
+                                const uint8_t* d_db_shard, const int* d_k_counts, int n_local, int k_cap, int id_base, int k,
+                                int* out_score, int* out_id)
+{
+    if(!ctx || !queries || !q_counts || !out_score || !out_id || n_query_frames < 1 || q_cap < 1 || k < 1)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    const size_t qb = (size_t)n_query_frames * q_cap * 32, cb = ((size_t)n_query_frames * sizeof(int) + 15) / 16 * 16;
+    const size_t ob = (size_t)n_query_frames * k * sizeof(int);
+    const size_t need = qb + cb + 2 * ob;
+    if(ctx->dbq_bytes < need)
+    {
+        MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(ctx->d_dbq);
+        ctx->d_dbq = nullptr, ctx->dbq_bytes = 0;
+        MSLAM_CUDA_OK(cudaMalloc(&ctx->d_dbq, need));
+        ctx->dbq_bytes = need;
+    }
+    uint8_t* d_q = ctx->d_dbq;
+    int* d_qc = reinterpret_cast<int*>(d_q + qb);
+    int* d_os = reinterpret_cast<int*>(d_q + qb + cb);
+    int* d_oi = d_os + (size_t)n_query_frames * k;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(d_qc, q_counts, n_query_frames * sizeof(int), cudaMemcpyHostToDevice, st));
+    const int rc = mslam_b200_db_query_sharded_dev(ctx, d_q, d_qc, n_query_frames, q_cap, d_db_shard, d_k_counts, n_local, k_cap,
+                                                   id_base, k, d_os, d_oi);
+    if(rc != MSLAM_B200_OK)
+        return rc;
+    MSLAM_CUDA_OK(cudaMemcpyAsync(out_score, d_os, ob, cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaMemcpyAsync(out_id, d_oi, ob, cudaMemcpyDeviceToHost, st));
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    return MSLAM_B200_OK;
+}
+
+// a shard the context owns: uploaded once, resident in HBM, queried by mslam_b200_db_query_loaded (the form a C++ caller
+// without its own device allocations uses -- host/sharded_keyframe_db_b200.cpp)
+int mslam_b200_db_load_shard(mslam_b200_ctx* ctx, const uint8_t* db, const int* k_counts, int n_local, int k_cap, int id_base)
+{
+    if(!ctx || n_local < 0 || (n_local > 0 && (!db || !k_counts || k_cap < 1)) || id_base < 0)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    cudaStream_t st = ctx->stream;
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    const size_t db_b = ((size_t)n_local * k_cap * 32 + 255) / 256 * 256, need = db_b + (size_t)n_local * sizeof(int);
+    if(ctx->shard_bytes < need)
+    {
+        cudaFree(ctx->d_shard);
+        ctx->d_shard = nullptr, ctx->shard_bytes = 0;
+        MSLAM_CUDA_OK(cudaMalloc(&ctx->d_shard, std::max<size_t>(need, 256)));
+        ctx->shard_bytes = std::max<size_t>(need, 256);
+    }
+    if(n_local > 0)
+    {
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_shard, db, (size_t)n_local * k_cap * 32, cudaMemcpyHostToDevice, st));
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_shard + db_b, k_counts, (size_t)n_local * sizeof(int), cudaMemcpyHostToDevice, st));
+        MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    }
+    ctx->shard_n = n_local, ctx->shard_cap = n_local > 0 ? k_cap : 1, ctx->shard_id_base = id_base;
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_db_query_loaded(mslam_b200_ctx* ctx, const uint8_t* queries, const int* q_counts, int n_query_frames, int q_cap, int k,
+                               int* out_score, int* out_id)
+{
+    if(!ctx)
+        return MSLAM_B200_E_INVALID;
+    const size_t db_b = ((size_t)ctx->shard_n * ctx->shard_cap * 32 + 255) / 256 * 256;
+    return mslam_b200_db_query_sharded(ctx, queries, q_counts, n_query_frames, q_cap, ctx->shard_n ? ctx->d_shard : nullptr,
+                                       ctx->shard_n ? reinterpret_cast<const int*>(ctx->d_shard + db_b) : nullptr, ctx->shard_n,
+                                       ctx->shard_cap, ctx->shard_id_base, k, out_score, out_id);
 }
 
 // grow-only device scratch of the host convenience entry points (back-projection, RANSAC PnP): a per-call cudaMalloc /

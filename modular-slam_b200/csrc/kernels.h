@@ -28,6 +28,10 @@ constexpr int kKnnMaxSlices = 8; // train-set slices of the small-batch kNN (scr
 void launch_knn2(cudaStream_t st, const uint8_t* q, const int* qn, const uint8_t* t, const int* tn, int n_pairs, int cap,
                  unsigned* key0, unsigned* key1, unsigned* part0, unsigned* part1, int sm_count, long long* launches);
 // tensor-core kNN (knn_mma.cu): descriptors expanded to +1/-1 int8 rows, then D = Q T^T on tcgen05 with a top-2 epilogue
+constexpr int kDbDpt = 4;                // keyframe descriptors per thread of the scalar DB kernel
+constexpr int kDbMaxSmem = 200 * 1024;   // largest resident query frame of the scalar DB kernel (6400 descriptors)
+cudaError_t configure_match_kernels();   // per-device kernel attributes (dynamic shared memory opt-in)
+cudaError_t configure_mma_kernels();
 int knn_mma_pad(int cap);
 size_t knn_mma_bytes(int n_pairs, int cap);
 void launch_expand_pm1(cudaStream_t st, const uint8_t* desc, const int* counts, int n_pairs, int cap, uint8_t* out,
@@ -49,8 +53,8 @@ void launch_unpack_knn(cudaStream_t st, const unsigned* key0, const unsigned* ke
 cudaError_t launch_db_scores(cudaStream_t st, const uint8_t* queries, const int* q_counts, int nq_frames, int q_cap,
                              const uint8_t* db, const int* k_counts, int n_keyframes, int k_cap, double ratio, int* scores,
                              int sm_count, long long* launches);
-void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists, int per_list, int n_queries, int id_base,
-                 int k, int* out_score, int* out_id, long long* launches);
+void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists, int per_list, long long list_stride,
+                 int n_queries, int id_base, int k, int* out_score, int* out_id, long long* launches);
 // RGB-D association (rgbd_kernels.cu)
 void launch_backproject(cudaStream_t st, const mslam_b200_keypoint* kp, int kp_cap, const int* index, const int* counts,
                         int n_pairs, int cap, const uint16_t* depth, int width, int height, const mslam_b200_camera& cam,

@@ -252,6 +252,14 @@ __global__ void __launch_bounds__(256) k_expand_pm1(ExpandSet s0, ExpandSet s1, 
 //             scores[query frame][keyframe] (zeroed by the launcher; integer adds commute, so the result is exact).
 __device__ unsigned long long g_mma_clk[2]; // MSLAM_MMA_DEBUG & 32: sum of SM cycles / of nanoseconds over sampled CTAs
 
+// Timing experiments (switching parts of the kernel off; results are WRONG) exist only in builds with -DMSLAM_MMA_DEBUG
+// (tools/gpu_mma_dbg.sh); the product library compiles the switches out.
+#ifdef MSLAM_MMA_DEBUG
+#define MMA_DBG(mask) (db.debug & (mask))
+#else
+#define MMA_DBG(mask) 0
+#endif
+
 struct DbArgs
 {
     int t_cap, t_cap_pad, n_keyframes, int_ratio;
@@ -279,7 +287,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
         return; // whole CTA, before any barrier or allocation
     long long clk0 = 0;
     unsigned long long ns0 = 0;
-    if((db.debug & 32) && threadIdx.x == 0)
+    if(MMA_DBG(32) && threadIdx.x == 0)
     {
         clk0 = clock64();
         asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns0));
@@ -369,11 +377,11 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                     mbar_wait(bar_cempty + 8 * as, ((it / ACC_STAGES) & 1) ^ 1);
                     tc_fence_after();
                     const uint32_t b_addr = smem_u32(sB + s * B_BYTES);
-                    for(int a = 0; a < ((db.debug & 16) ? 1 : n_row_tiles); ++a)
+                    for(int a = 0; a < (MMA_DBG(16) ? 1 : n_row_tiles); ++a)
                     {
 #pragma unroll
                         for(int k = 0; k < ROW_BYTES / 32; ++k)
-                            if(k == 0 || !(db.debug & 1))
+                            if(k == 0 || !MMA_DBG(1))
                                 umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
                                     smem_desc(b_addr + k * 256), k > 0);
                     }
@@ -400,7 +408,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                 const int col_base = j * MMA_N;
                 const int n_valid = nt - col_base; // >= 1
                 Top2x2 t;
-                if(db.debug & 8)
+                if(MMA_DBG(8))
                 {
                     // ALU work of the epilogue on whatever the registers hold, no tensor-memory load
                     uint32_t va[32];
@@ -414,9 +422,9 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                             asm volatile("" : "+r"(va[0]), "+r"(va[1]));
                         }
                 }
-                else if(db.debug & 6)
+                else if(MMA_DBG(6))
                 {
-                    if(active && (db.debug & 2))
+                    if(active && MMA_DBG(2))
                     {
                         uint32_t va[32];
                         for(int c = 0; c < MMA_N; c += 32)
@@ -463,7 +471,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     }
     tc_fence_before();
     __syncthreads();
-    if((db.debug & 32) && threadIdx.x == 0)
+    if(MMA_DBG(32) && threadIdx.x == 0)
     {
         unsigned long long ns1;
         asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns1));
@@ -480,6 +488,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
 
 static int mma_debug()
 {
+#ifdef MSLAM_MMA_DEBUG
     static int v = -1;
     if(v < 0)
     {
@@ -487,6 +496,17 @@ static int mma_debug()
         v = e ? atoi(e) : 0;
     }
     return v;
+#else
+    return 0;
+#endif
+}
+// per DEVICE (cudaFuncSetAttribute applies to the current device only): called from mslam_b200_create after cudaSetDevice
+cudaError_t configure_mma_kernels()
+{
+    cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if(e != cudaSuccess)
+        return e;
+    return cudaFuncSetAttribute(k_knn2_mma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
 }
 int knn_mma_pad(int cap)
 {
@@ -514,14 +534,6 @@ void launch_expand_pm1_x2(cudaStream_t st, const uint8_t* desc0, const int* coun
 cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, const uint8_t* xt, const int* tn, int n_pairs,
                             int cap, unsigned* key0, unsigned* key1, long long* launches)
 {
-    static bool configured = false;
-    if(!configured)
-    {
-        cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-        if(e != cudaSuccess)
-            return e;
-        configured = true;
-    }
     dim3 grd((cap + CTA_ROWS - 1) / CTA_ROWS, n_pairs);
     DbArgs none{};
     none.debug = mma_debug();
@@ -535,14 +547,6 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
                                  const uint8_t* xdb, const int* k_counts, int n_keyframes, int k_cap, double ratio, int* scores,
                                  int score_stride, long long* launches)
 {
-    static bool configured = false;
-    if(!configured)
-    {
-        cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-        if(e != cudaSuccess)
-            return e;
-        configured = true;
-    }
     DbArgs db;
     db.t_cap = q_cap, db.t_cap_pad = knn_mma_pad(q_cap), db.n_keyframes = score_stride, db.int_ratio = ratio == 0.7;
     db.ratio = ratio, db.scores = scores;
@@ -559,7 +563,7 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
                                                                xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
         ++*launches;
     }
-    if(db.debug & 32)
+    if(MMA_DBG(32))
     {
         unsigned long long h[2] = {0, 0};
         cudaStreamSynchronize(st);

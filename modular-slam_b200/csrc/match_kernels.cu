@@ -334,11 +334,13 @@ __global__ void __launch_bounds__(DB_THREADS) k_db_scores(const uint8_t* __restr
 }
 
 // per query frame: top-k of n entries by (score desc, id asc).  Entry e of query q is read through
-// (list = e / per_list, j = e % per_list) at  ((list * list_stride_q) + q) * per_list + j  so the same kernel
-// serves a plain score row (n_lists = 1, ids implicit = id_base + j) and the all-gathered shard lists.
+// (list = e / per_list, j = e % per_list) at  list * list_stride + q * per_list + j  so the same kernel serves a plain
+// score row (n_lists = 1, ids implicit = id_base + j), dense [n_lists][n_queries][per_list] candidate lists
+// (list_stride = n_queries * per_list) and the all-gathered shard lists, where every rank's block is its scores followed
+// by its ids (list_stride = 2 * n_queries * per_list, ids = scores + n_queries * per_list).
 __global__ void __launch_bounds__(256) k_topk(const int* __restrict__ scores, const int* __restrict__ ids, int n_lists,
-                                              int per_list, int n_queries, int id_base, int k, int* __restrict__ out_score,
-                                              int* __restrict__ out_id)
+                                              int per_list, long long list_stride, int n_queries, int id_base, int k,
+                                              int* __restrict__ out_score, int* __restrict__ out_id)
 {
     __shared__ unsigned long long s_best[8];
     __shared__ unsigned long long s_last;
@@ -351,7 +353,7 @@ __global__ void __launch_bounds__(256) k_topk(const int* __restrict__ scores, co
         for(int e = threadIdx.x; e < n; e += 256)
         {
             const int list = e / per_list, j = e - list * per_list;
-            const long long at = ((long long)list * n_queries + q) * per_list + j;
+            const long long at = (long long)list * list_stride + (long long)q * per_list + j;
             const int sc = scores[at];
             const int id = ids ? ids[at] : id_base + j;
             if(sc < 0 || id < 0)
@@ -587,21 +589,18 @@ void launch_unpack_knn(cudaStream_t st, const unsigned* key0, const unsigned* ke
     ++*launches;
 }
 
+// per DEVICE: called from mslam_b200_create after cudaSetDevice (the attribute applies to the current device only)
+cudaError_t configure_match_kernels()
+{
+    return cudaFuncSetAttribute(k_db_scores<kDbDpt>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDbMaxSmem);
+}
+
 cudaError_t launch_db_scores(cudaStream_t st, const uint8_t* queries, const int* q_counts, int nq_frames, int q_cap,
                              const uint8_t* db, const int* k_counts, int n_keyframes, int k_cap, double ratio, int* scores,
                              int sm_count, long long* launches)
 {
-    constexpr int DPT = 4;
-    const size_t smem = (size_t)q_cap * 32;
-    static size_t configured = 0;
-    if(smem > configured)
-    {
-        cudaError_t e =
-            cudaFuncSetAttribute(k_db_scores<DPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if(e != cudaSuccess)
-            return e;
-        configured = smem;
-    }
+    constexpr int DPT = kDbDpt;
+    const size_t smem = (size_t)q_cap * 32; // <= kDbMaxSmem (checked by the entry point), opted in by configure_match_kernels
     // enough CTAs to fill the machine a few times over, but long enough walks to amortise the query-frame load
     int kf_per_cta = 8;
     while(kf_per_cta > 1 && (long long)((n_keyframes + kf_per_cta - 1) / kf_per_cta) * nq_frames < 4LL * sm_count)
@@ -613,10 +612,10 @@ cudaError_t launch_db_scores(cudaStream_t st, const uint8_t* queries, const int*
     return cudaGetLastError();
 }
 
-void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists, int per_list, int n_queries, int id_base,
-                 int k, int* out_score, int* out_id, long long* launches)
+void launch_topk(cudaStream_t st, const int* scores, const int* ids, int n_lists, int per_list, long long list_stride,
+                 int n_queries, int id_base, int k, int* out_score, int* out_id, long long* launches)
 {
-    k_topk<<<n_queries, 256, 0, st>>>(scores, ids, n_lists, per_list, n_queries, id_base, k, out_score, out_id);
+    k_topk<<<n_queries, 256, 0, st>>>(scores, ids, n_lists, per_list, list_stride, n_queries, id_base, k, out_score, out_id);
     ++*launches;
 }
 

@@ -8,6 +8,9 @@
 //   plugin_host_test provider <associations.txt> <out.bin> [batch size]   (RgbdFileB200Provider; batch > 0 => fetchBatch, pinned)
 //   plugin_host_test pnp     <plugin.so> <in.bin> <out.bin>   (RansacPnpB200 through the ransacPnpFactory alias; in.bin = i64 n,
 //                            fx fy cx cy f64, n x 3 f64 landmarks, n x 2 f64 pixels; called twice: solvePnp, then solvePnpBatch)
+//   plugin_host_test db      <in.bin> <out.bin> [rank world idfile]   (ShardedKeyframeDbB200; in.bin = i32 K, n, Q, k, then
+//                            K x n x 32 keyframe descriptor bytes, Q x n x 32 query bytes; out.bin = Q x k x (i64 id, i32 score,
+//                            i32 pad); with world > 1 each process is one rank on device `rank`, rank 0 writes the NCCL id to idfile)
 //   plugin_host_test run     <plugin.so> <frame0.raw> <frame1.raw> <W> <H> <out.bin> [detector alias]
 #include <dlfcn.h>
 
@@ -20,6 +23,10 @@
 #include "orb_b200_plugin.hpp"
 #include "ransac_pnp_b200.hpp"
 #include "rgbd_file_b200_provider.hpp"
+#include "sharded_keyframe_db_b200.hpp"
+
+#include <chrono>
+#include <thread>
 
 template <typename BlockType>
 using BlockFactoryCreator = std::unique_ptr<BlockType>(); // plugin_loader.hpp:13-14
@@ -61,6 +68,78 @@ int main(int argc, char** argv)
             std::printf("library=%s detector=%s matcher=%s nfeatures=%d nlevels=%d scaleFactor=%.3f fastThreshold=%d ratio=%.3f\n",
                         e.library.c_str(), e.detectorFactory.c_str(), e.matcherFactory.c_str(), e.options.nfeatures,
                         e.options.nlevels, e.options.scaleFactor, e.options.fastThreshold, e.options.ratio);
+        return 0;
+    }
+    if(argc >= 4 && !std::strcmp(argv[1], "db"))
+    {
+        std::vector<std::uint8_t> raw;
+        if(!readFile(argv[2], &raw) || raw.size() < 16)
+            return 5;
+        int hdr[4];
+        std::memcpy(hdr, raw.data(), 16);
+        const int K = hdr[0], n = hdr[1], Q = hdr[2], k = hdr[3];
+        if(raw.size() < 16 + ((size_t)K + Q) * n * 32)
+            return 5;
+        auto frames = [&](const std::uint8_t* p, int count) {
+            std::vector<std::vector<mslam::OrbKeypoint>> v((size_t)count);
+            for(int f = 0; f < count; ++f)
+            {
+                v[(size_t)f].resize((size_t)n);
+                for(int i = 0; i < n; ++i)
+                    std::memcpy(v[(size_t)f][(size_t)i].descriptor.data(), p + ((size_t)f * n + i) * 32, 32);
+            }
+            return v;
+        };
+        try
+        {
+            mslam::ShardedKeyframeDbOptions o;
+            o.maxDescriptors = n;
+            if(argc >= 7)
+            {
+                o.rank = std::atoi(argv[4]), o.world = std::atoi(argv[5]), o.device = o.rank;
+                if(o.world > 1 && o.rank == 0)
+                {
+                    o.ncclUniqueId = mslam::ShardedKeyframeDbB200::createUniqueId();
+                    std::ofstream tmp(std::string(argv[6]) + ".tmp", std::ios::binary);
+                    tmp.write(o.ncclUniqueId.data(), (std::streamsize)o.ncclUniqueId.size());
+                    tmp.close();
+                    std::rename((std::string(argv[6]) + ".tmp").c_str(), argv[6]);
+                }
+                else if(o.world > 1)
+                {
+                    std::vector<std::uint8_t> id;
+                    for(int tries = 0; tries < 600 && (!readFile(argv[6], &id) || id.size() != o.ncclUniqueId.size()); ++tries)
+                        std::this_thread::sleep_for(std::chrono::milliseconds(100));
+                    if(id.size() != o.ncclUniqueId.size())
+                        return 10;
+                    std::memcpy(o.ncclUniqueId.data(), id.data(), id.size());
+                }
+            }
+            mslam::ShardedKeyframeDbB200 db(o);
+            db.load(frames(raw.data() + 16, K));
+            const auto queries = frames(raw.data() + 16 + (size_t)K * n * 32, Q);
+            auto result = db.query(queries, k);
+            result = db.query(queries, k); // a second query reuses the resident shard and the communicator
+            if(result.size() != (size_t)Q)
+                return 11;
+            std::ofstream out(argv[3], std::ios::binary);
+            for(int q = 0; q < Q; ++q)
+                for(int r = 0; r < k; ++r)
+                {
+                    const bool have = (size_t)r < result[(size_t)q].size();
+                    const long long id = have ? (long long)result[(size_t)q][(size_t)r].keyframeId : -1;
+                    const int rec[2] = {have ? result[(size_t)q][(size_t)r].score : -1, 0};
+                    out.write(reinterpret_cast<const char*>(&id), 8);
+                    out.write(reinterpret_cast<const char*>(rec), 8);
+                }
+            std::printf("db rank %d/%d: %zu local keyframes from id %zu, %d query frames\n", o.rank, o.world, db.localSize(),
+                        db.firstLocalId(), Q);
+        }
+        catch(const std::exception& e)
+        {
+            std::fprintf(stderr, "db failed: %s\n", e.what());
+            return 6;
+        }
         return 0;
     }
     if(argc >= 4 && !std::strcmp(argv[1], "provider"))
