@@ -81,6 +81,13 @@ class ShardedKeyframeDb:
         self.d_db, self.d_counts, self.id_base, self.n_local = d_db.contiguous(), d_counts.contiguous(), int(id_base), d_db.shape[0]
         self.k_cap = max(int(d_db.shape[1]), 1)
 
+    def score_local(self, d_queries, d_q_counts):
+        """-> int32 [Q][n_local] match counts of every query frame against every keyframe of this shard (measurement aid)"""
+        Q, qcap, _ = d_queries.shape
+        sc = torch.empty((Q, self.n_local), dtype=torch.int32, device=d_queries.device)
+        self.ctx.db_scores_dev(d_queries, d_q_counts, Q, qcap, self.d_db, self.d_counts, self.n_local, self.k_cap, sc)
+        return sc
+
     def query(self, d_queries, d_q_counts, k):
         """-> (scores [Q][k], ids [Q][k]) int32 CUDA tensors, identical on every rank; asynchronous on the context's stream"""
         Q, qcap, _ = d_queries.shape
