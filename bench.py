@@ -44,6 +44,14 @@ WORKLOADS = {
 N_TIMESTEPS = 4  # distinct input batches rotated through the timed region (together larger than the 126 MB L2 for c2..c4)
 
 
+def frames_config(label, W, H, nfeat, B, mode, world, T):
+    """the `config` object of a frame workload -- built by BOTH arms (this and --impl reference), so that they are equal"""
+    return {"workload": label, "frame": [W, H], "nfeatures": nfeat, "nlevels": 8, "batch_per_gpu": B,
+            "match": "crosscheck" if mode else "knn2+ratio0.7", "parallelism": f"frame-batch replicas x{world}",
+            "l2": f"inputs rotate over {T} distinct batches ({T * B * W * H * 3 / 1e6:.0f} MB/GPU) + pyramids; "
+                  "working set per step > L2 is not guaranteed for c2 (59 MB frames + 2x61 MB pyramids = 181 MB > 126 MB)"}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -144,22 +152,28 @@ def run_reference(args, rank, world):
     if args.workload == "dist":
         import bench_dist
         return bench_dist.run_reference(args)
-    W, H, nfeat, _, mode, label = WORKLOADS[args.workload if args.workload in WORKLOADS else "c2"]
+    W, H, nfeat, B, mode, label = WORKLOADS[args.workload if args.workload in WORKLOADS else "c2"]
     threads = os.cpu_count() or 1
-    n_sample = max(threads, 8)  # frames per step: one per host thread
-    n_sample = min(n_sample, 64)
-    fr = make_inputs(pkg, W, H, n_sample, 0, 1)
-    for _ in range(args.warmup):
-        cpu_port_time(pkg, O, fr[0], fr[1], nfeat, mode, threads)
-    t = [cpu_port_time(pkg, O, fr[0], fr[1], nfeat, mode, threads)[0] for _ in range(args.steps)]
+    # the SAME step as the B200 arm: one batch of B frames (frame t of B sequences, detect + match against frame t-1),
+    # OpenMP over frames on every host core; same generator, same rotation over the input batches
+    fr = make_inputs(pkg, W, H, B, 0, args.steps)
+    T = len(fr) - 1
+    for i in range(args.warmup):
+        cpu_port_time(pkg, O, fr[i % T], fr[1 + i % T], nfeat, mode, threads)
+    t = [cpu_port_time(pkg, O, fr[i % T], fr[1 + i % T], nfeat, mode, threads)[0] for i in range(args.steps)]
     total = float(np.sum(t))
-    v = n_sample * args.steps / total
+    v = B * args.steps / total
+    import bench_cv2
+    pool = bench_cv2.pool_frames_per_s(fr[0], fr[1], nfeat, mode, threads)
     line = {"metric": "ORB extract+match frames/sec", "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
-            "config": {"workload": label, "frame": [W, H], "nfeatures": nfeat, "nlevels": 8, "batch_per_step": n_sample},
+            "config": frames_config(label, W, H, nfeat, B, mode, args.gpus, T),
             "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port",
-                             "sample": f"{n_sample} frames per step (detect + match vs previous frame), OpenMP over frames"},
+                             "sample": f"{B} frames per step (detect + match vs previous frame), {args.steps} steps, OpenMP over frames",
+                             "cv2_process_pool_frames_per_s": pool,
+                             "cv2_note": "OpenCV itself (cv2 4.x, the library the reference wraps), one frame pair per worker process, "
+                                         f"{threads} processes, cv2 single-threaded in each (bench_cv2.py); informational"},
             "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -216,6 +230,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--serial", action="store_true", help="one stream for every kernel (MSLAM_B200_FLAG_SERIAL)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-sub", action="store_true", help="skip the db / c3 sub-records of the default (c2) line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -431,6 +446,15 @@ def main():
     # host results must equal the device-resident run's
     assert int(h_m[3].sum()) > 0 and int(h_cnt[cur ^ 1].sum()) >= B * nfeat // 2
 
+    # ---- sub-records (every rank takes part: the database path has a collective in it): keyframe-database scoring through
+    # the sharded C-ABI entry point, and configs[2]; after -- and outside -- the headline's timed regions ---------------------
+    sub = {}
+    if args.workload == "c2" and not args.no_sub:
+        import bench_sub
+        sub["db"] = bench_sub.db_subrecord(pkg, torch, dist, rank, world, local, stream, want_cpu=not args.no_cpu_baseline)
+        sub["c3"] = bench_sub.frames_subrecord(pkg, torch, dist, rank, world, local, stream, WORKLOADS["c3"], batch=16,
+                                               want_cpu=not args.no_cpu_baseline)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -517,15 +541,14 @@ def main():
         except Exception as ex:  # pragma: no cover
             cpu["cv2_frames_per_s"] = None
             cpu["cv2_note"] = str(ex)[:80]
+        import bench_cv2
+        cpu["cv2_process_pool_frames_per_s"] = bench_cv2.pool_frames_per_s(frames[0], frames[1], nfeat, mode, threads)
 
     line = {"metric": "ORB extract+match frames/sec", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": label, "frame": [W, H], "nfeatures": nfeat, "nlevels": 8, "batch_per_gpu": B,
-                       "match": "crosscheck" if mode else "knn2+ratio0.7", "parallelism": f"frame-batch replicas x{world}",
-                       "l2": f"inputs rotate over {T} distinct batches ({T * B * W * H * 3 / 1e6:.0f} MB/GPU) + pyramids; "
-                             "working set per step > L2 is not guaranteed for c2 (59 MB frames + 2x61 MB pyramids = 181 MB > 126 MB)",
-                       "keypoints_per_batch_check": n_kp_check, "matches_per_batch_check": n_matches_check},
+            "config": frames_config(label, W, H, nfeat, B, mode, world, T),
+            "checks": {"keypoints_per_batch": n_kp_check, "matches_per_batch": n_matches_check},
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps,
                     "h2d_gbs": h2d * args.steps / (e2e_ms * 1e-3) / 1e9,
@@ -537,6 +560,7 @@ def main():
                                     "note": "one blocking detect_batch + one blocking match_batch per step"}},
             "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "natural_frames": natural}
+    line.update(sub)
     print(json.dumps(line))
     ctx.close()
     if world > 1:

@@ -173,6 +173,10 @@ def main(args, rank, world, local):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e_ms = float(tt.item())
     e2e_value = pairs_per_step * args.steps / (e2e_ms * 1e-3)
+    score_sample = db.score_local(d_queries[:qb], d_qc[:qb]).clone()
+    barrier()
+    db.close()  # every rank leaves the database communicator together, before any of them can exit
+    barrier()
 
     if rank != 0:
         if world > 1:
@@ -219,7 +223,7 @@ def main(args, rank, world, local):
         ctx2 = pkg.Context(device=local, max_width=64, max_height=64, max_batch=1, nfeatures=n, stream=stream.cuda_stream,
                            flags=pkg.FLAG_KNN_SCALAR)
         sc2 = torch.empty((qb, k1 - k0), dtype=torch.int32, device=dev)
-        sc1 = db.score_local(d_queries[:qb], d_qc[:qb]).clone()
+        sc1 = score_sample
         ctx2.enable_stage_timing(True)
         for i in range(3 + 3):
             if i == 3:

@@ -413,6 +413,12 @@ MSLAM_B200_API int mslam_b200_stage_times(mslam_b200_ctx* ctx, double* total_ms,
  * out[4] = pair evaluations/s of the carry-save sequence the matcher uses (8 xor, 8 lop3, 4 popc) + top-2,
  * out[5] = LOP3 results/s when all three operands are live registers (12 independent chains per thread). */
 MSLAM_B200_API int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out6);
+/* int8 tensor-core roofline denominator of the tensor-core matcher (csrc/knn_mma.cu), measured on the context's device:
+ * tcgen05.mma.cta_group::1.kind::i8 issued back to back on every SM from operands resident in shared memory, accumulators
+ * in tensor memory, no loads and no epilogue.  out[0] / out[1] = int8 operations per second (2 M N K per instruction) of
+ * the M128 N128 K32 shape the matcher issues / of M128 N256 K32, SUSTAINED (the last quarter of ~0.4 s of back-to-back
+ * launches: the power-limited clock a long scoring step runs at); out[2] / out[3] = the same for one short launch (burst). */
+MSLAM_B200_API int mslam_b200_measure_tensor_peak(mslam_b200_ctx* ctx, double* out4);
 
 #ifdef __cplusplus
 }

@@ -500,6 +500,13 @@ class Context:
                 "sm_mhz": float(out[3]), "csa_pairs_per_s": float(out[4]), "lop3_3reg_per_s": float(out[5])}
 
 
+    def measure_tensor_peak(self):
+        out = np.zeros(4, np.float64)
+        self._chk(library().mslam_b200_measure_tensor_peak(self._h, _ptr(out)), "measure_tensor_peak")
+        return {"int8_ops_per_s_n128_sustained": float(out[0]), "int8_ops_per_s_n256_sustained": float(out[1]),
+                "int8_ops_per_s_n128_burst": float(out[2]), "int8_ops_per_s_n256_burst": float(out[3])}
+
+
 # ---- second detector: DistributedOrbOpenCvDetector (include/mslam_b200.h, "second detector") ---------------------------
 DIST_PYRAMID, DIST_BLURRED, DIST_N_FAST, DIST_N_TREE, DIST_PASSES = 0, 1, 2, 3, 4
 

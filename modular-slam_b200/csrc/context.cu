@@ -30,6 +30,7 @@ struct mslam_b200_ctx
     // geometry of the frame size currently configured (cv::ORB layer table)
     int geo_w = 0, geo_h = 0;
     PipeParams P;
+    FastMaps fast_maps; // tensor maps of k_fast's tile loads for the current geometry
     int kp_cap = 0, desc_cap = 0;
 
     // ---- HBM: detector ----
@@ -357,6 +358,7 @@ static int set_geometry(mslam_b200_ctx* ctx, int W, int H)
                                           ctx->stream));
         MSLAM_CUDA_OK(cudaStreamSynchronize(ctx->stream)); // the host vectors die with this scope
     }
+    MSLAM_CUDA_OK(build_fast_maps(g.P, ctx->d_pyr, ctx->cfg.max_batch, &ctx->fast_maps));
     ctx->P = g.P;
     ctx->geo_w = W;
     ctx->geo_h = H;
@@ -750,7 +752,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         const PipeParams& P = ctx->P;
         {
             StageTimer t(ctx, MSLAM_B200_T_FAST);
-            launch_fast(st, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, 0, P.nlevels, &ctx->launches);
+            launch_fast(st, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, ctx->fast_maps, 0, P.nlevels, &ctx->launches);
         }
         {
             StageTimer t(ctx, MSLAM_B200_T_SELECT);
@@ -793,13 +795,13 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         {
             MSLAM_CUDA_OK(cudaStreamWaitEvent(s_fast, ctx->ev_level[l], 0));
             StageTimer t(ctx, MSLAM_B200_T_FAST, s_fast);
-            launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, l, l + 1, &ctx->launches);
+            launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, ctx->fast_maps, l, l + 1, &ctx->launches);
         }
         if(l_split < nl)
         {
             MSLAM_CUDA_OK(cudaStreamWaitEvent(s_fast, ctx->ev_level[nl - 1], 0));
             StageTimer t(ctx, MSLAM_B200_T_FAST, s_fast);
-            launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, l_split, nl, &ctx->launches);
+            launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, ctx->fast_maps, l_split, nl, &ctx->launches);
         }
         {
             StageTimer t(ctx, MSLAM_B200_T_SELECT, s_fast);
@@ -1607,8 +1609,11 @@ int mslam_b200_db_detach(mslam_b200_ctx* ctx)
     {
         cudaSetDevice(ctx->cfg.device);
         cudaStreamSynchronize(ctx->stream);
+        // every collective this context enqueued has completed (stream synchronised), so nothing of ours is outstanding;
+        // ncclCommAbort releases the communicator without waiting for the peers -- ncclCommDestroy can block for ever when a
+        // peer process has already exited (measured: a rank that outlived its peer hung in teardown)
         if(ctx->db_own_comm)
-            nccl_api().CommDestroy(ctx->db_comm);
+            nccl_api().CommAbort(ctx->db_comm);
     }
     ctx->db_comm = nullptr, ctx->db_own_comm = false, ctx->db_rank = 0, ctx->db_world = 1;
     return MSLAM_B200_OK;
@@ -2024,6 +2029,15 @@ int mslam_b200_measure_int_peaks(mslam_b200_ctx* ctx, double* out4 /* 5 values *
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     MSLAM_CUDA_OK(measure_int_peaks(ctx->stream, ctx->sm_count, out4, &ctx->launches));
+    return MSLAM_B200_OK;
+}
+
+int mslam_b200_measure_tensor_peak(mslam_b200_ctx* ctx, double* out4)
+{
+    if(!ctx || !out4)
+        return MSLAM_B200_E_INVALID;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    MSLAM_CUDA_OK(measure_tensor_peak(ctx->stream, ctx->sm_count, out4, &ctx->launches));
     return MSLAM_B200_OK;
 }
 

@@ -13,8 +13,14 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
 void fast_tiles(int w, int h, int edge, int* tx, int* ty, int* tile_sh);
 void blur_warps(int w, int h, int* xblocks, int* warps);
 int blur_band_rows();
+// one CUtensorMap (128 opaque bytes) per pyramid level: the FAST kernel's tile loads (k_fast, orb_kernels.cu)
+struct alignas(64) FastMaps
+{
+    unsigned char m[kMaxLevels][128];
+};
+cudaError_t build_fast_maps(const PipeParams& P, const uint8_t* pyr, int max_batch, FastMaps* out);
 void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCounters* ctr, unsigned* hist,
-                 const PipeParams& P, int l_begin, int l_end, long long* launches);
+                 const PipeParams& P, const FastMaps& maps, int l_begin, int l_end, long long* launches);
 void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned* cand2, unsigned* keys, unsigned* keys2,
                    LevelCounters* ctr, const unsigned* hist, SelRec* sel, int* err, const PipeParams& P, int sm_count,
                    long long* launches);
@@ -66,5 +72,6 @@ void launch_pnp_ransac(cudaStream_t st, const float* obj, const float* img, cons
                        double fx, double fy, double cx, double cy, int iterations, double thr2, unsigned seed, int refine_iters,
                        double* out_rt, double* out_pose, uint8_t* out_mask, int* out_info, long long* launches);
 int pnp_max_hypotheses();
+cudaError_t measure_tensor_peak(cudaStream_t st, int sm_count, double* out4, long long* launches);
 cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4, long long* launches);
 } // namespace mslam_b200

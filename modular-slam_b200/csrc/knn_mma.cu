@@ -484,6 +484,128 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
     }
 }
+// ---------------------------------------------------------------------------------------------------------------
+// roofline denominator of the tensor-core matcher, MEASURED: the rate at which this GPU retires tcgen05.mma.kind::i8
+// when nothing else runs -- operands resident in shared memory (+1/-1 bytes, like the matcher's), accumulators in tensor
+// memory, one issuing thread per SM, no loads, no epilogue.  N = 128 is the instruction shape k_knn2_mma issues, N = 256
+// the widest cta_group::1 shape.
+// ---------------------------------------------------------------------------------------------------------------
+template <int N>
+__global__ void __launch_bounds__(128, 1) k_peak_i8(int iters, unsigned* sink)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + MMA_M * ROW_BYTES;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + (MMA_M + N) * ROW_BYTES);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar + 1);
+    for(int i = threadIdx.x; i < (MMA_M + N) * ROW_BYTES / 4; i += blockDim.x)
+    {
+        unsigned h = (i + blockIdx.x * 7919u) * 2654435761u;
+        h ^= h >> 15;
+        // four bytes, each +1 or -1
+        reinterpret_cast<unsigned*>(smem)[i] = 0x01010101u + ((h & 1u) * 0xfeu) + (((h >> 1) & 1u) * 0xfe00u) +
+                                               (((h >> 2) & 1u) * 0xfe0000u) + (((h >> 3) & 1u) * 0xfe000000u);
+    }
+    if(threadIdx.x == 0)
+    {
+        mbar_init(smem_u32(bar), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if(threadIdx.x < 32)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy writes of the operands -> visible to the MMA's async proxy
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *s_tmem;
+    if(threadIdx.x == 0)
+    {
+        constexpr uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(MMA_M >> 4) << 24);
+        const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+        for(int it = 0; it < iters; ++it)
+        {
+            const uint32_t d = tmem + (uint32_t)(it % (TMEM_COLS / N)) * N;
+#pragma unroll
+            for(int k = 0; k < ROW_BYTES / 32; ++k)
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                             "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+                             "l"(smem_desc(a_addr + k * 256)), "l"(smem_desc(b_addr + k * 256)), "r"(idesc), "r"((uint32_t)(k > 0))
+                             : "memory");
+        }
+        umma_commit(smem_u32(bar));
+        for(unsigned spins = 0; !mbar_try_wait(smem_u32(bar), 0); ++spins)
+            if(spins > (1u << 28))
+                __trap();
+        tc_fence_after();
+    }
+    __syncthreads();
+    if(threadIdx.x < 32)
+    {
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)0 << 16), v);
+        tmem_wait(v);
+        if(sink && v[threadIdx.x & 31] == 0x7fffffffu)
+            sink[0] = v[0];
+        tc_fence_before();
+        __syncwarp();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
+    }
+}
+} // namespace
+
+// out[0] / out[1]: int8 tensor operations per second (2 * M * N * K per MMA) of the N = 128 / N = 256 instruction shape,
+// sustained (timed over the last quarter of ~0.4 s of back-to-back launches, i.e. at the power-limited clock a long scoring
+// step runs at); out[2] / out[3]: the same for the first short launch after idle (burst).
+cudaError_t measure_tensor_peak(cudaStream_t st, int sm_count, double* out4, long long* launches)
+{
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaError_t err = cudaSuccess;
+    for(int shape = 0; shape < 2 && err == cudaSuccess; ++shape)
+    {
+        const int n = shape ? 256 : 128;
+        const int smem = (MMA_M + n) * ROW_BYTES + 64;
+        auto launch = [&](int iters) {
+            if(shape)
+                k_peak_i8<256><<<sm_count, 128, smem, st>>>(iters, nullptr);
+            else
+                k_peak_i8<128><<<sm_count, 128, smem, st>>>(iters, nullptr);
+            ++*launches;
+        };
+        const int iters = shape ? 8192 : 16384; // ~2^30 cycles-worth / 128: about 4 ms per launch
+        const double ops = (double)sm_count * iters * (ROW_BYTES / 32) * 2.0 * MMA_M * n * 32;
+        float ms = 0.f;
+        launch(64); // cold start (module load, first-touch of tensor memory)
+        cudaStreamSynchronize(st);
+        cudaEventRecord(e0, st);
+        launch(iters);
+        cudaEventRecord(e1, st);
+        cudaEventSynchronize(e1);
+        cudaEventElapsedTime(&ms, e0, e1);
+        out4[2 + shape] = ops / (ms * 1e-3);
+        const int reps = 100;
+        for(int r = 0; r < reps; ++r)
+        {
+            if(r == reps * 3 / 4)
+                cudaEventRecord(e0, st);
+            launch(iters);
+        }
+        cudaEventRecord(e1, st);
+        cudaEventSynchronize(e1);
+        cudaEventElapsedTime(&ms, e0, e1);
+        out4[shape] = ops * (reps - reps * 3 / 4) / (ms * 1e-3);
+        err = cudaGetLastError();
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return err;
+}
+namespace
+{
 } // namespace
 
 static int mma_debug()
@@ -506,7 +628,13 @@ cudaError_t configure_mma_kernels()
     cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if(e != cudaSuccess)
         return e;
-    return cudaFuncSetAttribute(k_knn2_mma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    e = cudaFuncSetAttribute(k_knn2_mma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaFuncSetAttribute(k_peak_i8<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (MMA_M + 128) * ROW_BYTES + 64);
+    if(e != cudaSuccess)
+        return e;
+    return cudaFuncSetAttribute(k_peak_i8<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (MMA_M + 256) * ROW_BYTES + 64);
 }
 int knn_mma_pad(int cap)
 {

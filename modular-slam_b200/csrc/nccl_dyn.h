@@ -28,6 +28,7 @@ struct NcclApi
     ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
     ncclResult_t (*CommCount)(const ncclComm_t, int*) = nullptr;
     ncclResult_t (*CommUserRank)(const ncclComm_t, int*) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -67,6 +68,7 @@ inline NcclApi& nccl_api()
     MSLAM_NCCL_SYM(GetUniqueId, "ncclGetUniqueId")
     MSLAM_NCCL_SYM(CommInitRank, "ncclCommInitRank")
     MSLAM_NCCL_SYM(CommDestroy, "ncclCommDestroy")
+    MSLAM_NCCL_SYM(CommAbort, "ncclCommAbort")
     MSLAM_NCCL_SYM(CommCount, "ncclCommCount")
     MSLAM_NCCL_SYM(CommUserRank, "ncclCommUserRank")
     MSLAM_NCCL_SYM(AllGather, "ncclAllGather")

@@ -6,6 +6,9 @@
 // All float stages use explicit round-to-nearest intrinsics so that nvcc can never contract them into
 // FMAs (the reference path is non-FMA float except the 7x7 blur, which is an explicit FMA chain).
 #include <stdlib.h>
+#include <string.h>
+
+#include <cuda.h> // CUtensorMap types only; the encoder is fetched through cudaGetDriverEntryPoint
 
 #include "common.cuh"
 #include "kernels.h"
@@ -385,8 +388,8 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
 // =================================================================================================
 constexpr int FS_SW = 128, FS_SH_MAX = 64;      // scored positions per CTA: 128 x (32 | 64), LevelDesc::tile_sh rows
 constexpr int FS_IW = FS_SW - 4;                // assigned interior: 124 x (tile_sh - 2)
-constexpr int FS_PW = FS_SW + 8, FS_PH_MAX = FS_SH_MAX + 6; // staged pixels
-constexpr int FS_PWW = FS_PW / 4;               // staged words per row (34)
+constexpr int FS_PW = FS_SW + 16, FS_PH_MAX = FS_SH_MAX + 6; // staged pixels: 136 are used, 144 is the next multiple of 16 (TMA box rows)
+constexpr int FS_PWW = FS_PW / 4;               // staged words per row (36)
 
 __device__ __forceinline__ unsigned lop3_maj_a_nb_c(unsigned a, unsigned b, unsigned c)
 {
@@ -479,11 +482,37 @@ __device__ __forceinline__ unsigned corner_score2(const uint8_t* ca, const uint8
     return v - m - 0x00010001u; // both lanes are >= fast_thr - 1 >= 0: no borrow crosses the lanes
 }
 
-__global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, int l_begin, int l_end,
+__device__ __forceinline__ unsigned fast_smem_u32(const void* p)
+{
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void fast_mbar_init(unsigned bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+// bounded wait: a protocol error becomes a trap (a CUDA error on the host), never a hung GPU
+__device__ __forceinline__ void fast_mbar_wait(unsigned bar, unsigned parity)
+{
+    for(unsigned spins = 0;; ++spins)
+    {
+        unsigned ok;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+        if(ok)
+            return;
+        if(spins > (1u << 24))
+            __trap();
+    }
+}
+
+__global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, const __grid_constant__ FastMaps M, int l_begin, int l_end,
                                               const uint8_t* __restrict__ pyr, unsigned* __restrict__ cand,
                                               LevelCounters* __restrict__ ctr, unsigned* __restrict__ hist)
 {
-    __shared__ __align__(16) uint8_t s_px[FS_PH_MAX][FS_PW];
+    __shared__ __align__(128) uint8_t s_px[FS_PH_MAX][FS_PW];
+    __shared__ __align__(8) unsigned long long s_bar;
     __shared__ __align__(16) uint8_t s_sc[FS_SH_MAX][FS_SW];
     __shared__ unsigned short s_q[FS_SH_MAX * FS_SW];
     __shared__ unsigned s_out[FS_IW * (FS_SH_MAX - 2) / 4 + 64];
@@ -507,38 +536,17 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     const int px0 = sx0 - 4, py0 = sy0 - 3;         // first staged pixel
     const uint8_t* img = pyr + L.img_off + (long long)b * L.img_frame_stride;
 
+    // ---- tile staging: ONE 3-D bulk-tensor (TMA) load per CTA -- box = 144 x PH x 1 of the level's (pitch, h, frame) plane
+    // stack, zero-filled past the image / the row pitch (what the per-word guards of the earlier version did by hand) ----
+    if(tid == 0)
     {
-        // all of the thread's tile words are requested before the first one is stored: one exposed load latency per CTA
-        constexpr int NLD = (FS_PH_MAX * FS_PWW + 255) / 256;
-        unsigned v[NLD];
-        // word i = tid + 256 k of the tile is (row r, word c): 256 = 7 * 34 + 18, so a step of k moves 7 rows and 18 words
-        // (one division per thread instead of one per word); rows past the tile / the image and words past the row pitch
-        // read as 0
-        static_assert(256 / FS_PWW == 7 && 256 % FS_PWW == 18, "staging walk assumes 34-word rows");
-        int r = tid / FS_PWW, c = tid - r * FS_PWW;
-        const int rows_ok = min(PH, L.h - py0);                    // staged rows that exist in the image
-        const int words_ok = (L.pitch - px0 + 3) >> 2;             // gx < pitch  <=>  c < words_ok
-        const unsigned* gp = reinterpret_cast<const unsigned*>(img + (long long)(py0 + r) * L.pitch + px0) + c;
-        const int row_words = L.pitch >> 2;                        // pitch is a multiple of 64
-#pragma unroll
-        for(int k = 0; k < NLD; ++k)
-        {
-            v[k] = 0;
-            if(r < rows_ok && c < words_ok)
-                v[k] = __ldg(gp);
-            c += 18, r += 7, gp += 7 * row_words + 18;
-            if(c >= FS_PWW)
-                c -= FS_PWW, r += 1, gp += row_words - FS_PWW;
-        }
-#pragma unroll
-        for(int k = 0; k < NLD; ++k)
-        {
-            const int i = tid + 256 * k;
-            if(i < PH * FS_PWW)
-            {
-                reinterpret_cast<unsigned*>(&s_px[0][0])[i] = v[k];
-            }
-        }
+        fast_mbar_init(fast_smem_u32(&s_bar), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fast_smem_u32(&s_bar)), "r"(PH * FS_PW) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                     ::"r"(fast_smem_u32(&s_px[0][0])), "l"(reinterpret_cast<const void*>(&M.m[l][0])), "r"(px0), "r"(py0), "r"(b),
+                     "r"(fast_smem_u32(&s_bar))
+                     : "memory");
     }
     for(int i = tid; i < SH * FS_SW / 16; i += 256)
         reinterpret_cast<uint4*>(&s_sc[0][0])[i] = make_uint4(0, 0, 0, 0);
@@ -547,7 +555,8 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         s_qn = 0;
         s_on = 0;
     }
-    __syncthreads();
+    __syncthreads(); // also publishes the barrier's initialisation to the waiting threads
+    fast_mbar_wait(fast_smem_u32(&s_bar), 0);
 
     // ---- phase A: classify 4 rows x 4 pixels per thread and pass (32 rows per pass) ----
 #pragma unroll 1
@@ -1247,15 +1256,54 @@ void fast_tiles(int w, int h, int edge, int* tx, int* ty, int* tile_sh)
 }
 
 // levels [l_begin, l_end) in one launch
+// tensor maps of the FAST tile loads: level l = a 3-D u8 tensor (pitch, h, max_batch) with strides (pitch, frame stride),
+// box (FS_PW, tile_sh + 6, 1).  cuTensorMapEncodeTiled is fetched through the runtime (no link against libcuda).
+cudaError_t build_fast_maps(const PipeParams& P, const uint8_t* pyr, int max_batch, FastMaps* out)
+{
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if(!encode)
+    {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if(e != cudaSuccess)
+            return e;
+        if(!fn || q != cudaDriverEntryPointSuccess)
+            return cudaErrorNotSupported;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    static_assert(sizeof(CUtensorMap) == 128, "FastMaps holds raw CUtensorMap bytes");
+    memset(out, 0, sizeof(*out));
+    for(int l = 0; l < P.nlevels; ++l)
+    {
+        const LevelDesc& L = P.lv[l];
+        if(L.tiles_x * L.tiles_y == 0)
+            continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.h, (cuuint64_t)max_batch};
+        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.img_frame_stride};
+        const cuuint32_t box[3] = {(cuuint32_t)FS_PW, (cuuint32_t)(L.tile_sh + 6), 1u};
+        const cuuint32_t estr[3] = {1u, 1u, 1u};
+        const CUresult r = encode(reinterpret_cast<CUtensorMap*>(&out->m[l][0]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3,
+                                  const_cast<uint8_t*>(pyr) + L.img_off, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if(r != CUDA_SUCCESS)
+            return cudaErrorInvalidValue;
+    }
+    return cudaSuccess;
+}
+
 void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCounters* ctr, unsigned* hist,
-                 const PipeParams& P, int l_begin, int l_end, long long* launches)
+                 const PipeParams& P, const FastMaps& maps, int l_begin, int l_end, long long* launches)
 {
     int tiles = 0;
     for(int l = l_begin; l < l_end; ++l)
         tiles += P.lv[l].tiles_x * P.lv[l].tiles_y;
     if(tiles <= 0)
         return;
-    k_fast<<<dim3(tiles, P.n_frames), 256, 0, st>>>(P, l_begin, l_end, pyr, cand, ctr, hist);
+    k_fast<<<dim3(tiles, P.n_frames), 256, 0, st>>>(P, maps, l_begin, l_end, pyr, cand, ctr, hist);
     ++*launches;
 }
 

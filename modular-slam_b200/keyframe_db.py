@@ -74,6 +74,11 @@ class ShardedKeyframeDb:
                 unique_id = broadcast_unique_id(rank, group, dev)
             ctx.db_attach(rank, world, unique_id)
 
+    def close(self):
+        """leave the communicator (call on every rank once the last query has completed)"""
+        self.ctx.synchronize()
+        self.ctx.db_detach()
+
     def load_shard(self, d_db, d_counts, id_base):
         """d_db: uint8 CUDA tensor [n_local][cap][32] (n_local may be 0); d_counts: int32 CUDA tensor [n_local]"""
         if d_db.dtype != torch.uint8 or d_db.dim() != 3 or d_db.shape[2] != 32 or not d_db.is_cuda:
