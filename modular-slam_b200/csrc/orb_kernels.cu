@@ -388,8 +388,11 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
 // =================================================================================================
 constexpr int FS_SW = 128, FS_SH_MAX = 64;      // scored positions per CTA: 128 x (32 | 64), LevelDesc::tile_sh rows
 constexpr int FS_IW = FS_SW - 4;                // assigned interior: 124 x (tile_sh - 2)
-constexpr int FS_PW = FS_SW + 16, FS_PH_MAX = FS_SH_MAX + 6; // staged pixels: 136 are used, 144 is the next multiple of 16 (TMA box rows)
-constexpr int FS_PWW = FS_PW / 4;               // staged words per row (36)
+// staged pixels: 136 columns are used.  The innermost coordinate of a tiled TMA load must be a multiple of 16 BYTES (measured:
+// tools/tma_probe.cu -- x0 = 24 raises cudaErrorIllegalInstruction, 32 is fine), and a tile starts at column 24 + 124 tx, so
+// the box starts at that rounded down to 16 (up to 12 columns early) and is 160 wide
+constexpr int FS_PW = FS_SW + 32, FS_PH_MAX = FS_SH_MAX + 6;
+constexpr int FS_PWW = FS_PW / 4;               // staged words per row (40)
 
 __device__ __forceinline__ unsigned lop3_maj_a_nb_c(unsigned a, unsigned b, unsigned c)
 {
@@ -491,7 +494,7 @@ __device__ __forceinline__ void fast_mbar_init(unsigned bar, unsigned count)
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
 // bounded wait: a protocol error becomes a trap (a CUDA error on the host), never a hung GPU
-__device__ __forceinline__ void fast_mbar_wait(unsigned bar, unsigned parity)
+__device__ __forceinline__ void fast_mbar_wait(unsigned bar, unsigned parity, int dbg = 0)
 {
     for(unsigned spins = 0;; ++spins)
     {
@@ -503,11 +506,15 @@ __device__ __forceinline__ void fast_mbar_wait(unsigned bar, unsigned parity)
         if(ok)
             return;
         if(spins > (1u << 24))
+        {
+            if(dbg & 1)
+                return; // debugging aid (MSLAM_FAST_DBG=1): carry on with whatever the tile holds instead of trapping
             __trap();
+        }
     }
 }
 
-__global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, const __grid_constant__ FastMaps M, int l_begin, int l_end,
+__global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, const __grid_constant__ FastMaps M, const FastMaps* __restrict__ gmaps, int dbg, int l_begin, int l_end,
                                               const uint8_t* __restrict__ pyr, unsigned* __restrict__ cand,
                                               LevelCounters* __restrict__ ctr, unsigned* __restrict__ hist)
 {
@@ -533,10 +540,11 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     const int sx0 = ((edge - 1) & ~3) + FS_IW * tx; // first scored column (multiple of 4)
     const int SH = L.tile_sh, PH = SH + 6;         // scored / staged rows of this level's tiles
     const int sy0 = edge - 1 + (SH - 2) * ty;       // first scored row
-    const int px0 = sx0 - 4, py0 = sy0 - 3;         // first staged pixel
+    const int px0 = sx0 - 4, py0 = sy0 - 3;         // first pixel the tile needs
+    const int px0a = px0 & ~15, xo = px0 - px0a;    // first staged column (16-byte aligned for the TMA) and where px0 sits in it
     const uint8_t* img = pyr + L.img_off + (long long)b * L.img_frame_stride;
 
-    // ---- tile staging: ONE 3-D bulk-tensor (TMA) load per CTA -- box = 144 x PH x 1 of the level's (pitch, h, frame) plane
+    // ---- tile staging: ONE 3-D bulk-tensor (TMA) load per CTA -- box = 160 x PH x 1 of the level's (pitch, h, frame) plane
     // stack, zero-filled past the image / the row pitch (what the per-word guards of the earlier version did by hand) ----
     if(tid == 0)
     {
@@ -544,7 +552,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fast_smem_u32(&s_bar)), "r"(PH * FS_PW) : "memory");
         asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-                     ::"r"(fast_smem_u32(&s_px[0][0])), "l"(reinterpret_cast<const void*>(&M.m[l][0])), "r"(px0), "r"(py0), "r"(b),
+                     ::"r"(fast_smem_u32(&s_px[0][0])), "l"(gmaps ? reinterpret_cast<const void*>(&gmaps->m[l][0]) : reinterpret_cast<const void*>(&M.m[l][0])), "r"(px0a), "r"(py0), "r"(b),
                      "r"(fast_smem_u32(&s_bar))
                      : "memory");
     }
@@ -556,7 +564,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         s_on = 0;
     }
     __syncthreads(); // also publishes the barrier's initialisation to the waiting threads
-    fast_mbar_wait(fast_smem_u32(&s_bar), 0);
+    fast_mbar_wait(fast_smem_u32(&s_bar), 0, dbg);
 
     // ---- phase A: classify 4 rows x 4 pixels per thread and pass (32 rows per pass) ----
 #pragma unroll 1
@@ -568,7 +576,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     {
         const unsigned t4 = (unsigned)thr * 0x01010101u;
         const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
-        const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[rb][0]) + lane;
+        const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[rb][0]) + lane + (xo >> 2);
         unsigned wm[10], w0[10], wp[10]; // staged rows 4 * warp .. 4 * warp + 9, words lane, lane + 1, lane + 2
 #pragma unroll
         for(int r = 0; r < 10; ++r)
@@ -648,7 +656,7 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
         const unsigned ea = s_q[j], eb = s_q[min(j + 1, nq - 1)];
         const int ia = ea & 0x1fff, ib = eb & 0x1fff;
         const int ya = ia / FS_SW, xa = ia - ya * FS_SW, yb = ib / FS_SW, xb = ib - yb * FS_SW;
-        const unsigned sc = corner_score2(&s_px[ya + 3][xa + 4], &s_px[yb + 3][xb + 4], ea & 0x2000u, eb & 0x2000u);
+        const unsigned sc = corner_score2(&s_px[ya + 3][xa + 4 + xo], &s_px[yb + 3][xb + 4 + xo], ea & 0x2000u, eb & 0x2000u);
         s_sc[ya][xa] = (uint8_t)(sc & 0xffu);
         s_sc[yb][xb] = (uint8_t)(sc >> 16);
     }
@@ -1303,7 +1311,20 @@ void launch_fast(cudaStream_t st, const uint8_t* pyr, unsigned* cand, LevelCount
         tiles += P.lv[l].tiles_x * P.lv[l].tiles_y;
     if(tiles <= 0)
         return;
-    k_fast<<<dim3(tiles, P.n_frames), 256, 0, st>>>(P, maps, l_begin, l_end, pyr, cand, ctr, hist);
+    static int dbg = -1;
+    static FastMaps* d_maps = nullptr;
+    if(dbg < 0)
+    {
+        const char* e = getenv("MSLAM_FAST_DBG"); // 1: no trap on a lost tile load, 2: tensor maps read from global memory
+        dbg = e ? atoi(e) : 0;
+    }
+    if(dbg & 2)
+    {
+        if(!d_maps)
+            cudaMalloc(&d_maps, sizeof(FastMaps));
+        cudaMemcpyAsync(d_maps, &maps, sizeof(FastMaps), cudaMemcpyHostToDevice, st);
+    }
+    k_fast<<<dim3(tiles, P.n_frames), 256, 0, st>>>(P, maps, (dbg & 2) ? d_maps : nullptr, dbg, l_begin, l_end, pyr, cand, ctr, hist);
     ++*launches;
 }
 
