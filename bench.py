@@ -460,6 +460,23 @@ def main():
             dist.destroy_process_group()
         return
 
+    # ---- the same end-to-end path through the C++ plugin classes (host/orb_b200_plugin.hpp), timed by a C++ loop:
+    # what a user of the reference's IFeatureDetector / IFeatureMatcher gets, one frame at a time and in pipelined batches ----
+    plugin = None
+    driver = os.path.join(graft.PKG_DIR, "lib", "plugin_host_test")
+    if args.workload == "c2" and not args.no_sub and os.path.exists(driver):
+        try:
+            with tempfile.TemporaryDirectory() as td:
+                raw = os.path.join(td, "frames.raw")
+                with open(raw, "wb") as f:
+                    for fr in frames:
+                        f.write(np.ascontiguousarray(fr).tobytes())
+                out = subprocess.run([driver, "bench", raw, str(W), str(H), str(B), str(T), str(args.steps)], capture_output=True,
+                                     text=True, timeout=180)  # rank 0 only: the plugin's default device 0 is this rank's GPU
+                plugin = json.loads(out.stdout.strip().splitlines()[-1]) if out.returncode == 0 else {"error": (out.stderr or out.stdout)[-300:], "rc": out.returncode}
+        except Exception as ex:  # noqa: BLE001
+            plugin = {"error": repr(ex)[:300]}
+
     # ---- roofline of the dominant kernel group ---------------------------------------------------------------------------
     pk, pk_kind = peaks()
     det_stages = {k: v for k, v in stage.items() if v[1] > 0}
@@ -560,6 +577,8 @@ def main():
                                     "note": "one blocking detect_batch + one blocking match_batch per step"}},
             "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "natural_frames": natural}
+    if plugin:
+        line["e2e"].update(plugin)
     line.update(sub)
     print(json.dumps(line))
     ctx.close()

@@ -32,7 +32,7 @@ class OrbB200Context
         cfg.device = o.device;
         cfg.max_width = o.maxWidth;
         cfg.max_height = o.maxHeight;
-        cfg.max_batch = kMaxBatch;
+        cfg.max_batch = maxBatch = o.maxBatch > 0 ? o.maxBatch : 8;
         cfg.nfeatures = o.nfeatures;
         cfg.nlevels = o.nlevels;
         cfg.scale_factor = o.scaleFactor;
@@ -58,7 +58,7 @@ class OrbB200Context
         reported = true;
     }
 
-    static constexpr int kMaxBatch = 8;
+    int maxBatch = 8; // frames per batched call: OrbB200Options::maxBatch (plugin_config.json "maxBatch")
     OrbB200Options options;
     mslam_b200_ctx* handle = nullptr;
     int kpCapacity = 0, descCapacity = 0;
@@ -104,7 +104,7 @@ static bool sameOptions(const OrbB200Options& a, const OrbB200Options& b)
 {
     return a.device == b.device && a.maxWidth == b.maxWidth && a.maxHeight == b.maxHeight && a.nfeatures == b.nfeatures &&
            a.nlevels == b.nlevels && a.scaleFactor == b.scaleFactor && a.fastThreshold == b.fastThreshold &&
-           a.ratio == b.ratio && a.maxDescriptors == b.maxDescriptors;
+           a.ratio == b.ratio && a.maxDescriptors == b.maxDescriptors && a.maxBatch == b.maxBatch;
 }
 
 // detector and matcher built with the same options share one context (one stream, one set of HBM buffers)
@@ -124,8 +124,8 @@ OrbB200Detector::OrbB200Detector() : OrbB200Detector(defaultOrbB200Options()) {}
 
 OrbB200Detector::OrbB200Detector(const OrbB200Options& options) : ctx(acquireContext(options))
 {
-    kpBuf.resize((size_t)ctx->kpCapacity * OrbB200Context::kMaxBatch);
-    descBuf.resize((size_t)ctx->kpCapacity * OrbB200Context::kMaxBatch * MSLAM_B200_DESC_BYTES);
+    kpBuf.resize((size_t)ctx->kpCapacity * ctx->maxBatch);
+    descBuf.resize((size_t)ctx->kpCapacity * ctx->maxBatch * MSLAM_B200_DESC_BYTES);
 }
 
 OrbB200Detector::~OrbB200Detector() = default;
@@ -166,11 +166,12 @@ std::vector<std::vector<OrbKeypoint>> OrbB200Detector::detectBatch(const std::ve
 {
     std::vector<std::vector<OrbKeypoint>> result(frames.size());
     std::lock_guard<std::mutex> lock(ctx->mutex);
-    for(size_t base = 0; base < frames.size(); base += OrbB200Context::kMaxBatch)
+    std::vector<const std::uint8_t*> ptrs((size_t)ctx->maxBatch);
+    std::vector<int> counts((size_t)ctx->maxBatch);
+    for(size_t base = 0; base < frames.size(); base += (size_t)ctx->maxBatch)
     {
-        const int nb = (int)std::min<size_t>(OrbB200Context::kMaxBatch, frames.size() - base);
+        const int nb = (int)std::min<size_t>((size_t)ctx->maxBatch, frames.size() - base);
         const int w = frames[base]->size.width, h = frames[base]->size.height;
-        const std::uint8_t* ptrs[OrbB200Context::kMaxBatch];
         bool uniform = w > 0 && h > 0;
         for(int i = 0; i < nb; ++i)
         {
@@ -180,9 +181,9 @@ std::vector<std::vector<OrbKeypoint>> OrbB200Detector::detectBatch(const std::ve
         }
         if(!uniform)
             continue; // frames of one batch must share a size; callers mix sizes through detect()
-        int counts[OrbB200Context::kMaxBatch] = {0};
-        const int rc = mslam_b200_detect_batch(ctx->handle, ptrs, nb, w, h, 3 * w, kpBuf.data(), descBuf.data(),
-                                               ctx->kpCapacity, counts);
+        std::fill(counts.begin(), counts.end(), 0);
+        const int rc = mslam_b200_detect_batch(ctx->handle, ptrs.data(), nb, w, h, 3 * w, kpBuf.data(), descBuf.data(),
+                                               ctx->kpCapacity, counts.data());
         if(rc != MSLAM_B200_OK && rc != MSLAM_B200_E_CAPACITY)
         {
             ctx->report("detectBatch", rc);
@@ -194,6 +195,66 @@ std::vector<std::vector<OrbKeypoint>> OrbB200Detector::detectBatch(const std::ve
                           counts[i] < ctx->kpCapacity ? counts[i] : ctx->kpCapacity, &result[base + (size_t)i]);
     }
     return result;
+}
+
+// ---- the throughput path: flat pinned results, two batches in flight --------------------------------------------------
+OrbB200BatchResult::OrbB200BatchResult(int maxFrames_, int capacity_) : maxFrames(maxFrames_), capacity(capacity_)
+{
+    void *a = nullptr, *b = nullptr, *c = nullptr;
+    const size_t n = (size_t)maxFrames * capacity;
+    if(maxFrames < 1 || capacity < 1 || mslam_b200_host_alloc(&a, n * sizeof(mslam_b200_keypoint)) != MSLAM_B200_OK ||
+       mslam_b200_host_alloc(&b, n * MSLAM_B200_DESC_BYTES) != MSLAM_B200_OK ||
+       mslam_b200_host_alloc(&c, (size_t)maxFrames * sizeof(int)) != MSLAM_B200_OK)
+    {
+        mslam_b200_host_free(a), mslam_b200_host_free(b), mslam_b200_host_free(c);
+        throw std::runtime_error("OrbB200BatchResult: pinned host allocation failed (no CUDA runtime?)");
+    }
+    kp = static_cast<mslam_b200_keypoint*>(a), desc = static_cast<std::uint8_t*>(b), counts = static_cast<int*>(c);
+    std::memset(counts, 0, (size_t)maxFrames * sizeof(int));
+}
+
+OrbB200BatchResult::~OrbB200BatchResult()
+{
+    mslam_b200_host_free(kp), mslam_b200_host_free(desc), mslam_b200_host_free(counts);
+}
+
+std::vector<OrbKeypoint> OrbB200BatchResult::keypoints(int frame) const
+{
+    std::vector<OrbKeypoint> out;
+    if(frame >= 0 && frame < nFrames)
+        fillKeypoints(raw(frame), descriptors(frame), count(frame), &out);
+    return out;
+}
+
+int OrbB200Detector::maxBatch() const { return ctx->maxBatch; }
+int OrbB200Detector::keypointCapacity() const { return ctx->kpCapacity; }
+
+bool OrbB200Detector::detectBatchBegin(const std::uint8_t* const* frames, int nFrames, int width, int height, OrbB200BatchResult* out)
+{
+    if(!frames || !out || nFrames < 1 || nFrames > ctx->maxBatch || nFrames > out->maxFrames || out->capacity != ctx->kpCapacity)
+        return false;
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    const int rc = mslam_b200_detect_batch_begin(ctx->handle, frames, nFrames, width, height, 3 * width, out->kp, out->desc,
+                                                 out->capacity, out->counts);
+    if(rc != MSLAM_B200_OK)
+    {
+        ctx->report("detectBatchBegin", rc);
+        return false;
+    }
+    out->nFrames = nFrames;
+    return true;
+}
+
+bool OrbB200Detector::detectBatchEnd()
+{
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    const int rc = mslam_b200_detect_batch_end(ctx->handle);
+    if(rc != MSLAM_B200_OK && rc != MSLAM_B200_E_CAPACITY)
+    {
+        ctx->report("detectBatchEnd", rc);
+        return false;
+    }
+    return true;
 }
 
 // ---- second detector ---------------------------------------------------------------------------------------------
@@ -248,7 +309,81 @@ OrbB200Matcher::OrbB200Matcher() : OrbB200Matcher(defaultOrbB200Options()) {}
 
 OrbB200Matcher::OrbB200Matcher(const OrbB200Options& options) : ctx(acquireContext(options)) {}
 
-OrbB200Matcher::~OrbB200Matcher() = default;
+OrbB200Matcher::~OrbB200Matcher()
+{
+    mslam_b200_host_free(mA), mslam_b200_host_free(mB), mslam_b200_host_free(mD), mslam_b200_host_free(mN);
+}
+
+bool OrbB200Matcher::ensureBatchBuffers()
+{
+    if(mA)
+        return true;
+    void* p[4] = {nullptr, nullptr, nullptr, nullptr};
+    const size_t n = (size_t)ctx->maxBatch * ctx->kpCapacity * sizeof(int);
+    bool ok = true;
+    for(int i = 0; i < 4; ++i)
+        ok = ok && mslam_b200_host_alloc(&p[i], i < 3 ? n : (size_t)ctx->maxBatch * sizeof(int)) == MSLAM_B200_OK;
+    if(!ok)
+    {
+        for(void* q : p)
+            mslam_b200_host_free(q);
+        return false;
+    }
+    mA = static_cast<int*>(p[0]), mB = static_cast<int*>(p[1]), mD = static_cast<int*>(p[2]), mN = static_cast<int*>(p[3]);
+    return true;
+}
+
+bool OrbB200Matcher::matchBatchBegin(const OrbB200BatchResult& first, const OrbB200BatchResult& second)
+{
+    const int P = first.frames(), cap = first.capacity;
+    if(P < 1 || P != second.frames() || cap != second.capacity || P > ctx->maxBatch || cap > ctx->descCapacity || cap != ctx->kpCapacity)
+        return false;
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if(pendingPairs || !ensureBatchBuffers())
+        return false;
+    // the C ABI's batch form: mode 0 = knn + ratio, out_a = fromIndex (index into `first`), out_b = toIndex (into `second`)
+    const int rc = mslam_b200_match_batch_begin(ctx->handle, 0, first.desc, first.counts, second.desc, second.counts, P, cap, mA, mB, mD, mN);
+    if(rc != MSLAM_B200_OK)
+    {
+        ctx->report("matchBatchBegin", rc);
+        return false;
+    }
+    pendingPairs = P, pendingCap = cap;
+    return true;
+}
+
+bool OrbB200Matcher::matchBatchEnd(std::vector<std::vector<DescriptorMatch>>* out)
+{
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if(!pendingPairs || !out)
+        return false;
+    const int P = pendingPairs, cap = pendingCap;
+    pendingPairs = 0;
+    const int rc = mslam_b200_match_batch_end(ctx->handle);
+    if(rc != MSLAM_B200_OK)
+    {
+        ctx->report("matchBatchEnd", rc);
+        return false;
+    }
+    out->resize((size_t)P);
+    for(int i = 0; i < P; ++i)
+    {
+        std::vector<DescriptorMatch>& m = (*out)[(size_t)i];
+        m.resize((size_t)mN[i]);
+        for(int j = 0; j < mN[i]; ++j)
+        {
+            m[(size_t)j].fromIndex = (std::size_t)mA[(size_t)i * cap + j];
+            m[(size_t)j].toIndex = (std::size_t)mB[(size_t)i * cap + j];
+        }
+    }
+    return true;
+}
+
+bool OrbB200Matcher::matchBatch(const OrbB200BatchResult& first, const OrbB200BatchResult& second,
+                                std::vector<std::vector<DescriptorMatch>>* out)
+{
+    return matchBatchBegin(first, second) && matchBatchEnd(out);
+}
 
 std::vector<DescriptorMatch> OrbB200Matcher::match(const std::vector<OrbKeypoint>& from, const std::vector<OrbKeypoint>& to)
 {

@@ -273,6 +273,7 @@ bool parsePluginConfig(const std::string& jsonText, std::vector<PluginEntry>* ou
             v = o.maxWidth;      if(!numberField(*prm, "maxWidth", 1, 4095, &v, &err)) return false;      o.maxWidth = (int)v;
             v = o.maxHeight;     if(!numberField(*prm, "maxHeight", 1, 4095, &v, &err)) return false;     o.maxHeight = (int)v;
             v = o.nfeatures;     if(!numberField(*prm, "nfeatures", 1, 65535, &v, &err)) return false;    o.nfeatures = (int)v;
+            v = o.maxBatch;      if(!numberField(*prm, "maxBatch", 1, 4096, &v, &err)) return false;      o.maxBatch = (int)v;
             v = o.nlevels;       if(!numberField(*prm, "nlevels", 1, MSLAM_B200_MAX_LEVELS, &v, &err)) return false; o.nlevels = (int)v;
             v = o.scaleFactor;   if(!numberField(*prm, "scaleFactor", 1.0001, 4.0, &v, &err)) return false; o.scaleFactor = (float)v;
             v = o.fastThreshold; if(!numberField(*prm, "fastThreshold", 1, 254, &v, &err)) return false;  o.fastThreshold = (int)v;

@@ -11,9 +11,14 @@
 //   plugin_host_test db      <in.bin> <out.bin> [rank world idfile]   (ShardedKeyframeDbB200; in.bin = i32 K, n, Q, k, then
 //                            K x n x 32 keyframe descriptor bytes, Q x n x 32 query bytes; out.bin = Q x k x (i64 id, i32 score,
 //                            i32 pad); with world > 1 each process is one rank on device `rank`, rank 0 writes the NCCL id to idfile)
+//   plugin_host_test bench   <frames.raw> <W> <H> <B> <T> <iters>   (C++ timing loops through the plugin classes; frames.raw =
+//                            (T + 1) batches x B frames x H x W x 3 bytes, batch t = frame t of B sequences.  Prints one JSON
+//                            object: per-frame detect + match of one sequence -- what RgbdFeatureFrontend does,
+//                            rgbd_feature_frontend.cpp:187,237 -- and B-frame pipelined batches from pinned memory)
 //   plugin_host_test run     <plugin.so> <frame0.raw> <frame1.raw> <W> <H> <out.bin> [detector alias]
 #include <dlfcn.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -68,6 +73,106 @@ int main(int argc, char** argv)
             std::printf("library=%s detector=%s matcher=%s nfeatures=%d nlevels=%d scaleFactor=%.3f fastThreshold=%d ratio=%.3f\n",
                         e.library.c_str(), e.detectorFactory.c_str(), e.matcherFactory.c_str(), e.options.nfeatures,
                         e.options.nlevels, e.options.scaleFactor, e.options.fastThreshold, e.options.ratio);
+        return 0;
+    }
+    if(argc >= 8 && !std::strcmp(argv[1], "bench"))
+    {
+        const int W = std::atoi(argv[3]), H = std::atoi(argv[4]), B = std::atoi(argv[5]), T = std::atoi(argv[6]), iters = std::atoi(argv[7]);
+        const size_t frameBytes = (size_t)W * H * 3, batchBytes = frameBytes * (size_t)B;
+        std::vector<std::uint8_t> raw;
+        if(W < 1 || H < 1 || B < 1 || T < 1 || iters < 1 || !readFile(argv[2], &raw) || raw.size() < batchBytes * (size_t)(T + 1))
+            return 5;
+        try
+        {
+            using clock = std::chrono::steady_clock;
+            mslam::OrbB200Options o;
+            o.maxWidth = W, o.maxHeight = H, o.maxBatch = B;
+            mslam::OrbB200Detector detector(o);
+            mslam::OrbB200Matcher matcher(o);
+            // ---- (1) one frame at a time, as the reference's front-end calls the interfaces ----
+            std::vector<mslam::RgbFrame> seq((size_t)T + 1);
+            for(int t = 0; t <= T; ++t)
+            {
+                seq[(size_t)t].size = mslam::Size{W, H};
+                seq[(size_t)t].data.assign(raw.data() + batchBytes * (size_t)t, raw.data() + batchBytes * (size_t)t + frameBytes);
+            }
+            std::vector<mslam::OrbKeypoint> prev = detector.detect(seq[0]), cur;
+            size_t matches = 0, keypoints = 0;
+            const int singleIters = iters * 8;
+            double singleMs = 0;
+            for(int pass = 0; pass < 2; ++pass) // pass 0 warms up (kernel graph capture, first-touch)
+            {
+                const auto t0 = clock::now();
+                for(int i = 0; i < (pass ? singleIters : 16); ++i)
+                {
+                    cur = detector.detect(seq[(size_t)(1 + i % T)]);
+                    const std::vector<mslam::DescriptorMatch> m = matcher.match(cur, prev); // rgbd_feature_frontend.cpp:237
+                    matches = m.size(), keypoints = cur.size();
+                    prev.swap(cur);
+                }
+                singleMs = std::chrono::duration<double, std::milli>(clock::now() - t0).count();
+            }
+            // ---- (2) B-frame batches from pinned memory, two detect batches in flight, match between them ----
+            void* pinned = nullptr;
+            if(mslam_b200_host_alloc(&pinned, batchBytes * (size_t)(T + 1)) != MSLAM_B200_OK)
+                return 7;
+            std::memcpy(pinned, raw.data(), batchBytes * (size_t)(T + 1));
+            std::vector<std::vector<const std::uint8_t*>> ptrs((size_t)T + 1, std::vector<const std::uint8_t*>((size_t)B));
+            for(int t = 0; t <= T; ++t)
+                for(int b = 0; b < B; ++b)
+                    ptrs[(size_t)t][(size_t)b] = static_cast<const std::uint8_t*>(pinned) + batchBytes * (size_t)t + frameBytes * (size_t)b;
+            std::vector<std::unique_ptr<mslam::OrbB200BatchResult>> sets;
+            for(int i = 0; i < 4; ++i)
+                sets.emplace_back(new mslam::OrbB200BatchResult(B, detector.keypointCapacity()));
+            std::vector<std::vector<mslam::DescriptorMatch>> bm;
+            size_t batchMatches = 0, batchKeypoints = 0;
+            bool ok = detector.detectBatchBegin(ptrs[0].data(), B, W, H, sets[3].get()) && detector.detectBatchEnd(); // "previous"
+            long long step = 0;
+            auto runPipelined = [&](int n) {
+                const long long base = step;
+                for(long long j = base; j < base + std::min(2, n); ++j)
+                    ok = ok && detector.detectBatchBegin(ptrs[(size_t)(1 + j % T)].data(), B, W, H, sets[(size_t)(j % 4)].get());
+                for(long long i = base; i < base + n; ++i)
+                {
+                    ok = ok && detector.detectBatchEnd();
+                    const mslam::OrbB200BatchResult &c = *sets[(size_t)(i % 4)], &p = *sets[(size_t)((i + 3) % 4)];
+                    ok = ok && matcher.matchBatchBegin(c, p);
+                    if(i + 2 < base + n)
+                        ok = ok && detector.detectBatchBegin(ptrs[(size_t)(1 + (i + 2) % T)].data(), B, W, H, sets[(size_t)((i + 2) % 4)].get());
+                    ok = ok && matcher.matchBatchEnd(&bm);
+                    batchMatches = 0, batchKeypoints = 0;
+                    for(int b = 0; ok && b < B; ++b)
+                        batchMatches += bm[(size_t)b].size(), batchKeypoints += (size_t)c.count(b);
+                }
+                step = base + n;
+            };
+            runPipelined(3);
+            const auto t1 = clock::now();
+            runPipelined(iters);
+            const double batchMs = std::chrono::duration<double, std::milli>(clock::now() - t1).count();
+            // a converted frame of the batched path equals the per-frame call on the same image
+            const int lastT = (int)(1 + (step - 1) % T);
+            const std::vector<mslam::OrbKeypoint> viaBatch = sets[(size_t)((step - 1) % 4)]->keypoints(0), viaSingle = detector.detect(seq[(size_t)lastT]);
+            bool same = viaBatch.size() == viaSingle.size();
+            for(size_t i = 0; same && i < viaBatch.size(); ++i)
+                same = viaBatch[i].keypoint.coordinates[0] == viaSingle[i].keypoint.coordinates[0] &&
+                       viaBatch[i].keypoint.coordinates[1] == viaSingle[i].keypoint.coordinates[1] && viaBatch[i].descriptor == viaSingle[i].descriptor;
+            mslam_b200_host_free(pinned);
+            if(!ok)
+                return 8;
+            std::printf("{\"plugin_single_frame\": {\"value\": %.2f, \"unit\": \"frames/s\", \"ms_per_frame\": %.4f, \"frames\": %d, "
+                        "\"keypoints\": %zu, \"matches\": %zu, \"call\": \"OrbB200Detector::detect + OrbB200Matcher::match per frame, pageable RgbFrame\"}, "
+                        "\"plugin_batched\": {\"value\": %.2f, \"unit\": \"frames/s\", \"ms_per_step\": %.4f, \"batch\": %d, \"steps\": %d, "
+                        "\"keypoints_per_batch\": %zu, \"matches_per_batch\": %zu, \"batched_equals_single\": %s, "
+                        "\"call\": \"detectBatchBegin/End (two batches in flight, pinned frames) + matchBatchBegin/End\"}}\n",
+                        singleIters / (singleMs * 1e-3), singleMs / singleIters, singleIters, keypoints, matches,
+                        (double)B * iters / (batchMs * 1e-3), batchMs / iters, B, iters, batchKeypoints, batchMatches, same ? "true" : "false");
+        }
+        catch(const std::exception& e)
+        {
+            std::fprintf(stderr, "bench failed: %s\n", e.what());
+            return 6;
+        }
         return 0;
     }
     if(argc >= 4 && !std::strcmp(argv[1], "db"))

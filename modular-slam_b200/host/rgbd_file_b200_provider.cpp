@@ -268,32 +268,57 @@ std::vector<std::string> getImages(const std::string& rootDir)
     return imagePaths;
 }
 
+// One association line is "<rgb time> <rgb file> <depth time> <depth file>" (associate.py of the TUM RGB-D tools); the
+// reference keeps the first time stamp and the two file names, relative to the list's directory, and skips lines that do
+// not have all four fields (rgbd_file_provider.cpp:109-134).  Tokenised by hand here: no stream state to reason about.
+namespace
+{
+bool nextToken(const std::string& text, std::size_t* at, std::string* token)
+{
+    const char* blanks = " \t\r\n";
+    const std::size_t first = text.find_first_not_of(blanks, *at);
+    if(first == std::string::npos)
+        return false;
+    const std::size_t last = text.find_first_of(blanks, first);
+    *token = text.substr(first, last == std::string::npos ? std::string::npos : last - first);
+    *at = last == std::string::npos ? text.size() : last;
+    return true;
+}
+
+bool toDouble(const std::string& token, double* value)
+{
+    char* end = nullptr;
+    *value = std::strtod(token.c_str(), &end);
+    return end != token.c_str(); // operator>> semantics: a leading number is enough ("1.5x" reads 1.5)
+}
+} // namespace
+
 RgbdFilePaths readTumRgbdDataset(const std::string& tumFile)
 {
-    std::ifstream ifss{tumFile};
-    RgbdFilePaths paths;
-    const std::size_t slash = tumFile.rfind('/');
-    const std::string rootDir = slash == std::string::npos ? std::string() : tumFile.substr(0, slash);
-    auto join = [&rootDir](const std::string& rel) { // std::filesystem::path operator/ : an absolute rhs replaces the lhs
-        if(!rel.empty() && rel[0] == '/')
-            return rel;
-        return rootDir.empty() ? rel : rootDir + "/" + rel;
+    RgbdFilePaths result;
+    std::string directory;
+    if(const std::size_t cut = tumFile.find_last_of('/'); cut != std::string::npos)
+        directory = tumFile.substr(0, cut);
+    // what std::filesystem::path::operator/ does for the two cases that occur: an absolute name stands alone
+    const auto resolve = [&directory](const std::string& name) {
+        return (name.front() == '/' || directory.empty()) ? name : directory + '/' + name;
     };
-    std::string line;
-    while(std::getline(ifss, line))
+    std::ifstream list(tumFile);
+    for(std::string row; std::getline(list, row);)
     {
-        std::istringstream iss{line};
-        std::string rgbPath, depthPath, temp;
-        double timestamp;
-        iss >> timestamp >> rgbPath >> temp >> depthPath; // "timestamp rgb timestamp depth" (associate.py output)
-        if(!iss.fail())
-        {
-            paths.rgbPaths.push_back(join(rgbPath));
-            paths.depthPaths.push_back(join(depthPath));
-            paths.timestamps.push_back(timestamp);
-        }
+        std::size_t cursor = 0;
+        std::string field[4];
+        bool complete = true;
+        for(std::string& f : field)
+            complete = complete && nextToken(row, &cursor, &f);
+        double stamp = 0.0;
+        if(!complete || !toDouble(field[0], &stamp))
+            continue;
+        result.timestamps.push_back(stamp);
+        result.rgbPaths.push_back(resolve(field[1]));
+        result.depthPaths.push_back(resolve(field[3]));
     }
-    return paths;
+    return result;
 }
 
 CameraParameters tumRgbdCameraParams()
@@ -319,39 +344,41 @@ RgbdFileB200Provider::~RgbdFileB200Provider()
 
 bool RgbdFileB200Provider::init()
 {
-    return filePaths.rgbPaths.size() > 0 && filePaths.rgbPaths.size() == filePaths.depthPaths.size();
+    // a usable sequence has at least one frame and a depth image for every colour image (rgbd_file_provider.cpp:50-55)
+    const std::size_t colour = filePaths.rgbPaths.size();
+    return colour != 0 && colour == filePaths.depthPaths.size();
 }
 
+// decode frame `index` of the sequence into a fresh RgbdFrame; null when it does not exist or either image is unreadable
+std::shared_ptr<RgbdFrame> RgbdFileB200Provider::decode(std::size_t index) const
+{
+    if(index >= filePaths.rgbPaths.size() || index >= filePaths.depthPaths.size())
+        return nullptr;
+    const std::string &colourFile = filePaths.rgbPaths[index], &depthFile = filePaths.depthPaths[index];
+    Size colour{0, 0}, depth{0, 0};
+    if(!readPngInfo(colourFile, &colour.width, &colour.height, nullptr, nullptr) ||
+       !readPngInfo(depthFile, &depth.width, &depth.height, nullptr, nullptr))
+        return nullptr;
+    auto out = std::make_shared<RgbdFrame>();
+    out->rgb.size = colour;
+    out->rgb.data.resize((std::size_t)colour.width * colour.height * 3);
+    out->depth.size = depth;
+    out->depth.data.resize((std::size_t)depth.width * depth.height);
+    out->depth.cameraParameters = cameraParameters;
+    out->timestamp.timePoint = index < filePaths.timestamps.size() ? filePaths.timestamps[index] : 0.0;
+    const bool readable = readPngBgr8(colourFile, out->rgb.data.data(), colour.width, colour.height) &&
+                          readPngGray16(depthFile, out->depth.data.data(), depth.width, depth.height);
+    return readable ? out : nullptr;
+}
+
+// The reference's contract (rgbd_file_provider.cpp:57-107): true and a new recentData() while frames remain; past the end,
+// or on an image that cannot be read, recentData() becomes null and the position does not advance.
 bool RgbdFileB200Provider::fetch()
 {
-    if(currentIndex >= filePaths.rgbPaths.size())
-    {
-        recentFrame = nullptr;
-        return false;
-    }
-    const std::string& rgbImagePath = filePaths.rgbPaths[currentIndex];
-    const std::string& depthPath = filePaths.depthPaths[currentIndex];
-    int w = 0, h = 0, dw = 0, dh = 0;
-    if(!readPngInfo(rgbImagePath, &w, &h, nullptr, nullptr) || !readPngInfo(depthPath, &dw, &dh, nullptr, nullptr))
-    {
-        recentFrame = nullptr; // rgbMat.empty() || depthMat.empty()  (rgbd_file_provider.cpp:69-73)
-        return false;
-    }
-    auto frame = std::make_shared<RgbdFrame>();
-    frame->timestamp.timePoint = currentIndex < filePaths.timestamps.size() ? filePaths.timestamps[currentIndex] : 0.0;
-    frame->rgb.data.resize((std::size_t)w * h * 3);
-    frame->rgb.size.width = w, frame->rgb.size.height = h;
-    frame->depth.data.resize((std::size_t)dw * dh);
-    frame->depth.size.width = dw, frame->depth.size.height = dh;
-    frame->depth.cameraParameters = cameraParameters;
-    if(!readPngBgr8(rgbImagePath, frame->rgb.data.data(), w, h) || !readPngGray16(depthPath, frame->depth.data.data(), dw, dh))
-    {
-        recentFrame = nullptr;
-        return false;
-    }
-    currentIndex += 1;
-    recentFrame = std::move(frame);
-    return true;
+    recentFrame = decode(currentIndex);
+    if(recentFrame)
+        ++currentIndex;
+    return recentFrame != nullptr;
 }
 
 std::shared_ptr<RgbdFrame> RgbdFileB200Provider::recentData() const

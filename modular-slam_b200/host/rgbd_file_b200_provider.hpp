@@ -77,6 +77,7 @@ class RgbdFileB200Provider : public DataProviderInterface<RgbdFrame>
     RgbdFilePaths filePaths;
     std::size_t currentIndex = 0;
     std::shared_ptr<RgbdFrame> recentFrame;
+    std::shared_ptr<RgbdFrame> decode(std::size_t index) const;
     CameraParameters cameraParameters;
     void* pinned = nullptr; // mslam_b200_host_alloc
     std::size_t pinnedBytes = 0;
