@@ -783,13 +783,23 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
             launch_gray(st, d_bgr, ctx->d_pyr, P, &ctx->launches);
         }
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[0], st));
-        for(int l = 1; l < nl; ++l)
+        // levels below l_split are waited for one by one (their own FAST / blur launches); the rest of the chain is one call
+        // (which fuses the trailing small levels into a single launch) with one event at its end
+        for(int l = 1; l < std::min(l_split, nl); ++l)
         {
             {
                 StageTimer t(ctx, MSLAM_B200_T_RESIZE);
                 launch_pyramid(st, ctx->d_pyr, P, ctx->d_xtab, ctx->d_ytab, ctx->d_qtab, ctx->sm_count, l, l + 1, &ctx->launches);
             }
             MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[l], st));
+        }
+        if(std::max(l_split, 1) < nl)
+        {
+            {
+                StageTimer t(ctx, MSLAM_B200_T_RESIZE);
+                launch_pyramid(st, ctx->d_pyr, P, ctx->d_xtab, ctx->d_ytab, ctx->d_qtab, ctx->sm_count, std::max(l_split, 1), nl, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[nl - 1], st));
         }
         for(int l = 0; l < l_split; ++l)
         {

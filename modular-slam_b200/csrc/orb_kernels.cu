@@ -147,18 +147,25 @@ __device__ __forceinline__ void resize_hrow(const Row3& W, int sh, unsigned selA
 // one coalesced load and are broadcast with shuffles, so no load sits on the row-to-row dependency chain.
 constexpr int RS_AHEAD = 4;
 
-__global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict__ src, int spitch, long long sfs, int sh_rows,
-                                                      uint8_t* __restrict__ dst, int dpitch, long long dfs, int dh, int nquads,
-                                                      int xblocks, int rs_band, const uint4* __restrict__ qtab,
-                                                      const short2* __restrict__ ytab)
+// one warp, one band of output rows [yb, yb + rs_band) x 128 columns (quads xb * 32 .. + 31) of one frame.  LDG: the source may
+// go through the read-only path (it was written by an earlier kernel); the fused tail kernel reads levels it wrote itself.
+template <bool LDG>
+__device__ __forceinline__ Row3 resize_load_t(const uint8_t* __restrict__ row, int wi)
 {
-    static_assert(RS_BAND_MAX <= 32, "one lane per output row of the band");
-    const int lane = threadIdx.x & 31;
-    const int wg = blockIdx.x * 4 + (threadIdx.x >> 5);
-    const int band = wg / xblocks, xb = wg - band * xblocks;
-    const int yb = band * rs_band;
-    if(yb >= dh) // warp-uniform
-        return;
+    const unsigned* p = reinterpret_cast<const unsigned*>(row) + wi;
+    Row3 r;
+    if(LDG)
+        r.a = __ldg(p), r.b = __ldg(p + 1), r.c = __ldg(p + 2);
+    else
+        r.a = p[0], r.b = p[1], r.c = p[2];
+    return r;
+}
+
+template <bool LDG>
+__device__ __forceinline__ void resize_band(const uint8_t* __restrict__ simg, int spitch, int sh_rows, uint8_t* __restrict__ dbase,
+                                            int dpitch, int dh, int nquads, int xb, int yb, int rs_band,
+                                            const uint4* __restrict__ qtab, const short2* __restrict__ ytab, int lane)
+{
     const int quad_raw = xb * 32 + lane;
     const bool live = quad_raw < nquads;
     const int quad = live ? quad_raw : nquads - 1; // dead lanes shadow the last quad (they must stay for the shuffles)
@@ -168,8 +175,7 @@ __global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict_
     const unsigned a10 = q.z & 0xffffu, a11 = q.z >> 16, a12 = q.w & 0xffffu, a13 = q.w >> 16;
     const unsigned w0 = (256u - a10) | (a10 << 16), w1 = (256u - a11) | (a11 << 16), w2 = (256u - a12) | (a12 << 16),
                    w3 = (256u - a13) | (a13 << 16);
-    const uint8_t* simg = src + (long long)blockIdx.y * sfs;
-    uint8_t* dimg = dst + (long long)blockIdx.y * dfs + 4 * quad;
+    uint8_t* dimg = dbase + 4 * quad;
     const int ye = min(yb + rs_band, dh);
     const short2 ty_lane = __ldg(ytab + min(yb + lane, dh - 1));
     const int r_first = __shfl_sync(0xffffffffu, (int)ty_lane.x, 0);
@@ -178,7 +184,7 @@ __global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict_
     Row3 buf[RS_AHEAD];
 #pragma unroll
     for(int k = 0; k < RS_AHEAD; ++k)
-        buf[k] = resize_load(simg + (long long)min(r_first + k, r_last) * spitch, wi);
+        buf[k] = resize_load_t<LDG>(simg + (long long)min(r_first + k, r_last) * spitch, wi);
     unsigned hP[4] = {0, 0, 0, 0}, hC[4] = {0, 0, 0, 0};
     int y = yb;
     int n0 = r_first;                                    // taps of output row y
@@ -196,7 +202,7 @@ __global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict_
                     hP[j] = hC[j];
                 resize_hrow(buf[k], sh, selA, selB, w0, w1, w2, w3, hC);
                 if(r + RS_AHEAD <= r_last)
-                    buf[k] = resize_load(simg + (long long)(r + RS_AHEAD) * spitch, wi);
+                    buf[k] = resize_load_t<LDG>(simg + (long long)(r + RS_AHEAD) * spitch, wi);
                 // emit the output rows whose second tap row min(n0 + 1, last source row) is r
                 while(y < ye && min(n0 + 1, sh_rows - 1) == r)
                 {
@@ -215,6 +221,52 @@ __global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict_
                 }
             }
         }
+    }
+}
+
+__global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict__ src, int spitch, long long sfs, int sh_rows,
+                                                      uint8_t* __restrict__ dst, int dpitch, long long dfs, int dh, int nquads,
+                                                      int xblocks, int rs_band, const uint4* __restrict__ qtab,
+                                                      const short2* __restrict__ ytab)
+{
+    static_assert(RS_BAND_MAX <= 32, "one lane per output row of the band");
+    const int lane = threadIdx.x & 31;
+    const int wg = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int band = wg / xblocks, xb = wg - band * xblocks;
+    const int yb = band * rs_band;
+    if(yb >= dh) // warp-uniform
+        return;
+    resize_band<true>(src + (long long)blockIdx.y * sfs, spitch, sh_rows, dst + (long long)blockIdx.y * dfs, dpitch, dh, nquads, xb, yb,
+                      rs_band, qtab, ytab, lane);
+}
+
+// The small levels of the chain in ONE launch: a CTA owns a frame and walks levels [l_begin, nlevels), every warp taking bands of
+// the current level, __syncthreads() between levels (level l-1 was written by this CTA: plain loads, not the read-only path).
+// A level of ~70k pixels and less is a 10-microsecond launch that cannot fill the machine, and the chain pays one such launch
+// per level; here the frames of the batch run side by side instead, one SM each.
+constexpr int RT_THREADS = 1024, RT_BAND = 4;
+__global__ void __launch_bounds__(RT_THREADS, 1) k_resize_tail(const __grid_constant__ PipeParams P, int l_begin, uint8_t* __restrict__ pyr,
+                                                               const uint4* __restrict__ qtab, const short2* __restrict__ ytab)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x + P.frame0;
+    for(int l = l_begin; l < P.nlevels; ++l)
+    {
+        const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
+        const uint8_t* simg = pyr + S.img_off + (long long)b * S.img_frame_stride;
+        uint8_t* dimg = pyr + D.img_off + (long long)b * D.img_frame_stride;
+        const int xblocks = (D.rs_quads + 31) / 32, bands = (D.h + RT_BAND - 1) / RT_BAND;
+        for(int task = warp; task < xblocks * bands; task += RT_THREADS / 32)
+        {
+            const int band = task / xblocks, xb = task - band * xblocks;
+            if(l == l_begin)
+                resize_band<true>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * RT_BAND, RT_BAND, qtab + D.qtab_off,
+                                  ytab + D.ytab_off, lane);
+            else
+                resize_band<false>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * RT_BAND, RT_BAND, qtab + D.qtab_off,
+                                   ytab + D.ytab_off, lane);
+        }
+        __syncthreads();
     }
 }
 
@@ -1183,10 +1235,32 @@ void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const Pipe
     ++*launches;
 }
 
+constexpr long long kResizeTailMaxPixels = 80000;
+static int resize_tail_min_frames()
+{
+    static int v = -1;
+    if(v < 0)
+    {
+        const char* e = getenv("MSLAM_RESIZE_TAIL_MIN_FRAMES"); // A/B aid: a huge value switches the fused tail off
+        v = e ? atoi(e) : 16;
+    }
+    return v;
+}
+
 void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const short2* xtab, const short2* ytab,
                     const uint4* qtab, int sm_count, int l_begin, int l_end, long long* launches)
 {
-    for(int l = l_begin < 1 ? 1 : l_begin; l < l_end; ++l)
+    // trailing small levels (all on the quad fast path) of a batch go to the fused per-frame kernel
+    int l_tail = l_end;
+    if(l_end == P.nlevels && P.n_frames >= resize_tail_min_frames())
+    {
+        while(l_tail - 1 >= (l_begin < 1 ? 1 : l_begin) && P.lv[l_tail - 1].rs_quads > 0 &&
+              (long long)P.lv[l_tail - 1].w * P.lv[l_tail - 1].h <= kResizeTailMaxPixels)
+            --l_tail;
+        if(l_end - l_tail < 2)
+            l_tail = l_end; // one level: nothing to fuse
+    }
+    for(int l = l_begin < 1 ? 1 : l_begin; l < l_tail; ++l)
     {
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
         if(D.rs_quads > 0)
@@ -1212,6 +1286,11 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
                                                   S.w, S.h, pyr + D.img_off + P.frame0 * D.img_frame_stride, D.pitch,
                                                   D.img_frame_stride, D.w, D.h, xtab + D.xtab_off, ytab + D.ytab_off);
         }
+        ++*launches;
+    }
+    if(l_tail < l_end)
+    {
+        k_resize_tail<<<P.n_frames, RT_THREADS, 0, st>>>(P, l_tail, pyr, qtab, ytab);
         ++*launches;
     }
 }
