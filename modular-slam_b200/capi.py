@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmslam_b200.so")
+# MSLAM_B200_LIB: load another build of the SAME library (A/B measurements of compile-time variants); default = the in-tree build
+LIB_PATH = os.environ.get("MSLAM_B200_LIB") or os.path.join(_HERE, "lib", "libmslam_b200.so")
 
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM = 0, -1, -2, -3, -4
 STAGE_PYRAMID, STAGE_BLURRED, STAGE_N_FAST, STAGE_N_CUT1, STAGE_N_FINAL = 0, 1, 2, 3, 4

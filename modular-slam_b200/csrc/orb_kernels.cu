@@ -240,23 +240,27 @@ __global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict_
                       rs_band, qtab, ytab, lane);
 }
 
-// The small levels of the chain in ONE launch: a CTA owns a frame and walks levels [l_begin, nlevels), every warp taking bands of
-// the current level, __syncthreads() between levels (level l-1 was written by this CTA: plain loads, not the read-only path).
-// A level of ~70k pixels and less is a 10-microsecond launch that cannot fill the machine, and the chain pays one such launch
-// per level; here the frames of the batch run side by side instead, one SM each.
-constexpr int RT_THREADS = 1024, RT_BAND = 4;
-__global__ void __launch_bounds__(RT_THREADS, 1) k_resize_tail(const __grid_constant__ PipeParams P, int l_begin, uint8_t* __restrict__ pyr,
-                                                               const uint4* __restrict__ qtab, const short2* __restrict__ ytab)
+// The small levels of the chain in ONE launch: a CLUSTER of RT_CLUSTER CTAs owns a frame and walks levels [l_begin, nlevels),
+// every warp of the cluster taking bands of the current level, a cluster barrier (release / acquire at cluster scope: the level
+// just written is visible to the other CTAs' plain loads) between levels.  A level of ~70k pixels and less is a
+// 10-microsecond launch that cannot fill the machine, and the chain pays one such launch per level; here the frames of the
+// batch run side by side.  (One CTA per frame -- 64 busy SMs of 148 -- was measured slower than the four launches it replaced.)
+constexpr int RT_THREADS = 512, RT_BAND = 4, RT_CLUSTER = 4;
+__global__ void __cluster_dims__(RT_CLUSTER, 1, 1) __launch_bounds__(RT_THREADS, 2)
+    k_resize_tail(const __grid_constant__ PipeParams P, int l_begin, uint8_t* __restrict__ pyr, const uint4* __restrict__ qtab,
+                  const short2* __restrict__ ytab)
 {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int b = blockIdx.x + P.frame0;
+    const int lane = threadIdx.x & 31;
+    const int crank = blockIdx.x % RT_CLUSTER;
+    const int worker = crank * (RT_THREADS / 32) + (threadIdx.x >> 5), n_workers = RT_CLUSTER * (RT_THREADS / 32);
+    const int b = blockIdx.x / RT_CLUSTER + P.frame0;
     for(int l = l_begin; l < P.nlevels; ++l)
     {
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
         const uint8_t* simg = pyr + S.img_off + (long long)b * S.img_frame_stride;
         uint8_t* dimg = pyr + D.img_off + (long long)b * D.img_frame_stride;
         const int xblocks = (D.rs_quads + 31) / 32, bands = (D.h + RT_BAND - 1) / RT_BAND;
-        for(int task = warp; task < xblocks * bands; task += RT_THREADS / 32)
+        for(int task = worker; task < xblocks * bands; task += n_workers)
         {
             const int band = task / xblocks, xb = task - band * xblocks;
             if(l == l_begin)
@@ -266,7 +270,11 @@ __global__ void __launch_bounds__(RT_THREADS, 1) k_resize_tail(const __grid_cons
                 resize_band<false>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * RT_BAND, RT_BAND, qtab + D.qtab_off,
                                    ytab + D.ytab_off, lane);
         }
-        __syncthreads();
+        if(l + 1 < P.nlevels)
+        {
+            asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+            asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        }
     }
 }
 
@@ -566,7 +574,10 @@ __device__ __forceinline__ void fast_mbar_wait(unsigned bar, unsigned parity, in
     }
 }
 
-__global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipeParams P, const __grid_constant__ FastMaps M, const FastMaps* __restrict__ gmaps, int dbg, int l_begin, int l_end,
+#ifndef MSLAM_FAST_CTAS
+#define MSLAM_FAST_CTAS 4 // resident CTAs per SM the register allocation aims for (A/B aid: -DMSLAM_FAST_CTAS=5 caps at 48 registers)
+#endif
+__global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_constant__ PipeParams P, const __grid_constant__ FastMaps M, const FastMaps* __restrict__ gmaps, int dbg, int l_begin, int l_end,
                                               const uint8_t* __restrict__ pyr, unsigned* __restrict__ cand,
                                               LevelCounters* __restrict__ ctr, unsigned* __restrict__ hist)
 {
@@ -594,7 +605,6 @@ __global__ void __launch_bounds__(256, 4) k_fast(const __grid_constant__ PipePar
     const int sy0 = edge - 1 + (SH - 2) * ty;       // first scored row
     const int px0 = sx0 - 4, py0 = sy0 - 3;         // first pixel the tile needs
     const int px0a = px0 & ~15, xo = px0 - px0a;    // first staged column (16-byte aligned for the TMA) and where px0 sits in it
-    const uint8_t* img = pyr + L.img_off + (long long)b * L.img_frame_stride;
 
     // ---- tile staging: ONE 3-D bulk-tensor (TMA) load per CTA -- box = 160 x PH x 1 of the level's (pitch, h, frame) plane
     // stack, zero-filled past the image / the row pitch (what the per-word guards of the earlier version did by hand) ----
@@ -1235,7 +1245,16 @@ void launch_gray(cudaStream_t st, const uint8_t* d_bgr, uint8_t* pyr, const Pipe
     ++*launches;
 }
 
-constexpr long long kResizeTailMaxPixels = 80000;
+static long long resize_tail_max_pixels()
+{
+    static long long v = -1;
+    if(v < 0)
+    {
+        const char* e = getenv("MSLAM_RESIZE_TAIL_MAX_PX"); // A/B aid
+        v = e ? atoll(e) : 150000; // VGA: levels 2..7 (measured: c2 107.1k -> 110.8k frames/s; 80000 = levels 4..7 was neutral)
+    }
+    return v;
+}
 static int resize_tail_min_frames()
 {
     static int v = -1;
@@ -1255,7 +1274,7 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
     if(l_end == P.nlevels && P.n_frames >= resize_tail_min_frames())
     {
         while(l_tail - 1 >= (l_begin < 1 ? 1 : l_begin) && P.lv[l_tail - 1].rs_quads > 0 &&
-              (long long)P.lv[l_tail - 1].w * P.lv[l_tail - 1].h <= kResizeTailMaxPixels)
+              (long long)P.lv[l_tail - 1].w * P.lv[l_tail - 1].h <= resize_tail_max_pixels())
             --l_tail;
         if(l_end - l_tail < 2)
             l_tail = l_end; // one level: nothing to fuse
@@ -1290,7 +1309,7 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
     }
     if(l_tail < l_end)
     {
-        k_resize_tail<<<P.n_frames, RT_THREADS, 0, st>>>(P, l_tail, pyr, qtab, ytab);
+        k_resize_tail<<<P.n_frames * RT_CLUSTER, RT_THREADS, 0, st>>>(P, l_tail, pyr, qtab, ytab);
         ++*launches;
     }
 }

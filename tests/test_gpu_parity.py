@@ -414,3 +414,20 @@ def test_single_frame_graph_replay_matches_oracle(pkg, oracle, bundled):
                 okp, odesc = oracle.orb_detect_rgb(frames[1], prm)
                 _assert_same_keypoints(kb[1, :cnt[1]], db[1, :cnt[1]], okp, odesc, "batch between replays")
         assert len(set(per_frame)) == 1 and per_frame[0] >= 10
+
+
+@pytest.mark.parametrize("W,H,B", [(320, 240, 16), (640, 480, 24)])
+def test_large_batches_take_the_fused_pyramid_tail_and_stay_bit_exact(pkg, oracle, W, H, B):
+    """batches of >= 16 frames build their small pyramid levels in one cluster-per-frame launch (k_resize_tail): every level of
+    every frame still equals the oracle's chained INTER_LINEAR_EXACT resize, and so do the keypoints and descriptors"""
+    frames, _ = pkg.synth.frame_batch(W, H, B, 0, seed=W + B)
+    with pkg.Context(max_width=W, max_height=H, max_batch=B, nfeatures=500) as c:
+        kps, descs, counts = c.detect_batch(frames)
+        w, h, _, _ = c.level_geometry(W, H)
+        for b in (0, 7, B - 1):
+            okp, od, dumps = oracle.orb_detect_gray(oracle.gray(frames[b]), oracle.default_params(500), dumps=True)
+            for l in range(8):
+                got = c.debug_read(pkg.STAGE_PYRAMID, b, l, int(w[l]), int(h[l]))
+                assert (got == dumps["pyr"][l]).all(), f"frame {b} level {l}: {(got != dumps['pyr'][l]).sum()} px differ"
+            n = int(counts[b])
+            assert n == len(okp) and kps[b, :n].tobytes() == okp.tobytes() and (descs[b, :n] == od).all(), f"frame {b}"
