@@ -1,5 +1,5 @@
 """Python mirror of the reference's feature interfaces, over the C ABI -- same names, argument meaning and error
-behaviour as the C++ plugin (host/plugin.cpp), so that tests read like the reference's:
+behaviour as the C++ plugin (host/orb_b200_plugin.cpp), so that tests read like the reference's:
 
     IFeatureDetector<RgbFrame, uint8_t, 32>::detect(const RgbFrame&)            feature_interface.hpp:50-56
     IFeatureMatcher<uint8_t, 32>::match(firstDescriptors, secondDescriptors)     feature_interface.hpp:62-70
