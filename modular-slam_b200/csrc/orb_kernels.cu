@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) k_gray1(const uint8_t* __restrict__ bgr, 
 //   two pixels each out of the 8-byte window, and the four alpha1.  Per SOURCE row a lane then issues 3 aligned 32-bit
 //   loads, 2 funnel shifts, 2 PRMT and 4 IDP.2A (h = a0*p[i] + a1*p[i+1], both taps in one instruction); consecutive
 //   output rows share their source rows (1.2 new source rows per output row), so the horizontal pass is never
-//   repeated.  Per OUTPUT row: 8 IMAD, 3 PRMT, one 32-bit store.  ~10 instructions per pixel against ~60 for the
+//   repeated.  Per OUTPUT row: 8 IMAD, 3 PRMT, one 32-bit store.  Against ~60 instructions per pixel for the
 //   per-pixel table walk of k_resize_generic, which stays as the fallback for scale factors whose 4-pixel footprint
 //   does not fit the 8-byte window.
 // =================================================================================================
@@ -141,26 +141,17 @@ __device__ __forceinline__ void resize_hrow(const Row3& W, int sh, unsigned selA
     h[3] = __dp2a_hi(w3, pB, 0u);
 }
 
-// The band's source rows form one contiguous run r_first .. r_last; the lane streams through them in order with the raw
-// words of the next RS_AHEAD rows already in flight, keeps the horizontal pass of the last two rows, and emits every
-// output row whose lower tap row has just been produced.  The per-row (ofs, alpha1) of the band sit in lanes 0..15 of
-// one coalesced load and are broadcast with shuffles, so no load sits on the row-to-row dependency chain.
-constexpr int RS_AHEAD = 4;
-
 // one warp, one band of output rows [yb, yb + rs_band) x 128 columns (quads xb * 32 .. + 31) of one frame.  LDG: the source may
 // go through the read-only path (it was written by an earlier kernel); the fused tail kernel reads levels it wrote itself.
-template <bool LDG>
-__device__ __forceinline__ Row3 resize_load_t(const uint8_t* __restrict__ row, int wi)
-{
-    const unsigned* p = reinterpret_cast<const unsigned*>(row) + wi;
-    Row3 r;
-    if(LDG)
-        r.a = __ldg(p), r.b = __ldg(p + 1), r.c = __ldg(p + 2);
-    else
-        r.a = p[0], r.b = p[1], r.c = p[2];
-    return r;
-}
-
+// Walks the band OUTPUT row by output row.  Output row y needs the horizontal pass of source rows n0(y) and n0(y) + 1 (the
+// last one clamped); from one output row to the next n0 advances by 1 (the lower tap row of y becomes the upper one of y + 1,
+// one new source row) or by 2 (two new rows) for every scale factor the quad table accepts, so the lane keeps the horizontal
+// pass of the current tap pair (hP, hC), the raw words of the next two source rows (already in flight while this row is
+// emitted), and does per output row: one or two horizontal passes, one or two row loads, the vertical blend, one store.  The
+// per-row (ofs, alpha1) of the band sit in lanes 0..31 of one coalesced load and are broadcast with shuffles.  An advance
+// outside {1, 2} (not produced by the host's tables today) reloads both tap rows directly.
+// (Round 1 walked SOURCE rows with a four-row prefetch ring and an inner `while` that emitted whatever output rows had
+// become ready: 30 instructions per pixel, 40 % of them loop bookkeeping -- profiles/r2_v2_*.)
 template <bool LDG>
 __device__ __forceinline__ void resize_band(const uint8_t* __restrict__ simg, int spitch, int sh_rows, uint8_t* __restrict__ dbase,
                                             int dpitch, int dh, int nquads, int xb, int yb, int rs_band,
@@ -175,50 +166,67 @@ __device__ __forceinline__ void resize_band(const uint8_t* __restrict__ simg, in
     const unsigned a10 = q.z & 0xffffu, a11 = q.z >> 16, a12 = q.w & 0xffffu, a13 = q.w >> 16;
     const unsigned w0 = (256u - a10) | (a10 << 16), w1 = (256u - a11) | (a11 << 16), w2 = (256u - a12) | (a12 << 16),
                    w3 = (256u - a13) | (a13 << 16);
-    uint8_t* dimg = dbase + 4 * quad;
     const int ye = min(yb + rs_band, dh);
     const short2 ty_lane = __ldg(ytab + min(yb + lane, dh - 1));
-    const int r_first = __shfl_sync(0xffffffffu, (int)ty_lane.x, 0);
-    const int r_last = min(__shfl_sync(0xffffffffu, (int)ty_lane.x, ye - 1 - yb) + 1, sh_rows - 1);
-
-    Row3 buf[RS_AHEAD];
-#pragma unroll
-    for(int k = 0; k < RS_AHEAD; ++k)
-        buf[k] = resize_load_t<LDG>(simg + (long long)min(r_first + k, r_last) * spitch, wi);
-    unsigned hP[4] = {0, 0, 0, 0}, hC[4] = {0, 0, 0, 0};
-    int y = yb;
-    int n0 = r_first;                                    // taps of output row y
-    unsigned b1 = (unsigned)__shfl_sync(0xffffffffu, (int)ty_lane.y, 0);
-    for(int r0 = r_first; r0 <= r_last; r0 += RS_AHEAD)
+    const int last = sh_rows - 1;
+    const uint8_t* srow = simg + 4 * (long long)wi; // byte address of the lane's first word in source row 0
+    auto load = [&](int r) {
+        const unsigned* p = reinterpret_cast<const unsigned*>(srow + (long long)min(r, last) * spitch);
+        Row3 w;
+        if(LDG)
+            w.a = __ldg(p), w.b = __ldg(p + 1), w.c = __ldg(p + 2);
+        else
+            w.a = p[0], w.b = p[1], w.c = p[2];
+        return w;
+    };
+    int n0 = __shfl_sync(0xffffffffu, (int)ty_lane.x, 0);
+    unsigned hP[4], hC[4];
     {
+        const Row3 t0 = load(n0), t1 = load(n0 + 1);
+        resize_hrow(t0, sh, selA, selB, w0, w1, w2, w3, hP);
+        resize_hrow(t1, sh, selA, selB, w0, w1, w2, w3, hC);
+    }
+    Row3 R0 = load(n0 + 2), R1 = load(n0 + 3); // the next two source rows, in flight
+    uint8_t* drow = dbase + 4 * quad + (long long)yb * dpitch;
+    for(int y = yb; y < ye; ++y, drow += dpitch)
+    {
+        const unsigned b1 = (unsigned)__shfl_sync(0xffffffffu, (int)ty_lane.y, y - yb);
+        const unsigned b0 = 256u - b1;
+        unsigned v[4];
 #pragma unroll
-        for(int k = 0; k < RS_AHEAD; ++k)
+        for(int j = 0; j < 4; ++j)
+            v[j] = b0 * hP[j] + (b1 * hC[j] + 32768u); // result byte = bits 16..23
+        const unsigned lo = __byte_perm(v[0], v[1], 0x0062), hi = __byte_perm(v[2], v[3], 0x0062);
+        if(live)
+            *reinterpret_cast<unsigned*>(drow) = __byte_perm(lo, hi, 0x5410);
+        if(y + 1 < ye) // warp-uniform: set up the tap pair of the next output row
         {
-            const int r = r0 + k;
-            if(r <= r_last) // warp-uniform
+            const int n1 = __shfl_sync(0xffffffffu, (int)ty_lane.x, y + 1 - yb);
+            const int adv = n1 - n0;
+            n0 = n1;
+            if(adv == 1)
             {
 #pragma unroll
                 for(int j = 0; j < 4; ++j)
                     hP[j] = hC[j];
-                resize_hrow(buf[k], sh, selA, selB, w0, w1, w2, w3, hC);
-                if(r + RS_AHEAD <= r_last)
-                    buf[k] = resize_load_t<LDG>(simg + (long long)(r + RS_AHEAD) * spitch, wi);
-                // emit the output rows whose second tap row min(n0 + 1, last source row) is r
-                while(y < ye && min(n0 + 1, sh_rows - 1) == r)
-                {
-                    const unsigned b0 = 256u - b1;
-                    unsigned v[4];
-#pragma unroll
-                    for(int j = 0; j < 4; ++j)
-                        v[j] = b0 * (n0 == r ? hC[j] : hP[j]) + b1 * hC[j] + 32768u; // result byte = bits 16..23
-                    const unsigned lo = __byte_perm(v[0], v[1], 0x0062), hi = __byte_perm(v[2], v[3], 0x0062);
-                    if(live)
-                        *reinterpret_cast<unsigned*>(dimg + (long long)y * dpitch) = __byte_perm(lo, hi, 0x5410);
-                    ++y;
-                    const int src_lane = min(y, ye - 1) - yb;
-                    n0 = __shfl_sync(0xffffffffu, (int)ty_lane.x, src_lane);
-                    b1 = (unsigned)__shfl_sync(0xffffffffu, (int)ty_lane.y, src_lane);
-                }
+                resize_hrow(R0, sh, selA, selB, w0, w1, w2, w3, hC);
+                R0 = R1;
+                R1 = load(n0 + 3);
+            }
+            else if(adv == 2)
+            {
+                resize_hrow(R0, sh, selA, selB, w0, w1, w2, w3, hP);
+                resize_hrow(R1, sh, selA, selB, w0, w1, w2, w3, hC);
+                R0 = load(n0 + 2);
+                R1 = load(n0 + 3);
+            }
+            else if(adv != 0)
+            {
+                const Row3 t0 = load(n0), t1 = load(n0 + 1);
+                resize_hrow(t0, sh, selA, selB, w0, w1, w2, w3, hP);
+                resize_hrow(t1, sh, selA, selB, w0, w1, w2, w3, hC);
+                R0 = load(n0 + 2);
+                R1 = load(n0 + 3);
             }
         }
     }
@@ -247,8 +255,8 @@ __global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict_
 // batch run side by side.  (One CTA per frame -- 64 busy SMs of 148 -- was measured slower than the four launches it replaced.)
 constexpr int RT_THREADS = 512, RT_BAND = 4, RT_CLUSTER = 4;
 __global__ void __cluster_dims__(RT_CLUSTER, 1, 1) __launch_bounds__(RT_THREADS, 2)
-    k_resize_tail(const __grid_constant__ PipeParams P, int l_begin, uint8_t* __restrict__ pyr, const uint4* __restrict__ qtab,
-                  const short2* __restrict__ ytab)
+    k_resize_tail(const __grid_constant__ PipeParams P, int l_begin, int rt_band, uint8_t* __restrict__ pyr,
+                  const uint4* __restrict__ qtab, const short2* __restrict__ ytab)
 {
     const int lane = threadIdx.x & 31;
     const int crank = blockIdx.x % RT_CLUSTER;
@@ -259,15 +267,15 @@ __global__ void __cluster_dims__(RT_CLUSTER, 1, 1) __launch_bounds__(RT_THREADS,
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
         const uint8_t* simg = pyr + S.img_off + (long long)b * S.img_frame_stride;
         uint8_t* dimg = pyr + D.img_off + (long long)b * D.img_frame_stride;
-        const int xblocks = (D.rs_quads + 31) / 32, bands = (D.h + RT_BAND - 1) / RT_BAND;
+        const int xblocks = (D.rs_quads + 31) / 32, bands = (D.h + rt_band - 1) / rt_band;
         for(int task = worker; task < xblocks * bands; task += n_workers)
         {
             const int band = task / xblocks, xb = task - band * xblocks;
             if(l == l_begin)
-                resize_band<true>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * RT_BAND, RT_BAND, qtab + D.qtab_off,
+                resize_band<true>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * rt_band, rt_band, qtab + D.qtab_off,
                                   ytab + D.ytab_off, lane);
             else
-                resize_band<false>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * RT_BAND, RT_BAND, qtab + D.qtab_off,
+                resize_band<false>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * rt_band, rt_band, qtab + D.qtab_off,
                                    ytab + D.ytab_off, lane);
         }
         if(l + 1 < P.nlevels)
@@ -1309,7 +1317,15 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
     }
     if(l_tail < l_end)
     {
-        k_resize_tail<<<P.n_frames * RT_CLUSTER, RT_THREADS, 0, st>>>(P, l_tail, pyr, qtab, ytab);
+        static int rt_band = 0;
+        if(rt_band == 0)
+        {
+            const char* e = getenv("MSLAM_RESIZE_TAIL_BAND"); // A/B aid
+            rt_band = e ? atoi(e) : RT_BAND;
+            if(rt_band < 1 || rt_band > 32)
+                rt_band = RT_BAND;
+        }
+        k_resize_tail<<<P.n_frames * RT_CLUSTER, RT_THREADS, 0, st>>>(P, l_tail, rt_band, pyr, qtab, ytab);
         ++*launches;
     }
 }
