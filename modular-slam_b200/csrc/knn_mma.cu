@@ -117,6 +117,40 @@ __device__ __forceinline__ void umma_commit(uint32_t bar)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
+// ---- CTA-pair (cta_group::2) forms: two CTAs of a cluster on the two SMs of a TPC execute one M = 256 MMA -- each computes
+// its own 128 rows, reads its own query rows (A) and HALF of the train tile (B) from its shared memory and gets the other
+// half from its peer, which halves the shared-memory bytes an MMA needs per SM ----
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of the same shared-memory location in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr)
+{
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void umma_i8_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+                 "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+                 : "memory");
+}
+// arrives (once the MMAs issued so far have completed) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"((unsigned short)3)
+                 : "memory");
+}
+
 // 32 consecutive accumulator columns of this thread's TMEM lane (asynchronous: the registers are valid after tmem_wait)
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
 {
@@ -163,6 +197,14 @@ struct Top2x2
         k1 = __vminu2(k1, __vmaxu2(k0, pk));
         k0 = __vminu2(k0, pk);
     }
+    // two new values at once: 5 packed min / max operations instead of 6 (second smallest of {k0, k1, a, b} =
+    // min3(k1, max(k0, min(a, b)), max(a, b)); VIMNMX3.U16x2 is a native instruction)
+    __device__ __forceinline__ void push2(unsigned a, unsigned b)
+    {
+        const unsigned m = __vminu2(a, b), M = __vmaxu2(a, b);
+        k1 = __vimin3_u16x2(k1, __vmaxu2(k0, m), M);
+        k0 = __vminu2(k0, m);
+    }
 };
 __device__ __forceinline__ unsigned widen_key(unsigned k16, unsigned col_base)
 {
@@ -170,42 +212,72 @@ __device__ __forceinline__ unsigned widen_key(unsigned k16, unsigned col_base)
     return k16 == 0xffffu ? kNoKey : ((k16 >> 7) << 16) | (col_base + (k16 & 127u));
 }
 
+// run-time copies of two constants (-64 and 65536): multiplying by a value the compiler cannot see keeps the key arithmetic
+// in IMAD form on the FMA pipe; with literals it becomes LEA / shift sequences on the ALU pipe, which the min / max work binds
+struct KeyMul
+{
+    unsigned neg64, two16;
+};
+
 // 32 accumulators (columns col0 .. col0 + 31 of the tile) -> 16 packed key pairs -> top-2 chains.
+//      pk = (16384 - 64 D_even + col) | (16384 - 64 D_odd + col + 1) << 16  =  (D_odd * 65536 + D_even) * -64 + C
+// (every lane value lies in 0 .. 32895, so the sum is exact and the lanes do not disturb each other): two IMADs per register
 template <bool MASKED>
-__device__ __forceinline__ void push32(Top2x2& t, const uint32_t (&v)[32], int col0, int n_valid)
+__device__ __forceinline__ void push32(Top2x2& t, const uint32_t (&v)[32], int col0, int n_valid, KeyMul km)
 {
 #pragma unroll
-    for(int i = 0; i < 32; i += 2)
+    for(int i = 0; i < 32; i += 4)
     {
-        const unsigned c = (16384u + (unsigned)(col0 + i)) | ((16384u + (unsigned)(col0 + i + 1)) << 16);
-        unsigned pk = v[i] * (unsigned)-64 + c;
-        pk = v[i + 1] * ((unsigned)-64 << 16) + pk;
-        if(MASKED)
+        unsigned pk[2];
+#pragma unroll
+        for(int h = 0; h < 2; ++h)
         {
-            pk |= (col0 + i) < n_valid ? 0u : 0x0000ffffu;
-            pk |= (col0 + i + 1) < n_valid ? 0u : 0xffff0000u;
+            const int c0 = col0 + i + 2 * h;
+            const unsigned c = (16384u + (unsigned)c0) | ((16384u + (unsigned)(c0 + 1)) << 16);
+            pk[h] = (v[i + 2 * h + 1] * km.two16 + v[i + 2 * h]) * km.neg64 + c;
+            if(MASKED)
+            {
+                pk[h] |= c0 < n_valid ? 0u : 0x0000ffffu;
+                pk[h] |= (c0 + 1) < n_valid ? 0u : 0xffff0000u;
+            }
         }
-        t.push(pk);
+        t.push2(pk[0], pk[1]);
     }
 }
 
-// One 128-column accumulator (4 loads of 32 columns), double-buffered in registers.
-template <bool MASKED>
-__device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_valid)
+// One 128-column accumulator (4 loads of 32 columns), double-buffered in registers.  RAGGED: only the first n_valid columns
+// exist (the last tile of a set); the one 32-column group that straddles n_valid is masked, the groups past it are skipped.
+template <bool RAGGED>
+__device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_valid, KeyMul km)
 {
     uint32_t va[32], vb[32];
+    auto group = [&](const uint32_t (&v)[32], int col0) {
+        if(!RAGGED || col0 + 32 <= n_valid) // warp-uniform
+            push32<false>(t, v, col0, n_valid, km);
+        else if(col0 < n_valid)
+            push32<true>(t, v, col0, n_valid, km);
+    };
     tmem_ld32(taddr, va);
     tmem_wait(va);
-    tmem_ld32(taddr + 32, vb);
-    push32<MASKED>(t, va, 0, n_valid);
+    if(!RAGGED || n_valid > 32)
+        tmem_ld32(taddr + 32, vb);
+    group(va, 0);
+    if(RAGGED && n_valid <= 32)
+        return;
     tmem_wait(vb);
-    tmem_ld32(taddr + 64, va);
-    push32<MASKED>(t, vb, 32, n_valid);
+    if(!RAGGED || n_valid > 64)
+        tmem_ld32(taddr + 64, va);
+    group(vb, 32);
+    if(RAGGED && n_valid <= 64)
+        return;
     tmem_wait(va);
-    tmem_ld32(taddr + 96, vb);
-    push32<MASKED>(t, va, 64, n_valid);
+    if(!RAGGED || n_valid > 96)
+        tmem_ld32(taddr + 96, vb);
+    group(va, 64);
+    if(RAGGED && n_valid <= 96)
+        return;
     tmem_wait(vb);
-    push32<MASKED>(t, vb, 96, n_valid);
+    group(vb, 96);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -268,8 +340,14 @@ struct DbArgs
                        // loads tensor memory but does not process, 4 = epilogue does not load at all
     double ratio;
     int* scores;
+    KeyMul km; // {-64, 65536}, set by the launchers
 };
-template <bool DB>
+// CG = 1: one CTA per SM works alone (tcgen05 cta_group::1).  CG = 2: the CTAs 2k, 2k + 1 of grid.x form a cluster on one TPC
+// and run as a pair (cta_group::2): CTA r keeps its own 256 query rows and loads train rows [64 r, 64 r + 64) of every
+// 128-row tile (8 ring stages of 16 KB instead of 4 of 32 KB); the LEADER (rank 0) issues M = 256 MMAs for both; its
+// tcgen05.commit arrives on both CTAs' "slot free" / "accumulators full" barriers (multicast); the peer forwards "my half of
+// the tile has landed" to the leader's full barrier and both CTAs' epilogue warps report "accumulators drained" to the leader.
+template <bool DB, int CG>
 __global__ void __launch_bounds__(MMA_THREADS, 1)
     k_knn2_mma(const uint8_t* __restrict__ xq, const int* __restrict__ q_counts, const uint8_t* __restrict__ xt,
                const int* __restrict__ t_counts, int cap, int cap_pad, unsigned* __restrict__ key0, unsigned* __restrict__ key1,
@@ -283,8 +361,12 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     const int p = DB ? blockIdx.z : blockIdx.y; // row set
     const int nq = min(q_counts[p], cap);
     const int q0 = blockIdx.x * CTA_ROWS;
-    if(q0 >= nq)
-        return; // whole CTA, before any barrier or allocation
+    const uint32_t crank = CG == 2 ? (blockIdx.x & 1u) : 0u; // == %cluster_ctarank for cluster dims (2, 1, 1)
+    const int q0p = CG == 2 ? (int)(blockIdx.x & ~1u) * CTA_ROWS : q0; // first row of the pair
+    if(q0p >= nq)
+        return; // whole CTA (CG = 2: the whole pair), before any barrier or allocation
+    constexpr int NSTAGES = CG == 2 ? 2 * STAGES : STAGES;   // ring depth
+    constexpr int STAGE_BYTES = B_BYTES / CG;                 // this CTA's share of a 128-row train tile
     long long clk0 = 0;
     unsigned long long ns0 = 0;
     if(MMA_DBG(32) && threadIdx.x == 0)
@@ -309,38 +391,53 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
             set_end(pt);
         }
     };
-    const int n_row_tiles = nq - q0 > MMA_M ? 2 : 1; // the second query tile may be empty
+    // query tiles that exist: in this CTA (epilogue, A load) / in the pair (the MMAs cover row tile a of both CTAs)
+    const int n_row_tiles = nq - q0 > MMA_M ? 2 : (nq - q0 > 0 ? 1 : 0);
+    const int n_row_tiles_mma = nq - q0p > MMA_M ? 2 : 1;
     uint8_t* sA = smem;
     uint8_t* sB = smem + A_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_BYTES + STAGES * B_BYTES);
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 24);
     const uint32_t bar_a = smem_u32(bars + 0);
-    const uint32_t bar_bfull = smem_u32(bars + 1), bar_bempty = smem_u32(bars + 1 + STAGES);          // [STAGES] each
-    const uint32_t bar_cfull = smem_u32(bars + 1 + 2 * STAGES), bar_cempty = bar_cfull + 8 * ACC_STAGES; // [ACC_STAGES] each
+    const uint32_t bar_bfull = smem_u32(bars + 1), bar_bempty = smem_u32(bars + 1 + NSTAGES);          // [NSTAGES] each
+    const uint32_t bar_cfull = smem_u32(bars + 1 + 2 * NSTAGES), bar_cempty = bar_cfull + 8 * ACC_STAGES; // [ACC_STAGES] each
+    static_assert(1 + 2 * 2 * STAGES + 2 * ACC_STAGES <= 24, "barrier block");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if(threadIdx.x == 0)
     {
         mbar_init(bar_a, 1);
-        for(int s = 0; s < STAGES; ++s)
+        for(int s = 0; s < NSTAGES; ++s)
         {
-            mbar_init(bar_bfull + 8 * s, 1);
+            // full: the local producer's expect_tx arrival (+ its bytes); the leader of a pair also waits for the peer's relay
+            mbar_init(bar_bfull + 8 * s, (CG == 2 && crank == 0) ? 2 : 1);
             mbar_init(bar_bempty + 8 * s, 1);
         }
         for(int s = 0; s < ACC_STAGES; ++s)
         {
             mbar_init(bar_cfull + 8 * s, 1);
-            mbar_init(bar_cempty + 8 * s, 8); // one arrival per epilogue warp
+            mbar_init(bar_cempty + 8 * s, 8 * CG); // one arrival per epilogue warp (of both CTAs, at the leader)
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if(warp == 0)
     {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TMEM_COLS)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if(CG == 2)
+        {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        }
+        else
+        {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if(CG == 2)
+        cluster_sync_all(); // both CTAs' barriers are initialised before anything can arrive on them from the other side
     tc_fence_after();
     const uint32_t tmem = *s_tmem;
 
@@ -348,19 +445,25 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     {
         if(lane == 0)
         {
-            // ---- producer: query tiles once, then the train tiles through the ring ----
+            // ---- producer: query tiles once, then (this CTA's share of) the train tiles through the ring ----
             const uint8_t* a_src = xq + ((size_t)p * cap_pad + q0) * ROW_BYTES;
             const int a_bytes = n_row_tiles * MMA_M * ROW_BYTES;
-            mbar_expect_tx(bar_a, a_bytes);
-            for(int o = 0; o < a_bytes; o += BULK)
-                bulk_g2s(smem_u32(sA + o), a_src + o, BULK, bar_a);
+            if(a_bytes > 0)
+            {
+                mbar_expect_tx(bar_a, a_bytes);
+                for(int o = 0; o < a_bytes; o += BULK)
+                    bulk_g2s(smem_u32(sA + o), a_src + o, BULK, bar_a);
+            }
+            else
+                mbar_arrive(bar_a); // a peer without rows of its own still takes part (its half of every train tile)
             for_each_tile([] {}, [&](int pt, int, int j, int it) {
-                    const int s = it % STAGES;
-                    mbar_wait(bar_bempty + 8 * s, ((it / STAGES) & 1) ^ 1);
-                    mbar_expect_tx(bar_bfull + 8 * s, B_BYTES);
-                    const uint8_t* b_src = xt + ((size_t)pt * t_pad + (size_t)j * MMA_N) * ROW_BYTES;
-                    for(int o = 0; o < B_BYTES; o += BULK)
-                        bulk_g2s(smem_u32(sB + s * B_BYTES + o), b_src + o, BULK, bar_bfull + 8 * s);
+                    const int s = it % NSTAGES;
+                    mbar_wait(bar_bempty + 8 * s, ((it / NSTAGES) & 1) ^ 1);
+                    mbar_expect_tx(bar_bfull + 8 * s, STAGE_BYTES);
+                    // rows [j * 128 + crank * (128 / CG), + 128 / CG) of the set: contiguous in the expanded layout
+                    const uint8_t* b_src = xt + ((size_t)pt * t_pad + (size_t)j * MMA_N + (size_t)crank * (MMA_N / CG)) * ROW_BYTES;
+                    for(int o = 0; o < STAGE_BYTES; o += BULK)
+                        bulk_g2s(smem_u32(sB + s * STAGE_BYTES + o), b_src + o, BULK, bar_bfull + 8 * s);
                 }, [](int) {});
         }
     }
@@ -368,26 +471,54 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     {
         if(lane == 0)
         {
-            // ---- MMA issuer ----
-            mbar_wait(bar_a, 0);
-            const uint32_t a_addr = smem_u32(sA);
-            for_each_tile([] {}, [&](int, int, int, int it) {
-                    const int s = it % STAGES, as = it % ACC_STAGES;
-                    mbar_wait(bar_bfull + 8 * s, (it / STAGES) & 1);
-                    mbar_wait(bar_cempty + 8 * as, ((it / ACC_STAGES) & 1) ^ 1);
-                    tc_fence_after();
-                    const uint32_t b_addr = smem_u32(sB + s * B_BYTES);
-                    for(int a = 0; a < (MMA_DBG(16) ? 1 : n_row_tiles); ++a)
-                    {
+            if(CG == 2 && crank != 0)
+            {
+                // ---- peer of a pair: no MMAs to issue; forward "my query rows / my half of tile `it` have landed" to the leader ----
+                mbar_wait(bar_a, 0);
+                for_each_tile([] {}, [&](int, int, int, int it) {
+                        const int s = it % NSTAGES;
+                        mbar_wait(bar_bfull + 8 * s, (it / NSTAGES) & 1);
+                        mbar_arrive_cluster(mapa_u32(bar_bfull + 8 * s, 0));
+                    }, [](int) {});
+            }
+            else
+            {
+                // ---- MMA issuer (CG = 2: for both CTAs of the pair) ----
+                mbar_wait(bar_a, 0);
+                const uint32_t a_addr = smem_u32(sA);
+                constexpr uint32_t kIdescPair = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(MMA_N >> 3) << 17) | ((uint32_t)((2 * MMA_M) >> 4) << 24);
+                for_each_tile([] {}, [&](int, int, int, int it) {
+                        const int s = it % NSTAGES, as = it % ACC_STAGES;
+                        mbar_wait(bar_bfull + 8 * s, (it / NSTAGES) & 1);
+                        mbar_wait(bar_cempty + 8 * as, ((it / ACC_STAGES) & 1) ^ 1);
+                        tc_fence_after();
+                        const uint32_t b_addr = smem_u32(sB + s * STAGE_BYTES);
+                        for(int a = 0; a < (MMA_DBG(16) ? 1 : n_row_tiles_mma); ++a)
+                        {
 #pragma unroll
-                        for(int k = 0; k < ROW_BYTES / 32; ++k)
-                            if(k == 0 || !MMA_DBG(1))
-                                umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
-                                    smem_desc(b_addr + k * 256), k > 0);
-                    }
-                    umma_commit(bar_bempty + 8 * s); // the train tile may be overwritten once these MMAs have read it
-                    umma_commit(bar_cfull + 8 * as); // ... and the accumulator stage is complete
-                }, [](int) {});
+                            for(int k = 0; k < ROW_BYTES / 32; ++k)
+                                if(k == 0 || !MMA_DBG(1))
+                                {
+                                    if(CG == 2)
+                                        umma_i8_pair(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
+                                                     smem_desc(b_addr + k * 256), kIdescPair, k > 0);
+                                    else
+                                        umma_i8(tmem + (as * 2 + a) * MMA_N, smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256),
+                                                smem_desc(b_addr + k * 256), k > 0);
+                                }
+                        }
+                        if(CG == 2)
+                        {
+                            umma_commit_pair(bar_bempty + 8 * s); // both CTAs' slot s may be overwritten once these MMAs have read it
+                            umma_commit_pair(bar_cfull + 8 * as); // ... and the accumulator stage is complete in both CTAs
+                        }
+                        else
+                        {
+                            umma_commit(bar_bempty + 8 * s); // the train tile may be overwritten once these MMAs have read it
+                            umma_commit(bar_cfull + 8 * as); // ... and the accumulator stage is complete
+                        }
+                    }, [](int) {});
+            }
         }
     }
     else
@@ -418,7 +549,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                     if(active)
                         for(int c = 0; c < MMA_N; c += 32)
                         {
-                            push32<false>(t, va, 0, MMA_N);
+                            push32<false>(t, va, 0, MMA_N, db.km);
                             asm volatile("" : "+r"(va[0]), "+r"(va[1]));
                         }
                 }
@@ -438,14 +569,19 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                 else if(active)
                 {
                     if(n_valid >= MMA_N)
-                        drain_tile<false>(t, taddr, n_valid);
+                        drain_tile<false>(t, taddr, n_valid, db.km);
                     else
-                        drain_tile<true>(t, taddr, n_valid);
+                        drain_tile<true>(t, taddr, n_valid, db.km);
                 }
                 tc_fence_before();
                 __syncwarp();
                 if(lane == 0)
-                    mbar_arrive(bar_cempty + 8 * as);
+                {
+                    if(CG == 2 && crank != 0)
+                        mbar_arrive_cluster(mapa_u32(bar_cempty + 8 * as, 0)); // the leader issues the MMAs: it collects both CTAs' arrivals
+                    else
+                        mbar_arrive(bar_cempty + 8 * as);
+                }
                 unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
                 merge2(t0, t1, widen_key(t.k0 >> 16, col_base), widen_key(t.k1 >> 16, col_base));
                 merge2(k0, k1, t0, t1);
@@ -478,10 +614,15 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
         atomicAdd(&g_mma_clk[0], (unsigned long long)(clock64() - clk0));
         atomicAdd(&g_mma_clk[1], ns1 - ns0);
     }
+    if(CG == 2)
+        cluster_sync_all(); // neither CTA may leave (or free its tensor memory) while the other can still reach into it
     if(warp == 0)
     {
         __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
+        if(CG == 2)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
     }
 }
 // ---------------------------------------------------------------------------------------------------------------
@@ -622,13 +763,49 @@ static int mma_debug()
     return 0;
 #endif
 }
+// cta_group of the matcher kernels: 1 = single CTAs (default), 2 = CTA pairs (MSLAM_MMA_CG=2).  The pair form is correct (same
+// bits, tests/test_knn_tensor.py runs under either) but measured SLOWER on this workload: 3.49 vs 3.64 T pairs/s, because its
+// feed path tops out at 4.8 T however few MMAs a tile gets (profiles/r2_v3_mma_experiments.txt): the leader's MMAs of tile
+// it + 2 wait for the PEER's epilogue warps to report tile `it` drained, a commit-multicast + remote-arrive round trip per
+// accumulator stage, and with all 512 tensor-memory columns in use there are only two stages to hide it behind.
+static int mma_cta_group()
+{
+    static int v = -1;
+    if(v < 0)
+    {
+        const char* e = getenv("MSLAM_MMA_CG");
+        v = (e && atoi(e) == 2) ? 2 : 1;
+    }
+    return v;
+}
+template <typename K, typename... Args>
+static cudaError_t launch_pair(K kernel, dim3 grd, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grd;
+    cfg.blockDim = dim3(MMA_THREADS);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 // per DEVICE (cudaFuncSetAttribute applies to the current device only): called from mslam_b200_create after cudaSetDevice
 cudaError_t configure_mma_kernels()
 {
-    cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(k_knn2_mma<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if(e != cudaSuccess)
         return e;
-    e = cudaFuncSetAttribute(k_knn2_mma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    e = cudaFuncSetAttribute(k_knn2_mma<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaFuncSetAttribute(k_knn2_mma<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaFuncSetAttribute(k_knn2_mma<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if(e != cudaSuccess)
         return e;
     e = cudaFuncSetAttribute(k_peak_i8<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (MMA_M + 128) * ROW_BYTES + 64);
@@ -665,7 +842,16 @@ cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, c
     dim3 grd((cap + CTA_ROWS - 1) / CTA_ROWS, n_pairs);
     DbArgs none{};
     none.debug = mma_debug();
-    k_knn2_mma<false><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, none);
+    none.km = KeyMul{(unsigned)-64, 65536u};
+    if(mma_cta_group() == 2)
+    {
+        grd.x = (grd.x + 1) & ~1u; // pairs: CTAs 2k, 2k + 1 are one cluster
+        cudaError_t e = launch_pair(k_knn2_mma<false, 2>, grd, st, xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, none);
+        if(e != cudaSuccess)
+            return e;
+    }
+    else
+        k_knn2_mma<false, 1><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, none);
     ++*launches;
     return cudaSuccess;
 }
@@ -680,6 +866,7 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
     db.ratio = ratio, db.scores = scores;
     db.group = kDbGroup, db.n_sets = nq_frames;
     db.debug = mma_debug();
+    db.km = KeyMul{(unsigned)-64, 65536u};
     // grid.y = query frames, grid.z = keyframes (<= 65535 per launch)
     for(int kf0 = 0; kf0 < n_keyframes; kf0 += 65535)
     {
@@ -687,8 +874,17 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
         DbArgs d = db;
         d.scores = scores + kf0;
         dim3 grd((k_cap + CTA_ROWS - 1) / CTA_ROWS, (nq_frames + kDbGroup - 1) / kDbGroup, nk);
-        k_knn2_mma<true><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
-                                                               xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
+        if(mma_cta_group() == 2)
+        {
+            grd.x = (grd.x + 1) & ~1u;
+            cudaError_t e = launch_pair(k_knn2_mma<true, 2>, grd, st, xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
+                                        xqueries, q_counts, k_cap, knn_mma_pad(k_cap), (unsigned*)nullptr, (unsigned*)nullptr, d);
+            if(e != cudaSuccess)
+                return e;
+        }
+        else
+            k_knn2_mma<true, 1><<<grd, MMA_THREADS, SMEM_BYTES, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
+                                                                  xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
         ++*launches;
     }
     if(MMA_DBG(32))
