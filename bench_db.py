@@ -188,19 +188,24 @@ def main(args, rank, world, local):
     pk, pk_kind = peaks()
     tensor_path = os.environ.get("MSLAM_KNN_MMA", "1") != "0"
     if tensor_path:
-        # k_knn2_mma<DB>: Hamming distances as an int8 GEMM (K = 256): 2 * 256 integer operations per descriptor pair
-        int8_peak = 2.0 * pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+        # k_knn2_mma<DB>: Hamming distances as an int8 GEMM (K = 256): 2 * 256 integer operations per descriptor pair, against
+        # the int8 tensor rate MEASURED on this GPU in this run (tcgen05.mma.kind::i8 back to back, operands resident)
+        tp = ctx.measure_tensor_peak()
+        int8_peak = tp["int8_ops_per_s_n128_sustained"] / 1e12
         roofline = {"bound": "tensor", "kernel": "k_knn2_mma<true> (+ k_expand_pm1)", "achieved": per_gpu_pairs * 512 / 1e12,
                     "peak": int8_peak, "unit": "TOP/s (int8; algorithmic: 2 x 256 per descriptor pair)",
                     "frac": per_gpu_pairs * 512 / 1e12 / int8_peak, "traffic": None,
-                    "peak_source": f"2 x the {pk_kind} dense bf16 figure of MEASURED_PEAKS.json (sustained: the step is "
-                                   "hundreds of ms); int8 tcgen05.mma runs at twice the bf16 rate",
+                    "peak_source": "mslam_b200_measure_tensor_peak in this run: M128 N128 K32 int8 MMAs issued back to back on all SMs, "
+                                   "sustained (the step is hundreds of ms)",
+                    "peaks_measured_TOPs": {k: v / 1e12 for k, v in tp.items()},
+                    "frac_of_2x_measured_bf16_sustained": per_gpu_pairs * 512 / 1e12 / (2.0 * pk.get("bf16_tflops_sustained", pk["bf16_tflops"])),
                     "pairs_per_s_per_gpu": per_gpu_pairs, "kernel_ms_per_launch": db_ms,
-                    "component_rates_T_pairs_per_s": {"all MMAs, no epilogue": 5.2, "epilogue alone": 5.0,
-                                                      "bulk-copy feed + barriers alone": 10.8, "tensor-memory loads alone": 10.0},
-                    "component_rates_source": "profiles/r1_v10_mma_experiments.txt (tools/gpu_mma_dbg.sh): the MMA side is held "
-                                              "by the shared-memory port (operand reads of N = 128 MMAs + the bulk-copy writes), "
-                                              "the epilogue by its ALU work; the two also slow each other",
+                    "component_rates_T_pairs_per_s": {"all MMAs, no epilogue": 5.13, "epilogue alone": 5.34,
+                                                      "bulk-copy feed + barriers alone": 10.3},
+                    "component_rates_source": "profiles/r2_v3_mma_experiments.txt (tools/gpu_mma_dbg2.sh, 2,500-keyframe shard): an "
+                                              "N = 128 MMA reads the whole 128 B/clk shared-memory port, so the next tile's bulk copy "
+                                              "lands only while the tensor pipe idles; the epilogue is as slow as the MMAs; with two "
+                                              "accumulator stages every hand-over is on the critical path",
                     "hbm_bytes_per_launch_algorithmic": kf_local * n * 32 + qb * n * 32,
                     "hbm_gbs_measured_peak": pk["hbm_gbs"], "int_peaks": ip}
     else:
