@@ -192,7 +192,7 @@ def main(args, rank, world, local):
         # the int8 tensor rate MEASURED on this GPU in this run (tcgen05.mma.kind::i8 back to back, operands resident)
         tp = ctx.measure_tensor_peak()
         int8_peak = tp["int8_ops_per_s_n128_sustained"] / 1e12
-        roofline = {"bound": "tensor", "kernel": "k_knn2_mma<true> (+ k_expand_pm1)", "achieved": per_gpu_pairs * 512 / 1e12,
+        roofline = {"bound": "tensor", "kernel": "k_knn2_mma_wide<true, 8> (+ k_expand_pm1)", "achieved": per_gpu_pairs * 512 / 1e12,
                     "peak": int8_peak, "unit": "TOP/s (int8; algorithmic: 2 x 256 per descriptor pair)",
                     "frac": per_gpu_pairs * 512 / 1e12 / int8_peak, "traffic": None,
                     "peak_source": "mslam_b200_measure_tensor_peak in this run: M128 N128 K32 int8 MMAs issued back to back on all SMs, "

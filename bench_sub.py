@@ -147,7 +147,7 @@ def db_subrecord(pkg, torch, dist, rank, world, local, stream, steps=3, warmup=2
                       "query_frames_per_step": qb, "top_k": k,
                       "entry_point": "mslam_b200_db_attach + mslam_b200_db_query_sharded_dev (one stream, no host synchronisation)"},
            "gpu_launches": int(launches),
-           "roofline": {"bound": "tensor", "kernel": "k_knn2_mma<true> (+ k_expand_pm1)", "achieved": per_gpu * 512 / 1e12,
+           "roofline": {"bound": "tensor", "kernel": "k_knn2_mma_wide<true, 8> (+ k_expand_pm1)", "achieved": per_gpu * 512 / 1e12,
                         "peak": peak / 1e12, "unit": "TOP/s (int8; algorithmic: 2 x 256 per descriptor pair)",
                         "frac": per_gpu * 512 / peak, "traffic": None,
                         "peak_source": "tcgen05.mma.kind::i8 M128 N128 K32 issued back to back on all SMs from resident operands, "

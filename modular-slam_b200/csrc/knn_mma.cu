@@ -280,6 +280,34 @@ __device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_vali
     group(vb, 96);
 }
 
+// NG groups of 32 accumulator columns starting at column col0 of a 128-column key window of which the first n_valid exist
+// (n_valid may be <= col0: nothing to do); loads double-buffered in registers
+template <int NG>
+__device__ __forceinline__ void drain_cols(Top2x2& t, uint32_t taddr, int col0, int n_valid, KeyMul km)
+{
+    uint32_t va[32], vb[32];
+    if(col0 >= n_valid)
+        return;
+    tmem_ld32(taddr, va);
+#pragma unroll
+    for(int g = 0; g < NG; ++g)
+    {
+        uint32_t(&cur)[32] = (g & 1) ? vb : va;
+        uint32_t(&nxt)[32] = (g & 1) ? va : vb;
+        const int c = col0 + 32 * g;
+        tmem_wait(cur);
+        const bool more = g + 1 < NG && c + 32 < n_valid; // warp-uniform
+        if(more)
+            tmem_ld32(taddr + 32 * (g + 1), nxt);
+        if(c + 32 <= n_valid)
+            push32<false>(t, cur, c, n_valid, km);
+        else
+            push32<true>(t, cur, c, n_valid, km);
+        if(!more)
+            break;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // descriptors (32 bytes) -> +1 / -1 int8 rows in the canonical core-matrix order described at the top.
 // One thread = one 16-byte K chunk of one descriptor (16 descriptor bits).  Rows >= the set's count are left as they
@@ -626,6 +654,228 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
     }
 }
 // ---------------------------------------------------------------------------------------------------------------
+// The same kernel with N = 256 instructions ("wide"; the default, MSLAM_MMA_WIDE=0 selects the N = 128 form above).  Why: an M128 N128 K32 MMA reads 4 KB of A and 4 KB of B
+// from shared memory in its 64 cycles -- the whole 128 B/clk port -- so the bulk copies of the next train tile only land while
+// the tensor pipe idles; an M128 N256 K32 MMA reads 4 + 8 KB in 128 cycles = 96 B/clk and leaves room for them.  A 256-column
+// accumulator per query tile fills tensor memory (2 x 256 = 512 columns), so the two accumulators cannot be double-buffered
+// per tile; instead the two QUERY TILES alternate: while the MMAs of query tile 1 run, all eight epilogue warps drain query
+// tile 0 (warp w: lane quarter w % 4, column half w / 4), and vice versa.  The two column halves of a row meet in shared
+// memory at the end of a set.  Train tiles are 256 descriptors (two adjacent 32 KB ring slots = one 64 KB stage, two stages).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int WIDE_N = 256, WIDE_STAGES = 2, WIDE_B_BYTES = WIDE_N * ROW_BYTES;
+constexpr int WIDE_X_BYTES = 2 * 2 * MMA_M * 3 * 2 * 4; // [set parity][query tile][row][column part 1..3][2 keys] handed to column part 0
+constexpr int SMEM_BYTES_WIDE = A_BYTES + WIDE_STAGES * WIDE_B_BYTES + 256 + WIDE_X_BYTES;
+// EW epilogue warps (8 or 16): warp w drains lane quarter w % 4, columns (256 / (EW / 4)) * (w / 4) .. of the accumulator
+template <bool DB, int EW>
+__global__ void __launch_bounds__(EW * 32 + 64, 1)
+    k_knn2_mma_wide(const uint8_t* __restrict__ xq, const int* __restrict__ q_counts, const uint8_t* __restrict__ xt,
+                    const int* __restrict__ t_counts, int cap, int cap_pad, unsigned* __restrict__ key0, unsigned* __restrict__ key1,
+                    DbArgs db)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int p = DB ? blockIdx.z : blockIdx.y; // row set
+    const int nq = min(q_counts[p], cap);
+    const int q0 = blockIdx.x * CTA_ROWS;
+    if(q0 >= nq)
+        return;
+    const int t_pad = DB ? db.t_cap_pad : cap_pad, t_cap = DB ? db.t_cap : cap;
+    const int pt_begin = DB ? blockIdx.y * db.group : p, pt_end = DB ? min(pt_begin + db.group, db.n_sets) : p + 1;
+    auto for_each_tile = [&](auto&& set_begin, auto&& tile, auto&& set_end) {
+        for(int pt = pt_begin, it = 0, set = 0; pt < pt_end; ++pt)
+        {
+            const int nt = min(t_counts[pt], t_cap);
+            if(DB && nt < 2)
+                continue;
+            const int n_tiles = (nt + WIDE_N - 1) / WIDE_N;
+            set_begin();
+            for(int j = 0; j < n_tiles; ++j, ++it)
+                tile(pt, nt, j, it);
+            set_end(pt, set++);
+        }
+    };
+    const int n_row_tiles = nq - q0 > MMA_M ? 2 : 1;
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_BYTES + WIDE_STAGES * WIDE_B_BYTES);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 24);
+    unsigned* s_x = reinterpret_cast<unsigned*>(smem + A_BYTES + WIDE_STAGES * WIDE_B_BYTES + 256);
+    const uint32_t bar_a = smem_u32(bars + 0);
+    const uint32_t bar_bfull = smem_u32(bars + 1), bar_bempty = smem_u32(bars + 3); // [2] each
+    const uint32_t bar_cfull = smem_u32(bars + 5), bar_cempty = smem_u32(bars + 7); // [query tile] each
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if(threadIdx.x == 0)
+    {
+        mbar_init(bar_a, 1);
+        for(int s = 0; s < 2; ++s)
+        {
+            mbar_init(bar_bfull + 8 * s, 1);
+            mbar_init(bar_bempty + 8 * s, 1);
+            mbar_init(bar_cfull + 8 * s, 1);
+            mbar_init(bar_cempty + 8 * s, EW); // one arrival per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if(warp == 0)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *s_tmem;
+
+    constexpr int NPARTS = EW / 4, CPW = WIDE_N / NPARTS; // column parts of an accumulator, columns per warp (128 or 64)
+    if(warp == EW) // producer (the two single-thread roles sit above the epilogue warps: arbiter priority)
+    {
+        if(lane == 0)
+        {
+            const uint8_t* a_src = xq + ((size_t)p * cap_pad + q0) * ROW_BYTES;
+            const int a_bytes = n_row_tiles * MMA_M * ROW_BYTES;
+            mbar_expect_tx(bar_a, a_bytes);
+            for(int o = 0; o < a_bytes; o += BULK)
+                bulk_g2s(smem_u32(sA + o), a_src + o, BULK, bar_a);
+            for_each_tile([] {}, [&](int pt, int, int j, int it) {
+                    const int s = it & 1;
+                    mbar_wait(bar_bempty + 8 * s, ((it >> 1) & 1) ^ 1);
+                    mbar_expect_tx(bar_bfull + 8 * s, WIDE_B_BYTES);
+                    const uint8_t* b_src = xt + ((size_t)pt * t_pad + (size_t)j * WIDE_N) * ROW_BYTES;
+                    for(int o = 0; o < WIDE_B_BYTES; o += BULK)
+                        bulk_g2s(smem_u32(sB + s * WIDE_B_BYTES + o), b_src + o, BULK, bar_bfull + 8 * s);
+                }, [](int, int) {});
+        }
+    }
+    else if(warp == EW + 1)
+    {
+        if(lane == 0)
+        {
+            mbar_wait(bar_a, 0);
+            const uint32_t a_addr = smem_u32(sA);
+            constexpr uint32_t kIdescWide = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(WIDE_N >> 3) << 17) | ((uint32_t)(MMA_M >> 4) << 24);
+            for_each_tile([] {}, [&](int, int, int, int it) {
+                    const int s = it & 1;
+                    mbar_wait(bar_bfull + 8 * s, (it >> 1) & 1);
+                    const uint32_t b_addr = smem_u32(sB + s * WIDE_B_BYTES);
+                    for(int a = 0; a < n_row_tiles; ++a)
+                    {
+                        mbar_wait(bar_cempty + 8 * a, (it & 1) ^ 1); // query tile a's accumulator of the previous train tile is drained
+                        tc_fence_after();
+#pragma unroll
+                        for(int k = 0; k < ROW_BYTES / 32; ++k)
+                            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem + a * WIDE_N),
+                                         "l"(smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256)), "l"(smem_desc(b_addr + k * 256)),
+                                         "r"(kIdescWide), "r"((uint32_t)(k > 0))
+                                         : "memory");
+                        umma_commit(bar_cfull + 8 * a);
+                    }
+                    umma_commit(bar_bempty + 8 * s);
+                }, [](int, int) {});
+        }
+    }
+    else
+    {
+        // ---- epilogue: warp w owns TMEM lanes 32 * (w % 4) .. and columns CPW * (w / 4) .. of BOTH query tiles, in turn ----
+        const int quarter = warp & 3, part = warp >> 2;
+        const int win = (part * CPW) / MMA_N, col0 = (part * CPW) % MMA_N; // 128-column key window of the part, first column in it
+        unsigned k0[2], k1[2];
+        for_each_tile(
+            [&] { k0[0] = k0[1] = k1[0] = k1[1] = kNoKey; },
+            [&](int, int nt, int j, int it) {
+                const int col_base = j * WIDE_N + win * MMA_N;
+                const int n_valid = nt - col_base; // columns of this key window that exist (may be <= col0: nothing for this warp)
+#pragma unroll
+                for(int a = 0; a < 2; ++a)
+                {
+                    if(a >= n_row_tiles) // CTA-uniform
+                        continue;
+                    mbar_wait(bar_cfull + 8 * a, it & 1);
+                    tc_fence_after();
+                    const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * WIDE_N + part * CPW;
+                    Top2x2 t;
+                    if(CPW == MMA_N) // a whole key window per warp: the hand-scheduled four-group form
+                    {
+                        if(n_valid >= MMA_N)
+                            drain_tile<false>(t, taddr, n_valid, db.km);
+                        else if(n_valid > 0)
+                            drain_tile<true>(t, taddr, n_valid, db.km);
+                    }
+                    else
+                        drain_cols<CPW / 32>(t, taddr, col0, n_valid, db.km);
+                    tc_fence_before();
+                    __syncwarp();
+                    if(lane == 0)
+                        mbar_arrive(bar_cempty + 8 * a);
+                    if(n_valid > col0)
+                    {
+                        unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
+                        merge2(t0, t1, widen_key(t.k0 >> 16, col_base), widen_key(t.k1 >> 16, col_base));
+                        merge2(k0[a], k1[a], t0, t1);
+                    }
+                }
+            },
+            [&](int pt, int set) {
+                // column parts 1.. hand their top-2 to part 0 (same rows), which finishes the set
+                unsigned* xs = s_x + (set & 1) * (2 * MMA_M * 3 * 2);
+                if(part > 0)
+                {
+#pragma unroll
+                    for(int a = 0; a < 2; ++a)
+                    {
+                        unsigned* e = xs + (((a * MMA_M + quarter * 32 + lane) * 3) + (part - 1)) * 2;
+                        e[0] = k0[a];
+                        e[1] = k1[a];
+                    }
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory"); // the epilogue warps
+                if(part == 0)
+                {
+                    int cnt = 0;
+#pragma unroll
+                    for(int a = 0; a < 2; ++a)
+                    {
+                        const int q = q0 + a * MMA_M + quarter * 32 + lane;
+#pragma unroll
+                        for(int o = 0; o < NPARTS - 1; ++o)
+                        {
+                            const unsigned* e = xs + (((a * MMA_M + quarter * 32 + lane) * 3) + o) * 2;
+                            merge2(k0[a], k1[a], e[0], e[1]);
+                        }
+                        const bool live = a < n_row_tiles && q < nq;
+                        if(!DB)
+                        {
+                            if(live)
+                            {
+                                key0[(long long)p * cap + q] = k0[a];
+                                key1[(long long)p * cap + q] = k1[a];
+                            }
+                        }
+                        else
+                        {
+                            const int d0 = (int)(k0[a] >> 16), d1 = (int)(k1[a] >> 16); // nt >= 2: both exist
+                            const bool pass = db.int_ratio ? (10 * d0 < 7 * d1) : ((double)(float)d0 < db.ratio * (double)(float)d1);
+                            cnt += (live && pass) ? 1 : 0;
+                        }
+                    }
+                    if(DB)
+                    {
+                        cnt = __reduce_add_sync(0xffffffffu, cnt);
+                        if(lane == 0 && cnt)
+                            atomicAdd(db.scores + (long long)pt * db.n_keyframes + p, cnt);
+                    }
+                }
+            });
+    }
+    tc_fence_before();
+    __syncthreads();
+    if(warp == 0)
+    {
+        __syncwarp();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // roofline denominator of the tensor-core matcher, MEASURED: the rate at which this GPU retires tcgen05.mma.kind::i8
 // when nothing else runs -- operands resident in shared memory (+1/-1 bytes, like the matcher's), accumulators in tensor
 // memory, one issuing thread per SM, no loads, no epilogue.  N = 128 is the instruction shape k_knn2_mma issues, N = 256
@@ -778,6 +1028,21 @@ static int mma_cta_group()
     }
     return v;
 }
+// Which form of the kernel runs.  Default: the N = 256 form (k_knn2_mma_wide) with 8 epilogue warps -- measured on c5:
+// 4.82 T pairs/s against 3.87 T for the N = 128 form (MSLAM_MMA_WIDE=0) and 3.86 T for 16 epilogue warps (=16: 96 registers,
+// spills, and three times the end-of-set merging).  Same bits in every form.
+static int mma_wide()
+{
+    static int v = -1;
+    if(v < 0)
+    {
+        const char* e = getenv("MSLAM_MMA_WIDE");
+        v = e ? atoi(e) : 8;
+        if(v != 8 && v != 16)
+            v = 0;
+    }
+    return v;
+}
 template <typename K, typename... Args>
 static cudaError_t launch_pair(K kernel, dim3 grd, cudaStream_t st, Args... args)
 {
@@ -800,6 +1065,18 @@ cudaError_t configure_mma_kernels()
     if(e != cudaSuccess)
         return e;
     e = cudaFuncSetAttribute(k_knn2_mma<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaFuncSetAttribute(k_knn2_mma_wide<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES_WIDE);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaFuncSetAttribute(k_knn2_mma_wide<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES_WIDE);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaFuncSetAttribute(k_knn2_mma_wide<false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES_WIDE);
+    if(e != cudaSuccess)
+        return e;
+    e = cudaFuncSetAttribute(k_knn2_mma_wide<true, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES_WIDE);
     if(e != cudaSuccess)
         return e;
     e = cudaFuncSetAttribute(k_knn2_mma<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
@@ -843,7 +1120,11 @@ cudaError_t launch_knn2_mma(cudaStream_t st, const uint8_t* xq, const int* qn, c
     DbArgs none{};
     none.debug = mma_debug();
     none.km = KeyMul{(unsigned)-64, 65536u};
-    if(mma_cta_group() == 2)
+    if(mma_wide() == 16)
+        k_knn2_mma_wide<false, 16><<<grd, 16 * 32 + 64, SMEM_BYTES_WIDE, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, none);
+    else if(mma_wide() == 8)
+        k_knn2_mma_wide<false, 8><<<grd, 8 * 32 + 64, SMEM_BYTES_WIDE, st>>>(xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, none);
+    else if(mma_cta_group() == 2)
     {
         grd.x = (grd.x + 1) & ~1u; // pairs: CTAs 2k, 2k + 1 are one cluster
         cudaError_t e = launch_pair(k_knn2_mma<false, 2>, grd, st, xq, qn, xt, tn, cap, knn_mma_pad(cap), key0, key1, none);
@@ -874,7 +1155,13 @@ cudaError_t launch_db_scores_mma(cudaStream_t st, const uint8_t* xqueries, const
         DbArgs d = db;
         d.scores = scores + kf0;
         dim3 grd((k_cap + CTA_ROWS - 1) / CTA_ROWS, (nq_frames + kDbGroup - 1) / kDbGroup, nk);
-        if(mma_cta_group() == 2)
+        if(mma_wide() == 16)
+            k_knn2_mma_wide<true, 16><<<grd, 16 * 32 + 64, SMEM_BYTES_WIDE, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
+                                                                                 xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
+        else if(mma_wide() == 8)
+            k_knn2_mma_wide<true, 8><<<grd, 8 * 32 + 64, SMEM_BYTES_WIDE, st>>>(xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
+                                                                               xqueries, q_counts, k_cap, knn_mma_pad(k_cap), nullptr, nullptr, d);
+        else if(mma_cta_group() == 2)
         {
             grd.x = (grd.x + 1) & ~1u;
             cudaError_t e = launch_pair(k_knn2_mma<true, 2>, grd, st, xdb + (size_t)kf0 * knn_mma_pad(k_cap) * ROW_BYTES, k_counts + kf0,
