@@ -192,6 +192,21 @@ __device__ __forceinline__ void merge2(unsigned& k0, unsigned& k1, unsigned o0, 
 struct Top2x2
 {
     unsigned k0 = 0xffffffffu, k1 = 0xffffffffu;
+    unsigned a0 = 0xffffffffu, a1 = 0xffffffffu; // the second, independent chain
+    __device__ __forceinline__ void push2_alt(unsigned a, unsigned b)
+    {
+        const unsigned m = __vminu2(a, b), M = __vmaxu2(a, b);
+        a1 = __vimin3_u16x2(a1, __vmaxu2(a0, m), M);
+        a0 = __vminu2(a0, m);
+    }
+    // merge the second chain into (k0, k1): two sorted pairs -> the two smallest of the four, per 16-bit lane
+    __device__ __forceinline__ void fold()
+    {
+        const unsigned lo = __vminu2(k0, a0), hi = __vmaxu2(k0, a0);
+        k1 = __vimin3_u16x2(hi, k1, a1);
+        k0 = lo;
+        a0 = a1 = 0xffffffffu;
+    }
     __device__ __forceinline__ void push(unsigned pk)
     {
         k1 = __vminu2(k1, __vmaxu2(k0, pk));
@@ -222,6 +237,8 @@ struct KeyMul
 // 32 accumulators (columns col0 .. col0 + 31 of the tile) -> 16 packed key pairs -> top-2 chains.
 //      pk = (16384 - 64 D_even + col) | (16384 - 64 D_odd + col + 1) << 16  =  (D_odd * 65536 + D_even) * -64 + C
 // (every lane value lies in 0 .. 32895, so the sum is exact and the lanes do not disturb each other): two IMADs per register
+// (the pair updates alternate between two independent top-2 chains, t and its shadow t.alt, merged by fold(): the serial
+// dependency through k0 / k1 is the epilogue's critical path -- ncu: "wait" is its first stall reason)
 template <bool MASKED>
 __device__ __forceinline__ void push32(Top2x2& t, const uint32_t (&v)[32], int col0, int n_valid, KeyMul km)
 {
@@ -241,7 +258,10 @@ __device__ __forceinline__ void push32(Top2x2& t, const uint32_t (&v)[32], int c
                 pk[h] |= (c0 + 1) < n_valid ? 0u : 0xffff0000u;
             }
         }
-        t.push2(pk[0], pk[1]);
+        if(i & 4)
+            t.push2_alt(pk[0], pk[1]);
+        else
+            t.push2(pk[0], pk[1]);
     }
 }
 
@@ -281,30 +301,24 @@ __device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_vali
 }
 
 // NG groups of 32 accumulator columns starting at column col0 of a 128-column key window of which the first n_valid exist
-// (n_valid may be <= col0: nothing to do); loads double-buffered in registers
+// (n_valid may be <= col0: nothing to do).  One register buffer: this form runs with four epilogue warps per scheduler, which
+// cover each other's tensor-memory load latency, and has to fit 112 registers.
 template <int NG>
 __device__ __forceinline__ void drain_cols(Top2x2& t, uint32_t taddr, int col0, int n_valid, KeyMul km)
 {
-    uint32_t va[32], vb[32];
-    if(col0 >= n_valid)
-        return;
-    tmem_ld32(taddr, va);
+    uint32_t v[32];
 #pragma unroll
     for(int g = 0; g < NG; ++g)
     {
-        uint32_t(&cur)[32] = (g & 1) ? vb : va;
-        uint32_t(&nxt)[32] = (g & 1) ? va : vb;
         const int c = col0 + 32 * g;
-        tmem_wait(cur);
-        const bool more = g + 1 < NG && c + 32 < n_valid; // warp-uniform
-        if(more)
-            tmem_ld32(taddr + 32 * (g + 1), nxt);
-        if(c + 32 <= n_valid)
-            push32<false>(t, cur, c, n_valid, km);
-        else
-            push32<true>(t, cur, c, n_valid, km);
-        if(!more)
+        if(c >= n_valid) // warp-uniform
             break;
+        tmem_ld32(taddr + 32 * g, v);
+        tmem_wait(v);
+        if(c + 32 <= n_valid)
+            push32<false>(t, v, c, n_valid, km);
+        else
+            push32<true>(t, v, c, n_valid, km);
     }
 }
 
@@ -610,6 +624,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1)
                     else
                         mbar_arrive(bar_cempty + 8 * as);
                 }
+                t.fold();
                 unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
                 merge2(t0, t1, widen_key(t.k0 >> 16, col_base), widen_key(t.k1 >> 16, col_base));
                 merge2(k0, k1, t0, t1);
@@ -808,7 +823,8 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                         mbar_arrive(bar_cempty + 8 * a);
                     if(n_valid > col0)
                     {
-                        unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
+                        t.fold();
+                unsigned t0 = widen_key(t.k0 & 0xffffu, col_base), t1 = widen_key(t.k1 & 0xffffu, col_base);
                         merge2(t0, t1, widen_key(t.k0 >> 16, col_base), widen_key(t.k1 >> 16, col_base));
                         merge2(k0[a], k1[a], t0, t1);
                     }
