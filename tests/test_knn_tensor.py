@@ -1,7 +1,9 @@
 """GPU parity tests of the tensor-core kNN / keyframe-DB scoring kernel (csrc/knn_mma.cu), forced on with
 MSLAM_B200_FLAG_KNN_TENSOR and compared bit for bit with the CPU oracle (oracle/orb_oracle.c: orc_knn2 / orc_match_*,
 orc_db_scores) and with the scalar XOR + POPC kernel (MSLAM_B200_FLAG_KNN_SCALAR).  The cases sit on the kernel's seams:
-128-descriptor train tiles, 256-query CTAs, the 4-stage ring and 2-stage accumulator wrap-around, ragged last tiles,
+128-descriptor key windows and 256-descriptor train tiles (the N = 256 form: the two column halves of a tile are drained by
+different warps, so last tiles that end inside the first half, on the half boundary and inside the second half all occur),
+256-query CTAs, the ring and accumulator-stage wrap-around, ragged last tiles,
 distance extremes (0 and 256) and ties (equal distance -> lower train index)."""
 import numpy as np
 import pytest
@@ -34,7 +36,7 @@ def _sets(rng, n_q, n_t, copies=0.3):
 
 @pytest.mark.parametrize("n_q,n_t", [(1, 1), (1, 2), (5, 127), (127, 128), (128, 129), (129, 255), (255, 256), (256, 257),
                                      (257, 511), (300, 512), (513, 513), (640, 1025), (1400, 1400), (1400, 3), (3, 1400),
-                                     (1279, 1281)])
+                                     (1279, 1281), (300, 383), (300, 384), (300, 385), (700, 641), (260, 897), (131, 769)])
 def test_knn2_sizes_on_tile_seams(tensor_ctx, scalar_ctx, oracle, n_q, n_t):
     rng = np.random.default_rng(n_q * 7919 + n_t)
     q, t = _sets(rng, n_q, n_t)
