@@ -777,7 +777,15 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         ctx->P.n_frames = n_frames;
         const PipeParams& P = ctx->P;
         cudaStream_t s_fast = ctx->aux[0], s_blur = ctx->aux[1];
-        const int nl = P.nlevels, l_split = std::min(2, nl); // levels < l_split get their own FAST launch
+        static int split_env = -1; // A/B aid: MSLAM_FAST_SPLIT = number of leading levels with their own FAST / blur launches
+        if(split_env < 0)
+        {
+            const char* e = getenv("MSLAM_FAST_SPLIT");
+            split_env = e ? atoi(e) : 2;
+            if(split_env < 1 || split_env > 4)
+                split_env = 2;
+        }
+        const int nl = P.nlevels, l_split = std::min(split_env, nl); // levels < l_split get their own FAST launch
         {
             StageTimer t(ctx, MSLAM_B200_T_GRAY);
             launch_gray(st, d_bgr, ctx->d_pyr, P, &ctx->launches);
