@@ -300,6 +300,104 @@ __device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_vali
     group(vb, 96);
 }
 
+// ---- keyframe-database scoring needs distances only, not indices: with accumulators that START at 256 (the epilogue writes the
+// bias back after every drain, all eight K steps accumulate) every value 256 + dot = 512 - 2 hamming is non-negative, two of
+// them pack into one register with ONE IMAD (odd * 65536 + even, no carries), and the two LARGEST per 16-bit lane are the two
+// nearest neighbours.  (One IMAD per key pair instead of two measured +7 % on the epilogue-bound kernel.) ----
+__device__ __forceinline__ void tmem_st32_const(uint32_t taddr, uint32_t c)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr),
+                 "r"(c)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st()
+{
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+constexpr uint32_t kAccBias = 256;
+struct Top2Max
+{
+    unsigned k0 = 0, k1 = 0, a0 = 0, a1 = 0; // two independent chains of (largest, second largest) per 16-bit lane; 0 = nothing yet
+    __device__ __forceinline__ void push2(unsigned a, unsigned b)
+    {
+        const unsigned M = __vmaxu2(a, b), m = __vminu2(a, b);
+        k1 = __vimax3_u16x2(k1, __vminu2(k0, M), m);
+        k0 = __vmaxu2(k0, M);
+    }
+    __device__ __forceinline__ void push2_alt(unsigned a, unsigned b)
+    {
+        const unsigned M = __vmaxu2(a, b), m = __vminu2(a, b);
+        a1 = __vimax3_u16x2(a1, __vminu2(a0, M), m);
+        a0 = __vmaxu2(a0, M);
+    }
+    // the two largest of all four lanes' (largest, second largest), as plain integers
+    __device__ __forceinline__ void top2(unsigned& m0, unsigned& m1) const
+    {
+        const unsigned hi = __vmaxu2(k0, a0), lo = __vminu2(k0, a0);
+        const unsigned se = __vimax3_u16x2(lo, k1, a1); // per lane: (hi, se) = its two largest
+        const unsigned h0 = hi & 0xffffu, h1 = hi >> 16, s0 = se & 0xffffu, s1 = se >> 16;
+        m0 = max(h0, h1);
+        m1 = max(min(h0, h1), max(s0, s1));
+    }
+};
+__device__ __forceinline__ void merge2max(unsigned& m0, unsigned& m1, unsigned o0, unsigned o1)
+{
+    const unsigned hi = max(m0, o0), lo = min(m0, o0);
+    m1 = max(lo, max(m1, o1));
+    m0 = hi;
+}
+// 32 biased accumulators -> 16 packed pairs -> the max chains; MASKED: columns >= n_valid count as 0 ("nothing")
+template <bool MASKED>
+__device__ __forceinline__ void push32_max(Top2Max& t, const uint32_t (&v)[32], int col0, int n_valid, unsigned two16)
+{
+#pragma unroll
+    for(int i = 0; i < 32; i += 4)
+    {
+        unsigned pk[2];
+#pragma unroll
+        for(int h = 0; h < 2; ++h)
+        {
+            const int c0 = col0 + i + 2 * h;
+            pk[h] = v[i + 2 * h + 1] * two16 + v[i + 2 * h];
+            if(MASKED)
+                pk[h] &= (c0 < n_valid ? 0x0000ffffu : 0u) | ((c0 + 1) < n_valid ? 0xffff0000u : 0u);
+        }
+        if(i & 4)
+            t.push2_alt(pk[0], pk[1]);
+        else
+            t.push2(pk[0], pk[1]);
+    }
+}
+// one 128-column key window of a biased accumulator: drain (double-buffered loads) and write the bias back behind every load
+__device__ __forceinline__ void drain_tile_max(Top2Max& t, uint32_t taddr, int n_valid, unsigned two16)
+{
+    uint32_t va[32], vb[32];
+    auto group = [&](const uint32_t (&v)[32], int col0) {
+        if(col0 + 32 <= n_valid) // warp-uniform
+            push32_max<false>(t, v, col0, n_valid, two16);
+        else if(col0 < n_valid)
+            push32_max<true>(t, v, col0, n_valid, two16);
+    };
+    tmem_ld32(taddr, va);
+    tmem_wait(va);
+    tmem_ld32(taddr + 32, vb);
+    tmem_st32_const(taddr, kAccBias);
+    group(va, 0);
+    tmem_wait(vb);
+    tmem_ld32(taddr + 64, va);
+    tmem_st32_const(taddr + 32, kAccBias);
+    group(vb, 32);
+    tmem_wait(va);
+    tmem_ld32(taddr + 96, vb);
+    tmem_st32_const(taddr + 64, kAccBias);
+    group(va, 64);
+    tmem_wait(vb);
+    tmem_st32_const(taddr + 96, kAccBias);
+    group(vb, 96);
+    tmem_wait_st();
+}
+
 // NG groups of 32 accumulator columns starting at column col0 of a 128-column key window of which the first n_valid exist
 // (n_valid may be <= col0: nothing to do).  One register buffer: this form runs with four epilogue warps per scheduler, which
 // cover each other's tensor-memory load latency, and has to fit 112 registers.
@@ -709,6 +807,9 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
         }
     };
     const int n_row_tiles = nq - q0 > MMA_M ? 2 : 1;
+    // database scoring with the eight-warp epilogue runs on biased accumulators (see drain_tile_max): the epilogue warps write
+    // 256 into every accumulator column once at the start and again behind every drain, all eight K steps accumulate
+    constexpr bool BIAS = DB && EW == 8;
     uint8_t* sA = smem;
     uint8_t* sB = smem + A_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_BYTES + WIDE_STAGES * WIDE_B_BYTES);
@@ -773,14 +874,16 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                     const uint32_t b_addr = smem_u32(sB + s * WIDE_B_BYTES);
                     for(int a = 0; a < n_row_tiles; ++a)
                     {
-                        mbar_wait(bar_cempty + 8 * a, (it & 1) ^ 1); // query tile a's accumulator of the previous train tile is drained
+                        // query tile a's accumulator of the previous train tile is drained (BIAS: and re-initialised; the first
+                        // phase of the barrier is the epilogue's initial write of the bias)
+                        mbar_wait(bar_cempty + 8 * a, BIAS ? (it & 1) : ((it & 1) ^ 1));
                         tc_fence_after();
 #pragma unroll
                         for(int k = 0; k < ROW_BYTES / 32; ++k)
                             asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                                          "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem + a * WIDE_N),
                                          "l"(smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256)), "l"(smem_desc(b_addr + k * 256)),
-                                         "r"(kIdescWide), "r"((uint32_t)(k > 0))
+                                         "r"(kIdescWide), "r"((uint32_t)(BIAS || k > 0))
                                          : "memory");
                         umma_commit(bar_cfull + 8 * a);
                     }
@@ -794,8 +897,27 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
         const int quarter = warp & 3, part = warp >> 2;
         const int win = (part * CPW) / MMA_N, col0 = (part * CPW) % MMA_N; // 128-column key window of the part, first column in it
         unsigned k0[2], k1[2];
+        if(BIAS)
+        {
+#pragma unroll
+            for(int a = 0; a < 2; ++a)
+            {
+                const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * WIDE_N + part * CPW;
+#pragma unroll
+                for(int c = 0; c < CPW; c += 32)
+                    tmem_st32_const(taddr + c, kAccBias);
+            }
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if(lane == 0)
+            {
+                mbar_arrive(bar_cempty);
+                mbar_arrive(bar_cempty + 8);
+            }
+        }
         for_each_tile(
-            [&] { k0[0] = k0[1] = k1[0] = k1[1] = kNoKey; },
+            [&] { k0[0] = k0[1] = k1[0] = k1[1] = BIAS ? 0u : kNoKey; },
             [&](int, int nt, int j, int it) {
                 const int col_base = j * WIDE_N + win * MMA_N;
                 const int n_valid = nt - col_base; // columns of this key window that exist (may be <= col0: nothing for this warp)
@@ -807,6 +929,19 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                     mbar_wait(bar_cfull + 8 * a, it & 1);
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * WIDE_N + part * CPW;
+                    if(BIAS)
+                    {
+                        Top2Max tm;
+                        drain_tile_max(tm, taddr, max(n_valid, 0), db.km.two16);
+                        tc_fence_before();
+                        __syncwarp();
+                        if(lane == 0)
+                            mbar_arrive(bar_cempty + 8 * a);
+                        unsigned m0, m1;
+                        tm.top2(m0, m1);
+                        merge2max(k0[a], k1[a], m0, m1);
+                        continue;
+                    }
                     Top2x2 t;
                     if(CPW == MMA_N) // a whole key window per warp: the hand-scheduled four-group form
                     {
@@ -855,7 +990,10 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                         for(int o = 0; o < NPARTS - 1; ++o)
                         {
                             const unsigned* e = xs + (((a * MMA_M + quarter * 32 + lane) * 3) + o) * 2;
-                            merge2(k0[a], k1[a], e[0], e[1]);
+                            if(BIAS)
+                                merge2max(k0[a], k1[a], e[0], e[1]);
+                            else
+                                merge2(k0[a], k1[a], e[0], e[1]);
                         }
                         const bool live = a < n_row_tiles && q < nq;
                         if(!DB)
@@ -868,7 +1006,8 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                         }
                         else
                         {
-                            const int d0 = (int)(k0[a] >> 16), d1 = (int)(k1[a] >> 16); // nt >= 2: both exist
+                            // nt >= 2: both exist.  BIAS: the values are 512 - 2 hamming
+                            const int d0 = BIAS ? (int)(512u - k0[a]) >> 1 : (int)(k0[a] >> 16), d1 = BIAS ? (int)(512u - k1[a]) >> 1 : (int)(k1[a] >> 16);
                             const bool pass = db.int_ratio ? (10 * d0 < 7 * d1) : ((double)(float)d0 < db.ratio * (double)(float)d1);
                             cnt += (live && pass) ? 1 : 0;
                         }
