@@ -4,6 +4,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include <algorithm>
 #include <new>
@@ -80,6 +81,15 @@ struct mslam_b200_ctx
         long long launches = 0;
     } graph1[2];
     int graphs_enabled = -1; // -1: read MSLAM_B200_GRAPH on first use
+    // ---- single-frame latency path (mslam_b200_detect with nothing else in flight) ----
+    // one result block per frame: [count, err, pad, pad | kp_cap keypoints | kp_cap descriptors], written by the kernels of a
+    // captured graph that also clears the frame's counters first and copies the block to its pinned mirror last, so a call is
+    // copy-in + graph launch + one wait on ONE stream (the general path hops through two copy streams and four D2H copies).
+    // (Measured and not kept: the describe kernel writing straight into mapped pinned memory instead of the copy node --
+    // the kernel grows from 10 to 14 us of posted PCIe writes, which is what the 75 KB copy node costs.)
+    uint8_t *d_one = nullptr, *h_one = nullptr;
+    size_t one_bytes = 0, one_kp_off = 0, one_desc_off = 0;
+    FrameGraph graph_lat;
     // ---- HBM: matcher ----
     uint8_t *d_mfrom = nullptr, *d_mto = nullptr, *d_raw = nullptr;
     int *d_nfrom = nullptr, *d_nto = nullptr;
@@ -114,8 +124,10 @@ struct mslam_b200_ctx
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t ev_level[kMaxLevels] = {nullptr};
     cudaEvent_t ev_join[2] = {nullptr, nullptr};
+    cudaEvent_t ev_fast0 = nullptr; // few-frames structure: FAST of level 0 done (it runs on the blur fork)
     // ---- per-stage event timing (mslam_b200_enable_stage_timing) ----
     bool timing = false;
+    bool timing_in_graph = false; // the stage events become real record nodes of a graph being captured (latency trace)
     std::vector<cudaEvent_t> ev_pool; // pairs: [2i] start, [2i+1] stop
     std::vector<int> ev_stage;        // stage of pair i
     std::vector<long long> ev_launches;
@@ -137,13 +149,19 @@ struct StageTimer
             return;
         pair = (int)c->ev_used++;
         c->ev_stage[pair] = stage;
-        cudaEventRecord(c->ev_pool[2 * pair], st);
+        if(c->timing_in_graph)
+            cudaEventRecordWithFlags(c->ev_pool[2 * pair], st, cudaEventRecordExternal);
+        else
+            cudaEventRecord(c->ev_pool[2 * pair], st);
     }
     ~StageTimer()
     {
         if(pair < 0)
             return;
-        cudaEventRecord(c->ev_pool[2 * pair + 1], st);
+        if(c->timing_in_graph)
+            cudaEventRecordWithFlags(c->ev_pool[2 * pair + 1], st, cudaEventRecordExternal);
+        else
+            cudaEventRecord(c->ev_pool[2 * pair + 1], st);
         c->ev_launches[pair] = c->launches - l0;
     }
 };
@@ -302,7 +320,7 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
         L.cand_cap = (wi > 0 && hi > 0) ? ((wi + 1) / 2) * ((hi + 1) / 2) : 0;
         L.cand_off = coff;
         coff += (long long)align_up((size_t)L.cand_cap, 4);
-        fast_tiles(L.w, L.h, cfg.edge_threshold, &L.tiles_x, &L.tiles_y, &L.tile_sh);
+        fast_tiles(L.w, L.h, cfg.edge_threshold, cfg.max_batch <= 2, &L.tiles_x, &L.tiles_y, &L.tile_sh);
         L.tile_base = tiles;
         tiles += L.tiles_x * L.tiles_y;
         int bw = 0;
@@ -446,11 +464,11 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb, ctx->d_xdb, ctx->d_xqf, ctx->d_pnp};
+                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb, ctx->d_xdb, ctx->d_xqf, ctx->d_pnp, ctx->d_one};
     for(void* p : dev)
         if(p)
             cudaFree(p);
-    void* host[] = {ctx->h_counts, ctx->h_err, ctx->h_out_a, ctx->h_out_b, ctx->h_out_d, ctx->h_nout, ctx->h_n2, ctx->h_pnp};
+    void* host[] = {ctx->h_counts, ctx->h_err, ctx->h_out_a, ctx->h_out_b, ctx->h_out_d, ctx->h_nout, ctx->h_n2, ctx->h_pnp, ctx->h_one};
     for(void* p : host)
         if(p)
             cudaFreeHost(p);
@@ -481,12 +499,14 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     for(int i = 0; i <= kMaxChunks; ++i)
         if(ctx->ev_done[i])
             cudaEventDestroy(ctx->ev_done[i]);
-    for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done, ctx->ev_match_done, ctx->ev_match_in, ctx->ev_match_k})
+    for(cudaEvent_t e : {ctx->ev_slot_done[0], ctx->ev_slot_done[1], ctx->ev_out_done, ctx->ev_match_done, ctx->ev_match_in, ctx->ev_match_k, ctx->ev_fast0})
         if(e)
             cudaEventDestroy(e);
     for(auto& g : ctx->graph1)
         if(g.exec)
             cudaGraphExecDestroy(g.exec);
+    if(ctx->graph_lat.exec)
+        cudaGraphExecDestroy(ctx->graph_lat.exec);
     if(ctx->own_stream && ctx->stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -567,6 +587,7 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     }
     for(int i = 0; i < kMaxLevels; ++i)
         CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_level[i], cudaEventDisableTiming));
+    CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_fast0, cudaEventDisableTiming));
     for(int i = 0; i < 2; ++i)
         CREATE_OK(cudaStreamCreateWithFlags(&ctx->copy[i], cudaStreamNonBlocking));
     for(int i = 0; i < kMaxChunks; ++i)
@@ -613,6 +634,11 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
         CREATE_OK(cudaMalloc(&ctx->d_icw, icw.size() * sizeof(unsigned)));
         CREATE_OK(cudaMemcpy(ctx->d_icw, icw.data(), icw.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
     }
+    ctx->one_kp_off = 16;
+    ctx->one_desc_off = align_up(ctx->one_kp_off + (size_t)ctx->kp_cap * sizeof(mslam_b200_keypoint), 32);
+    ctx->one_bytes = ctx->one_desc_off + (size_t)ctx->kp_cap * 32;
+    CREATE_OK(cudaMalloc(&ctx->d_one, ctx->one_bytes));
+    CREATE_OK(cudaHostAlloc(&ctx->h_one, ctx->one_bytes, cudaHostAllocDefault));
     CREATE_OK(cudaHostAlloc(&ctx->h_counts, 2 * B * sizeof(int), cudaHostAllocDefault));
     CREATE_OK(cudaHostAlloc(&ctx->h_err, 2 * B * sizeof(int), cudaHostAllocDefault));
     for(int i = 0; i < 2; ++i)
@@ -702,6 +728,9 @@ int mslam_b200_set_flags(mslam_b200_ctx* ctx, int flags)
             cudaGraphExecDestroy(g.exec);
         g = mslam_b200_ctx::FrameGraph{};
     }
+    if(ctx->graph_lat.exec)
+        cudaGraphExecDestroy(ctx->graph_lat.exec);
+    ctx->graph_lat = mslam_b200_ctx::FrameGraph{};
     return apply_knn_flags(ctx);
 }
 
@@ -741,9 +770,11 @@ static int run_pyramid(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int n_frames)
 // enqueue the detect pipeline for frames [frame0, frame0 + n_frames) of the batch buffers (geometry already set, the
 // zero block already cleared); outputs are indexed by absolute frame
 static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, int n_frames, mslam_b200_keypoint* d_kp,
-                        uint8_t* d_desc, int capacity, int* d_counts)
+                        uint8_t* d_desc, int capacity, int* d_counts, int* d_err = nullptr)
 {
     cudaStream_t st = ctx->stream;
+    if(!d_err)
+        d_err = ctx->d_err; // per-frame "selection overflowed" flags, part of the zeroed block
     ctx->P.frame0 = frame0;
     const int n_slots = std::min(capacity, ctx->kp_cap * ctx->P.nlevels);
     if(ctx->cfg.flags & MSLAM_B200_FLAG_SERIAL)
@@ -757,7 +788,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         {
             StageTimer t(ctx, MSLAM_B200_T_SELECT);
             launch_select(st, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
-                          ctx->d_sel, ctx->d_err, P, ctx->sm_count, &ctx->launches);
+                          ctx->d_sel, d_err, P, ctx->sm_count, &ctx->launches);
         }
         {
             StageTimer t(ctx, MSLAM_B200_T_BLUR);
@@ -765,7 +796,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         }
         StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
         launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_icw, d_kp, d_desc, d_counts, capacity,
-                               n_slots, P, &ctx->launches);
+                               n_slots, P, ctx->sm_count, &ctx->launches);
     }
     else
     {
@@ -777,6 +808,58 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         ctx->P.n_frames = n_frames;
         const PipeParams& P = ctx->P;
         cudaStream_t s_fast = ctx->aux[0], s_blur = ctx->aux[1];
+        if(n_frames <= 2)
+        {
+            // One or two frames: every launch is a step of a latency chain (a tile's walk, ~10 us), not throughput, and launches
+            // on one stream run one after the other.  The MSLAM_B200_LAT_TRACE=2 timeline of the batch structure below showed the
+            // chain done at 40 us while FAST(0), FAST(1), FAST(2..) in a row on the fork kept select waiting until 72.  Here
+            // FAST(0) runs under the chain on the blur stream, FAST(1..) is ONE launch behind the chain on the other fork (all
+            // its tiles fit the machine at once), the blur is one launch behind FAST(0), select waits for both FAST launches.
+            const int nl = P.nlevels;
+            {
+                StageTimer t(ctx, MSLAM_B200_T_GRAY);
+                launch_gray(st, d_bgr, ctx->d_pyr, P, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[0], st));
+            if(nl > 1)
+            {
+                StageTimer t(ctx, MSLAM_B200_T_RESIZE);
+                launch_pyramid(st, ctx->d_pyr, P, ctx->d_xtab, ctx->d_ytab, ctx->d_qtab, ctx->sm_count, 1, nl, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_level[nl - 1], st));
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_blur, ctx->ev_level[0], 0));
+            {
+                StageTimer t(ctx, MSLAM_B200_T_FAST, s_blur);
+                launch_fast(s_blur, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, ctx->fast_maps, 0, 1, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_fast0, s_blur));
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_blur, ctx->ev_level[nl - 1], 0));
+            {
+                StageTimer t(ctx, MSLAM_B200_T_BLUR, s_blur);
+                launch_blur(s_blur, ctx->d_pyr, ctx->d_blur, P, 0, nl, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[1], s_blur));
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_fast, ctx->ev_level[nl - 1], 0));
+            if(nl > 1)
+            {
+                StageTimer t(ctx, MSLAM_B200_T_FAST, s_fast);
+                launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, ctx->fast_maps, 1, nl, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(s_fast, ctx->ev_fast0, 0));
+            {
+                StageTimer t(ctx, MSLAM_B200_T_SELECT, s_fast);
+                launch_select(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
+                              ctx->d_sel, d_err, P, ctx->sm_count, &ctx->launches);
+            }
+            MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[0], s_fast));
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[0], 0));
+            MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[1], 0));
+            StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
+            launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_icw, d_kp, d_desc, d_counts, capacity,
+                                   n_slots, P, ctx->sm_count, &ctx->launches);
+            MSLAM_CUDA_OK(cudaGetLastError());
+            return MSLAM_B200_OK;
+        }
         static int split_env = -1; // A/B aid: MSLAM_FAST_SPLIT = number of leading levels with their own FAST / blur launches
         if(split_env < 0)
         {
@@ -824,7 +907,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         {
             StageTimer t(ctx, MSLAM_B200_T_SELECT, s_fast);
             launch_select(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_cand2, ctx->d_keys, ctx->d_keys2, ctx->d_ctr, ctx->d_hist,
-                          ctx->d_sel, ctx->d_err, P, ctx->sm_count, &ctx->launches);
+                          ctx->d_sel, d_err, P, ctx->sm_count, &ctx->launches);
         }
         MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_join[0], s_fast));
         for(int l = 0; l < l_split; ++l)
@@ -844,7 +927,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
         MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join[1], 0));
         StageTimer t(ctx, MSLAM_B200_T_DESCRIBE);
         launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_icw, d_kp, d_desc, d_counts, capacity,
-                               n_slots, P, &ctx->launches);
+                               n_slots, P, ctx->sm_count, &ctx->launches);
     }
     MSLAM_CUDA_OK(cudaGetLastError());
     return MSLAM_B200_OK;
@@ -1017,6 +1100,8 @@ static int detect_batch_finish(mslam_b200_ctx* ctx, int slot)
     mslam_b200_ctx::PendingBatch& pb = ctx->pend[slot];
     pb.active = false;
     MSLAM_CUDA_OK(cudaEventSynchronize(ctx->ev_slot_done[slot]));
+    if(!ctx->pend[slot ^ 1].active)
+        ctx->out_done_valid = false; // the copy-out stream has drained: nothing for the next call to wait for
     const size_t B = (size_t)ctx->cfg.max_batch;
     int rc = MSLAM_B200_OK;
     for(int i = 0; i < pb.n_frames; ++i)
@@ -1076,12 +1161,199 @@ int mslam_b200_detect_batch_end(mslam_b200_ctx* ctx)
     return detect_batch_finish(ctx, slot);
 }
 
+// The call the reference's frontend makes once per frame (IFeatureDetector::detect, rgbd_feature_frontend.cpp:187) with nothing
+// else in flight on the context.  Returns kTakeGeneralPath when the call has to take the general path (first call of a geometry, graphs off,
+// stage timing on, a pipelined batch in flight), else the status of the finished call.
+// Measured (tools/latency_breakdown.py, 640x480 / 1000 keypoints): the kernels of one frame span ~57 us on the GPU and the
+// 0.9 MB frame copy 18 us, but the general path took 194 us wall -- three streams, six event hops, a memset, four device->host
+// copies into caller memory.  Here: copy-in, ONE graph launch (clear counters -> kernels -> result block to its pinned
+// mirror), one stream wait, two host memcpy into the caller's arrays.
+constexpr int kTakeGeneralPath = 1; // not a status of the C ABI (those are <= 0)
+static int detect_one_latency(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int height, int stride_bytes,
+                              mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(ctx->graphs_enabled < 0)
+    {
+        const char* e = getenv("MSLAM_B200_GRAPH");
+        ctx->graphs_enabled = e ? atoi(e) != 0 : 1;
+    }
+    static int lat_env = -1; // A/B aid: MSLAM_B200_LATENCY_PATH=0 sends single frames through the general path
+    if(lat_env < 0)
+    {
+        const char* e = getenv("MSLAM_B200_LATENCY_PATH");
+        lat_env = e ? atoi(e) != 0 : 1;
+    }
+    if(!lat_env || !ctx->graphs_enabled || ctx->timing || (ctx->cfg.flags & MSLAM_B200_FLAG_SERIAL) || ctx->pend[0].active ||
+       ctx->pend[1].active)
+        return kTakeGeneralPath;
+    MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    int rc = set_geometry(ctx, width, height);
+    if(rc)
+        return rc;
+    cudaStream_t st = ctx->stream;
+    auto& g = ctx->graph_lat;
+    if(g.width != width || g.height != height)
+    {
+        if(g.exec)
+            cudaGraphExecDestroy(g.exec);
+        g = mslam_b200_ctx::FrameGraph{};
+        g.width = width, g.height = height;
+    }
+    // MSLAM_B200_LAT_TRACE=1: where a call's time goes (host clock at each step, GPU time of the copy-in and of the graph), averaged
+    // over 100 calls to stderr.  The events sit between the operations, so a traced call is a few microseconds slower.
+    // =2: the graph is also captured with the stage timers' event pairs in it, and every 100th call prints when each stage began
+    // and ended on the GPU (microseconds after the copy-in).
+    static int trace = -1;
+    static cudaEvent_t tev[3];
+    static double tacc[6];
+    static int tn = 0, tpairs = 0;
+    if(trace < 0)
+    {
+        const char* e = getenv("MSLAM_B200_LAT_TRACE");
+        trace = e ? atoi(e) : 0;
+        if(trace)
+            for(auto& ev : tev)
+                cudaEventCreate(&ev);
+    }
+    int* d_hdr = reinterpret_cast<int*>(ctx->d_one);
+    mslam_b200_keypoint* d_kp1 = reinterpret_cast<mslam_b200_keypoint*>(ctx->d_one + ctx->one_kp_off);
+    uint8_t* d_desc1 = ctx->d_one + ctx->one_desc_off;
+    if(!g.exec)
+    {
+        if(g.uses++ < 1)
+            return kTakeGeneralPath; // first call of a geometry: direct launches (one-time kernel set-up happens outside any capture)
+        const long long l0 = ctx->launches;
+        cudaGraph_t graph = nullptr;
+        bool ok = cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+        if(ok)
+        {
+            // frame 0's slice of the zeroed block (counters and histograms are [frame][level]) and the result header
+            ok = cudaMemsetAsync(ctx->d_ctr, 0, ctx->P.nlevels * sizeof(LevelCounters), st) == cudaSuccess && ok;
+            ok = cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->P.nlevels * 256 * sizeof(unsigned), st) == cudaSuccess && ok;
+            ok = cudaMemsetAsync(ctx->d_one, 0, 16, st) == cudaSuccess && ok;
+            if(trace >= 2)
+            {
+                if(ctx->ev_pool.empty())
+                {
+                    ctx->ev_pool.resize(128);
+                    for(auto& ev : ctx->ev_pool)
+                        cudaEventCreate(&ev);
+                    ctx->ev_stage.assign(64, 0);
+                    ctx->ev_launches.assign(64, 0);
+                }
+                ctx->timing = ctx->timing_in_graph = true, ctx->ev_used = 0;
+            }
+            ok = detect_range(ctx, ctx->d_bgr, 0, 1, d_kp1, d_desc1, ctx->kp_cap, d_hdr, d_hdr + 1) == MSLAM_B200_OK && ok;
+            if(trace >= 2)
+            {
+                tpairs = (int)ctx->ev_used;
+                ctx->timing = ctx->timing_in_graph = false, ctx->ev_used = 0;
+            }
+            ok = cudaMemcpyAsync(ctx->h_one, ctx->d_one, ctx->one_bytes, cudaMemcpyDeviceToHost, st) == cudaSuccess && ok;
+            ok = (cudaStreamEndCapture(st, &graph) == cudaSuccess) && ok && graph;
+        }
+        if(ok)
+            ok = cudaGraphInstantiate(&g.exec, graph, 0) == cudaSuccess;
+        if(graph)
+            cudaGraphDestroy(graph);
+        g.launches = ctx->launches - l0;
+        ctx->launches = l0; // nothing ran yet
+        if(!ok)
+        {
+            cudaGetLastError();
+            g.exec = nullptr;
+            ctx->graphs_enabled = 0;
+            return kTakeGeneralPath;
+        }
+    }
+    // results of an earlier batch may still be leaving through the copy-out stream, which reads the zeroed block's err flags
+    if(ctx->out_done_valid)
+    {
+        MSLAM_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_out_done, 0));
+        ctx->out_done_valid = false;
+    }
+    auto now_us = []() {
+        timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+    };
+    const double t0 = trace ? now_us() : 0.0;
+    if(trace)
+        cudaEventRecord(tev[0], st);
+    const size_t row = (size_t)width * 3;
+    if((size_t)stride_bytes == row)
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_bgr, bgr, row * height, cudaMemcpyHostToDevice, st));
+    else
+        MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr, row, bgr, (size_t)stride_bytes, row, (size_t)height, cudaMemcpyHostToDevice, st));
+    const double t1 = trace ? now_us() : 0.0;
+    if(trace)
+        cudaEventRecord(tev[1], st);
+    ctx->P.frame0 = 0, ctx->P.n_frames = 1;
+    ctx->last_frames = 1;
+    MSLAM_CUDA_OK(cudaGraphLaunch(g.exec, st));
+    ctx->launches += g.launches;
+    const double t2 = trace ? now_us() : 0.0;
+    if(trace)
+        cudaEventRecord(tev[2], st);
+    MSLAM_CUDA_OK(cudaStreamSynchronize(st));
+    const double t3 = trace ? now_us() : 0.0;
+    const int* hdr = reinterpret_cast<const int*>(ctx->h_one);
+    const int n = hdr[0], m = std::max(0, std::min(std::min(n, capacity), ctx->kp_cap));
+    memcpy(out_kp, ctx->h_one + ctx->one_kp_off, (size_t)m * sizeof(mslam_b200_keypoint));
+    memcpy(out_desc, ctx->h_one + ctx->one_desc_off, (size_t)m * 32);
+    n_out[0] = n;
+    if(trace)
+    {
+        float g01 = 0.f, g12 = 0.f;
+        cudaEventElapsedTime(&g01, tev[0], tev[1]);
+        cudaEventElapsedTime(&g12, tev[1], tev[2]);
+        const double t4 = now_us();
+        const double v[6] = {t1 - t0, t2 - t1, t3 - t2, t4 - t3, g01 * 1e3, g12 * 1e3};
+        for(int i = 0; i < 6; ++i)
+            tacc[i] += v[i];
+        if(++tn == 100)
+        {
+            fprintf(stderr, "[mslam_b200 latency path, us] host: copy-in enqueue %.1f, graph launch %.1f, wait %.1f, unpack %.1f | gpu: copy-in %.1f, graph %.1f\n",
+                    tacc[0] / tn, tacc[1] / tn, tacc[2] / tn, tacc[3] / tn, tacc[4] / tn, tacc[5] / tn);
+            tn = 0;
+            for(double& a : tacc)
+                a = 0.0;
+            if(trace >= 2)
+            {
+                static const char* names[] = {"gray", "resize", "fast", "select", "blur", "describe", "knn", "compact"};
+                for(int i = 0; i < tpairs; ++i)
+                {
+                    float a = 0.f, b = 0.f;
+                    // relative to the first event inside the graph (gray's start)
+                    const cudaError_t ea = cudaEventElapsedTime(&a, ctx->ev_pool[0], ctx->ev_pool[2 * i]);
+                    const cudaError_t eb = cudaEventElapsedTime(&b, ctx->ev_pool[0], ctx->ev_pool[2 * i + 1]);
+                    if(ea != cudaSuccess || eb != cudaSuccess)
+                    {
+                        fprintf(stderr, "    (event query: %s / %s)\n", cudaGetErrorName(ea), cudaGetErrorName(eb));
+                        cudaGetLastError();
+                    }
+                    const int sg = ctx->ev_stage[i];
+                    fprintf(stderr, "    %-8s %6.1f .. %6.1f\n", sg >= 0 && sg < 8 ? names[sg] : "?", a * 1e3, b * 1e3);
+                }
+                fprintf(stderr, "    graph end %6.1f\n", g12 * 1e3);
+            }
+        }
+    }
+    return (n > capacity || hdr[1]) ? MSLAM_B200_E_CAPACITY : MSLAM_B200_OK;
+}
+
 int mslam_b200_detect_batch(mslam_b200_ctx* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
                             int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
 {
     if(!detect_batch_args_ok(ctx, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity, n_out) ||
        ctx->pend[0].active || ctx->pend[1].active)
         return MSLAM_B200_E_INVALID;
+    if(n_frames == 1)
+    {
+        const int rc1 = detect_one_latency(ctx, frames[0], width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
+        if(rc1 != kTakeGeneralPath)
+            return rc1;
+    }
     int rc = mslam_b200_detect_batch_begin(ctx, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
     if(rc)
         return rc;
@@ -1152,7 +1424,7 @@ int mslam_b200_describe(mslam_b200_ctx* ctx, const uint8_t* bgr, int width, int 
     run_pyramid(ctx, ctx->d_bgr, 1);
     launch_blur(st, ctx->d_pyr, ctx->d_blur, ctx->P, 0, ctx->P.nlevels, &ctx->launches);
     launch_orient_describe(st, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel, ctx->d_pat, ctx->d_icw, ctx->d_kp, ctx->d_desc, ctx->d_counts, icap,
-                           std::max(n_kp, 1), ctx->P, &ctx->launches);
+                           std::max(n_kp, 1), ctx->P, ctx->sm_count, &ctx->launches);
     std::vector<mslam_b200_keypoint> hk((size_t)std::max(n_kp, 1));
     std::vector<uint8_t> hd((size_t)std::max(n_kp, 1) * 32);
     if(n_kp > 0)

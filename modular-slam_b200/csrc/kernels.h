@@ -10,7 +10,7 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
                     const uint4* qtab, int sm_count, int l_begin, int l_end, long long* launches);
 void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, int l_begin, int l_end,
                  long long* launches);
-void fast_tiles(int w, int h, int edge, int* tx, int* ty, int* tile_sh);
+void fast_tiles(int w, int h, int edge, bool few_frames, int* tx, int* ty, int* tile_sh);
 void blur_warps(int w, int h, int* xblocks, int* warps);
 int blur_band_rows();
 // one CUtensorMap (128 opaque bytes) per pyramid level: the FAST kernel's tile loads (k_fast, orb_kernels.cu)
@@ -26,7 +26,8 @@ void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned
                    long long* launches);
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
                             const SelRec* sel, const float4* pat_t, const uint2* ic_w, mslam_b200_keypoint* out_kp,
-                            uint8_t* out_desc, int* out_counts, int out_cap, int n_slots, const PipeParams& P, long long* launches);
+                            uint8_t* out_desc, int* out_counts, int out_cap, int n_slots, const PipeParams& P, int sm_count,
+                            long long* launches);
 void ic_weight_table(unsigned* out /* 4 * 31 * 9 * 2 */);
 void brief_pattern_transposed(float* out1024);
 // matching path

@@ -860,7 +860,7 @@ __device__ float harris_response(const uint8_t* __restrict__ img, int pitch, int
     return __fmul_rn(t, s4);
 }
 
-constexpr int SEL_RANK_SMEM = 2048; // final (y, x) ranking runs out of shared memory up to this many survivors
+constexpr int SEL_SMEM = 2048; // the survivor lists of both cuts live in shared memory up to this many entries (global beyond)
 
 // Block-wide "k-th largest bin" over a 256-bin histogram, one bin per thread (bin = tid):
 //   S[v] = sum of bins >= v.  The unique v with S[v] >= k > S[v + 1] is written to *s_thr and k - S[v + 1] to *s_k.
@@ -892,6 +892,11 @@ __device__ __forceinline__ void suffix_select(unsigned hval, unsigned k, unsigne
     __syncthreads();
 }
 
+// The CTA is a chain of dependent steps (scan -> Harris -> four radix passes -> compaction -> ranking); with the lists in global
+// memory every step began with an exposed L2 round trip (~14 of them, most of the kernel's 17 us on one frame).  Now the
+// first-cut survivors (record + response key) and the final survivors sit in shared memory whenever they fit -- 2 n_l + ties
+// and n_l + ties entries: always, for the reference's feature counts -- and the global lists are written only as the
+// overflow fallback reads them; the candidate scan keeps four loads in flight per thread.
 template <int SEL_THREADS>
 __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                         unsigned* __restrict__ cand, unsigned* __restrict__ cand2,
@@ -901,7 +906,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
 {
     __shared__ unsigned s_hist[256];
     __shared__ unsigned s_w[8];
-    __shared__ unsigned s_rank[SEL_RANK_SMEM];
+    __shared__ unsigned s_rec[SEL_SMEM], s_key[SEL_SMEM];   // first-cut survivors: candidate record, ordered response key
+    __shared__ unsigned s_frec[SEL_SMEM], s_fkey[SEL_SMEM]; // final survivors
     __shared__ unsigned s_cnt, s_thr, s_k;
     const int l = blockIdx.x, b = blockIdx.y + P.frame0, tid = threadIdx.x;
     const LevelDesc& L = P.lv[l];
@@ -912,6 +918,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
     unsigned* k2v = keys2 + (long long)b * P.cand_frame_stride + L.cand_off;
     const uint8_t* img = pyr + L.img_off + (long long)b * L.img_frame_stride;
 
+    // the counter and the histogram bin travel together (the bin is only needed when the cut is)
+    const unsigned hval = tid < 256 ? hist[((long long)b * P.nlevels + l) * 256 + tid] : 0u;
     unsigned n = C->n_fast;
     if(n > (unsigned)L.cand_cap)
     {
@@ -929,28 +937,49 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
         else
         {
             // the histogram counts every NMS survivor (>= n > kcut1 entries), so the k-th largest exists
-            suffix_select(tid < 256 ? hist[((long long)b * P.nlevels + l) * 256 + tid] : 0u, kcut1, s_w, &s_thr, &s_k);
+            suffix_select(hval, kcut1, s_w, &s_thr, &s_k);
             thr1 = s_thr;
         }
     }
     if(tid == 0)
         s_cnt = 0;
     __syncthreads();
-    for(unsigned i = tid; i < n; i += SEL_THREADS)
+    for(unsigned i0 = 0; i0 < n; i0 += 4 * SEL_THREADS)
     {
-        const unsigned rec = c1[i];
-        if((rec & 255u) >= thr1)
-            c2[atomicAdd(&s_cnt, 1u)] = rec;
+        unsigned rec[4];
+#pragma unroll
+        for(int j = 0; j < 4; ++j)
+        {
+            const unsigned i = i0 + j * SEL_THREADS + tid;
+            rec[j] = i < n ? c1[i] : 0u;
+        }
+#pragma unroll
+        for(int j = 0; j < 4; ++j)
+        {
+            const unsigned i = i0 + j * SEL_THREADS + tid;
+            if(i < n && (rec[j] & 255u) >= thr1)
+            {
+                const unsigned pos = atomicAdd(&s_cnt, 1u);
+                if(pos < (unsigned)SEL_SMEM)
+                    s_rec[pos] = rec[j];
+                c2[pos] = rec[j];
+            }
+        }
     }
     __syncthreads();
     const unsigned m = s_cnt;
+    const bool m_smem = m <= (unsigned)SEL_SMEM;
     if(tid == 0)
         C->n_cut1 = m;
     // ---- Harris on the survivors ----
     for(unsigned i = tid; i < m; i += SEL_THREADS)
     {
-        const unsigned rec = c2[i];
-        k1v[i] = fkey(harris_response(img, L.pitch, (rec >> 8) & 0xfffu, rec >> 20));
+        const unsigned rec = m_smem ? s_rec[i] : c2[i];
+        const unsigned k = fkey(harris_response(img, L.pitch, (rec >> 8) & 0xfffu, rec >> 20));
+        if(m_smem)
+            s_key[i] = k;
+        else
+            k1v[i] = k;
     }
     __syncthreads();
     // ---- cut 2: k-th largest response (radix select, MSB first) ----
@@ -970,7 +999,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
                 __syncthreads();
                 for(unsigned i = tid; i < m; i += SEL_THREADS)
                 {
-                    const unsigned k = k1v[i];
+                    const unsigned k = m_smem ? s_key[i] : k1v[i];
                     if((k & mask) == prefix)
                         atomicAdd(&s_hist[(k >> shift) & 255u], 1u);
                 }
@@ -985,18 +1014,24 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
             thrkey = prefix;
         }
     }
-    // ---- final compaction (list reuses the dead first-cut input) ----
+    // ---- final compaction (the global list reuses the dead first-cut input) ----
     if(tid == 0)
         s_cnt = 0;
     __syncthreads();
     const bool keep_none = (m > kcut2 && kcut2 == 0);
     for(unsigned i = tid; i < m; i += SEL_THREADS)
     {
-        const unsigned k = k1v[i];
+        const unsigned k = m_smem ? s_key[i] : k1v[i];
         if(!keep_none && k >= thrkey)
         {
             const unsigned pos = atomicAdd(&s_cnt, 1u);
-            c1[pos] = c2[i];
+            const unsigned rec = m_smem ? s_rec[i] : c2[i];
+            if(pos < (unsigned)SEL_SMEM)
+            {
+                s_frec[pos] = rec;
+                s_fkey[pos] = k;
+            }
+            c1[pos] = rec;
             k2v[pos] = k;
         }
     }
@@ -1010,22 +1045,16 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
     }
     // ---- canonical order: rank by (y, x) ----
     SelRec* out = sel + ((long long)b * P.nlevels + l) * P.kp_cap;
-    const bool in_smem = nf <= (unsigned)SEL_RANK_SMEM;
-    if(in_smem)
-    {
-        for(unsigned i = tid; i < nf; i += SEL_THREADS)
-            s_rank[i] = c1[i] >> 8;
-        __syncthreads();
-    }
+    const bool in_smem = nf <= (unsigned)SEL_SMEM;
     for(unsigned i = tid; i < nf; i += SEL_THREADS)
     {
-        const unsigned rec = c1[i], me = rec >> 8;
+        const unsigned rec = in_smem ? s_frec[i] : c1[i], me = rec >> 8;
         unsigned rank = 0;
         if(in_smem)
         {
 #pragma unroll 4
             for(unsigned j = 0; j < nf; ++j)
-                rank += s_rank[j] < me;
+                rank += (s_frec[j] >> 8) < me;
         }
         else
             for(unsigned j = 0; j < nf; ++j)
@@ -1034,7 +1063,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
         {
             SelRec r;
             r.yx_score = rec;
-            r.response = funkey(k2v[i]);
+            r.response = funkey(in_smem ? s_fkey[i] : k2v[i]);
             out[rank] = r;
         }
     }
@@ -1047,13 +1076,15 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const __grid_constant__ 
 //   descriptor byte i.
 // =================================================================================================
 
-constexpr int OD_SLOTS = 32; // keypoints per CTA: 8 warps x 4 rounds
+constexpr int OD_SLOTS = 32; // keypoints per CTA on a full machine: 8 warps x 4 rounds
+constexpr int OD_SLOTS_FEW = 8; // ... when 32 per CTA would leave SMs idle (single frames): one round per warp
 constexpr int IC_WORDS = 31 * 9; // aligned words covering the 31 x 31 orientation patch (any alignment)
 
 // One CTA takes 32 consecutive output slots of one frame.  Phase 0: thread i finds (level, rank) of slot i.  Phase 1: a
 // warp per keypoint computes the intensity-centroid angle.  Phase 2: the 32 double-precision sincos of the CTA run in
 // the 32 lanes of ONE warp (as one warp-per-keypoint step they would cost every warp ~240 issue slots for a single
 // active lane).  Phase 3: a warp per keypoint evaluates the 256 rotated tests, lane i -> descriptor byte i.
+template <int SLOTS>
 __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ PipeParams P, const uint8_t* __restrict__ pyr,
                                                          const uint8_t* __restrict__ blur,
                                                          const LevelCounters* __restrict__ ctr, const SelRec* __restrict__ sel,
@@ -1061,14 +1092,14 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
                                                          mslam_b200_keypoint* __restrict__ out_kp, uint8_t* __restrict__ out_desc,
                                                          int* __restrict__ out_counts, int out_cap)
 {
-    __shared__ int s_l[OD_SLOTS];
-    __shared__ unsigned s_yx[OD_SLOTS];
-    __shared__ float s_resp[OD_SLOTS], s_ang[OD_SLOTS], s_cos[OD_SLOTS], s_sin[OD_SLOTS];
+    __shared__ int s_l[SLOTS];
+    __shared__ unsigned s_yx[SLOTS];
+    __shared__ float s_resp[SLOTS], s_ang[SLOTS], s_cos[SLOTS], s_sin[SLOTS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int b = blockIdx.y + P.frame0;
-    const int slot0 = blockIdx.x * OD_SLOTS;
+    const int slot0 = blockIdx.x * SLOTS;
     // ---- phase 0: slot -> (level, rank) ----
-    if(threadIdx.x < OD_SLOTS)
+    if(threadIdx.x < SLOTS)
     {
         const int slot = slot0 + threadIdx.x;
         int base = 0, l = -1, r = 0;
@@ -1100,7 +1131,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     // v * inside(u, v) for its four columns, tabulated per alignment of the patch -- in two IDP.4A instructions:
     // m10 += sum u * I, m01 += sum v * I.  9 word loads per lane instead of 31 predicated byte loads.
 #pragma unroll 1
-    for(int rnd = 0; rnd < OD_SLOTS / 8; ++rnd)
+    for(int rnd = 0; rnd < SLOTS / 8; ++rnd)
     {
         const int s = rnd * 8 + warp;
         const int l = s_l[s];
@@ -1137,7 +1168,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     }
     __syncthreads();
     // ---- phase 2: (float)cos((double)a), (float)sin((double)a) of OpenCV, one keypoint per lane ----
-    if(warp == 0 && s_l[lane] >= 0)
+    if(warp == 0 && lane < SLOTS && s_l[lane] >= 0)
     {
         const float ang = __fmul_rn(s_ang[lane], (float)(3.1415926535897932384626433832795 / 180.f));
         double sd, cd;
@@ -1148,7 +1179,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     __syncthreads();
     // ---- phase 3: rotated BRIEF, lane i produces descriptor byte i ----
 #pragma unroll 1
-    for(int rnd = 0; rnd < OD_SLOTS / 8; ++rnd)
+    for(int rnd = 0; rnd < SLOTS / 8; ++rnd)
     {
         const int s = rnd * 8 + warp;
         const int l = s_l[s];
@@ -1363,13 +1394,14 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
     ++*launches;
 }
 
-void fast_tiles(int w, int h, int edge, int* tx, int* ty, int* tile_sh)
+void fast_tiles(int w, int h, int edge, bool few_frames, int* tx, int* ty, int* tile_sh)
 {
     const int ox0 = ((edge - 1) & ~3) + 2; // first assigned interior column of tile 0
     const int wi = w - edge - ox0, hi = h - 2 * edge;
     // tall tiles (64 scored rows) halve the per-tile fixed cost and the halo share; short ones waste fewer rows on levels
-    // whose interior is only a few tiles high
-    const int sh = hi > 150 ? 64 : 32;
+    // whose interior is only a few tiles high -- and a context for one or two frames at a time never fills the machine, so its
+    // launches last as long as ONE tile: short tiles everywhere
+    const int sh = (hi > 150 && !few_frames) ? 64 : 32;
     *tile_sh = sh;
     *tx = wi > 0 ? (wi + FS_IW - 1) / FS_IW : 0;
     *ty = hi > 0 ? (hi + (sh - 2) - 1) / (sh - 2) : 0;
@@ -1456,11 +1488,17 @@ void launch_select(cudaStream_t st, const uint8_t* pyr, unsigned* cand, unsigned
 
 void launch_orient_describe(cudaStream_t st, const uint8_t* pyr, const uint8_t* blur, const LevelCounters* ctr,
                             const SelRec* sel, const float4* pat_t, const uint2* ic_w, mslam_b200_keypoint* out_kp,
-                            uint8_t* out_desc, int* out_counts, int out_cap, int n_slots, const PipeParams& P, long long* launches)
+                            uint8_t* out_desc, int* out_counts, int out_cap, int n_slots, const PipeParams& P, int sm_count, long long* launches)
 {
     const int slots = n_slots < 1 ? 1 : n_slots;
-    k_orient_describe<<<dim3((slots + OD_SLOTS - 1) / OD_SLOTS, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, pat_t, ic_w, out_kp,
-                                                                         out_desc, out_counts, out_cap);
+    // 32 keypoints per CTA amortise the per-CTA phases; with few frames that grid is smaller than the machine and the four
+    // rounds of a warp run one after the other on mostly idle SMs, so small batches take 8 per CTA (one round per warp)
+    if((long long)((slots + OD_SLOTS - 1) / OD_SLOTS) * P.n_frames < 2LL * sm_count)
+        k_orient_describe<OD_SLOTS_FEW><<<dim3((slots + OD_SLOTS_FEW - 1) / OD_SLOTS_FEW, P.n_frames), 256, 0, st>>>(
+            P, pyr, blur, ctr, sel, pat_t, ic_w, out_kp, out_desc, out_counts, out_cap);
+    else
+        k_orient_describe<OD_SLOTS><<<dim3((slots + OD_SLOTS - 1) / OD_SLOTS, P.n_frames), 256, 0, st>>>(P, pyr, blur, ctr, sel, pat_t, ic_w,
+                                                                                              out_kp, out_desc, out_counts, out_cap);
     ++*launches;
 }
 

@@ -101,6 +101,20 @@ def test_synthetic_frames_vs_oracle(pkg, oracle, W, H, n):
                     assert c.debug_read(pkg.STAGE_N_FAST, b, l) > 2 * c.level_geometry(W, H)[3][l]
 
 
+@pytest.mark.parametrize("W,H,n", [(1280, 720, 6000), (1920, 1080, 10000)])
+def test_feature_counts_beyond_the_selection_kernels_shared_lists(pkg, oracle, W, H, n):
+    """k_select keeps the survivors of both retainBest cuts in shared memory up to 2048 entries per level and falls back to
+    its global lists beyond: 6000 features put level 0's first cut (2 n_0 + ties) past that, 10000 the final list as well"""
+    frames, _ = pkg.synth.frame_batch(W, H, 1, 0, seed=5 + W)
+    with pkg.Context(max_width=W, max_height=H, max_batch=1, nfeatures=n) as c:
+        n0 = int(c.level_geometry(W, H)[3][0])
+        assert 2 * n0 > 2048 and (n < 10000 or n0 > 2048)
+        kp, desc = c.detect(frames[0])
+        assert c.debug_read(pkg.STAGE_N_CUT1, 0, 0) > 2048
+        okp, odesc = oracle.orb_detect_rgb(frames[0], oracle.default_params(n))
+        _assert_same_keypoints(kp, desc, okp, odesc, f"{W}x{H} / {n} features")
+
+
 def test_batch_equals_single(pkg, ctx):
     frames, _ = pkg.synth.frame_batch(640, 480, 4, 1, seed=5)
     kp, desc, cnt = ctx.detect_batch(frames)
