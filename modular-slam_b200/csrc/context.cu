@@ -32,6 +32,8 @@ struct mslam_b200_ctx
     int geo_w = 0, geo_h = 0;
     PipeParams P;
     FastMaps fast_maps; // tensor maps of k_fast's tile loads for the current geometry
+    PipeParams P_few;   // the same geometry cut into short FAST tiles (calls of one or two frames), and its tensor maps
+    FastMaps fast_maps_few;
     int kp_cap = 0, desc_cap = 0;
 
     // ---- HBM: detector ----
@@ -90,6 +92,12 @@ struct mslam_b200_ctx
     uint8_t *d_one = nullptr, *h_one = nullptr;
     size_t one_bytes = 0, one_kp_off = 0, one_desc_off = 0;
     FrameGraph graph_lat;
+    // ---- single-pair matcher call (mslam_b200_match_knn_ratio / _crosscheck): one staged block in, one block out ----
+    // in:  [n_from, n_to, pad.. (32 B) | from descriptors, packed | to descriptors, packed]   (pinned mirror h_m1)
+    // out: [n_out, pad.. (16 B) | a[desc_cap] | b[desc_cap] | dist[desc_cap]]               (pinned mirror h_mo)
+    uint8_t *d_m1 = nullptr, *h_m1 = nullptr, *d_mo = nullptr, *h_mo = nullptr;
+    size_t m1_bytes = 0, mo_bytes = 0;
+    const int *lat_a = nullptr, *lat_b = nullptr, *lat_d = nullptr; // where the last single-pair call left its results
     // ---- HBM: matcher ----
     uint8_t *d_mfrom = nullptr, *d_mto = nullptr, *d_raw = nullptr;
     int *d_nfrom = nullptr, *d_nto = nullptr;
@@ -281,7 +289,7 @@ struct Geometry
     std::vector<uint4> qtab;
 };
 
-static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int H, Geometry* g)
+static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int H, Geometry* g, bool short_tiles = false)
 {
     PipeParams& P = g->P;
     memset(&P, 0, sizeof(P));
@@ -320,7 +328,7 @@ static void build_geometry(const mslam_b200_config& cfg, int kp_cap, int W, int 
         L.cand_cap = (wi > 0 && hi > 0) ? ((wi + 1) / 2) * ((hi + 1) / 2) : 0;
         L.cand_off = coff;
         coff += (long long)align_up((size_t)L.cand_cap, 4);
-        fast_tiles(L.w, L.h, cfg.edge_threshold, cfg.max_batch <= 2, &L.tiles_x, &L.tiles_y, &L.tile_sh);
+        fast_tiles(L.w, L.h, cfg.edge_threshold, short_tiles, &L.tiles_x, &L.tiles_y, &L.tile_sh);
         L.tile_base = tiles;
         tiles += L.tiles_x * L.tiles_y;
         int bw = 0;
@@ -378,6 +386,12 @@ static int set_geometry(mslam_b200_ctx* ctx, int W, int H)
     }
     MSLAM_CUDA_OK(build_fast_maps(g.P, ctx->d_pyr, ctx->cfg.max_batch, &ctx->fast_maps));
     ctx->P = g.P;
+    {
+        Geometry gs;
+        build_geometry(ctx->cfg, ctx->kp_cap, W, H, &gs, true);
+        MSLAM_CUDA_OK(build_fast_maps(gs.P, ctx->d_pyr, ctx->cfg.max_batch, &ctx->fast_maps_few));
+        ctx->P_few = gs.P;
+    }
     ctx->geo_w = W;
     ctx->geo_h = H;
     return MSLAM_B200_OK;
@@ -464,11 +478,11 @@ void mslam_b200_destroy(mslam_b200_ctx* ctx)
     void* dev[] = {ctx->d_qtab, ctx->d_bgr,  ctx->d_pyr,   ctx->d_blur,  ctx->d_xtab,  ctx->d_ytab,  ctx->d_cand,  ctx->d_cand2,
                    ctx->d_keys, ctx->d_keys2, ctx->d_zero,  ctx->d_sel,   ctx->d_kp,    ctx->d_desc,  ctx->d_counts,
                    ctx->d_mfrom, ctx->d_mto,  ctx->d_raw,   ctx->d_nfrom, ctx->d_nto,   ctx->d_key0,  ctx->d_key1,
-                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb, ctx->d_xdb, ctx->d_xqf, ctx->d_pnp, ctx->d_one};
+                   ctx->d_part0, ctx->d_part1, ctx->d_key0b, ctx->d_key1b, ctx->d_out_a, ctx->d_out_b, ctx->d_out_d, ctx->d_nout, ctx->d_pat, ctx->d_icw, ctx->d_xa, ctx->d_xb, ctx->d_xdb, ctx->d_xqf, ctx->d_pnp, ctx->d_one, ctx->d_m1, ctx->d_mo};
     for(void* p : dev)
         if(p)
             cudaFree(p);
-    void* host[] = {ctx->h_counts, ctx->h_err, ctx->h_out_a, ctx->h_out_b, ctx->h_out_d, ctx->h_nout, ctx->h_n2, ctx->h_pnp, ctx->h_one};
+    void* host[] = {ctx->h_counts, ctx->h_err, ctx->h_out_a, ctx->h_out_b, ctx->h_out_d, ctx->h_nout, ctx->h_n2, ctx->h_pnp, ctx->h_one, ctx->h_m1, ctx->h_mo};
     for(void* p : host)
         if(p)
             cudaFreeHost(p);
@@ -679,6 +693,12 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
     CREATE_OK(cudaHostAlloc(&ctx->h_out_d, B * dc * sizeof(int), cudaHostAllocDefault));
     CREATE_OK(cudaHostAlloc(&ctx->h_nout, B * sizeof(int), cudaHostAllocDefault));
     CREATE_OK(cudaHostAlloc(&ctx->h_n2, 2 * B * sizeof(int), cudaHostAllocDefault));
+    ctx->m1_bytes = 32 + 2 * dc * 32;
+    ctx->mo_bytes = 16 + 3 * dc * sizeof(int);
+    CREATE_OK(cudaMalloc(&ctx->d_m1, ctx->m1_bytes));
+    CREATE_OK(cudaMalloc(&ctx->d_mo, ctx->mo_bytes));
+    CREATE_OK(cudaHostAlloc(&ctx->h_m1, ctx->m1_bytes, cudaHostAllocDefault));
+    CREATE_OK(cudaHostAlloc(&ctx->h_mo, ctx->mo_bytes, cudaHostAllocDefault));
 #undef CREATE_OK
     *out_ctx = ctx;
     return MSLAM_B200_OK;
@@ -816,6 +836,9 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
             // FAST(0) runs under the chain on the blur stream, FAST(1..) is ONE launch behind the chain on the other fork (all
             // its tiles fit the machine at once), the blur is one launch behind FAST(0), select waits for both FAST launches.
             const int nl = P.nlevels;
+            // FAST in short tiles: these launches never fill the machine, so each lasts as long as ONE tile
+            PipeParams Pf = ctx->P_few;
+            Pf.frame0 = P.frame0, Pf.n_frames = P.n_frames;
             {
                 StageTimer t(ctx, MSLAM_B200_T_GRAY);
                 launch_gray(st, d_bgr, ctx->d_pyr, P, &ctx->launches);
@@ -830,7 +853,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
             MSLAM_CUDA_OK(cudaStreamWaitEvent(s_blur, ctx->ev_level[0], 0));
             {
                 StageTimer t(ctx, MSLAM_B200_T_FAST, s_blur);
-                launch_fast(s_blur, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, ctx->fast_maps, 0, 1, &ctx->launches);
+                launch_fast(s_blur, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, Pf, ctx->fast_maps_few, 0, 1, &ctx->launches);
             }
             MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_fast0, s_blur));
             MSLAM_CUDA_OK(cudaStreamWaitEvent(s_blur, ctx->ev_level[nl - 1], 0));
@@ -843,7 +866,7 @@ static int detect_range(mslam_b200_ctx* ctx, const uint8_t* d_bgr, int frame0, i
             if(nl > 1)
             {
                 StageTimer t(ctx, MSLAM_B200_T_FAST, s_fast);
-                launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, P, ctx->fast_maps, 1, nl, &ctx->launches);
+                launch_fast(s_fast, ctx->d_pyr, ctx->d_cand, ctx->d_ctr, ctx->d_hist, Pf, ctx->fast_maps_few, 1, nl, &ctx->launches);
             }
             MSLAM_CUDA_OK(cudaStreamWaitEvent(s_fast, ctx->ev_fast0, 0));
             {
@@ -1618,7 +1641,7 @@ int mslam_b200_match_batch(mslam_b200_ctx* ctx, int mode, const uint8_t* from, c
 static int match_single(mslam_b200_ctx* ctx, int mode, const uint8_t* from, int n_from, int from_stride, const uint8_t* to,
                         int n_to, int to_stride, int* n_found)
 {
-    // results land in ctx->h_out_{a,b,d}; *n_found = count
+    // results land in ctx->lat_{a,b,d}; *n_found = count
     *n_found = 0;
     if(n_from < 0 || n_to < 0 || n_from > ctx->desc_cap || n_to > ctx->desc_cap || from_stride < 32 || to_stride < 32)
         return MSLAM_B200_E_INVALID;
@@ -1628,27 +1651,47 @@ static int match_single(mslam_b200_ctx* ctx, int mode, const uint8_t* from, int 
         return MSLAM_B200_E_INVALID;
     MSLAM_CUDA_OK(cudaSetDevice(ctx->cfg.device));
     cudaStream_t st = ctx->stream;
-    int rc = upload_desc(ctx, from, n_from, from_stride, ctx->d_mfrom);
-    if(rc)
-        return rc;
-    // d_raw is reused by the second upload: stream order makes that safe
-    rc = upload_desc(ctx, to, n_to, to_stride, ctx->d_mto);
-    if(rc)
-        return rc;
-    rc = upload_counts(ctx, n_from, n_to);
-    if(rc)
-        return rc;
+    // The call the frontend makes once per frame (rgbd_feature_frontend.cpp:237).  Both descriptor sets are packed by the host
+    // into ONE pinned block with their counts in front (the caller's arrays are pageable, 64-byte OrbKeypoint records), one
+    // copy takes it in, the kernels run on the packed sets in place, one copy brings count + indices + distances back:
+    // two copies, the kernels and a wait instead of two pageable copies, two pack kernels, two count copies and four
+    // result copies (0.072 -> see tools/latency.py).
+    int* hh = reinterpret_cast<int*>(ctx->h_m1);
+    hh[0] = n_from, hh[1] = n_to;
+    auto pack = [](uint8_t* dst, const uint8_t* src, int n, int stride) {
+        if(stride == 32)
+            memcpy(dst, src, (size_t)n * 32);
+        else
+            for(int i = 0; i < n; ++i)
+                memcpy(dst + (size_t)i * 32, src + (size_t)i * stride, 32);
+    };
+    pack(ctx->h_m1 + 32, from, n_from, from_stride);
+    pack(ctx->h_m1 + 32 + (size_t)n_from * 32, to, n_to, to_stride);
+    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_m1, ctx->h_m1, 32 + (size_t)(n_from + n_to) * 32, cudaMemcpyHostToDevice, st));
+    const int* d_nf = reinterpret_cast<const int*>(ctx->d_m1);
+    const uint8_t* d_from = ctx->d_m1 + 32;
+    const uint8_t* d_to = d_from + (size_t)n_from * 32;
     const int cap = ctx->desc_cap;
-    rc = mslam_b200_match_batch_dev(ctx, mode, ctx->d_mfrom, ctx->d_nfrom, ctx->d_mto, ctx->d_nto, 1, cap, ctx->d_out_a,
-                                    ctx->d_out_b, ctx->d_out_d, ctx->d_nout);
+    int* o_n = reinterpret_cast<int*>(ctx->d_mo);
+    int* o_a = reinterpret_cast<int*>(ctx->d_mo + 16);
+    int rc = mslam_b200_match_batch_dev(ctx, mode, d_from, d_nf, d_to, d_nf + 1, 1, cap, o_a, o_a + cap, o_a + 2 * cap, o_n);
     if(rc)
         return rc;
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_nout, ctx->d_nout, sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_out_a, ctx->d_out_a, (size_t)n_to * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_out_b, ctx->d_out_b, (size_t)n_to * sizeof(int), cudaMemcpyDeviceToHost, st));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_out_d, ctx->d_out_d, (size_t)n_to * sizeof(int), cudaMemcpyDeviceToHost, st));
+    const int* h_n = reinterpret_cast<const int*>(ctx->h_mo);
+    const int* h_a = reinterpret_cast<const int*>(ctx->h_mo + 16);
+    if(ctx->mo_bytes <= (64u << 10))
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_mo, ctx->d_mo, ctx->mo_bytes, cudaMemcpyDeviceToHost, st));
+    else
+    {
+        // a context sized for very large sets: only the n_to entries that can be filled
+        MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_mo, ctx->d_mo, 16, cudaMemcpyDeviceToHost, st));
+        for(int k = 0; k < 3; ++k)
+            MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->h_mo + 16 + (size_t)k * cap * sizeof(int), ctx->d_mo + 16 + (size_t)k * cap * sizeof(int),
+                                          (size_t)n_to * sizeof(int), cudaMemcpyDeviceToHost, st));
+    }
     MSLAM_CUDA_OK(cudaStreamSynchronize(st));
-    *n_found = ctx->h_nout[0];
+    ctx->lat_a = h_a, ctx->lat_b = h_a + cap, ctx->lat_d = h_a + 2 * cap;
+    *n_found = h_n[0];
     return MSLAM_B200_OK;
 }
 
@@ -1666,10 +1709,10 @@ int mslam_b200_match_knn_ratio(mslam_b200_ctx* ctx, const uint8_t* from, int n_f
     const int m = std::min(n, capacity);
     for(int i = 0; i < m; ++i)
     {
-        out_from_idx[i] = (uint64_t)ctx->h_out_a[i];
-        out_to_idx[i] = (uint64_t)ctx->h_out_b[i];
+        out_from_idx[i] = (uint64_t)ctx->lat_a[i];
+        out_to_idx[i] = (uint64_t)ctx->lat_b[i];
         if(out_dist)
-            out_dist[i] = ctx->h_out_d[i];
+            out_dist[i] = ctx->lat_d[i];
     }
     return n > capacity ? MSLAM_B200_E_CAPACITY : MSLAM_B200_OK;
 }
@@ -1689,10 +1732,10 @@ int mslam_b200_match_crosscheck(mslam_b200_ctx* ctx, const uint8_t* query, int n
     const int m = std::min(n, capacity);
     for(int i = 0; i < m; ++i)
     {
-        out_train_idx[i] = ctx->h_out_a[i];
-        out_query_idx[i] = ctx->h_out_b[i];
+        out_train_idx[i] = ctx->lat_a[i];
+        out_query_idx[i] = ctx->lat_b[i];
         if(out_dist)
-            out_dist[i] = ctx->h_out_d[i];
+            out_dist[i] = ctx->lat_d[i];
     }
     return n > capacity ? MSLAM_B200_E_CAPACITY : MSLAM_B200_OK;
 }

@@ -10,7 +10,7 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
                     const uint4* qtab, int sm_count, int l_begin, int l_end, long long* launches);
 void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeParams& P, int l_begin, int l_end,
                  long long* launches);
-void fast_tiles(int w, int h, int edge, bool few_frames, int* tx, int* ty, int* tile_sh);
+void fast_tiles(int w, int h, int edge, bool short_tiles, int* tx, int* ty, int* tile_sh);
 void blur_warps(int w, int h, int* xblocks, int* warps);
 int blur_band_rows();
 // one CUtensorMap (128 opaque bytes) per pyramid level: the FAST kernel's tile loads (k_fast, orb_kernels.cu)

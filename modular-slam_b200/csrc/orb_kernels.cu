@@ -1394,14 +1394,14 @@ void launch_blur(cudaStream_t st, const uint8_t* pyr, uint8_t* blur, const PipeP
     ++*launches;
 }
 
-void fast_tiles(int w, int h, int edge, bool few_frames, int* tx, int* ty, int* tile_sh)
+void fast_tiles(int w, int h, int edge, bool short_tiles, int* tx, int* ty, int* tile_sh)
 {
     const int ox0 = ((edge - 1) & ~3) + 2; // first assigned interior column of tile 0
     const int wi = w - edge - ox0, hi = h - 2 * edge;
     // tall tiles (64 scored rows) halve the per-tile fixed cost and the halo share; short ones waste fewer rows on levels
-    // whose interior is only a few tiles high -- and a context for one or two frames at a time never fills the machine, so its
-    // launches last as long as ONE tile: short tiles everywhere
-    const int sh = (hi > 150 && !few_frames) ? 64 : 32;
+    // whose interior is only a few tiles high -- and are what a call of one or two frames uses everywhere (short_tiles): its
+    // launches never fill the machine, so they last as long as ONE tile
+    const int sh = (hi > 150 && !short_tiles) ? 64 : 32;
     *tile_sh = sh;
     *tx = wi > 0 ? (wi + FS_IW - 1) / FS_IW : 0;
     *ty = hi > 0 ? (hi + (sh - 2) - 1) / (sh - 2) : 0;
