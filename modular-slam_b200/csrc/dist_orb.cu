@@ -1023,6 +1023,11 @@ struct mslam_b200_dist
         long long launches = 0;
     } graph1[2];
     int graphs_enabled = -1;
+    // single-frame latency path (as mslam_b200_detect's, context.cu): result block [count, pad.. (16 B) | counters of the levels
+    // (kMaxLevels) | kp_cap keypoints | kp_cap descriptors] + pinned mirror, filled by one captured graph
+    uint8_t *d_one = nullptr, *h_one = nullptr;
+    size_t one_bytes = 0, one_ctr_off = 0, one_kp_off = 0, one_desc_off = 0;
+    FrameGraph graph_lat;
     int last_frames = 0;
     bool timing = false;
     cudaEvent_t ev[7] = {nullptr};
@@ -1108,6 +1113,12 @@ void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
         cudaFreeHost(ctx->h_counts);
     if(ctx->h_ctr)
         cudaFreeHost(ctx->h_ctr);
+    if(ctx->h_one)
+        cudaFreeHost(ctx->h_one);
+    if(ctx->d_one)
+        cudaFree(ctx->d_one);
+    if(ctx->graph_lat.exec)
+        cudaGraphExecDestroy(ctx->graph_lat.exec);
     for(cudaEvent_t e : ctx->ev)
         if(e)
             cudaEventDestroy(e);
@@ -1224,6 +1235,12 @@ int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist
     CREATE_OK(cudaMalloc(&ctx->d_counts, B * sizeof(int)));
     CREATE_OK(cudaMallocHost(&ctx->h_counts, 2 * B * sizeof(int)));
     CREATE_OK(cudaMallocHost(&ctx->h_ctr, 2 * B * kMaxLevels * sizeof(DistCounters)));
+    ctx->one_ctr_off = 16;
+    ctx->one_kp_off = ctx->one_ctr_off + kMaxLevels * sizeof(DistCounters);
+    ctx->one_desc_off = (ctx->one_kp_off + (size_t)ctx->kp_cap * sizeof(mslam_b200_keypoint) + 31) / 32 * 32;
+    ctx->one_bytes = ctx->one_desc_off + (size_t)ctx->kp_cap * 32;
+    CREATE_OK(cudaMalloc(&ctx->d_one, ctx->one_bytes));
+    CREATE_OK(cudaMallocHost(&ctx->h_one, ctx->one_bytes));
     for(int i = 0; i < 2; ++i)
         CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_slot_done[i], cudaEventDisableTiming));
     CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_out_done, cudaEventDisableTiming));
@@ -1512,6 +1529,8 @@ int mslam_b200_dist_detect_batch_end(mslam_b200_dist* ctx)
     mslam_b200_dist::PendingBatch& pb = ctx->pend[slot];
     pb.active = false;
     DIST_CUDA_OK(cudaEventSynchronize(ctx->ev_slot_done[slot]));
+    if(!ctx->pend[slot ^ 1].active)
+        ctx->out_done_valid = false; // the copy-out stream has drained
     const size_t B = (size_t)ctx->cfg.max_batch;
     const int nl = ctx->P.nlevels;
     int rc = MSLAM_B200_OK;
@@ -1528,12 +1547,116 @@ int mslam_b200_dist_detect_batch_end(mslam_b200_dist* ctx)
     return rc;
 }
 
+// One frame with nothing else in flight (DistributedOrbOpenCvDetector::detect as the Viewer calls it, viewer.cpp:183): copy-in,
+// ONE captured graph (dist_run + the frame's counters and result block to their pinned mirror) and one wait, all on the context
+// stream; the caller's arrays are filled by the host.  Returns kDistGeneralPath when the call has to take the batch machinery
+// (first call of a geometry, graphs off, stage timing on, a pipelined batch in flight).
+constexpr int kDistGeneralPath = 1; // not a status of the C ABI (those are <= 0)
+static int dist_one_latency(mslam_b200_dist* ctx, const uint8_t* bgr, int width, int height, int stride_bytes,
+                            mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
+{
+    if(ctx->graphs_enabled < 0)
+    {
+        const char* e = getenv("MSLAM_B200_GRAPH");
+        ctx->graphs_enabled = e ? atoi(e) != 0 : 1;
+    }
+    static int lat_env = -1; // A/B aid: MSLAM_B200_LATENCY_PATH=0
+    if(lat_env < 0)
+    {
+        const char* e = getenv("MSLAM_B200_LATENCY_PATH");
+        lat_env = e ? atoi(e) != 0 : 1;
+    }
+    if(!lat_env || !ctx->graphs_enabled || ctx->timing || ctx->pend[0].active || ctx->pend[1].active)
+        return kDistGeneralPath;
+    DIST_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    const int rc = dist_set_geometry(ctx, width, height);
+    if(rc)
+        return rc;
+    cudaStream_t st = ctx->stream;
+    auto& g = ctx->graph_lat;
+    if(g.width != width || g.height != height)
+    {
+        if(g.exec)
+            cudaGraphExecDestroy(g.exec);
+        g = mslam_b200_dist::FrameGraph{};
+        g.width = width, g.height = height;
+    }
+    const int nl = ctx->P.nlevels;
+    if(!g.exec)
+    {
+        if(g.uses++ < 1)
+            return kDistGeneralPath; // first call of a geometry: direct launches
+        const long long l0 = ctx->launches;
+        cudaGraph_t graph = nullptr;
+        bool ok = cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+        if(ok)
+        {
+            ok = dist_run(ctx, ctx->d_bgr, 0, 1, reinterpret_cast<mslam_b200_keypoint*>(ctx->d_one + ctx->one_kp_off),
+                          ctx->d_one + ctx->one_desc_off, ctx->kp_cap, reinterpret_cast<int*>(ctx->d_one)) == MSLAM_B200_OK;
+            // the level counters stay where mslam_b200_dist_debug_read looks for them; a copy joins the result block
+            ok = cudaMemcpyAsync(ctx->d_one + ctx->one_ctr_off, ctx->d_ctr, nl * sizeof(DistCounters), cudaMemcpyDeviceToDevice, st) == cudaSuccess && ok;
+            ok = cudaMemcpyAsync(ctx->h_one, ctx->d_one, ctx->one_bytes, cudaMemcpyDeviceToHost, st) == cudaSuccess && ok;
+            ok = (cudaStreamEndCapture(st, &graph) == cudaSuccess) && ok && graph;
+        }
+        if(ok)
+            ok = cudaGraphInstantiate(&g.exec, graph, 0) == cudaSuccess;
+        if(graph)
+            cudaGraphDestroy(graph);
+        g.launches = ctx->launches - l0;
+        ctx->launches = l0; // nothing ran yet
+        if(!ok)
+        {
+            cudaGetLastError();
+            g.exec = nullptr;
+            ctx->graphs_enabled = 0;
+            return kDistGeneralPath;
+        }
+    }
+    if(ctx->out_done_valid)
+    {
+        DIST_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_out_done, 0));
+        ctx->out_done_valid = false;
+    }
+    const size_t row = (size_t)width * 3;
+    if((size_t)stride_bytes == row)
+        DIST_CUDA_OK(cudaMemcpyAsync(ctx->d_bgr, bgr, row * height, cudaMemcpyHostToDevice, st));
+    else
+        DIST_CUDA_OK(cudaMemcpy2DAsync(ctx->d_bgr, row, bgr, (size_t)stride_bytes, row, (size_t)height, cudaMemcpyHostToDevice, st));
+    ctx->P.n_frames = 1, ctx->P.frame0 = 0;
+    ctx->last_frames = 1;
+    DIST_CUDA_OK(cudaGraphLaunch(g.exec, st));
+    ctx->launches += g.launches;
+    DIST_CUDA_OK(cudaStreamSynchronize(st));
+    const int n = *reinterpret_cast<const int*>(ctx->h_one);
+    const DistCounters* hc = reinterpret_cast<const DistCounters*>(ctx->h_one + ctx->one_ctr_off);
+    int status = MSLAM_B200_OK;
+    for(int l = 0; l < nl; ++l)
+        if(hc[l].err)
+            status = MSLAM_B200_E_CAPACITY;
+    if(n > capacity || n > ctx->kp_cap)
+        status = MSLAM_B200_E_CAPACITY;
+    const int m = std::max(0, std::min(std::min(n, capacity), ctx->kp_cap));
+    if(m > 0)
+    {
+        memcpy(out_kp, ctx->h_one + ctx->one_kp_off, (size_t)m * sizeof(mslam_b200_keypoint));
+        memcpy(out_desc, ctx->h_one + ctx->one_desc_off, (size_t)m * 32);
+    }
+    n_out[0] = n;
+    return status;
+}
+
 int mslam_b200_dist_detect_batch(mslam_b200_dist* ctx, const uint8_t* const* frames, int n_frames, int width, int height,
                                  int stride_bytes, mslam_b200_keypoint* out_kp, uint8_t* out_desc, int capacity, int* n_out)
 {
     if(!dist_batch_args_ok(ctx, frames, n_frames, width, stride_bytes, out_kp, out_desc, capacity, n_out) || ctx->pend[0].active ||
        ctx->pend[1].active)
         return MSLAM_B200_E_INVALID;
+    if(n_frames == 1 && width >= 1 && height >= 1)
+    {
+        const int rc1 = dist_one_latency(ctx, frames[0], width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
+        if(rc1 != kDistGeneralPath)
+            return rc1;
+    }
     int rc = mslam_b200_dist_detect_batch_begin(ctx, frames, n_frames, width, height, stride_bytes, out_kp, out_desc, capacity, n_out);
     if(rc)
         return rc;
