@@ -318,16 +318,19 @@ __device__ __forceinline__ bool area_stops(int bx, int by, int ex, int ey, float
 
 // place a keypoint in its initial node (initialize_nodes, :1032-1041): ix = (unsigned)(pt.x / delta_x).  Only one axis
 // ever has more than one initial node; its quotients come from a per-CTA table filled once with the same double
-// division (init_tab[c] = (unsigned)((double)(float)c / delta)), so the walk itself is integer-only.
-__device__ __forceinline__ void walk_init(const DistLevel& L, const uint8_t* __restrict__ init_tab, int x, int y, Walk& w)
+// division (init_tab[c] = (unsigned)((double)(float)c / delta)), and the initial nodes' bounds ((int)(delta * i), double
+// products in the reference) from a second per-CTA table, so the walk itself is integer-only -- it runs once per keypoint and
+// pass, and four FP64 multiplies + conversions per call were a tenth of the kernel's instructions on a pipe B200 barely has.
+__device__ __forceinline__ void walk_init(const DistLevel& L, const uint8_t* __restrict__ init_tab, const int4* __restrict__ init_box,
+                                          int x, int y, Walk& w)
 {
     const int ninit = L.ninit_x * L.ninit_y;
     unsigned ix = L.ninit_x > 1 ? init_tab[x] : 0u, iy = L.ninit_y > 1 ? init_tab[y] : 0u;
     unsigned i0 = ix + iy * (unsigned)L.ninit_x;
     if(i0 >= (unsigned)ninit)
-        i0 = ninit - 1, ix = i0 % L.ninit_x, iy = i0 / L.ninit_x;
-    w.bx = (int)(L.delta_x * ix), w.by = (int)(L.delta_y * iy);
-    w.ex = (int)(L.delta_x * (ix + 1)), w.ey = (int)(L.delta_y * (iy + 1));
+        i0 = ninit - 1;
+    const int4 bx = init_box[i0];
+    w.bx = bx.x, w.by = bx.y, w.ex = bx.z, w.ey = bx.w;
     w.depth = 0, w.key = (int)i0, w.off = 0, w.nslots = ninit;
 }
 
@@ -352,10 +355,10 @@ __device__ __forceinline__ void walk_down(int x, int y, Walk& w)
 
 // walk from the root towards depth `target`; stops early at a node that is final (one keypoint, or small area).
 // Returns true when the walk arrived at `target` through divided nodes only.
-__device__ __forceinline__ bool walk_to(const DistLevel& L, const uint8_t* __restrict__ init_tab, const unsigned* cnt, int x, int y,
-                                        int target, Walk& w)
+__device__ __forceinline__ bool walk_to(const DistLevel& L, const uint8_t* __restrict__ init_tab, const int4* __restrict__ init_box,
+                                        const unsigned* cnt, int x, int y, int target, Walk& w)
 {
-    walk_init(L, init_tab, x, y, w);
+    walk_init(L, init_tab, init_box, x, y, w);
     while(w.depth < target)
     {
         const unsigned c = cnt[w.off + w.key];
@@ -374,6 +377,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
     __shared__ unsigned s_created, s_divided;
     __shared__ unsigned s_warp[32];
     __shared__ uint8_t s_init[4096]; // initial-node index of a coordinate along the axis that has several initial nodes
+    __shared__ int4 s_box[kMaxInit];  // bounds of the initial nodes: (int)(delta_x * ix), (int)(delta_y * iy), ... (ix + 1), ... (iy + 1)
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int l = blockIdx.y, frame = P.frame0 + blockIdx.x; // level-major launch order: the big levels start first
     const DistLevel& L = P.lv[l];
@@ -387,6 +391,11 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
     unsigned* best = cnt + L.tree_slots;
     for(int i = tid; i < 2 * L.tree_slots; i += kTreeThreads)
         cnt[i] = 0;
+    if(tid < L.ninit_x * L.ninit_y)
+    {
+        const unsigned ix = (unsigned)tid % (unsigned)L.ninit_x, iy = (unsigned)tid / (unsigned)L.ninit_x;
+        s_box[tid] = make_int4((int)(L.delta_x * ix), (int)(L.delta_y * iy), (int)(L.delta_x * (ix + 1)), (int)(L.delta_y * (iy + 1)));
+    }
     if(L.ninit_x * L.ninit_y > 1)
     {
         const double delta = L.ninit_x > 1 ? L.delta_x : L.delta_y;
@@ -404,7 +413,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
         const unsigned r = list[k];
         const int x = (r >> 8) & 0xfff, y = r >> 20;
         Walk w;
-        walk_init(L, s_init, x, y, w);
+        walk_init(L, s_init, s_box, x, y, w);
         const unsigned old = atomicAdd(&cnt[w.key], 1u);
         if(old == 0 && area_stops(w.bx, w.by, w.ex, w.ey, s, P.min_size))
             atomicOr(&cnt[w.key], kFlag);
@@ -426,7 +435,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
             const unsigned r = list[k];
             const int x = (r >> 8) & 0xfff, y = r >> 20;
             Walk w;
-            if(!walk_to(L, s_init, cnt, x, y, p, w))
+            if(!walk_to(L, s_init, s_box, cnt, x, y, p, w))
                 continue;
             const unsigned c = cnt[w.off + w.key];
             if((c & ~kFlag) == 1u || (c & kFlag))
@@ -476,7 +485,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_dist_tree(const __grid_constan
         const unsigned r = list[k];
         const int x = (r >> 8) & 0xfff, y = r >> 20;
         Walk w;
-        walk_to(L, s_init, cnt, x, y, t_end, w);
+        walk_to(L, s_init, s_box, cnt, x, y, t_end, w);
         const int cj = (x - 3) >> 6, ci = (y - 3) >> 6;
         const unsigned ord = (unsigned)(ci * L.ncx + cj) << 12 | (unsigned)((y - 3) & 63) << 6 | (unsigned)((x - 3) & 63);
         atomicMax(&best[w.off + w.key], (r & 0xffu) << 24 | (0xffffffu - ord));
