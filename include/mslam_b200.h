@@ -181,6 +181,31 @@ MSLAM_B200_API int mslam_b200_match_batch_dev(mslam_b200_ctx* ctx, int mode, con
                                               const uint8_t* d_to, const int* d_n_to, int n_pairs, int capacity,
                                               int* d_out_a, int* d_out_b, int* d_out_dist, int* d_n_out);
 
+/* ---- matching without any allocation ------------------------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  One (from, to) pair, the knn + ratio
+ * semantics of mslam_b200_match_knn_ratio (query = `to`, train = `from`, k = 2, ties to the lower train index, keep iff
+ * (double)(float)d0 < ratio * (double)(float)d1, ascending toIndex), device in / device out, NO context:
+ *   d_from [n_from][32], d_to [n_to][32]       dense descriptor rows in device memory
+ *   d_out_from / d_out_to / d_out_dist [n_to]  fromIndex, toIndex, Hamming distance of the kept matches (d_out_dist may be NULL)
+ *   d_n_out [1]                                number of matches (0 when n_to < 1 or n_from < 2, as the other entry points)
+ * The kernels' scratch (the packed top-2 keys of every query, the partial lists of the train-set slices, the two counts:
+ * 164 KB) lives in a file-scope __device__ array of the library, which every GPU that loads the library holds until the
+ * process exits; nothing is allocated or freed by this call, ever (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: n_from, n_to <= MSLAM_B200_NOALLOC_MAX_DESC; larger sets are rejected with MSLAM_B200_E_INVALID and a message in
+ * err_msg (optional buffer of err_len bytes, always NUL-terminated when given; also filled for CUDA errors).
+ * `device` is made current; work is enqueued on `cuda_stream` (NULL = the legacy default stream) and the call returns
+ * without waiting.  The first call per device looks up the scratch array's device address (cudaGetSymbolAddress) and the
+ * SM count -- make that first call outside any graph capture.
+ * ALL calls in the process that target one device share the one scratch array: calls whose kernels may overlap on the GPU
+ * (different streams without an ordering between them) race on it; calls on one stream, or ordered by events, are safe.
+ * The array keeps the previous call's contents; every call rewrites the counts and every key it later reads. */
+#define MSLAM_B200_NOALLOC_MAX_DESC 4096
+MSLAM_B200_API int mslam_b200_match_knn_ratio_noalloc_dev(int device, void* cuda_stream, const uint8_t* d_from, int n_from,
+                                                          const uint8_t* d_to, int n_to, double ratio, int* d_out_from,
+                                                          int* d_out_to, int* d_out_dist, int* d_n_out, char* err_msg,
+                                                          size_t err_len);
+
 /* ---- keyframe-database scoring (loop-candidate verification; rgbd_feature_frontend.cpp:499-533 intent) --------- */
 /* score[q][k] = |match(from = query frame q, to = keyframe k)| with the knn+ratio semantics above.
  * Descriptor blocks are device arrays [n][cap][32] with per-frame counts; scores is a device array

@@ -138,6 +138,23 @@ def default_config(**kw):
     return cfg
 
 
+NOALLOC_MAX_DESC = 4096
+
+
+def match_knn_ratio_noalloc_dev(d_from, n_from, d_to, n_to, d_out_from, d_out_to, d_out_dist, d_n_out, ratio=0.7, device=0,
+                                stream=None):
+    """mslam_b200_match_knn_ratio_noalloc_dev: one (from, to) pair, device in / device out, no context and no allocation (the
+    kernels' scratch is a static __device__ array of the library; calls that overlap on one GPU race on it).  Arguments are
+    device addresses or torch tensors; asynchronous on `stream` (a CUDA stream handle; None = the legacy default stream)."""
+    msg = C.create_string_buffer(512)
+    rc = library().mslam_b200_match_knn_ratio_noalloc_dev(C.c_int(device), C.c_void_p(stream or 0), _ptr(d_from), C.c_int(n_from),
+                                                          _ptr(d_to), C.c_int(n_to), C.c_double(ratio), _ptr(d_out_from),
+                                                          _ptr(d_out_to), _ptr(d_out_dist), _ptr(d_n_out), msg,
+                                                          C.c_size_t(len(msg)))
+    if rc != OK:
+        raise MslamB200Error(rc, "match_knn_ratio_noalloc_dev", msg.value.decode(errors="replace"))
+
+
 def pinned_empty(shape, dtype):
     """numpy array backed by pinned host memory from mslam_b200_host_alloc (freed with the array)."""
     dtype = np.dtype(dtype)

@@ -5,6 +5,8 @@
 // -- per query the two smallest distances, ties to the lower train index (cv::batchDistance) -- then the
 // 0.7 ratio test (orb_feature.cpp:101) and {fromIndex = trainIdx, toIndex = queryIdx} in ascending toIndex
 // (orb_feature.cpp:110-114).  Everything here is XOR + POPC on the integer pipes; no tensor cores.
+#include <pthread.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -674,4 +676,121 @@ cudaError_t measure_int_peaks(cudaStream_t st, int sm_count, double* out4 /* 5 v
     return e == cudaSuccess ? cudaGetLastError() : e;
 }
 
+
+// =================================================================================================
+// matching without any allocation (mslam_b200_match_knn_ratio_noalloc_dev, include/mslam_b200.h)
+//   The kNN kernel's scratch -- packed top-2 keys per query, the per-slice partial lists, the two counts -- lives in a
+//   file-scope __device__ array instead of a context's cudaMalloc'ed buffers.  In HOST code the array's name is only a
+//   stand-in for the symbol: its device address comes from cudaGetSymbolAddress, once per device with that device current.
+// =================================================================================================
+constexpr int kNaMax = MSLAM_B200_NOALLOC_MAX_DESC, kNaSlices = 4;
+constexpr int kNaCounts = 64; // words in front: [0] n_from, [1] n_to (256-byte block)
+constexpr int kNaWords = kNaCounts + 2 * kNaMax + 2 * kNaSlices * kNaMax;
+static __device__ __align__(256) unsigned g_noalloc_scratch[kNaWords];
+
+__global__ void k_noalloc_set(unsigned* scratch, int n_from, int n_to, int* n_out)
+{
+    if(threadIdx.x == 0)
+    {
+        scratch[0] = (unsigned)n_from;
+        scratch[1] = (unsigned)n_to;
+        *n_out = 0; // what the reference's matcher leaves for an empty / one-descriptor set; k_ratio_compact overwrites it
+    }
+}
+
+struct NoAllocDevice
+{
+    int state = 0; // 0 not set up, 1 ready, -1 failed
+    unsigned* scratch = nullptr;
+    int sm_count = 0;
+    cudaError_t err = cudaSuccess;
+};
+constexpr int kNaMaxDevices = 64;
+static NoAllocDevice g_na_dev[kNaMaxDevices];
+static pthread_mutex_t g_na_mutex = PTHREAD_MUTEX_INITIALIZER;
+
+// once per device, with that device current
+static cudaError_t noalloc_setup(int device, NoAllocDevice** out)
+{
+    NoAllocDevice& d = g_na_dev[device];
+    pthread_mutex_lock(&g_na_mutex);
+    if(d.state == 0)
+    {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if(e == cudaSuccess)
+            e = cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, device);
+        d.scratch = static_cast<unsigned*>(p);
+        d.err = e;
+        d.state = (e == cudaSuccess && p) ? 1 : -1;
+        if(e == cudaSuccess && !p)
+            d.err = cudaErrorInvalidSymbol;
+    }
+    pthread_mutex_unlock(&g_na_mutex);
+    *out = &d;
+    return d.state == 1 ? cudaSuccess : d.err;
+}
+
 } // namespace mslam_b200
+
+using namespace mslam_b200;
+
+extern "C" int mslam_b200_match_knn_ratio_noalloc_dev(int device, void* cuda_stream, const uint8_t* d_from, int n_from,
+                                                      const uint8_t* d_to, int n_to, double ratio, int* d_out_from, int* d_out_to,
+                                                      int* d_out_dist, int* d_n_out, char* err_msg, size_t err_len)
+{
+    auto fail = [&](int status, const char* fmt, auto... a) {
+        if(err_msg && err_len > 0)
+            snprintf(err_msg, err_len, fmt, a...);
+        return status;
+    };
+    if(err_msg && err_len > 0)
+        err_msg[0] = 0;
+    if(n_from > kNaMax || n_to > kNaMax)
+        return fail(MSLAM_B200_E_INVALID,
+                    "mslam_b200_match_knn_ratio_noalloc_dev: n_from = %d, n_to = %d exceed MSLAM_B200_NOALLOC_MAX_DESC = %d, the "
+                    "size of the library's static scratch (use a context and mslam_b200_match_batch_dev for larger sets)",
+                    n_from, n_to, kNaMax);
+    if(n_from < 0 || n_to < 0 || !d_n_out || !(ratio > 0.0) || device < 0 || device >= kNaMaxDevices ||
+       (n_to > 0 && n_from > 0 && (!d_from || !d_to || !d_out_from || !d_out_to)))
+        return fail(MSLAM_B200_E_INVALID, "mslam_b200_match_knn_ratio_noalloc_dev: bad argument (null pointer, negative count, "
+                                          "ratio <= 0 or device outside 0..%d)", kNaMaxDevices - 1);
+    cudaError_t e = cudaSetDevice(device);
+    NoAllocDevice* dv = nullptr;
+    if(e == cudaSuccess)
+        e = noalloc_setup(device, &dv);
+    if(e != cudaSuccess)
+        return fail(MSLAM_B200_E_CUDA, "mslam_b200_match_knn_ratio_noalloc_dev: set-up on device %d: %s (%s)", device,
+                    cudaGetErrorName(e), cudaGetErrorString(e));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    unsigned* sc = dv->scratch;
+    const int* d_nfrom = reinterpret_cast<const int*>(sc);
+    const int* d_nto = d_nfrom + 1;
+    unsigned *key0 = sc + kNaCounts, *key1 = key0 + kNaMax, *part0 = key1 + kNaMax, *part1 = part0 + kNaSlices * kNaMax;
+    k_noalloc_set<<<1, 32, 0, st>>>(sc, n_from, n_to, d_n_out);
+    if(n_to >= 1 && n_from >= 2) // otherwise: no match (the reference is undefined there, orb_feature.cpp:88-91,101)
+    {
+        // one pair: `cap` is only the bound of the counts and the row stride between pairs, so the larger set's size does;
+        // train set cut into slices until the 64-query CTAs fill the machine (the rule of launch_knn2 for small problems)
+        const int cap = n_to > n_from ? n_to : n_from;
+        const int ctas = (n_to + 63) / 64;
+        int slices = 1;
+        while(slices < kNaSlices && (long long)ctas * slices < 28LL * dv->sm_count && n_from / (slices * 2) >= 128)
+            slices *= 2;
+        dim3 grd(ctas, 1, slices);
+        if(slices == 1)
+            k_knn2<1, 64><<<grd, 64, 0, st>>>(d_to, d_nto, d_from, d_nfrom, cap, key0, key1);
+        else
+        {
+            // slice z writes its partial lists at part + z * cap (gridDim.y = 1): kNaSlices * kNaMax words hold them
+            k_knn2<1, 64><<<grd, 64, 0, st>>>(d_to, d_nto, d_from, d_nfrom, cap, part0, part1);
+            k_merge_keys<<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(part0, part1, slices, (long long)cap, key0, key1);
+        }
+        k_ratio_compact<<<1, 256, 0, st>>>(key0, key1, d_nto, d_nfrom, cap, ratio, d_out_from, d_out_to, d_out_dist, d_n_out);
+    }
+    e = cudaGetLastError();
+    if(e != cudaSuccess)
+        return fail(MSLAM_B200_E_CUDA, "mslam_b200_match_knn_ratio_noalloc_dev: launch: %s (%s)", cudaGetErrorName(e),
+                    cudaGetErrorString(e));
+    return MSLAM_B200_OK;
+}
