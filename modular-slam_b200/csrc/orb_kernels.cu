@@ -482,19 +482,25 @@ __device__ __forceinline__ unsigned or3(unsigned a, unsigned b, unsigned c)
 }
 
 // bit 7 of each byte of the result: does the pixel have 9 contiguous set masks among m[0..15] (cyclic)?
+// Every 9-arc is an even-aligned 8-arc 2j .. 2j+7 plus the position after it (start 2j) or the one before it (start 2j - 1):
+//   e_j = pair (2j, 2j+1), f_j = e_j & e_j+1 (4 from 2j), arc8_j = f_j & f_j+2, any = OR_j arc8_j & (m_2j+8 | m_2j-1)
+// -- 36 LOP3 (8 + 8 + 8 for the neighbours + 8 + 4) against 40 for the "three triples" form it replaces.
 __device__ __forceinline__ unsigned any_run9(const unsigned (&m)[16])
 {
-    unsigned a3[16];
+    unsigned e[8], f[8], c[8];
 #pragma unroll
-    for(int k = 0; k < 16; ++k)
-        a3[k] = and3(m[k], m[(k + 1) & 15], m[(k + 2) & 15]);
-    unsigned a9[16];
+    for(int j = 0; j < 8; ++j)
+        e[j] = m[2 * j] & m[2 * j + 1];
 #pragma unroll
-    for(int k = 0; k < 16; ++k)
-        a9[k] = and3(a3[k], a3[(k + 3) & 15], a3[(k + 6) & 15]);
-    const unsigned o0 = or3(a9[0], a9[1], a9[2]), o1 = or3(a9[3], a9[4], a9[5]), o2 = or3(a9[6], a9[7], a9[8]),
-                   o3 = or3(a9[9], a9[10], a9[11]), o4 = or3(a9[12], a9[13], a9[14]);
-    return or3(or3(o0, o1, o2), or3(o3, o4, a9[15]), 0u);
+    for(int j = 0; j < 8; ++j)
+        f[j] = e[j] & e[(j + 1) & 7];
+#pragma unroll
+    for(int j = 0; j < 8; ++j)
+    {
+        const unsigned nb = m[(2 * j + 8) & 15] | m[(2 * j + 15) & 15];
+        c[j] = and3(f[j], f[(j + 2) & 7], nb);
+    }
+    return or3(or3(c[0], c[1], c[2]), or3(c[3], c[4], c[5]), c[6] | c[7]);
 }
 
 // the 4 pixels starting dx (in -3..3) bytes from the start of word w0, out of the row's three staged words
@@ -626,8 +632,6 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
                      "r"(fast_smem_u32(&s_bar))
                      : "memory");
     }
-    for(int i = tid; i < SH * FS_SW / 16; i += 256)
-        reinterpret_cast<uint4*>(&s_sc[0][0])[i] = make_uint4(0, 0, 0, 0);
     if(tid == 0)
     {
         s_qn = 0;
@@ -642,7 +646,6 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
     {
     const int rb = 32 * pass + 4 * warp; // first scored row of this thread's group
     unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row 4 * warp + row is a corner
-    unsigned bright16 = 0; // ... and its arc is brighter than the centre
     {
         const unsigned t4 = (unsigned)thr * 0x01010101u;
         const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
@@ -677,10 +680,13 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
                 mb[k] = lop3_maj_a_nb_c(R, H, r7 * one + nH7);  // bit 7: R > centre + t
                 md[k] = lop3_maj_a_nb_c(Lo, R, r7 * mone + K);  // bit 7: R < centre - t
             }
-            const unsigned fb = any_run9(mb) & 0x80808080u, f = fb | (any_run9(md) & 0x80808080u);
+            const unsigned fb = any_run9(mb), f = (fb | any_run9(md)) & 0x80808080u;
             // gather the four bit-7 flags into a nibble
             flags16 |= (((f >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
-            bright16 |= (((fb >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
+            // "the arc is brighter than the centre" goes into the score map as 0 / 1 per position -- one word store per row,
+            // which also is the map's initialisation (every position of the tile is classified by exactly one thread);
+            // phase B reads the flag of a corner before it overwrites it with the score (>= fast_thr - 1 > 1)
+            reinterpret_cast<unsigned*>(&s_sc[rb + row][0])[lane] = (fb >> 7) & 0x01010101u;
         }
     }
     // only positions that can matter: inside the image interior +- 1 (the NMS halo):
@@ -707,13 +713,17 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
         if(lane == 31)
             wbase_q = atomicAdd(&s_qn, incl);
         wbase_q = __shfl_sync(0xffffffffu, wbase_q, 31);
-        int pos = wbase_q + incl - cnt;
+        // The loop runs as often as the busiest lane of the warp has corners, so its body is kept to the bone: highest set bit
+        // (one FLO), entry = position of the group | (bit & 3) | (bit >> 2) << 7 -- the group's position has zeros in those four
+        // bits (4 * lane and a row that is a multiple of 4), and bit * 33 puts both fields in place with one IMAD.
+        unsigned short* q = s_q + (wbase_q + incl - cnt);
+        const unsigned ebase = (unsigned)(rb * FS_SW + 4 * lane);
         unsigned f = flags16;
         while(f)
         {
-            const int bit = __ffs(f) - 1;
-            f &= f - 1;
-            s_q[pos++] = (unsigned short)(((rb + (bit >> 2)) * FS_SW + 4 * lane + (bit & 3)) | ((bright16 >> bit & 1u) << 13));
+            const unsigned bit = 31u - (unsigned)__clz(f);
+            f ^= 1u << bit;
+            *q++ = (unsigned short)(ebase | ((bit * 33u) & 0x183u));
         }
     }
     } // passes
@@ -723,16 +733,16 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
     const int nq = s_qn;
     for(int j = 2 * tid; j < nq; j += 512)
     {
-        const unsigned ea = s_q[j], eb = s_q[min(j + 1, nq - 1)];
-        const int ia = ea & 0x1fff, ib = eb & 0x1fff;
+        const int ia = s_q[j], ib = s_q[min(j + 1, nq - 1)];
         const int ya = ia / FS_SW, xa = ia - ya * FS_SW, yb = ib / FS_SW, xb = ib - yb * FS_SW;
-        const unsigned sc = corner_score2(&s_px[ya + 3][xa + 4 + xo], &s_px[yb + 3][xb + 4 + xo], ea & 0x2000u, eb & 0x2000u);
+        const unsigned sc = corner_score2(&s_px[ya + 3][xa + 4 + xo], &s_px[yb + 3][xb + 4 + xo], s_sc[ya][xa], s_sc[yb][xb]);
         s_sc[ya][xa] = (uint8_t)(sc & 0xffu);
         s_sc[yb][xb] = (uint8_t)(sc >> 16);
     }
     __syncthreads();
 
     // ---- phase C: 3x3 strict NMS + border filter over the queue ----
+    const int own_x0 = max(2, edge - sx0), own_x1 = min(FS_SW - 3, L.w - edge - 1 - sx0), own_y1 = min(SH - 2, L.h - edge - 1 - sy0);
     for(int j0 = 0; j0 < nq; j0 += 256)
     {
         const int j = j0 + tid;
@@ -740,10 +750,11 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
         unsigned rec = 0;
         if(j < nq)
         {
-            const int i = s_q[j] & 0x1fff;
+            const int i = s_q[j];
             const int sy = i / FS_SW, sx = i - sy * FS_SW;
             const int x = sx0 + sx, y = sy0 + sy;
-            if(sx >= 2 && sx < FS_SW - 2 && sy >= 1 && sy < SH - 1 && x >= edge && x < L.w - edge && y < L.h - edge)
+            // assigned interior of the tile and of the level's border (sy >= 1 already means y >= edge), as CTA-wide bounds
+            if(sx >= own_x0 && sx <= own_x1 && sy >= 1 && sy <= own_y1)
             {
                 const uint8_t* s = &s_sc[sy][sx];
                 // all eight neighbours are requested before the first comparison (no short-circuit chain of dependent
