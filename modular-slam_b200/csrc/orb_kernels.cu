@@ -363,6 +363,26 @@ __device__ __forceinline__ void blur_row4(const Row12& wd_in, bool left_edge, fl
     }
 }
 
+// column pass + store of one output row: ring slot (k + j) % 7 holds the row pass of source row y - 3 + j
+__device__ __forceinline__ void blur_col_store(const float (&r)[7][4], const int k, uint8_t* __restrict__ dst_px)
+{
+    const float k1 = __int_as_float(0x3e434a39), k2 = __int_as_float(0x3e06387e), k3 = __int_as_float(0x3d8fafb1),
+                kc = __int_as_float(0x3e5d4ae0); // kernel[3 + 1], [3 + 2], [3 + 3], [3]
+    unsigned bits[4];
+#pragma unroll
+    for(int q = 0; q < 4; ++q)
+    {
+        float acc = __fmul_rn(kc, r[(k + 3) % 7][q]);
+        acc = __fmaf_rn(k1, __fadd_rn(r[(k + 4) % 7][q], r[(k + 2) % 7][q]), acc);
+        acc = __fmaf_rn(k2, __fadd_rn(r[(k + 5) % 7][q], r[(k + 1) % 7][q]), acc);
+        acc = __fmaf_rn(k3, __fadd_rn(r[(k + 6) % 7][q], r[k % 7][q]), acc);
+        // 0 <= acc < 256 (weights sum to 1 within rounding): the low byte of acc + 1.5 * 2^23 is rint(acc)
+        bits[q] = __float_as_uint(__fadd_rn(acc, 12582912.f));
+    }
+    const unsigned lo = __byte_perm(bits[0], bits[1], 0x0040), hi = __byte_perm(bits[2], bits[3], 0x0040);
+    *reinterpret_cast<unsigned*>(dst_px) = __byte_perm(lo, hi, 0x5410);
+}
+
 // A lane owns a 4-pixel-wide column strip and walks down a band of BT_H rows: the row pass of each new source row goes
 // into a 7-deep register ring, the column pass reads the ring -- no shared memory, no barriers, every source byte is
 // read once per band (+6 halo rows).  Source rows sit in a 7-slot register buffer that is refilled right after a slot
@@ -373,8 +393,6 @@ __device__ __forceinline__ void blur_row4(const Row12& wd_in, bool left_edge, fl
 __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipeParams P, int l_begin, int l_end,
                                                  const uint8_t* __restrict__ src, uint8_t* __restrict__ dst)
 {
-    const float k1 = __int_as_float(0x3e434a39), k2 = __int_as_float(0x3e06387e), k3 = __int_as_float(0x3d8fafb1),
-                kc = __int_as_float(0x3e5d4ae0); // kernel[3 + 1], [3 + 2], [3 + 3], [3]
     const int lane = threadIdx.x & 31;
     int wg = blockIdx.x * 4 + (threadIdx.x >> 5) + P.lv[l_begin].blur_warp_base;
     int l = l_begin;
@@ -406,6 +424,34 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
         for(int s = 0; s < 6; ++s)
             blur_row4(pre[s], x == 0, r[s]);
     }
+    if(rows % 7 == 0 && y0 + rows + 2 < h) // warp-uniform
+    {
+        // A whole band whose look-ahead rows (up to y0 + rows + 2) stay inside the image -- every band but the last one or two
+        // of a level: no reflection and no row guards in the walk, the source / destination addresses advance by one pitch
+        // per row, blocks of seven rows without a branch (the last block fetches nothing).  The general walk below spends a
+        // fifth of its instructions on those guards and on 64-bit row addresses.
+        const unsigned* ldw = reinterpret_cast<const unsigned*>(img + (long long)(y0 + 10) * pitch + x);
+        const unsigned* lda = ldw - (x > 0);
+        uint8_t* stp = out + (long long)y0 * pitch + x;
+        const int pw = pitch >> 2;
+        for(int i0 = 0; i0 < rows; i0 += 7)
+        {
+            const bool fetch = i0 + 7 < rows;
+#pragma unroll
+            for(int k = 0; k < 7; ++k)
+            {
+                blur_row4(buf[k], x == 0, r[(k + 6) % 7]);
+                if(fetch)
+                {
+                    buf[k].b = __ldg(ldw), buf[k].c = __ldg(ldw + 1), buf[k].a = __ldg(lda);
+                    ldw += pw, lda += pw;
+                }
+                blur_col_store(r, k, stp);
+                stp += pitch;
+            }
+        }
+        return;
+    }
     for(int i0 = 0; i0 < rows; i0 += 7)
     {
 #pragma unroll
@@ -414,23 +460,10 @@ __global__ void __launch_bounds__(128, 6) k_blur(const __grid_constant__ PipePar
             const int i = i0 + k;
             if(i < rows)
             {
-                // ring slot (k + j) % 7 holds source row y - 3 + j of output row y = y0 + i
                 blur_row4(buf[k], x == 0, r[(k + 6) % 7]);
                 if(i + 7 < rows)
                     buf[k] = blur_load(img + (long long)reflect101(y0 + 3 + i + 7, h) * pitch, x);
-                unsigned bits[4];
-#pragma unroll
-                for(int q = 0; q < 4; ++q)
-                {
-                    float acc = __fmul_rn(kc, r[(k + 3) % 7][q]);
-                    acc = __fmaf_rn(k1, __fadd_rn(r[(k + 4) % 7][q], r[(k + 2) % 7][q]), acc);
-                    acc = __fmaf_rn(k2, __fadd_rn(r[(k + 5) % 7][q], r[(k + 1) % 7][q]), acc);
-                    acc = __fmaf_rn(k3, __fadd_rn(r[(k + 6) % 7][q], r[k % 7][q]), acc);
-                    // 0 <= acc < 256 (weights sum to 1 within rounding): the low byte of acc + 1.5 * 2^23 is rint(acc)
-                    bits[q] = __float_as_uint(__fadd_rn(acc, 12582912.f));
-                }
-                const unsigned lo = __byte_perm(bits[0], bits[1], 0x0040), hi = __byte_perm(bits[2], bits[3], 0x0040);
-                *reinterpret_cast<unsigned*>(out + (long long)(y0 + i) * pitch + x) = __byte_perm(lo, hi, 0x5410);
+                blur_col_store(r, k, out + (long long)(y0 + i) * pitch + x);
             }
         }
     }
@@ -721,7 +754,8 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
         unsigned f = flags16;
         while(f)
         {
-            const unsigned bit = 31u - (unsigned)__clz(f);
+            unsigned bit; // index of the highest set bit: one FLO (31 - __clz(f) compiles to three instructions)
+            asm("bfind.u32 %0, %1;" : "=r"(bit) : "r"(f));
             f ^= 1u << bit;
             *q++ = (unsigned short)(ebase | ((bit * 33u) & 0x183u));
         }
@@ -1378,9 +1412,9 @@ int blur_band_rows()
     if(band == 0)
     {
         const char* e = getenv("MSLAM_BLUR_BAND");
-        band = e ? atoi(e) : 32;
+        band = e ? atoi(e) : 35; // a multiple of 7: whole bands take k_blur's guard-free walk
         if(band < 7)
-            band = 32;
+            band = 35;
     }
     return band;
 }
