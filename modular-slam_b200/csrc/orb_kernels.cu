@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(128) k_resize_quads(const uint8_t* __restrict_
 // batch run side by side.  (One CTA per frame -- 64 busy SMs of 148 -- was measured slower than the four launches it replaced.)
 constexpr int RT_THREADS = 512, RT_BAND = 4, RT_CLUSTER = 4;
 __global__ void __cluster_dims__(RT_CLUSTER, 1, 1) __launch_bounds__(RT_THREADS, 2)
-    k_resize_tail(const __grid_constant__ PipeParams P, int l_begin, int rt_band, uint8_t* __restrict__ pyr,
+    k_resize_tail(const __grid_constant__ PipeParams P, int l_begin, int rt_band, int rt_adapt, uint8_t* __restrict__ pyr,
                   const uint4* __restrict__ qtab, const short2* __restrict__ ytab)
 {
     const int lane = threadIdx.x & 31;
@@ -267,15 +267,27 @@ __global__ void __cluster_dims__(RT_CLUSTER, 1, 1) __launch_bounds__(RT_THREADS,
         const LevelDesc &S = P.lv[l - 1], &D = P.lv[l];
         const uint8_t* simg = pyr + S.img_off + (long long)b * S.img_frame_stride;
         uint8_t* dimg = pyr + D.img_off + (long long)b * D.img_frame_stride;
-        const int xblocks = (D.rs_quads + 31) / 32, bands = (D.h + rt_band - 1) / rt_band;
+        // Band height per level: a warp's walk is a chain (row after row), so a level costs (rounds of tasks) x (rows per band).
+        // The shortest band that gives every warp of the cluster at most ONE task wastes the least of that product (VGA levels
+        // 2..7 with 64 warps: 21, 14, 11, 10, 6, 5 rows = 67 per warp against 80 with four-row bands in 6, 4, 3, 3, 2, 2 rounds);
+        // rt_band remains the fallback for a level too large for one round of bands of at most 32 rows.
+        const int xblocks = (D.rs_quads + 31) / 32;
+        int bh = rt_band;
+        if(rt_adapt && xblocks <= n_workers)
+        {
+            const int one_round = (D.h + n_workers / xblocks - 1) / (n_workers / xblocks);
+            if(one_round <= 32)
+                bh = max(one_round, 2);
+        }
+        const int bands = (D.h + bh - 1) / bh;
         for(int task = worker; task < xblocks * bands; task += n_workers)
         {
             const int band = task / xblocks, xb = task - band * xblocks;
             if(l == l_begin)
-                resize_band<true>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * rt_band, rt_band, qtab + D.qtab_off,
+                resize_band<true>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * bh, bh, qtab + D.qtab_off,
                                   ytab + D.ytab_off, lane);
             else
-                resize_band<false>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * rt_band, rt_band, qtab + D.qtab_off,
+                resize_band<false>(simg, S.pitch, S.h, dimg, D.pitch, D.h, D.rs_quads, xb, band * bh, bh, qtab + D.qtab_off,
                                    ytab + D.ytab_off, lane);
         }
         if(l + 1 < P.nlevels)
@@ -1401,7 +1413,13 @@ void launch_pyramid(cudaStream_t st, uint8_t* pyr, const PipeParams& P, const sh
             if(rt_band < 1 || rt_band > 32)
                 rt_band = RT_BAND;
         }
-        k_resize_tail<<<P.n_frames * RT_CLUSTER, RT_THREADS, 0, st>>>(P, l_tail, rt_band, pyr, qtab, ytab);
+        static int rt_adapt = -1;
+        if(rt_adapt < 0)
+        {
+            const char* e = getenv("MSLAM_RESIZE_TAIL_ADAPT"); // A/B aid: 0 = the fixed band height everywhere
+            rt_adapt = e ? atoi(e) : 1;
+        }
+        k_resize_tail<<<P.n_frames * RT_CLUSTER, RT_THREADS, 0, st>>>(P, l_tail, rt_band, rt_adapt, pyr, qtab, ytab);
         ++*launches;
     }
 }
