@@ -1187,6 +1187,15 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     // words i, i + 32, ...); every word meets two packed signed-byte weight words -- u * inside(u, v) and
     // v * inside(u, v) for its four columns, tabulated per alignment of the patch -- in two IDP.4A instructions:
     // m10 += sum u * I, m01 += sum v * I.  9 word loads per lane instead of 31 predicated byte loads.
+    // (row, byte offset of the word) of this lane's nine patch words do not depend on the keypoint: once per CTA
+    unsigned ic_row[(IC_WORDS + 31) / 32], ic_col[(IC_WORDS + 31) / 32];
+#pragma unroll
+    for(int it = 0; it < (IC_WORDS + 31) / 32; ++it)
+    {
+        const unsigned i = min(lane + 32 * it, IC_WORDS - 1);
+        ic_row[it] = i / 9u;
+        ic_col[it] = 4u * (i - 9u * ic_row[it]);
+    }
 #pragma unroll 1
     for(int rnd = 0; rnd < SLOTS / 8; ++rnd)
     {
@@ -1196,8 +1205,9 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
             continue;
         const LevelDesc& L = P.lv[l];
         const int x = (s_yx[s] >> 8) & 0xfff, y = s_yx[s] >> 20;
-        const int pitch = L.pitch;
+        const unsigned pitch = (unsigned)L.pitch;
         const int al = (x - 15) & 3;
+        // keypoints keep 31 pixels from the level's border: the patch origin is inside the plane, every offset is unsigned
         const uint8_t* base = pyr + L.img_off + (long long)b * L.img_frame_stride + (long long)(y - 15) * pitch + ((x - 15) & ~3);
         const uint2* wtab = ic_w + al * IC_WORDS;
         int m10 = 0, m01 = 0;
@@ -1207,8 +1217,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
             const int i = lane + 32 * it;
             if(i < IC_WORDS)
             {
-                const int r = i / 9, k = i - 9 * r;
-                const unsigned word = __ldg(reinterpret_cast<const unsigned*>(base + r * pitch) + k);
+                const unsigned word = __ldg(reinterpret_cast<const unsigned*>(base + (ic_row[it] * pitch + ic_col[it])));
                 const uint2 wgt = __ldg(wtab + i);
                 asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(word), "r"(wgt.x));
                 asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m01) : "r"(word), "r"(wgt.y));
