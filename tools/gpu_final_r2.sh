@@ -1,6 +1,7 @@
 #!/bin/bash
 # end-of-round evidence: GPU tests, bench lines of every workload WITH their CPU baselines, reference arm, launch list, DRAM traffic
 mkdir -p gpurun_out
+timeout 200 python -c 'import __graft_entry__ as g; g.smoke()' 2>&1 | tail -1
 timeout 400 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 > gpurun_out/f_pytest.log; tail -2 gpurun_out/f_pytest.log
 timeout 400 python bench.py --steps 20 --warmup 3 > gpurun_out/f_c2.json 2> gpurun_out/f_c2.err; tail -1 gpurun_out/f_c2.err
 timeout 300 python bench.py --impl reference --steps 20 --warmup 3 > gpurun_out/f_ref.json 2> gpurun_out/f_ref.err
