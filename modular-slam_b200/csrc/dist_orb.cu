@@ -10,10 +10,10 @@
 // How it is mapped to the GPU (one launch per stage covers every frame of the batch and every level):
 //   k_dist_resize   level l-1 -> l, 11-bit fixed-point bilinear taps from per-level tables (tables built on the host in
 //                   IEEE double / float exactly as OpenCV builds them); 4 output pixels per thread
-//   k_dist_fast     one CTA per (frame, level, cell): the cell's 70x70 tile in shared memory, a queue of the pixels that
-//                   pass the 4-compass-point test, exact cornerScore of the queued pixels in one packed-s16x2 min/max
-//                   network (both polarities at once), strict 3x3 NMS inside the cell, threshold fallback, one atomic
-//                   per cell to append the survivors to the (frame, level) list
+//   k_dist_fast     one CTA per (frame, level, cell): the cell's 70x70 tile in shared memory, the exact FAST-9 classification
+//                   of the 64x64 cell in byte-SIMD (fast_simd.cuh, shared with k_fast), a queue of the corners, their exact
+//                   cornerScore two at a time in one packed u16x2 min/max network, strict 3x3 NMS inside the cell, threshold
+//                   fallback, one atomic per cell to append the survivors to the (frame, level) list
 //   k_dist_tree     one CTA per (frame, level).  The reference's std::list surgery is replaced by an order-key
 //                   formulation: every keypoint's path through the tree is a pure function of the node geometry, a
 //                   pass of the reference divides exactly the divisible nodes of one depth, and the final list order
@@ -37,6 +37,7 @@
 #include <vector>
 
 #include "kernels.h"
+#include "fast_simd.cuh"
 
 using namespace mslam_b200;
 
@@ -74,6 +75,7 @@ struct DistParams
 {
     int nlevels, n_frames, W, H;
     int ini_thr, min_thr;
+    int one, minus_one;       // +1 / -1 the compiler cannot see: byte-lane additions of k_dist_fast as IMADs on the FMA pipe
     unsigned min_size;
     int kp_cap;               // per-frame keypoint capacity of the handle
     int total_cells, total_gtiles;
@@ -156,44 +158,6 @@ __device__ __forceinline__ int level_of_gtile(const DistParams& P, int idx)
     return l;
 }
 
-// Both polarities of a ring difference ride in the two 16-bit halves of one register, biased by +256 so that they stay
-// positive: lo = (v - p) + 256, hi = (p - v) + 256.  Because lo + hi * 65536 = [v' + (512 - v') * 65536] + p * 0xFFFF with
-// v' = v + 256, one IMAD per ring pixel builds the pair from a per-pixel base.
-__device__ __forceinline__ unsigned pair_base(int v) { return (unsigned)(v + 256) + ((unsigned)(256 - v) << 16); }
-__device__ __forceinline__ unsigned pair_of(unsigned base, unsigned p) { return base + p * 0xFFFFu; }
-
-// exact cornerScore<16> of a pixel known to sit >= 3 px inside the tile: max over the 16 arcs of 9 contiguous ring
-// pixels of min(v - p) and of min(p - v), minus one (the caller subtracts it).
-__device__ __forceinline__ int corner_best(const uint8_t* __restrict__ c)
-{
-    const unsigned base = pair_base(c[0]);
-    unsigned e[25];
-    const int off[16] = {3 * FT_PITCH,      3 * FT_PITCH + 1,  2 * FT_PITCH + 2,  FT_PITCH + 3,  3,  -FT_PITCH + 3,
-                         -2 * FT_PITCH + 2, -3 * FT_PITCH + 1, -3 * FT_PITCH,     -3 * FT_PITCH - 1, -2 * FT_PITCH - 2,
-                         -FT_PITCH - 3,     -3,                FT_PITCH - 3,      2 * FT_PITCH - 2,  3 * FT_PITCH - 1};
-#pragma unroll
-    for(int k = 0; k < 16; ++k)
-        e[k] = pair_of(base, c[off[k]]);
-#pragma unroll
-    for(int k = 16; k < 25; ++k)
-        e[k] = e[k - 16];
-    unsigned m2[24], m4[22], best = 0; // biased values are >= 1
-#pragma unroll
-    for(int k = 0; k < 24; ++k)
-        m2[k] = __vminu2(e[k], e[k + 1]);
-#pragma unroll
-    for(int k = 0; k < 22; ++k)
-        m4[k] = __vminu2(m2[k], m2[k + 2]);
-#pragma unroll
-    for(int k = 0; k < 16; ++k)
-    {
-        const unsigned m8 = __vminu2(m4[k], m4[k + 4]);
-        best = __vmaxu2(best, __vminu2(m8, e[k + 8]));
-    }
-    const int lo = (int)(best & 0xffff), hi = (int)(best >> 16);
-    return (lo > hi ? lo : hi) - 256;
-}
-
 __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
                                                    unsigned* __restrict__ cand, DistCounters* __restrict__ ctr)
 {
@@ -214,12 +178,16 @@ __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistP
     // the tile starts at column x0 - 3 = 19 + 64 cj; rows are fetched as aligned words from column 16 + 64 cj, so the
     // tile's column 0 sits at byte 3 of a shared-memory row (T below)
     const uint8_t* img = pyr + L.img_off + frame * L.img_frame_stride + (long long)(y0 - 3) * L.pitch + (x0 - 6);
+    // ... and is stored shifted down by two bytes, which puts cell pixel lx at byte lx + 4 of a tile row: the four centres of
+    // a byte-SIMD group are one aligned word (T below points at pixel (-3, -3) of the cell, byte 1 of the tile)
     const int th = ch + 6, nwords = (cw + 12) >> 2;
     for(int r = tid >> 5; r < th; r += 8)
         if(lane < nwords)
-            reinterpret_cast<unsigned*>(tile + r * FT_PITCH)[lane] =
-                __ldg(reinterpret_cast<const unsigned*>(img + (long long)r * L.pitch) + lane);
-    const uint8_t* T = tile + 3;
+        {
+            const unsigned* g = reinterpret_cast<const unsigned*>(img + (long long)r * L.pitch) + lane;
+            reinterpret_cast<unsigned*>(tile + r * FT_PITCH)[lane] = __funnelshift_r(__ldg(g), __ldg(g + 1), 16);
+        }
+    const uint8_t* T = tile + 1;
     int thr = P.ini_thr;
     int ns = 0;
     for(int attempt = 0; attempt < 2; ++attempt)
@@ -229,50 +197,95 @@ __global__ void __launch_bounds__(256) k_dist_fast(const __grid_constant__ DistP
         if(tid == 0)
             s_nq = 0, s_ns = 0;
         __syncthreads();
-        // phase A: the 4-compass-point test (a 9-arc of the 16-ring always holds two of ring pixels 0, 4, 8, 12)
-#pragma unroll 4
-        for(int i = 0; i < 16; ++i)
+        // phase A: exact FAST-9 classification, byte-SIMD (fast_simd.cuh, as k_fast): a thread owns 4 adjacent centres x 4 rows
+        // -- 16 word columns x 16 row groups = the 256 threads of the CTA cover the 64 x 64 cell in one pass.  Only the corners
+        // go to the queue (the earlier compass pre-test let 55 % of the bench's pixels through to the 94-operation exact
+        // score; a fifth of them are corners).
         {
-            const int ly = (tid >> 6) + 4 * i, lx = tid & 63;
-            bool pass = false;
-            if(lx < cw && ly < ch)
+            const int wcol = tid & 15, rb = (tid >> 4) * 4; // cell columns 4 * wcol .. + 3, rows rb .. rb + 3
+            unsigned flags16 = 0, bright16 = 0;
+            const unsigned t4 = (unsigned)thr * 0x01010101u;
+            const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
+            const unsigned* wbase = reinterpret_cast<const unsigned*>(tile + rb * FT_PITCH) + wcol;
+            unsigned wm[10], w0[10], wp[10]; // tile rows rb .. rb + 9, words wcol, wcol + 1 (the centres), wcol + 2
+#pragma unroll
+            for(int r = 0; r < 10; ++r)
             {
-                const uint8_t* p = T + (ly + 3) * FT_PITCH + lx + 3;
-                const unsigned base = pair_base(p[0]);
-                const unsigned a = pair_of(base, p[3 * FT_PITCH]), b = pair_of(base, p[-3 * FT_PITCH]);
-                const unsigned c4 = pair_of(base, p[3]), d12 = pair_of(base, p[-3]);
-                // second largest of the four, per polarity: two of the four compass differences exceed thr
-                const unsigned second = __vmaxu2(__vmaxu2(__vminu2(a, b), __vminu2(c4, d12)),
-                                                 __vminu2(__vmaxu2(a, b), __vmaxu2(c4, d12)));
-                const unsigned lim = (unsigned)(thr + 256);
-                pass = (second & 0xffffu) > lim || (second >> 16) > lim;
+                wm[r] = wbase[r * (FT_PITCH / 4)];
+                w0[r] = wbase[r * (FT_PITCH / 4) + 1];
+                wp[r] = wbase[r * (FT_PITCH / 4) + 2];
             }
-            const unsigned m = __ballot_sync(0xffffffffu, pass);
-            if(m)
+#pragma unroll
+            for(int row = 0; row < 4; ++row)
             {
-                int base = 0;
-                if(lane == 0)
-                    base = atomicAdd(&s_nq, __popc(m));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if(pass)
-                    q[base + __popc(m & ((1u << lane) - 1))] = (unsigned short)(ly << 8 | lx);
+                const unsigned C = w0[row + 3];
+                const unsigned H = __vaddus4(C, t4), Lo = __vsubus4(C, t4);
+                const unsigned nH7 = ~H & 0x7f7f7f7fu;
+                const unsigned K = (Lo & 0x7f7f7f7fu) + 0x7f7f7f7fu;
+                unsigned mb[16], md[16];
+                constexpr int DX[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
+                constexpr int DY[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+#pragma unroll
+                for(int k = 0; k < 16; ++k)
+                {
+                    const int r = row + 3 + DY[k];
+                    const unsigned R = ring4(wm[r], w0[r], wp[r], DX[k]);
+                    const unsigned r7 = R & 0x7f7f7f7fu;
+                    mb[k] = lop3_maj_a_nb_c(R, H, r7 * one + nH7); // bit 7: R > centre + thr
+                    md[k] = lop3_maj_a_nb_c(Lo, R, r7 * mone + K); // bit 7: R < centre - thr
+                }
+                const unsigned fb = any_run9(mb) & 0x80808080u, f = fb | (any_run9(md) & 0x80808080u);
+                flags16 |= (((f >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
+                bright16 |= (((fb >> 7) * 0x00204081u) >> 21 & 0xfu) << (4 * row);
+            }
+            // positions inside the cell only (cells at the right / bottom edge are narrower)
+            {
+                const int nx = min(4, max(0, cw - 4 * wcol)), ny = min(4, max(0, ch - rb));
+                flags16 &= (((1u << nx) - 1u) * 0x1111u) & ((1u << (4 * ny)) - 1u);
+            }
+            const int cnt = __popc(flags16);
+            int incl = cnt;
+#pragma unroll
+            for(int o = 1; o < 32; o <<= 1)
+            {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if(lane >= o)
+                    incl += t;
+            }
+            int wq = 0;
+            if(lane == 31)
+                wq = atomicAdd(&s_nq, incl);
+            wq = __shfl_sync(0xffffffffu, wq, 31);
+            unsigned short* qp = q + (wq + incl - cnt);
+            const unsigned ebase = (unsigned)(rb << 8 | 4 * wcol);
+            const unsigned b2 = bright16 << 15;
+            unsigned f = flags16;
+            while(f)
+            {
+                unsigned bit;
+                asm("bfind.u32 %0, %1;" : "=r"(bit) : "r"(f));
+                f ^= 1u << bit;
+                // entry: row (rb + bit / 4) << 8 | column 4 * wcol + bit % 4 | bright << 15
+                *qp++ = (unsigned short)(ebase + ((bit * 65u) & 0x303u) + ((b2 >> bit) & 0x8000u));
             }
         }
         __syncthreads();
-        // phase B: exact score of the queued pixels
+        // phase B: exact score of the queued corners, two per thread in the lanes of one packed min / max network
         const int nq = s_nq;
-        for(int i = tid; i < nq; i += 256)
+        for(int i = 2 * tid; i < nq; i += 512)
         {
-            const int ly = q[i] >> 8, lx = q[i] & 255;
-            const int best = corner_best(T + (ly + 3) * FT_PITCH + lx + 3);
-            if(best > thr)
-                sc[(ly + 1) * FS_PITCH + lx + 1] = (uint8_t)(best - 1);
+            const unsigned ea = q[i], eb = q[min(i + 1, nq - 1)];
+            const int ya = (ea >> 8) & 127, xa = ea & 255, yb = (eb >> 8) & 127, xb = eb & 255;
+            const unsigned scs = corner_score2<FT_PITCH>(T + (ya + 3) * FT_PITCH + xa + 3, T + (yb + 3) * FT_PITCH + xb + 3, ea & 0x8000u,
+                                                        eb & 0x8000u);
+            sc[(ya + 1) * FS_PITCH + xa + 1] = (uint8_t)(scs & 0xffu);
+            sc[(yb + 1) * FS_PITCH + xb + 1] = (uint8_t)(scs >> 16);
         }
         __syncthreads();
         // phase C: strict 3x3 non-max suppression inside the cell
         for(int i = tid; i < nq; i += 256)
         {
-            const int ly = q[i] >> 8, lx = q[i] & 255;
+            const int ly = (q[i] >> 8) & 127, lx = q[i] & 255;
             const uint8_t* s = sc + (ly + 1) * FS_PITCH + lx + 1;
             const int v = s[0];
             if(v && v > s[-1] && v > s[1] && v > s[-FS_PITCH - 1] && v > s[-FS_PITCH] && v > s[-FS_PITCH + 1] &&
@@ -855,6 +868,7 @@ void build_dist_geometry(const mslam_b200_dist_config& cfg, int W, int H, DistGe
     P.nlevels = cfg.nlevels;
     P.W = W, P.H = H;
     P.ini_thr = cfg.ini_fast_threshold;
+    P.one = 1, P.minus_one = -1;
     P.min_thr = cfg.min_fast_threshold;
     P.min_size = (unsigned)cfg.min_size;
     size_t off = 0, tree_smem = 0;
