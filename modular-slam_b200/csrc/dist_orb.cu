@@ -64,6 +64,7 @@ struct DistLevel
     int tree_slots;           // sum over depths 0..depth of ninit * 4^d
     int tree_in_smem;
     int xtab_off, ytab_off;
+    int qtab_off, nquads;     // k_dist_resize_quads' table (uint4 pairs); nquads = 0: the level uses k_dist_resize
     long long img_off, img_frame_stride;
     long long cand_off;       // elements, within one frame's candidate block
     long long tree_off;       // words, within one frame's global tree scratch (levels that do not fit in smem)
@@ -135,6 +136,48 @@ __global__ void __launch_bounds__(256) k_dist_resize(const uint8_t* __restrict__
         out |= (o & 0xff) << (8 * i);
     }
     *reinterpret_cast<unsigned*>(dst + blockIdx.z * dfs + (long long)y * dpitch + x4) = out; // pitch covers the tail
+}
+
+// The same arithmetic, four output pixels per lane from one table entry: entry q of a level covers columns 4q .. 4q + 3 --
+// {first source byte of an 8-byte window, PRMT selectors that pull (left, right) taps of pixels 0, 1 and of pixels 2, 3 out of
+// the window | the four (a0 | a1 << 16) weight pairs}.  Per source row 3 aligned word loads, 2 funnel shifts, 2 PRMT and
+// 4 IDP.2A (both taps of a pixel in one instruction) instead of four table loads, eight byte loads and eight IMADs; used
+// for every level whose quads fit the window (scale factors up to 2), k_dist_resize above stays as the fallback.
+__global__ void __launch_bounds__(256) k_dist_resize_quads(const uint8_t* __restrict__ src, int spitch, long long sfs,
+                                                           uint8_t* __restrict__ dst, int dpitch, long long dfs, int nquads, int dh,
+                                                           const uint4* __restrict__ qt, const YTap* __restrict__ yt)
+{
+    const int q = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int y = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if(q >= nquads || y >= dh)
+        return;
+    const uint4 e0 = __ldg(qt + 2 * q), wts = __ldg(qt + 2 * q + 1);
+    const YTap Y = yt[y];
+    const int wi = (int)(e0.x >> 2), sh = (int)(e0.x & 3u) * 8;
+    const unsigned selA = e0.y & 0xffffu, selB = e0.y >> 16;
+    const unsigned* s0 = reinterpret_cast<const unsigned*>(src + blockIdx.z * sfs + (long long)Y.sy0 * spitch) + wi;
+    const unsigned* s1 = reinterpret_cast<const unsigned*>(src + blockIdx.z * sfs + (long long)Y.sy1 * spitch) + wi;
+    const unsigned a0 = __ldg(s0), a1 = __ldg(s0 + 1), a2 = __ldg(s0 + 2), c0 = __ldg(s1), c1 = __ldg(s1 + 1), c2 = __ldg(s1 + 2);
+    unsigned r0[4], r1[4];
+    {
+        const unsigned S0 = __funnelshift_r(a0, a1, sh), S1 = __funnelshift_r(a1, a2, sh);
+        const unsigned pA = __byte_perm(S0, S1, selA), pB = __byte_perm(S0, S1, selB);
+        r0[0] = __dp2a_lo(wts.x, pA, 0u), r0[1] = __dp2a_hi(wts.y, pA, 0u), r0[2] = __dp2a_lo(wts.z, pB, 0u), r0[3] = __dp2a_hi(wts.w, pB, 0u);
+    }
+    {
+        const unsigned S0 = __funnelshift_r(c0, c1, sh), S1 = __funnelshift_r(c1, c2, sh);
+        const unsigned pA = __byte_perm(S0, S1, selA), pB = __byte_perm(S0, S1, selB);
+        r1[0] = __dp2a_lo(wts.x, pA, 0u), r1[1] = __dp2a_hi(wts.y, pA, 0u), r1[2] = __dp2a_lo(wts.z, pB, 0u), r1[3] = __dp2a_hi(wts.w, pB, 0u);
+    }
+    const unsigned b0 = Y.b & 0xffffu, b1 = Y.b >> 16;
+    unsigned out = 0;
+#pragma unroll
+    for(int i = 0; i < 4; ++i)
+    {
+        const unsigned o = (((b0 * (r0[i] >> 4)) >> 16) + ((b1 * (r1[i] >> 4)) >> 16) + 2u) >> 2;
+        out |= (o & 0xffu) << (8 * i);
+    }
+    *reinterpret_cast<unsigned*>(dst + blockIdx.z * dfs + (long long)y * dpitch + 4 * q) = out; // pitch covers the tail
 }
 
 // =================================================================================================
@@ -846,6 +889,37 @@ void linear_taps_y(int src, int dst, YTap* t)
     }
 }
 
+// quad table of k_dist_resize_quads for one level (see the kernel); false when a quad's taps do not fit the 8-byte window
+bool linear_quads(const XTap* xt, int dw, std::vector<uint4>* out)
+{
+    const int nq = (dw + 3) / 4;
+    const size_t before = out->size();
+    for(int q = 0; q < nq; ++q)
+    {
+        int ofs[4], base = 1 << 30;
+        unsigned a[4];
+        for(int j = 0; j < 4; ++j)
+        {
+            const XTap& t = xt[std::min(4 * q + j, dw - 1)];
+            ofs[j] = t.ofs, a[j] = t.a;
+            base = std::min(base, ofs[j]);
+        }
+        unsigned sel[4];
+        for(int j = 0; j < 4; ++j)
+        {
+            if(ofs[j] - base + 1 > 7) // the right tap must lie inside the 8-byte window that starts at `base`
+            {
+                out->resize(before);
+                return false;
+            }
+            sel[j] = (unsigned)(ofs[j] - base) | ((unsigned)(ofs[j] - base + 1) << 4);
+        }
+        out->push_back(make_uint4((unsigned)base, (sel[0] | (sel[1] << 8)) | ((sel[2] | (sel[3] << 8)) << 16), 0u, 0u));
+        out->push_back(make_uint4(a[0], a[1], a[2], a[3]));
+    }
+    return true;
+}
+
 struct DistGeometry
 {
     DistParams P;
@@ -855,6 +929,7 @@ struct DistGeometry
     size_t tree_smem;
     std::vector<XTap> xtab;
     std::vector<YTap> ytab;
+    std::vector<uint4> qtab;
     bool ok;
 };
 
@@ -865,6 +940,7 @@ void build_dist_geometry(const mslam_b200_dist_config& cfg, int W, int H, DistGe
     g->ok = false;
     g->xtab.clear();
     g->ytab.clear();
+    g->qtab.clear();
     P.nlevels = cfg.nlevels;
     P.W = W, P.H = H;
     P.ini_thr = cfg.ini_fast_threshold;
@@ -985,6 +1061,8 @@ void build_dist_geometry(const mslam_b200_dist_config& cfg, int W, int H, DistGe
             g->ytab.resize(yo + L.h);
             linear_taps_x(P.lv[l - 1].w, L.w, g->xtab.data() + xo);
             linear_taps_y(P.lv[l - 1].h, L.h, g->ytab.data() + yo);
+            L.qtab_off = (int)g->qtab.size();
+            L.nquads = linear_quads(g->xtab.data() + xo, L.w, &g->qtab) ? (L.w + 3) / 4 : 0;
             xo += L.w, yo += L.h;
         }
     }
@@ -1018,7 +1096,8 @@ struct mslam_b200_dist
     size_t pyr_bytes = 0;
     XTap* d_xtab = nullptr;
     YTap* d_ytab = nullptr;
-    int xtab_cap = 0, ytab_cap = 0;
+    uint4* d_qtab = nullptr;
+    int xtab_cap = 0, ytab_cap = 0, qtab_cap = 0;
     unsigned *d_cand = nullptr, *d_sel = nullptr, *d_tree = nullptr;
     long long cand_elems = 0, tree_words = 0;
     int sel_elems = 0;
@@ -1086,13 +1165,15 @@ static int dist_set_geometry(mslam_b200_dist* ctx, int W, int H)
     if(!g.ok)
         return MSLAM_B200_E_INVALID;
     if(g.pyr_bytes > ctx->pyr_bytes || g.cand_elems > ctx->cand_elems || g.tree_words > ctx->tree_words ||
-       g.sel_elems > ctx->sel_elems || (int)g.xtab.size() > ctx->xtab_cap || (int)g.ytab.size() > ctx->ytab_cap ||
+       g.sel_elems > ctx->sel_elems || (int)g.xtab.size() > ctx->xtab_cap || (int)g.ytab.size() > ctx->ytab_cap || (int)g.qtab.size() > ctx->qtab_cap ||
        g.tree_smem > ctx->tree_smem_max)
         return MSLAM_B200_E_INVALID;
     if(!g.xtab.empty())
     {
         DIST_CUDA_OK(cudaMemcpyAsync(ctx->d_xtab, g.xtab.data(), g.xtab.size() * sizeof(XTap), cudaMemcpyHostToDevice, ctx->stream));
         DIST_CUDA_OK(cudaMemcpyAsync(ctx->d_ytab, g.ytab.data(), g.ytab.size() * sizeof(YTap), cudaMemcpyHostToDevice, ctx->stream));
+        if(!g.qtab.empty())
+            DIST_CUDA_OK(cudaMemcpyAsync(ctx->d_qtab, g.qtab.data(), g.qtab.size() * sizeof(uint4), cudaMemcpyHostToDevice, ctx->stream));
         DIST_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     }
     ctx->P = g.P;
@@ -1127,7 +1208,7 @@ void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
     cudaSetDevice(ctx->cfg.device);
     if(ctx->stream)
         cudaStreamSynchronize(ctx->stream);
-    void* dev[] = {ctx->d_bgr, ctx->d_pyr, ctx->d_blur, ctx->d_xtab, ctx->d_ytab, ctx->d_cand, ctx->d_sel, ctx->d_tree,
+    void* dev[] = {ctx->d_qtab, ctx->d_bgr, ctx->d_pyr, ctx->d_blur, ctx->d_xtab, ctx->d_ytab, ctx->d_cand, ctx->d_sel, ctx->d_tree,
                    ctx->d_ctr, ctx->d_kp,  ctx->d_desc, ctx->d_counts};
     for(void* p : dev)
         if(p)
@@ -1239,15 +1320,18 @@ int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist
     ctx->sel_elems = g.sel_elems + 64;
     ctx->xtab_cap = (int)g.xtab.size() + 16;
     ctx->ytab_cap = (int)g.ytab.size() + 16;
+    ctx->qtab_cap = ctx->xtab_cap / 2 + 4 * kMaxLevels + 16; // two entries per quad, (w + 3) / 4 quads per level: monotone in the frame size
     ctx->tree_smem_max = g.tree_smem;
     ctx->bgr_bytes = B * c.max_width * c.max_height * 3;
     CREATE_OK(cudaMalloc(&ctx->d_bgr, 2 * ctx->bgr_bytes)); // two pipeline slots
-    CREATE_OK(cudaMalloc(&ctx->d_pyr, ctx->pyr_bytes));
+    // + 256: k_dist_resize_quads reads whole 12-byte windows, up to 10 bytes past a row's last pixel (weights there are 0)
+    CREATE_OK(cudaMalloc(&ctx->d_pyr, ctx->pyr_bytes + 256));
     CREATE_OK(cudaMalloc(&ctx->d_blur, ctx->pyr_bytes));
     CREATE_OK(cudaMemset(ctx->d_pyr, 0, ctx->pyr_bytes));
     CREATE_OK(cudaMemset(ctx->d_blur, 0, ctx->pyr_bytes));
     CREATE_OK(cudaMalloc(&ctx->d_xtab, ctx->xtab_cap * sizeof(XTap)));
     CREATE_OK(cudaMalloc(&ctx->d_ytab, ctx->ytab_cap * sizeof(YTap)));
+    CREATE_OK(cudaMalloc(&ctx->d_qtab, ctx->qtab_cap * sizeof(uint4)));
     CREATE_OK(cudaMalloc(&ctx->d_cand, B * ctx->cand_elems * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_sel, B * ctx->sel_elems * sizeof(unsigned)));
     if(ctx->tree_words > 0)
@@ -1329,6 +1413,12 @@ static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int frame0, int 
     for(int l = 1; l < P.nlevels; ++l)
     {
         const DistLevel &S = P.lv[l - 1], &D = P.lv[l];
+        if(D.nquads > 0)
+            k_dist_resize_quads<<<dim3((D.nquads + 63) / 64, (D.h + 3) / 4, n_frames), 256, 0, st>>>(
+                ctx->d_pyr + S.img_off + frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride,
+                ctx->d_pyr + D.img_off + frame0 * D.img_frame_stride, D.pitch, D.img_frame_stride, D.nquads, D.h,
+                ctx->d_qtab + D.qtab_off, ctx->d_ytab + D.ytab_off);
+        else
         k_dist_resize<<<dim3((D.w + 255) / 256, (D.h + 3) / 4, n_frames), 256, 0, st>>>(
             ctx->d_pyr + S.img_off + frame0 * S.img_frame_stride, S.pitch, S.img_frame_stride, S.w,
             ctx->d_pyr + D.img_off + frame0 * D.img_frame_stride, D.pitch, D.img_frame_stride, D.w,
