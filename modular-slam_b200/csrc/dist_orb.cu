@@ -651,30 +651,33 @@ __device__ __forceinline__ int reflect101_d(int p, int n)
     return p;
 }
 
+// tile: 64 columns x GT_H rows.  GT_H + 6 = 64 source rows = 32 row pairs x 16 column groups = two full rounds of the CTA in the
+// horizontal pass (a 32-row tile had 19 pairs: 304 items for 256 threads), and 6 halo rows per 58 instead of per 32
+constexpr int GT_H = 58, GT_IN = GT_H + 6, GT_RP = GT_IN / 2;
 __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
                                                     uint8_t* __restrict__ blur)
 {
-    __shared__ __align__(16) uint8_t in[38][76];
-    __shared__ __align__(16) unsigned hp[19][64]; // horizontally filtered rows, stored as row pairs
+    __shared__ __align__(16) uint8_t in[GT_IN][76];
+    __shared__ __align__(16) unsigned hp[GT_RP][64]; // horizontally filtered rows, stored as row pairs
     const int tid = threadIdx.x;
     const int l = level_of_gtile(P, blockIdx.x);
     const DistLevel& L = P.lv[l];
     const int t = blockIdx.x - L.gtile_base;
     const int ty = t / L.gtx, tx = t - ty * L.gtx;
-    const int x0 = tx * 64, y0 = ty * 32;
+    const int x0 = tx * 64, y0 = ty * GT_H;
     const uint8_t* img = pyr + L.img_off + (P.frame0 + blockIdx.y) * L.img_frame_stride;
     // shared row r holds columns x0 - 4 .. x0 + 71 of source row reflect(y0 + r - 3): 19 aligned words when the tile
     // is clear of the left / right image border, byte-wise with REFLECT_101 otherwise
     if(x0 >= 4 && x0 + 72 <= L.w)
     {
         const int lane = tid & 31;
-        for(int r = tid >> 5; r < 38; r += 8)
+        for(int r = tid >> 5; r < GT_IN; r += 8)
             if(lane < 19)
                 reinterpret_cast<unsigned*>(&in[r][0])[lane] = __ldg(
                     reinterpret_cast<const unsigned*>(img + (long long)reflect101_d(y0 + r - 3, L.h) * L.pitch + x0 - 4) + lane);
     }
     else
-        for(int i = tid; i < 38 * 70; i += 256)
+        for(int i = tid; i < GT_IN * 70; i += 256)
         {
             const int r = i / 70, c = i - r * 70;
             const int sy = reflect101_d(y0 + r - 3, L.h), sx = reflect101_d(x0 + c - 3, L.w);
@@ -684,7 +687,7 @@ __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ Dist
     // horizontal pass, exact in 8.8: an item is (row pair, 4 columns); the 10 bytes a row needs come from three aligned
     // words, every output is two IDP.4A over byte windows cut with PRMT.  Results are stored as row PAIRS -- word
     // (rp, x) = h[2 rp][x] | h[2 rp + 1][x] << 16 -- so that the vertical pass can run on IDP.2A.
-    for(int i = tid; i < 19 * 16; i += 256)
+    for(int i = tid; i < GT_RP * 16; i += 256)
     {
         const int rp = i >> 4, c = (i & 15) * 4;
         unsigned h[2][4];
@@ -706,7 +709,7 @@ __global__ void __launch_bounds__(256) k_dist_gauss(const __grid_constant__ Dist
     // vertical pass, exact in 16.16: output row y uses h rows y .. y+6 = row pairs (y >> 1) .. (y >> 1) + 3, with the tap
     // pairs shifted by one row when y is odd
     uint8_t* dst = blur + L.img_off + (P.frame0 + blockIdx.y) * L.img_frame_stride;
-    for(int i = tid; i < 32 * 16; i += 256)
+    for(int i = tid; i < GT_H * 16; i += 256)
     {
         const int y = i >> 4, xq = (i & 15) * 4;
         if(y0 + y >= L.h || x0 + xq >= L.w)
@@ -985,7 +988,7 @@ void build_dist_geometry(const mslam_b200_dist_config& cfg, int W, int H, DistGe
         L.cand_cap = cap;
         L.cand_off = coff;
         coff += (long long)align_up((size_t)cap, 4);
-        L.gtx = (L.w + 63) / 64, L.gty = (L.h + 31) / 32;
+        L.gtx = (L.w + 63) / 64, L.gty = (L.h + GT_H - 1) / GT_H;
         L.gtile_base = gtiles;
         gtiles += L.gtx * L.gty;
         // tree geometry (initialize_nodes, :989-1011)
