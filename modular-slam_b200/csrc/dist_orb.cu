@@ -23,8 +23,9 @@
 //                   (created == divided), per-leaf argmax by atomicMax on (score, arrival order), block scan for the
 //                   output rank.
 //   k_dist_gauss    64x32 tiles, 8.8 horizontal / 16.16 vertical fixed point, REFLECT_101
-//   k_dist_describe one warp per keypoint: moments with lane = patch column, cv::fastAtan2, polynomial cos/sin in
-//                   separately rounded f32, lane = descriptor byte
+//   k_dist_describe one warp per keypoint: moments as IDP.4A of aligned patch words against packed disc weights, cv::fastAtan2,
+//                   polynomial cos/sin in separately rounded f32, lane = descriptor byte (float pattern table, rounding
+//                   by the 1.5 * 2^23 magic add: nothing on the XU pipe)
 // All integer stages are exact by construction; every float operation is an explicit round-to-nearest intrinsic
 // (the library is also compiled with -fmad=false).
 #include <algorithm>
@@ -91,9 +92,6 @@ struct DistCounters
     unsigned n_fast, n_tree, passes, err;
 };
 
-__device__ __align__(16) const signed char g_pairs[256 * 4] = {
-#include "brief_pattern.inc"
-};
 
 // =================================================================================================
 // resize: cv::resize INTER_LINEAR, CV_8UC1 (OpenCV resize.cpp HResizeLinear / VResizeLinear, 11-bit coefficients)
@@ -764,7 +762,8 @@ __device__ __forceinline__ float util_cos(float v)
 
 __global__ void __launch_bounds__(256) k_dist_describe(const __grid_constant__ DistParams P, const uint8_t* __restrict__ pyr,
                                                        const uint8_t* __restrict__ blur, const DistCounters* __restrict__ ctr,
-                                                       const unsigned* __restrict__ sel, mslam_b200_keypoint* __restrict__ out_kp,
+                                                       const unsigned* __restrict__ sel, const float4* __restrict__ pat_t,
+                                                       const uint2* __restrict__ ic_w, mslam_b200_keypoint* __restrict__ out_kp,
                                                        uint8_t* __restrict__ out_desc, int* __restrict__ out_counts, int out_cap)
 {
     const int lane = threadIdx.x & 31;
@@ -792,32 +791,29 @@ __global__ void __launch_bounds__(256) k_dist_describe(const __grid_constant__ D
     const unsigned r = sel[(long long)frame * P.sel_frame_stride + L.sel_off + (g - base)];
     const int x = (r >> 8) & 0xfff, y = r >> 20;
     const uint8_t* img = pyr + L.img_off + frame * L.img_frame_stride;
-    // intensity-centroid moments over the radius-15 disc, lane = column u
+    // intensity-centroid moments over the radius-15 disc (u_max of orb_impl::orb_impl, :521-541 -- OpenCV's table): the 31 x 31
+    // patch as 31 rows x 9 ALIGNED words, every word against two packed signed-byte weight words (u resp. v inside the disc,
+    // 0 outside; ic_weight_table of the ORB path, per alignment of the patch) in two IDP.4A -- 9 word loads per lane where
+    // the first version issued 31 predicated byte loads
     int m10 = 0, m01 = 0;
     {
-        const int u = lane - 15;
-        const int au = u < 0 ? -u : u;
-        // u_max of orb_impl::orb_impl (:521-541), packed 4 bits per |v| (v = 0..15): 15 15 15 15 14 14 14 13 13 12 11 10 9 8 6 3
-        const unsigned long long umax = 0x3689ABCDDEEEFFFFull;
-        if(lane < 31)
-        {
-            // the disc is symmetric (u_max[|v|] >= |u|  <=>  |v| <= u_max[|u|]), so column u spans rows -vm .. vm
-            const int vm = (int)((umax >> (4 * au)) & 15);
-            const uint8_t* c = img + (long long)y * L.pitch + x + u;
-            int sum = 0;
-            // all 31 rows unrolled and predicated, so that the loads of a lane are independent and in flight together
+        constexpr int kIcWords = 31 * 9;
+        const unsigned pitch = (unsigned)L.pitch;
+        const int al = (x - 15) & 3;
+        const uint8_t* base = img + (long long)(y - 15) * pitch + ((x - 15) & ~3); // keypoints keep 19 px from the border
+        const uint2* wtab = ic_w + al * kIcWords;
 #pragma unroll
-            for(int v = -15; v <= 15; ++v)
+        for(int it = 0; it < (kIcWords + 31) / 32; ++it)
+        {
+            const unsigned i = (unsigned)(lane + 32 * it);
+            if(i < (unsigned)kIcWords)
             {
-                const int av = v < 0 ? -v : v;
-                if(av <= vm)
-                {
-                    const int val = __ldg(c + (long long)v * L.pitch);
-                    sum += val;
-                    m01 += v * val;
-                }
+                const unsigned rr = i / 9u, kk = i - 9u * rr;
+                const unsigned word = __ldg(reinterpret_cast<const unsigned*>(base + (rr * pitch + 4u * kk)));
+                const uint2 wgt = __ldg(wtab + i);
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(word), "r"(wgt.x));
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m01) : "r"(word), "r"(wgt.y));
             }
-            m10 = u * sum;
         }
         m10 = __reduce_add_sync(0xffffffffu, m10);
         m01 = __reduce_add_sync(0xffffffffu, m01);
@@ -826,18 +822,24 @@ __global__ void __launch_bounds__(256) k_dist_describe(const __grid_constant__ D
     // keypt.angle * M_PI / 180.0 in double, then float (:574)
     const float rad = (float)((double)angle * 3.14159265358979323846 / 180.0);
     const float ca = util_cos(rad), sa = util_cos(__fsub_rn(__fdiv_rn(3.14159265358979f, 2.0f), rad));
-    const uint8_t* bc = blur + L.img_off + frame * L.img_frame_stride + (long long)y * L.pitch + x;
+    // rotated tests: cvRound(v) = low bits of (v + 1.5 * 2^23) - 0x4B400000 (round-to-nearest-even, what __float2int_rn gave);
+    // the two subtractions are folded into the base pointer: iy * pitch + ix = by * pitch + bx - 0x4B400000 * (pitch + 1)
+    // (mod 2^32).  Pattern as floats (brief_pattern_transposed of the ORB path): no I2F / F2I, which run on the 16-lane XU
+    // pipe and were 64 of them per lane and keypoint.
+    const int pitch = L.pitch;
+    const unsigned kfold = 0x4B400000u * (unsigned)(pitch + 1);
+    const uint8_t* bc = blur + L.img_off + frame * L.img_frame_stride + (long long)y * pitch + x;
     unsigned byte = 0;
 #pragma unroll
     for(int b = 0; b < 8; ++b)
     {
-        const char4 p = reinterpret_cast<const char4*>(g_pairs)[lane * 8 + b];
-        const float x0 = (float)p.x, y0 = (float)p.y, x1 = (float)p.z, y1 = (float)p.w;
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
-        const int v0 = __ldg(bc + (long long)r0 * L.pitch + c0), v1 = __ldg(bc + (long long)r1 * L.pitch + c1);
+        const float4 t = __ldg(pat_t + b * 32 + lane); // test (lane * 8 + b): x0, y0, x1, y1
+        const unsigned by0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.x, sa), __fmul_rn(t.y, ca)), 12582912.f));
+        const unsigned bx0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.x, ca), __fmul_rn(t.y, sa)), 12582912.f));
+        const unsigned by1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(t.z, sa), __fmul_rn(t.w, ca)), 12582912.f));
+        const unsigned bx1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(t.z, ca), __fmul_rn(t.w, sa)), 12582912.f));
+        const int o0 = (int)(by0 * (unsigned)pitch + bx0 - kfold), o1 = (int)(by1 * (unsigned)pitch + bx1 - kfold);
+        const int v0 = __ldg(bc + o0), v1 = __ldg(bc + o1);
         byte |= (unsigned)(v0 < v1) << b;
     }
     out_desc[((long long)frame * out_cap + g) * 32 + lane] = (uint8_t)byte;
@@ -1100,6 +1102,8 @@ struct mslam_b200_dist
     XTap* d_xtab = nullptr;
     YTap* d_ytab = nullptr;
     uint4* d_qtab = nullptr;
+    float4* d_pat = nullptr; // rBRIEF pattern as floats, transposed (brief_pattern_transposed)
+    uint2* d_icw = nullptr;  // intensity-centroid byte weights (ic_weight_table)
     int xtab_cap = 0, ytab_cap = 0, qtab_cap = 0;
     unsigned *d_cand = nullptr, *d_sel = nullptr, *d_tree = nullptr;
     long long cand_elems = 0, tree_words = 0;
@@ -1211,7 +1215,7 @@ void mslam_b200_dist_destroy(mslam_b200_dist* ctx)
     cudaSetDevice(ctx->cfg.device);
     if(ctx->stream)
         cudaStreamSynchronize(ctx->stream);
-    void* dev[] = {ctx->d_qtab, ctx->d_bgr, ctx->d_pyr, ctx->d_blur, ctx->d_xtab, ctx->d_ytab, ctx->d_cand, ctx->d_sel, ctx->d_tree,
+    void* dev[] = {ctx->d_pat, ctx->d_icw, ctx->d_qtab, ctx->d_bgr, ctx->d_pyr, ctx->d_blur, ctx->d_xtab, ctx->d_ytab, ctx->d_cand, ctx->d_sel, ctx->d_tree,
                    ctx->d_ctr, ctx->d_kp,  ctx->d_desc, ctx->d_counts};
     for(void* p : dev)
         if(p)
@@ -1335,6 +1339,16 @@ int mslam_b200_dist_create(const mslam_b200_dist_config* cfg_in, mslam_b200_dist
     CREATE_OK(cudaMalloc(&ctx->d_xtab, ctx->xtab_cap * sizeof(XTap)));
     CREATE_OK(cudaMalloc(&ctx->d_ytab, ctx->ytab_cap * sizeof(YTap)));
     CREATE_OK(cudaMalloc(&ctx->d_qtab, ctx->qtab_cap * sizeof(uint4)));
+    {
+        float pat[1024];
+        brief_pattern_transposed(pat);
+        CREATE_OK(cudaMalloc(&ctx->d_pat, sizeof(pat)));
+        CREATE_OK(cudaMemcpy(ctx->d_pat, pat, sizeof(pat), cudaMemcpyHostToDevice));
+        std::vector<unsigned> icw(4 * 31 * 9 * 2);
+        ic_weight_table(icw.data());
+        CREATE_OK(cudaMalloc(&ctx->d_icw, icw.size() * sizeof(unsigned)));
+        CREATE_OK(cudaMemcpy(ctx->d_icw, icw.data(), icw.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
+    }
     CREATE_OK(cudaMalloc(&ctx->d_cand, B * ctx->cand_elems * sizeof(unsigned)));
     CREATE_OK(cudaMalloc(&ctx->d_sel, B * ctx->sel_elems * sizeof(unsigned)));
     if(ctx->tree_words > 0)
@@ -1460,7 +1474,7 @@ static int dist_run(mslam_b200_dist* ctx, const uint8_t* d_bgr, int frame0, int 
         DIST_CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
     const int slots = std::min(capacity, ctx->kp_cap);
     k_dist_describe<<<dim3((std::max(slots, 1) + 7) / 8, n_frames), 256, 0, st>>>(P, ctx->d_pyr, ctx->d_blur, ctx->d_ctr, ctx->d_sel,
-                                                                                  d_kp, d_desc, d_counts, capacity);
+                                                                                  ctx->d_pat, ctx->d_icw, d_kp, d_desc, d_counts, capacity);
     ++ctx->launches;
     if(tm)
         cudaEventRecord(ctx->ev[6], st);
