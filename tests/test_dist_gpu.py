@@ -52,9 +52,11 @@ def test_synthetic_sizes_bit_exact(pkg, oracle, W, H):
 
 
 @pytest.mark.parametrize("nlevels,sf,ini,mn,min_size,W,H", [(5, 1.5, 30, 10, 400, 640, 480), (3, 2.0, 12, 12, 5000, 800, 300),
-                                                            (8, 1.2, 20, 7, 150, 400, 400), (11, 1.1, 40, 5, 1000, 512, 384)])
+                                                            (8, 1.2, 20, 7, 150, 400, 400), (11, 1.1, 40, 5, 1000, 512, 384),
+                                                            (3, 2.5, 20, 7, 1000, 900, 700)])
 def test_non_default_parameters(pkg, oracle, nlevels, sf, ini, mn, min_size, W, H):
-    """orb_params / min_size other than the hard-coded ones, including an exact 2x pyramid and several initial tree nodes"""
+    """orb_params / min_size other than the hard-coded ones, including an exact 2x pyramid, a 2.5x one (the resize kernel's
+    per-pixel fallback: four output pixels span more than the quad kernel's 8-byte window) and several initial tree nodes"""
     frames, _ = pkg.synth.frame_batch(W, H, 1, 0, seed=nlevels * 100 + ini)
     prm = oracle.dist_default_params(nlevels=nlevels, ini_fast_thr=ini, min_fast_thr=mn, min_size=min_size, scale_factor=sf)
     with pkg.DistContext(max_width=W, max_height=H, nlevels=nlevels, scale_factor=sf, ini_fast_threshold=ini,
