@@ -1,8 +1,11 @@
 #!/usr/bin/env python
 """k_fast's instructions and stall samples by phase, from the source page of an .ncu-rep captured with --import-source on
-   python tools/ncu_phases.py gpurun_out/r2_prof_fast.ncu-rep [launch index]"""
+   python tools/ncu_phases.py gpurun_out/r2_prof_fast.ncu-rep [launch index]
+The report has one section per (launch, source file): the kernel's own file (orb_kernels.cu: phases by line markers), the
+shared helpers (fast_simd.cuh: by function) and CUDA headers inlined into it."""
 import collections
 import csv
+import os
 import subprocess
 import sys
 
@@ -12,49 +15,59 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-n
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hs = [i for i, r in enumerate(rows) if "Instructions Executed" in r and r[0] == "Line No"]
-# per launch: one section per source file (the kernel's own file first, then CUDA headers inlined into it)
-per = max(1, len(hs) // max(1, sum(1 for i in hs if rows[i + 1][0:1] and rows[i + 1][1].startswith("asm(lop3")) or 1))
-h = hs[which * per]
-end = hs[which * per + 1] if which * per + 1 < len(hs) else len(rows)
-hdr = rows[h]
-ci, cs = hdr.index("Instructions Executed"), hdr.index("# Samples")
-src = []
-for r in rows[h + 1:end]:
-    if len(r) < len(hdr) or r[0] == "":
-        continue
-    try:
-        src.append((int(r[0]), r[1].strip(), int(r[ci] or 0), int(r[cs] or 0)))
-    except ValueError:
-        continue
-tot = sum(x[2] for x in src) or 1
-stot = sum(x[3] for x in src) or 1
-lines = open("modular-slam_b200/csrc/orb_kernels.cu").read().splitlines()
+files = []
+for h in hs:
+    f = next((r[1] for r in rows[max(0, h - 4):h] if r and r[0] == "File Path"), "?")
+    files.append(os.path.basename(f))
+# a launch = the run of sections up to the next repetition of the first file
+first = files[0]
+starts = [i for i, f in enumerate(files) if f == first]
+lo = starts[which]
+hi = starts[which + 1] if which + 1 < len(starts) else len(hs)
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def find(s):
-    return next(i + 1 for i, l in enumerate(lines) if s in l)
+def marks_of(path, marks):
+    lines = open(os.path.join(ROOT, "modular-slam_b200", "csrc", path)).read().splitlines()
+    out = []
+    for name, text in marks:
+        out.append((name, next(i + 1 for i, l in enumerate(lines) if text in l)))
+    return out
 
 
-marks = [("staging", find("which level does this tile belong to")), ("phase A compare+run9", find("---- phase A: classify")),
-         ("queue append", find("only positions that can matter")), ("phase B score", find("---- phase B: exact cornerScore")),
-         ("phase C nms", find("---- phase C: 3x3 strict NMS")), ("output", find("const int n_out = s_on;")), ("end", find("// K4  select"))]
-helpers = [("any_run9", find("__device__ __forceinline__ unsigned any_run9"), find("// the 4 pixels starting dx")),
-           ("ring4", find("// the 4 pixels starting dx"), find("// exact cornerScore of TWO pixels")),
-           ("corner_score2", find("// exact cornerScore of TWO pixels"), find("__device__ __forceinline__ unsigned fast_smem_u32")),
-           ("lop3 helpers", find("__device__ __forceinline__ unsigned lop3_maj_a_nb_c"), find("// bit 7 of each byte of the result")),
-           ("mbarrier", find("__device__ __forceinline__ unsigned fast_smem_u32"), find("#ifndef MSLAM_FAST_CTAS"))]
+PHASES = {
+    "orb_kernels.cu": marks_of("orb_kernels.cu", [("staging", "which level does this tile belong to"), ("phase A compare", "---- phase A: classify"),
+                                                  ("queue append", "only positions that can matter"),
+                                                  ("phase B decode", "---- phase B: exact cornerScore"), ("phase C nms", "---- phase C: 3x3 strict NMS"),
+                                                  ("output", "const int n_out = s_on;"), ("end", "// K4  select")]),
+    "fast_simd.cuh": marks_of("fast_simd.cuh", [("lop3 helpers", "lop3_maj_a_nb_c(unsigned a"), ("any_run9", "__device__ __forceinline__ unsigned any_run9"),
+                                                ("ring4", "__device__ __forceinline__ unsigned ring4"), ("corner_score2", "template <int S"),
+                                                ("end", "} // namespace mslam_b200")]),
+}
 agg, sagg = collections.Counter(), collections.Counter()
-for ln, txt, n, s in src:
-    name = None
-    for nm, a, b in helpers:
-        if a <= ln < b:
-            name = nm
-    if name is None:
-        for (nm, a), (_, b) in zip(marks, marks[1:]):
-            if a <= ln < b:
-                name = nm
-    agg[name or "other"] += n
-    sagg[name or "other"] += s
-print(f"total warp instructions {tot}, samples {stot}")
+for si in range(lo, hi):
+    h = hs[si]
+    end = hs[si + 1] if si + 1 < len(hs) else len(rows)
+    hdr = rows[h]
+    ci, cs = hdr.index("Instructions Executed"), hdr.index("# Samples")
+    marks = PHASES.get(files[si])
+    for r in rows[h + 1:end]:
+        if len(r) < len(hdr) or r[0] == "":
+            continue
+        try:
+            ln, n, s = int(r[0]), int(r[ci] or 0), int(r[cs] or 0)
+        except ValueError:
+            continue
+        name = files[si]
+        if marks:
+            name = "(before the kernel)"
+            for (nm, a), (_, b) in zip(marks, marks[1:]):
+                if a <= ln < b:
+                    name = nm
+        agg[name] += n
+        sagg[name] += s
+tot = sum(agg.values()) or 1
+stot = sum(sagg.values()) or 1
+print(f"launch {which}: total warp instructions {tot}, samples {stot}")
 for k, v in agg.most_common():
-    print(f"{k:22s} inst {v / tot:6.3f}  samples {sagg[k] / stot:6.3f}")
+    print(f"{k:28s} inst {v / tot:6.3f}  samples {sagg[k] / stot:6.3f}")
