@@ -304,12 +304,44 @@ __device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_vali
 // bias back after every drain, all eight K steps accumulate) every value 256 + dot = 512 - 2 hamming is non-negative, two of
 // them pack into one register with ONE IMAD (odd * 65536 + even, no carries), and the two LARGEST per 16-bit lane are the two
 // nearest neighbours.  (One IMAD per key pair instead of two measured +7 % on the epilogue-bound kernel.) ----
-__device__ __forceinline__ void tmem_st32_const(uint32_t taddr, uint32_t c)
+// The store takes 32 CONSECUTIVE registers.  Fed from one value (the first version: "{%1, %1, ...}") the compiler builds that
+// tuple with 32 moves in front of EVERY store -- 128 extra instructions per 128-column window in a warp whose useful work is
+// ~270 (seen in the SASS: IMAD.MOV.U32 R4..R35, 0x100; STTM.x32).  So the bias lives in 32 registers of its own, filled once per
+// thread (AccBias), and the store names them.
+#ifndef MSLAM_BIAS_TUPLE
+#define MSLAM_BIAS_TUPLE 8 // registers per bias store (8: four tcgen05.st.x8 per 32 columns; 16: two .x16) -- A/B aid
+#endif
+struct AccBias
 {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-                 "{%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr),
-                 "r"(c)
-                 : "memory");
+    uint32_t r[MSLAM_BIAS_TUPLE];
+    // `zero` is a run-time 0 the compiler cannot see through: r[i] = c + bit i of it are values that are equal but not provably
+    // so (ptxas folds plain copies of one value back into one register and re-creates the moves at every store)
+    __device__ __forceinline__ void fill(uint32_t c, uint32_t zero)
+    {
+#pragma unroll
+        for(int i = 0; i < MSLAM_BIAS_TUPLE; ++i)
+            r[i] = c + ((zero >> i) & 1u);
+    }
+};
+// 32 columns of bias: several narrower stores that all name the SAME short register tuple (a .x32 store fed from its own 32
+// registers still made ptxas copy them next to the load buffers at most call sites)
+__device__ __forceinline__ void tmem_st32_bias(uint32_t taddr, const AccBias& b)
+{
+#if MSLAM_BIAS_TUPLE == 16
+#pragma unroll
+    for(int c = 0; c < 32; c += 16)
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+                     "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr + c),
+                     "r"(b.r[0]), "r"(b.r[1]), "r"(b.r[2]), "r"(b.r[3]), "r"(b.r[4]), "r"(b.r[5]), "r"(b.r[6]), "r"(b.r[7]), "r"(b.r[8]),
+                     "r"(b.r[9]), "r"(b.r[10]), "r"(b.r[11]), "r"(b.r[12]), "r"(b.r[13]), "r"(b.r[14]), "r"(b.r[15])
+                     : "memory");
+#else
+#pragma unroll
+    for(int c = 0; c < 32; c += 8)
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr + c), "r"(b.r[0]),
+                     "r"(b.r[1]), "r"(b.r[2]), "r"(b.r[3]), "r"(b.r[4]), "r"(b.r[5]), "r"(b.r[6]), "r"(b.r[7])
+                     : "memory");
+#endif
 }
 __device__ __forceinline__ void tmem_wait_st()
 {
@@ -370,7 +402,7 @@ __device__ __forceinline__ void push32_max(Top2Max& t, const uint32_t (&v)[32], 
     }
 }
 // one 128-column key window of a biased accumulator: drain (double-buffered loads) and write the bias back behind every load
-__device__ __forceinline__ void drain_tile_max(Top2Max& t, uint32_t taddr, int n_valid, unsigned two16)
+__device__ __forceinline__ void drain_tile_max(Top2Max& t, uint32_t taddr, int n_valid, unsigned two16, const AccBias& bias)
 {
     uint32_t va[32], vb[32];
     auto group = [&](const uint32_t (&v)[32], int col0) {
@@ -382,18 +414,18 @@ __device__ __forceinline__ void drain_tile_max(Top2Max& t, uint32_t taddr, int n
     tmem_ld32(taddr, va);
     tmem_wait(va);
     tmem_ld32(taddr + 32, vb);
-    tmem_st32_const(taddr, kAccBias);
+    tmem_st32_bias(taddr, bias);
     group(va, 0);
     tmem_wait(vb);
     tmem_ld32(taddr + 64, va);
-    tmem_st32_const(taddr + 32, kAccBias);
+    tmem_st32_bias(taddr + 32, bias);
     group(vb, 32);
     tmem_wait(va);
     tmem_ld32(taddr + 96, vb);
-    tmem_st32_const(taddr + 64, kAccBias);
+    tmem_st32_bias(taddr + 64, bias);
     group(va, 64);
     tmem_wait(vb);
-    tmem_st32_const(taddr + 96, kAccBias);
+    tmem_st32_bias(taddr + 96, bias);
     group(vb, 96);
     tmem_wait_st();
 }
@@ -897,15 +929,17 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
         const int quarter = warp & 3, part = warp >> 2;
         const int win = (part * CPW) / MMA_N, col0 = (part * CPW) % MMA_N; // 128-column key window of the part, first column in it
         unsigned k0[2], k1[2];
+        AccBias bias;
         if(BIAS)
         {
+            bias.fill(kAccBias, db.km.two16 & 0xffffu); // two16 = 65536: its low half is the run-time zero
 #pragma unroll
             for(int a = 0; a < 2; ++a)
             {
                 const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * WIDE_N + part * CPW;
 #pragma unroll
                 for(int c = 0; c < CPW; c += 32)
-                    tmem_st32_const(taddr + c, kAccBias);
+                    tmem_st32_bias(taddr + c, bias);
             }
             tmem_wait_st();
             tc_fence_before();
@@ -932,7 +966,7 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                     if(BIAS)
                     {
                         Top2Max tm;
-                        drain_tile_max(tm, taddr, max(n_valid, 0), db.km.two16);
+                        drain_tile_max(tm, taddr, max(n_valid, 0), db.km.two16, bias);
                         tc_fence_before();
                         __syncwarp();
                         if(lane == 0)
