@@ -300,77 +300,49 @@ __device__ __forceinline__ void drain_tile(Top2x2& t, uint32_t taddr, int n_vali
     group(vb, 96);
 }
 
-// ---- keyframe-database scoring needs distances only, not indices: with accumulators that START at 256 (the epilogue writes the
-// bias back after every drain, all eight K steps accumulate) every value 256 + dot = 512 - 2 hamming is non-negative, two of
-// them pack into one register with ONE IMAD (odd * 65536 + even, no carries), and the two LARGEST per 16-bit lane are the two
-// nearest neighbours.  (One IMAD per key pair instead of two measured +7 % on the epilogue-bound kernel.) ----
-// The store takes 32 CONSECUTIVE registers.  Fed from one value (the first version: "{%1, %1, ...}") the compiler builds that
-// tuple with 32 moves in front of EVERY store -- 128 extra instructions per 128-column window in a warp whose useful work is
-// ~270 (seen in the SASS: IMAD.MOV.U32 R4..R35, 0x100; STTM.x32).  So the bias lives in 32 registers of its own, filled once per
-// thread (AccBias), and the store names them.
-#ifndef MSLAM_BIAS_TUPLE
-#define MSLAM_BIAS_TUPLE 8 // registers per bias store (8: four tcgen05.st.x8 per 32 columns; 16: two .x16) -- A/B aid
-#endif
-struct AccBias
+// ---- keyframe-database scoring needs distances only, not indices, and tcgen05.ld can PACK: with .pack::16b one register receives
+// the low 16 bits of two adjacent 32-bit accumulator columns, (column 2i + 1) << 16 | column 2i (measured: tools/tmem_pack_probe.cu)
+// -- exactly the pair the epilogue used to build with an IMAD, for dots in [-256, 256] as two's-complement s16 lanes.  So the
+// database epilogue loads 64 columns into 32 registers, keeps the two LARGEST dots (= the two nearest neighbours) per signed
+// 16-bit lane with VIMNMX.S16x2, and needs neither packing arithmetic nor biased accumulators (the first version of this path
+// wrote 256 into every accumulator behind each drain to make the values non-negative for an IMAD pack). ----
+__device__ __forceinline__ void tmem_ld64_pack(uint32_t taddr, uint32_t (&v)[32])
 {
-    uint32_t r[MSLAM_BIAS_TUPLE];
-    // `zero` is a run-time 0 the compiler cannot see through: r[i] = c + bit i of it are values that are equal but not provably
-    // so (ptxas folds plain copies of one value back into one register and re-creates the moves at every store)
-    __device__ __forceinline__ void fill(uint32_t c, uint32_t zero)
-    {
-#pragma unroll
-        for(int i = 0; i < MSLAM_BIAS_TUPLE; ++i)
-            r[i] = c + ((zero >> i) & 1u);
-    }
-};
-// 32 columns of bias: several narrower stores that all name the SAME short register tuple (a .x32 store fed from its own 32
-// registers still made ptxas copy them next to the load buffers at most call sites)
-__device__ __forceinline__ void tmem_st32_bias(uint32_t taddr, const AccBias& b)
-{
-#if MSLAM_BIAS_TUPLE == 16
-#pragma unroll
-    for(int c = 0; c < 32; c += 16)
-        asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-                     "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr + c),
-                     "r"(b.r[0]), "r"(b.r[1]), "r"(b.r[2]), "r"(b.r[3]), "r"(b.r[4]), "r"(b.r[5]), "r"(b.r[6]), "r"(b.r[7]), "r"(b.r[8]),
-                     "r"(b.r[9]), "r"(b.r[10]), "r"(b.r[11]), "r"(b.r[12]), "r"(b.r[13]), "r"(b.r[14]), "r"(b.r[15])
-                     : "memory");
-#else
-#pragma unroll
-    for(int c = 0; c < 32; c += 8)
-        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr + c), "r"(b.r[0]),
-                     "r"(b.r[1]), "r"(b.r[2]), "r"(b.r[3]), "r"(b.r[4]), "r"(b.r[5]), "r"(b.r[6]), "r"(b.r[7])
-                     : "memory");
-#endif
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+                   "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+                   "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr)
+                 : "memory");
 }
-__device__ __forceinline__ void tmem_wait_st()
+constexpr unsigned kNothingS16x2 = 0x80008000u; // -32768 in both lanes: below every dot
+constexpr int kDotBias = 256;                   // the scalar results leave Top2MaxS as dot + 256 = 512 - 2 hamming, 0 = nothing
+struct Top2MaxS
 {
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-}
-constexpr uint32_t kAccBias = 256;
-struct Top2Max
-{
-    unsigned k0 = 0, k1 = 0, a0 = 0, a1 = 0; // two independent chains of (largest, second largest) per 16-bit lane; 0 = nothing yet
+    unsigned k0 = kNothingS16x2, k1 = kNothingS16x2, a0 = kNothingS16x2, a1 = kNothingS16x2; // two independent chains
     __device__ __forceinline__ void push2(unsigned a, unsigned b)
     {
-        const unsigned M = __vmaxu2(a, b), m = __vminu2(a, b);
-        k1 = __vimax3_u16x2(k1, __vminu2(k0, M), m);
-        k0 = __vmaxu2(k0, M);
+        const unsigned M = __vmaxs2(a, b), m = __vmins2(a, b);
+        k1 = __vimax3_s16x2(k1, __vmins2(k0, M), m);
+        k0 = __vmaxs2(k0, M);
     }
     __device__ __forceinline__ void push2_alt(unsigned a, unsigned b)
     {
-        const unsigned M = __vmaxu2(a, b), m = __vminu2(a, b);
-        a1 = __vimax3_u16x2(a1, __vminu2(a0, M), m);
-        a0 = __vmaxu2(a0, M);
+        const unsigned M = __vmaxs2(a, b), m = __vmins2(a, b);
+        a1 = __vimax3_s16x2(a1, __vmins2(a0, M), m);
+        a0 = __vmaxs2(a0, M);
     }
-    // the two largest of all four lanes' (largest, second largest), as plain integers
+    // the two largest of all four lanes' (largest, second largest), as dot + 256 (0 = nothing)
     __device__ __forceinline__ void top2(unsigned& m0, unsigned& m1) const
     {
-        const unsigned hi = __vmaxu2(k0, a0), lo = __vminu2(k0, a0);
-        const unsigned se = __vimax3_u16x2(lo, k1, a1); // per lane: (hi, se) = its two largest
-        const unsigned h0 = hi & 0xffffu, h1 = hi >> 16, s0 = se & 0xffffu, s1 = se >> 16;
-        m0 = max(h0, h1);
-        m1 = max(min(h0, h1), max(s0, s1));
+        const unsigned hi = __vmaxs2(k0, a0), lo = __vmins2(k0, a0);
+        const unsigned se = __vimax3_s16x2(lo, k1, a1); // per lane: (hi, se) = its two largest
+        const int h0 = (short)(hi & 0xffffu), h1 = (short)(hi >> 16), s0 = (short)(se & 0xffffu), s1 = (short)(se >> 16);
+        m0 = (unsigned)max(max(h0, h1) + kDotBias, 0);
+        m1 = (unsigned)max(max(min(h0, h1), max(s0, s1)) + kDotBias, 0);
     }
 };
 __device__ __forceinline__ void merge2max(unsigned& m0, unsigned& m1, unsigned o0, unsigned o1)
@@ -379,55 +351,46 @@ __device__ __forceinline__ void merge2max(unsigned& m0, unsigned& m1, unsigned o
     m1 = max(lo, max(m1, o1));
     m0 = hi;
 }
-// 32 biased accumulators -> 16 packed pairs -> the max chains; MASKED: columns >= n_valid count as 0 ("nothing")
+// 32 packed registers = 64 columns starting at col0 -> the max chains; MASKED: columns >= n_valid count as "nothing"
 template <bool MASKED>
-__device__ __forceinline__ void push32_max(Top2Max& t, const uint32_t (&v)[32], int col0, int n_valid, unsigned two16)
+__device__ __forceinline__ void push64_pack(Top2MaxS& t, const uint32_t (&v)[32], int col0, int n_valid)
 {
 #pragma unroll
-    for(int i = 0; i < 32; i += 4)
+    for(int i = 0; i < 32; i += 2)
     {
-        unsigned pk[2];
-#pragma unroll
-        for(int h = 0; h < 2; ++h)
+        unsigned pk[2] = {v[i], v[i + 1]};
+        if(MASKED)
         {
-            const int c0 = col0 + i + 2 * h;
-            pk[h] = v[i + 2 * h + 1] * two16 + v[i + 2 * h];
-            if(MASKED)
-                pk[h] &= (c0 < n_valid ? 0x0000ffffu : 0u) | ((c0 + 1) < n_valid ? 0xffff0000u : 0u);
+#pragma unroll
+            for(int h = 0; h < 2; ++h)
+            {
+                const int c0 = col0 + 2 * (i + h);
+                const unsigned keep = (c0 < n_valid ? 0x0000ffffu : 0u) | ((c0 + 1) < n_valid ? 0xffff0000u : 0u);
+                pk[h] = (pk[h] & keep) | (kNothingS16x2 & ~keep);
+            }
         }
-        if(i & 4)
+        if(i & 2)
             t.push2_alt(pk[0], pk[1]);
         else
             t.push2(pk[0], pk[1]);
     }
 }
-// one 128-column key window of a biased accumulator: drain (double-buffered loads) and write the bias back behind every load
-__device__ __forceinline__ void drain_tile_max(Top2Max& t, uint32_t taddr, int n_valid, unsigned two16, const AccBias& bias)
+// one 128-column key window: two packed loads of 64 columns, the second in flight while the first is processed
+__device__ __forceinline__ void drain_tile_pack(Top2MaxS& t, uint32_t taddr, int n_valid)
 {
     uint32_t va[32], vb[32];
     auto group = [&](const uint32_t (&v)[32], int col0) {
-        if(col0 + 32 <= n_valid) // warp-uniform
-            push32_max<false>(t, v, col0, n_valid, two16);
+        if(col0 + 64 <= n_valid) // warp-uniform
+            push64_pack<false>(t, v, col0, n_valid);
         else if(col0 < n_valid)
-            push32_max<true>(t, v, col0, n_valid, two16);
+            push64_pack<true>(t, v, col0, n_valid);
     };
-    tmem_ld32(taddr, va);
+    tmem_ld64_pack(taddr, va);
     tmem_wait(va);
-    tmem_ld32(taddr + 32, vb);
-    tmem_st32_bias(taddr, bias);
+    tmem_ld64_pack(taddr + 64, vb);
     group(va, 0);
     tmem_wait(vb);
-    tmem_ld32(taddr + 64, va);
-    tmem_st32_bias(taddr + 32, bias);
-    group(vb, 32);
-    tmem_wait(va);
-    tmem_ld32(taddr + 96, vb);
-    tmem_st32_bias(taddr + 64, bias);
-    group(va, 64);
-    tmem_wait(vb);
-    tmem_st32_bias(taddr + 96, bias);
-    group(vb, 96);
-    tmem_wait_st();
+    group(vb, 64);
 }
 
 // NG groups of 32 accumulator columns starting at column col0 of a 128-column key window of which the first n_valid exist
@@ -839,9 +802,8 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
         }
     };
     const int n_row_tiles = nq - q0 > MMA_M ? 2 : 1;
-    // database scoring with the eight-warp epilogue runs on biased accumulators (see drain_tile_max): the epilogue warps write
-    // 256 into every accumulator column once at the start and again behind every drain, all eight K steps accumulate
-    constexpr bool BIAS = DB && EW == 8;
+    // database scoring with the eight-warp epilogue reads its accumulators as packed s16 pairs (see drain_tile_pack)
+    constexpr bool PACK = DB && EW == 8;
     uint8_t* sA = smem;
     uint8_t* sB = smem + A_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_BYTES + WIDE_STAGES * WIDE_B_BYTES);
@@ -906,16 +868,16 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                     const uint32_t b_addr = smem_u32(sB + s * WIDE_B_BYTES);
                     for(int a = 0; a < n_row_tiles; ++a)
                     {
-                        // query tile a's accumulator of the previous train tile is drained (BIAS: and re-initialised; the first
-                        // phase of the barrier is the epilogue's initial write of the bias)
-                        mbar_wait(bar_cempty + 8 * a, BIAS ? (it & 1) : ((it & 1) ^ 1));
+                        // query tile a's accumulator of the previous train tile is drained
+                        mbar_wait(bar_cempty + 8 * a, (it & 1) ^ 1);
                         tc_fence_after();
 #pragma unroll
                         for(int k = 0; k < ROW_BYTES / 32; ++k)
+                            if(k == 0 || !MMA_DBG(1))
                             asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                                          "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem + a * WIDE_N),
                                          "l"(smem_desc(a_addr + a * (MMA_M * ROW_BYTES) + k * 256)), "l"(smem_desc(b_addr + k * 256)),
-                                         "r"(kIdescWide), "r"((uint32_t)(BIAS || k > 0))
+                                         "r"(kIdescWide), "r"((uint32_t)(k > 0))
                                          : "memory");
                         umma_commit(bar_cfull + 8 * a);
                     }
@@ -929,29 +891,8 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
         const int quarter = warp & 3, part = warp >> 2;
         const int win = (part * CPW) / MMA_N, col0 = (part * CPW) % MMA_N; // 128-column key window of the part, first column in it
         unsigned k0[2], k1[2];
-        AccBias bias;
-        if(BIAS)
-        {
-            bias.fill(kAccBias, db.km.two16 & 0xffffu); // two16 = 65536: its low half is the run-time zero
-#pragma unroll
-            for(int a = 0; a < 2; ++a)
-            {
-                const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * WIDE_N + part * CPW;
-#pragma unroll
-                for(int c = 0; c < CPW; c += 32)
-                    tmem_st32_bias(taddr + c, bias);
-            }
-            tmem_wait_st();
-            tc_fence_before();
-            __syncwarp();
-            if(lane == 0)
-            {
-                mbar_arrive(bar_cempty);
-                mbar_arrive(bar_cempty + 8);
-            }
-        }
         for_each_tile(
-            [&] { k0[0] = k0[1] = k1[0] = k1[1] = BIAS ? 0u : kNoKey; },
+            [&] { k0[0] = k0[1] = k1[0] = k1[1] = PACK ? 0u : kNoKey; },
             [&](int, int nt, int j, int it) {
                 const int col_base = j * WIDE_N + win * MMA_N;
                 const int n_valid = nt - col_base; // columns of this key window that exist (may be <= col0: nothing for this warp)
@@ -963,10 +904,11 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                     mbar_wait(bar_cfull + 8 * a, it & 1);
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * WIDE_N + part * CPW;
-                    if(BIAS)
+                    if(PACK)
                     {
-                        Top2Max tm;
-                        drain_tile_max(tm, taddr, max(n_valid, 0), db.km.two16, bias);
+                        Top2MaxS tm;
+                        if(!MMA_DBG(4)) // debug 4: the epilogue only hands the accumulator back
+                            drain_tile_pack(tm, taddr, max(n_valid, 0));
                         tc_fence_before();
                         __syncwarp();
                         if(lane == 0)
@@ -1024,7 +966,7 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                         for(int o = 0; o < NPARTS - 1; ++o)
                         {
                             const unsigned* e = xs + (((a * MMA_M + quarter * 32 + lane) * 3) + o) * 2;
-                            if(BIAS)
+                            if(PACK)
                                 merge2max(k0[a], k1[a], e[0], e[1]);
                             else
                                 merge2(k0[a], k1[a], e[0], e[1]);
@@ -1040,8 +982,8 @@ __global__ void __launch_bounds__(EW * 32 + 64, 1)
                         }
                         else
                         {
-                            // nt >= 2: both exist.  BIAS: the values are 512 - 2 hamming
-                            const int d0 = BIAS ? (int)(512u - k0[a]) >> 1 : (int)(k0[a] >> 16), d1 = BIAS ? (int)(512u - k1[a]) >> 1 : (int)(k1[a] >> 16);
+                            // nt >= 2: both exist.  PACK: the values are dot + 256 = 512 - 2 hamming
+                            const int d0 = PACK ? (int)(512u - k0[a]) >> 1 : (int)(k0[a] >> 16), d1 = PACK ? (int)(512u - k1[a]) >> 1 : (int)(k1[a] >> 16);
                             const bool pass = db.int_ratio ? (10 * d0 < 7 * d1) : ((double)(float)d0 < db.ratio * (double)(float)d1);
                             cnt += (live && pass) ? 1 : 0;
                         }
