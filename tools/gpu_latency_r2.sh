@@ -1,9 +1,10 @@
 #!/bin/bash
+# single-frame path (what the reference's frontend calls: one detect + one match per frame): wall times with and without the
+# latency path, the per-stage timeline inside the captured graph, the breakdown of a call, and warm per-kernel times
 mkdir -p gpurun_out
 timeout 200 python tools/latency.py 2>&1 | tail -1
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-timeout 300 python bench.py --workload dist --steps 10 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
-import sys,json
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['value'], d['ms_per_step'], d.get('e2e',{}).get('value'))"
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none --launch-skip 100 -c 16 --csv --log-file gpurun_out/lat_dist_warm.csv python tools/lat_dist.py > gpurun_out/lat_ncu.log 2>&1
-grep k_dist_tree gpurun_out/lat_dist_warm.csv | head -2 | cut -c1-40,230-
+MSLAM_B200_LATENCY_PATH=0 timeout 200 python tools/latency.py 2>&1 | tail -1
+MSLAM_B200_LAT_TRACE=2 timeout 200 python tools/latency.py 2>&1 | head -12
+timeout 200 python tools/latency_breakdown.py 2>&1 | tail -1
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none --launch-skip 400 -c 40 --csv --log-file gpurun_out/lat_launches_warm.csv python tools/latency.py > gpurun_out/lat_ncu.log 2>&1
+echo "launch list rc=$?"
