@@ -595,6 +595,12 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
     {
     const int rb = 32 * pass + 4 * warp; // first scored row of this thread's group
     unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row 4 * warp + row is a corner
+    // Rows below the level's last scored row (y > h - edge) exist only because tiles have a fixed height: a warp whose four rows
+    // all lie there has nothing to classify, nothing to queue, and nobody reads its part of the score map (the NMS of an owned
+    // position looks at most one row past the last owned row, which is y = h - edge).  Over the eight levels of a VGA frame
+    // that is 9 % of the tile rows.
+    if(L.h - edge - (sy0 + rb) + 1 <= 0) // warp-uniform
+        continue;
     {
         const unsigned t4 = (unsigned)thr * 0x01010101u;
         const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
