@@ -441,7 +441,8 @@ def main():
         e2e_ms = float(tt.item())
     e2e_value = frames_total / (e2e_ms * 1e-3)
     assert int(h_m[3].sum()) > 0
-    h2d = int(B * W * H * 3 + 2 * B * cap * 32 + 2 * B * 4)
+    # frames + the descriptor rows match_batch_begin copies (one strided copy per set, as wide as the fullest pair) + counts
+    h2d = int(B * W * H * 3 + B * 32 * (int(h_cnt[0].max()) + int(h_cnt[1].max())) + 2 * B * 4)
     d2h = int(B * cap * (24 + 32) + 2 * B * 4 + 3 * B * cap * 4 + B * 4)
     # host results must equal the device-resident run's
     assert int(h_m[3].sum()) > 0 and int(h_cnt[cur ^ 1].sum()) >= B * nfeat // 2

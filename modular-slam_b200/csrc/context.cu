@@ -1599,8 +1599,19 @@ int mslam_b200_match_batch_begin(mslam_b200_ctx* ctx, int mode, const uint8_t* f
     const size_t blk = (size_t)n_pairs * capacity;
     // descriptors go in on the copy-in engine and results come out on the copy-out engine, so that neither transfer
     // stalls kernels of a detect batch queued on the context stream around this match
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mfrom, from, blk * 32, cudaMemcpyHostToDevice, s_in));
-    MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_mto, to, blk * 32, cudaMemcpyHostToDevice, s_in));
+    // only the rows that hold descriptors cross the bus: one strided copy per set, as wide as the pair with the most of them
+    // (the counts are host arrays; capacity is typically 30 % above the feature count)
+    int max_from = 0, max_to = 0;
+    for(int i = 0; i < n_pairs; ++i)
+    {
+        max_from = std::max(max_from, std::min(std::max(n_from[i], 0), capacity));
+        max_to = std::max(max_to, std::min(std::max(n_to[i], 0), capacity));
+    }
+    const size_t pitch = (size_t)capacity * 32;
+    if(max_from > 0)
+        MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_mfrom, pitch, from, pitch, (size_t)max_from * 32, (size_t)n_pairs, cudaMemcpyHostToDevice, s_in));
+    if(max_to > 0)
+        MSLAM_CUDA_OK(cudaMemcpy2DAsync(ctx->d_mto, pitch, to, pitch, (size_t)max_to * 32, (size_t)n_pairs, cudaMemcpyHostToDevice, s_in));
     MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nfrom, n_from, n_pairs * sizeof(int), cudaMemcpyHostToDevice, s_in));
     MSLAM_CUDA_OK(cudaMemcpyAsync(ctx->d_nto, n_to, n_pairs * sizeof(int), cudaMemcpyHostToDevice, s_in));
     MSLAM_CUDA_OK(cudaEventRecord(ctx->ev_match_in, s_in));
