@@ -417,7 +417,7 @@ __device__ __forceinline__ void drain_cols(Top2x2& t, uint32_t taddr, int col0, 
 
 // ---------------------------------------------------------------------------------------------------------------
 // descriptors (32 bytes) -> +1 / -1 int8 rows in the canonical core-matrix order described at the top.
-// One thread = one 16-byte K chunk of one descriptor (16 descriptor bits).  Rows >= the set's count are left as they
+// One thread = four 16-byte K chunks of one descriptor (16 descriptor bits each).  Rows >= the set's count are left as they
 // are: they only ever reach accumulator rows that are not stored / columns that the epilogue masks.
 // ---------------------------------------------------------------------------------------------------------------
 struct ExpandSet
@@ -431,22 +431,30 @@ __global__ void __launch_bounds__(256) k_expand_pm1(ExpandSet s0, ExpandSet s1, 
     const ExpandSet s = blockIdx.z ? s1 : s0;
     const int p = blockIdx.y;
     const int n = min(s.counts[p], cap);
-    // (row % 8) fastest, then the K chunk, then the 8-row group: 8 consecutive lanes write one 128-byte core matrix
+    // (row % 8) fastest, then the K chunk, then the 8-row group: 8 consecutive lanes write one 128-byte core matrix.  A thread
+    // takes chunks c, c + 4, c + 8, c + 12 of its row (four independent 16-byte stores; a quarter of the threads of the
+    // one-chunk-per-thread version, which spent its time launching and retiring them)
     const int gid = blockIdx.x * 256 + threadIdx.x;
-    const int row = ((gid >> 7) << 3) | (gid & 7), chunk = (gid >> 3) & 15;
+    const int row = ((gid >> 5) << 3) | (gid & 7), chunk0 = (gid >> 3) & 3;
     if(row >= n)
         return;
-    const unsigned bits = reinterpret_cast<const unsigned short*>(s.desc + ((size_t)p * cap + row) * 32)[chunk];
-    unsigned w[4];
+    const unsigned short* bits16 = reinterpret_cast<const unsigned short*>(s.desc + ((size_t)p * cap + row) * 32);
+    uint8_t* dst = s.out + (size_t)p * cap_pad * ROW_BYTES + (size_t)(row >> 3) * 2048 + (size_t)(row & 7) * 16;
 #pragma unroll
-    for(int i = 0; i < 4; ++i)
+    for(int k = 0; k < 4; ++k)
     {
-        const unsigned nib = (bits >> (4 * i)) & 15u;
-        const unsigned spread = (nib * 0x00204081u) & 0x01010101u; // bit b of the nibble -> byte b, value 0 / 1
-        w[i] = ~(spread * 0xfeu);                                  // 1 -> 0x01 (+1), 0 -> 0xff (-1)
+        const int chunk = chunk0 + 4 * k;
+        const unsigned bits = bits16[chunk];
+        unsigned w[4];
+#pragma unroll
+        for(int i = 0; i < 4; ++i)
+        {
+            const unsigned nib = (bits >> (4 * i)) & 15u;
+            const unsigned spread = (nib * 0x00204081u) & 0x01010101u; // bit b of the nibble -> byte b, value 0 / 1
+            w[i] = ~(spread * 0xfeu);                                  // 1 -> 0x01 (+1), 0 -> 0xff (-1)
+        }
+        *reinterpret_cast<uint4*>(dst + chunk * 128) = make_uint4(w[0], w[1], w[2], w[3]);
     }
-    uint8_t* dst = s.out + (size_t)p * cap_pad * ROW_BYTES + (size_t)gid * 16;
-    *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1233,14 +1241,14 @@ void launch_expand_pm1(cudaStream_t st, const uint8_t* desc, const int* counts, 
                        long long* launches)
 {
     const ExpandSet s{desc, counts, out};
-    dim3 grd(((cap + 7) / 8 * 128 + 255) / 256, n_pairs, 1);
+    dim3 grd(((cap + 7) / 8 * 32 + 255) / 256, n_pairs, 1);
     k_expand_pm1<<<grd, 256, 0, st>>>(s, s, cap, knn_mma_pad(cap));
     ++*launches;
 }
 void launch_expand_pm1_x2(cudaStream_t st, const uint8_t* desc0, const int* counts0, uint8_t* out0, const uint8_t* desc1,
                           const int* counts1, uint8_t* out1, int n_pairs, int cap, long long* launches)
 {
-    dim3 grd(((cap + 7) / 8 * 128 + 255) / 256, n_pairs, 2);
+    dim3 grd(((cap + 7) / 8 * 32 + 255) / 256, n_pairs, 2);
     k_expand_pm1<<<grd, 256, 0, st>>>(ExpandSet{desc0, counts0, out0}, ExpandSet{desc1, counts1, out1}, cap, knn_mma_pad(cap));
     ++*launches;
 }

@@ -139,14 +139,20 @@ __global__ void __launch_bounds__(256) k_merge_keys(const unsigned* __restrict__
     key1[i] = b;
 }
 
-// block-wide exclusive scan of one flag per thread (256 threads); returns the offset, total in *total
-__device__ __forceinline__ int block_scan_flag(bool flag, int* total, int* s_warp /* >= 9 ints */)
+// block-wide exclusive scan of a small count per thread (256 threads); returns the offset, total in *total
+__device__ __forceinline__ int block_scan_count(int cnt, int* total, int* s_warp /* >= 8 ints */)
 {
-    const unsigned bal = __ballot_sync(0xffffffffu, flag);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int within = __popc(bal & ((1u << lane) - 1u));
-    if(lane == 0)
-        s_warp[wid] = __popc(bal);
+    int incl = cnt;
+#pragma unroll
+    for(int o = 1; o < 32; o <<= 1)
+    {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if(lane >= o)
+            incl += t;
+    }
+    if(lane == 31)
+        s_warp[wid] = incl;
     __syncthreads();
     int off = 0, tot = 0;
 #pragma unroll
@@ -158,7 +164,7 @@ __device__ __forceinline__ int block_scan_flag(bool flag, int* total, int* s_war
     }
     __syncthreads();
     *total = tot;
-    return off + within;
+    return off + incl - cnt;
 }
 
 // ratio test + ordered compaction: one CTA per pair, ascending query (= toIndex) order.
@@ -172,27 +178,40 @@ __global__ void __launch_bounds__(256) k_ratio_compact(const unsigned* __restric
     const int p = blockIdx.x;
     const int nq = min(q_counts[p], cap), nt = min(t_counts[p], cap);
     int run = 0;
+    // four consecutive queries per thread: a frame's ~1000 queries are one round of the CTA (one scan, two barriers) instead of four
     if(nt >= 2)
-        for(int base = 0; base < nq; base += 256)
+        for(int base = 0; base < nq; base += 1024)
         {
-            const int q = base + threadIdx.x;
-            bool keep = false;
-            unsigned a = 0;
-            if(q < nq)
+            const int q0 = base + 4 * threadIdx.x;
+            unsigned a[4];
+            bool keep[4];
+            int cnt = 0;
+#pragma unroll
+            for(int j = 0; j < 4; ++j)
             {
-                a = key0[(long long)p * cap + q];
-                const unsigned b = key1[(long long)p * cap + q];
-                keep = (double)(float)(a >> 16) < ratio * (double)(float)(b >> 16);
+                const int q = q0 + j;
+                keep[j] = false;
+                a[j] = 0;
+                if(q < nq)
+                {
+                    a[j] = key0[(long long)p * cap + q];
+                    const unsigned b = key1[(long long)p * cap + q];
+                    keep[j] = (double)(float)(a[j] >> 16) < ratio * (double)(float)(b >> 16);
+                }
+                cnt += keep[j] ? 1 : 0;
             }
             int tot;
-            const int pos = run + block_scan_flag(keep, &tot, s_warp);
-            if(keep)
-            {
-                out_a[(long long)p * cap + pos] = (int)(a & 0xffffu); // fromIndex = trainIdx
-                out_b[(long long)p * cap + pos] = q;                  // toIndex = queryIdx
-                if(out_d)
-                    out_d[(long long)p * cap + pos] = (int)(a >> 16);
-            }
+            int pos = run + block_scan_count(cnt, &tot, s_warp);
+#pragma unroll
+            for(int j = 0; j < 4; ++j)
+                if(keep[j])
+                {
+                    out_a[(long long)p * cap + pos] = (int)(a[j] & 0xffffu); // fromIndex = trainIdx
+                    out_b[(long long)p * cap + pos] = q0 + j;                // toIndex = queryIdx
+                    if(out_d)
+                        out_d[(long long)p * cap + pos] = (int)(a[j] >> 16);
+                    ++pos;
+                }
             run += tot;
         }
     if(threadIdx.x == 0)
@@ -211,26 +230,38 @@ __global__ void __launch_bounds__(256) k_mutual_compact(const unsigned* __restri
     const int nq = min(q_counts[p], cap), nt = min(t_counts[p], cap);
     int run = 0;
     if(nt >= 1)
-        for(int base = 0; base < nq; base += 256)
+        for(int base = 0; base < nq; base += 1024) // four consecutive queries per thread, as k_ratio_compact
         {
-            const int q = base + threadIdx.x;
-            bool keep = false;
-            unsigned a = 0;
-            if(q < nq)
+            const int q0 = base + 4 * threadIdx.x;
+            unsigned a[4];
+            bool keep[4];
+            int cnt = 0;
+#pragma unroll
+            for(int j = 0; j < 4; ++j)
             {
-                a = key0_q[(long long)p * cap + q];
-                const unsigned back = key0_t[(long long)p * cap + (a & 0xffffu)];
-                keep = (int)(back & 0xffffu) == q;
+                const int q = q0 + j;
+                keep[j] = false;
+                a[j] = 0;
+                if(q < nq)
+                {
+                    a[j] = key0_q[(long long)p * cap + q];
+                    const unsigned back = key0_t[(long long)p * cap + (a[j] & 0xffffu)];
+                    keep[j] = (int)(back & 0xffffu) == q;
+                }
+                cnt += keep[j] ? 1 : 0;
             }
             int tot;
-            const int pos = run + block_scan_flag(keep, &tot, s_warp);
-            if(keep)
-            {
-                out_a[(long long)p * cap + pos] = (int)(a & 0xffffu); // trainIdx
-                out_b[(long long)p * cap + pos] = q;                  // queryIdx
-                if(out_d)
-                    out_d[(long long)p * cap + pos] = (int)(a >> 16);
-            }
+            int pos = run + block_scan_count(cnt, &tot, s_warp);
+#pragma unroll
+            for(int j = 0; j < 4; ++j)
+                if(keep[j])
+                {
+                    out_a[(long long)p * cap + pos] = (int)(a[j] & 0xffffu); // trainIdx
+                    out_b[(long long)p * cap + pos] = q0 + j;                // queryIdx
+                    if(out_d)
+                        out_d[(long long)p * cap + pos] = (int)(a[j] >> 16);
+                    ++pos;
+                }
             run += tot;
         }
     if(threadIdx.x == 0)
