@@ -594,10 +594,18 @@ int mslam_b200_create(const mslam_b200_config* cfg_in, mslam_b200_ctx** out_ctx)
         CREATE_OK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
         ctx->own_stream = true;
     }
-    for(int i = 0; i < 2; ++i)
     {
-        CREATE_OK(cudaStreamCreateWithFlags(&ctx->aux[i], cudaStreamNonBlocking));
-        CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
+        // the FAST + selection fork is the long pole of a batch (its kernels are ALU-bound and 40 % of the step): its CTAs go
+        // first, the blur fork fills what they leave.  MSLAM_B200_STREAM_PRIO=0 creates both forks at the default priority.
+        int prio_lo = 0, prio_hi = 0;
+        CREATE_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        const char* e = getenv("MSLAM_B200_STREAM_PRIO");
+        const int mode = e ? atoi(e) : 1; // A/B aid: bit 0 = the FAST fork high, bit 1 = the blur fork high
+        for(int i = 0; i < 2; ++i)
+        {
+            CREATE_OK(cudaStreamCreateWithPriority(&ctx->aux[i], cudaStreamNonBlocking, ((mode >> i) & 1) ? prio_hi : prio_lo));
+            CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
+        }
     }
     for(int i = 0; i < kMaxLevels; ++i)
         CREATE_OK(cudaEventCreateWithFlags(&ctx->ev_level[i], cudaEventDisableTiming));
