@@ -590,21 +590,29 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
     fast_mbar_wait(fast_smem_u32(&s_bar), 0, dbg);
 
     // ---- phase A: classify 4 rows x 4 pixels per thread and pass (32 rows per pass) ----
+    // A tile of the level's last column may hold only a few scored columns (tiles are 128 wide whatever the level's width).  When
+    // the last column that matters lies in the tile's left half, a warp covers TWO row groups of 16 column groups each instead of
+    // one of 32, and the tile takes half the passes (VGA: the last tile columns of levels 2, 3 and 6).
+    const bool narrow = L.w - edge - sx0 < 62; // CTA-uniform: every scored or NMS-halo column has sx <= 61, its ring sx <= 64
+    const int clane = narrow ? (lane & 15) : lane;            // column group of this thread
+    const int rows_per_pass = narrow ? 64 : 32;
 #pragma unroll 1
-    for(int pass = 0; pass < SH / 32; ++pass)
+    for(int pass = 0; pass * rows_per_pass < SH; ++pass)
     {
-    const int rb = 32 * pass + 4 * warp; // first scored row of this thread's group
-    unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row 4 * warp + row is a corner
-    // Rows below the level's last scored row (y > h - edge) exist only because tiles have a fixed height: a warp whose four rows
-    // all lie there has nothing to classify, nothing to queue, and nobody reads its part of the score map (the NMS of an owned
-    // position looks at most one row past the last owned row, which is y = h - edge).  Over the eight levels of a VGA frame
-    // that is 9 % of the tile rows.
-    if(L.h - edge - (sy0 + rb) + 1 <= 0) // warp-uniform
+    const int rb = rows_per_pass * pass + 4 * (narrow ? 2 * warp + (lane >> 4) : warp); // first scored row of this thread's group
+    unsigned flags16 = 0; // bit (4 * row + j): pixel j of the group in row rb + row is a corner
+    // Rows below the level's last scored row (y > h - edge) exist only because tiles have a fixed height: a warp whose rows
+    // all lie there (or past the tile) has nothing to classify, nothing to queue, and nobody reads its part of the score map (the
+    // NMS of an owned position looks at most one row past the last owned row, which is y = h - edge).  Over the eight levels of
+    // a VGA frame that is 9 % of the tile rows.
+    const bool rows_live = rb < SH && L.h - edge - (sy0 + rb) + 1 > 0;
+    if(!__any_sync(0xffffffffu, rows_live))
         continue;
+    if(rows_live)
     {
         const unsigned t4 = (unsigned)thr * 0x01010101u;
         const unsigned one = (unsigned)P.one, mone = (unsigned)P.minus_one;
-        const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[rb][0]) + lane + (xo >> 2);
+        const unsigned* wbase = reinterpret_cast<const unsigned*>(&s_px[rb][0]) + clane + (xo >> 2);
         unsigned wm[10], w0[10], wp[10]; // staged rows 4 * warp .. 4 * warp + 9, words lane, lane + 1, lane + 2
 #pragma unroll
         for(int r = 0; r < 10; ++r)
@@ -641,16 +649,16 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
             // "the arc is brighter than the centre" goes into the score map as 0 / 1 per position -- one word store per row,
             // which also is the map's initialisation (every position of the tile is classified by exactly one thread);
             // phase B reads the flag of a corner before it overwrites it with the score (>= fast_thr - 1 > 1)
-            reinterpret_cast<unsigned*>(&s_sc[rb + row][0])[lane] = (fb >> 7) & 0x01010101u;
+            reinterpret_cast<unsigned*>(&s_sc[rb + row][0])[clane] = (fb >> 7) & 0x01010101u;
         }
     }
     // only positions that can matter: inside the image interior +- 1 (the NMS halo):
     //   edge - 1 <= x <= w - edge (a nibble, the same for the 4 rows) and y <= h - edge (y >= edge - 1 by construction)
     {
-        const int x = sx0 + 4 * lane;
+        const int x = sx0 + 4 * clane;
         const int jlo = max(0, edge - 1 - x), jhi = min(3, L.w - edge - x);
         const unsigned nib = jlo <= jhi ? ((0xfu >> (3 - jhi)) & (0xfu << jlo) & 0xfu) : 0u;
-        const int nrows = min(4, max(0, L.h - edge - (sy0 + rb) + 1));
+        const int nrows = rows_live ? min(4, max(0, L.h - edge - (sy0 + rb) + 1)) : 0;
         flags16 &= (nib * 0x1111u) & ((1u << (4 * nrows)) - 1u);
     }
     // warp-aggregated append to the CTA's corner queue
@@ -672,7 +680,7 @@ __global__ void __launch_bounds__(256, MSLAM_FAST_CTAS) k_fast(const __grid_cons
         // (one FLO), entry = position of the group | (bit & 3) | (bit >> 2) << 7 -- the group's position has zeros in those four
         // bits (4 * lane and a row that is a multiple of 4), and bit * 33 puts both fields in place with one IMAD.
         unsigned short* q = s_q + (wbase_q + incl - cnt);
-        const unsigned ebase = (unsigned)(rb * FS_SW + 4 * lane);
+        const unsigned ebase = (unsigned)(rb * FS_SW + 4 * clane);
         unsigned f = flags16;
         while(f)
         {
