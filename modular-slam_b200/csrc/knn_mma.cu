@@ -207,11 +207,6 @@ struct Top2x2
         k0 = lo;
         a0 = a1 = 0xffffffffu;
     }
-    __device__ __forceinline__ void push(unsigned pk)
-    {
-        k1 = __vminu2(k1, __vmaxu2(k0, pk));
-        k0 = __vminu2(k0, pk);
-    }
     // two new values at once: 5 packed min / max operations instead of 6 (second smallest of {k0, k1, a, b} =
     // min3(k1, max(k0, min(a, b)), max(a, b)); VIMNMX3.U16x2 is a native instruction)
     __device__ __forceinline__ void push2(unsigned a, unsigned b)
